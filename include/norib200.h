@@ -1,0 +1,211 @@
+/* norib200.h — C ABI of the B200-native path-tracing backend (libnorib200.so).
+ *
+ * This is the drop-in boundary for the reference's GPU side-car. It replaces the call shape of
+ * `OptixState` (reference include/nori/optix/OptixState.h:88-109: preRender / renderSubframe /
+ * clear) and of the flatten hooks that feed it (getOptixMaterialData bsdf.h:122,
+ * getOptixEmitterData emitter.h:159, getOptixData camera.h:86, getOptixBuildInput shape.h:194-201,
+ * gathered in OptixState::preRender, OptixState.render.cpp:19-85). The caller is
+ * RenderThread::renderThreadOptix (src/utils/render.cpp:462-574).
+ *
+ * Conventions: plain C, plain pointers and sizes, no C++/torch types. Every entry returns an
+ * int (NB_OK == 0, negative NB_E_*), never throws or aborts across the boundary;
+ * nb_last_error() returns the text of the last failure on that context (or the global one for
+ * nb_create). All `const T*` inputs are HOST pointers copied during the call (the caller keeps
+ * ownership) unless the name says `_device`.
+ */
+#ifndef NORIB200_H
+#define NORIB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB_ABI_VERSION 1
+
+enum {
+    NB_OK = 0,
+    NB_E_INVALID = -1,      /* bad argument / inconsistent scene description */
+    NB_E_CUDA = -2,         /* CUDA runtime error (text in nb_last_error) */
+    NB_E_NOMEM = -3,
+    NB_E_STATE = -4,        /* call out of order (e.g. render before upload) */
+    NB_E_UNSUPPORTED = -5,  /* a plugin tag this backend has no kernel for: caller renders on CPU
+                               (mirrors preRender() == false, render.cpp:488-489) */
+    NB_E_NO_DEVICE = -6     /* no CUDA device: there is NO CPU fallback in this library */
+};
+
+/* ---- plugin tags (the flatten hooks emit these) -------------------------------------------- */
+enum { NB_SHAPE_MESH = 0, NB_SHAPE_SPHERE = 1 };
+enum { NB_BSDF_DIFFUSE = 0, NB_BSDF_MIRROR = 1, NB_BSDF_DIELECTRIC = 2, NB_BSDF_MICROFACET = 3,
+       NB_BSDF_NONE = 0xff };
+enum { NB_EMITTER_AREA = 0, NB_EMITTER_POINT = 1, NB_EMITTER_ENVMAP = 2 };
+enum { NB_INTEGRATOR_PATH_MIS = 0, NB_INTEGRATOR_PATH_MATS = 1, NB_INTEGRATOR_DIRECT_EMS = 2,
+       NB_INTEGRATOR_DIRECT_MATS = 3, NB_INTEGRATOR_DIRECT_MIS = 4, NB_INTEGRATOR_NORMALS = 5,
+       NB_INTEGRATOR_DIRECT = 6, NB_INTEGRATOR_AV = 7 };
+enum { NB_SHAPE_HAS_NORMALS = 1u, NB_SHAPE_HAS_UVS = 2u };
+
+/* ---- scene records ------------------------------------------------------------------------- */
+
+/* One Shape (src/shapes/mesh.cpp, sphere.cpp; include/nori/shape.h:104-237). Primitive numbering
+ * is the BVH's: shapes concatenated in scene order (BVH::addShape, bvh.cpp:308-317). */
+typedef struct nb_shape {
+    uint32_t type;           /* NB_SHAPE_* */
+    uint32_t prim_count;     /* triangles, or 1 for a sphere */
+    uint32_t vertex_offset;  /* first vertex of this mesh in positions/normals/uvs */
+    uint32_t vertex_count;
+    uint32_t face_offset;    /* first triangle of this mesh in faces (3 u32 each, mesh-local ids) */
+    uint32_t flags;          /* NB_SHAPE_HAS_* */
+    int32_t  bsdf;           /* index into bsdfs, -1 = none (medium interface) */
+    int32_t  emitter;        /* index into emitters, -1 = not a light */
+    int32_t  medium;         /* reserved (volume path), -1 */
+    uint32_t cdf_offset;     /* first of prim_count+1 floats in area_cdf (DiscretePDF::m_cdf) */
+    float    pdf_norm;       /* DiscretePDF::getNormalization() = 1/total area (mesh.cpp:70) */
+    float    radius;         /* sphere */
+    float    center[3];      /* sphere */
+    uint32_t pad;
+} nb_shape;                  /* 64 bytes */
+
+/* BSDF::getOptixMaterialData replacement (bsdf/diffuse.cpp, mirror.cpp, dielectric.cpp,
+ * microfacet.cpp). */
+typedef struct nb_bsdf {
+    uint32_t type;           /* NB_BSDF_* */
+    float    albedo[3];      /* diffuse albedo / microfacet kd */
+    float    alpha;          /* microfacet roughness */
+    float    int_ior, ext_ior;
+    float    ks;             /* microfacet: 1 - max(kd) (microfacet.cpp:52) */
+} nb_bsdf;                   /* 32 bytes */
+
+/* Emitter::getOptixEmitterData replacement (emitters/arealight.cpp, pointlight.cpp,
+ * environmentmap.cpp). */
+typedef struct nb_emitter {
+    uint32_t type;           /* NB_EMITTER_* */
+    int32_t  shape;          /* area light: owning shape */
+    float    radiance[3];    /* area: radiance; point: power/(4 pi) (pointlight.cpp:44) */
+    float    position[3];    /* point light */
+} nb_emitter;                /* 32 bytes */
+
+/* Camera::getOptixData replacement (cameras/perspective.cpp:48-141). Matrices are row-major
+ * 4x4 as Eigen prints them (element [r*4+c]). */
+typedef struct nb_camera {
+    float    sample_to_camera[16];
+    float    camera_to_world[16];
+    float    inv_output_size[2];
+    float    near_clip, far_clip;
+    float    lens_radius, focal_distance;
+    uint32_t width, height;
+} nb_camera;                 /* 160 bytes */
+
+/* BVHNode of the reference (include/nori/bvh.h:127-164), bit for bit: word0 bit0 = leaf flag,
+ * bits 1..31 = leaf size | split axis; word1 = leaf start | right child; then bbox min, max. */
+typedef struct nb_bvh_node {
+    uint32_t word0, word1;
+    float    bmin[3], bmax[3];
+} nb_bvh_node;               /* 32 bytes */
+
+typedef struct nb_scene_desc {
+    uint32_t n_shapes;    const nb_shape   *shapes;
+    uint64_t n_vertices;  const float      *positions;   /* 3 per vertex, world space */
+                          const float      *normals;     /* 3 per vertex or NULL */
+                          const float      *uvs;         /* 2 per vertex or NULL */
+                          const float      *tangents;    /* 3 per vertex or NULL (Mesh::m_T)  */
+                          const float      *bitangents;  /* 3 per vertex or NULL (Mesh::m_BT) */
+    uint64_t n_faces;     const uint32_t   *faces;       /* 3 per triangle */
+    uint32_t n_bsdfs;     const nb_bsdf    *bsdfs;
+    uint32_t n_emitters;  const nb_emitter *emitters;
+                          const float      *emitter_cdf; /* n_emitters+1 (scene.cpp:180-184) */
+    uint64_t n_area_cdf;  const float      *area_cdf;
+    nb_camera camera;
+} nb_scene_desc;
+
+/* nb_build_bvh(mode = NB_BVH_IMPORT): the caller's own arrays (BVH::m_nodes / m_indices after
+ * Scene::update, scene.cpp:187-194). Same tree, same visiting order => bit-identical hits. */
+enum { NB_BVH_IMPORT = 0 };
+typedef struct nb_bvh_import {
+    uint32_t n_nodes;    const nb_bvh_node *nodes;
+    uint32_t n_indices;  const uint32_t    *indices;    /* global primitive ids, leaf order */
+} nb_bvh_import;
+
+/* ---- rays (parity entry) ------------------------------------------------------------------- */
+typedef struct nb_ray { float o[3], d[3], mint, maxt; } nb_ray;      /* 32 bytes, Ray3f fields */
+typedef struct nb_hit {
+    float   t, u, v;     /* as Shape::rayIntersect returns them (before setHitInformation) */
+    int32_t shape;       /* index into shapes, -1 = miss */
+    int32_t prim;        /* primitive index local to the shape */
+    uint32_t any_hit;    /* result of the shadow-ray query on the same ray (any_hit mode) */
+} nb_hit;                /* 24 bytes */
+
+/* ---- rendering ----------------------------------------------------------------------------- */
+#define NB_FILTER_RESOLUTION 32   /* NORI_FILTER_RESOLUTION, include/nori/rfilter.h:25 */
+
+typedef struct nb_render_params {
+    uint32_t integrator;                       /* NB_INTEGRATOR_* */
+    float    filter_radius;                    /* ReconstructionFilter::getRadius() */
+    float    filter_table[NB_FILTER_RESOLUTION + 1]; /* ImageBlock::m_filter (block.cpp:58-64) */
+    uint64_t seed;                             /* mixed into every per-pixel pcg32 stream */
+    uint32_t pool_paths;                       /* path slots in flight; 0 = library default */
+    uint32_t max_depth;                        /* 0 = unbounded, as the reference */
+    uint32_t reserved[4];
+} nb_render_params;
+
+typedef struct nb_counters {
+    uint64_t samples;        /* camera paths started (renderBlock iterations, render.cpp:436) */
+    uint64_t rays_closest;   /* BVH::rayIntersect(shadowRay=false) queries, probe/main deduped */
+    uint64_t rays_any;       /* BVH::rayIntersect(shadowRay=true) queries */
+    uint64_t iterations;     /* wavefront iterations launched */
+    uint64_t kernel_launches;
+    uint64_t invalid_samples;/* dropped by the isValid() rule of ImageBlock::put (block.cpp:94) */
+    double   device_ms;      /* CUDA-event time of the last nb_sync()ed render span */
+    double   trace_ms, shade_ms; /* filled when profiling timers are on (nb_set_option) */
+} nb_counters;
+
+typedef struct nb_ctx nb_ctx;
+
+int  nb_abi_version(void);
+/* sizeof() of the records above as this build sees them; which = 0 shape, 1 bsdf, 2 emitter,
+ * 3 camera, 4 bvh_node, 5 scene_desc, 6 ray, 7 hit, 8 render_params, 9 counters */
+int  nb_abi_sizeof(int which);
+
+int  nb_create(int device, nb_ctx **out);       /* fails with NB_E_NO_DEVICE when there is none */
+int  nb_destroy(nb_ctx *ctx);
+const char *nb_last_error(const nb_ctx *ctx);   /* ctx may be NULL: error of the last nb_create */
+
+/* OptixState::preRender (OptixState.render.cpp:19-85): flatten + upload. */
+int  nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *scene);
+int  nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *import);
+
+/* Parity entry: Scene::rayIntersect (include/nori/scene.h:114-138) over n host rays.
+ * any_hit = 0: closest hit per ray. any_hit = 1: also runs the shadow-ray query and fills
+ * nb_hit.any_hit. */
+int  nb_trace_rays(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_hit, nb_hit *out);
+/* Same on rays already resident on the device (timing the kernel alone); out_device gets
+ * n float4 {t,u,v,bits(prim slot)}; returns the kernel's CUDA-event time. */
+int  nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int any_hit,
+                          void *out_device, int repeats, float *ms_per_launch);
+
+/* RenderThread::renderThreadOptix loop (render.cpp:462-574). */
+int  nb_render_begin(nb_ctx *ctx, const nb_render_params *params);  /* allocates + clears film */
+/* OptixState::renderSubframe (OptixState.cpp:485-510): samples [first, first+count) of every
+ * pixel; sample s of pixel p always uses the same random stream, whatever the launch split.
+ * Only samples with (s % sample_stride) == sample_offset are rendered (multi-GPU sample slices;
+ * 1,0 = all). Asynchronous: returns once the work is queued. */
+int  nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count,
+                        uint32_t sample_stride, uint32_t sample_offset);
+int  nb_sync(nb_ctx *ctx);
+int  nb_film_clear(nb_ctx *ctx);
+/* Film geometry: rows = H + 2b, cols = W + 2b, b = ceil(radius - 0.5) (block.cpp:57,73). */
+int  nb_film_shape(nb_ctx *ctx, uint32_t *rows, uint32_t *cols, uint32_t *border);
+/* Copies the accumulators into caller memory laid out like ImageBlock's storage (row-major
+ * Color4f = {sum w*r, sum w*g, sum w*b, sum w}, block.h:49). normalize != 0: instead writes
+ * H x W x 3 floats = ImageBlock::toBitmap() (block.cpp:76-82). */
+int  nb_film_download(nb_ctx *ctx, float *out, int normalize);
+/* Device address of the accumulators (rows*cols*4 floats) for the NCCL film reduce. */
+int  nb_film_device_ptr(nb_ctx *ctx, void **ptr, uint64_t *n_floats);
+int  nb_get_counters(nb_ctx *ctx, nb_counters *out);
+/* options: "profile" (per-kernel event timers), "sort" (material-sorted shading queues) */
+int  nb_set_option(nb_ctx *ctx, const char *name, int64_t value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NORIB200_H */

@@ -1,0 +1,286 @@
+"""nori-b200: ctypes binding of the C ABI in include/norib200.h (libnorib200.so).
+
+The library is the product; this module only loads it, mirrors its records and moves numpy
+buffers across the boundary. There is no Python or CPU implementation of the path behind it: if
+the shared library is missing, or no CUDA device is present, calls fail loudly.
+
+Import with ``importlib.import_module("optix-renderer_b200")`` (the directory name carries a
+hyphen) or through ``norib200.py`` at the repo root.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnorib200.so")
+HOST_LIB_PATH = os.path.join(HERE, "libnorib200_host.so")
+
+NB_OK, NB_E_INVALID, NB_E_CUDA, NB_E_NOMEM, NB_E_STATE, NB_E_UNSUPPORTED, NB_E_NO_DEVICE = 0, -1, -2, -3, -4, -5, -6
+SHAPE_MESH, SHAPE_SPHERE = 0, 1
+BSDF_DIFFUSE, BSDF_MIRROR, BSDF_DIELECTRIC, BSDF_MICROFACET = 0, 1, 2, 3
+EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP = 0, 1, 2
+INTEGRATORS = {"path_mis": 0, "path_mats": 1, "direct_ems": 2, "direct_mats": 3, "direct_mis": 4,
+               "normals": 5, "direct": 6, "av": 7}
+FILTER_RESOLUTION = 32
+
+# numpy mirrors of the records (field order and padding as in the header)
+shape_dtype = np.dtype([("type", "<u4"), ("prim_count", "<u4"), ("vertex_offset", "<u4"), ("vertex_count", "<u4"),
+                        ("face_offset", "<u4"), ("flags", "<u4"), ("bsdf", "<i4"), ("emitter", "<i4"),
+                        ("medium", "<i4"), ("cdf_offset", "<u4"), ("pdf_norm", "<f4"), ("radius", "<f4"),
+                        ("center", "<f4", 3), ("pad", "<u4")])
+bsdf_dtype = np.dtype([("type", "<u4"), ("albedo", "<f4", 3), ("alpha", "<f4"), ("int_ior", "<f4"),
+                       ("ext_ior", "<f4"), ("ks", "<f4")])
+emitter_dtype = np.dtype([("type", "<u4"), ("shape", "<i4"), ("radiance", "<f4", 3), ("position", "<f4", 3)])
+camera_dtype = np.dtype([("sample_to_camera", "<f4", 16), ("camera_to_world", "<f4", 16),
+                         ("inv_output_size", "<f4", 2), ("near_clip", "<f4"), ("far_clip", "<f4"),
+                         ("lens_radius", "<f4"), ("focal_distance", "<f4"), ("width", "<u4"), ("height", "<u4")])
+bvh_node_dtype = np.dtype([("word0", "<u4"), ("word1", "<u4"), ("bmin", "<f4", 3), ("bmax", "<f4", 3)])
+ray_dtype = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("mint", "<f4"), ("maxt", "<f4")])
+hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("shape", "<i4"), ("prim", "<i4"), ("any_hit", "<u4")])
+render_params_dtype = np.dtype([("integrator", "<u4"), ("filter_radius", "<f4"),
+                                ("filter_table", "<f4", FILTER_RESOLUTION + 1), ("pad0", "<u4"), ("seed", "<u8"),
+                                ("pool_paths", "<u4"), ("max_depth", "<u4"), ("reserved", "<u4", 4)])
+SECTION_DTYPES = {"shapes": shape_dtype, "bsdfs": bsdf_dtype, "emitters": emitter_dtype, "camera": camera_dtype,
+                  "bvh_nodes": bvh_node_dtype, "render": render_params_dtype}
+
+
+class Camera(C.Structure):
+    _fields_ = [("sample_to_camera", C.c_float * 16), ("camera_to_world", C.c_float * 16),
+                ("inv_output_size", C.c_float * 2), ("near_clip", C.c_float), ("far_clip", C.c_float),
+                ("lens_radius", C.c_float), ("focal_distance", C.c_float), ("width", C.c_uint32), ("height", C.c_uint32)]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("n_shapes", C.c_uint32), ("shapes", C.c_void_p),
+                ("n_vertices", C.c_uint64), ("positions", C.c_void_p), ("normals", C.c_void_p), ("uvs", C.c_void_p),
+                ("tangents", C.c_void_p), ("bitangents", C.c_void_p),
+                ("n_faces", C.c_uint64), ("faces", C.c_void_p),
+                ("n_bsdfs", C.c_uint32), ("bsdfs", C.c_void_p),
+                ("n_emitters", C.c_uint32), ("emitters", C.c_void_p), ("emitter_cdf", C.c_void_p),
+                ("n_area_cdf", C.c_uint64), ("area_cdf", C.c_void_p),
+                ("camera", Camera)]
+
+
+class BvhImport(C.Structure):
+    _fields_ = [("n_nodes", C.c_uint32), ("nodes", C.c_void_p), ("n_indices", C.c_uint32), ("indices", C.c_void_p)]
+
+
+class Counters(C.Structure):
+    _fields_ = [("samples", C.c_uint64), ("rays_closest", C.c_uint64), ("rays_any", C.c_uint64),
+                ("iterations", C.c_uint64), ("kernel_launches", C.c_uint64), ("invalid_samples", C.c_uint64),
+                ("device_ms", C.c_double), ("trace_ms", C.c_double), ("shade_ms", C.c_double)]
+
+
+EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",
+           "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
+           "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
+           "nb_get_counters", "nb_set_option"]
+
+_lib = None
+
+
+class NbError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__("norib200 error %d: %s" % (code, text))
+        self.code = code
+
+
+def load_library(path=None):
+    """dlopen libnorib200.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise FileNotFoundError("%s is not built: run `python optix-renderer_b200/build.py` (there is no "
+                                "CPU or Python fallback for the render path)" % path)
+    lib = C.CDLL(path)
+    lib.nb_last_error.restype = C.c_char_p
+    lib.nb_last_error.argtypes = [C.c_void_p]
+    lib.nb_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.nb_destroy.argtypes = [C.c_void_p]
+    lib.nb_upload_scene.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
+    lib.nb_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(BvhImport)]
+    lib.nb_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+    lib.nb_trace_rays_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_float)]
+    lib.nb_render_begin.argtypes = [C.c_void_p, C.c_void_p]
+    lib.nb_render_subframe.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+    lib.nb_sync.argtypes = [C.c_void_p]
+    lib.nb_film_clear.argtypes = [C.c_void_p]
+    lib.nb_film_shape.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    lib.nb_film_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    lib.nb_film_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.nb_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
+    lib.nb_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
+    if path == LIB_PATH:
+        _lib = lib
+    return lib
+
+
+# ---- .nbs container (include/nb_scene_file.h) ---------------------------------------------------
+NBS_MAGIC = 0x3153424E
+_sec_dtype = np.dtype([("name", "S16"), ("elem_size", "<u4"), ("reserved", "<u4"), ("count", "<u8"), ("offset", "<u8")])
+
+
+def read_nbs(path):
+    """Returns {section name: numpy array}. Record sections come back as structured arrays."""
+    raw = np.fromfile(path, dtype=np.uint8)
+    magic, n = np.frombuffer(raw[:8].tobytes(), dtype="<u4")
+    if magic != NBS_MAGIC:
+        raise ValueError("%s: not an .nbs file" % path)
+    table = np.frombuffer(raw[8:8 + 40 * int(n)].tobytes(), dtype=_sec_dtype)
+    out = {}
+    for sec in table:
+        name = sec["name"].decode().rstrip("\0")
+        a, b = int(sec["offset"]), int(sec["offset"]) + int(sec["count"]) * int(sec["elem_size"])
+        buf = raw[a:b].tobytes()
+        if name in SECTION_DTYPES:
+            dt = SECTION_DTYPES[name]
+            assert dt.itemsize == int(sec["elem_size"]), (name, dt.itemsize, int(sec["elem_size"]))
+            out[name] = np.frombuffer(buf, dtype=dt).copy()
+        elif name in ("faces", "bvh_indices", "spp"):
+            out[name] = np.frombuffer(buf, dtype="<u4").copy()
+        else:
+            out[name] = np.frombuffer(buf, dtype="<f4").copy()
+    return out
+
+
+def write_nbs(path, sections):
+    names = list(sections)
+    arrays = [np.ascontiguousarray(sections[k]) for k in names]
+    table = np.zeros(len(names), dtype=_sec_dtype)
+    off = 8 + 40 * len(names)
+    for i, (k, a) in enumerate(zip(names, arrays)):
+        off = (off + 15) & ~15
+        table[i] = (k.encode(), a.dtype.itemsize, 0, a.size, off)
+        off += a.nbytes
+    with open(path, "wb") as f:
+        f.write(np.array([NBS_MAGIC, len(names)], dtype="<u4").tobytes())
+        f.write(table.tobytes())
+        for i, a in enumerate(arrays):
+            f.write(b"\0" * (int(table[i]["offset"]) - f.tell()))
+            f.write(a.tobytes())
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+class Context:
+    """One nb_ctx: a device, its uploaded scene and (optionally) a render in progress."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        self.handle = C.c_void_p()
+        rc = self.lib.nb_create(device, C.byref(self.handle))
+        if rc != NB_OK:
+            raise NbError(rc, self.lib.nb_last_error(None).decode())
+        self._keep = []
+
+    def _check(self, rc):
+        if rc != NB_OK:
+            raise NbError(rc, self.lib.nb_last_error(self.handle).decode())
+
+    def close(self):
+        if self.handle:
+            self.lib.nb_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def upload_scene(self, s):
+        """s: dict of sections as read_nbs returns them (bvh_* used by build_bvh)."""
+        d = SceneDesc()
+        keep = {k: np.ascontiguousarray(v) for k, v in s.items()}
+        d.n_shapes = len(keep["shapes"]); d.shapes = _ptr(keep["shapes"])
+        d.n_vertices = keep["positions"].size // 3; d.positions = _ptr(keep["positions"])
+        d.normals = _ptr(keep.get("normals")); d.uvs = _ptr(keep.get("uvs"))
+        d.tangents = _ptr(keep.get("tangents")); d.bitangents = _ptr(keep.get("bitangents"))
+        d.n_faces = keep["faces"].size // 3; d.faces = _ptr(keep["faces"])
+        bs = keep.get("bsdfs"); d.n_bsdfs = 0 if bs is None else len(bs); d.bsdfs = _ptr(bs)
+        em = keep.get("emitters"); d.n_emitters = 0 if em is None else len(em); d.emitters = _ptr(em)
+        d.emitter_cdf = _ptr(keep.get("emitter_cdf")) if d.n_emitters else None
+        ac = keep.get("area_cdf"); d.n_area_cdf = 0 if ac is None else ac.size; d.area_cdf = _ptr(ac)
+        if "camera" in keep:
+            C.memmove(C.byref(d.camera), keep["camera"].ctypes.data, C.sizeof(Camera))
+        self._check(self.lib.nb_upload_scene(self.handle, C.byref(d)))
+
+    def build_bvh(self, nodes, indices):
+        nodes = np.ascontiguousarray(nodes); indices = np.ascontiguousarray(indices, dtype="<u4")
+        imp = BvhImport(len(nodes), _ptr(nodes), len(indices), _ptr(indices))
+        self._check(self.lib.nb_build_bvh(self.handle, 0, C.byref(imp)))
+
+    def load(self, s):
+        self.upload_scene(s)
+        self.build_bvh(s["bvh_nodes"], s["bvh_indices"])
+
+    def trace_rays(self, rays, any_hit=False):
+        """rays: (n, 8) float32 [o, d, mint, maxt] or ray_dtype; returns hit_dtype array."""
+        rays = np.ascontiguousarray(rays)
+        n = rays.size * rays.dtype.itemsize // 32
+        out = np.zeros(n, dtype=hit_dtype)
+        self._check(self.lib.nb_trace_rays(self.handle, _ptr(rays), n, int(any_hit), _ptr(out)))
+        return out
+
+    def trace_rays_device(self, rays_ptr, n, out_ptr, any_hit=False, repeats=1):
+        ms = C.c_float()
+        self._check(self.lib.nb_trace_rays_device(self.handle, C.c_void_p(rays_ptr), n, int(any_hit),
+                                                  C.c_void_p(out_ptr), repeats, C.byref(ms)))
+        return ms.value
+
+    def render_begin(self, params):
+        params = np.ascontiguousarray(params)
+        assert params.dtype == render_params_dtype
+        self._check(self.lib.nb_render_begin(self.handle, _ptr(params)))
+
+    def render_subframe(self, first, count, stride=1, offset=0):
+        self._check(self.lib.nb_render_subframe(self.handle, first, count, stride, offset))
+
+    def sync(self):
+        self._check(self.lib.nb_sync(self.handle))
+
+    def film_clear(self):
+        self._check(self.lib.nb_film_clear(self.handle))
+
+    def film_shape(self):
+        r, c, b = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        self._check(self.lib.nb_film_shape(self.handle, C.byref(r), C.byref(c), C.byref(b)))
+        return r.value, c.value, b.value
+
+    def film_download(self, normalize=True, out=None):
+        rows, cols, b = self.film_shape()
+        shape = (rows - 2 * b, cols - 2 * b, 3) if normalize else (rows, cols, 4)
+        if out is None:
+            out = np.empty(shape, dtype=np.float32)
+        self._check(self.lib.nb_film_download(self.handle, _ptr(out), int(normalize)))
+        return out
+
+    def film_device_ptr(self):
+        p, n = C.c_void_p(), C.c_uint64()
+        self._check(self.lib.nb_film_device_ptr(self.handle, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def counters(self):
+        c = Counters()
+        self._check(self.lib.nb_get_counters(self.handle, C.byref(c)))
+        return {k: getattr(c, k) for k, _ in Counters._fields_}
+
+    def set_option(self, name, value):
+        self._check(self.lib.nb_set_option(self.handle, name.encode(), int(value)))
+
+
+def make_render_params(scene, integrator="path_mis", seed=0, pool_paths=0, max_depth=0):
+    """nb_render_params from a scene dict's "render" section (filter table) + overrides."""
+    p = np.zeros(1, dtype=render_params_dtype)
+    if "render" in scene:
+        p[0] = scene["render"][0]
+    p["integrator"] = INTEGRATORS[integrator] if isinstance(integrator, str) else int(integrator)
+    p["seed"] = seed
+    p["pool_paths"] = pool_paths
+    p["max_depth"] = max_depth
+    return p

@@ -1,0 +1,164 @@
+/* nb_api.cu — the C ABI of include/norib200.h: context, scene upload, BVH import, parity
+ * trace entry. Rendering entries live in nb_render.cu. No CPU fallback anywhere: without a CUDA
+ * device nb_create fails with NB_E_NO_DEVICE. */
+#include "nb_internal.h"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+static thread_local std::string g_create_error;
+
+int nb_fail(nb_ctx *ctx, int code, const char *fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->error = buf; else g_create_error = buf;
+    return code;
+}
+
+template <typename T>
+static int nb_upload(nb_ctx *ctx, std::vector<void *> &owner, const T *host, size_t count, const T **dev) {
+    *dev = nullptr;
+    if (count == 0 || host == nullptr) return NB_OK;
+    void *p = nullptr;
+    NB_CUDA(ctx, cudaMalloc(&p, count * sizeof(T)));
+    owner.push_back(p);
+    NB_CUDA(ctx, cudaMemcpyAsync(p, host, count * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *dev = (const T *) p;
+    return NB_OK;
+}
+
+static void nb_free_list(std::vector<void *> &v) {
+    for (void *p : v) cudaFree(p);
+    v.clear();
+}
+
+extern "C" {
+
+int nb_abi_version(void) { return NB_ABI_VERSION; }
+
+int nb_abi_sizeof(int which) {
+    switch (which) {
+        case 0: return (int) sizeof(nb_shape);
+        case 1: return (int) sizeof(nb_bsdf);
+        case 2: return (int) sizeof(nb_emitter);
+        case 3: return (int) sizeof(nb_camera);
+        case 4: return (int) sizeof(nb_bvh_node);
+        case 5: return (int) sizeof(nb_scene_desc);
+        case 6: return (int) sizeof(nb_ray);
+        case 7: return (int) sizeof(nb_hit);
+        case 8: return (int) sizeof(nb_render_params);
+        case 9: return (int) sizeof(nb_counters);
+        default: return -1;
+    }
+}
+
+const char *nb_last_error(const nb_ctx *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int nb_create(int device, nb_ctx **out) {
+    if (!out) return nb_fail(nullptr, NB_E_INVALID, "nb_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return nb_fail(nullptr, NB_E_NO_DEVICE, "nb_create: no CUDA device (%s); this backend has no CPU fallback",
+                       e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    if (device < 0 || device >= n) return nb_fail(nullptr, NB_E_INVALID, "nb_create: device %d out of range [0,%d)", device, n);
+    nb_ctx *ctx = new nb_ctx();
+    ctx->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        delete ctx;
+        return nb_fail(nullptr, NB_E_CUDA, "nb_create: %s", cudaGetErrorString(e));
+    }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    *out = ctx;
+    return NB_OK;
+}
+
+int nb_destroy(nb_ctx *ctx) {
+    if (!ctx) return NB_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    nb_render_free(ctx);
+    nb_free_list(ctx->scene_allocs);
+    nb_free_list(ctx->bvh_allocs);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return NB_OK;
+}
+
+int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
+    if (!ctx || !s) return nb_fail(ctx, NB_E_INVALID, "nb_upload_scene: NULL argument");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (s->n_shapes == 0 || !s->shapes) return nb_fail(ctx, NB_E_INVALID, "nb_upload_scene: scene has no shapes");
+    /* validate before touching the device */
+    uint64_t prims = 0;
+    for (uint32_t i = 0; i < s->n_shapes; ++i) {
+        const nb_shape &sh = s->shapes[i];
+        if (sh.type == NB_SHAPE_MESH) {
+            if ((uint64_t) sh.vertex_offset + sh.vertex_count > s->n_vertices || (uint64_t) sh.face_offset + sh.prim_count > s->n_faces)
+                return nb_fail(ctx, NB_E_INVALID, "shape %u: vertex/face range outside the arrays", i);
+            for (uint32_t f = 0; f < sh.prim_count * 3u; ++f)
+                if (s->faces[(size_t) sh.face_offset * 3 + f] >= sh.vertex_count)
+                    return nb_fail(ctx, NB_E_INVALID, "shape %u: face index out of range", i);
+            if ((sh.flags & NB_SHAPE_HAS_NORMALS) && !s->normals) return nb_fail(ctx, NB_E_INVALID, "shape %u: normals flagged but absent", i);
+            if ((sh.flags & NB_SHAPE_HAS_UVS) && !s->uvs) return nb_fail(ctx, NB_E_INVALID, "shape %u: uvs flagged but absent", i);
+            if (sh.emitter >= 0 && (uint64_t) sh.cdf_offset + sh.prim_count + 1 > s->n_area_cdf)
+                return nb_fail(ctx, NB_E_INVALID, "shape %u: area CDF range outside the array", i);
+        } else if (sh.type == NB_SHAPE_SPHERE) {
+            if (sh.prim_count != 1) return nb_fail(ctx, NB_E_INVALID, "shape %u: a sphere has exactly one primitive", i);
+        } else return nb_fail(ctx, NB_E_UNSUPPORTED, "shape %u: unknown shape tag %u", i, sh.type);
+        if (sh.bsdf >= (int32_t) s->n_bsdfs || sh.emitter >= (int32_t) s->n_emitters)
+            return nb_fail(ctx, NB_E_INVALID, "shape %u: bsdf/emitter index out of range", i);
+        prims += sh.prim_count;
+    }
+    if (prims >= NB_SLOT_LAST) return nb_fail(ctx, NB_E_UNSUPPORTED, "too many primitives (%llu)", (unsigned long long) prims);
+    for (uint32_t i = 0; i < s->n_bsdfs; ++i)
+        if (s->bsdfs[i].type > NB_BSDF_MICROFACET)
+            return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: tag %u has no kernel in this backend", i, s->bsdfs[i].type);
+    int32_t envmap = -1;
+    for (uint32_t i = 0; i < s->n_emitters; ++i) {
+        const nb_emitter &e = s->emitters[i];
+        if (e.type == NB_EMITTER_AREA) {
+            if (e.shape < 0 || e.shape >= (int32_t) s->n_shapes) return nb_fail(ctx, NB_E_INVALID, "emitter %u: area light without a shape", i);
+        } else if (e.type == NB_EMITTER_POINT) {
+        } else return nb_fail(ctx, NB_E_UNSUPPORTED, "emitter %u: tag %u has no kernel in this backend", i, e.type);
+    }
+    if (s->n_emitters && !s->emitter_cdf) return nb_fail(ctx, NB_E_INVALID, "emitter_cdf missing");
+
+    nb_render_free(ctx);
+    nb_free_list(ctx->scene_allocs);
+    nb_free_list(ctx->bvh_allocs);
+    ctx->scene_ready = ctx->bvh_ready = false;
+    ctx->dev = NbDeviceScene();
+
+    ctx->h_shapes.assign(s->shapes, s->shapes + s->n_shapes);
+    ctx->h_positions.assign(s->positions, s->positions + s->n_vertices * 3);
+    ctx->h_faces.assign(s->faces, s->faces + s->n_faces * 3);
+    ctx->h_shape_prim_offset.assign(s->n_shapes + 1, 0);
+    for (uint32_t i = 0; i < s->n_shapes; ++i) ctx->h_shape_prim_offset[i + 1] = ctx->h_shape_prim_offset[i] + s->shapes[i].prim_count;
+
+    NbDeviceScene &d = ctx->dev;
+    int rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->shapes, s->n_shapes, &d.shapes))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->positions, s->n_vertices * 3, &d.positions))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->normals, s->n_vertices * 3, &d.normals))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->uvs, s->n_vertices * 2, &d.uvs))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->tangents, s->n_vertices * 3, &d.tangents))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->bitangents, s->n_vertices * 3, &d.bitangents))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->faces, s->n_faces * 3, &d.faces))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->bsdfs, s->n_bsdfs, &d.bsdfs))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->emitters, s->n_emitters, &d.emitters))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->emitter_cdf, s->n_emitters ? s->n_emitters + 1 : 0, &d.emitter_cdf))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->area_cdf, s->n_area_cdf, &d.area_cdf))) return rc;
+    d.n_shapes = s->n_shapes; d.n_bsdfs = s->n_bsdfs; d.n_emitters = s->n_emitters;
+    d.envmap_emitter = envmap;
+    d.camera = s->camera;
+    NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->scene_ready = true;
+    return NB_OK;
+}
+
+} /* extern "C" */

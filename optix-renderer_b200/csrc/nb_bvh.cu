@@ -1,0 +1,189 @@
+/* nb_bvh.cu — nb_build_bvh (import of the caller's BVH) and the parity trace entries. */
+#include "nb_internal.h"
+#include <algorithm>
+#include <cstring>
+
+extern "C" {
+
+/* Re-encodes BVH::m_nodes / m_indices (include/nori/bvh.h:127-164) into the stackless device
+ * layout of nb_internal.h. The tree and the order in which nodes and primitives are visited
+ * are unchanged; only "pop the stack" is precomputed as a skip link. */
+int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
+    if (!ctx) return NB_E_INVALID;
+    if (!ctx->scene_ready) return nb_fail(ctx, NB_E_STATE, "nb_build_bvh: upload a scene first");
+    if (mode != NB_BVH_IMPORT) return nb_fail(ctx, NB_E_UNSUPPORTED, "nb_build_bvh: mode %d not available", mode);
+    if (!imp || !imp->nodes || !imp->indices || imp->n_nodes == 0)
+        return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: empty import");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const uint32_t n = imp->n_nodes, ni = imp->n_indices;
+    const uint32_t total_prims = ctx->h_shape_prim_offset.back();
+    if (ni != total_prims) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: %u indices for %u primitives", ni, total_prims);
+
+    std::vector<uint32_t> skip(n, NB_NODE_END);
+    std::vector<uint8_t> seen(n, 0);
+    std::vector<uint32_t> stack;
+    stack.push_back(0);
+    while (!stack.empty()) {
+        const uint32_t i = stack.back();
+        stack.pop_back();
+        if (i >= n || seen[i]) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: node %u out of range or visited twice", i);
+        seen[i] = 1;
+        const nb_bvh_node &nd = imp->nodes[i];
+        if (nd.word0 & 1u) {
+            const uint32_t size = nd.word0 >> 1, start = nd.word1;
+            if ((uint64_t) start + size > ni) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: leaf %u range outside indices", i);
+        } else {
+            const uint32_t left = i + 1, right = nd.word1;
+            if (left >= n || right >= n) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: inner node %u has a child out of range", i);
+            skip[left] = right;
+            skip[right] = skip[i];
+            stack.push_back(right);
+            stack.push_back(left);
+        }
+    }
+
+    /* primitive slots in leaf (m_indices) order */
+    std::vector<float4> slots((size_t) ni * 3);
+    for (uint32_t k = 0; k < ni; ++k) {
+        const uint32_t gid = imp->indices[k];
+        if (gid >= total_prims) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: primitive id %u out of range", gid);
+        /* BVH::findShape, bvh.h:105-109 */
+        const uint32_t sid = (uint32_t) (std::upper_bound(ctx->h_shape_prim_offset.begin(), ctx->h_shape_prim_offset.end(), gid)
+                                         - ctx->h_shape_prim_offset.begin()) - 1;
+        const nb_shape &sh = ctx->h_shapes[sid];
+        const uint32_t local = gid - ctx->h_shape_prim_offset[sid];
+        float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
+        uint32_t tag = sid;
+        if (sh.type == NB_SHAPE_SPHERE) {
+            a = make_float4(sh.center[0], sh.center[1], sh.center[2], sh.radius);
+            tag |= NB_SLOT_SPHERE;
+        } else {
+            const uint32_t *f = &ctx->h_faces[((size_t) sh.face_offset + local) * 3];
+            const float *p0 = &ctx->h_positions[((size_t) sh.vertex_offset + f[0]) * 3];
+            const float *p1 = &ctx->h_positions[((size_t) sh.vertex_offset + f[1]) * 3];
+            const float *p2 = &ctx->h_positions[((size_t) sh.vertex_offset + f[2]) * 3];
+            /* edge1 = p1 - p0, edge2 = p2 - p0 (mesh.cpp:107) */
+            a = make_float4(p0[0], p0[1], p0[2], p1[0] - p0[0]);
+            b = make_float4(p1[1] - p0[1], p1[2] - p0[2], p2[0] - p0[0], p2[1] - p0[1]);
+            c.x = p2[2] - p0[2];
+        }
+        memcpy(&c.y, &tag, 4);
+        memcpy(&c.z, &local, 4);
+        slots[(size_t) k * 3] = a; slots[(size_t) k * 3 + 1] = b; slots[(size_t) k * 3 + 2] = c;
+    }
+
+    std::vector<float4> nodes((size_t) n * 2);
+    for (uint32_t i = 0; i < n; ++i) {
+        const nb_bvh_node &nd = imp->nodes[i];
+        uint32_t w1 = NB_NODE_INNER;
+        if (nd.word0 & 1u) {
+            const uint32_t size = nd.word0 >> 1, start = nd.word1;
+            if (size == 0) w1 = NB_NODE_EMPTY_LEAF;
+            else {
+                w1 = start;
+                uint32_t tag;
+                memcpy(&tag, &slots[(size_t) (start + size - 1) * 3 + 2].y, 4);
+                tag |= NB_SLOT_LAST;
+                memcpy(&slots[(size_t) (start + size - 1) * 3 + 2].y, &tag, 4);
+            }
+        }
+        float4 A, B;
+        memcpy(&A.x, &skip[i], 4);
+        memcpy(&A.y, &w1, 4);
+        A.z = nd.bmin[0]; A.w = nd.bmin[1];
+        B = make_float4(nd.bmin[2], nd.bmax[0], nd.bmax[1], nd.bmax[2]);
+        nodes[(size_t) i * 2] = A; nodes[(size_t) i * 2 + 1] = B;
+    }
+
+    for (void *p : ctx->bvh_allocs) cudaFree(p);
+    ctx->bvh_allocs.clear();
+    void *dn = nullptr, *ds = nullptr;
+    NB_CUDA(ctx, cudaMalloc(&dn, nodes.size() * sizeof(float4)));
+    ctx->bvh_allocs.push_back(dn);
+    NB_CUDA(ctx, cudaMalloc(&ds, std::max<size_t>(slots.size(), 1) * sizeof(float4)));
+    ctx->bvh_allocs.push_back(ds);
+    NB_CUDA(ctx, cudaMemcpyAsync(dn, nodes.data(), nodes.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    NB_CUDA(ctx, cudaMemcpyAsync(ds, slots.data(), slots.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
+    NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->dev.nodes = (const float4 *) dn; ctx->dev.slots = (const float4 *) ds;
+    ctx->dev.n_nodes = n; ctx->dev.n_slots = ni;
+    ctx->h_slot_tag.resize(ni); ctx->h_slot_prim.resize(ni);
+    for (uint32_t k = 0; k < ni; ++k) {
+        memcpy(&ctx->h_slot_tag[k], &slots[(size_t) k * 3 + 2].y, 4);
+        memcpy(&ctx->h_slot_prim[k], &slots[(size_t) k * 3 + 2].z, 4);
+    }
+    ctx->bvh_ready = true;
+    return NB_OK;
+}
+
+int nb_trace_rays(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_hit, nb_hit *out) {
+    if (!ctx) return NB_E_INVALID;
+    if (!ctx->bvh_ready) return nb_fail(ctx, NB_E_STATE, "nb_trace_rays: no BVH (call nb_build_bvh)");
+    if (n == 0) return NB_OK;
+    if (!rays || !out) return nb_fail(ctx, NB_E_INVALID, "nb_trace_rays: NULL buffer");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    std::vector<float4> packed((size_t) n * 2);
+    for (uint64_t i = 0; i < n; ++i) {
+        const nb_ray &r = rays[i];
+        packed[2 * i] = make_float4(r.o[0], r.o[1], r.o[2], r.mint);
+        packed[2 * i + 1] = make_float4(r.d[0], r.d[1], r.d[2], r.maxt);
+    }
+    float4 *d_rays = nullptr, *d_out = nullptr;
+    uint32_t *d_any = nullptr;
+    int rc = NB_OK;
+    std::vector<float4> h_out((size_t) n);
+    std::vector<uint32_t> h_any(any_hit ? (size_t) n : 0);
+    cudaError_t e;
+    if ((e = cudaMalloc((void **) &d_rays, packed.size() * sizeof(float4))) != cudaSuccess ||
+        (e = cudaMalloc((void **) &d_out, (size_t) n * sizeof(float4))) != cudaSuccess ||
+        (any_hit && (e = cudaMalloc((void **) &d_any, (size_t) n * 4)) != cudaSuccess)) {
+        rc = nb_fail(ctx, NB_E_NOMEM, "nb_trace_rays: %s", cudaGetErrorString(e));
+    } else {
+        cudaMemcpyAsync(d_rays, packed.data(), packed.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream);
+        nb_launch_trace_hits(ctx->dev, d_rays, n, any_hit, d_out, d_any, ctx->sm_count, ctx->stream);
+        cudaMemcpyAsync(h_out.data(), d_out, (size_t) n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream);
+        if (any_hit) cudaMemcpyAsync(h_any.data(), d_any, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+        e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) rc = nb_fail(ctx, NB_E_CUDA, "nb_trace_rays: %s", cudaGetErrorString(e));
+    }
+    cudaFree(d_rays); cudaFree(d_out); cudaFree(d_any);
+    if (rc != NB_OK) return rc;
+    for (uint64_t i = 0; i < n; ++i) {
+        uint32_t slot;
+        memcpy(&slot, &h_out[i].w, 4);
+        nb_hit &h = out[i];
+        h.t = h_out[i].x; h.u = h_out[i].y; h.v = h_out[i].z;
+        if (slot == 0xffffffffu) { h.shape = -1; h.prim = -1; }
+        else { h.shape = (int32_t) (ctx->h_slot_tag[slot] & NB_SLOT_SHAPE_MASK); h.prim = (int32_t) ctx->h_slot_prim[slot]; }
+        h.any_hit = any_hit ? h_any[i] : 0u;
+    }
+    return NB_OK;
+}
+
+int nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int any_hit, void *out_device,
+                         int repeats, float *ms_per_launch) {
+    if (!ctx) return NB_E_INVALID;
+    if (!ctx->bvh_ready) return nb_fail(ctx, NB_E_STATE, "nb_trace_rays_device: no BVH");
+    if (!rays_device || !out_device || repeats < 1) return nb_fail(ctx, NB_E_INVALID, "nb_trace_rays_device: bad argument");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t *d_any = nullptr;
+    if (any_hit) NB_CUDA(ctx, cudaMalloc((void **) &d_any, (size_t) n * 4));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, ctx->stream);
+    for (int r = 0; r < repeats; ++r)
+        nb_launch_trace_hits(ctx->dev, (const float4 *) rays_device, n, any_hit, (float4 *) out_device, d_any, ctx->sm_count, ctx->stream);
+    cudaEventRecord(e1, ctx->stream);
+    cudaError_t e = cudaEventSynchronize(e1);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(d_any);
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_trace_rays_device: %s", cudaGetErrorString(e));
+    if (ms_per_launch) *ms_per_launch = ms / repeats;
+    return NB_OK;
+}
+
+} /* extern "C" */

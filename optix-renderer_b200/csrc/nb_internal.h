@@ -1,0 +1,73 @@
+/* nb_internal.h — private to libnorib200.so: context, device scene, error plumbing. */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/norib200.h"
+
+/* ---- device-side layouts ------------------------------------------------------------------
+ * Node (32 B, two 16-byte loads): the reference's tree in the reference's order, re-encoded for
+ * stackless traversal. The reference walks left-first with an explicit stack (bvh.cpp:428-451);
+ * in its pre-order array "pop the stack" always lands on one fixed node per subtree, so we store
+ * that node as `skip` and need no stack at all. Visiting order is unchanged.
+ *   A = { skip, leaf_start (0xffffffff = inner), bmin.x, bmin.y }   B = { bmin.z, bmax.xyz }
+ * Primitive slot (48 B, three 16-byte loads), in leaf order (BVH::m_indices order):
+ *   triangle: { p0.xyz, e1.x } { e1.yz, e2.xy } { e2.z, bits(tag), bits(local prim), 0 }
+ *   sphere:   { c.xyz, r }     { 0 }            { 0,    bits(tag), 0, 0 }
+ *   tag = shape id | NB_SLOT_SPHERE | NB_SLOT_LAST (last slot of its leaf)
+ * e1 = p1 - p0 and e2 = p2 - p0 are the same fp32 subtractions Mesh::rayIntersect does per test
+ * (mesh.cpp:107), done once. */
+#define NB_SLOT_SPHERE 0x80000000u
+#define NB_SLOT_LAST   0x40000000u
+#define NB_SLOT_SHAPE_MASK 0x3fffffffu
+#define NB_NODE_END 0xffffffffu
+#define NB_NODE_INNER 0xffffffffu
+#define NB_NODE_EMPTY_LEAF 0xfffffffeu
+
+struct NbDeviceScene {
+    const float4 *nodes = nullptr;      /* 2 per node */
+    const float4 *slots = nullptr;      /* 3 per primitive slot */
+    uint32_t n_nodes = 0, n_slots = 0;
+    /* shading data */
+    const nb_shape *shapes = nullptr;
+    const float *positions = nullptr, *normals = nullptr, *uvs = nullptr, *tangents = nullptr, *bitangents = nullptr;
+    const uint32_t *faces = nullptr;
+    const nb_bsdf *bsdfs = nullptr;
+    const nb_emitter *emitters = nullptr;
+    const float *emitter_cdf = nullptr, *area_cdf = nullptr;
+    uint32_t n_shapes = 0, n_bsdfs = 0, n_emitters = 0;
+    int32_t envmap_emitter = -1;
+    nb_camera camera;
+};
+
+struct NbRenderState;   /* nb_render.cu */
+
+struct nb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string error;
+    /* host copies kept for nb_build_bvh / hit translation */
+    std::vector<nb_shape> h_shapes;
+    std::vector<float> h_positions;
+    std::vector<uint32_t> h_faces;
+    std::vector<uint32_t> h_shape_prim_offset;   /* BVH::m_shapeOffset */
+    std::vector<uint32_t> h_slot_tag, h_slot_prim; /* per leaf-order slot: shape tag, local prim */
+    bool scene_ready = false, bvh_ready = false;
+    NbDeviceScene dev;
+    std::vector<void *> scene_allocs, bvh_allocs;
+    NbRenderState *render = nullptr;
+    int sm_count = 148;
+    int opt_profile = 0, opt_sort = 0;
+};
+
+int nb_fail(nb_ctx *ctx, int code, const char *fmt, ...);
+#define NB_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+    return nb_fail(ctx, NB_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+
+/* nb_trace.cu */
+void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64_t n, int any_hit,
+                          float4 *out, uint32_t *out_any, int sm_count, cudaStream_t stream);
+
+/* nb_render.cu */
+int nb_render_free(nb_ctx *ctx);

@@ -1,0 +1,532 @@
+/* nb_render.cu — K_shade (ray generation, per-bounce shading, NEE + MIS, Russian roulette, queue
+ * compaction, film splat) and the host side of the wavefront loop.
+ *
+ * Restates, per path and per bounce, PathMISIntegrator::Li (src/integrators/path_mis.cpp:16-150)
+ * and PathMATSIntegrator::Li (path_mats.cpp:16-78) on top of renderBlock (src/utils/render.cpp:
+ * 421-459), PerspectiveCamera::sampleRay (src/cameras/perspective.cpp:97-141) and
+ * ImageBlock::put (src/utils/block.cpp:93-123). The reference traces the BSDF-sampled ray twice
+ * (MIS probe path_mis.cpp:119, then as the next main ray :34); here it is traced once and the
+ * probe's MIS weight is computed when the hit arrives, from state carried in the path.
+ */
+#include "nb_internal.h"
+#include "nb_wavefront.h"
+#include "nb_shading.cuh"
+#include <cstring>
+#include <algorithm>
+
+struct NbFilm {
+    float4 *data;
+    uint32_t rows, cols, border;
+    float radius, lookup;
+    float table[NB_FILTER_RESOLUTION + 1];
+};
+
+struct NbPlan {
+    unsigned long long total;     /* camera samples of this subframe */
+    unsigned long long seed;
+    uint32_t npix, width;
+    uint32_t first, stride;       /* sample index of pass k = first + k * stride */
+    uint32_t max_depth;
+};
+
+/* ImageBlock::put(pos, value), block.cpp:93-123, on the full-image block (offset 0). */
+__device__ __forceinline__ void nb_film_put(const NbFilm &film, float px, float py, f3 v, unsigned long long *stats) {
+    const bool valid = v.x >= 0.f && v.y >= 0.f && v.z >= 0.f && isfinite(v.x) && isfinite(v.y) && isfinite(v.z);
+    if (!valid) { atomicAdd(&stats[NB_STAT_INVALID], 1ULL); return; }      /* Color3f::isValid, common.cpp:254 */
+    const float posx = px - 0.5f + (float) film.border, posy = py - 0.5f + (float) film.border;
+    int x0 = (int) ceilf(posx - film.radius), x1 = (int) floorf(posx + film.radius);
+    int y0 = (int) ceilf(posy - film.radius), y1 = (int) floorf(posy + film.radius);
+    x0 = max(x0, 0); y0 = max(y0, 0);
+    x1 = min(x1, (int) film.cols - 1); y1 = min(y1, (int) film.rows - 1);
+    for (int y = y0; y <= y1; ++y) {
+        const float wy = film.table[(int) (fabsf((float) y - posy) * film.lookup)];
+        float4 *row = film.data + (size_t) y * film.cols;
+        for (int x = x0; x <= x1; ++x) {
+            const float wgt = film.table[(int) (fabsf((float) x - posx) * film.lookup)] * wy;
+            atomicAdd(row + x, make_float4(v.x * wgt, v.y * wgt, v.z * wgt, wgt));   /* RED.128 on sm_90+ */
+        }
+    }
+}
+
+__device__ __forceinline__ f3 nb_xform_point(const float *m, f3 p) {           /* transform.h:83-86 */
+    const float x = m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3];
+    const float y = m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7];
+    const float z = m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11];
+    const float w = m[12] * p.x + m[13] * p.y + m[14] * p.z + m[15];
+    return mk3(x / w, y / w, z / w);
+}
+__device__ __forceinline__ f3 nb_xform_vector(const float *m, f3 v) {          /* transform.h:73-75 */
+    return mk3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z,
+               m[8] * v.x + m[9] * v.y + m[10] * v.z);
+}
+
+/* renderBlock's per-sample prologue (render.cpp:441-447) + PerspectiveCamera::sampleRay. */
+__device__ __forceinline__ void nb_generate_path(const NbDeviceScene &sc, const NbWave &w, const NbPlan &plan,
+                                                 uint32_t p, unsigned long long n) {
+    const uint32_t pass = (uint32_t) (n / plan.npix), pix = (uint32_t) (n % plan.npix);
+    const uint32_t x = pix % plan.width, y = pix / plan.width;
+    const uint32_t sidx = plan.first + pass * plan.stride;
+    NbRng rng;
+    rng.seed(plan.seed * 0x9E3779B97F4A7C15ULL + sidx, pix);
+    const float px = (float) x + rng.next_float(), py = (float) y + rng.next_float();
+    const float2 ap = make_float2(rng.next_float(), rng.next_float());     /* always drawn, render.cpp:443 */
+    const nb_camera &cam = sc.camera;
+    const f3 nearP = nb_xform_point(cam.sample_to_camera, mk3(px * cam.inv_output_size[0], py * cam.inv_output_size[1], 0.f));
+    const f3 d0 = normalize(nearP);
+    f3 o = mk3(0.f), d = d0;
+    if (cam.lens_radius > NB_EPS) {
+        /* thin lens; the reference draws the lens point from a hidden static sampler
+         * (perspective.cpp:118-122) — here it comes from the path's own stream */
+        const float2 dk = square_to_uniform_disk(ap);
+        const float ft = cam.focal_distance / d0.z;
+        const f3 focus = d0 * ft;
+        o = mk3(cam.lens_radius * dk.x, cam.lens_radius * dk.y, 0.f);
+        d = normalize(focus - o);
+    }
+    o = nb_xform_point(cam.camera_to_world, o);
+    d = nb_xform_vector(cam.camera_to_world, d);
+    const float invZ = 1.0f / d0.z;
+    w.ray_o[p] = make_float4(o.x, o.y, o.z, cam.near_clip * invZ);
+    w.ray_d[p] = make_float4(d.x, d.y, d.z, cam.far_clip * invZ);
+    w.st0[p] = make_float4(0.f, 0.f, 0.f, 1.f);
+    w.st1[p] = make_float4(1.f, 1.f, 1.f, 0.f);
+    w.st2[p] = make_float4(px, py, 0.f, __uint_as_float(NB_FLAG_PRIMARY));
+    w.rng[p] = make_uint4((uint32_t) rng.state, (uint32_t) (rng.state >> 32), pix, sidx);
+}
+
+/* ---- K_shade ---------------------------------------------------------------------------------
+ * One thread per live path slot. MIS = path_mis.cpp, !MIS = path_mats.cpp. Ends with two
+ * warp-ballot compactions: surviving / regenerated paths -> queue_next, NEE rays -> shadow queue
+ * (one atomicAdd per warp each). */
+struct NbShadowOut { f3 o, d, c; float mint, maxt, cand; };
+
+template <bool MIS>
+__device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbWave &w, const NbFilm &film,
+                                              const NbPlan &plan, uint32_t p, bool &emit_shadow, NbShadowOut &so) {
+    /* returns true when the path lives on into the next iteration */
+    float4 s2 = w.st2[p];
+    uint32_t flags = __float_as_uint(s2.w);
+    if (flags & NB_FLAG_EMPTY) return false;
+    float4 s0 = w.st0[p];
+    f3 Li = mk3(s0.x, s0.y, s0.z);
+    if (flags & NB_FLAG_FINALIZE) { nb_film_put(film, s2.x, s2.y, Li, w.stats); return false; }
+    const float4 hit = w.hit[p];
+    const uint32_t slot = __float_as_uint(hit.w);
+    if (slot == 0xffffffffu) {              /* miss: no environment emitter in this backend yet */
+        nb_film_put(film, s2.x, s2.y, Li, w.stats);
+        return false;
+    }
+    const float4 ro = w.ray_o[p], rd = w.ray_d[p];
+    const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
+    float4 s1 = w.st1[p];
+    f3 thr = mk3(s1.x, s1.y, s1.z);
+    float w_mats = s0.w;
+    const float4 sl = __ldg(sc.slots + 3 * slot + 2);
+    const uint32_t sid = __float_as_uint(sl.y) & NB_SLOT_SHAPE_MASK, prim = __float_as_uint(sl.z);
+    const nb_shape sh = sc.shapes[sid];
+    NbIts its;
+    its.shape = sid;
+    if (sh.type == NB_SHAPE_SPHERE) nb_sphere_hit_info(sh, o, d, hit.x, its);
+    else nb_mesh_hit_info(sc, sh, prim, hit.y, hit.z, its);
+    const float n_lights = (float) sc.n_emitters;
+
+    /* emitter hit (path_mis.cpp:51-56) with the probe's MIS weight (path_mis.cpp:117-140) */
+    if (sh.emitter >= 0) {
+        const nb_emitter em = sc.emitters[sh.emitter];
+        const f3 wi_e = normalize(its.p - o);                       /* EmitterQueryRecord(ref, p, n) */
+        if (MIS && !(flags & NB_FLAG_PRIMARY) && (flags & NB_FLAG_BSDF_OK)) {
+            const float pdfmat = s1.w;
+            const float pdfmat_ems = nb_area_pdf(sh, o, its.p, its.sh.n, wi_e) / n_lights;
+            if (pdfmat + pdfmat_ems > NB_EPS) w_mats = pdfmat / (pdfmat + pdfmat_ems);
+        }
+        if (MIS && (flags & NB_FLAG_DISCRETE)) w_mats = 1.f;
+        if (dot(its.sh.n, -wi_e) >= 0.f) {                           /* AreaEmitter::eval */
+            const f3 Le = mk3(em.radiance[0], em.radiance[1], em.radiance[2]);
+            Li += (MIS ? w_mats : 1.f) * thr * Le;
+        }
+    } else if (MIS && (flags & NB_FLAG_DISCRETE)) w_mats = 1.f;
+
+    const uint32_t bounce = flags >> NB_BOUNCE_SHIFT;
+    uint4 rs = w.rng[p];
+    NbRng rng;
+    rng.state = ((uint64_t) rs.y << 32) | rs.x;
+    rng.inc = ((uint64_t) rs.z << 1) | 1u;
+
+    /* Russian roulette: path_mis.cpp:58-71 (always, clamped) / path_mats.cpp:49-61 (after 3) */
+    float succ = fminf(max3(thr), 0.99f);
+    bool die = false;
+    if (MIS) {
+        succ = fmaxf(succ, NB_EPS);
+        if (rng.next_float() > succ) die = true; else thr = thr / succ;
+    } else if (bounce >= 3) {
+        if (rng.next_float() > succ) die = true; else thr = thr / succ;
+    }
+    if (plan.max_depth && bounce >= plan.max_depth) die = true;
+    if (die || sh.bsdf < 0) { nb_film_put(film, s2.x, s2.y, Li, w.stats); return false; }
+
+    const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    const f3 wi = its.sh.to_local(-d);
+    float w_ems = s2.z;
+
+    if (MIS) {                                                       /* path_mis.cpp:75-106 */
+        const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, rng.next_float());
+        const nb_emitter em = sc.emitters[ei];
+        float2 s; s.x = rng.next_float(); s.y = rng.next_float();
+        NbEmitterSample es;
+        const f3 ems_col = nb_emitter_sample(sc, em, its.p, s, es);
+        if (!is_zero(ems_col, NB_EPS)) {
+            const f3 we = its.sh.to_local(es.wi);
+            const f3 f = nb_bsdf_eval(bsdf, wi, we);
+            const f3 C = thr * (ems_col * we.z * f * n_lights);
+            if (!is_black(C)) {
+                const float pdf_b = nb_bsdf_pdf(bsdf, wi, we), pdf_e = es.pdf / n_lights;
+                emit_shadow = true;
+                so.o = es.ray_o; so.d = es.ray_d; so.mint = es.ray_mint; so.maxt = es.ray_maxt;
+                so.c = C;
+                so.cand = (pdf_b + pdf_e > NB_EPS) ? pdf_e / (pdf_b + pdf_e) : -1.f;
+            }
+        }
+    }
+
+    /* BSDF sampling (path_mis.cpp:108-146 / path_mats.cpp:63-74) */
+    float2 s; s.x = rng.next_float(); s.y = rng.next_float();
+    f3 wo; bool discrete; float pdfmat;
+    const f3 col = nb_bsdf_sample(bsdf, wi, s, wo, discrete, pdfmat);
+    uint32_t nf = (bounce + 1) << NB_BOUNCE_SHIFT;
+    if (discrete) { nf |= NB_FLAG_DISCRETE; w_ems = 0.f; }
+    if (!is_zero(col, NB_EPS)) nf |= NB_FLAG_BSDF_OK;
+    thr = thr * col;
+    const f3 nd = its.sh.to_world(wo);
+    float maxt = INFINITY;
+    if (is_black(thr)) { nf |= NB_FLAG_FINALIZE; maxt = -1.f; }     /* nothing further can contribute */
+    w.ray_o[p] = make_float4(its.p.x, its.p.y, its.p.z, NB_EPS);
+    w.ray_d[p] = make_float4(nd.x, nd.y, nd.z, maxt);
+    w.st0[p] = make_float4(Li.x, Li.y, Li.z, w_mats);
+    w.st1[p] = make_float4(thr.x, thr.y, thr.z, pdfmat);
+    w.st2[p] = make_float4(s2.x, s2.y, w_ems, __uint_as_float(nf));
+    rs.x = (uint32_t) rng.state; rs.y = (uint32_t) (rng.state >> 32);
+    w.rng[p] = rs;
+    return true;
+}
+
+template <bool MIS>
+__global__ void __launch_bounds__(256)
+nb_k_shade(NbDeviceScene sc, NbWave w, NbFilm film, NbPlan plan) {
+    const uint32_t n = w.counts[NB_CNT_ACTIVE_CUR];
+    const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+    unsigned long long started = 0;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+        const uint32_t i = base + threadIdx.x;
+        const bool valid = i < n;
+        const uint32_t p = valid ? w.queue_cur[i] : 0u;
+        bool alive = false, emit_shadow = false;
+        NbShadowOut so;
+        if (valid) alive = nb_shade_path<MIS>(sc, w, film, plan, p, emit_shadow, so);
+
+        /* regeneration: dead slots claim the next camera samples (one atomic per warp) */
+        const bool want = valid && !alive;
+        const uint32_t wmask = __ballot_sync(0xffffffffu, want);
+        if (wmask) {
+            const int leader = __ffs(wmask) - 1;
+            unsigned long long first = 0;
+            if ((int) lane == leader) first = atomicAdd(&w.stats[NB_STAT_NEXT_SAMPLE], (unsigned long long) __popc(wmask));
+            first = __shfl_sync(0xffffffffu, first, leader);
+            if (want) {
+                const unsigned long long nidx = first + __popc(wmask & lt_mask);
+                if (nidx < plan.total) { nb_generate_path(sc, w, plan, p, nidx); alive = true; ++started; }
+                else w.st2[p].w = __uint_as_float(NB_FLAG_EMPTY);
+            }
+        }
+        /* compaction of the live set */
+        const uint32_t amask = __ballot_sync(0xffffffffu, alive);
+        if (amask) {
+            const int leader = __ffs(amask) - 1;
+            uint32_t first = 0;
+            if ((int) lane == leader) first = atomicAdd(&w.counts_next[NB_CNT_ACTIVE_CUR], (uint32_t) __popc(amask));
+            first = __shfl_sync(0xffffffffu, first, leader);
+            if (alive) w.queue_next[first + __popc(amask & lt_mask)] = p;
+        }
+        /* NEE shadow rays for the next K_trace */
+        const uint32_t smask = __ballot_sync(0xffffffffu, emit_shadow);
+        if (smask) {
+            const int leader = __ffs(smask) - 1;
+            uint32_t first = 0;
+            if ((int) lane == leader) first = atomicAdd(&w.counts_next[NB_CNT_SHADOW], (uint32_t) __popc(smask));
+            first = __shfl_sync(0xffffffffu, first, leader);
+            if (emit_shadow) {
+                const uint32_t j = first + __popc(smask & lt_mask);
+                w.sh_o[j] = make_float4(so.o.x, so.o.y, so.o.z, so.mint);
+                w.sh_d[j] = make_float4(so.d.x, so.d.y, so.d.z, so.maxt);
+                w.sh_c[j] = make_float4(so.c.x, so.c.y, so.c.z, __uint_as_float(p));
+                w.sh_w[j] = so.cand;
+            }
+        }
+    }
+    for (int off = 16; off; off >>= 1) started += __shfl_xor_sync(0xffffffffu, started, off);
+    if (lane == 0 && started) atomicAdd(&w.stats[NB_STAT_SAMPLES], started);
+}
+
+__global__ void nb_k_pool_init(NbWave w, uint32_t n_live) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < w.pool) {
+        w.st2[i] = make_float4(0.f, 0.f, 0.f, __uint_as_float(NB_FLAG_EMPTY));
+        w.ray_o[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        w.ray_d[i] = make_float4(0.f, 0.f, 1.f, -1.f);
+    }
+    if (i < n_live) ((uint32_t *) w.queue_cur)[i] = i;
+    if (i == 0) {
+        w.counts[NB_CNT_ACTIVE_CUR] = n_live; w.counts[NB_CNT_SHADOW] = 0;
+        w.counts_next[NB_CNT_ACTIVE_CUR] = 0; w.counts_next[NB_CNT_SHADOW] = 0;
+        w.stats[NB_STAT_NEXT_SAMPLE] = 0;
+    }
+}
+
+/* ImageBlock::toBitmap + Color4f::divideByFilterWeight (block.cpp:76-82, color.h:113-118) */
+__global__ void nb_k_film_finalize(const float4 *film, uint32_t cols, uint32_t border, uint32_t W, uint32_t H, float *rgb) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= W * H) return;
+    const uint32_t x = i % W, y = i / W;
+    const float4 c = film[(size_t) (y + border) * cols + (x + border)];
+    float3 o = make_float3(0.f, 0.f, 0.f);
+    if (fabsf(c.w) > NB_EPS) o = make_float3(c.x / c.w, c.y / c.w, c.z / c.w);
+    rgb[3 * (size_t) i] = o.x; rgb[3 * (size_t) i + 1] = o.y; rgb[3 * (size_t) i + 2] = o.z;
+}
+
+/* ---- host side --------------------------------------------------------------------------------- */
+struct NbRenderState {
+    nb_render_params params;
+    NbFilm film;
+    NbWave wave;                  /* pointers; queue/count ping-pong resolved per launch */
+    uint32_t *queue[2] = { nullptr, nullptr };
+    uint32_t *counts = nullptr;   /* 2 sets x NB_CNT_WORDS */
+    unsigned long long *stats = nullptr;
+    uint32_t *h_counts = nullptr; /* pinned mirror of counts */
+    unsigned long long *h_stats = nullptr;
+    std::vector<void *> allocs;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_batch[2] = { nullptr, nullptr };
+    nb_counters totals;
+    int grid = 0;
+};
+
+int nb_render_free(nb_ctx *ctx) {
+    NbRenderState *r = ctx->render;
+    if (!r) return NB_OK;
+    for (void *p : r->allocs) cudaFree(p);
+    if (r->h_counts) cudaFreeHost(r->h_counts);
+    if (r->h_stats) cudaFreeHost(r->h_stats);
+    if (r->ev_begin) cudaEventDestroy(r->ev_begin);
+    if (r->ev_end) cudaEventDestroy(r->ev_end);
+    for (int i = 0; i < 2; ++i) if (r->ev_batch[i]) cudaEventDestroy(r->ev_batch[i]);
+    delete r;
+    ctx->render = nullptr;
+    return NB_OK;
+}
+
+template <typename T>
+static int nb_dev_alloc(nb_ctx *ctx, NbRenderState *r, T **out, size_t count) {
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_NOMEM, "cudaMalloc(%zu bytes): %s", count * sizeof(T), cudaGetErrorString(e));
+    r->allocs.push_back(p);
+    *out = (T *) p;
+    return NB_OK;
+}
+
+extern "C" {
+
+int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
+    if (!ctx || !params) return nb_fail(ctx, NB_E_INVALID, "nb_render_begin: NULL argument");
+    if (!ctx->bvh_ready) return nb_fail(ctx, NB_E_STATE, "nb_render_begin: scene/BVH not ready");
+    if (params->integrator != NB_INTEGRATOR_PATH_MIS && params->integrator != NB_INTEGRATOR_PATH_MATS)
+        return nb_fail(ctx, NB_E_UNSUPPORTED, "integrator tag %u has no kernel in this backend", params->integrator);
+    if (params->integrator == NB_INTEGRATOR_PATH_MIS && ctx->dev.n_emitters == 0)
+        return nb_fail(ctx, NB_E_INVALID, "path_mis: No Emitter in scene!");      /* path_mis.cpp:76-79 */
+    if (!(params->filter_radius > 0.f)) return nb_fail(ctx, NB_E_INVALID, "filter radius must be positive");
+    const nb_camera &cam = ctx->dev.camera;
+    if (cam.width == 0 || cam.height == 0) return nb_fail(ctx, NB_E_INVALID, "camera has no output size");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    nb_render_free(ctx);
+    NbRenderState *r = new NbRenderState();
+    ctx->render = r;
+    r->params = *params;
+    memset(&r->totals, 0, sizeof(r->totals));
+    r->film.border = (uint32_t) ceilf(params->filter_radius - 0.5f);             /* block.cpp:57 */
+    r->film.rows = cam.height + 2 * r->film.border;
+    r->film.cols = cam.width + 2 * r->film.border;
+    r->film.radius = params->filter_radius;
+    r->film.lookup = NB_FILTER_RESOLUTION / params->filter_radius;               /* block.cpp:65 */
+    memcpy(r->film.table, params->filter_table, sizeof(r->film.table));
+    uint32_t pool = params->pool_paths ? params->pool_paths : (1u << 20);
+    pool = (pool + 255u) & ~255u;
+    int rc;
+    if ((rc = nb_dev_alloc(ctx, r, &r->film.data, (size_t) r->film.rows * r->film.cols))) return rc;
+    NbWave &w = r->wave;
+    w.pool = pool;
+    if ((rc = nb_dev_alloc(ctx, r, &w.ray_o, pool)) || (rc = nb_dev_alloc(ctx, r, &w.ray_d, pool)) ||
+        (rc = nb_dev_alloc(ctx, r, &w.hit, pool)) || (rc = nb_dev_alloc(ctx, r, &w.st0, pool)) ||
+        (rc = nb_dev_alloc(ctx, r, &w.st1, pool)) || (rc = nb_dev_alloc(ctx, r, &w.st2, pool)) ||
+        (rc = nb_dev_alloc(ctx, r, &w.rng, pool)) || (rc = nb_dev_alloc(ctx, r, &w.sh_o, pool)) ||
+        (rc = nb_dev_alloc(ctx, r, &w.sh_d, pool)) || (rc = nb_dev_alloc(ctx, r, &w.sh_c, pool)) ||
+        (rc = nb_dev_alloc(ctx, r, &w.sh_w, pool)) || (rc = nb_dev_alloc(ctx, r, &r->queue[0], pool)) ||
+        (rc = nb_dev_alloc(ctx, r, &r->queue[1], pool)) || (rc = nb_dev_alloc(ctx, r, &r->counts, 2 * NB_CNT_WORDS)) ||
+        (rc = nb_dev_alloc(ctx, r, &r->stats, NB_STAT_WORDS)))
+        return rc;
+    w.stats = r->stats;
+    NB_CUDA(ctx, cudaMallocHost((void **) &r->h_counts, 2 * 2 * NB_CNT_WORDS * sizeof(uint32_t)));
+    NB_CUDA(ctx, cudaMallocHost((void **) &r->h_stats, NB_STAT_WORDS * sizeof(unsigned long long)));
+    NB_CUDA(ctx, cudaEventCreate(&r->ev_begin));
+    NB_CUDA(ctx, cudaEventCreate(&r->ev_end));
+    NB_CUDA(ctx, cudaEventCreateWithFlags(&r->ev_batch[0], cudaEventDisableTiming));
+    NB_CUDA(ctx, cudaEventCreateWithFlags(&r->ev_batch[1], cudaEventDisableTiming));
+    NB_CUDA(ctx, cudaMemsetAsync(r->film.data, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
+    NB_CUDA(ctx, cudaMemsetAsync(r->stats, 0, NB_STAT_WORDS * sizeof(unsigned long long), ctx->stream));
+    NB_CUDA(ctx, cudaMemsetAsync(r->counts, 0, 2 * NB_CNT_WORDS * sizeof(uint32_t), ctx->stream));
+    r->grid = ctx->sm_count * 8;
+    NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NB_OK;
+}
+
+int nb_film_clear(nb_ctx *ctx) {
+    if (!ctx || !ctx->render) return nb_fail(ctx, NB_E_STATE, "nb_film_clear: no render in progress");
+    NbRenderState *r = ctx->render;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaMemsetAsync(r->film.data, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
+    NB_CUDA(ctx, cudaMemsetAsync(r->stats, 0, NB_STAT_WORDS * sizeof(unsigned long long), ctx->stream));
+    memset(&r->totals, 0, sizeof(r->totals));
+    return NB_OK;
+}
+
+/* The wavefront loop. Iteration = K_shade (consumes hits, regenerates, compacts) then K_trace
+ * (main rays + the shadow rays K_shade just made). The host never reads a queue length to size
+ * a launch; it only polls "anything left?" one batch behind the GPU. */
+int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t stride, uint32_t offset) {
+    if (!ctx || !ctx->render) return nb_fail(ctx, NB_E_STATE, "nb_render_subframe: call nb_render_begin first");
+    if (stride == 0 || offset >= stride) return nb_fail(ctx, NB_E_INVALID, "nb_render_subframe: bad sample slice %u/%u", offset, stride);
+    NbRenderState *r = ctx->render;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    const nb_camera &cam = ctx->dev.camera;
+    /* samples s in [first, first+count) with s % stride == offset */
+    uint32_t s0 = first + ((offset + stride - first % stride) % stride);
+    uint32_t passes = (s0 < first + count) ? (first + count - s0 + stride - 1) / stride : 0;
+    NbPlan plan;
+    plan.npix = cam.width * cam.height; plan.width = cam.width;
+    plan.total = (unsigned long long) passes * plan.npix;
+    plan.seed = r->params.seed; plan.first = s0; plan.stride = stride; plan.max_depth = r->params.max_depth;
+    cudaEventRecord(r->ev_begin, ctx->stream);
+    if (plan.total == 0) { cudaEventRecord(r->ev_end, ctx->stream); return NB_OK; }
+    NbWave w = r->wave;
+    const uint32_t n_live = (uint32_t) std::min<unsigned long long>(w.pool, plan.total);
+    w.queue_cur = r->queue[0]; w.queue_next = r->queue[1];
+    w.counts = r->counts; w.counts_next = r->counts + NB_CNT_WORDS;
+    nb_k_pool_init<<<(w.pool + 255) / 256, 256, 0, ctx->stream>>>(w, n_live);
+    const bool mis = r->params.integrator == NB_INTEGRATOR_PATH_MIS;
+    const int BATCH = 8;
+    uint64_t iter = 0, launches = 1;
+    int pending[2] = { 0, 0 };
+    bool done = false;
+    for (int batch = 0; !done; ++batch) {
+        for (int k = 0; k < BATCH; ++k, ++iter) {
+            const int a = (int) (iter & 1), b = a ^ 1;
+            NbWave ws = w;
+            ws.queue_cur = r->queue[a]; ws.queue_next = r->queue[b];
+            ws.counts = r->counts + a * NB_CNT_WORDS; ws.counts_next = r->counts + b * NB_CNT_WORDS;
+            if (mis) nb_k_shade<true><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, r->film, plan);
+            else nb_k_shade<false><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, r->film, plan);
+            NbWave wt = w;
+            wt.queue_cur = r->queue[b]; wt.queue_next = r->queue[a];
+            wt.counts = r->counts + b * NB_CNT_WORDS; wt.counts_next = r->counts + a * NB_CNT_WORDS;
+            nb_launch_trace_wave(ctx->dev, wt, r->grid, ctx->stream);
+            launches += 2;
+        }
+        /* after an even number of iterations the live count for the next K_shade is in set 0 */
+        const int slot = batch & 1;
+        cudaMemcpyAsync(r->h_counts + slot * 2 * NB_CNT_WORDS, r->counts, 2 * NB_CNT_WORDS * sizeof(uint32_t),
+                        cudaMemcpyDeviceToHost, ctx->stream);
+        cudaEventRecord(r->ev_batch[slot], ctx->stream);
+        pending[slot] = 1;
+        const int prev = slot ^ 1;
+        if (pending[prev]) {
+            NB_CUDA(ctx, cudaEventSynchronize(r->ev_batch[prev]));
+            pending[prev] = 0;
+            if (r->h_counts[prev * 2 * NB_CNT_WORDS + NB_CNT_ACTIVE_CUR] == 0) done = true;
+        }
+        if (!done && batch > (1 << 22)) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: wavefront did not drain");
+    }
+    cudaEventRecord(r->ev_end, ctx->stream);
+    cudaMemcpyAsync(r->h_stats, r->stats, NB_STAT_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: %s", cudaGetErrorString(e));
+    /* the last polled batch may be stale by one: verify the queue really drained */
+    NB_CUDA(ctx, cudaMemcpy(r->h_counts, r->counts, 2 * NB_CNT_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    if (r->h_counts[NB_CNT_ACTIVE_CUR] != 0) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: internal: live paths left");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end);
+    r->totals.device_ms += ms;
+    r->totals.iterations += iter;
+    r->totals.kernel_launches += launches;
+    r->totals.samples = r->h_stats[NB_STAT_SAMPLES];
+    r->totals.rays_closest = r->h_stats[NB_STAT_RAYS_CLOSEST];
+    r->totals.rays_any = r->h_stats[NB_STAT_RAYS_ANY];
+    r->totals.invalid_samples = r->h_stats[NB_STAT_INVALID];
+    return NB_OK;
+}
+
+int nb_sync(nb_ctx *ctx) {
+    if (!ctx) return NB_E_INVALID;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return NB_OK;
+}
+
+int nb_film_shape(nb_ctx *ctx, uint32_t *rows, uint32_t *cols, uint32_t *border) {
+    if (!ctx || !ctx->render) return nb_fail(ctx, NB_E_STATE, "nb_film_shape: no render in progress");
+    if (rows) *rows = ctx->render->film.rows;
+    if (cols) *cols = ctx->render->film.cols;
+    if (border) *border = ctx->render->film.border;
+    return NB_OK;
+}
+
+int nb_film_download(nb_ctx *ctx, float *out, int normalize) {
+    if (!ctx || !ctx->render || !out) return nb_fail(ctx, NB_E_STATE, "nb_film_download: no render in progress or NULL buffer");
+    NbRenderState *r = ctx->render;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!normalize) {
+        NB_CUDA(ctx, cudaMemcpyAsync(out, r->film.data, (size_t) r->film.rows * r->film.cols * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        return NB_OK;
+    }
+    const nb_camera &cam = ctx->dev.camera;
+    const size_t n = (size_t) cam.width * cam.height;
+    float *d_rgb = nullptr;
+    NB_CUDA(ctx, cudaMalloc((void **) &d_rgb, n * 3 * sizeof(float)));
+    nb_k_film_finalize<<<(unsigned) ((n + 255) / 256), 256, 0, ctx->stream>>>(r->film.data, r->film.cols, r->film.border, cam.width, cam.height, d_rgb);
+    cudaMemcpyAsync(out, d_rgb, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_rgb);
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_film_download: %s", cudaGetErrorString(e));
+    return NB_OK;
+}
+
+int nb_film_device_ptr(nb_ctx *ctx, void **ptr, uint64_t *n_floats) {
+    if (!ctx || !ctx->render) return nb_fail(ctx, NB_E_STATE, "nb_film_device_ptr: no render in progress");
+    if (ptr) *ptr = ctx->render->film.data;
+    if (n_floats) *n_floats = (uint64_t) ctx->render->film.rows * ctx->render->film.cols * 4;
+    return NB_OK;
+}
+
+int nb_get_counters(nb_ctx *ctx, nb_counters *out) {
+    if (!ctx || !ctx->render || !out) return nb_fail(ctx, NB_E_STATE, "nb_get_counters: no render in progress");
+    *out = ctx->render->totals;
+    return NB_OK;
+}
+
+int nb_set_option(nb_ctx *ctx, const char *name, int64_t value) {
+    if (!ctx || !name) return NB_E_INVALID;
+    if (!strcmp(name, "profile")) ctx->opt_profile = (int) value;
+    else if (!strcmp(name, "sort")) ctx->opt_sort = (int) value;
+    else return nb_fail(ctx, NB_E_INVALID, "nb_set_option: unknown option '%s'", name);
+    return NB_OK;
+}
+
+} /* extern "C" */

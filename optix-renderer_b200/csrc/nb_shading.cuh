@@ -1,0 +1,246 @@
+/* nb_shading.cuh — device restatement of the plugin math K_shade needs: hit reconstruction,
+ * the four BSDFs, the emitters. One function per reference method, cited beside it. */
+#pragma once
+#include "nb_internal.h"
+#include "nb_math.cuh"
+
+struct NbIts {          /* Intersection, include/nori/shape.h:44-76 */
+    f3 p;
+    float2 uv;
+    NbFrame sh;
+    f3 geo_n;
+    uint32_t shape;
+};
+
+__device__ __forceinline__ f3 ld3(const float *a, size_t i) { return mk3(__ldg(a + 3 * i), __ldg(a + 3 * i + 1), __ldg(a + 3 * i + 2)); }
+
+/* Mesh::setHitInformation (src/shapes/mesh.cpp:141-196) without normal maps */
+__device__ __forceinline__ void nb_mesh_hit_info(const NbDeviceScene &sc, const nb_shape &sh, uint32_t prim,
+                                                 float u, float v, NbIts &its) {
+    const float b0 = 1.f - (u + v), b1 = u, b2 = v;
+    const uint32_t *f = sc.faces + ((size_t) sh.face_offset + prim) * 3;
+    const size_t i0 = sh.vertex_offset + __ldg(f), i1 = sh.vertex_offset + __ldg(f + 1), i2 = sh.vertex_offset + __ldg(f + 2);
+    const f3 p0 = ld3(sc.positions, i0), p1 = ld3(sc.positions, i1), p2 = ld3(sc.positions, i2);
+    its.p = b0 * p0 + b1 * p1 + b2 * p2;
+    its.uv = make_float2(u, v);
+    if (sh.flags & NB_SHAPE_HAS_UVS) {
+        its.uv.x = b0 * __ldg(sc.uvs + 2 * i0) + b1 * __ldg(sc.uvs + 2 * i1) + b2 * __ldg(sc.uvs + 2 * i2);
+        its.uv.y = b0 * __ldg(sc.uvs + 2 * i0 + 1) + b1 * __ldg(sc.uvs + 2 * i1 + 1) + b2 * __ldg(sc.uvs + 2 * i2 + 1);
+    }
+    its.geo_n = normalize(cross(p1 - p0, p2 - p0));
+    if (sh.flags & NB_SHAPE_HAS_NORMALS) {
+        const f3 n = normalize(b0 * ld3(sc.normals, i0) + b1 * ld3(sc.normals, i1) + b2 * ld3(sc.normals, i2));
+        if ((sh.flags & NB_SHAPE_HAS_UVS) && sc.tangents) {
+            /* Frame(aTangent, aBitangent, normal), mesh.cpp:168-186 (not re-orthogonalised) */
+            its.sh.s = normalize(b0 * ld3(sc.tangents, i0) + b1 * ld3(sc.tangents, i1) + b2 * ld3(sc.tangents, i2));
+            its.sh.t = normalize(b0 * ld3(sc.bitangents, i0) + b1 * ld3(sc.bitangents, i1) + b2 * ld3(sc.bitangents, i2));
+            its.sh.n = n;
+        } else {
+            its.sh = frame_from_normal(n);
+        }
+    } else {
+        its.sh = frame_from_normal(its.geo_n);
+    }
+}
+
+/* Sphere::setHitInformation (src/shapes/sphere.cpp:96-124) without normal maps */
+__device__ __forceinline__ void nb_sphere_hit_info(const nb_shape &sh, f3 o, f3 d, float t, NbIts &its) {
+    its.p = o + d * t;
+    const f3 c = mk3(sh.center[0], sh.center[1], sh.center[2]);
+    const f3 n = normalize(its.p - c);
+    /* sphericalCoordinates(-n), swapped, mapped to [0,1] (common.cpp:283-291) */
+    float phi = atan2f(-n.y, -n.x);
+    if (phi < 0.f) phi += 2.f * NB_PI;
+    its.uv = make_float2(phi / (2.f * NB_PI), acosf(-n.z) / NB_PI);
+    its.geo_n = n;
+    const f3 tt = normalize(cross(mk3(0.f, 0.f, 1.f), n));
+    its.sh.s = tt; its.sh.t = cross(n, tt); its.sh.n = n;
+}
+
+/* fresnel(), src/utils/common.cpp:308-337 */
+__device__ __forceinline__ float nb_fresnel(float cosThetaI, float extIOR, float intIOR) {
+    float etaI = extIOR, etaT = intIOR;
+    if (extIOR == intIOR) return 0.0f;
+    if (cosThetaI < 0.0f) { const float s = etaI; etaI = etaT; etaT = s; cosThetaI = -cosThetaI; }
+    const float eta = etaI / etaT, sinThetaTSqr = eta * eta * (1.f - cosThetaI * cosThetaI);
+    if (sinThetaTSqr > 1.0f) return 1.0f;
+    const float cosThetaT = sqrtf(1.0f - sinThetaTSqr);
+    const float Rs = (etaI * cosThetaI - etaT * cosThetaT) / (etaI * cosThetaI + etaT * cosThetaT);
+    const float Rp = (etaT * cosThetaI - etaI * cosThetaT) / (etaT * cosThetaI + etaI * cosThetaT);
+    return (Rs * Rs + Rp * Rp) / 2.0f;
+}
+
+/* ---- microfacet (src/bsdf/microfacet.cpp:60-148) ------------------------------------------- */
+__device__ __forceinline__ float nb_tan_theta(f3 v) {       /* Frame::tanTheta, frame.h */
+    const float temp = 1.f - v.z * v.z;
+    if (temp <= 0.0f) return 0.0f;
+    return sqrtf(temp) / v.z;
+}
+__device__ __forceinline__ float nb_beckmann_D(f3 m, float alpha) {
+    const float temp = nb_tan_theta(m) / alpha, ct = m.z, ct2 = ct * ct;
+    return __expf(-temp * temp) / (NB_PI * alpha * alpha * ct2 * ct2);
+}
+__device__ __forceinline__ float nb_smith_G1(f3 v, f3 m, float alpha) {
+    const float tanTheta = nb_tan_theta(v);
+    if (tanTheta == 0.0f) return 1.0f;
+    if (dot(m, v) * v.z <= 0.f) return 0.0f;
+    const float a = 1.0f / (alpha * tanTheta);
+    if (a >= 1.6f) return 1.0f;
+    const float a2 = a * a;
+    return (3.535f * a + 2.181f * a2) / (1.0f + 2.276f * a + 2.577f * a2);
+}
+__device__ __forceinline__ f3 nb_microfacet_eval(const nb_bsdf &b, f3 wi, f3 wo) {
+    if (wo.z < 0.f) return mk3(0.f);
+    const f3 wh = normalize(wi + wo);
+    const float den = b.ks * nb_beckmann_D(wh, b.alpha) * nb_fresnel(dot(wh, wi), b.ext_ior, b.int_ior) *
+                      nb_smith_G1(wi, wh, b.alpha) * nb_smith_G1(wo, wh, b.alpha);
+    const float num = 4.f * wi.z * wo.z;
+    const float spec = den / num;
+    return mk3(b.albedo[0] * NB_INV_PI + spec, b.albedo[1] * NB_INV_PI + spec, b.albedo[2] * NB_INV_PI + spec);
+}
+__device__ __forceinline__ float nb_microfacet_pdf(const nb_bsdf &b, f3 wi, f3 wo) {
+    if (wo.z <= 0.f) return 0.f;
+    const f3 wh = normalize(wo + wi);
+    const float part1 = b.ks * nb_beckmann_D(wh, b.alpha) * wh.z / (4.f * dot(wo, wh));
+    const float part2 = (1.f - b.ks) * wo.z * NB_INV_PI;
+    return part1 + part2;
+}
+
+/* BSDF::eval for measure ESolidAngle */
+__device__ __forceinline__ f3 nb_bsdf_eval(const nb_bsdf &b, f3 wi, f3 wo) {
+    switch (b.type) {
+        case NB_BSDF_DIFFUSE:                                  /* diffuse.cpp:94-103 */
+            if (wi.z <= 0.f || wo.z <= 0.f) return mk3(0.f);
+            return mk3(b.albedo[0], b.albedo[1], b.albedo[2]) * NB_INV_PI;
+        case NB_BSDF_MICROFACET: return nb_microfacet_eval(b, wi, wo);
+        default: return mk3(0.f);                              /* mirror.cpp, dielectric.cpp: discrete */
+    }
+}
+/* BSDF::pdf for measure ESolidAngle */
+__device__ __forceinline__ float nb_bsdf_pdf(const nb_bsdf &b, f3 wi, f3 wo) {
+    switch (b.type) {
+        case NB_BSDF_DIFFUSE:                                  /* diffuse.cpp:106-120 */
+            if (wi.z <= 0.f || wo.z <= 0.f) return 0.f;
+            return NB_INV_PI * wo.z;
+        case NB_BSDF_MICROFACET: return nb_microfacet_pdf(b, wi, wo);
+        default: return 0.f;
+    }
+}
+
+/* BSDF::sample. Returns the weight; sets wo, `discrete` (measure == EDiscrete) and `pdf`
+ * (= bsdf->pdf(bRec) for the sampled direction, needed by the MIS probe, path_mis.cpp:126). */
+__device__ __forceinline__ f3 nb_bsdf_sample(const nb_bsdf &b, f3 wi, float2 s, f3 &wo, bool &discrete, float &pdf) {
+    discrete = false; pdf = 0.f; wo = mk3(0.f, 0.f, 1.f);
+    switch (b.type) {
+        case NB_BSDF_DIFFUSE: {                                /* diffuse.cpp:123-140 */
+            if (wi.z <= 0.f) return mk3(0.f);
+            wo = square_to_cosine_hemisphere(s);
+            pdf = wo.z <= 0.f ? 0.f : NB_INV_PI * wo.z;
+            return mk3(b.albedo[0], b.albedo[1], b.albedo[2]);
+        }
+        case NB_BSDF_MIRROR: {                                 /* mirror.cpp:41-57 */
+            if (wi.z <= 0.f) return mk3(0.f);
+            wo = mk3(-wi.x, -wi.y, wi.z);
+            discrete = true;
+            return mk3(1.f);
+        }
+        case NB_BSDF_DIELECTRIC: {                             /* dielectric.cpp:51-102 */
+            const float cosI = wi.z;
+            const float F = nb_fresnel(cosI, b.ext_ior, b.int_ior);
+            discrete = true;
+            if (s.x < F) { wo = mk3(-wi.x, -wi.y, wi.z); return mk3(1.f); }
+            float nz = 1.f, eta;
+            if (cosI < 0.f) { nz = -1.f; eta = b.int_ior / b.ext_ior; } else eta = b.ext_ior / b.int_ior;
+            const float wn = wi.z * nz;                         /* wi . normal */
+            const f3 wt1 = mk3(-eta * wi.x, -eta * wi.y, -eta * (wi.z - wn * nz));
+            const float c2 = -sqrtf(1.f - eta * eta * (1.f - wn * wn));
+            wo = mk3(wt1.x, wt1.y, wt1.z + c2 * nz);
+            return mk3(1.f / eta / eta);
+        }
+        case NB_BSDF_MICROFACET: {                             /* microfacet.cpp:122-148 */
+            if (wi.z < 0.f) return mk3(0.f);
+            if (s.y < b.ks) {
+                s.y /= b.ks;
+                const f3 wh = square_to_beckmann(s, b.alpha);
+                wo = 2.f * (dot(wi, wh) * wh) - wi;
+            } else {
+                s.y = (s.y - b.ks) / (1.f - b.ks);
+                wo = square_to_cosine_hemisphere(s);
+            }
+            if (wo.z <= 0.f) return mk3(0.f);
+            pdf = nb_microfacet_pdf(b, wi, wo);
+            return nb_microfacet_eval(b, wi, wo) / pdf * wo.z;
+        }
+        default: return mk3(0.f);
+    }
+}
+
+/* ---- emitters -------------------------------------------------------------------------------- */
+struct NbEmitterSample {       /* EmitterQueryRecord after Emitter::sample, emitter.h:37-67 */
+    f3 wi;                     /* ref -> light */
+    f3 ray_o, ray_d;           /* shadow ray (starts at the light) */
+    float ray_mint, ray_maxt;
+    float pdf;                 /* emitter->pdf(eqr) */
+};
+
+/* AreaEmitter::pdf (arealight.cpp:105-125) */
+__device__ __forceinline__ float nb_area_pdf(const nb_shape &sh, f3 ref, f3 p, f3 n, f3 wi) {
+    const float c = dot(n, -wi);
+    if (c < 0.f) return 0.f;
+    /* Mesh::pdfSurface (mesh.cpp:72-75) / Sphere::pdfSurface (sphere.cpp:134-137) */
+    const float prob = sh.type == NB_SHAPE_SPHERE ? (1.f / sh.radius) * (1.f / sh.radius) * NB_INV_FOURPI : sh.pdf_norm;
+    const f3 dlt = p - ref;
+    return prob * dot(dlt, dlt) / fabsf(c);
+}
+
+/* DiscretePDF::sample (dpdf.h:124-129): lower_bound on cdf[0..n], index clamp */
+__device__ __forceinline__ uint32_t nb_cdf_sample(const float *cdf, uint32_t n_entries, float x) {
+    uint32_t lo = 0, hi = n_entries + 1;         /* cdf has n_entries+1 values */
+    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(cdf + mid) < x) lo = mid + 1; else hi = mid; }
+    const int idx = (int) lo - 1;
+    const uint32_t i = idx < 0 ? 0u : (uint32_t) idx;
+    return i < n_entries - 1 ? i : n_entries - 1;
+}
+
+/* Emitter::sample for area (arealight.cpp:75-103 -> mesh.cpp:50-71 / sphere.cpp:126-132) and
+ * point lights (pointlight.cpp:47-63). Returns radiance / pdf. */
+__device__ __forceinline__ f3 nb_emitter_sample(const NbDeviceScene &sc, const nb_emitter &em, f3 ref, float2 s,
+                                                NbEmitterSample &out) {
+    if (em.type == NB_EMITTER_POINT) {
+        const f3 pos = mk3(em.position[0], em.position[1], em.position[2]);
+        const f3 dlt = ref - pos;
+        const float dist = length(dlt);
+        out.ray_o = pos; out.ray_d = normalize(dlt); out.ray_mint = NB_EPS; out.ray_maxt = dist - NB_EPS;
+        out.wi = normalize(pos - ref);
+        out.pdf = 1.f;
+        return mk3(em.radiance[0], em.radiance[1], em.radiance[2]) / dot(dlt, dlt);
+    }
+    const nb_shape sh = sc.shapes[em.shape];
+    f3 p, n;
+    if (sh.type == NB_SHAPE_SPHERE) {
+        const f3 q = square_to_uniform_sphere(s);
+        p = mk3(sh.center[0], sh.center[1], sh.center[2]) + sh.radius * q;
+        n = q;
+    } else {
+        const float *cdf = sc.area_cdf + sh.cdf_offset;
+        const uint32_t tri = nb_cdf_sample(cdf, sh.prim_count, s.x);
+        const float c0 = __ldg(cdf + tri), c1 = __ldg(cdf + tri + 1);
+        s.x = (s.x - c0) / (c1 - c0);                           /* sampleReuse, dpdf.h:157-162 */
+        const f3 bc = square_to_uniform_triangle(s);
+        const uint32_t *f = sc.faces + ((size_t) sh.face_offset + tri) * 3;
+        const size_t i0 = sh.vertex_offset + __ldg(f), i1 = sh.vertex_offset + __ldg(f + 1), i2 = sh.vertex_offset + __ldg(f + 2);
+        const f3 p0 = ld3(sc.positions, i0), p1 = ld3(sc.positions, i1), p2 = ld3(sc.positions, i2);
+        p = bc.x * p0 + bc.y * p1 + bc.z * p2;
+        if (sh.flags & NB_SHAPE_HAS_NORMALS)
+            n = normalize(bc.x * ld3(sc.normals, i0) + bc.y * ld3(sc.normals, i1) + bc.z * ld3(sc.normals, i2));
+        else
+            n = normalize(cross(p1 - p0, p2 - p0));
+    }
+    const f3 dlt = p - ref;
+    out.wi = normalize(dlt);
+    out.ray_o = p; out.ray_d = -out.wi; out.ray_mint = NB_EPS; out.ray_maxt = length(dlt) - NB_EPS;
+    out.pdf = nb_area_pdf(sh, ref, p, n, out.wi);
+    if (fabsf(out.pdf) < NB_EPS) return mk3(0.f);
+    /* eval (arealight.cpp:58-73): front side only; pdf > 0 already implies it */
+    return mk3(em.radiance[0], em.radiance[1], em.radiance[2]) / out.pdf;
+}

@@ -1,0 +1,128 @@
+/* nb_trace.cuh — ray/BVH traversal, bit-exact restatement of the reference's query.
+ *
+ * Follows BVH::rayIntersect (src/utils/bvh.cpp:402-460), TBoundingBox::rayIntersect
+ * (include/nori/bbox.h:336-363), Mesh::rayIntersect (src/shapes/mesh.cpp:101-139) and
+ * Sphere::rayIntersect (src/shapes/sphere.cpp:67-94) operation by operation:
+ *   - fp32, no FMA contraction (this header is only included from translation units built with
+ *     -fmad=false; x86-64 gcc emits no FMA for the reference),
+ *   - Eigen 3.3.8 association: dot3 = a0*b0 + (a1*b1 + a2*b2) (Eigen/src/Core/Redux.h:91-105),
+ *     cross as Eigen/src/Geometry/OrthoMethods.h:43-47,
+ *   - std::max/std::min/std::swap written as the comparisons they are (NaN behaviour included),
+ *   - the sphere roots are evaluated in DOUBLE, because `sqrt(discr)` in sphere.cpp:80-81
+ *     resolves to ::sqrt(double) (verified in the oracle's object code: cvtss2sd/sqrtsd/divsd).
+ * Visiting order is the reference's (left child first, leaves in m_indices order), expressed
+ * with precomputed skip links instead of a stack (see nb_internal.h).
+ */
+#pragma once
+#include "nb_internal.h"
+
+#define NB_EPSILON 1e-4f
+
+struct NbHit { float t, u, v; uint32_t slot; };
+
+__device__ __forceinline__ float nb_dot3(float ax, float ay, float az, float bx, float by, float bz) {
+    return ax * bx + (ay * by + az * bz);
+}
+
+/* bbox.h:336-363 */
+__device__ __forceinline__ bool nb_box_hit(const float4 A, const float4 B, const float3 o, const float3 d,
+                                           const float3 r, float mint, float maxt) {
+    float nearT = -INFINITY, farT = INFINITY;
+    const float mn[3] = { A.z, A.w, B.x }, mx[3] = { B.y, B.z, B.w };
+    const float oo[3] = { o.x, o.y, o.z }, dd[3] = { d.x, d.y, d.z }, rr[3] = { r.x, r.y, r.z };
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        if (dd[i] == 0.f) {
+            if (oo[i] < mn[i] || oo[i] > mx[i]) return false;
+        } else {
+            float t1 = (mn[i] - oo[i]) * rr[i];
+            float t2 = (mx[i] - oo[i]) * rr[i];
+            if (t1 > t2) { float s = t1; t1 = t2; t2 = s; }
+            nearT = (t1 < nearT) ? nearT : t1;      /* std::max(t1, nearT) */
+            farT = (farT < t2) ? farT : t2;         /* std::min(t2, farT)  */
+            if (!(nearT <= farT)) return false;
+        }
+    }
+    return mint <= farT && nearT <= maxt;
+}
+
+/* mesh.cpp:101-139 with e1/e2 precomputed */
+__device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, const float4 s2, const float3 o,
+                                           const float3 d, float mint, float maxt, float &u, float &v, float &t) {
+    const float p0x = s0.x, p0y = s0.y, p0z = s0.z;
+    const float e1x = s0.w, e1y = s1.x, e1z = s1.y;
+    const float e2x = s1.z, e2y = s1.w, e2z = s2.x;
+    const float pvx = d.y * e2z - d.z * e2y, pvy = d.z * e2x - d.x * e2z, pvz = d.x * e2y - d.y * e2x;
+    const float det = nb_dot3(e1x, e1y, e1z, pvx, pvy, pvz);
+    if (det > -1e-8f && det < 1e-8f) return false;
+    const float inv = 1.0f / det;
+    const float tvx = o.x - p0x, tvy = o.y - p0y, tvz = o.z - p0z;
+    u = nb_dot3(tvx, tvy, tvz, pvx, pvy, pvz) * inv;
+    if (u < 0.0f || u > 1.0f) return false;
+    const float qvx = tvy * e1z - tvz * e1y, qvy = tvz * e1x - tvx * e1z, qvz = tvx * e1y - tvy * e1x;
+    v = nb_dot3(d.x, d.y, d.z, qvx, qvy, qvz) * inv;
+    if (v < 0.0f || u + v > 1.0f) return false;
+    t = nb_dot3(e2x, e2y, e2z, qvx, qvy, qvz) * inv;
+    return t >= mint && t <= maxt;
+}
+
+/* sphere.cpp:67-94 */
+__device__ __forceinline__ bool nb_sphere_hit(const float4 s0, const float3 o, const float3 d, float mint,
+                                              float maxt, float &t) {
+    const float Lx = o.x - s0.x, Ly = o.y - s0.y, Lz = o.z - s0.z;
+    const float a = nb_dot3(d.x, d.y, d.z, d.x, d.y, d.z);
+    const float b = 2.f * nb_dot3(d.x, d.y, d.z, Lx, Ly, Lz);
+    const float c = nb_dot3(Lx, Ly, Lz, Lx, Ly, Lz) - s0.w * s0.w;
+    const float discr = b * b - 4.f * a * c;
+    if (discr < 0.f) return false;
+    const double sd = sqrt((double) discr), nb = (double) (-b), da = (double) a;
+    const float tmin = (float) ((nb - sd) / 2.0 / da);
+    const float tmax = (float) ((nb + sd) / 2.0 / da);
+    if (mint <= tmin && maxt >= tmin) { t = tmin; return true; }
+    if (mint <= tmax && maxt >= tmax) { t = tmax; return true; }
+    return false;
+}
+
+/* bvh.cpp:402-460. ANY = shadow-ray query (returns at the first accepted primitive). */
+template <bool ANY>
+__device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, const float4 *__restrict__ slots,
+                                            uint32_t n_nodes, float3 o, float3 d, float mint, float maxt,
+                                            NbHit &hit) {
+    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
+    if (mint == NB_EPSILON) {                       /* adaptive ray epsilon, bvh.cpp:409-410 */
+        float m = fabsf(o.x);
+        m = fmaxf(m, fabsf(o.y));
+        m = fmaxf(m, fabsf(o.z));
+        const float s = mint * m;
+        mint = (mint < s) ? s : mint;
+    }
+    if (n_nodes == 0 || maxt < mint) return false;
+    const float3 r = make_float3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);   /* Ray3f::update, ray.h */
+    bool found = false;
+    uint32_t idx = 0;
+    while (idx != NB_NODE_END) {
+        const float4 A = __ldg(nodes + 2 * idx), B = __ldg(nodes + 2 * idx + 1);
+        const uint32_t skip = __float_as_uint(A.x), start = __float_as_uint(A.y);
+        if (!nb_box_hit(A, B, o, d, r, mint, maxt)) { idx = skip; continue; }
+        if (start == NB_NODE_INNER) { idx = idx + 1; continue; }
+        if (start == NB_NODE_EMPTY_LEAF) { idx = skip; continue; }
+        uint32_t s = start;
+        while (true) {
+            const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
+            const uint32_t tag = __float_as_uint(s2.y);
+            float u = 0.f, v = 0.f, t;
+            const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
+                                                   : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+            if (ok) {
+                if (ANY) return true;
+                found = true;
+                maxt = t;
+                hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+            }
+            if (tag & NB_SLOT_LAST) break;
+            ++s;
+        }
+        idx = skip;
+    }
+    return found;
+}

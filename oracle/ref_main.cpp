@@ -13,6 +13,7 @@
  *   genrays  scene.xml rays.bin n_primary seed
  *   hits     scene.xml rays.bin hits.bin
  *   bvh      scene.xml bvh.bin
+ *   flat     scene.xml scene.nbs
  *   test     test.xml                 (runs <test type="ttest|chi2test"> roots)
  *   ttest    test.xml [samples=N]     (scene-mode t-tests; restated, see modeTTestScenes)
  *   rng      n                        (pcg32 known-answer stream)
@@ -50,13 +51,15 @@
 #include <nori/scene.h>
 #include <nori/mesh.h>
 #include <nori/sphere.h>
+#include <nori/camera.h>
+#include <nori/perspective.h>
+#include <nori/emitter.h>
+#include <nori/dpdf.h>
 #undef private
 #undef protected
 #include <nori/parser.h>
-#include <nori/camera.h>
 #include <nori/integrator.h>
 #include <nori/sampler.h>
-#include <nori/emitter.h>
 #include <nori/bsdf.h>
 #include <nori/block.h>
 #include <nori/bitmap.h>
@@ -66,6 +69,8 @@
 #include <pugixml.hpp>
 #include <hypothesis.h>
 #include <unistd.h>
+#include "../include/norib200.h"
+#include "../include/nb_scene_file.h"
 
 using namespace nori;
 
@@ -404,6 +409,141 @@ static int modeBvh(int argc, char **argv) {
     return 0;
 }
 
+
+/* ---- flat: dump what the reference holds after Scene::update() as an .nbs container -------
+ * (include/nb_scene_file.h). Geometry, area CDFs, emitter CDF, camera matrices and the BVH are
+ * read out of the reference's own objects; BSDF parameters live in classes private to their
+ * .cpp files and are therefore NOT dumped (the product's own loader reads them from the XML).
+ * Used as the golden for the product loader and as the first GPU fixtures. */
+struct NbsWriter {
+    struct Sec { std::string name; uint32_t elem; std::vector<char> bytes; };
+    std::vector<Sec> secs;
+    void add(const char *name, uint32_t elem, const void *data, size_t count) {
+        Sec s; s.name = name; s.elem = elem;
+        s.bytes.assign((const char *) data, (const char *) data + (size_t) elem * count);
+        secs.push_back(std::move(s));
+    }
+    void write(const std::string &path) {
+        FILE *f = fopen(path.c_str(), "wb");
+        if (!f) throw NoriException("cannot write %s", path);
+        uint32_t hdr[2] = { NBS_MAGIC, (uint32_t) secs.size() };
+        fwrite(hdr, 4, 2, f);
+        uint64_t off = 8 + sizeof(nbs_section) * secs.size();
+        std::vector<nbs_section> table(secs.size());
+        for (size_t i = 0; i < secs.size(); ++i) {
+            off = (off + 15) & ~(uint64_t) 15;
+            memset(&table[i], 0, sizeof(nbs_section));
+            strncpy(table[i].name, secs[i].name.c_str(), 15);
+            table[i].elem_size = secs[i].elem;
+            table[i].count = secs[i].bytes.size() / secs[i].elem;
+            table[i].offset = off;
+            off += secs[i].bytes.size();
+        }
+        fwrite(table.data(), sizeof(nbs_section), table.size(), f);
+        for (size_t i = 0; i < secs.size(); ++i) {
+            long cur = ftell(f);
+            for (uint64_t k = cur; k < table[i].offset; ++k) fputc(0, f);
+            fwrite(secs[i].bytes.data(), 1, secs[i].bytes.size(), f);
+        }
+        fclose(f);
+    }
+};
+
+static int modeFlat(int argc, char **argv) {
+    if (argc < 4) return 2;
+    LoadedScene ls = loadScene(argv[2]);
+    Scene *scene = ls.render.get();
+    const std::vector<Shape *> &shapes = scene->getShapes();
+    const std::vector<Emitter *> &lights = scene->getLights();
+    std::vector<nb_shape> nshapes;
+    std::vector<float> positions, normals, uvs, tangents, bitangents, areaCdf;
+    std::vector<uint32_t> faces;
+    bool anyN = false, anyUV = false, anyT = false;
+    for (Shape *sh : shapes) {
+        if (auto *m = dynamic_cast<Mesh *>(sh)) { anyN |= m->m_N.size() > 0; anyUV |= m->m_UV.size() > 0; anyT |= m->m_T.size() > 0; }
+    }
+    for (Shape *sh : shapes) {
+        nb_shape ns; memset(&ns, 0, sizeof(ns));
+        ns.bsdf = -1; ns.emitter = -1; ns.medium = -1;
+        for (size_t e = 0; e < lights.size(); ++e) if (lights[e] == sh->getEmitter()) ns.emitter = (int32_t) e;
+        ns.prim_count = sh->getPrimitiveCount();
+        if (auto *m = dynamic_cast<Mesh *>(sh)) {
+            ns.type = NB_SHAPE_MESH;
+            ns.vertex_offset = (uint32_t) (positions.size() / 3);
+            ns.vertex_count = (uint32_t) m->m_V.cols();
+            ns.face_offset = (uint32_t) (faces.size() / 3);
+            for (int v = 0; v < m->m_V.cols(); ++v) {
+                for (int k = 0; k < 3; ++k) positions.push_back(m->m_V(k, v));
+                if (anyN) for (int k = 0; k < 3; ++k) normals.push_back(m->m_N.size() > 0 ? m->m_N(k, v) : 0.f);
+                if (anyUV) for (int k = 0; k < 2; ++k) uvs.push_back(m->m_UV.size() > 0 ? m->m_UV(k, v) : 0.f);
+                if (anyT) for (int k = 0; k < 3; ++k) {
+                    tangents.push_back(m->m_T.size() > 0 ? m->m_T(k, v) : 0.f);
+                    bitangents.push_back(m->m_BT.size() > 0 ? m->m_BT(k, v) : 0.f);
+                }
+            }
+            for (int t = 0; t < m->m_F.cols(); ++t) for (int k = 0; k < 3; ++k) faces.push_back(m->m_F(k, t));
+            if (m->m_N.size() > 0) ns.flags |= NB_SHAPE_HAS_NORMALS;
+            if (m->m_UV.size() > 0) ns.flags |= NB_SHAPE_HAS_UVS;
+            ns.cdf_offset = (uint32_t) areaCdf.size();
+            areaCdf.insert(areaCdf.end(), m->m_pdf.m_cdf.begin(), m->m_pdf.m_cdf.end());
+            ns.pdf_norm = m->m_pdf.m_normalization;
+        } else if (auto *s = dynamic_cast<Sphere *>(sh)) {
+            ns.type = NB_SHAPE_SPHERE;
+            ns.radius = s->m_radius;
+            for (int k = 0; k < 3; ++k) ns.center[k] = s->m_position[k];
+        } else throw NoriException("flat: unknown shape class");
+        nshapes.push_back(ns);
+    }
+    NbsWriter w;
+    w.add("shapes", sizeof(nb_shape), nshapes.data(), nshapes.size());
+    w.add("positions", 4, positions.data(), positions.size());
+    if (anyN) w.add("normals", 4, normals.data(), normals.size());
+    if (anyUV) w.add("uvs", 4, uvs.data(), uvs.size());
+    if (anyT) { w.add("tangents", 4, tangents.data(), tangents.size()); w.add("bitangents", 4, bitangents.data(), bitangents.size()); }
+    w.add("faces", 4, faces.data(), faces.size());
+    w.add("area_cdf", 4, areaCdf.data(), areaCdf.size());
+    w.add("emitter_cdf", 4, scene->emitterDpdf.m_cdf.data(), scene->emitterDpdf.m_cdf.size());
+    std::vector<nb_emitter> nem;
+    for (Emitter *e : lights) {
+        nb_emitter ne; memset(&ne, 0, sizeof(ne));
+        ne.type = e->m_shape ? NB_EMITTER_AREA : NB_EMITTER_POINT;
+        ne.shape = -1;
+        for (size_t i = 0; i < shapes.size(); ++i) if (shapes[i] == e->m_shape) ne.shape = (int32_t) i;
+        for (int k = 0; k < 3; ++k) ne.radiance[k] = e->m_radiance[k];
+        nem.push_back(ne);
+    }
+    w.add("emitters", sizeof(nb_emitter), nem.data(), nem.size());
+    if (auto *cam = dynamic_cast<const PerspectiveCamera *>(scene->getCamera())) {
+        nb_camera c; memset(&c, 0, sizeof(c));
+        for (int r = 0; r < 4; ++r) for (int col = 0; col < 4; ++col) {
+            c.sample_to_camera[r * 4 + col] = cam->m_sampleToCamera.getMatrix()(r, col);
+            c.camera_to_world[r * 4 + col] = cam->m_cameraToWorld.getMatrix()(r, col);
+        }
+        c.inv_output_size[0] = cam->m_invOutputSize.x(); c.inv_output_size[1] = cam->m_invOutputSize.y();
+        c.near_clip = cam->m_nearClip; c.far_clip = cam->m_farClip;
+        c.lens_radius = cam->m_lensRadius; c.focal_distance = cam->m_focalDistance;
+        c.width = cam->getOutputSize().x(); c.height = cam->getOutputSize().y();
+        w.add("camera", sizeof(nb_camera), &c, 1);
+        /* the tabulated filter exactly as ImageBlock::init builds it (block.cpp:58-64) */
+        nb_render_params rp; memset(&rp, 0, sizeof(rp));
+        const ReconstructionFilter *rf = cam->getReconstructionFilter();
+        rp.filter_radius = rf->getRadius();
+        for (int i = 0; i < NB_FILTER_RESOLUTION; ++i) rp.filter_table[i] = rf->eval((rp.filter_radius * i) / NB_FILTER_RESOLUTION);
+        rp.filter_table[NB_FILTER_RESOLUTION] = 0.f;
+        w.add("render", sizeof(nb_render_params), &rp, 1);
+    }
+    uint32_t spp = (uint32_t) scene->getSampler()->getSampleCount();
+    w.add("spp", 4, &spp, 1);
+    const BVH *bvh = scene->getBVH();
+    static_assert(sizeof(BVH::BVHNode) == sizeof(nb_bvh_node), "node layout");
+    w.add("bvh_nodes", sizeof(nb_bvh_node), bvh->m_nodes.data(), bvh->m_nodes.size());
+    w.add("bvh_indices", 4, bvh->m_indices.data(), bvh->m_indices.size());
+    w.write(argv[3]);
+    printf("{\"mode\": \"flat\", \"shapes\": %zu, \"vertices\": %zu, \"faces\": %zu, \"nodes\": %zu, \"emitters\": %zu}\n",
+           nshapes.size(), positions.size() / 3, faces.size() / 3, bvh->m_nodes.size(), nem.size());
+    return 0;
+}
+
 /* <test> roots never execute in this fork (render.cpp:133-137); drive them the only way the
  * classes allow: cloneAndInit() then update(gui), which calls execute() (ttest.cpp:93,:120). */
 static int modeTest(int argc, char **argv) {
@@ -494,6 +634,9 @@ static int modeRng(int argc, char **argv) {
     pcg32 b; b.seed(32, 64);       /* Independent::prepare(block at offset (32,64)) */
     for (int i = 0; i < n; ++i) printf("%.9g ", b.nextFloat());
     printf("\n");
+    pcg32 c; c.seed(42u, 54u);     /* ext/pcg32/pcg32-demo.cpp:54 -> pcg32-demo.out "Round 1" */
+    for (int i = 0; i < n; ++i) printf("%08x ", c.nextUInt());
+    printf("\n");
     return 0;
 }
 
@@ -504,6 +647,7 @@ static int usage() {
         "  nori_ref genrays scene.xml rays.bin n_primary seed\n"
         "  nori_ref hits    scene.xml rays.bin hits.bin\n"
         "  nori_ref bvh     scene.xml bvh.bin\n"
+        "  nori_ref flat    scene.xml scene.nbs      (flattened scene container, include/nb_scene_file.h)\n"
         "  nori_ref test    test.xml\n"
         "  nori_ref ttest   test.xml [samples=N]   (scene-mode t-tests, restated: see modeTTestScenes)\n"
         "  nori_ref rng     n\n");
@@ -519,6 +663,7 @@ int main(int argc, char **argv) {
         else if (mode == "genrays") rc = modeGenRays(argc, argv);
         else if (mode == "hits") rc = modeHits(argc, argv);
         else if (mode == "bvh") rc = modeBvh(argc, argv);
+        else if (mode == "flat") rc = modeFlat(argc, argv);
         else if (mode == "test") rc = modeTest(argc, argv);
         else if (mode == "ttest") rc = modeTTestScenes(argc, argv);
         else if (mode == "rng") rc = modeRng(argc, argv);
