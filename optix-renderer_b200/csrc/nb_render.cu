@@ -306,6 +306,7 @@ struct NbRenderState {
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_batch[2] = { nullptr, nullptr };
     nb_counters totals;
     int grid = 0;
+    std::vector<cudaEvent_t> prof_events;   /* "profile" option: 3 per iteration (before shade, between, after trace) */
 };
 
 int nb_render_free(nb_ctx *ctx) {
@@ -317,6 +318,7 @@ int nb_render_free(nb_ctx *ctx) {
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
     if (r->ev_end) cudaEventDestroy(r->ev_end);
     for (int i = 0; i < 2; ++i) if (r->ev_batch[i]) cudaEventDestroy(r->ev_batch[i]);
+    for (cudaEvent_t e : r->prof_events) cudaEventDestroy(e);
     delete r;
     ctx->render = nullptr;
     return NB_OK;
@@ -424,18 +426,28 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     uint64_t iter = 0, launches = 1;
     int pending[2] = { 0, 0 };
     bool done = false;
+    const bool prof = ctx->opt_profile != 0;
+    size_t prof_used = 0;
+    auto prof_mark = [&]() {
+        if (!prof) return;
+        if (prof_used == r->prof_events.size()) { cudaEvent_t e; cudaEventCreate(&e); r->prof_events.push_back(e); }
+        cudaEventRecord(r->prof_events[prof_used++], ctx->stream);
+    };
     for (int batch = 0; !done; ++batch) {
         for (int k = 0; k < BATCH; ++k, ++iter) {
             const int a = (int) (iter & 1), b = a ^ 1;
             NbWave ws = w;
             ws.queue_cur = r->queue[a]; ws.queue_next = r->queue[b];
             ws.counts = r->counts + a * NB_CNT_WORDS; ws.counts_next = r->counts + b * NB_CNT_WORDS;
+            prof_mark();
             if (mis) nb_k_shade<true><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, r->film, plan);
             else nb_k_shade<false><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, r->film, plan);
+            prof_mark();
             NbWave wt = w;
             wt.queue_cur = r->queue[b]; wt.queue_next = r->queue[a];
             wt.counts = r->counts + b * NB_CNT_WORDS; wt.counts_next = r->counts + a * NB_CNT_WORDS;
             nb_launch_trace_wave(ctx->dev, wt, r->grid, ctx->stream);
+            prof_mark();
             launches += 2;
         }
         /* after an even number of iterations the live count for the next K_shade is in set 0 */
@@ -462,6 +474,12 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     if (r->h_counts[NB_CNT_ACTIVE_CUR] != 0) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: internal: live paths left");
     float ms = 0.f;
     cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end);
+    for (size_t k = 0; k + 2 < prof_used + 0 && prof; k += 3) {
+        float a = 0.f, b = 0.f;
+        cudaEventElapsedTime(&a, r->prof_events[k], r->prof_events[k + 1]);
+        cudaEventElapsedTime(&b, r->prof_events[k + 1], r->prof_events[k + 2]);
+        r->totals.shade_ms += a; r->totals.trace_ms += b;
+    }
     r->totals.device_ms += ms;
     r->totals.iterations += iter;
     r->totals.kernel_launches += launches;

@@ -127,10 +127,8 @@ def main():
             tuv = full[:, 8:20].copy().view("<f4")
             h["t"], h["u"], h["v"] = tuv[:, 0], tuv[:, 1], tuv[:, 2]
             h["any_hit"] = full[:, 28:32].copy().view("<u4")[:, 0]
-            # the harness reports primitives by their BVH-global id; the ABI reports shape-local
-            offs = np.concatenate([[0], np.cumsum(shapes["prim_count"])]).astype(np.int64)
+            # BVH::findShape (bvh.h:105-109) rewrites the index in place: prim is already shape-local
             hit = h["shape"] >= 0
-            h["prim"][hit] -= offs[h["shape"][hit]].astype(np.int32)
             h.tofile(os.path.join(HERE, name + "_hits.bin"))
             # per-ray traversal work, for the roofline's bytes/ray
             nodes = full[:, 20:24].copy().view("<u4")[:, 0]; prims = full[:, 24:28].copy().view("<u4")[:, 0]
