@@ -156,7 +156,7 @@ typedef struct nb_counters {
     uint64_t kernel_launches;
     uint64_t invalid_samples;/* dropped by the isValid() rule of ImageBlock::put (block.cpp:94) */
     double   device_ms;      /* CUDA-event time of the last nb_sync()ed render span */
-    double   trace_ms, shade_ms; /* filled when profiling timers are on (nb_set_option) */
+    double   trace_ms, shade_ms, regen_ms; /* per-kernel sums when the "profile" option is on */
 } nb_counters;
 
 typedef struct nb_ctx nb_ctx;

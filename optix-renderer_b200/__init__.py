@@ -69,7 +69,8 @@ class BvhImport(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("rays_closest", C.c_uint64), ("rays_any", C.c_uint64),
                 ("iterations", C.c_uint64), ("kernel_launches", C.c_uint64), ("invalid_samples", C.c_uint64),
-                ("device_ms", C.c_double), ("trace_ms", C.c_double), ("shade_ms", C.c_double)]
+                ("device_ms", C.c_double), ("trace_ms", C.c_double), ("shade_ms", C.c_double),
+                ("regen_ms", C.c_double)]
 
 
 EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",

@@ -23,7 +23,8 @@ CLI = os.path.join(HERE, "nori_b200")
 NVCC = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 CXX = shutil.which("g++") or "g++"
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"] + ARCH
+NVCC_FLAGS = (["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"] + ARCH
+              + os.environ.get("NB_NVCC_EXTRA", "").split())
 # the traversal TU must not contract a*b+c into FMA: hit parity with the x86-64 reference
 PER_FILE = {"nb_trace.cu": ["-fmad=false"]}
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-ffp-contract=off", "-pthread"]

@@ -128,10 +128,9 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     }
     if (s->n_emitters && !s->emitter_cdf) return nb_fail(ctx, NB_E_INVALID, "emitter_cdf missing");
 
-    nb_render_free(ctx);
     nb_free_list(ctx->scene_allocs);
     nb_free_list(ctx->bvh_allocs);
-    ctx->scene_ready = ctx->bvh_ready = false;
+    ctx->scene_ready = ctx->bvh_ready = ctx->render_begun = false;
     ctx->dev = NbDeviceScene();
 
     ctx->h_shapes.assign(s->shapes, s->shapes + s->n_shapes);

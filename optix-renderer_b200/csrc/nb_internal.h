@@ -53,7 +53,7 @@ struct nb_ctx {
     std::vector<uint32_t> h_faces;
     std::vector<uint32_t> h_shape_prim_offset;   /* BVH::m_shapeOffset */
     std::vector<uint32_t> h_slot_tag, h_slot_prim; /* per leaf-order slot: shape tag, local prim */
-    bool scene_ready = false, bvh_ready = false;
+    bool scene_ready = false, bvh_ready = false, render_begun = false;
     NbDeviceScene dev;
     std::vector<void *> scene_allocs, bvh_allocs;
     NbRenderState *render = nullptr;

@@ -101,24 +101,24 @@ __device__ __forceinline__ void nb_generate_path(const NbDeviceScene &sc, const 
 struct NbShadowOut { f3 o, d, c; float mint, maxt, cand; };
 
 template <bool MIS>
-__device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbWave &w, const NbFilm &film,
-                                              const NbPlan &plan, uint32_t p, bool &emit_shadow, NbShadowOut &so) {
-    /* returns true when the path lives on into the next iteration */
+__device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbWave &w, const NbPlan &plan,
+                                              uint32_t p, bool &emit_shadow, NbShadowOut &so) {
+    /* returns true when the path lives on into the next iteration; an ended path leaves its
+     * final radiance in st0 for K_regen to splat */
+    /* every per-path vector is requested up front: one memory round trip instead of a chain of
+     * dependent ones (the loads of a path that turns out to be finished are simply unused) */
     float4 s2 = w.st2[p];
-    uint32_t flags = __float_as_uint(s2.w);
-    if (flags & NB_FLAG_EMPTY) return false;
-    float4 s0 = w.st0[p];
-    f3 Li = mk3(s0.x, s0.y, s0.z);
-    if (flags & NB_FLAG_FINALIZE) { nb_film_put(film, s2.x, s2.y, Li, w.stats); return false; }
     const float4 hit = w.hit[p];
-    const uint32_t slot = __float_as_uint(hit.w);
-    if (slot == 0xffffffffu) {              /* miss: no environment emitter in this backend yet */
-        nb_film_put(film, s2.x, s2.y, Li, w.stats);
-        return false;
-    }
-    const float4 ro = w.ray_o[p], rd = w.ray_d[p];
-    const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
+    float4 s0 = w.st0[p];
     float4 s1 = w.st1[p];
+    const float4 ro = w.ray_o[p], rd = w.ray_d[p];
+    uint4 rs = w.rng[p];
+    uint32_t flags = __float_as_uint(s2.w);
+    if (flags & (NB_FLAG_EMPTY | NB_FLAG_FINALIZE)) return false;
+    const uint32_t slot = __float_as_uint(hit.w);
+    if (slot == 0xffffffffu) return false;  /* miss: no environment emitter in this backend yet */
+    f3 Li = mk3(s0.x, s0.y, s0.z);
+    const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
     f3 thr = mk3(s1.x, s1.y, s1.z);
     float w_mats = s0.w;
     const float4 sl = __ldg(sc.slots + 3 * slot + 2);
@@ -147,7 +147,6 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
     } else if (MIS && (flags & NB_FLAG_DISCRETE)) w_mats = 1.f;
 
     const uint32_t bounce = flags >> NB_BOUNCE_SHIFT;
-    uint4 rs = w.rng[p];
     NbRng rng;
     rng.state = ((uint64_t) rs.y << 32) | rs.x;
     rng.inc = ((uint64_t) rs.z << 1) | 1u;
@@ -162,7 +161,10 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
         if (rng.next_float() > succ) die = true; else thr = thr / succ;
     }
     if (plan.max_depth && bounce >= plan.max_depth) die = true;
-    if (die || sh.bsdf < 0) { nb_film_put(film, s2.x, s2.y, Li, w.stats); return false; }
+    if (die || sh.bsdf < 0) {
+        if (sh.emitter >= 0) w.st0[p] = make_float4(Li.x, Li.y, Li.z, w_mats);
+        return false;
+    }
 
     const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
     const f3 wi = its.sh.to_local(-d);
@@ -209,61 +211,71 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
     return true;
 }
 
+#ifndef NB_SHADE_MIN_BLOCKS
+#define NB_SHADE_MIN_BLOCKS 3
+#endif
 template <bool MIS>
-__global__ void __launch_bounds__(256)
-nb_k_shade(NbDeviceScene sc, NbWave w, NbFilm film, NbPlan plan) {
-    const uint32_t n = w.counts[NB_CNT_ACTIVE_CUR];
+__global__ void __launch_bounds__(256, NB_SHADE_MIN_BLOCKS)
+nb_k_shade(NbDeviceScene sc, NbWave w, NbPlan plan) {
+    const uint32_t n = w.counts[NB_CNT_ACTIVE];
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
-    unsigned long long started = 0;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
         const uint32_t i = base + threadIdx.x;
         const bool valid = i < n;
         const uint32_t p = valid ? w.queue_cur[i] : 0u;
         bool alive = false, emit_shadow = false;
         NbShadowOut so;
-        if (valid) alive = nb_shade_path<MIS>(sc, w, film, plan, p, emit_shadow, so);
-
-        /* regeneration: dead slots claim the next camera samples (one atomic per warp) */
-        const bool want = valid && !alive;
-        const uint32_t wmask = __ballot_sync(0xffffffffu, want);
-        if (wmask) {
-            const int leader = __ffs(wmask) - 1;
-            unsigned long long first = 0;
-            if ((int) lane == leader) first = atomicAdd(&w.stats[NB_STAT_NEXT_SAMPLE], (unsigned long long) __popc(wmask));
-            first = __shfl_sync(0xffffffffu, first, leader);
-            if (want) {
-                const unsigned long long nidx = first + __popc(wmask & lt_mask);
-                if (nidx < plan.total) { nb_generate_path(sc, w, plan, p, nidx); alive = true; ++started; }
-                else w.st2[p].w = __uint_as_float(NB_FLAG_EMPTY);
-            }
-        }
-        /* compaction of the live set */
+        if (valid) alive = nb_shade_path<MIS>(sc, w, plan, p, emit_shadow, so);
+        /* warp-ballot compaction into three queues; lanes 0..2 each issue one aggregated atomic
+         * (LIVE, SHADOW, DEAD are consecutive counter words) so the three latencies overlap */
         const uint32_t amask = __ballot_sync(0xffffffffu, alive);
-        if (amask) {
-            const int leader = __ffs(amask) - 1;
-            uint32_t first = 0;
-            if ((int) lane == leader) first = atomicAdd(&w.counts_next[NB_CNT_ACTIVE_CUR], (uint32_t) __popc(amask));
-            first = __shfl_sync(0xffffffffu, first, leader);
-            if (alive) w.queue_next[first + __popc(amask & lt_mask)] = p;
-        }
-        /* NEE shadow rays for the next K_trace */
         const uint32_t smask = __ballot_sync(0xffffffffu, emit_shadow);
-        if (smask) {
-            const int leader = __ffs(smask) - 1;
-            uint32_t first = 0;
-            if ((int) lane == leader) first = atomicAdd(&w.counts_next[NB_CNT_SHADOW], (uint32_t) __popc(smask));
-            first = __shfl_sync(0xffffffffu, first, leader);
-            if (emit_shadow) {
-                const uint32_t j = first + __popc(smask & lt_mask);
-                w.sh_o[j] = make_float4(so.o.x, so.o.y, so.o.z, so.mint);
-                w.sh_d[j] = make_float4(so.d.x, so.d.y, so.d.z, so.maxt);
-                w.sh_c[j] = make_float4(so.c.x, so.c.y, so.c.z, __uint_as_float(p));
-                w.sh_w[j] = so.cand;
-            }
+        const uint32_t dmask = __ballot_sync(0xffffffffu, valid && !alive);
+        const uint32_t mine = lane == 0 ? amask : (lane == 1 ? smask : (lane == 2 ? dmask : 0u));
+        uint32_t first = 0;
+        if (mine) first = atomicAdd(&w.counts[lane], (uint32_t) __popc(mine));
+        const uint32_t first_live = __shfl_sync(0xffffffffu, first, NB_CNT_LIVE);
+        const uint32_t first_shadow = __shfl_sync(0xffffffffu, first, NB_CNT_SHADOW);
+        const uint32_t first_dead = __shfl_sync(0xffffffffu, first, NB_CNT_DEAD);
+        if (alive) w.queue_next[first_live + __popc(amask & lt_mask)] = p;
+        else if (valid) w.queue_dead[first_dead + __popc(dmask & lt_mask)] = p;
+        if (emit_shadow) {
+            const uint32_t j = first_shadow + __popc(smask & lt_mask);
+            w.sh_o[j] = make_float4(so.o.x, so.o.y, so.o.z, so.mint);
+            w.sh_d[j] = make_float4(so.d.x, so.d.y, so.d.z, so.maxt);
+            w.sh_c[j] = make_float4(so.c.x, so.c.y, so.c.z, __uint_as_float(p));
+            w.sh_w[j] = so.cand;
+        }
+    }
+}
+
+/* ---- K_regen ---------------------------------------------------------------------------------
+ * One thread per ended path: ImageBlock::put of its radiance, then the slot starts the next
+ * camera sample (renderBlock prologue + sampleRay). Sample numbers and live-queue positions
+ * follow from the thread's index in the dead queue — no atomics besides the film's. */
+__global__ void __launch_bounds__(256)
+nb_k_regen(NbDeviceScene sc, NbWave w, NbFilm film, NbPlan plan) {
+    const uint32_t n = w.counts[NB_CNT_DEAD], live = w.counts[NB_CNT_LIVE];
+    const unsigned long long sbase = ((unsigned long long) w.counts[NB_CNT_BASE_HI] << 32) | w.counts[NB_CNT_BASE_LO];
+    unsigned long long started = 0;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        const uint32_t p = w.queue_dead[j];
+        const float4 s2 = w.st2[p];
+        const float4 s0 = w.st0[p];
+        if (!(__float_as_uint(s2.w) & NB_FLAG_EMPTY)) {
+            nb_film_put(film, s2.x, s2.y, mk3(s0.x, s0.y, s0.z), w.stats);
+        }
+        const unsigned long long nidx = sbase + j;
+        if (nidx < plan.total) {
+            nb_generate_path(sc, w, plan, p, nidx);
+            w.queue_next[live + j] = p;
+            ++started;
+        } else {
+            w.st2[p].w = __uint_as_float(NB_FLAG_EMPTY);
         }
     }
     for (int off = 16; off; off >>= 1) started += __shfl_xor_sync(0xffffffffu, started, off);
-    if (lane == 0 && started) atomicAdd(&w.stats[NB_STAT_SAMPLES], started);
+    if ((threadIdx.x & 31) == 0 && started) atomicAdd(&w.stats[NB_STAT_SAMPLES], started);
 }
 
 __global__ void nb_k_pool_init(NbWave w, uint32_t n_live) {
@@ -273,12 +285,8 @@ __global__ void nb_k_pool_init(NbWave w, uint32_t n_live) {
         w.ray_o[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         w.ray_d[i] = make_float4(0.f, 0.f, 1.f, -1.f);
     }
-    if (i < n_live) ((uint32_t *) w.queue_cur)[i] = i;
-    if (i == 0) {
-        w.counts[NB_CNT_ACTIVE_CUR] = n_live; w.counts[NB_CNT_SHADOW] = 0;
-        w.counts_next[NB_CNT_ACTIVE_CUR] = 0; w.counts_next[NB_CNT_SHADOW] = 0;
-        w.stats[NB_STAT_NEXT_SAMPLE] = 0;
-    }
+    if (i < n_live) w.queue_dead[i] = i;            /* every slot starts as an ended, empty path */
+    if (i < NB_CNT_WORDS) { w.counts[i] = (i == NB_CNT_DEAD) ? n_live : 0u; w.counts_next[i] = 0u; }
 }
 
 /* ImageBlock::toBitmap + Color4f::divideByFilterWeight (block.cpp:76-82, color.h:113-118) */
@@ -306,7 +314,7 @@ struct NbRenderState {
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_batch[2] = { nullptr, nullptr };
     nb_counters totals;
     int grid = 0;
-    std::vector<cudaEvent_t> prof_events;   /* "profile" option: 3 per iteration (before shade, between, after trace) */
+    std::vector<cudaEvent_t> prof_events;   /* "profile" option: 4 per iteration (shade | regen | trace) */
 };
 
 int nb_render_free(nb_ctx *ctx) {
@@ -347,19 +355,31 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     const nb_camera &cam = ctx->dev.camera;
     if (cam.width == 0 || cam.height == 0) return nb_fail(ctx, NB_E_INVALID, "camera has no output size");
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t pool = params->pool_paths ? params->pool_paths : (1u << 20);
+    pool = (pool + 255u) & ~255u;
+    const uint32_t border = (uint32_t) ceilf(params->filter_radius - 0.5f);      /* block.cpp:57 */
+    if (ctx->render && ctx->render->wave.pool == pool && ctx->render->film.rows == cam.height + 2 * border &&
+        ctx->render->film.cols == cam.width + 2 * border) {
+        /* same geometry as the previous render: keep the device buffers, start a fresh film */
+        NbRenderState *r = ctx->render;
+        r->params = *params;
+        r->film.border = border; r->film.radius = params->filter_radius;
+        r->film.lookup = NB_FILTER_RESOLUTION / params->filter_radius;
+        memcpy(r->film.table, params->filter_table, sizeof(r->film.table));
+        ctx->render_begun = true;
+        return nb_film_clear(ctx);
+    }
     nb_render_free(ctx);
     NbRenderState *r = new NbRenderState();
     ctx->render = r;
     r->params = *params;
     memset(&r->totals, 0, sizeof(r->totals));
-    r->film.border = (uint32_t) ceilf(params->filter_radius - 0.5f);             /* block.cpp:57 */
+    r->film.border = border;
     r->film.rows = cam.height + 2 * r->film.border;
     r->film.cols = cam.width + 2 * r->film.border;
     r->film.radius = params->filter_radius;
     r->film.lookup = NB_FILTER_RESOLUTION / params->filter_radius;               /* block.cpp:65 */
     memcpy(r->film.table, params->filter_table, sizeof(r->film.table));
-    uint32_t pool = params->pool_paths ? params->pool_paths : (1u << 20);
-    pool = (pool + 255u) & ~255u;
     int rc;
     if ((rc = nb_dev_alloc(ctx, r, &r->film.data, (size_t) r->film.rows * r->film.cols))) return rc;
     NbWave &w = r->wave;
@@ -370,7 +390,7 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
         (rc = nb_dev_alloc(ctx, r, &w.rng, pool)) || (rc = nb_dev_alloc(ctx, r, &w.sh_o, pool)) ||
         (rc = nb_dev_alloc(ctx, r, &w.sh_d, pool)) || (rc = nb_dev_alloc(ctx, r, &w.sh_c, pool)) ||
         (rc = nb_dev_alloc(ctx, r, &w.sh_w, pool)) || (rc = nb_dev_alloc(ctx, r, &r->queue[0], pool)) ||
-        (rc = nb_dev_alloc(ctx, r, &r->queue[1], pool)) || (rc = nb_dev_alloc(ctx, r, &r->counts, 2 * NB_CNT_WORDS)) ||
+        (rc = nb_dev_alloc(ctx, r, &r->queue[1], pool)) || (rc = nb_dev_alloc(ctx, r, &w.queue_dead, pool)) || (rc = nb_dev_alloc(ctx, r, &r->counts, 2 * NB_CNT_WORDS)) ||
         (rc = nb_dev_alloc(ctx, r, &r->stats, NB_STAT_WORDS)))
         return rc;
     w.stats = r->stats;
@@ -385,11 +405,12 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     NB_CUDA(ctx, cudaMemsetAsync(r->counts, 0, 2 * NB_CNT_WORDS * sizeof(uint32_t), ctx->stream));
     r->grid = ctx->sm_count * 8;
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->render_begun = true;
     return NB_OK;
 }
 
 int nb_film_clear(nb_ctx *ctx) {
-    if (!ctx || !ctx->render) return nb_fail(ctx, NB_E_STATE, "nb_film_clear: no render in progress");
+    if (!ctx || !ctx->render || !ctx->render_begun) return nb_fail(ctx, NB_E_STATE, "nb_film_clear: no render in progress");
     NbRenderState *r = ctx->render;
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
     NB_CUDA(ctx, cudaMemsetAsync(r->film.data, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
@@ -402,7 +423,7 @@ int nb_film_clear(nb_ctx *ctx) {
  * (main rays + the shadow rays K_shade just made). The host never reads a queue length to size
  * a launch; it only polls "anything left?" one batch behind the GPU. */
 int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t stride, uint32_t offset) {
-    if (!ctx || !ctx->render) return nb_fail(ctx, NB_E_STATE, "nb_render_subframe: call nb_render_begin first");
+    if (!ctx || !ctx->render || !ctx->render_begun) return nb_fail(ctx, NB_E_STATE, "nb_render_subframe: call nb_render_begin first");
     if (stride == 0 || offset >= stride) return nb_fail(ctx, NB_E_INVALID, "nb_render_subframe: bad sample slice %u/%u", offset, stride);
     NbRenderState *r = ctx->render;
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -418,11 +439,12 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     if (plan.total == 0) { cudaEventRecord(r->ev_end, ctx->stream); return NB_OK; }
     NbWave w = r->wave;
     const uint32_t n_live = (uint32_t) std::min<unsigned long long>(w.pool, plan.total);
+    w.total_samples = plan.total;
     w.queue_cur = r->queue[0]; w.queue_next = r->queue[1];
     w.counts = r->counts; w.counts_next = r->counts + NB_CNT_WORDS;
     nb_k_pool_init<<<(w.pool + 255) / 256, 256, 0, ctx->stream>>>(w, n_live);
     const bool mis = r->params.integrator == NB_INTEGRATOR_PATH_MIS;
-    const int BATCH = 8;
+    const int BATCH = 8;                      /* even: after a batch, "next" inputs sit in set 0 */
     uint64_t iter = 0, launches = 1;
     int pending[2] = { 0, 0 };
     bool done = false;
@@ -440,17 +462,18 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
             ws.queue_cur = r->queue[a]; ws.queue_next = r->queue[b];
             ws.counts = r->counts + a * NB_CNT_WORDS; ws.counts_next = r->counts + b * NB_CNT_WORDS;
             prof_mark();
-            if (mis) nb_k_shade<true><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, r->film, plan);
-            else nb_k_shade<false><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, r->film, plan);
+            if (iter > 0) {                   /* the first iteration only has empty slots to fill */
+                if (mis) nb_k_shade<true><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, plan);
+                else nb_k_shade<false><<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, plan);
+                ++launches;
+            }
             prof_mark();
-            NbWave wt = w;
-            wt.queue_cur = r->queue[b]; wt.queue_next = r->queue[a];
-            wt.counts = r->counts + b * NB_CNT_WORDS; wt.counts_next = r->counts + a * NB_CNT_WORDS;
-            nb_launch_trace_wave(ctx->dev, wt, r->grid, ctx->stream);
+            nb_k_regen<<<r->grid, 256, 0, ctx->stream>>>(ctx->dev, ws, r->film, plan);
+            prof_mark();
+            nb_launch_trace_wave(ctx->dev, ws, r->grid, ctx->stream);
             prof_mark();
             launches += 2;
         }
-        /* after an even number of iterations the live count for the next K_shade is in set 0 */
         const int slot = batch & 1;
         cudaMemcpyAsync(r->h_counts + slot * 2 * NB_CNT_WORDS, r->counts, 2 * NB_CNT_WORDS * sizeof(uint32_t),
                         cudaMemcpyDeviceToHost, ctx->stream);
@@ -460,7 +483,7 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
         if (pending[prev]) {
             NB_CUDA(ctx, cudaEventSynchronize(r->ev_batch[prev]));
             pending[prev] = 0;
-            if (r->h_counts[prev * 2 * NB_CNT_WORDS + NB_CNT_ACTIVE_CUR] == 0) done = true;
+            if (r->h_counts[prev * 2 * NB_CNT_WORDS + NB_CNT_ACTIVE] == 0) done = true;
         }
         if (!done && batch > (1 << 22)) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: wavefront did not drain");
     }
@@ -471,14 +494,15 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: %s", cudaGetErrorString(e));
     /* the last polled batch may be stale by one: verify the queue really drained */
     NB_CUDA(ctx, cudaMemcpy(r->h_counts, r->counts, 2 * NB_CNT_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost));
-    if (r->h_counts[NB_CNT_ACTIVE_CUR] != 0) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: internal: live paths left");
+    if (r->h_counts[NB_CNT_ACTIVE] != 0) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: internal: live paths left");
     float ms = 0.f;
     cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end);
-    for (size_t k = 0; k + 2 < prof_used + 0 && prof; k += 3) {
-        float a = 0.f, b = 0.f;
+    for (size_t k = 0; prof && k + 3 < prof_used; k += 4) {
+        float a = 0.f, b = 0.f, c = 0.f;
         cudaEventElapsedTime(&a, r->prof_events[k], r->prof_events[k + 1]);
         cudaEventElapsedTime(&b, r->prof_events[k + 1], r->prof_events[k + 2]);
-        r->totals.shade_ms += a; r->totals.trace_ms += b;
+        cudaEventElapsedTime(&c, r->prof_events[k + 2], r->prof_events[k + 3]);
+        r->totals.shade_ms += a; r->totals.regen_ms += b; r->totals.trace_ms += c;
     }
     r->totals.device_ms += ms;
     r->totals.iterations += iter;

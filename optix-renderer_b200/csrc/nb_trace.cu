@@ -39,20 +39,30 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
  * Grid-stride over counts read from device memory, so the host never waits on them. */
 __global__ void __launch_bounds__(256)
 nb_k_trace_wave(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes, NbWave w) {
-    const uint32_t n_main = w.counts[NB_CNT_ACTIVE_CUR], n_sh = w.counts[NB_CNT_SHADOW];
+    /* live paths = survivors of K_shade + the paths K_regen could start within the sample budget */
+    const unsigned long long base = ((unsigned long long) w.counts[NB_CNT_BASE_HI] << 32) | w.counts[NB_CNT_BASE_LO];
+    const unsigned long long left = w.total_samples - base;
+    const uint32_t n_dead = w.counts[NB_CNT_DEAD];
+    const uint32_t n_regen = left < n_dead ? (uint32_t) left : n_dead;
+    const uint32_t n_main = w.counts[NB_CNT_LIVE] + n_regen, n_sh = w.counts[NB_CNT_SHADOW];
     const uint32_t total = n_main + n_sh;
-    /* the other counter set is idle during this launch: clear it for the K_shade that follows */
-    if (blockIdx.x == 0 && threadIdx.x == 0) { w.counts_next[NB_CNT_ACTIVE_CUR] = 0; w.counts_next[NB_CNT_SHADOW] = 0; }
+    /* the other counter set is idle during this launch: publish the next iteration's inputs there */
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const unsigned long long nb = base + n_regen;
+        w.counts_next[NB_CNT_LIVE] = 0; w.counts_next[NB_CNT_SHADOW] = 0; w.counts_next[NB_CNT_DEAD] = 0;
+        w.counts_next[NB_CNT_ACTIVE] = n_main;
+        w.counts_next[NB_CNT_BASE_LO] = (uint32_t) nb; w.counts_next[NB_CNT_BASE_HI] = (uint32_t) (nb >> 32);
+    }
     unsigned long long closest = 0, any = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         if (i < n_main) {
-            const uint32_t p = w.queue_cur[i];
+            const uint32_t p = w.queue_next[i];
             const float4 ro = w.ray_o[p], rd = w.ray_d[p];
             NbHit hit;
             nb_traverse<false>(nodes, slots, n_nodes, make_float3(ro.x, ro.y, ro.z), make_float3(rd.x, rd.y, rd.z),
                                ro.w, rd.w, hit);
             w.hit[p] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot));
-            ++closest;
+            if (!(rd.w < ro.w)) ++closest;      /* ended paths park their ray with maxt < mint */
         } else {
             const uint32_t j = i - n_main;
             const float4 ro = w.sh_o[j], rd = w.sh_d[j], c = w.sh_c[j];

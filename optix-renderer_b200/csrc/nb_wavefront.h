@@ -8,6 +8,9 @@
  *   st1   {throughput.rgb, pdfmat}                       path_mis.cpp:19; bsdf->pdf of the last sample
  *   st2   {pixelSample.x, pixelSample.y, w_ems, bits(flags | bounce << 8)}
  *   rng   {state lo, state hi, pixel index, sample index}   pcg32 (inc derives from the pixel)
+ * Iteration = K_shade (consume hits, shade, NEE, RR; compact survivors / NEE rays / ended paths
+ * into three queues) -> K_regen (splat ended paths into the film, start new camera paths in
+ * their slots) -> K_trace (closest hit for every live path + any-hit for the NEE rays).
  * Shadow-ray queue (written by K_shade, resolved by the next K_trace):
  *   sh_o, sh_d as above; sh_c {t*Li_EMS rgb, bits(path slot)}; sh_w candidate w_ems (<0: keep)
  */
@@ -15,9 +18,13 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-enum { NB_CNT_ACTIVE_CUR = 0, NB_CNT_SHADOW = 1, NB_CNT_WORDS = 4 };
+/* One counter set per iteration parity. K_shade fills LIVE/SHADOW/DEAD (warp-aggregated atomics);
+ * K_regen and K_trace read them; K_trace publishes ACTIVE and SAMPLE_BASE for the next iteration
+ * into the other set and clears that set's LIVE/SHADOW/DEAD. */
+enum { NB_CNT_LIVE = 0, NB_CNT_SHADOW = 1, NB_CNT_DEAD = 2, NB_CNT_ACTIVE = 3, NB_CNT_BASE_LO = 4, NB_CNT_BASE_HI = 5,
+       NB_CNT_WORDS = 8 };
 enum { NB_STAT_RAYS_CLOSEST = 0, NB_STAT_RAYS_ANY = 1, NB_STAT_SAMPLES = 2, NB_STAT_INVALID = 3,
-       NB_STAT_NEXT_SAMPLE = 4, NB_STAT_WORDS = 8 };
+       NB_STAT_WORDS = 8 };
 
 #define NB_FLAG_EMPTY      1u    /* slot holds no path: nothing to splat */
 #define NB_FLAG_FINALIZE   2u    /* path ended (throughput became 0): splat and regenerate */
@@ -31,10 +38,12 @@ struct NbWave {
     uint4  *rng;
     float4 *sh_o, *sh_d, *sh_c;
     float  *sh_w;
-    const uint32_t *queue_cur;   /* live path slots this iteration */
-    uint32_t *queue_next;
-    uint32_t *counts;            /* this iteration's {active, shadow} */
-    uint32_t *counts_next;       /* being filled for the next iteration */
+    const uint32_t *queue_cur;   /* live path slots K_shade consumes this iteration */
+    uint32_t *queue_next;        /* survivors (K_shade) then regenerated paths (K_regen); K_trace reads it */
+    uint32_t *queue_dead;        /* slots whose path ended: K_shade -> K_regen */
+    uint32_t *counts;            /* this iteration's counter set */
+    uint32_t *counts_next;       /* the other set (published by K_trace) */
+    unsigned long long total_samples;   /* camera samples of this subframe */
     unsigned long long *stats;   /* NB_STAT_* */
     uint32_t pool;
 };
