@@ -153,11 +153,7 @@ def main():
     ctx = nb.Context(local)
     ctx.load(scene)
     ctx.render_begin(params)
-    ptr, nfl = ctx.film_device_ptr()
-
-    class _Alias:
-        __cuda_array_interface__ = {"shape": (nfl,), "typestr": "<f4", "data": (ptr, False), "version": 3}
-    film = torch.as_tensor(_Alias(), device="cuda:%d" % local)
+    film = nb.film_tensor(ctx, local)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
 
     def barrier():
@@ -168,8 +164,7 @@ def main():
     def step():
         ctx.film_clear()
         ctx.render_subframe(0, args.spp * world, world, rank)
-        if world > 1:
-            dist.reduce(film, dst=0, op=dist.ReduceOp.SUM)
+        nb.reduce_film(film, dst=0)
 
     for _ in range(args.warmup):
         step()
@@ -209,11 +204,7 @@ def main():
         ctx.load(scene)                              # H2D: scene arrays + BVH, through the C ABI
         ctx.render_begin(params)
         ctx.render_subframe(0, args.spp * world, world, rank)
-        if world > 1:
-            p2, n2 = ctx.film_device_ptr()
-            class _A2:
-                __cuda_array_interface__ = {"shape": (n2,), "typestr": "<f4", "data": (p2, False), "version": 3}
-            dist.reduce(torch.as_tensor(_A2(), device="cuda:%d" % local), dst=0, op=dist.ReduceOp.SUM)
+        nb.reduce_film(nb.film_tensor(ctx, local), dst=0)
         ctx.film_download(normalize=False, out=host_film)   # D2H
         e2e_samples += ctx.counters()["samples"]
     barrier()

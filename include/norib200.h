@@ -191,6 +191,11 @@ int  nb_render_begin(nb_ctx *ctx, const nb_render_params *params);  /* allocates
  * 1,0 = all). Asynchronous: returns once the work is queued. */
 int  nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count,
                         uint32_t sample_stride, uint32_t sample_offset);
+/* Host-only helper (no device needed): which samples a (first, count, stride, offset) slice holds:
+ * *first_sample = smallest s >= first with s % stride == offset, *n_samples = how many such s lie
+ * below first+count. The slices of offsets 0..stride-1 partition [first, first+count). */
+int  nb_sample_slice(uint32_t first, uint32_t count, uint32_t stride, uint32_t offset,
+                     uint32_t *first_sample, uint32_t *n_samples);
 int  nb_sync(nb_ctx *ctx);
 int  nb_film_clear(nb_ctx *ctx);
 /* Film geometry: rows = H + 2b, cols = W + 2b, b = ceil(radius - 0.5) (block.cpp:57,73). */

@@ -76,7 +76,7 @@ class Counters(C.Structure):
 EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
-           "nb_get_counters", "nb_set_option"]
+           "nb_get_counters", "nb_set_option", "nb_sample_slice"]
 
 _lib = None
 
@@ -114,6 +114,7 @@ def load_library(path=None):
     lib.nb_film_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.nb_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
     lib.nb_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
+    lib.nb_sample_slice.argtypes = [C.c_uint32] * 4 + [C.POINTER(C.c_uint32)] * 2
     if path == LIB_PATH:
         _lib = lib
     return lib
@@ -285,3 +286,32 @@ def make_render_params(scene, integrator="path_mis", seed=0, pool_paths=0, max_d
     p["pool_paths"] = pool_paths
     p["max_depth"] = max_depth
     return p
+
+
+def sample_slice(first, count, stride, offset):
+    """(first_sample, n_samples) of one rank's slice — nb_sample_slice, host only."""
+    a, b = C.c_uint32(), C.c_uint32()
+    rc = load_library().nb_sample_slice(first, count, stride, offset, C.byref(a), C.byref(b))
+    if rc != NB_OK:
+        raise NbError(rc, "bad sample slice %d/%d" % (offset, stride))
+    return a.value, b.value
+
+
+# ---- multi-GPU plumbing (torch.distributed; NCCL on GPUs, gloo in the CPU tests) ----------------
+def film_tensor(ctx, device_index):
+    """torch tensor aliasing the context's film accumulators (no copy)."""
+    import torch
+    ptr, n = ctx.film_device_ptr()
+
+    class _Alias:
+        __cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3}
+    return torch.as_tensor(_Alias(), device="cuda:%d" % device_index)
+
+
+def reduce_film(film, dst=0):
+    """The path's only collective: sum of the per-rank accumulators (sum w*rgb, sum w) on rank
+    dst. Linear film (block.cpp:120-122) => the N-rank image is the 1-rank image of all samples."""
+    import torch.distributed as dist
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
+    return film

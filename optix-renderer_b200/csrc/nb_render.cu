@@ -409,6 +409,15 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     return NB_OK;
 }
 
+int nb_sample_slice(uint32_t first, uint32_t count, uint32_t stride, uint32_t offset, uint32_t *first_sample, uint32_t *n_samples) {
+    if (stride == 0 || offset >= stride) return NB_E_INVALID;
+    const uint64_t s0 = (uint64_t) first + ((offset + stride - first % stride) % stride);
+    const uint64_t end = (uint64_t) first + count;
+    if (first_sample) *first_sample = (uint32_t) s0;
+    if (n_samples) *n_samples = s0 < end ? (uint32_t) ((end - s0 + stride - 1) / stride) : 0u;
+    return NB_OK;
+}
+
 int nb_film_clear(nb_ctx *ctx) {
     if (!ctx || !ctx->render || !ctx->render_begun) return nb_fail(ctx, NB_E_STATE, "nb_film_clear: no render in progress");
     NbRenderState *r = ctx->render;
@@ -428,9 +437,8 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     NbRenderState *r = ctx->render;
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
     const nb_camera &cam = ctx->dev.camera;
-    /* samples s in [first, first+count) with s % stride == offset */
-    uint32_t s0 = first + ((offset + stride - first % stride) % stride);
-    uint32_t passes = (s0 < first + count) ? (first + count - s0 + stride - 1) / stride : 0;
+    uint32_t s0 = 0, passes = 0;
+    nb_sample_slice(first, count, stride, offset, &s0, &passes);
     NbPlan plan;
     plan.npix = cam.width * cam.height; plan.width = cam.width;
     plan.total = (unsigned long long) passes * plan.npix;
