@@ -315,3 +315,35 @@ def reduce_film(film, dst=0):
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
     return film
+
+
+# ---- host library (C++ mirror of the Nori scene/plugin surface) ------------------------------------
+_host = None
+
+
+def load_host_library():
+    global _host
+    if _host is None:
+        if not os.path.exists(HOST_LIB_PATH):
+            raise FileNotFoundError("%s is not built: run `python optix-renderer_b200/build.py`" % HOST_LIB_PATH)
+        load_library()                      # libnorib200_host.so links against libnorib200.so
+        _host = C.CDLL(HOST_LIB_PATH)
+        _host.nbh_last_error.restype = C.c_char_p
+        _host.nbh_flatten_xml.argtypes = [C.c_char_p, C.c_char_p]
+        _host.nbh_parse_xml.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+    return _host
+
+
+def load_xml(xml_path, nbs_path=None):
+    """Scene XML -> flattened scene dict, through the C++ host loader (parser, OBJ loader, plugin
+    flatten hooks, SAH BVH build). Raises NbError(NB_E_UNSUPPORTED) for plugins without a kernel."""
+    import tempfile
+    h = load_host_library()
+    tmp = nbs_path or os.path.join(tempfile.mkdtemp(prefix="nbs_"), "scene.nbs")
+    rc = h.nbh_flatten_xml(os.fsencode(xml_path), os.fsencode(tmp))
+    if rc != 0:
+        raise NbError(rc, h.nbh_last_error().decode())
+    s = read_nbs(tmp)
+    if nbs_path is None:
+        os.remove(tmp)
+    return s

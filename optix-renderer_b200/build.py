@@ -92,10 +92,10 @@ def build_host(verbose=False):
         else:
             objs.append(obj)
     if objs and _newer(LIB_HOST, objs):
-        _run([CXX, "-shared", "-o", LIB_HOST] + objs + ["-pthread", "-static-libstdc++", "-static-libgcc"], verbose)
+        _run([CXX, "-shared", "-o", LIB_HOST] + objs + ["-L", HERE, "-lnorib200", "-Wl,-rpath,$ORIGIN", "-pthread"], verbose)
     if main_obj and _newer(CLI, [main_obj, LIB_HOST, LIB_CUDA]):
         _run([CXX, "-o", CLI, main_obj, "-L", HERE, "-lnorib200_host", "-lnorib200", "-Wl,-rpath,$ORIGIN",
-              "-pthread", "-ldl", "-static-libstdc++", "-static-libgcc"], verbose)
+              "-pthread", "-ldl"], verbose)
     return LIB_HOST
 
 

@@ -1,0 +1,32 @@
+/* b200state.h — the backend object with OptixState's call shape
+ * (include/nori/optix/OptixState.h:88-109), forwarding to the C ABI of include/norib200.h. */
+#pragma once
+#include "plugins.h"
+
+namespace nori {
+
+class B200State {
+public:
+    explicit B200State(int device = 0);
+    ~B200State();
+    B200State(const B200State &) = delete;
+    /* OptixState::preRender (OptixState.render.cpp:19-85): flatten + upload + BVH + film setup.
+     * false = the scene uses a plugin without a GPU kernel (the caller renders on its CPU path). */
+    bool preRender(const Scene &scene, uint64_t seed = 0, uint32_t poolPaths = 0);
+    /* OptixState::renderSubframe (OptixState.cpp:485-510) */
+    void renderSubframe(uint32_t currentSample, uint32_t samplesPerLaunch, uint32_t stride = 1, uint32_t offset = 0);
+    /* accumulators in ImageBlock layout (rows x cols x {sum w*rgb, sum w}) or the normalised bitmap */
+    void download(std::vector<float> &out, bool normalize, uint32_t *rows = nullptr, uint32_t *cols = nullptr);
+    void clear();                                   /* OptixState::clear */
+    nb_counters counters() const;
+    const FlatScene &flat() const { return m_flat; }
+    const std::string &whyUnsupported() const { return m_why; }
+    nb_ctx *handle() const { return m_ctx; }
+private:
+    void check(int rc) const;
+    nb_ctx *m_ctx = nullptr;
+    FlatScene m_flat;
+    std::string m_why;
+};
+
+} // namespace nori

@@ -1,0 +1,84 @@
+/* main.cpp — nori_b200: command-line renderer. Plays the role of RenderThread's render loop
+ * (src/utils/render.cpp:232-419 with the GPU thread of :462-574): load XML, preRender, subframes
+ * of samplesPerLaunch until the sampler's sampleCount is reached, save. Output is .npy (H x W x 3
+ * float32) or .pfm — the reference's EXR writer needs OpenEXR, which this build does not carry. */
+#include "b200state.h"
+#include <chrono>
+#include <cstring>
+#include <memory>
+
+using namespace nori;
+
+static void writeNpy(const std::string &path, const float *data, size_t h, size_t w, size_t c) {
+    std::string hdr = "{'descr': '<f4', 'fortran_order': False, 'shape': (" + std::to_string(h) + ", " + std::to_string(w) + ", " + std::to_string(c) + "), }";
+    while ((10 + hdr.size() + 1) % 64) hdr += ' ';
+    hdr += '\n';
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) throw NoriException("cannot write %s", path);
+    const unsigned char magic[8] = { 0x93, 'N', 'U', 'M', 'P', 'Y', 1, 0 };
+    fwrite(magic, 1, 8, f);
+    const uint16_t hl = (uint16_t) hdr.size();
+    fwrite(&hl, 2, 1, f);
+    fwrite(hdr.data(), 1, hdr.size(), f);
+    fwrite(data, 4, h * w * c, f);
+    fclose(f);
+}
+
+static void writePfm(const std::string &path, const float *data, size_t h, size_t w) {
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) throw NoriException("cannot write %s", path);
+    fprintf(f, "PF\n%zu %zu\n-1.0\n", w, h);
+    for (size_t y = h; y-- > 0;) fwrite(data + y * w * 3, 4, w * 3, f);      /* PFM is bottom-up */
+    fclose(f);
+}
+
+int main(int argc, char **argv) {
+    if (argc < 3) {
+        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D] [seed=S] [launch=N] [flat=scene.nbs]\n");
+        return 2;
+    }
+    try {
+        int spp = -1, device = 0, launch = 0;
+        uint64_t seed = 0;
+        std::string flatOut;
+        for (int i = 3; i < argc; ++i) {
+            if (!strncmp(argv[i], "spp=", 4)) spp = atoi(argv[i] + 4);
+            else if (!strncmp(argv[i], "device=", 7)) device = atoi(argv[i] + 7);
+            else if (!strncmp(argv[i], "seed=", 5)) seed = strtoull(argv[i] + 5, nullptr, 10);
+            else if (!strncmp(argv[i], "launch=", 7)) launch = atoi(argv[i] + 7);
+            else if (!strncmp(argv[i], "flat=", 5)) flatOut = argv[i] + 5;
+        }
+        auto t0 = std::chrono::steady_clock::now();
+        std::unique_ptr<NoriObject> root(loadFromXML(argv[1]));
+        if (root->getClassType() != NoriObject::EScene) throw NoriException("root of %s is not a scene", argv[1]);
+        Scene *scene = static_cast<Scene *>(root.get());
+        B200State state(device);
+        if (!state.preRender(*scene, seed)) {
+            fprintf(stderr, "nori_b200: this scene cannot run on the GPU backend: %s\n", state.whyUnsupported().c_str());
+            return 3;
+        }
+        if (!flatOut.empty()) state.flat().writeNbs(flatOut);
+        if (spp < 0) spp = (int) scene->getSampler()->getSampleCount();
+        if (launch <= 0) launch = spp;
+        double load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        auto t1 = std::chrono::steady_clock::now();
+        for (int s = 0; s < spp; s += launch) state.renderSubframe((uint32_t) s, (uint32_t) std::min(launch, spp - s));
+        double render_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
+        std::vector<float> img;
+        uint32_t h = 0, w = 0;
+        state.download(img, true, &h, &w);
+        std::string out(argv[2]);
+        if (out.size() > 4 && out.substr(out.size() - 4) == ".pfm") writePfm(out, img.data(), h, w); else writeNpy(out, img.data(), h, w, 3);
+        nb_counters c = state.counters();
+        printf("{\"scene\": \"%s\", \"width\": %u, \"height\": %u, \"spp\": %d, \"load_seconds\": %.3f, \"seconds\": %.6f, "
+               "\"samples\": %llu, \"samples_per_s\": %.1f, \"rays_closest\": %llu, \"rays_any\": %llu, \"rays_per_s\": %.1f, "
+               "\"device_ms\": %.3f, \"invalid_samples\": %llu}\n",
+               argv[1], w, h, spp, load_s, render_s, (unsigned long long) c.samples, c.samples / render_s,
+               (unsigned long long) c.rays_closest, (unsigned long long) c.rays_any, (c.rays_closest + c.rays_any) / render_s,
+               c.device_ms, (unsigned long long) c.invalid_samples);
+        return 0;
+    } catch (const std::exception &e) {
+        fprintf(stderr, "nori_b200: %s\n", e.what());
+        return 1;
+    }
+}

@@ -1,0 +1,302 @@
+/* plugins.cpp — BSDF / emitter / camera / filter / integrator / sampler / sphere plugins.
+ * Each constructor reads the properties the reference's constructor reads, with its defaults
+ * (file:line beside each class); each flatten hook fills the matching C-ABI record. */
+#include "plugins.h"
+#include <cstring>
+
+namespace nori {
+
+static thread_local std::string g_resolveRoot;
+void setResolveRoot(const std::string &dir) { g_resolveRoot = dir; }
+std::string resolvePath(const std::string &rel) {
+    if (rel.empty() || rel[0] == '/' || g_resolveRoot.empty()) return rel;
+    return g_resolveRoot + "/" + rel;
+}
+
+/* ---- BSDFs ------------------------------------------------------------------------------------- */
+class Diffuse : public BSDF {                       /* src/bsdf/diffuse.cpp:31-60: albedo default 0.5 */
+public:
+    explicit Diffuse(const PropertyList &p) : m_albedo(p.getColor("albedo", Color3f(0.5f))) {}
+    void addChild(NoriObject *obj) override {
+        /* textured albedo (diffuse.cpp:62-91) has no kernel yet */
+        if (obj->getClassType() == ETexture) { m_textured = true; delete obj; return; }
+        BSDF::addChild(obj);
+    }
+    bool getB200MaterialData(nb_bsdf &o) const override {
+        if (m_textured) return false;
+        memset(&o, 0, sizeof(o));
+        o.type = NB_BSDF_DIFFUSE;
+        for (int i = 0; i < 3; ++i) o.albedo[i] = m_albedo[i];
+        return true;
+    }
+    std::string toString() const override { return NoriException::format("Diffuse[albedo=[%f, %f, %f]]", m_albedo[0], m_albedo[1], m_albedo[2]); }
+private:
+    Color3f m_albedo;
+    bool m_textured = false;
+};
+NORI_REGISTER_CLASS(Diffuse, "diffuse")
+
+class Mirror : public BSDF {                        /* src/bsdf/mirror.cpp */
+public:
+    explicit Mirror(const PropertyList &) {}
+    bool getB200MaterialData(nb_bsdf &o) const override { memset(&o, 0, sizeof(o)); o.type = NB_BSDF_MIRROR; return true; }
+    std::string toString() const override { return "Mirror[]"; }
+};
+NORI_REGISTER_CLASS(Mirror, "mirror")
+
+class Dielectric : public BSDF {                    /* src/bsdf/dielectric.cpp:28-35 */
+public:
+    explicit Dielectric(const PropertyList &p)
+        : m_intIOR(p.getFloat("intIOR", 1.5046f)), m_extIOR(p.getFloat("extIOR", 1.000277f)) {}
+    bool getB200MaterialData(nb_bsdf &o) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_BSDF_DIELECTRIC; o.int_ior = m_intIOR; o.ext_ior = m_extIOR;
+        return true;
+    }
+    std::string toString() const override { return NoriException::format("Dielectric[intIOR=%f, extIOR=%f]", m_intIOR, m_extIOR); }
+private:
+    float m_intIOR, m_extIOR;
+};
+NORI_REGISTER_CLASS(Dielectric, "dielectric")
+
+class Microfacet : public BSDF {                    /* src/bsdf/microfacet.cpp:33-53 */
+public:
+    explicit Microfacet(const PropertyList &p)
+        : m_alpha(p.getFloat("alpha", 0.1f)), m_intIOR(p.getFloat("intIOR", 1.5046f)),
+          m_extIOR(p.getFloat("extIOR", 1.000277f)), m_kd(p.getColor("kd", Color3f(0.5f))) {
+        m_ks = 1 - m_kd.maxCoeff();
+    }
+    bool getB200MaterialData(nb_bsdf &o) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_BSDF_MICROFACET; o.alpha = m_alpha; o.int_ior = m_intIOR; o.ext_ior = m_extIOR; o.ks = m_ks;
+        for (int i = 0; i < 3; ++i) o.albedo[i] = m_kd[i];
+        return true;
+    }
+    std::string toString() const override { return NoriException::format("Microfacet[alpha=%f, intIOR=%f, extIOR=%f, ks=%f]", m_alpha, m_intIOR, m_extIOR, m_ks); }
+private:
+    float m_alpha, m_intIOR, m_extIOR, m_ks;
+    Color3f m_kd;
+};
+NORI_REGISTER_CLASS(Microfacet, "microfacet")
+
+/* A plugin the parser must accept so scenes load, but for which the backend has no kernel:
+ * flatten() reports it and the caller keeps its CPU path. */
+class UnsupportedBSDF : public BSDF {
+public:
+    explicit UnsupportedBSDF(const PropertyList &) {}
+    void addChild(NoriObject *obj) override { delete obj; }
+    bool getB200MaterialData(nb_bsdf &) const override { return false; }
+    std::string toString() const override { return "UnsupportedBSDF[]"; }
+};
+NORI_REGISTER_CLASS(UnsupportedBSDF, "disney")
+
+/* ---- emitters ---------------------------------------------------------------------------------- */
+class AreaEmitter : public Emitter {                /* src/emitters/arealight.cpp:27-33 */
+public:
+    explicit AreaEmitter(const PropertyList &p) { m_radiance = p.getColor("radiance"); lightProb = p.getFloat("lightWeight", 1.f); }
+    bool getB200EmitterData(nb_emitter &o) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_EMITTER_AREA; o.shape = -1;
+        for (int i = 0; i < 3; ++i) o.radiance[i] = m_radiance[i];
+        return true;
+    }
+    std::string toString() const override { return NoriException::format("AreaLight[radiance=[%f, %f, %f]]", m_radiance[0], m_radiance[1], m_radiance[2]); }
+};
+NORI_REGISTER_CLASS(AreaEmitter, "area")
+
+class PointLight : public Emitter {                 /* src/emitters/pointlight.cpp:14-45 */
+public:
+    explicit PointLight(const PropertyList &p) {
+        m_power = p.getColor("power"); m_position = p.getPoint3("position"); lightProb = p.getFloat("lightWeight", 1.f);
+        m_radiance = m_power / (float) (4 * M_PI);                       /* pointlight.cpp:44 */
+    }
+    bool getB200EmitterData(nb_emitter &o) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_EMITTER_POINT; o.shape = -1;
+        for (int i = 0; i < 3; ++i) { o.radiance[i] = m_radiance[i]; o.position[i] = m_position[i]; }
+        return true;
+    }
+    std::string toString() const override { return "PointLight[]"; }
+private:
+    Color3f m_power;
+    Point3f m_position;
+};
+NORI_REGISTER_CLASS(PointLight, "point")
+
+/* ---- reconstruction filters (src/cameras/rfilter.cpp) -------------------------------------------- */
+class GaussianFilter : public ReconstructionFilter {                     /* rfilter.cpp:30-47 */
+public:
+    explicit GaussianFilter(const PropertyList &p) { m_radius = p.getFloat("radius", 2.0f); m_stddev = p.getFloat("stddev", 0.5f); }
+    float eval(float x) const override {
+        float alpha = -1.0f / (2.0f * m_stddev * m_stddev);
+        return std::max(0.0f, std::exp(alpha * x * x) - std::exp(alpha * m_radius * m_radius));
+    }
+    std::string toString() const override { return NoriException::format("GaussianFilter[radius=%f, stddev=%f]", m_radius, m_stddev); }
+private:
+    float m_stddev;
+};
+NORI_REGISTER_CLASS(GaussianFilter, "gaussian")
+
+class MitchellNetravaliFilter : public ReconstructionFilter {            /* rfilter.cpp:80-113 */
+public:
+    explicit MitchellNetravaliFilter(const PropertyList &p) {
+        m_radius = p.getFloat("radius", 2.0f); m_B = p.getFloat("B", 1.0f / 3.0f); m_C = p.getFloat("C", 1.0f / 3.0f);
+    }
+    float eval(float x) const override {
+        x = std::abs(2.0f * x / m_radius);
+        float x2 = x * x, x3 = x2 * x;
+        if (x < 1) return 1.0f / 6.0f * ((12 - 9 * m_B - 6 * m_C) * x3 + (-18 + 12 * m_B + 6 * m_C) * x2 + (6 - 2 * m_B));
+        if (x < 2) return 1.0f / 6.0f * ((-m_B - 6 * m_C) * x3 + (6 * m_B + 30 * m_C) * x2 + (-12 * m_B - 48 * m_C) * x + (8 * m_B + 24 * m_C));
+        return 0.0f;
+    }
+    std::string toString() const override { return NoriException::format("MitchellNetravaliFilter[radius=%f, B=%f, C=%f]", m_radius, m_B, m_C); }
+private:
+    float m_B, m_C;
+};
+NORI_REGISTER_CLASS(MitchellNetravaliFilter, "mitchell")
+
+class TentFilter : public ReconstructionFilter {                         /* rfilter.cpp:129-141 */
+public:
+    explicit TentFilter(const PropertyList &) { m_radius = 1.0f; }
+    float eval(float x) const override { return std::max(0.0f, 1.0f - std::abs(x)); }
+    std::string toString() const override { return "TentFilter[]"; }
+};
+NORI_REGISTER_CLASS(TentFilter, "tent")
+
+class BoxFilter : public ReconstructionFilter {                          /* rfilter.cpp:150-163 */
+public:
+    explicit BoxFilter(const PropertyList &) { m_radius = 0.5f; }
+    float eval(float) const override { return 1.0f; }
+    std::string toString() const override { return "BoxFilter[]"; }
+};
+NORI_REGISTER_CLASS(BoxFilter, "box")
+
+/* ---- camera (src/cameras/perspective.cpp:10-96) --------------------------------------------------- */
+class PerspectiveCamera : public Camera {
+public:
+    explicit PerspectiveCamera(const PropertyList &p) {
+        m_outputSize = Vector2i(p.getInteger("width", 1280), p.getInteger("height", 720));
+        m_cameraToWorld = p.getTransform("toWorld", Transform());
+        m_fov = p.getFloat("fov", 30.0f);
+        m_nearClip = p.getFloat("nearClip", 1e-4f);
+        m_farClip = p.getFloat("farClip", 1e4f);
+        m_focalDistance = p.getFloat("focalDistance", 10.f);
+        m_fstop = p.getFloat("fstop", 0.f);
+        m_lensRadius = p.getFloat("lensRadius", 0.f);
+    }
+    void addChild(NoriObject *obj) override {
+        if (obj->getClassType() != EReconstructionFilter) return Camera::addChild(obj);
+        if (m_rfilter) throw NoriException("Camera: tried to register multiple reconstruction filters!");
+        m_rfilter = static_cast<ReconstructionFilter *>(obj);
+    }
+    void activate() override {                                           /* perspective.cpp:33-46, 67-95 */
+        if (!m_rfilter) m_rfilter = static_cast<ReconstructionFilter *>(NoriObjectFactory::createInstance("gaussian"));
+        if (m_fstop == 0.f) m_fstop = m_focalDistance / m_lensRadius; else m_lensRadius = m_focalDistance / m_fstop;
+        const float aspect = m_outputSize.x() / (float) m_outputSize.y();
+        const float recip = 1.0f / (m_farClip - m_nearClip), cot = 1.0f / std::tan(degToRad(m_fov / 2.0f));
+        Matrix4f persp;
+        memset(persp.m, 0, sizeof(persp.m));
+        persp(0, 0) = cot; persp(1, 1) = cot; persp(2, 2) = m_farClip * recip; persp(2, 3) = -m_nearClip * m_farClip * recip; persp(3, 2) = 1;
+        Matrix4f scale = Matrix4f::identity(), trans = Matrix4f::identity();
+        scale(0, 0) = 0.5f; scale(1, 1) = -0.5f * aspect;
+        trans(0, 3) = 1.0f; trans(1, 3) = -1.0f / aspect;
+        m_sampleToCamera = Transform((scale * trans * persp).inverse());
+    }
+    void getB200Data(nb_camera &o) const override {
+        memset(&o, 0, sizeof(o));
+        memcpy(o.sample_to_camera, m_sampleToCamera.m.m, sizeof(o.sample_to_camera));
+        memcpy(o.camera_to_world, m_cameraToWorld.m.m, sizeof(o.camera_to_world));
+        o.inv_output_size[0] = 1.0f / (float) m_outputSize.x(); o.inv_output_size[1] = 1.0f / (float) m_outputSize.y();
+        o.near_clip = m_nearClip; o.far_clip = m_farClip; o.lens_radius = m_lensRadius; o.focal_distance = m_focalDistance;
+        o.width = (uint32_t) m_outputSize.x(); o.height = (uint32_t) m_outputSize.y();
+    }
+    std::string toString() const override { return NoriException::format("PerspectiveCamera[fov=%f, %dx%d]", m_fov, m_outputSize.x(), m_outputSize.y()); }
+private:
+    float m_fov, m_nearClip, m_farClip, m_focalDistance, m_fstop, m_lensRadius;
+    Transform m_cameraToWorld, m_sampleToCamera;
+};
+NORI_REGISTER_CLASS(PerspectiveCamera, "perspective")
+
+/* ---- integrators: only the tag crosses the boundary (integrator.h:91) ------------------------------ */
+#define NB_INTEGRATOR_CLASS(cls, name, tag) \
+    class cls : public Integrator { public: explicit cls(const PropertyList &) {} \
+        int getB200IntegratorType() const override { return tag; } \
+        std::string toString() const override { return #cls "[]"; } }; \
+    NORI_REGISTER_CLASS(cls, name)
+NB_INTEGRATOR_CLASS(PathMISIntegrator, "path_mis", NB_INTEGRATOR_PATH_MIS)
+NB_INTEGRATOR_CLASS(PathMATSIntegrator, "path_mats", NB_INTEGRATOR_PATH_MATS)
+NB_INTEGRATOR_CLASS(DirectEMSIntegrator, "direct_ems", NB_INTEGRATOR_DIRECT_EMS)
+NB_INTEGRATOR_CLASS(DirectMATSIntegrator, "direct_mats", NB_INTEGRATOR_DIRECT_MATS)
+NB_INTEGRATOR_CLASS(DirectMISIntegrator, "direct_mis", NB_INTEGRATOR_DIRECT_MIS)
+NB_INTEGRATOR_CLASS(DirectIntegrator, "direct", NB_INTEGRATOR_DIRECT)
+NB_INTEGRATOR_CLASS(NormalIntegrator, "normals", NB_INTEGRATOR_NORMALS)
+NB_INTEGRATOR_CLASS(AverageVisibility, "av", NB_INTEGRATOR_AV)
+NB_INTEGRATOR_CLASS(PathVolMATSIntegrator, "path_vol_mats", -1)
+NB_INTEGRATOR_CLASS(PathVolMISIntegrator, "path_vol_mis", -1)
+NB_INTEGRATOR_CLASS(PhotonMapper, "photonmapper", -1)
+NB_INTEGRATOR_CLASS(PreviewIntegrator, "preview", -1)
+
+class Independent : public Sampler {                /* src/samplers/independent.cpp:35-39 */
+public:
+    explicit Independent(const PropertyList &p) { m_sampleCount = (size_t) p.getInteger("sampleCount", 1); }
+    std::string toString() const override { return NoriException::format("Independent[sampleCount=%d]", (int) m_sampleCount); }
+};
+NORI_REGISTER_CLASS(Independent, "independent")
+
+/* the GPU side-car's own settings object (OptixRenderer, include/nori/optix/OptixRenderer.cpp:9-14) */
+class B200Renderer : public NoriObject {
+public:
+    explicit B200Renderer(const PropertyList &p) : samplesPerLaunch(p.getInteger("samplesPerLaunch", 16)) {}
+    EClassType getClassType() const override { return ERenderer; }
+    std::string toString() const override { return NoriException::format("B200Renderer[samplesPerLaunch=%d]", samplesPerLaunch); }
+    int samplesPerLaunch;
+};
+NORI_REGISTER_CLASS(B200Renderer, "b200")
+class OptixAlias : public B200Renderer { public: explicit OptixAlias(const PropertyList &p) : B200Renderer(p) {} };
+NORI_REGISTER_CLASS(OptixAlias, "optix")
+
+/* ---- Shape base (src/shapes/shape.cpp) --------------------------------------------------------------- */
+Shape::~Shape() { delete m_bsdf; delete m_emitter; }
+
+void Shape::addChild(NoriObject *obj) {
+    switch (obj->getClassType()) {
+        case EBSDF:
+            if (m_bsdf) throw NoriException("Shape: tried to register multiple BSDF instances!");
+            m_bsdf = static_cast<BSDF *>(obj);
+            break;
+        case EEmitter:
+            if (m_emitter) throw NoriException("Shape: tried to register multiple Emitter instances!");
+            m_emitter = static_cast<Emitter *>(obj);
+            m_emitter->setShape(this);
+            break;
+        default:
+            throw NoriException("Shape::addChild(<%s>) is not supported!", classTypeName(obj->getClassType()));
+    }
+}
+
+void Shape::activate() {
+    if (!m_bsdf) m_bsdf = static_cast<BSDF *>(NoriObjectFactory::createInstance("diffuse"));   /* shape.cpp:33-35 */
+}
+
+/* ---- Sphere (src/shapes/sphere.cpp:30-38) ---------------------------------------------------------------- */
+class Sphere : public Shape {
+public:
+    explicit Sphere(const PropertyList &p) : m_position(p.getPoint3("center", Point3f())), m_radius(p.getFloat("radius", 1.f)) {
+        m_bbox.expandBy(m_position - Vector3f(m_radius));
+        m_bbox.expandBy(m_position + Vector3f(m_radius));
+    }
+    uint32_t getPrimitiveCount() const override { return 1; }
+    BoundingBox3f getBoundingBox(uint32_t) const override { return m_bbox; }
+    Point3f getCentroid(uint32_t) const override { return m_position; }
+    void getB200Shape(nb_shape &rec, FlatScene &) const override {
+        rec.type = NB_SHAPE_SPHERE; rec.prim_count = 1; rec.radius = m_radius;
+        for (int i = 0; i < 3; ++i) rec.center[i] = m_position[i];
+    }
+    std::string toString() const override { return NoriException::format("Sphere[radius=%f]", m_radius); }
+private:
+    Point3f m_position;
+    float m_radius;
+};
+NORI_REGISTER_CLASS(Sphere, "sphere")
+
+} // namespace nori

@@ -1,0 +1,81 @@
+"""The C++ host mirror (XML parser, OBJ loader, plugin flatten hooks, SAH BVH builder) against
+what the reference itself holds after Scene::update() (oracle `flat` dumps, tests/golden/*.nbs)."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import golden
+
+
+@pytest.mark.parametrize("name,xml", [("cbox", "scenes/cbox/cbox_path_mis.xml"), ("cbox_mats", "scenes/cbox/cbox_path_mats.xml"),
+                                      ("table", "scenes/table/table_path_mis.xml")])
+def test_flatten_matches_reference_bit_for_bit(nb, built_lib, name, xml):
+    got = nb.load_xml(golden(xml))
+    want = nb.read_nbs(golden(name + ".nbs"))
+    assert set(got) == set(want)
+    for k in want:
+        if k == "camera":
+            continue
+        assert got[k].tobytes() == want[k].tobytes(), k       # vertices, tangents, CDFs, BVH nodes + indices, filter table
+    # camera: identical except the 4x4 inverse (Eigen fp32 cofactors there, double Gauss-Jordan here)
+    for f in got["camera"].dtype.names:
+        if f == "sample_to_camera":
+            np.testing.assert_allclose(got["camera"][f], want["camera"][f], rtol=2e-6, atol=1e-9)
+        else:
+            assert got["camera"][f].tobytes() == want["camera"][f].tobytes(), f
+
+
+def test_bvh_structure(nb, built_lib):
+    s = nb.load_xml(golden("scenes/table/table_path_mis.xml"))
+    n = s["bvh_nodes"]
+    leaf = (n["word0"] & 1) == 1
+    size = n["word0"][leaf] >> 1
+    assert size.sum() == len(s["bvh_indices"]) == s["shapes"]["prim_count"].sum()
+    assert sorted(s["bvh_indices"].tolist()) == list(range(len(s["bvh_indices"])))
+    inner = ~leaf
+    assert np.all(n["word1"][inner] < len(n)) and np.all(n["word1"][inner] > np.nonzero(inner)[0])
+
+
+def write(tmp_path, text):
+    p = tmp_path / "s.xml"
+    p.write_text(text)
+    return str(p)
+
+
+CAM = '<camera type="perspective"><integer name="width" value="8"/><integer name="height" value="8"/></camera>'
+
+
+def test_parser_errors_and_defaults(nb, built_lib, tmp_path):
+    with pytest.raises(nb.NbError) as e:
+        nb.load_xml(write(tmp_path, "<scene><integrator type='path_mis'/>" + CAM + "<shape type='cube'/></scene>"))
+    assert "could not be found" in str(e.value)
+    with pytest.raises(nb.NbError) as e:
+        nb.load_xml(write(tmp_path, "<scene><integrator type='path_mis'/></scene>"))
+    assert "No camera" in str(e.value)
+    with pytest.raises(nb.NbError) as e:
+        nb.load_xml(write(tmp_path, "<scene><float name='x' value='abc'/></scene>"))
+    assert "floating point" in str(e.value)
+    with pytest.raises(nb.NbError) as e:
+        nb.load_xml(write(tmp_path, "<scene><shape type='sphere'></scene>"))
+    assert "mismatched" in str(e.value)
+    # defaults: sphere radius 1 at the origin, diffuse 0.5, independent sampler with 1 spp, gaussian r=2
+    s = nb.load_xml(write(tmp_path, "<!-- c --><scene><integrator type='path_mats'/>" + CAM +
+                          "<shape type='sphere'/><emitter type='point'><color name='power' value='1 2 3'/>"
+                          "<point name='position' value='0,5,0'/></emitter></scene>"))
+    assert s["shapes"]["radius"][0] == 1 and s["bsdfs"]["albedo"][0].tolist() == [0.5, 0.5, 0.5]
+    assert s["spp"][0] == 1 and s["render"]["filter_radius"][0] == 2 and s["render"]["integrator"][0] == 1
+    assert s["emitters"]["type"][0] == nb.EMITTER_POINT
+    np.testing.assert_allclose(s["emitters"]["radiance"][0], np.array([1, 2, 3]) / (4 * np.pi), rtol=1e-6)
+
+
+def test_unsupported_plugin_is_reported_not_emulated(nb, built_lib, tmp_path):
+    xml = write(tmp_path, "<scene><integrator type='path_mis'/>" + CAM +
+                "<shape type='sphere'><bsdf type='disney'/></shape></scene>")
+    with pytest.raises(nb.NbError) as e:
+        nb.load_xml(xml)
+    assert e.value.code == nb.NB_E_UNSUPPORTED
+    xml = write(tmp_path, "<scene><integrator type='photonmapper'/>" + CAM + "<shape type='sphere'/></scene>")
+    with pytest.raises(nb.NbError) as e:
+        nb.load_xml(xml)
+    assert e.value.code == nb.NB_E_UNSUPPORTED

@@ -66,3 +66,23 @@ def test_small_pool_same_image(nb, ctx):
     b, cb = render(nb, ctx, scene, "path_mis", 4, size=(64, 48), seed=3, pool=1024)
     assert cb["samples"] == 64 * 48 * 4
     np.testing.assert_allclose(a, b, rtol=2e-4, atol=2e-5)
+
+
+def test_cli_renders_reference_xml(nb, tmp_path):
+    """The C++ host path end to end: nori_b200 loads the reference's own scene XML (parser, OBJ
+    loader, SAH BVH build, flatten hooks), renders on the GPU through the C ABI, writes .npy."""
+    import json
+    import os
+    import subprocess
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nori_b200")
+    out = tmp_path / "cbox.npy"
+    r = subprocess.run([cli, golden("scenes/cbox/cbox_path_mis_small.xml"), str(out), "spp=128", "seed=4"],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert r.returncode == 0, r.stderr
+    stats = json.loads(r.stdout.strip().splitlines()[-1])
+    img = np.load(out)
+    want = np.load(golden("cbox_ref_256spp.npy"))
+    assert img.shape == want.shape and stats["samples"] == 200 * 150 * 128
+    bias = (img.mean(axis=(0, 1)) - want.mean(axis=(0, 1))) / want.mean(axis=(0, 1))
+    assert np.all(np.abs(bias) <= 0.01), bias
+    assert rel_rmse(img, want) < 0.2
