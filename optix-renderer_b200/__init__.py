@@ -276,12 +276,15 @@ class Context:
         self._check(self.lib.nb_set_option(self.handle, name.encode(), int(value)))
 
 
-def make_render_params(scene, integrator="path_mis", seed=0, pool_paths=0, max_depth=0):
-    """nb_render_params from a scene dict's "render" section (filter table) + overrides."""
+def make_render_params(scene, integrator=None, seed=0, pool_paths=0, max_depth=0):
+    """nb_render_params from a scene dict's "render" section (filter table, integrator) + overrides."""
     p = np.zeros(1, dtype=render_params_dtype)
     if "render" in scene:
         p[0] = scene["render"][0]
-    p["integrator"] = INTEGRATORS[integrator] if isinstance(integrator, str) else int(integrator)
+    if integrator is not None:
+        p["integrator"] = INTEGRATORS[integrator] if isinstance(integrator, str) else int(integrator)
+    elif "render" not in scene:
+        p["integrator"] = INTEGRATORS["path_mis"]
     p["seed"] = seed
     p["pool_paths"] = pool_paths
     p["max_depth"] = max_depth

@@ -58,7 +58,7 @@ struct nb_ctx {
     std::vector<void *> scene_allocs, bvh_allocs;
     NbRenderState *render = nullptr;
     int sm_count = 148;
-    int opt_profile = 0, opt_sort = 0;
+    int opt_profile = 0, opt_sort = 0, opt_strategy = 0;
 };
 
 int nb_fail(nb_ctx *ctx, int code, const char *fmt, ...);
@@ -71,3 +71,10 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
 
 /* nb_render.cu */
 int nb_render_free(nb_ctx *ctx);
+
+/* nb_mega.cu */
+struct NbFilm;
+struct NbPlan;
+cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const NbPlan &plan, uint32_t height, uint32_t passes,
+                           uint32_t integrator, uint32_t *item_counter, unsigned long long *stats, int sm_count,
+                           cudaStream_t stream);

@@ -1,0 +1,357 @@
+/* nb_mega.cu — K_tile: persistent per-warp path tracing with the whole path state in registers.
+ *
+ * Second execution strategy next to the wavefront pipeline of nb_render.cu, for scenes whose BVH
+ * and shading data stay cache-resident (the Cornell box of the headline metric is < 2 KB): no
+ * path pool in HBM, no queues, no per-iteration launches. Every warp repeatedly takes a work item
+ * (one 16x8-pixel tile x a chunk of sample passes) from a global counter; a lane whose path ends
+ * splats it (ImageBlock::put) and starts the item's next camera sample in the same loop
+ * iteration, so all 32 lanes stay busy and stay in the same phase of the loop
+ *      regenerate -> closest-hit -> shade/NEE/RR -> any-hit (shadow) -> splat.
+ * Sample numbering, pcg32 streams and draw order per path are identical to the wavefront
+ * pipeline's, so both strategies produce the same per-sample radiance.
+ *
+ * Integrators restated here: PathMISIntegrator::Li (src/integrators/path_mis.cpp:16-150),
+ * PathMATSIntegrator::Li (path_mats.cpp:16-78), DirectIntegrator::Li (direct.cpp:16-67),
+ * DirectEMSIntegrator::Li (direct_ems.cpp:15-74), DirectMATSIntegrator::Li (direct_mats.cpp:16-83),
+ * DirectMISIntegrator::Li (direct_mis.cpp:15-139). */
+#include "nb_internal.h"
+#include "nb_wavefront.h"
+#include "nb_shading.cuh"
+#include "nb_film.cuh"
+#include "nb_trace.cuh"
+
+#ifndef NB_TILE_THREADS
+#define NB_TILE_THREADS 128
+#endif
+#ifndef NB_TILE_MIN_BLOCKS
+#define NB_TILE_MIN_BLOCKS 4
+#endif
+
+struct NbTilePlan {
+    NbPlan plan;
+    uint32_t height, passes;          /* image rows; sample passes of this subframe */
+    uint32_t tile_w, tile_h;          /* pixels per tile */
+    uint32_t tiles_x, n_tiles;
+    uint32_t chunk;                   /* passes per work item */
+    uint32_t n_items;                 /* n_tiles * ceil(passes / chunk) */
+};
+
+struct NbPathRegs {                   /* path_mis.cpp:18-24 locals + the ray being traced */
+    f3 Li, thr, o, d;
+    float mint, maxt, w_mats, w_ems, pdfmat, px, py;
+    uint32_t flags;
+    NbRng rng;
+};
+
+struct NbShadowRay { f3 o, d, c; float mint, maxt, cand; };
+
+__device__ __forceinline__ void nb_hit_info(const NbDeviceScene &sc, const NbHit &hit, f3 o, f3 d, nb_shape &sh, NbIts &its) {
+    const float4 sl = __ldg(sc.slots + 3 * hit.slot + 2);
+    const uint32_t sid = __float_as_uint(sl.y) & NB_SLOT_SHAPE_MASK, prim = __float_as_uint(sl.z);
+    sh = sc.shapes[sid];
+    its.shape = sid;
+    if (sh.type == NB_SHAPE_SPHERE) nb_sphere_hit_info(sh, o, d, hit.t, its);
+    else nb_mesh_hit_info(sc, sh, prim, hit.u, hit.v, its);
+}
+
+/* AreaEmitter::eval (arealight.cpp:58-73) for EmitterQueryRecord(ref, p, n) */
+__device__ __forceinline__ f3 nb_area_eval(const nb_emitter &em, f3 ref, f3 p, f3 n) {
+    const f3 wi = normalize(p - ref);
+    if (dot(n, -wi) >= 0.f) return mk3(em.radiance[0], em.radiance[1], em.radiance[2]);
+    return mk3(0.f);
+}
+
+__device__ __forceinline__ bool nb_occluded(const NbDeviceScene &sc, f3 o, f3 d, float mint, float maxt) {
+    NbHit dummy;
+    return nb_traverse<true>(sc.nodes, sc.slots, sc.n_nodes, o, d, mint, maxt, dummy);
+}
+
+/* One bounce of path_mis / path_mats for a path whose closest hit just arrived. Returns false
+ * when the path ended at this vertex; `shadow` is set when an NEE ray must be resolved. */
+template <bool MIS>
+__device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t max_depth, NbPathRegs &ps, const NbHit &hit,
+                                               bool &shadow, NbShadowRay &so) {
+    nb_shape sh; NbIts its;
+    nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
+    const float n_lights = (float) sc.n_emitters;
+    /* emitter hit (path_mis.cpp:51-56); the MIS weight of the BSDF-sampled ray that led here
+     * (path_mis.cpp:117-140) is evaluated now that its hit is known */
+    if (sh.emitter >= 0) {
+        const nb_emitter em = sc.emitters[sh.emitter];
+        if (MIS && !(ps.flags & NB_FLAG_PRIMARY) && (ps.flags & NB_FLAG_BSDF_OK)) {
+            const f3 wi_e = normalize(its.p - ps.o);
+            const float pdfmat_ems = nb_area_pdf(sh, ps.o, its.p, its.sh.n, wi_e) / n_lights;
+            if (ps.pdfmat + pdfmat_ems > NB_EPS) ps.w_mats = ps.pdfmat / (ps.pdfmat + pdfmat_ems);
+        }
+        if (MIS && (ps.flags & NB_FLAG_DISCRETE)) ps.w_mats = 1.f;
+        ps.Li += (MIS ? ps.w_mats : 1.f) * ps.thr * nb_area_eval(em, ps.o, its.p, its.sh.n);
+    } else if (MIS && (ps.flags & NB_FLAG_DISCRETE)) ps.w_mats = 1.f;
+
+    const uint32_t bounce = ps.flags >> NB_BOUNCE_SHIFT;
+    /* Russian roulette: path_mis.cpp:58-71 (always, clamped) / path_mats.cpp:49-61 (after 3) */
+    float succ = fminf(max3(ps.thr), 0.99f);
+    if (MIS) {
+        succ = fmaxf(succ, NB_EPS);
+        if (ps.rng.next_float() > succ) return false;
+        ps.thr = ps.thr / succ;
+    } else if (bounce >= 3) {
+        if (ps.rng.next_float() > succ) return false;
+        ps.thr = ps.thr / succ;
+    }
+    if ((max_depth && bounce >= max_depth) || sh.bsdf < 0) return false;
+
+    const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    const f3 wi = its.sh.to_local(-ps.d);
+    if (MIS) {                                                       /* path_mis.cpp:75-106 */
+        const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
+        const nb_emitter em = sc.emitters[ei];
+        float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+        NbEmitterSample es;
+        const f3 ems_col = nb_emitter_sample(sc, em, its.p, s, es);
+        if (!is_zero(ems_col, NB_EPS)) {
+            const f3 we = its.sh.to_local(es.wi);
+            const f3 C = ps.thr * (ems_col * we.z * nb_bsdf_eval(bsdf, wi, we) * n_lights);
+            if (!is_black(C)) {
+                const float pdf_b = nb_bsdf_pdf(bsdf, wi, we), pdf_e = es.pdf / n_lights;
+                shadow = true;
+                so.o = es.ray_o; so.d = es.ray_d; so.mint = es.ray_mint; so.maxt = es.ray_maxt; so.c = C;
+                so.cand = (pdf_b + pdf_e > NB_EPS) ? pdf_e / (pdf_b + pdf_e) : -1.f;
+            }
+        }
+    }
+    /* BSDF sampling (path_mis.cpp:108-146 / path_mats.cpp:63-74) */
+    float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+    f3 wo; bool discrete;
+    const f3 col = nb_bsdf_sample(bsdf, wi, s, wo, discrete, ps.pdfmat);
+    ps.flags = (bounce + 1) << NB_BOUNCE_SHIFT;
+    if (discrete) { ps.flags |= NB_FLAG_DISCRETE; ps.w_ems = 0.f; }
+    if (!is_zero(col, NB_EPS)) ps.flags |= NB_FLAG_BSDF_OK;
+    ps.thr = ps.thr * col;
+    ps.o = its.p; ps.d = its.sh.to_world(wo); ps.mint = NB_EPS; ps.maxt = INFINITY;
+    return !is_black(ps.thr);                                       /* a black path can gain nothing more */
+}
+
+/* The depth-1 integrators, one whole sample. Returns Li. */
+template <int INTEG>
+__device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any) {
+    NbHit hit;
+    ++n_closest;
+    if (!nb_traverse<false>(sc.nodes, sc.slots, sc.n_nodes, ps.o, ps.d, ps.mint, ps.maxt, hit)) return mk3(0.f);
+    nb_shape sh; NbIts its;
+    nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
+    f3 result = mk3(0.f);
+    if (INTEG != NB_INTEGRATOR_DIRECT && sh.emitter >= 0)
+        result += nb_area_eval(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
+    if (sh.bsdf < 0) return result;
+    const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    const float n_lights = (float) sc.n_emitters;
+
+    if (INTEG == NB_INTEGRATOR_DIRECT) {                              /* direct.cpp:37-63 */
+        const f3 wo = its.sh.to_local(normalize(ps.o - its.p));
+        for (uint32_t l = 0; l < sc.n_emitters; ++l) {
+            float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+            NbEmitterSample es;
+            const f3 li = nb_emitter_sample(sc, sc.emitters[l], its.p, s, es);
+            const f3 wi = its.sh.to_local(es.wi);
+            ++n_any;
+            if (nb_occluded(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
+            const float c = fabsf(dot(es.wi, its.sh.n)) / length(es.wi);
+            result += li * c * nb_bsdf_eval(bsdf, wi, wo);
+        }
+        return result;
+    }
+    const f3 wi = its.sh.to_local(-ps.d);
+    if (INTEG == NB_INTEGRATOR_DIRECT_EMS) {                          /* direct_ems.cpp:42-70 */
+        for (uint32_t l = 0; l < sc.n_emitters; ++l) {
+            float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+            NbEmitterSample es;
+            const f3 li = nb_emitter_sample(sc, sc.emitters[l], its.p, s, es);
+            if (is_zero(li, NB_EPS)) continue;
+            ++n_any;
+            if (nb_occluded(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
+            const f3 we = its.sh.to_local(es.wi);
+            result += li * fabsf(we.z) * nb_bsdf_eval(bsdf, wi, we);
+        }
+        return result;
+    }
+    float w_ems = 0.f, w_mat = 0.f;
+    f3 result_ems = mk3(0.f), result_mats = mk3(0.f);
+    if (INTEG == NB_INTEGRATOR_DIRECT_MIS) {                          /* direct_mis.cpp:49-90 */
+        const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
+        float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+        NbEmitterSample es;
+        const f3 li = nb_emitter_sample(sc, sc.emitters[ei], its.p, s, es);
+        if (!is_zero(li, NB_EPS)) {
+            ++n_any;
+            if (!nb_occluded(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) {
+                const f3 we = its.sh.to_local(es.wi);
+                const float pdf_ems = es.pdf / n_lights, pdf_mat = nb_bsdf_pdf(bsdf, wi, we);
+                result_ems = li * we.z * nb_bsdf_eval(bsdf, wi, we) * n_lights;
+                if (pdf_ems + pdf_mat > NB_EPS) w_ems = pdf_ems / (pdf_ems + pdf_mat);
+            }
+        }
+    }
+    /* BSDF sampling: direct_mats.cpp:46-80 / direct_mis.cpp:92-135 */
+    float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+    f3 wo; bool discrete; float pdf_mat;
+    const f3 col = nb_bsdf_sample(bsdf, wi, s, wo, discrete, pdf_mat);
+    if (!is_zero(col, NB_EPS)) {
+        const f3 d2 = its.sh.to_world(wo);
+        NbHit hit2;
+        ++n_closest;
+        if (nb_traverse<false>(sc.nodes, sc.slots, sc.n_nodes, its.p, d2, NB_EPS, INFINITY, hit2)) {
+            nb_shape sh2; NbIts its2;
+            nb_hit_info(sc, hit2, its.p, d2, sh2, its2);
+            if (sh2.emitter >= 0) {
+                result_mats = col * nb_area_eval(sc.emitters[sh2.emitter], its.p, its2.p, its2.sh.n);
+                if (INTEG == NB_INTEGRATOR_DIRECT_MIS) {
+                    const float pdf_ems = nb_area_pdf(sh2, its.p, its2.p, its2.sh.n, normalize(its2.p - its.p)) / n_lights;
+                    if (pdf_mat + pdf_ems > NB_EPS) w_mat = pdf_mat / (pdf_mat + pdf_ems);
+                }
+            }
+        }
+    }
+    if (INTEG == NB_INTEGRATOR_DIRECT_MATS) return result + result_mats;
+    return result + w_ems * result_ems + w_mat * result_mats;
+}
+
+/* ---- K_tile ---------------------------------------------------------------------------------- */
+template <int INTEG>
+__global__ void __launch_bounds__(NB_TILE_THREADS, NB_TILE_MIN_BLOCKS)
+nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
+    constexpr bool PATH = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_MATS;
+    constexpr bool MIS = INTEG == NB_INTEGRATOR_PATH_MIS;
+    const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+    uint32_t n_closest = 0, n_any = 0, n_samples = 0;
+    /* the warp's current work item (warp-uniform) */
+    uint32_t it_x0 = 0, it_y0 = 0, it_tw = 1, it_tpx = 0, it_pass0 = 0, it_n = 0, it_next = 0;
+    bool exhausted = false;
+    bool active = false;
+    NbPathRegs ps;
+    ps.flags = 0;
+    for (;;) {
+        /* --- regenerate: idle lanes take the next camera samples of the warp's item --- */
+        uint32_t need = __ballot_sync(0xffffffffu, !active);
+        while (need) {
+            if (it_next == it_n) {
+                if (exhausted) break;
+                uint32_t item = 0;
+                if (lane == 0) item = atomicAdd(item_counter, 1u);
+                item = __shfl_sync(0xffffffffu, item, 0);
+                if (item >= tp.n_items) { exhausted = true; break; }
+                /* chunk-major order: concurrently running warps work on different tiles */
+                const uint32_t tile = item % tp.n_tiles, chunk = item / tp.n_tiles;
+                it_x0 = (tile % tp.tiles_x) * tp.tile_w; it_y0 = (tile / tp.tiles_x) * tp.tile_h;
+                it_tw = min(tp.tile_w, tp.plan.width - it_x0);
+                it_tpx = it_tw * min(tp.tile_h, tp.height - it_y0);
+                it_pass0 = chunk * tp.chunk;
+                it_n = it_tpx * min(tp.chunk, tp.passes - it_pass0);
+                it_next = 0;
+            }
+            const uint32_t take = min((uint32_t) __popc(need), it_n - it_next);
+            const uint32_t rank = __popc(need & lt_mask);
+            if (!active && rank < take) {
+                const uint32_t k = it_next + rank;
+                const uint32_t pl = k / it_tpx, q = k - pl * it_tpx;
+                const uint32_t y = q / it_tw, x = q - y * it_tw;
+                const uint32_t pix = (it_y0 + y) * tp.plan.width + it_x0 + x;
+                const uint32_t sidx = tp.plan.first + (it_pass0 + pl) * tp.plan.stride;
+                NbCameraRay r;
+                nb_camera_sample(sc.camera, tp.plan, pix, sidx, ps.rng, r);
+                ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
+                ps.Li = mk3(0.f); ps.thr = mk3(1.f); ps.w_mats = 1.f; ps.w_ems = 0.f; ps.pdfmat = 0.f;
+                ps.flags = NB_FLAG_PRIMARY;
+                active = true;
+                ++n_samples;
+            }
+            it_next += take;
+            need = __ballot_sync(0xffffffffu, !active);
+        }
+        if (!__any_sync(0xffffffffu, active)) break;
+
+        if (PATH) {
+            bool ended = false, shadow = false;
+            NbShadowRay so;
+            if (active) {
+                NbHit hit;
+                ++n_closest;
+                if (!nb_traverse<false>(sc.nodes, sc.slots, sc.n_nodes, ps.o, ps.d, ps.mint, ps.maxt, hit)) ended = true;
+                else ended = !nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
+            }
+            if (MIS && shadow) {
+                ++n_any;
+                if (!nb_occluded(sc, so.o, so.d, so.mint, so.maxt)) {
+                    /* path_mis.cpp:102-105,141: w_ems is updated only when the pdf sum passes the
+                     * Epsilon test, otherwise the value of an earlier bounce is used */
+                    if (so.cand >= 0.f) ps.w_ems = so.cand;
+                    ps.Li += ps.w_ems * so.c;
+                }
+            }
+            if (active && ended) {
+                nb_film_put(film, ps.px, ps.py, ps.Li, stats);
+                active = false;
+            }
+        } else if (active) {
+            const f3 Li = nb_direct_sample<INTEG>(sc, ps, n_closest, n_any);
+            nb_film_put(film, ps.px, ps.py, Li, stats);
+            active = false;
+        }
+    }
+    for (int off = 16; off; off >>= 1) {
+        n_closest += __shfl_xor_sync(0xffffffffu, n_closest, off);
+        n_any += __shfl_xor_sync(0xffffffffu, n_any, off);
+        n_samples += __shfl_xor_sync(0xffffffffu, n_samples, off);
+    }
+    if (lane == 0) {
+        if (n_closest) atomicAdd(&stats[NB_STAT_RAYS_CLOSEST], (unsigned long long) n_closest);
+        if (n_any) atomicAdd(&stats[NB_STAT_RAYS_ANY], (unsigned long long) n_any);
+        if (n_samples) atomicAdd(&stats[NB_STAT_SAMPLES], (unsigned long long) n_samples);
+    }
+}
+
+template <int INTEG>
+static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
+                                    unsigned long long *stats, int sm_count, cudaStream_t stream) {
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile<INTEG>, NB_TILE_THREADS, 0);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    const uint64_t warps_wanted = ((uint64_t) tp.n_items + 0) ;
+    uint64_t blocks = (uint64_t) sm_count * per_sm;
+    const uint64_t blocks_useful = (warps_wanted + NB_TILE_THREADS / 32 - 1) / (NB_TILE_THREADS / 32);
+    if (blocks > blocks_useful) blocks = blocks_useful;
+    if (blocks < 1) blocks = 1;
+    nb_k_tile<INTEG><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
+    return cudaGetLastError();
+}
+
+/* Host entry used by nb_render_subframe. `passes` sample passes over the image, pass k drawing
+ * sample index plan.first + k * plan.stride. Asynchronous on `stream`. */
+cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const NbPlan &plan, uint32_t height, uint32_t passes,
+                           uint32_t integrator, uint32_t *item_counter, unsigned long long *stats, int sm_count,
+                           cudaStream_t stream) {
+    NbTilePlan tp;
+    tp.plan = plan;
+    tp.height = height; tp.passes = passes;
+    tp.tile_w = 16; tp.tile_h = 8;
+    tp.tiles_x = (plan.width + tp.tile_w - 1) / tp.tile_w;
+    tp.n_tiles = tp.tiles_x * ((height + tp.tile_h - 1) / tp.tile_h);
+    /* items of about 4096 samples (128 per lane), but enough of them to balance ~5000 warps */
+    uint32_t chunk = 32;
+    while (chunk > 1 && (uint64_t) tp.n_tiles * ((passes + chunk - 1) / chunk) < (uint64_t) sm_count * 16 * 8) chunk >>= 1;
+    tp.chunk = chunk;
+    const uint64_t items = (uint64_t) tp.n_tiles * ((passes + chunk - 1) / chunk);
+    if (items >= 0xffff0000ull) return cudaErrorInvalidValue;
+    tp.n_items = (uint32_t) items;
+    cudaError_t e = cudaMemsetAsync(item_counter, 0, sizeof(uint32_t), stream);
+    if (e != cudaSuccess) return e;
+    switch (integrator) {
+        case NB_INTEGRATOR_PATH_MIS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_PATH_MATS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_MATS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_DIRECT: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_DIRECT_EMS: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT_EMS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_DIRECT_MATS: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT_MATS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_DIRECT_MIS: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        default: return cudaErrorInvalidValue;
+    }
+}

@@ -11,86 +11,23 @@
 #include "nb_internal.h"
 #include "nb_wavefront.h"
 #include "nb_shading.cuh"
+#include "nb_film.cuh"
 #include <cstring>
 #include <algorithm>
 
-struct NbFilm {
-    float4 *data;
-    uint32_t rows, cols, border;
-    float radius, lookup;
-    float table[NB_FILTER_RESOLUTION + 1];
-};
-
-struct NbPlan {
-    unsigned long long total;     /* camera samples of this subframe */
-    unsigned long long seed;
-    uint32_t npix, width;
-    uint32_t first, stride;       /* sample index of pass k = first + k * stride */
-    uint32_t max_depth;
-};
-
-/* ImageBlock::put(pos, value), block.cpp:93-123, on the full-image block (offset 0). */
-__device__ __forceinline__ void nb_film_put(const NbFilm &film, float px, float py, f3 v, unsigned long long *stats) {
-    const bool valid = v.x >= 0.f && v.y >= 0.f && v.z >= 0.f && isfinite(v.x) && isfinite(v.y) && isfinite(v.z);
-    if (!valid) { atomicAdd(&stats[NB_STAT_INVALID], 1ULL); return; }      /* Color3f::isValid, common.cpp:254 */
-    const float posx = px - 0.5f + (float) film.border, posy = py - 0.5f + (float) film.border;
-    int x0 = (int) ceilf(posx - film.radius), x1 = (int) floorf(posx + film.radius);
-    int y0 = (int) ceilf(posy - film.radius), y1 = (int) floorf(posy + film.radius);
-    x0 = max(x0, 0); y0 = max(y0, 0);
-    x1 = min(x1, (int) film.cols - 1); y1 = min(y1, (int) film.rows - 1);
-    for (int y = y0; y <= y1; ++y) {
-        const float wy = film.table[(int) (fabsf((float) y - posy) * film.lookup)];
-        float4 *row = film.data + (size_t) y * film.cols;
-        for (int x = x0; x <= x1; ++x) {
-            const float wgt = film.table[(int) (fabsf((float) x - posx) * film.lookup)] * wy;
-            atomicAdd(row + x, make_float4(v.x * wgt, v.y * wgt, v.z * wgt, wgt));   /* RED.128 on sm_90+ */
-        }
-    }
-}
-
-__device__ __forceinline__ f3 nb_xform_point(const float *m, f3 p) {           /* transform.h:83-86 */
-    const float x = m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3];
-    const float y = m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7];
-    const float z = m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11];
-    const float w = m[12] * p.x + m[13] * p.y + m[14] * p.z + m[15];
-    return mk3(x / w, y / w, z / w);
-}
-__device__ __forceinline__ f3 nb_xform_vector(const float *m, f3 v) {          /* transform.h:73-75 */
-    return mk3(m[0] * v.x + m[1] * v.y + m[2] * v.z, m[4] * v.x + m[5] * v.y + m[6] * v.z,
-               m[8] * v.x + m[9] * v.y + m[10] * v.z);
-}
-
-/* renderBlock's per-sample prologue (render.cpp:441-447) + PerspectiveCamera::sampleRay. */
+/* start camera sample n of the plan in pool slot p */
 __device__ __forceinline__ void nb_generate_path(const NbDeviceScene &sc, const NbWave &w, const NbPlan &plan,
                                                  uint32_t p, unsigned long long n) {
     const uint32_t pass = (uint32_t) (n / plan.npix), pix = (uint32_t) (n % plan.npix);
-    const uint32_t x = pix % plan.width, y = pix / plan.width;
     const uint32_t sidx = plan.first + pass * plan.stride;
     NbRng rng;
-    rng.seed(plan.seed * 0x9E3779B97F4A7C15ULL + sidx, pix);
-    const float px = (float) x + rng.next_float(), py = (float) y + rng.next_float();
-    const float2 ap = make_float2(rng.next_float(), rng.next_float());     /* always drawn, render.cpp:443 */
-    const nb_camera &cam = sc.camera;
-    const f3 nearP = nb_xform_point(cam.sample_to_camera, mk3(px * cam.inv_output_size[0], py * cam.inv_output_size[1], 0.f));
-    const f3 d0 = normalize(nearP);
-    f3 o = mk3(0.f), d = d0;
-    if (cam.lens_radius > NB_EPS) {
-        /* thin lens; the reference draws the lens point from a hidden static sampler
-         * (perspective.cpp:118-122) — here it comes from the path's own stream */
-        const float2 dk = square_to_uniform_disk(ap);
-        const float ft = cam.focal_distance / d0.z;
-        const f3 focus = d0 * ft;
-        o = mk3(cam.lens_radius * dk.x, cam.lens_radius * dk.y, 0.f);
-        d = normalize(focus - o);
-    }
-    o = nb_xform_point(cam.camera_to_world, o);
-    d = nb_xform_vector(cam.camera_to_world, d);
-    const float invZ = 1.0f / d0.z;
-    w.ray_o[p] = make_float4(o.x, o.y, o.z, cam.near_clip * invZ);
-    w.ray_d[p] = make_float4(d.x, d.y, d.z, cam.far_clip * invZ);
+    NbCameraRay r;
+    nb_camera_sample(sc.camera, plan, pix, sidx, rng, r);
+    w.ray_o[p] = make_float4(r.o.x, r.o.y, r.o.z, r.mint);
+    w.ray_d[p] = make_float4(r.d.x, r.d.y, r.d.z, r.maxt);
     w.st0[p] = make_float4(0.f, 0.f, 0.f, 1.f);
     w.st1[p] = make_float4(1.f, 1.f, 1.f, 0.f);
-    w.st2[p] = make_float4(px, py, 0.f, __uint_as_float(NB_FLAG_PRIMARY));
+    w.st2[p] = make_float4(r.px, r.py, 0.f, __uint_as_float(NB_FLAG_PRIMARY));
     w.rng[p] = make_uint4((uint32_t) rng.state, (uint32_t) (rng.state >> 32), pix, sidx);
 }
 
@@ -308,6 +245,7 @@ struct NbRenderState {
     uint32_t *queue[2] = { nullptr, nullptr };
     uint32_t *counts = nullptr;   /* 2 sets x NB_CNT_WORDS */
     unsigned long long *stats = nullptr;
+    uint32_t *tile_counter = nullptr;   /* work-item counter of K_tile (nb_mega.cu) */
     uint32_t *h_counts = nullptr; /* pinned mirror of counts */
     unsigned long long *h_stats = nullptr;
     std::vector<void *> allocs;
@@ -342,15 +280,27 @@ static int nb_dev_alloc(nb_ctx *ctx, NbRenderState *r, T **out, size_t count) {
     return NB_OK;
 }
 
+/* Which execution strategy renders the path integrators: the wavefront pipeline keeps thousands
+ * of rays per SM in flight to cover L2/HBM latency of a large BVH; K_tile keeps everything in
+ * registers and wins while the scene is cache-resident. */
+static bool nb_use_tile_strategy(const nb_ctx *ctx) {
+    if (ctx->opt_strategy == NB_STRATEGY_TILE) return true;
+    if (ctx->opt_strategy == NB_STRATEGY_WAVEFRONT) return false;
+    return false;
+}
+
 extern "C" {
 
 int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     if (!ctx || !params) return nb_fail(ctx, NB_E_INVALID, "nb_render_begin: NULL argument");
     if (!ctx->bvh_ready) return nb_fail(ctx, NB_E_STATE, "nb_render_begin: scene/BVH not ready");
-    if (params->integrator != NB_INTEGRATOR_PATH_MIS && params->integrator != NB_INTEGRATOR_PATH_MATS)
-        return nb_fail(ctx, NB_E_UNSUPPORTED, "integrator tag %u has no kernel in this backend", params->integrator);
-    if (params->integrator == NB_INTEGRATOR_PATH_MIS && ctx->dev.n_emitters == 0)
-        return nb_fail(ctx, NB_E_INVALID, "path_mis: No Emitter in scene!");      /* path_mis.cpp:76-79 */
+    switch (params->integrator) {
+        case NB_INTEGRATOR_PATH_MIS: case NB_INTEGRATOR_PATH_MATS: case NB_INTEGRATOR_DIRECT:
+        case NB_INTEGRATOR_DIRECT_EMS: case NB_INTEGRATOR_DIRECT_MATS: case NB_INTEGRATOR_DIRECT_MIS: break;
+        default: return nb_fail(ctx, NB_E_UNSUPPORTED, "integrator tag %u has no kernel in this backend", params->integrator);
+    }
+    if ((params->integrator == NB_INTEGRATOR_PATH_MIS || params->integrator == NB_INTEGRATOR_DIRECT_MIS) && ctx->dev.n_emitters == 0)
+        return nb_fail(ctx, NB_E_INVALID, "No Emitter in scene!");                 /* path_mis.cpp:76-79 */
     if (!(params->filter_radius > 0.f)) return nb_fail(ctx, NB_E_INVALID, "filter radius must be positive");
     const nb_camera &cam = ctx->dev.camera;
     if (cam.width == 0 || cam.height == 0) return nb_fail(ctx, NB_E_INVALID, "camera has no output size");
@@ -391,7 +341,7 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
         (rc = nb_dev_alloc(ctx, r, &w.sh_d, pool)) || (rc = nb_dev_alloc(ctx, r, &w.sh_c, pool)) ||
         (rc = nb_dev_alloc(ctx, r, &w.sh_w, pool)) || (rc = nb_dev_alloc(ctx, r, &r->queue[0], pool)) ||
         (rc = nb_dev_alloc(ctx, r, &r->queue[1], pool)) || (rc = nb_dev_alloc(ctx, r, &w.queue_dead, pool)) || (rc = nb_dev_alloc(ctx, r, &r->counts, 2 * NB_CNT_WORDS)) ||
-        (rc = nb_dev_alloc(ctx, r, &r->stats, NB_STAT_WORDS)))
+        (rc = nb_dev_alloc(ctx, r, &r->stats, NB_STAT_WORDS)) || (rc = nb_dev_alloc(ctx, r, &r->tile_counter, 1)))
         return rc;
     w.stats = r->stats;
     NB_CUDA(ctx, cudaMallocHost((void **) &r->h_counts, 2 * 2 * NB_CNT_WORDS * sizeof(uint32_t)));
@@ -445,6 +395,29 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     plan.seed = r->params.seed; plan.first = s0; plan.stride = stride; plan.max_depth = r->params.max_depth;
     cudaEventRecord(r->ev_begin, ctx->stream);
     if (plan.total == 0) { cudaEventRecord(r->ev_end, ctx->stream); return NB_OK; }
+    const uint32_t integ = r->params.integrator;
+    const bool is_path = integ == NB_INTEGRATOR_PATH_MIS || integ == NB_INTEGRATOR_PATH_MATS;
+    if (!is_path || nb_use_tile_strategy(ctx)) {
+        /* K_tile: one persistent launch, path state in registers (nb_mega.cu) */
+        cudaError_t e = nb_launch_tile(ctx->dev, r->film, plan, cam.height, passes, integ, r->tile_counter, r->stats,
+                                       ctx->sm_count, ctx->stream);
+        if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: K_tile launch: %s", cudaGetErrorString(e));
+        cudaEventRecord(r->ev_end, ctx->stream);
+        cudaMemcpyAsync(r->h_stats, r->stats, NB_STAT_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream);
+        e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: %s", cudaGetErrorString(e));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end);
+        r->totals.device_ms += ms;
+        r->totals.iterations += 1;
+        r->totals.kernel_launches += 1;
+        r->totals.samples = r->h_stats[NB_STAT_SAMPLES];
+        r->totals.rays_closest = r->h_stats[NB_STAT_RAYS_CLOSEST];
+        r->totals.rays_any = r->h_stats[NB_STAT_RAYS_ANY];
+        r->totals.invalid_samples = r->h_stats[NB_STAT_INVALID];
+        return NB_OK;
+    }
     NbWave w = r->wave;
     const uint32_t n_live = (uint32_t) std::min<unsigned long long>(w.pool, plan.total);
     w.total_samples = plan.total;
@@ -575,6 +548,10 @@ int nb_set_option(nb_ctx *ctx, const char *name, int64_t value) {
     if (!ctx || !name) return NB_E_INVALID;
     if (!strcmp(name, "profile")) ctx->opt_profile = (int) value;
     else if (!strcmp(name, "sort")) ctx->opt_sort = (int) value;
+    else if (!strcmp(name, "strategy")) {
+        if (value < NB_STRATEGY_AUTO || value > NB_STRATEGY_TILE) return nb_fail(ctx, NB_E_INVALID, "nb_set_option: strategy %lld out of range", (long long) value);
+        ctx->opt_strategy = (int) value;
+    }
     else return nb_fail(ctx, NB_E_INVALID, "nb_set_option: unknown option '%s'", name);
     return NB_OK;
 }

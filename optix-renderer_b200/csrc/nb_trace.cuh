@@ -3,8 +3,9 @@
  * Follows BVH::rayIntersect (src/utils/bvh.cpp:402-460), TBoundingBox::rayIntersect
  * (include/nori/bbox.h:336-363), Mesh::rayIntersect (src/shapes/mesh.cpp:101-139) and
  * Sphere::rayIntersect (src/shapes/sphere.cpp:67-94) operation by operation:
- *   - fp32, no FMA contraction (this header is only included from translation units built with
- *     -fmad=false; x86-64 gcc emits no FMA for the reference),
+ *   - fp32, no FMA contraction: every product/sum that decides a hit is written with the
+ *     round-to-nearest intrinsics (__fmul_rn/__fadd_rn/__fsub_rn), which nvcc never fuses, so the
+ *     header gives the same bits in any translation unit (x86-64 gcc emits no FMA for the reference),
  *   - Eigen 3.3.8 association: dot3 = a0*b0 + (a1*b1 + a2*b2) (Eigen/src/Core/Redux.h:91-105),
  *     cross as Eigen/src/Geometry/OrthoMethods.h:43-47,
  *   - std::max/std::min/std::swap written as the comparisons they are (NaN behaviour included),
@@ -21,7 +22,11 @@
 struct NbHit { float t, u, v; uint32_t slot; };
 
 __device__ __forceinline__ float nb_dot3(float ax, float ay, float az, float bx, float by, float bz) {
-    return ax * bx + (ay * by + az * bz);
+    return __fadd_rn(__fmul_rn(ax, bx), __fadd_rn(__fmul_rn(ay, by), __fmul_rn(az, bz)));
+}
+/* a*b - c*d, each product rounded (Eigen cross component) */
+__device__ __forceinline__ float nb_det2(float a, float b, float c, float d) {
+    return __fsub_rn(__fmul_rn(a, b), __fmul_rn(c, d));
 }
 
 /* bbox.h:336-363 */
@@ -35,8 +40,8 @@ __device__ __forceinline__ bool nb_box_hit(const float4 A, const float4 B, const
         if (dd[i] == 0.f) {
             if (oo[i] < mn[i] || oo[i] > mx[i]) return false;
         } else {
-            float t1 = (mn[i] - oo[i]) * rr[i];
-            float t2 = (mx[i] - oo[i]) * rr[i];
+            float t1 = __fmul_rn(__fsub_rn(mn[i], oo[i]), rr[i]);
+            float t2 = __fmul_rn(__fsub_rn(mx[i], oo[i]), rr[i]);
             if (t1 > t2) { float s = t1; t1 = t2; t2 = s; }
             nearT = (t1 < nearT) ? nearT : t1;      /* std::max(t1, nearT) */
             farT = (farT < t2) ? farT : t2;         /* std::min(t2, farT)  */
@@ -52,32 +57,32 @@ __device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, con
     const float p0x = s0.x, p0y = s0.y, p0z = s0.z;
     const float e1x = s0.w, e1y = s1.x, e1z = s1.y;
     const float e2x = s1.z, e2y = s1.w, e2z = s2.x;
-    const float pvx = d.y * e2z - d.z * e2y, pvy = d.z * e2x - d.x * e2z, pvz = d.x * e2y - d.y * e2x;
+    const float pvx = nb_det2(d.y, e2z, d.z, e2y), pvy = nb_det2(d.z, e2x, d.x, e2z), pvz = nb_det2(d.x, e2y, d.y, e2x);
     const float det = nb_dot3(e1x, e1y, e1z, pvx, pvy, pvz);
     if (det > -1e-8f && det < 1e-8f) return false;
     const float inv = 1.0f / det;
-    const float tvx = o.x - p0x, tvy = o.y - p0y, tvz = o.z - p0z;
-    u = nb_dot3(tvx, tvy, tvz, pvx, pvy, pvz) * inv;
+    const float tvx = __fsub_rn(o.x, p0x), tvy = __fsub_rn(o.y, p0y), tvz = __fsub_rn(o.z, p0z);
+    u = __fmul_rn(nb_dot3(tvx, tvy, tvz, pvx, pvy, pvz), inv);
     if (u < 0.0f || u > 1.0f) return false;
-    const float qvx = tvy * e1z - tvz * e1y, qvy = tvz * e1x - tvx * e1z, qvz = tvx * e1y - tvy * e1x;
-    v = nb_dot3(d.x, d.y, d.z, qvx, qvy, qvz) * inv;
-    if (v < 0.0f || u + v > 1.0f) return false;
-    t = nb_dot3(e2x, e2y, e2z, qvx, qvy, qvz) * inv;
+    const float qvx = nb_det2(tvy, e1z, tvz, e1y), qvy = nb_det2(tvz, e1x, tvx, e1z), qvz = nb_det2(tvx, e1y, tvy, e1x);
+    v = __fmul_rn(nb_dot3(d.x, d.y, d.z, qvx, qvy, qvz), inv);
+    if (v < 0.0f || __fadd_rn(u, v) > 1.0f) return false;
+    t = __fmul_rn(nb_dot3(e2x, e2y, e2z, qvx, qvy, qvz), inv);
     return t >= mint && t <= maxt;
 }
 
 /* sphere.cpp:67-94 */
 __device__ __forceinline__ bool nb_sphere_hit(const float4 s0, const float3 o, const float3 d, float mint,
                                               float maxt, float &t) {
-    const float Lx = o.x - s0.x, Ly = o.y - s0.y, Lz = o.z - s0.z;
+    const float Lx = __fsub_rn(o.x, s0.x), Ly = __fsub_rn(o.y, s0.y), Lz = __fsub_rn(o.z, s0.z);
     const float a = nb_dot3(d.x, d.y, d.z, d.x, d.y, d.z);
-    const float b = 2.f * nb_dot3(d.x, d.y, d.z, Lx, Ly, Lz);
-    const float c = nb_dot3(Lx, Ly, Lz, Lx, Ly, Lz) - s0.w * s0.w;
-    const float discr = b * b - 4.f * a * c;
+    const float b = __fmul_rn(2.f, nb_dot3(d.x, d.y, d.z, Lx, Ly, Lz));
+    const float c = __fsub_rn(nb_dot3(Lx, Ly, Lz, Lx, Ly, Lz), __fmul_rn(s0.w, s0.w));
+    const float discr = __fsub_rn(__fmul_rn(b, b), __fmul_rn(__fmul_rn(4.f, a), c));
     if (discr < 0.f) return false;
     const double sd = sqrt((double) discr), nb = (double) (-b), da = (double) a;
-    const float tmin = (float) ((nb - sd) / 2.0 / da);
-    const float tmax = (float) ((nb + sd) / 2.0 / da);
+    const float tmin = (float) (__dsub_rn(nb, sd) / 2.0 / da);
+    const float tmax = (float) (__dadd_rn(nb, sd) / 2.0 / da);
     if (mint <= tmin && maxt >= tmin) { t = tmin; return true; }
     if (mint <= tmax && maxt >= tmax) { t = tmax; return true; }
     return false;
@@ -93,7 +98,7 @@ __device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, co
         float m = fabsf(o.x);
         m = fmaxf(m, fabsf(o.y));
         m = fmaxf(m, fabsf(o.z));
-        const float s = mint * m;
+        const float s = __fmul_rn(mint, m);
         mint = (mint < s) ? s : mint;
     }
     if (n_nodes == 0 || maxt < mint) return false;

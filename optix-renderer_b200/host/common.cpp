@@ -20,27 +20,59 @@ Matrix4f Matrix4f::operator*(const Matrix4f &o) const {
     return r;
 }
 
+/* The reference inverts with Eigen 3.3.8's fp32 4x4 kernel (Transform ctor, transform.h:29 ->
+ * Eigen/src/LU/arch/Inverse_SSE.h): the matrix is split into four 2x2 blocks
+ *      M = | A C |      (blocks held column-wise: {m00, m10, m01, m11})
+ *          | B D |
+ * and the inverse assembled from adjugate products,
+ *      det  = |A||D| + |B||C| - tr(A# B D# C)
+ *      iA = A|D| - B (D# C)      iD = D|A| - C (A# B)
+ *      iB = C|B| - D (A# B)#     iC = B|C| - A (D# C)#
+ * scaled by +-1/det. Restated here four lanes at a time in the same operation order, so the
+ * result (including the signs of its zeros) is the reference's bit for bit. */
+namespace {
+struct Quad { float v[4]; };
+inline Quad lanes(const Quad &x, const Quad &y, int a, int b, int c, int d) { return Quad{{ x.v[a], x.v[b], y.v[c], y.v[d] }}; }
+inline Quad operator*(const Quad &a, const Quad &b) { return Quad{{ a.v[0] * b.v[0], a.v[1] * b.v[1], a.v[2] * b.v[2], a.v[3] * b.v[3] }}; }
+inline Quad operator-(const Quad &a, const Quad &b) { return Quad{{ a.v[0] - b.v[0], a.v[1] - b.v[1], a.v[2] - b.v[2], a.v[3] - b.v[3] }}; }
+inline Quad operator+(const Quad &a, const Quad &b) { return Quad{{ a.v[0] + b.v[0], a.v[1] + b.v[1], a.v[2] + b.v[2], a.v[3] + b.v[3] }}; }
+inline Quad splat(float f) { return Quad{{ f, f, f, f }}; }
+/* A# * B for column-wise 2x2 blocks (A# = adjugate) */
+inline Quad adj_mul(const Quad &A, const Quad &B) { return lanes(A, A, 3, 3, 0, 0) * B - lanes(A, A, 1, 1, 2, 2) * lanes(B, B, 2, 3, 0, 1); }
+inline float det2(const Quad &A) { const Quad t = lanes(A, A, 3, 3, 1, 1) * A; return t.v[0] - t.v[2]; }
+/* X * Y for column-wise blocks */
+inline Quad blk_mul(const Quad &X, const Quad &Y) { return lanes(X, X, 0, 0, 2, 2) * lanes(Y, Y, 0, 1, 0, 1) + lanes(X, X, 1, 1, 3, 3) * lanes(Y, Y, 2, 3, 2, 3); }
+/* X * (Y)# */
+inline Quad mul_adj(const Quad &X, const Quad &Y) { return X * lanes(Y, Y, 3, 0, 3, 0) - lanes(X, X, 1, 0, 3, 2) * lanes(Y, Y, 2, 1, 2, 1); }
+}
+
 Matrix4f Matrix4f::inverse() const {
-    /* Gauss-Jordan with partial pivoting in double; the reference uses Eigen's 4x4 inverse in
-     * fp32 — results agree to ~1 ulp, which only shifts camera rays / normals within noise. */
-    double a[4][8];
-    for (int i = 0; i < 4; ++i)
-        for (int j = 0; j < 4; ++j) { a[i][j] = m[i * 4 + j]; a[i][4 + j] = (i == j) ? 1.0 : 0.0; }
-    for (int c = 0; c < 4; ++c) {
-        int piv = c;
-        for (int r = c + 1; r < 4; ++r) if (std::fabs(a[r][c]) > std::fabs(a[piv][c])) piv = r;
-        if (a[piv][c] == 0.0) throw NoriException("Matrix4f::inverse(): singular matrix");
-        if (piv != c) for (int j = 0; j < 8; ++j) std::swap(a[piv][j], a[c][j]);
-        const double d = a[c][c];
-        for (int j = 0; j < 8; ++j) a[c][j] /= d;
-        for (int r = 0; r < 4; ++r) {
-            if (r == c) continue;
-            const double f = a[r][c];
-            if (f != 0.0) for (int j = 0; j < 8; ++j) a[r][j] -= f * a[c][j];
-        }
-    }
+    auto col = [&](int k) { return Quad{{ m[0 * 4 + k], m[1 * 4 + k], m[2 * 4 + k], m[3 * 4 + k] }}; };
+    const Quad c0 = col(0), c1 = col(1), c2 = col(2), c3 = col(3);
+    const Quad A = lanes(c0, c1, 0, 1, 0, 1), B = lanes(c0, c1, 2, 3, 2, 3);
+    const Quad C = lanes(c2, c3, 0, 1, 0, 1), D = lanes(c2, c3, 2, 3, 2, 3);
+    const Quad AB = adj_mul(A, B), DC = adj_mul(D, C);
+    const float dA = det2(A), dB = det2(B), dC = det2(C), dD = det2(D);
+    Quad tr = lanes(DC, DC, 0, 2, 1, 3) * AB;
+    Quad iD = blk_mul(C, AB);
+    Quad iA = blk_mul(B, DC);
+    const float t0 = tr.v[0] + tr.v[2], t1 = tr.v[1] + tr.v[3];
+    const float trace = t0 + t1;
+    const float d1 = dA * dD, d2 = dB * dC;
+    iD = D * splat(dA) - iD;
+    iA = A * splat(dD) - iA;
+    const float det = (d1 + d2) - trace;
+    const float rd = 1.0f / det;
+    Quad iB = mul_adj(D, AB);
+    Quad iC = mul_adj(A, DC);
+    const Quad rdv = Quad{{ rd, -rd, -rd, rd }};
+    iB = C * splat(dB) - iB;
+    iC = B * splat(dC) - iC;
+    iA = rdv * iA; iB = rdv * iB; iC = rdv * iC; iD = rdv * iD;
+    const Quad r0 = lanes(iA, iB, 3, 1, 3, 1), r1 = lanes(iA, iB, 2, 0, 2, 0);
+    const Quad r2 = lanes(iC, iD, 3, 1, 3, 1), r3 = lanes(iC, iD, 2, 0, 2, 0);
     Matrix4f out;
-    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out.m[i * 4 + j] = (float) a[i][4 + j];
+    for (int i = 0; i < 4; ++i) { out.m[i * 4 + 0] = r0.v[i]; out.m[i * 4 + 1] = r1.v[i]; out.m[i * 4 + 2] = r2.v[i]; out.m[i * 4 + 3] = r3.v[i]; }
     return out;
 }
 

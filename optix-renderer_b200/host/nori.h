@@ -76,7 +76,7 @@ struct Matrix4f {
     float &operator()(int r, int c) { return m[r * 4 + c]; }
     float operator()(int r, int c) const { return m[r * 4 + c]; }
     Matrix4f operator*(const Matrix4f &o) const;
-    Matrix4f inverse() const;     /* computed in double, rounded once */
+    Matrix4f inverse() const;     /* Eigen's fp32 block-adjugate scheme, operation for operation */
 };
 
 /* Transform (include/nori/transform.h:20-100): matrix + inverse */

@@ -33,10 +33,18 @@ def built_lib(nb):
 
 
 @pytest.fixture(scope="session")
-def ctx(nb, built_lib):
+def _session_ctx(nb, built_lib):
     c = nb.Context(0)
     yield c
     c.close()
+
+
+@pytest.fixture
+def ctx(_session_ctx):
+    """One device context for the whole session, options back to their defaults per test."""
+    _session_ctx.set_option("strategy", 0)
+    _session_ctx.set_option("profile", 0)
+    return _session_ctx
 
 
 def golden(name):

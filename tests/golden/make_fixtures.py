@@ -11,6 +11,8 @@
   <name>_hits.bin        `nori_ref hits` result reduced to nb_hit records (n x 24 bytes)
   <name>_ref_<spp>.npy   reference CPU render of the *_small scene
   rng_kat.txt            pcg32 known-answer streams (`nori_ref rng`)
+  scenes/ttests/<pa>/    the reference's own Student-t known-answer scenes (scenes/pa3/tests,
+                         scenes/pa4/tests: XML with the expected radiance per scene + OBJ inputs)
 """
 import importlib
 import json
@@ -35,7 +37,14 @@ SCENES = {
     "cbox": ("pa4/cbox/cbox_path_mis.xml", (200, 150), 256, 6000),
     "cbox_mats": ("pa4/cbox/cbox_path_mats.xml", (200, 150), 256, 0),
     "table": ("pa4/table/table_path_mis.xml", (200, 150), 64, 6000),
+    # depth-1 integrators on the reference's pa3 scenes (microfacet plates, 4 mesh area lights)
+    "veach": ("pa3/veach_mi/veach_mis.xml", (192, 128), 64, 0),
+    "veach_ems": ("pa3/veach_mi/veach_ems.xml", (192, 128), 64, 0),
+    "veach_mats": ("pa3/veach_mi/veach_mats.xml", (192, 128), 64, 0),
+    "odyssey": ("pa3/odyssey/odyssey_ems.xml", (192, 108), 64, 0),
+    "odyssey_mis": ("pa3/odyssey/odyssey_mis.xml", (192, 108), 64, 0),
 }
+NO_FLAT = {"veach_ems", "veach_mats", "odyssey_mis"}     # same geometry as their first variant
 
 
 def run(*args):
@@ -98,11 +107,30 @@ def small_variant(xml, size):
     return out
 
 
+TTESTS = {"pa3": ["test-mesh.xml", "test-mesh-furnace.xml"], "pa4": ["test-direct.xml", "test-furnace.xml"]}
+
+
+def copy_ttests():
+    for pa, files in TTESTS.items():
+        src_dir = os.path.join(REF, "scenes", pa, "tests")
+        dst_dir = os.path.join(HERE, "scenes", "ttests", pa)
+        os.makedirs(dst_dir, exist_ok=True)
+        for f in files:
+            shutil.copyfile(os.path.join(src_dir, f), os.path.join(dst_dir, f))
+            for s in ET.parse(os.path.join(src_dir, f)).getroot().iter("string"):
+                if s.get("name") == "filename":
+                    shutil.copyfile(os.path.join(src_dir, s.get("value")), os.path.join(dst_dir, s.get("value")))
+
+
 def main():
     os.chmod(HERE, 0o755)
+    copy_ttests()
+    only = set(sys.argv[1:])
     for name, (xml_rel, small, spp, n_primary) in SCENES.items():
+        if only and name not in only:
+            continue
         xml = copy_scene(xml_rel, name.split("_")[0] if name != "cbox_mats" else "cbox")
-        nbs = os.path.join(HERE, name + ".nbs")
+        nbs = os.path.join(HERE, name + ".nbs") if name not in NO_FLAT else "/tmp/%s.nbs" % name
         print(run("flat", xml, nbs))
         sec = nb.read_nbs(nbs)
         shapes = sec["shapes"]

@@ -9,21 +9,16 @@ from conftest import golden
 
 
 @pytest.mark.parametrize("name,xml", [("cbox", "scenes/cbox/cbox_path_mis.xml"), ("cbox_mats", "scenes/cbox/cbox_path_mats.xml"),
-                                      ("table", "scenes/table/table_path_mis.xml")])
+                                      ("table", "scenes/table/table_path_mis.xml"),
+                                      ("veach", "scenes/veach/veach_mis.xml"), ("odyssey", "scenes/odyssey/odyssey_ems.xml")])
 def test_flatten_matches_reference_bit_for_bit(nb, built_lib, name, xml):
     got = nb.load_xml(golden(xml))
     want = nb.read_nbs(golden(name + ".nbs"))
     assert set(got) == set(want)
     for k in want:
-        if k == "camera":
-            continue
-        assert got[k].tobytes() == want[k].tobytes(), k       # vertices, tangents, CDFs, BVH nodes + indices, filter table
-    # camera: identical except the 4x4 inverse (Eigen fp32 cofactors there, double Gauss-Jordan here)
-    for f in got["camera"].dtype.names:
-        if f == "sample_to_camera":
-            np.testing.assert_allclose(got["camera"][f], want["camera"][f], rtol=2e-6, atol=1e-9)
-        else:
-            assert got["camera"][f].tobytes() == want["camera"][f].tobytes(), f
+        # vertices, normals (signed zeros included), tangents, CDFs, camera matrices (Eigen's fp32
+        # 4x4 inverse restated), filter table, BVH nodes + indices
+        assert got[k].tobytes() == want[k].tobytes(), k
 
 
 def test_bvh_structure(nb, built_lib):

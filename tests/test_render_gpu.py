@@ -11,7 +11,8 @@ from conftest import golden, rel_rmse
 pytestmark = pytest.mark.gpu
 
 
-def render(nb, ctx, scene, integrator, spp, size=None, seed=1, pool=0):
+def render(nb, ctx, scene, integrator, spp, size=None, seed=1, pool=0, strategy=0):
+    ctx.set_option("strategy", strategy)
     s = dict(scene)
     if size:
         cam = scene["camera"].copy()
@@ -43,6 +44,55 @@ def test_image_matches_reference(nb, ctx, name, integrator, spp, ref):
     print(name, "bias", bias, "relRMSE", err, "noise floor", floor, "invalid", ca["invalid_samples"])
     assert np.all(np.abs(bias) <= 0.01), bias
     assert err <= 1.25 * floor + 1e-3, (err, floor)
+
+
+@pytest.mark.parametrize("xml,ref,spp", [
+    ("veach/veach_mis_small.xml", "veach_ref_64spp.npy", 64),          # direct_mis, microfacet, 4 mesh lights
+    ("veach/veach_ems_small.xml", "veach_ems_ref_64spp.npy", 64),      # direct_ems
+    ("veach/veach_mats_small.xml", "veach_mats_ref_64spp.npy", 64),    # direct_mats
+    ("odyssey/odyssey_ems_small.xml", "odyssey_ref_64spp.npy", 64),
+    ("odyssey/odyssey_mis_small.xml", "odyssey_mis_ref_64spp.npy", 64),
+])
+def test_direct_integrators_match_reference(nb, ctx, xml, ref, spp):
+    """Depth-1 integrators on the reference's pa3 scenes, loaded from the reference's XML by the
+    C++ host loader, against reference CPU renders at equal spp."""
+    s = nb.load_xml(golden("scenes/" + xml))
+    want = np.load(golden(ref))
+    imgs = []
+    for seed in (1, 2):
+        ctx.load(s)
+        ctx.render_begin(nb.make_render_params(s, seed=seed))
+        ctx.render_subframe(0, spp)
+        imgs.append(ctx.film_download(normalize=True))
+    a, b = imgs
+    assert a.shape == want.shape and np.isfinite(a).all()
+    assert ctx.counters()["samples"] == a.shape[0] * a.shape[1] * spp
+    bias = (a.mean(axis=(0, 1)) - want.mean(axis=(0, 1))) / want.mean(axis=(0, 1))
+    floor, err = rel_rmse(a, b), rel_rmse(a, want)
+    print(xml, "bias", bias, "relRMSE", err, "noise floor", floor)
+    assert np.all(np.abs(bias) <= 0.02), bias
+    assert err <= 1.25 * floor + 1e-3, (err, floor)
+
+
+@pytest.mark.parametrize("name,integrator,spp", [("cbox", "path_mis", 64), ("cbox_mats", "path_mats", 64), ("table", "path_mis", 16)])
+def test_tile_strategy_equals_wavefront(nb, ctx, name, integrator, spp):
+    """K_tile (registers, one launch) and the wavefront pipeline draw the same pcg32 stream per
+    (pixel, sample) in the same order, so with one seed they trace the same paths: the images
+    agree far below the Monte-Carlo noise (not bit-for-bit: the film sums in a different order
+    and the two translation units may contract a*b+c differently in shading)."""
+    scene = nb.read_nbs(golden(name + ".nbs"))
+    size = (200, 150)
+    a, ca = render(nb, ctx, scene, integrator, spp, size=size, seed=3, strategy=1)
+    b, cb = render(nb, ctx, scene, integrator, spp, size=size, seed=3, strategy=2)
+    c, _ = render(nb, ctx, scene, integrator, spp, size=size, seed=4, strategy=2)
+    assert ca["samples"] == cb["samples"] == size[0] * size[1] * spp
+    assert cb["kernel_launches"] == 1
+    floor = rel_rmse(b, c)
+    diff = rel_rmse(a, b)
+    print(name, "tile vs wavefront relRMSE", diff, "noise floor", floor, "rays", ca["rays_closest"], cb["rays_closest"])
+    assert diff <= 0.05 * floor
+    assert abs(ca["rays_closest"] - cb["rays_closest"]) <= 1e-3 * ca["rays_closest"]
+    assert abs(ca["rays_any"] - cb["rays_any"]) <= 1e-3 * ca["rays_any"]
 
 
 def test_sample_slices_add_up(nb, ctx):

@@ -1,0 +1,81 @@
+"""The reference's own Student-t known-answer scenes (scenes/pa3/tests/test-mesh*.xml,
+scenes/pa4/tests/test-direct.xml, test-furnace.xml; 35 scenes covering direct_ems, direct_mats,
+direct_mis, path_mats and path_mis) run on the GPU backend.
+
+The reference (src/utils/ttest.cpp:191-240) draws 100 000 camera paths through a 1x1-pixel camera
+and t-tests the mean luminance against the value stored in the XML. Here each scene is loaded by
+the C++ host loader, rendered RENDERS times with independent seeds at SPP samples per pixel with a
+box filter (all weights 1, so the pixel is the plain sample mean), and the RENDERS pixel means are
+t-tested against the same reference value at the same significance level (0.01, Sidak-corrected
+for the number of scenes in the file, ext/hypothesis/hypothesis.h:314-346)."""
+import os
+import xml.etree.ElementTree as ET
+
+import numpy as np
+import pytest
+from scipy import stats
+
+from conftest import golden
+
+pytestmark = pytest.mark.gpu
+
+RENDERS, SPP = 24, 8192
+FILES = ["pa3/test-mesh.xml", "pa3/test-mesh-furnace.xml", "pa4/test-direct.xml", "pa4/test-furnace.xml"]
+
+
+def scenes_of(path, tmp_path):
+    """(reference value, scene xml file) per <scene> of a <test type="ttest"> file."""
+    root = ET.parse(path).getroot()
+    assert root.tag == "test" and root.get("type") == "ttest"
+    refs = None
+    for c in root:
+        if c.tag == "string" and c.get("name") == "references":
+            refs = [float(x) for x in c.get("value").replace(",", " ").split()]
+    scenes = [c for c in root if c.tag == "scene"]
+    assert refs is not None and len(refs) == len(scenes)
+    out = []
+    for i, sc in enumerate(scenes):
+        for s in sc.iter("string"):
+            if s.get("name") == "filename":     # OBJ paths are relative to the test file
+                s.set("value", os.path.join(os.path.dirname(path), s.get("value")))
+        f = tmp_path / ("scene%02d.xml" % i)
+        ET.ElementTree(sc).write(f)
+        out.append((refs[i], str(f), sc.find("integrator").get("type")))
+    return out
+
+
+def luminance(rgb):                               # Color3f::getLuminance, src/utils/common.cpp
+    return rgb[..., 0] * 0.212671 + rgb[..., 1] * 0.715160 + rgb[..., 2] * 0.072169
+
+
+@pytest.mark.parametrize("strategy", ["wavefront", "tile"])
+@pytest.mark.parametrize("rel", FILES)
+def test_reference_known_answers(nb, ctx, tmp_path, rel, strategy):
+    cases = scenes_of(golden("scenes/ttests/" + rel), tmp_path)
+    alpha = 1.0 - (1.0 - 0.01) ** (1.0 / len(cases))
+    ctx.set_option("strategy", {"wavefront": 1, "tile": 2}[strategy])
+    failures = []
+    for ref, xml, integ in cases:
+        s = nb.load_xml(xml)
+        assert s["camera"]["width"] == 1 and s["camera"]["height"] == 1
+        ctx.load(s)
+        means = []
+        for k in range(RENDERS):
+            rp = nb.make_render_params(s, integ, seed=1000 + k, pool_paths=8192)
+            rp["filter_radius"] = 0.5
+            rp["filter_table"][0, :] = 1.0
+            rp["filter_table"][0, -1] = 0.0
+            ctx.render_begin(rp)
+            ctx.render_subframe(0, SPP)
+            means.append(float(luminance(ctx.film_download(normalize=True))[0, 0]))
+        assert ctx.counters()["samples"] == SPP
+        means = np.array(means)
+        mean, var = means.mean(), means.var(ddof=1)
+        t = abs(mean - ref) * np.sqrt(RENDERS / max(var, 1e-12))
+        p = 2.0 * stats.t.sf(t, RENDERS - 1)
+        print("%-12s ref %.6f mean %.6f sd(mean) %.2e t %.2f p %.3f" % (integ, ref, mean, np.sqrt(var / RENDERS), t, p))
+        # a deterministic scene (zero variance) must hit the reference to fp32 accuracy
+        ok = abs(mean - ref) <= 2e-6 * max(1.0, abs(ref)) + 5e-7 if var < 1e-14 else p >= alpha
+        if not ok:
+            failures.append((integ, ref, mean, p))
+    assert not failures, failures
