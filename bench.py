@@ -133,6 +133,7 @@ def main():
     ap.add_argument("--ref-spp", type=int, default=16)
     ap.add_argument("--pool", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strategy", default="auto", choices=["auto", "wavefront", "tile"])
     args = ap.parse_args()
     if args.impl == "reference":
         return impl_reference(args)
@@ -151,6 +152,7 @@ def main():
     scene = nb.read_nbs(SCENE_NBS)
     params = nb.make_render_params(scene, "path_mis", seed=1, pool_paths=args.pool)
     ctx = nb.Context(local)
+    ctx.set_option("strategy", {"auto": 0, "wavefront": 1, "tile": 2}[args.strategy])
     ctx.load(scene)
     ctx.render_begin(params)
     film = nb.film_tensor(ctx, local)
@@ -171,6 +173,7 @@ def main():
     torch.cuda.synchronize()
     dev_ms, c0 = 0.0, None
     launches = samples = rays = 0
+    kernel_ms = 0.0
     barrier()
     with ClockSampler(local) as clk:
         for _ in range(args.steps):
@@ -184,6 +187,8 @@ def main():
             dev_ms += e0.elapsed_time(e1)
             c = ctx.counters()
             launches += c["kernel_launches"] + (1 if world > 1 else 0)
+            kernel_ms += c["device_ms"]
+            single_launch = c["kernel_launches"] == 1
             samples += c["samples"]; rays += c["rays_closest"] + c["rays_any"]
     barrier()
     t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
@@ -215,26 +220,36 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX); dist.all_reduce(se, op=dist.ReduceOp.SUM)
 
     if rank == 0:
-        # ---- roofline of the dominant kernel (K_trace), one extra profiled step
-        ctx.render_begin(params)
-        ctx.set_option("profile", 1)
-        ctx.render_subframe(0, max(16, args.spp // 8))
-        ctx.set_option("profile", 0)
-        pc = ctx.counters()
         stats = json.load(open(os.path.join(GOLDEN, "cbox_raystats.json")))
         # algorithmic bytes per ray: 32 B per node visited + 48 B per primitive tested
         # + 32 B ray in + 16 B hit out, with the oracle's mean counters for this ray population
         bytes_per_ray = 32.0 * stats["mean_nodes_visited"] + 48.0 * stats["mean_prims_tested"] + 48.0
-        prof_rays = pc["rays_closest"] + pc["rays_any"]
-        achieved = bytes_per_ray * prof_rays / (pc["trace_ms"] * 1e-3) / 1e9 if pc["trace_ms"] > 0 else None
         peak, how = measured_peak()
-        roofline = {"bound": "hbm", "kernel": "nb_k_trace_wave", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak if achieved else None, "traffic": None, "peak_source": how,
-                    "bytes_per_ray": bytes_per_ray, "launches_timed": int(pc["iterations"]),
-                    "avg_launch_ms": pc["trace_ms"] / max(1, pc["iterations"]),
-                    "kernel_share": {"trace": pc["trace_ms"] / pc["device_ms"], "shade": pc["shade_ms"] / pc["device_ms"], "regen": pc["regen_ms"] / pc["device_ms"]},
-                    "note": "cbox is 14 primitives (L1-resident): K_trace is SM-issue-bound, the HBM figure is the "
-                            "algorithmic-bytes convention of SURVEY 8(d); see DESIGN.md for the issue roofline"}
+        note = ("cbox is 14 primitives (L1-resident): the kernel is SM-issue-bound, the HBM figure is the "
+                "algorithmic-bytes convention of SURVEY 8(d); see DESIGN.md for the issue roofline")
+        if single_launch:
+            # K_tile: the step IS one launch of the dominant kernel, timed by the library's own
+            # CUDA events on its launch stream during the timed steps above
+            achieved = bytes_per_ray * rays / (kernel_ms * 1e-3) / 1e9
+            roofline = {"bound": "hbm", "kernel": "nb_k_tile<path_mis>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak, "traffic": None, "peak_source": how, "bytes_per_ray": bytes_per_ray,
+                        "launches_timed": args.steps, "avg_launch_ms": kernel_ms / args.steps,
+                        "kernel_share": {"tile": kernel_ms / ms}, "note": note}
+        else:
+            # wavefront: dominant kernel K_trace, one extra step with per-kernel event timers
+            ctx.render_begin(params)
+            ctx.set_option("profile", 1)
+            ctx.render_subframe(0, max(16, args.spp // 8))
+            ctx.set_option("profile", 0)
+            pc = ctx.counters()
+            prof_rays = pc["rays_closest"] + pc["rays_any"]
+            achieved = bytes_per_ray * prof_rays / (pc["trace_ms"] * 1e-3) / 1e9 if pc["trace_ms"] > 0 else None
+            roofline = {"bound": "hbm", "kernel": "nb_k_trace_wave", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak if achieved else None, "traffic": None, "peak_source": how,
+                        "bytes_per_ray": bytes_per_ray, "launches_timed": int(pc["iterations"]),
+                        "avg_launch_ms": pc["trace_ms"] / max(1, pc["iterations"]),
+                        "kernel_share": {"trace": pc["trace_ms"] / pc["device_ms"], "shade": pc["shade_ms"] / pc["device_ms"], "regen": pc["regen_ms"] / pc["device_ms"]},
+                        "note": note}
         cpu = None
         if not args.no_cpu_baseline:
             try:
@@ -248,6 +263,7 @@ def main():
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "spp_per_gpu": args.spp, "integrator": "path_mis",
+                           "strategy": "tile" if single_launch else "wavefront",
                            "parallelism": "sample slices x%d, scene replicated, 1 NCCL film reduce" % world,
                            "l2": "256 MB flush write between timed steps; path pool (1M slots x 164 B) exceeds L2"},
                 "rays_per_s": rays_all / (ms * 1e-3), "rays_per_sample": rays_all / samples_all,

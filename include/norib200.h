@@ -209,7 +209,8 @@ int  nb_film_device_ptr(nb_ctx *ctx, void **ptr, uint64_t *n_floats);
 int  nb_get_counters(nb_ctx *ctx, nb_counters *out);
 /* options: "profile" (per-kernel event timers of the wavefront pipeline), "sort" (reserved),
  * "strategy" (NB_STRATEGY_*: how path_mis / path_mats are executed; the direct_* integrators
- * always run as one K_tile launch) */
+ * always run as one K_tile launch), "flat_scan" (-1 auto, 0 always walk the tree, 1 always scan
+ * the primitive list: same hits, see nb_trace.cuh) */
 enum { NB_STRATEGY_AUTO = 0, NB_STRATEGY_WAVEFRONT = 1, NB_STRATEGY_TILE = 2 };
 int  nb_set_option(nb_ctx *ctx, const char *name, int64_t value);
 

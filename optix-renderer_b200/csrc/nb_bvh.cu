@@ -107,6 +107,7 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->dev.nodes = (const float4 *) dn; ctx->dev.slots = (const float4 *) ds;
     ctx->dev.n_nodes = n; ctx->dev.n_slots = ni;
+    ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;
     ctx->h_slot_tag.resize(ni); ctx->h_slot_prim.resize(ni);
     for (uint32_t k = 0; k < ni; ++k) {
         memcpy(&ctx->h_slot_tag[k], &slots[(size_t) k * 3 + 2].y, 4);

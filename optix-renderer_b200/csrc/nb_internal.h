@@ -24,11 +24,13 @@
 #define NB_NODE_END 0xffffffffu
 #define NB_NODE_INNER 0xffffffffu
 #define NB_NODE_EMPTY_LEAF 0xfffffffeu
+#define NB_FLAT_MAX_SLOTS 24u
 
 struct NbDeviceScene {
     const float4 *nodes = nullptr;      /* 2 per node */
     const float4 *slots = nullptr;      /* 3 per primitive slot */
     uint32_t n_nodes = 0, n_slots = 0;
+    uint32_t flat = 0;                  /* queries scan the slots instead of walking the tree (nb_trace.cuh) */
     /* shading data */
     const nb_shape *shapes = nullptr;
     const float *positions = nullptr, *normals = nullptr, *uvs = nullptr, *tangents = nullptr, *bitangents = nullptr;
@@ -59,9 +61,14 @@ struct nb_ctx {
     NbRenderState *render = nullptr;
     int sm_count = 148;
     int opt_profile = 0, opt_sort = 0, opt_strategy = 0;
+    int opt_flat = -1;                  /* -1: flat scan iff the scene has at most NB_FLAT_MAX_SLOTS primitives */
 };
 
 int nb_fail(nb_ctx *ctx, int code, const char *fmt, ...);
+inline bool nb_scene_flat(const nb_ctx *ctx) {
+    if (ctx->opt_flat >= 0) return ctx->opt_flat != 0;
+    return ctx->dev.n_slots <= NB_FLAT_MAX_SLOTS;
+}
 #define NB_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
     return nb_fail(ctx, NB_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
 

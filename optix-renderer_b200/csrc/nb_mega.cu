@@ -24,7 +24,7 @@
 #define NB_TILE_THREADS 128
 #endif
 #ifndef NB_TILE_MIN_BLOCKS
-#define NB_TILE_MIN_BLOCKS 4
+#define NB_TILE_MIN_BLOCKS 6
 #endif
 
 struct NbTilePlan {
@@ -61,9 +61,14 @@ __device__ __forceinline__ f3 nb_area_eval(const nb_emitter &em, f3 ref, f3 p, f
     return mk3(0.f);
 }
 
+template <bool FLAT>
 __device__ __forceinline__ bool nb_occluded(const NbDeviceScene &sc, f3 o, f3 d, float mint, float maxt) {
     NbHit dummy;
-    return nb_traverse<true>(sc.nodes, sc.slots, sc.n_nodes, o, d, mint, maxt, dummy);
+    return nb_query<true, FLAT>(sc.nodes, sc.slots, sc.n_nodes, sc.n_slots, o, d, mint, maxt, dummy);
+}
+template <bool FLAT>
+__device__ __forceinline__ bool nb_closest(const NbDeviceScene &sc, f3 o, f3 d, float mint, float maxt, NbHit &hit) {
+    return nb_query<false, FLAT>(sc.nodes, sc.slots, sc.n_nodes, sc.n_slots, o, d, mint, maxt, hit);
 }
 
 /* One bounce of path_mis / path_mats for a path whose closest hit just arrived. Returns false
@@ -132,11 +137,11 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
 }
 
 /* The depth-1 integrators, one whole sample. Returns Li. */
-template <int INTEG>
+template <int INTEG, bool FLAT>
 __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any) {
     NbHit hit;
     ++n_closest;
-    if (!nb_traverse<false>(sc.nodes, sc.slots, sc.n_nodes, ps.o, ps.d, ps.mint, ps.maxt, hit)) return mk3(0.f);
+    if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) return mk3(0.f);
     nb_shape sh; NbIts its;
     nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
     f3 result = mk3(0.f);
@@ -154,7 +159,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
             const f3 li = nb_emitter_sample(sc, sc.emitters[l], its.p, s, es);
             const f3 wi = its.sh.to_local(es.wi);
             ++n_any;
-            if (nb_occluded(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
+            if (nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
             const float c = fabsf(dot(es.wi, its.sh.n)) / length(es.wi);
             result += li * c * nb_bsdf_eval(bsdf, wi, wo);
         }
@@ -168,7 +173,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
             const f3 li = nb_emitter_sample(sc, sc.emitters[l], its.p, s, es);
             if (is_zero(li, NB_EPS)) continue;
             ++n_any;
-            if (nb_occluded(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
+            if (nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
             const f3 we = its.sh.to_local(es.wi);
             result += li * fabsf(we.z) * nb_bsdf_eval(bsdf, wi, we);
         }
@@ -183,7 +188,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
         const f3 li = nb_emitter_sample(sc, sc.emitters[ei], its.p, s, es);
         if (!is_zero(li, NB_EPS)) {
             ++n_any;
-            if (!nb_occluded(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) {
+            if (!nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) {
                 const f3 we = its.sh.to_local(es.wi);
                 const float pdf_ems = es.pdf / n_lights, pdf_mat = nb_bsdf_pdf(bsdf, wi, we);
                 result_ems = li * we.z * nb_bsdf_eval(bsdf, wi, we) * n_lights;
@@ -199,7 +204,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
         const f3 d2 = its.sh.to_world(wo);
         NbHit hit2;
         ++n_closest;
-        if (nb_traverse<false>(sc.nodes, sc.slots, sc.n_nodes, its.p, d2, NB_EPS, INFINITY, hit2)) {
+        if (nb_closest<FLAT>(sc, its.p, d2, NB_EPS, INFINITY, hit2)) {
             nb_shape sh2; NbIts its2;
             nb_hit_info(sc, hit2, its.p, d2, sh2, its2);
             if (sh2.emitter >= 0) {
@@ -216,7 +221,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
 }
 
 /* ---- K_tile ---------------------------------------------------------------------------------- */
-template <int INTEG>
+template <int INTEG, bool FLAT>
 __global__ void __launch_bounds__(NB_TILE_THREADS, NB_TILE_MIN_BLOCKS)
 nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     constexpr bool PATH = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_MATS;
@@ -275,12 +280,12 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
             if (active) {
                 NbHit hit;
                 ++n_closest;
-                if (!nb_traverse<false>(sc.nodes, sc.slots, sc.n_nodes, ps.o, ps.d, ps.mint, ps.maxt, hit)) ended = true;
+                if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) ended = true;
                 else ended = !nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
             }
             if (MIS && shadow) {
                 ++n_any;
-                if (!nb_occluded(sc, so.o, so.d, so.mint, so.maxt)) {
+                if (!nb_occluded<FLAT>(sc, so.o, so.d, so.mint, so.maxt)) {
                     /* path_mis.cpp:102-105,141: w_ems is updated only when the pdf sum passes the
                      * Epsilon test, otherwise the value of an earlier bounce is used */
                     if (so.cand >= 0.f) ps.w_ems = so.cand;
@@ -292,7 +297,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 active = false;
             }
         } else if (active) {
-            const f3 Li = nb_direct_sample<INTEG>(sc, ps, n_closest, n_any);
+            const f3 Li = nb_direct_sample<INTEG, FLAT>(sc, ps, n_closest, n_any);
             nb_film_put(film, ps.px, ps.py, Li, stats);
             active = false;
         }
@@ -309,11 +314,11 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     }
 }
 
-template <int INTEG>
-static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
+template <int INTEG, bool FLAT>
+static cudaError_t nb_tile_launch_flat(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
                                     unsigned long long *stats, int sm_count, cudaStream_t stream) {
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile<INTEG>, NB_TILE_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile<INTEG, FLAT>, NB_TILE_THREADS, 0);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
     const uint64_t warps_wanted = ((uint64_t) tp.n_items + 0) ;
@@ -321,8 +326,15 @@ static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film,
     const uint64_t blocks_useful = (warps_wanted + NB_TILE_THREADS / 32 - 1) / (NB_TILE_THREADS / 32);
     if (blocks > blocks_useful) blocks = blocks_useful;
     if (blocks < 1) blocks = 1;
-    nb_k_tile<INTEG><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
+    nb_k_tile<INTEG, FLAT><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
     return cudaGetLastError();
+}
+
+template <int INTEG>
+static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
+                                    unsigned long long *stats, int sm_count, cudaStream_t stream) {
+    return sc.flat ? nb_tile_launch_flat<INTEG, true>(sc, film, tp, item_counter, stats, sm_count, stream)
+                   : nb_tile_launch_flat<INTEG, false>(sc, film, tp, item_counter, stats, sm_count, stream);
 }
 
 /* Host entry used by nb_render_subframe. `passes` sample passes over the image, pass k drawing

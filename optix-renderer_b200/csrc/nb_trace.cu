@@ -3,19 +3,20 @@
 #include "nb_wavefront.h"
 
 /* Parity / benchmark entry: one thread per ray, rays as two float4 {o, mint} {d, maxt}. */
+template <bool FLAT>
 __global__ void __launch_bounds__(256)
-nb_k_trace_hits(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes,
+nb_k_trace_hits(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes, uint32_t n_slots,
                 const float4 *__restrict__ rays, uint64_t n, int any_hit,
                 float4 *__restrict__ out, uint32_t *__restrict__ out_any) {
     for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
         const float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
         const float3 o = make_float3(ro.x, ro.y, ro.z), d = make_float3(rd.x, rd.y, rd.z);
         NbHit hit;
-        nb_traverse<false>(nodes, slots, n_nodes, o, d, ro.w, rd.w, hit);
+        nb_query<false, FLAT>(nodes, slots, n_nodes, n_slots, o, d, ro.w, rd.w, hit);
         out[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot));
         if (any_hit) {
             NbHit dummy;
-            out_any[i] = nb_traverse<true>(nodes, slots, n_nodes, o, d, ro.w, rd.w, dummy) ? 1u : 0u;
+            out_any[i] = nb_query<true, FLAT>(nodes, slots, n_nodes, n_slots, o, d, ro.w, rd.w, dummy) ? 1u : 0u;
         }
     }
 }
@@ -26,8 +27,12 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
     uint64_t blocks = (n + 255) / 256;
     const uint64_t cap = (uint64_t) sm_count * 64;      /* grid-stride beyond 64 CTAs per SM */
     if (blocks > cap) blocks = cap;
-    nb_k_trace_hits<<<(unsigned) blocks, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, rays, n,
-                                                           any_hit, out, out_any);
+    if (scene.flat)
+        nb_k_trace_hits<true><<<(unsigned) blocks, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, rays, n,
+                                                                     any_hit, out, out_any);
+    else
+        nb_k_trace_hits<false><<<(unsigned) blocks, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, rays, n,
+                                                                      any_hit, out, out_any);
 }
 
 /* ---- wavefront stage: K_trace -------------------------------------------------------------
@@ -37,8 +42,9 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
  *                          (path_mis.cpp:87-89); an unoccluded one adds its pre-weighted
  *                          contribution to the path's radiance and commits the candidate w_ems.
  * Grid-stride over counts read from device memory, so the host never waits on them. */
+template <bool FLAT>
 __global__ void __launch_bounds__(256)
-nb_k_trace_wave(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes, NbWave w) {
+nb_k_trace_wave(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes, uint32_t n_slots, NbWave w) {
     /* live paths = survivors of K_shade + the paths K_regen could start within the sample budget */
     const unsigned long long base = ((unsigned long long) w.counts[NB_CNT_BASE_HI] << 32) | w.counts[NB_CNT_BASE_LO];
     const unsigned long long left = w.total_samples - base;
@@ -59,16 +65,16 @@ nb_k_trace_wave(const float4 *__restrict__ nodes, const float4 *__restrict__ slo
             const uint32_t p = w.queue_next[i];
             const float4 ro = w.ray_o[p], rd = w.ray_d[p];
             NbHit hit;
-            nb_traverse<false>(nodes, slots, n_nodes, make_float3(ro.x, ro.y, ro.z), make_float3(rd.x, rd.y, rd.z),
-                               ro.w, rd.w, hit);
+            nb_query<false, FLAT>(nodes, slots, n_nodes, n_slots, make_float3(ro.x, ro.y, ro.z), make_float3(rd.x, rd.y, rd.z),
+                                  ro.w, rd.w, hit);
             w.hit[p] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot));
             if (!(rd.w < ro.w)) ++closest;      /* ended paths park their ray with maxt < mint */
         } else {
             const uint32_t j = i - n_main;
             const float4 ro = w.sh_o[j], rd = w.sh_d[j], c = w.sh_c[j];
             NbHit dummy;
-            const bool occluded = nb_traverse<true>(nodes, slots, n_nodes, make_float3(ro.x, ro.y, ro.z),
-                                                    make_float3(rd.x, rd.y, rd.z), ro.w, rd.w, dummy);
+            const bool occluded = nb_query<true, FLAT>(nodes, slots, n_nodes, n_slots, make_float3(ro.x, ro.y, ro.z),
+                                                       make_float3(rd.x, rd.y, rd.z), ro.w, rd.w, dummy);
             ++any;
             if (!occluded) {
                 const uint32_t p = __float_as_uint(c.w) & 0x7fffffffu;
@@ -98,5 +104,6 @@ nb_k_trace_wave(const float4 *__restrict__ nodes, const float4 *__restrict__ slo
 }
 
 void nb_launch_trace_wave(const NbDeviceScene &scene, const NbWave &w, int grid, cudaStream_t stream) {
-    nb_k_trace_wave<<<grid, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, w);
+    if (scene.flat) nb_k_trace_wave<true><<<grid, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, w);
+    else nb_k_trace_wave<false><<<grid, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, w);
 }

@@ -5,7 +5,8 @@
  * Sphere::rayIntersect (src/shapes/sphere.cpp:67-94) operation by operation:
  *   - fp32, no FMA contraction: every product/sum that decides a hit is written with the
  *     round-to-nearest intrinsics (__fmul_rn/__fadd_rn/__fsub_rn), which nvcc never fuses, so the
- *     header gives the same bits in any translation unit (x86-64 gcc emits no FMA for the reference),
+ *     header gives the same bits in any translation unit, whatever -fmad / -prec-div / -prec-sqrt
+ *     say (x86-64 gcc emits no FMA for the reference); divisions and the square root likewise,
  *   - Eigen 3.3.8 association: dot3 = a0*b0 + (a1*b1 + a2*b2) (Eigen/src/Core/Redux.h:91-105),
  *     cross as Eigen/src/Geometry/OrthoMethods.h:43-47,
  *   - std::max/std::min/std::swap written as the comparisons they are (NaN behaviour included),
@@ -60,7 +61,7 @@ __device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, con
     const float pvx = nb_det2(d.y, e2z, d.z, e2y), pvy = nb_det2(d.z, e2x, d.x, e2z), pvz = nb_det2(d.x, e2y, d.y, e2x);
     const float det = nb_dot3(e1x, e1y, e1z, pvx, pvy, pvz);
     if (det > -1e-8f && det < 1e-8f) return false;
-    const float inv = 1.0f / det;
+    const float inv = __fdiv_rn(1.0f, det);
     const float tvx = __fsub_rn(o.x, p0x), tvy = __fsub_rn(o.y, p0y), tvz = __fsub_rn(o.z, p0z);
     u = __fmul_rn(nb_dot3(tvx, tvy, tvz, pvx, pvy, pvz), inv);
     if (u < 0.0f || u > 1.0f) return false;
@@ -80,9 +81,9 @@ __device__ __forceinline__ bool nb_sphere_hit(const float4 s0, const float3 o, c
     const float c = __fsub_rn(nb_dot3(Lx, Ly, Lz, Lx, Ly, Lz), __fmul_rn(s0.w, s0.w));
     const float discr = __fsub_rn(__fmul_rn(b, b), __fmul_rn(__fmul_rn(4.f, a), c));
     if (discr < 0.f) return false;
-    const double sd = sqrt((double) discr), nb = (double) (-b), da = (double) a;
-    const float tmin = (float) (__dsub_rn(nb, sd) / 2.0 / da);
-    const float tmax = (float) (__dadd_rn(nb, sd) / 2.0 / da);
+    const double sd = __dsqrt_rn((double) discr), nb = (double) (-b), da = (double) a;
+    const float tmin = (float) __ddiv_rn(__ddiv_rn(__dsub_rn(nb, sd), 2.0), da);
+    const float tmax = (float) __ddiv_rn(__ddiv_rn(__dadd_rn(nb, sd), 2.0), da);
     if (mint <= tmin && maxt >= tmin) { t = tmin; return true; }
     if (mint <= tmax && maxt >= tmax) { t = tmax; return true; }
     return false;
@@ -102,7 +103,7 @@ __device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, co
         mint = (mint < s) ? s : mint;
     }
     if (n_nodes == 0 || maxt < mint) return false;
-    const float3 r = make_float3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);   /* Ray3f::update, ray.h */
+    const float3 r = make_float3(__fdiv_rn(1.0f, d.x), __fdiv_rn(1.0f, d.y), __fdiv_rn(1.0f, d.z));   /* Ray3f::update, ray.h */
     bool found = false;
     uint32_t idx = 0;
     while (idx != NB_NODE_END) {
@@ -130,4 +131,47 @@ __device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, co
         idx = skip;
     }
     return found;
+}
+
+/* Flat scan for scenes of a few primitives (the Cornell box has 14): test every slot in leaf
+ * order, no tree. The reference's left-first walk also visits leaves in exactly this order and
+ * only skips primitives whose node box the ray misses within [mint, current maxt] — primitives
+ * that could not have been accepted anyway — so the sequence of accepted hits, and with it the
+ * reported (t, u, v, primitive), is the same; every lane of a warp executes the same slot at the
+ * same time, which the per-lane tree walk cannot offer. nb_trace_rays checks it against the same
+ * 1M-ray oracle set as the tree walk (tests/test_trace_gpu.py). */
+template <bool ANY>
+__device__ __forceinline__ bool nb_scan(const float4 *__restrict__ slots, uint32_t n_slots, float3 o, float3 d,
+                                        float mint, float maxt, NbHit &hit) {
+    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
+    if (mint == NB_EPSILON) {
+        float m = fabsf(o.x);
+        m = fmaxf(m, fabsf(o.y));
+        m = fmaxf(m, fabsf(o.z));
+        const float s = __fmul_rn(mint, m);
+        mint = (mint < s) ? s : mint;
+    }
+    if (maxt < mint) return false;
+    bool found = false;
+    for (uint32_t s = 0; s < n_slots; ++s) {
+        const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
+        float u = 0.f, v = 0.f, t;
+        const bool ok = (__float_as_uint(s2.y) & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
+                                                                : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+        if (ok) {
+            if (ANY) return true;
+            found = true;
+            maxt = t;
+            hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+        }
+    }
+    return found;
+}
+
+/* The query the render kernels use: tree walk, or flat scan when the scene qualifies. */
+template <bool ANY, bool FLAT>
+__device__ __forceinline__ bool nb_query(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes,
+                                         uint32_t n_slots, float3 o, float3 d, float mint, float maxt, NbHit &hit) {
+    if (FLAT) return nb_scan<ANY>(slots, n_slots, o, d, mint, maxt, hit);
+    return nb_traverse<ANY>(nodes, slots, n_nodes, o, d, mint, maxt, hit);
 }

@@ -44,6 +44,7 @@ def ctx(_session_ctx):
     """One device context for the whole session, options back to their defaults per test."""
     _session_ctx.set_option("strategy", 0)
     _session_ctx.set_option("profile", 0)
+    _session_ctx.set_option("flat_scan", -1)
     return _session_ctx
 
 

@@ -10,7 +10,8 @@ from conftest import golden, have_oracle_binary, run_oracle
 pytestmark = pytest.mark.gpu
 
 
-def check(nb, ctx, scene, rays, want):
+def check(nb, ctx, scene, rays, want, flat=-1):
+    ctx.set_option("flat_scan", flat)       # 0: the reference's tree walk; 1: flat scan of the primitive list
     ctx.load(scene)
     got = ctx.trace_rays(rays, any_hit=True)
     assert len(got) == len(want)
@@ -23,18 +24,20 @@ def check(nb, ctx, scene, rays, want):
     assert np.array_equal(got["any_hit"], want["any_hit"])
 
 
+@pytest.mark.parametrize("flat", [0, 1])
 @pytest.mark.parametrize("name", ["cbox", "table"])
-def test_golden_hits_bit_exact(nb, ctx, name):
+def test_golden_hits_bit_exact(nb, ctx, name, flat):
     scene = nb.read_nbs(golden(name + ".nbs"))
     rays = np.fromfile(golden(name + "_rays.bin"), dtype="<f4").reshape(-1, 8)
     want = np.fromfile(golden(name + "_hits.bin"), dtype=nb.hit_dtype)
     assert len(rays) > 20000
-    check(nb, ctx, scene, rays, want)
+    check(nb, ctx, scene, rays, want, flat)
 
 
 @pytest.mark.skipif(not have_oracle_binary(), reason="oracle/_ref/nori_ref not present")
+@pytest.mark.parametrize("flat", [0, 1])
 @pytest.mark.parametrize("name,xml,n", [("cbox", "scenes/cbox/cbox_path_mis.xml", 200000), ("table", "scenes/table/table_path_mis.xml", 150000)])
-def test_live_oracle_hits_bit_exact(nb, ctx, name, xml, n, tmp_path):
+def test_live_oracle_hits_bit_exact(nb, ctx, name, xml, n, tmp_path, flat):
     """~1M rays per scene: primary, bounce (mint == Epsilon -> adaptive epsilon) and NEE shadow
     rays with finite maxt, answered by the reference code itself on this machine."""
     rays_f, hits_f = str(tmp_path / "rays.bin"), str(tmp_path / "hits.bin")
@@ -50,7 +53,7 @@ def test_live_oracle_hits_bit_exact(nb, ctx, name, xml, n, tmp_path):
     want["t"], want["u"], want["v"] = tuv[:, 0], tuv[:, 1], tuv[:, 2]
     want["any_hit"] = full[:, 28:32].copy().view("<u4")[:, 0]
     assert len(rays) > 500000
-    check(nb, ctx, scene, rays, want)
+    check(nb, ctx, scene, rays, want, flat)
 
 
 def test_edge_cases(nb, ctx):
