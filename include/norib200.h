@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 1
+#define NB_ABI_VERSION 2
 
 enum {
     NB_OK = 0,
@@ -42,7 +42,10 @@ enum { NB_BSDF_DIFFUSE = 0, NB_BSDF_MIRROR = 1, NB_BSDF_DIELECTRIC = 2, NB_BSDF_
 enum { NB_EMITTER_AREA = 0, NB_EMITTER_POINT = 1, NB_EMITTER_ENVMAP = 2 };
 enum { NB_INTEGRATOR_PATH_MIS = 0, NB_INTEGRATOR_PATH_MATS = 1, NB_INTEGRATOR_DIRECT_EMS = 2,
        NB_INTEGRATOR_DIRECT_MATS = 3, NB_INTEGRATOR_DIRECT_MIS = 4, NB_INTEGRATOR_NORMALS = 5,
-       NB_INTEGRATOR_DIRECT = 6, NB_INTEGRATOR_AV = 7 };
+       NB_INTEGRATOR_DIRECT = 6, NB_INTEGRATOR_AV = 7, NB_INTEGRATOR_PATH_VOL_MATS = 8,
+       NB_INTEGRATOR_PATH_VOL_MIS = 9 };
+enum { NB_MEDIUM_VACUUM = 0, NB_MEDIUM_HOMOGENEOUS = 1, NB_MEDIUM_HETEROGENEOUS = 2 };
+enum { NB_PHASE_ISOTROPIC = 0, NB_PHASE_HENYEY_GREENSTEIN = 1, NB_PHASE_SCHLICK = 2 };
 enum { NB_SHAPE_HAS_NORMALS = 1u, NB_SHAPE_HAS_UVS = 2u };
 
 /* ---- scene records ------------------------------------------------------------------------- */
@@ -58,7 +61,7 @@ typedef struct nb_shape {
     uint32_t flags;          /* NB_SHAPE_HAS_* */
     int32_t  bsdf;           /* index into bsdfs, -1 = none (medium interface) */
     int32_t  emitter;        /* index into emitters, -1 = not a light */
-    int32_t  medium;         /* reserved (volume path), -1 */
+    int32_t  medium;         /* index into media (Shape::getMedium, shape.h:146), -1 = none */
     uint32_t cdf_offset;     /* first of prim_count+1 floats in area_cdf (DiscretePDF::m_cdf) */
     float    pdf_norm;       /* DiscretePDF::getNormalization() = 1/total area (mesh.cpp:70) */
     float    radius;         /* sphere */
@@ -103,6 +106,23 @@ typedef struct nb_bvh_node {
     float    bmin[3], bmax[3];
 } nb_bvh_node;               /* 32 bytes */
 
+/* One Medium with its phase function (replaces Medium::getOptixMediumData, medium.h:68).
+ * Homogeneous (src/media/homogmedium.cpp:48-73): mu_t = density * (sigma_a + sigma_s) per channel.
+ * Heterogeneous (src/media/heterogmedium.cpp): density on a dense grid (first_voxel/dims into the
+ * scene's density array, index space mapped by world_to_grid), majorant max_density, scaled by
+ * density_scale; see DESIGN.md for what is and is not pinned there. */
+typedef struct nb_medium {
+    uint32_t type;           /* NB_MEDIUM_* */
+    float    mu_t[3];        /* homogeneous: extinction; heterogeneous: sigma_t = sigma_a + sigma_s */
+    uint32_t phase;          /* NB_PHASE_* (src/bsdf/isophase.cpp, anisophase.cpp, schlickphase.cpp) */
+    float    phase_param;    /* g (Henyey-Greenstein) or k = 1.55 g - 0.55 g^3 (Schlick) */
+    float    density_scale;  /* heterogeneous */
+    float    max_density;    /* heterogeneous: unscaled grid maximum */
+    uint32_t grid_dims[3];   /* heterogeneous: voxels in x, y, z */
+    uint32_t first_voxel;    /* heterogeneous: offset into nb_scene_desc.density */
+    float    world_to_grid[12]; /* heterogeneous: row-major 3x4, world point -> voxel coordinates */
+} nb_medium;                 /* 96 bytes */
+
 typedef struct nb_scene_desc {
     uint32_t n_shapes;    const nb_shape   *shapes;
     uint64_t n_vertices;  const float      *positions;   /* 3 per vertex, world space */
@@ -116,6 +136,9 @@ typedef struct nb_scene_desc {
                           const float      *emitter_cdf; /* n_emitters+1 (scene.cpp:180-184) */
     uint64_t n_area_cdf;  const float      *area_cdf;
     nb_camera camera;
+    uint32_t n_media;     const nb_medium  *media;       /* may be 0 / NULL */
+    int32_t  ambient_medium;                             /* Scene::getAmbientMedium, -1 = vacuum */
+    uint64_t n_density;   const float      *density;     /* voxel data of heterogeneous media or NULL */
 } nb_scene_desc;
 
 /* nb_build_bvh(mode = NB_BVH_IMPORT): the caller's own arrays (BVH::m_nodes / m_indices after

@@ -21,7 +21,9 @@ SHAPE_MESH, SHAPE_SPHERE = 0, 1
 BSDF_DIFFUSE, BSDF_MIRROR, BSDF_DIELECTRIC, BSDF_MICROFACET = 0, 1, 2, 3
 EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP = 0, 1, 2
 INTEGRATORS = {"path_mis": 0, "path_mats": 1, "direct_ems": 2, "direct_mats": 3, "direct_mis": 4,
-               "normals": 5, "direct": 6, "av": 7}
+               "normals": 5, "direct": 6, "av": 7, "path_vol_mats": 8, "path_vol_mis": 9}
+MEDIUM_VACUUM, MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1, 2
+PHASE_ISOTROPIC, PHASE_HENYEY_GREENSTEIN, PHASE_SCHLICK = 0, 1, 2
 FILTER_RESOLUTION = 32
 
 # numpy mirrors of the records (field order and padding as in the header)
@@ -35,6 +37,9 @@ emitter_dtype = np.dtype([("type", "<u4"), ("shape", "<i4"), ("radiance", "<f4",
 camera_dtype = np.dtype([("sample_to_camera", "<f4", 16), ("camera_to_world", "<f4", 16),
                          ("inv_output_size", "<f4", 2), ("near_clip", "<f4"), ("far_clip", "<f4"),
                          ("lens_radius", "<f4"), ("focal_distance", "<f4"), ("width", "<u4"), ("height", "<u4")])
+medium_dtype = np.dtype([("type", "<u4"), ("mu_t", "<f4", 3), ("phase", "<u4"), ("phase_param", "<f4"),
+                         ("density_scale", "<f4"), ("max_density", "<f4"), ("grid_dims", "<u4", 3),
+                         ("first_voxel", "<u4"), ("world_to_grid", "<f4", 12)])
 bvh_node_dtype = np.dtype([("word0", "<u4"), ("word1", "<u4"), ("bmin", "<f4", 3), ("bmax", "<f4", 3)])
 ray_dtype = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("mint", "<f4"), ("maxt", "<f4")])
 hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("shape", "<i4"), ("prim", "<i4"), ("any_hit", "<u4")])
@@ -42,7 +47,7 @@ render_params_dtype = np.dtype([("integrator", "<u4"), ("filter_radius", "<f4"),
                                 ("filter_table", "<f4", FILTER_RESOLUTION + 1), ("pad0", "<u4"), ("seed", "<u8"),
                                 ("pool_paths", "<u4"), ("max_depth", "<u4"), ("reserved", "<u4", 4)])
 SECTION_DTYPES = {"shapes": shape_dtype, "bsdfs": bsdf_dtype, "emitters": emitter_dtype, "camera": camera_dtype,
-                  "bvh_nodes": bvh_node_dtype, "render": render_params_dtype}
+                  "bvh_nodes": bvh_node_dtype, "render": render_params_dtype, "media": medium_dtype}
 
 
 class Camera(C.Structure):
@@ -59,7 +64,9 @@ class SceneDesc(C.Structure):
                 ("n_bsdfs", C.c_uint32), ("bsdfs", C.c_void_p),
                 ("n_emitters", C.c_uint32), ("emitters", C.c_void_p), ("emitter_cdf", C.c_void_p),
                 ("n_area_cdf", C.c_uint64), ("area_cdf", C.c_void_p),
-                ("camera", Camera)]
+                ("camera", Camera),
+                ("n_media", C.c_uint32), ("media", C.c_void_p), ("ambient_medium", C.c_int32),
+                ("n_density", C.c_uint64), ("density", C.c_void_p)]
 
 
 class BvhImport(C.Structure):
@@ -143,6 +150,8 @@ def read_nbs(path):
             out[name] = np.frombuffer(buf, dtype=dt).copy()
         elif name in ("faces", "bvh_indices", "spp"):
             out[name] = np.frombuffer(buf, dtype="<u4").copy()
+        elif name == "ambient":
+            out[name] = np.frombuffer(buf, dtype="<i4").copy()
         else:
             out[name] = np.frombuffer(buf, dtype="<f4").copy()
     return out
@@ -210,6 +219,9 @@ class Context:
         ac = keep.get("area_cdf"); d.n_area_cdf = 0 if ac is None else ac.size; d.area_cdf = _ptr(ac)
         if "camera" in keep:
             C.memmove(C.byref(d.camera), keep["camera"].ctypes.data, C.sizeof(Camera))
+        md = keep.get("media"); d.n_media = 0 if md is None else len(md); d.media = _ptr(md)
+        d.ambient_medium = int(keep["ambient"][0]) if "ambient" in keep else -1
+        dn = keep.get("density"); d.n_density = 0 if dn is None else dn.size; d.density = _ptr(dn)
         self._check(self.lib.nb_upload_scene(self.handle, C.byref(d)))
 
     def build_bvh(self, nodes, indices):

@@ -51,6 +51,7 @@ int nb_abi_sizeof(int which) {
         case 7: return (int) sizeof(nb_hit);
         case 8: return (int) sizeof(nb_render_params);
         case 9: return (int) sizeof(nb_counters);
+        case 10: return (int) sizeof(nb_medium);
         default: return -1;
     }
 }
@@ -110,8 +111,8 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
         } else if (sh.type == NB_SHAPE_SPHERE) {
             if (sh.prim_count != 1) return nb_fail(ctx, NB_E_INVALID, "shape %u: a sphere has exactly one primitive", i);
         } else return nb_fail(ctx, NB_E_UNSUPPORTED, "shape %u: unknown shape tag %u", i, sh.type);
-        if (sh.bsdf >= (int32_t) s->n_bsdfs || sh.emitter >= (int32_t) s->n_emitters)
-            return nb_fail(ctx, NB_E_INVALID, "shape %u: bsdf/emitter index out of range", i);
+        if (sh.bsdf >= (int32_t) s->n_bsdfs || sh.emitter >= (int32_t) s->n_emitters || sh.medium >= (int32_t) s->n_media)
+            return nb_fail(ctx, NB_E_INVALID, "shape %u: bsdf/emitter/medium index out of range", i);
         prims += sh.prim_count;
     }
     if (prims >= NB_SLOT_LAST) return nb_fail(ctx, NB_E_UNSUPPORTED, "too many primitives (%llu)", (unsigned long long) prims);
@@ -127,6 +128,20 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
         } else return nb_fail(ctx, NB_E_UNSUPPORTED, "emitter %u: tag %u has no kernel in this backend", i, e.type);
     }
     if (s->n_emitters && !s->emitter_cdf) return nb_fail(ctx, NB_E_INVALID, "emitter_cdf missing");
+    if (s->n_media && !s->media) return nb_fail(ctx, NB_E_INVALID, "media missing");
+    if (s->ambient_medium >= (int32_t) s->n_media) return nb_fail(ctx, NB_E_INVALID, "ambient medium index out of range");
+    for (uint32_t i = 0; i < s->n_media; ++i) {
+        const nb_medium &m = s->media[i];
+        if (m.type > NB_MEDIUM_HETEROGENEOUS || m.phase > NB_PHASE_SCHLICK)
+            return nb_fail(ctx, NB_E_UNSUPPORTED, "medium %u: medium tag %u / phase tag %u has no kernel in this backend", i, m.type, m.phase);
+        if (m.type == NB_MEDIUM_HETEROGENEOUS)
+            return nb_fail(ctx, NB_E_UNSUPPORTED, "medium %u: heterogeneous media have no kernel in this backend yet", i);
+        if (m.type == NB_MEDIUM_HETEROGENEOUS) {
+            const uint64_t vox = (uint64_t) m.grid_dims[0] * m.grid_dims[1] * m.grid_dims[2];
+            if (vox == 0 || !s->density || (uint64_t) m.first_voxel + vox > s->n_density)
+                return nb_fail(ctx, NB_E_INVALID, "medium %u: density grid outside the density array", i);
+        }
+    }
 
     nb_free_list(ctx->scene_allocs);
     nb_free_list(ctx->bvh_allocs);
@@ -152,6 +167,9 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->emitters, s->n_emitters, &d.emitters))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->emitter_cdf, s->n_emitters ? s->n_emitters + 1 : 0, &d.emitter_cdf))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->area_cdf, s->n_area_cdf, &d.area_cdf))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->media, s->n_media, &d.media))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->density, s->n_density, &d.density))) return rc;
+    d.n_media = s->n_media; d.ambient_medium = s->ambient_medium;
     d.n_shapes = s->n_shapes; d.n_bsdfs = s->n_bsdfs; d.n_emitters = s->n_emitters;
     d.envmap_emitter = envmap;
     d.camera = s->camera;

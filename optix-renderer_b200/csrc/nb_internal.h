@@ -38,8 +38,10 @@ struct NbDeviceScene {
     const nb_bsdf *bsdfs = nullptr;
     const nb_emitter *emitters = nullptr;
     const float *emitter_cdf = nullptr, *area_cdf = nullptr;
-    uint32_t n_shapes = 0, n_bsdfs = 0, n_emitters = 0;
-    int32_t envmap_emitter = -1;
+    const nb_medium *media = nullptr;
+    const float *density = nullptr;     /* voxels of heterogeneous media */
+    uint32_t n_shapes = 0, n_bsdfs = 0, n_emitters = 0, n_media = 0;
+    int32_t envmap_emitter = -1, ambient_medium = -1;
     nb_camera camera;
 };
 

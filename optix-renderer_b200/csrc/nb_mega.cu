@@ -19,6 +19,7 @@
 #include "nb_shading.cuh"
 #include "nb_film.cuh"
 #include "nb_trace.cuh"
+#include "nb_volume.cuh"
 
 #ifndef NB_TILE_THREADS
 #define NB_TILE_THREADS 128
@@ -220,12 +221,122 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
     return result + w_ems * result_ems + w_mat * result_mats;
 }
 
+/* PathVolMISIntegrator::sampleEmitter + traceShadowray (path_vol_mis.cpp:26-104). `its`/`sh` are
+ * the SURFACE hit of the current ray even when the interaction is inside the medium (the
+ * reference passes `its` in both cases); exactly one of bsdf / phase is non-null. */
+template <bool FLAT>
+__device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbPathRegs &ps, int32_t medium, const NbIts &its,
+                                                    const nb_shape &sh, uint32_t measure, const nb_bsdf *bsdf,
+                                                    const nb_medium *phase, uint32_t &n_closest) {
+    if (measure != NB_MEASURE_SOLID_ANGLE) return mk3(0.f);              /* skip delta bsdfs */
+    const float n_lights = (float) sc.n_emitters;
+    const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
+    float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+    NbEmitterSample es;
+    const f3 Le = nb_emitter_sample(sc, sc.emitters[ei], its.p, s, es) * n_lights;
+    const float pdf_em = es.pdf / n_lights;
+    if (is_black(Le)) return mk3(0.f);                                   /* result would be 0; the shadow walk draws nothing */
+    int32_t sm = dot(ps.d, es.ray_d) > 0.f ? nb_medium_behind(sc, sh, its.geo_n, es.ray_d) : medium;
+    /* traceShadowray: closest hits along the ray until a surface with a BSDF blocks it */
+    f3 tr = mk3(1.f), so = es.ray_o;
+    float smaxt = es.ray_maxt;
+    for (int seg = 0; seg < 64; ++seg) {
+        NbHit h;
+        ++n_closest;
+        if (!nb_closest<FLAT>(sc, so, es.ray_d, es.ray_mint, smaxt, h)) break;
+        nb_shape sh2; NbIts its2;
+        nb_hit_info(sc, h, so, es.ray_d, sh2, its2);
+        if (sh2.bsdf >= 0) return mk3(0.f);
+        tr = tr * nb_transmittance(sc, sm, so, its2.p);
+        sm = nb_medium_behind(sc, sh2, its2.geo_n, es.ray_d);
+        so = its2.p;
+        smaxt -= h.t;
+    }
+    float pdf_em_mat;
+    f3 f = mk3(1.f);                                                     /* |wi . shadowRay.d| = 1 for a phase function */
+    if (phase) pdf_em_mat = nb_phase_pdf(*phase, its.sh.to_local(es.ray_d));
+    else {
+        const f3 wi = its.sh.to_local(-ps.d), we = its.sh.to_local(es.wi);
+        pdf_em_mat = nb_bsdf_pdf(*bsdf, wi, we);
+        f = nb_bsdf_eval(*bsdf, wi, we) * fabsf(dot(es.wi, its.sh.n));
+    }
+    const float w_em = pdf_em > NB_EPS ? pdf_em / (pdf_em + pdf_em_mat) : 0.f;
+    if (w_em > NB_EPS) return tr * w_em * ps.thr * Le * f;
+    return mk3(0.f);
+}
+
+/* One loop iteration of path_vol_mats.cpp:32-119 / path_vol_mis.cpp:124-229 after the closest
+ * hit of the current ray arrived. Returns false when the path ended. */
+template <bool MIS, bool FLAT>
+__device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t max_depth, NbPathRegs &ps, int32_t &medium,
+                                              const NbHit &hit, uint32_t &n_closest) {
+    nb_shape sh; NbIts its;
+    nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
+    const float tm = nb_free_path(sc, medium, ps.rng);
+    const bool mi = tm < hit.t;                                          /* isMediumInteraction */
+    const f3 p = mi ? ps.o + ps.d * tm : its.p;
+    ps.thr = ps.thr * nb_transmittance(sc, medium, ps.o, p);
+    uint32_t measure = (ps.flags >> NB_MEASURE_SHIFT) & 3u;
+    /* captured emission; volume emitters have no kernel (the host loader refuses them) */
+    if (!mi && sh.emitter >= 0) {
+        const f3 Le = nb_area_eval(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
+        float w = 1.f;
+        if (MIS && measure != NB_MEASURE_DISCRETE) {
+            const float pdf_mat_em = nb_area_pdf(sh, ps.o, its.p, its.sh.n, normalize(its.p - ps.o)) / (float) sc.n_emitters;
+            w = ps.pdfmat > NB_EPS ? ps.pdfmat / (ps.pdfmat + pdf_mat_em) : 0.f;
+        }
+        ps.Li += w * ps.thr * Le;
+    }
+    const uint32_t bounce = ps.flags >> NB_BOUNCE_SHIFT;
+    if (bounce >= 3 && (mi || sh.bsdf >= 0)) {                           /* Russian roulette */
+        const float succ = fminf(max3(ps.thr), 0.99f);
+        if (ps.rng.next_float() > succ || succ < NB_EPS) return false;
+        ps.thr = ps.thr / succ;
+    }
+    if (max_depth && bounce >= max_depth) return false;
+    f3 wo = ps.d;                                                        /* default: unperturbed */
+    if (mi) {
+        const nb_medium med = sc.media[medium];
+        float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+        const f3 pwo = nb_phase_sample(med, s);
+        wo = frame_from_normal(ps.d).to_world(pwo);
+        if (MIS) {
+            ps.pdfmat = nb_phase_pdf(med, pwo);
+            measure = NB_MEASURE_SOLID_ANGLE;
+            ps.Li += nb_vol_sample_emitter<FLAT>(sc, ps, medium, its, sh, measure, nullptr, &med, n_closest);
+        }
+    } else {
+        if (sh.bsdf >= 0) {
+            const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+            const f3 wi = its.sh.to_local(-ps.d);
+            float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+            f3 lwo; bool discrete; float pdf;
+            const f3 col = nb_bsdf_sample(bsdf, wi, s, lwo, discrete, pdf);
+            wo = its.sh.to_world(lwo);
+            if (MIS) {
+                /* bRec.measure after sample(): diffuse sets ESolidAngle and mirror EDiscrete only when
+                 * wi is on the upper side, dielectric always EDiscrete, microfacet never sets it */
+                measure = discrete ? NB_MEASURE_DISCRETE
+                        : (bsdf.type == NB_BSDF_DIFFUSE && wi.z > 0.f) ? NB_MEASURE_SOLID_ANGLE : NB_MEASURE_UNKNOWN;
+                ps.pdfmat = pdf;
+                ps.Li += nb_vol_sample_emitter<FLAT>(sc, ps, medium, its, sh, measure, &bsdf, nullptr, n_closest);
+            }
+            ps.thr = ps.thr * col;
+        }
+        if (dot(ps.d, wo) > 0.f) medium = nb_medium_behind(sc, sh, its.geo_n, wo);   /* transmitted: entering or leaving */
+    }
+    ps.o = p; ps.d = wo; ps.mint = NB_EPS; ps.maxt = INFINITY;
+    ps.flags = ((bounce + 1) << NB_BOUNCE_SHIFT) | (measure << NB_MEASURE_SHIFT);
+    return !is_black(ps.thr);
+}
+
 /* ---- K_tile ---------------------------------------------------------------------------------- */
 template <int INTEG, bool FLAT>
 __global__ void __launch_bounds__(NB_TILE_THREADS, NB_TILE_MIN_BLOCKS)
 nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     constexpr bool PATH = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_MATS;
-    constexpr bool MIS = INTEG == NB_INTEGRATOR_PATH_MIS;
+    constexpr bool VOL = INTEG == NB_INTEGRATOR_PATH_VOL_MIS || INTEG == NB_INTEGRATOR_PATH_VOL_MATS;
+    constexpr bool MIS = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_VOL_MIS;
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t n_closest = 0, n_any = 0, n_samples = 0;
     /* the warp's current work item (warp-uniform) */
@@ -234,6 +345,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     bool active = false;
     NbPathRegs ps;
     ps.flags = 0;
+    int32_t medium = sc.ambient_medium;     /* volume integrators: the medium the path is in */
     for (;;) {
         /* --- regenerate: idle lanes take the next camera samples of the warp's item --- */
         uint32_t need = __ballot_sync(0xffffffffu, !active);
@@ -266,6 +378,10 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
                 ps.Li = mk3(0.f); ps.thr = mk3(1.f); ps.w_mats = 1.f; ps.w_ems = 0.f; ps.pdfmat = 0.f;
                 ps.flags = NB_FLAG_PRIMARY;
+                if (VOL) {                   /* path_vol_mis.cpp:118-121: the camera acts like a delta bsdf */
+                    ps.pdfmat = 1.f; ps.flags = NB_MEASURE_DISCRETE << NB_MEASURE_SHIFT;
+                    medium = sc.ambient_medium;
+                }
                 active = true;
                 ++n_samples;
             }
@@ -295,6 +411,17 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
             if (active && ended) {
                 nb_film_put(film, ps.px, ps.py, ps.Li, stats);
                 active = false;
+            }
+        } else if (VOL) {
+            if (active) {
+                NbHit hit;
+                ++n_closest;
+                bool alive = nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit);
+                if (alive) alive = nb_vol_bounce<MIS, FLAT>(sc, tp.plan.max_depth, ps, medium, hit, n_closest);
+                if (!alive) {
+                    nb_film_put(film, ps.px, ps.py, ps.Li, stats);
+                    active = false;
+                }
             }
         } else if (active) {
             const f3 Li = nb_direct_sample<INTEG, FLAT>(sc, ps, n_closest, n_any);
@@ -364,6 +491,8 @@ cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const Nb
         case NB_INTEGRATOR_DIRECT_EMS: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT_EMS>(sc, film, tp, item_counter, stats, sm_count, stream);
         case NB_INTEGRATOR_DIRECT_MATS: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT_MATS>(sc, film, tp, item_counter, stats, sm_count, stream);
         case NB_INTEGRATOR_DIRECT_MIS: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_PATH_VOL_MATS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_VOL_MATS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_PATH_VOL_MIS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_VOL_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);
         default: return cudaErrorInvalidValue;
     }
 }

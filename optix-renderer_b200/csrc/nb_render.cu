@@ -299,10 +299,12 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     if (!ctx->bvh_ready) return nb_fail(ctx, NB_E_STATE, "nb_render_begin: scene/BVH not ready");
     switch (params->integrator) {
         case NB_INTEGRATOR_PATH_MIS: case NB_INTEGRATOR_PATH_MATS: case NB_INTEGRATOR_DIRECT:
-        case NB_INTEGRATOR_DIRECT_EMS: case NB_INTEGRATOR_DIRECT_MATS: case NB_INTEGRATOR_DIRECT_MIS: break;
+        case NB_INTEGRATOR_DIRECT_EMS: case NB_INTEGRATOR_DIRECT_MATS: case NB_INTEGRATOR_DIRECT_MIS:
+        case NB_INTEGRATOR_PATH_VOL_MATS: case NB_INTEGRATOR_PATH_VOL_MIS: break;
         default: return nb_fail(ctx, NB_E_UNSUPPORTED, "integrator tag %u has no kernel in this backend", params->integrator);
     }
-    if ((params->integrator == NB_INTEGRATOR_PATH_MIS || params->integrator == NB_INTEGRATOR_DIRECT_MIS) && ctx->dev.n_emitters == 0)
+    if ((params->integrator == NB_INTEGRATOR_PATH_MIS || params->integrator == NB_INTEGRATOR_DIRECT_MIS ||
+         params->integrator == NB_INTEGRATOR_PATH_VOL_MIS) && ctx->dev.n_emitters == 0)
         return nb_fail(ctx, NB_E_INVALID, "No Emitter in scene!");                 /* path_mis.cpp:76-79 */
     if (!(params->filter_radius > 0.f)) return nb_fail(ctx, NB_E_INVALID, "filter radius must be positive");
     const nb_camera &cam = ctx->dev.camera;

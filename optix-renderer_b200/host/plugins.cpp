@@ -231,8 +231,8 @@ NB_INTEGRATOR_CLASS(DirectMISIntegrator, "direct_mis", NB_INTEGRATOR_DIRECT_MIS)
 NB_INTEGRATOR_CLASS(DirectIntegrator, "direct", NB_INTEGRATOR_DIRECT)
 NB_INTEGRATOR_CLASS(NormalIntegrator, "normals", NB_INTEGRATOR_NORMALS)
 NB_INTEGRATOR_CLASS(AverageVisibility, "av", NB_INTEGRATOR_AV)
-NB_INTEGRATOR_CLASS(PathVolMATSIntegrator, "path_vol_mats", -1)
-NB_INTEGRATOR_CLASS(PathVolMISIntegrator, "path_vol_mis", -1)
+NB_INTEGRATOR_CLASS(PathVolMATSIntegrator, "path_vol_mats", NB_INTEGRATOR_PATH_VOL_MATS)
+NB_INTEGRATOR_CLASS(PathVolMISIntegrator, "path_vol_mis", NB_INTEGRATOR_PATH_VOL_MIS)
 NB_INTEGRATOR_CLASS(PhotonMapper, "photonmapper", -1)
 NB_INTEGRATOR_CLASS(PreviewIntegrator, "preview", -1)
 
@@ -256,7 +256,116 @@ class OptixAlias : public B200Renderer { public: explicit OptixAlias(const Prope
 NORI_REGISTER_CLASS(OptixAlias, "optix")
 
 /* ---- Shape base (src/shapes/shape.cpp) --------------------------------------------------------------- */
-Shape::~Shape() { delete m_bsdf; delete m_emitter; }
+/* ---- phase functions (src/bsdf/isophase.cpp, anisophase.cpp, schlickphase.cpp) ---------------------------- */
+class IsoPhase : public PhaseFunction {
+public:
+    explicit IsoPhase(const PropertyList &) {}
+    void getB200PhaseData(nb_medium &out) const override { out.phase = NB_PHASE_ISOTROPIC; out.phase_param = 0.f; }
+    std::string toString() const override { return "IsoPhase[]"; }
+};
+NORI_REGISTER_CLASS(IsoPhase, "isophase")
+
+class AnisoPhase : public PhaseFunction {           /* anisophase.cpp:26-29: g default 0 */
+public:
+    explicit AnisoPhase(const PropertyList &p) : m_g(p.getFloat("g", 0.f)) {}
+    void getB200PhaseData(nb_medium &out) const override { out.phase = NB_PHASE_HENYEY_GREENSTEIN; out.phase_param = m_g; }
+    std::string toString() const override { return NoriException::format("AnisoPhase[g=%f]", m_g); }
+private:
+    float m_g;
+};
+NORI_REGISTER_CLASS(AnisoPhase, "anisophase")
+
+class SchlickPhase : public PhaseFunction {         /* schlickphase.cpp:26-30: k = 1.55 g - 0.55 g^3 */
+public:
+    explicit SchlickPhase(const PropertyList &p) : m_g(p.getFloat("g", 0.f)) { m_k = 1.55f * m_g - 0.55f * std::pow(m_g, 3); }
+    void getB200PhaseData(nb_medium &out) const override { out.phase = NB_PHASE_SCHLICK; out.phase_param = m_k; }
+    std::string toString() const override { return NoriException::format("SchlickPhase[g=%f]", m_g); }
+private:
+    float m_g, m_k;
+};
+NORI_REGISTER_CLASS(SchlickPhase, "schlickphase")
+
+/* ---- media (src/media/medium.cpp, homogmedium.cpp, vacuum.cpp, heterogmedium.cpp) --------------------------- */
+Medium::Medium(const PropertyList &p) {             /* medium.cpp:10-17 + updateDerivedProperties :112-117 */
+    m_sigma_a = p.getColor("sigma_a", Color3f(0.5f)) * p.getFloat("sigma_a_intensity", 1.f);
+    m_sigma_s = p.getColor("sigma_s", Color3f(0.f)) * p.getFloat("sigma_s_intensity", 1.f);
+}
+Medium::~Medium() { delete m_phase; delete m_emitter; }
+void Medium::addChild(NoriObject *obj) {
+    switch (obj->getClassType()) {
+        case EPhaseFunction:
+            if (m_phase) throw NoriException("Medium: tried to register multiple PhaseFunction instances!");
+            m_phase = static_cast<PhaseFunction *>(obj);
+            break;
+        case EEmitter:
+            if (m_emitter) throw NoriException("Medium: tried to register multiple Emitter instances!");
+            m_emitter = static_cast<Emitter *>(obj);
+            break;
+        default:
+            throw NoriException("Medium::addChild(<%s>) is not supported!", classTypeName(obj->getClassType()));
+    }
+}
+void Medium::activate() {
+    if (!m_phase) m_phase = static_cast<PhaseFunction *>(NoriObjectFactory::createInstance("isophase"));
+}
+
+class VacuumMedium : public Medium {
+public:
+    explicit VacuumMedium(const PropertyList &p) : Medium(p) {}
+    bool getB200MediumData(nb_medium &out) const override {
+        memset(&out, 0, sizeof(out));
+        out.type = NB_MEDIUM_VACUUM;
+        return m_emitter == nullptr;
+    }
+    std::string toString() const override { return "VacuumMedium[]"; }
+};
+NORI_REGISTER_CLASS(VacuumMedium, "vacuum")
+
+class HomogeneousMedium : public Medium {           /* homogmedium.cpp:16-19, 48-60 */
+public:
+    explicit HomogeneousMedium(const PropertyList &p) : Medium(p), m_density(p.getFloat("density", 1.f)) {}
+    bool getB200MediumData(nb_medium &out) const override {
+        memset(&out, 0, sizeof(out));
+        out.type = NB_MEDIUM_HOMOGENEOUS;
+        for (int i = 0; i < 3; ++i) out.mu_t[i] = m_density * m_sigma_a[i] + m_density * m_sigma_s[i];   /* mu_a + mu_s */
+        m_phase->getB200PhaseData(out);
+        return m_emitter == nullptr;                    /* volume emitters (volumelight.cpp) have no kernel */
+    }
+    std::string toString() const override { return "HomogeneousMedium[]"; }
+private:
+    float m_density;
+};
+NORI_REGISTER_CLASS(HomogeneousMedium, "homog")
+
+/* <volume type="volume"> (src/textures/NvdbVolume.cpp): an OpenVDB file converted to NanoVDB at load
+ * time by OpenVDB, which this image does not have — the object parses, the medium reports no kernel */
+class NvdbVolumeStub : public NoriObject {
+public:
+    explicit NvdbVolumeStub(const PropertyList &p) : m_filename(p.getString("filename", "")) {}
+    EClassType getClassType() const override { return EVolume; }
+    std::string toString() const override { return "NvdbVolume[" + m_filename + "]"; }
+private:
+    std::string m_filename;
+};
+NORI_REGISTER_CLASS(NvdbVolumeStub, "volume")
+
+class HeterogeneousMedium : public Medium {         /* needs a NanoVDB grid converted from .vdb by OpenVDB: not available here */
+public:
+    explicit HeterogeneousMedium(const PropertyList &p) : Medium(p) {}
+    ~HeterogeneousMedium() override { delete m_volume; }
+    void addChild(NoriObject *obj) override {
+        if (obj->getClassType() != EVolume) { Medium::addChild(obj); return; }
+        if (m_volume) throw NoriException("There is already an volume defined!");
+        m_volume = obj;
+    }
+    bool getB200MediumData(nb_medium &) const override { return false; }
+    std::string toString() const override { return "HeterogeneousMedium[]"; }
+private:
+    NoriObject *m_volume = nullptr;
+};
+NORI_REGISTER_CLASS(HeterogeneousMedium, "heterog")
+
+Shape::~Shape() { delete m_bsdf; delete m_emitter; delete m_medium; }
 
 void Shape::addChild(NoriObject *obj) {
     switch (obj->getClassType()) {
@@ -269,13 +378,18 @@ void Shape::addChild(NoriObject *obj) {
             m_emitter = static_cast<Emitter *>(obj);
             m_emitter->setShape(this);
             break;
+        case EMedium:
+            if (m_medium) throw NoriException("Shape: tried to register multiple medium instances!");
+            m_medium = static_cast<Medium *>(obj);
+            break;
         default:
             throw NoriException("Shape::addChild(<%s>) is not supported!", classTypeName(obj->getClassType()));
     }
 }
 
 void Shape::activate() {
-    if (!m_bsdf) m_bsdf = static_cast<BSDF *>(NoriObjectFactory::createInstance("diffuse"));   /* shape.cpp:33-35 */
+    /* "If no material or medium was assigned, instantiate a diffuse BRDF" (shape.cpp:33-35) */
+    if (!m_bsdf && !m_medium) m_bsdf = static_cast<BSDF *>(NoriObjectFactory::createInstance("diffuse"));
 }
 
 /* ---- Sphere (src/shapes/sphere.cpp:30-38) ---------------------------------------------------------------- */

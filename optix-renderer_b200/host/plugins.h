@@ -34,6 +34,29 @@ protected:
     Color3f m_radiance;
 };
 
+/* include/nori/phase.h:28-41 */
+class PhaseFunction : public NoriObject {
+public:
+    EClassType getClassType() const override { return EPhaseFunction; }
+    virtual void getB200PhaseData(nb_medium &out) const = 0;          /* fills phase, phase_param */
+};
+
+/* include/nori/medium.h + src/media/medium.cpp */
+class Medium : public NoriObject {
+public:
+    explicit Medium(const PropertyList &p);
+    ~Medium() override;
+    EClassType getClassType() const override { return EMedium; }
+    void addChild(NoriObject *obj) override;            /* medium.cpp:50-72: one phase, one emitter */
+    void activate() override;                           /* isotropic phase by default (medium.cpp:22-24) */
+    /* replaces getOptixMediumData (medium.h:68); false = no GPU kernel for this medium */
+    virtual bool getB200MediumData(nb_medium &out) const = 0;
+protected:
+    Color3f m_sigma_a, m_sigma_s;                       /* normalized colour * intensity */
+    PhaseFunction *m_phase = nullptr;
+    Emitter *m_emitter = nullptr;                       /* volume emitter: no kernel */
+};
+
 /* include/nori/shape.h:104-237 */
 class Shape : public NoriObject {
 public:
@@ -46,6 +69,7 @@ public:
     virtual Point3f getCentroid(uint32_t index) const = 0;
     const BoundingBox3f &getBoundingBox() const { return m_bbox; }
     const BSDF *getBSDF() const { return m_bsdf; }
+    const Medium *getMedium() const { return m_medium; }
     Emitter *getEmitter() const { return m_emitter; }
     bool isEmitter() const { return m_emitter != nullptr; }
     /* replaces getOptixBuildInput / getOptixHitgroupRecords (shape.h:194-201): appends this
@@ -54,6 +78,7 @@ public:
 protected:
     BSDF *m_bsdf = nullptr;
     Emitter *m_emitter = nullptr;
+    Medium *m_medium = nullptr;
     BoundingBox3f m_bbox;
 };
 
@@ -121,6 +146,8 @@ struct FlatScene {
     std::vector<uint32_t> faces;
     std::vector<nb_bsdf> bsdfs;
     std::vector<nb_emitter> emitters;
+    std::vector<nb_medium> media;
+    int32_t ambient_medium = -1;
     nb_camera camera;
     nb_render_params render;
     uint32_t spp = 1;
@@ -155,6 +182,7 @@ private:
     Camera *m_camera = nullptr;
     Integrator *m_integrator = nullptr;
     Sampler *m_sampler = nullptr;
+    Medium *m_ambientMedium = nullptr;                  /* scene.cpp:248-252; vacuum when absent */
     std::vector<NoriObject *> m_other;
 };
 

@@ -13,7 +13,7 @@ Scene::Scene(const PropertyList &) {}
 Scene::~Scene() {
     for (Emitter *e : m_emitters) if (!e->hasShape()) delete e;   /* shape-owned emitters die with their shape */
     for (Shape *s : m_shapes) delete s;
-    delete m_camera; delete m_integrator; delete m_sampler;
+    delete m_camera; delete m_integrator; delete m_sampler; delete m_ambientMedium;
     for (NoriObject *o : m_other) delete o;
 }
 
@@ -36,6 +36,10 @@ void Scene::addChild(NoriObject *obj) {
         case EIntegrator:
             if (m_integrator) throw NoriException("There can only be one integrator per scene!");
             m_integrator = static_cast<Integrator *>(obj);
+            break;
+        case EMedium:
+            if (m_ambientMedium) throw NoriException("There can only be one ambient medium per scene.");
+            m_ambientMedium = static_cast<Medium *>(obj);
             break;
         case ERenderer: case EDenoiser: case EPixelSampler: m_other.push_back(obj); break;
         default:
@@ -79,6 +83,12 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
             rec.bsdf = (int32_t) out.bsdfs.size();
             out.bsdfs.push_back(b);
         }
+        if (s->getMedium()) {
+            nb_medium m;
+            if (!s->getMedium()->getB200MediumData(m)) return fail("medium '" + s->getMedium()->toString() + "' has no GPU kernel");
+            rec.medium = (int32_t) out.media.size();
+            out.media.push_back(m);
+        }
         for (size_t e = 0; e < m_emitters.size(); ++e)
             if (m_emitters[e] == s->getEmitter()) { rec.emitter = (int32_t) e; out.emitters[e].shape = (int32_t) i; }
         out.shapes.push_back(rec);
@@ -94,6 +104,11 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
         for (Emitter *e : m_emitters) out.emitter_cdf.push_back(out.emitter_cdf.back() + e->lightProb);
         const float sum = out.emitter_cdf.back();
         if (sum > 0) { const float n = 1.0f / sum; for (size_t i = 1; i < out.emitter_cdf.size(); ++i) out.emitter_cdf[i] *= n; out.emitter_cdf.back() = 1.0f; }
+    }
+    if (m_ambientMedium) {
+        nb_medium m;
+        if (!m_ambientMedium->getB200MediumData(m)) return fail("ambient medium '" + m_ambientMedium->toString() + "' has no GPU kernel");
+        if (m.type != NB_MEDIUM_VACUUM) { out.ambient_medium = (int32_t) out.media.size(); out.media.push_back(m); }
     }
     m_camera->getB200Data(out.camera);
     memset(&out.render, 0, sizeof(out.render));
@@ -123,6 +138,8 @@ nb_scene_desc FlatScene::desc() const {
     d.emitter_cdf = emitter_cdf.empty() ? nullptr : emitter_cdf.data();
     d.n_area_cdf = area_cdf.size(); d.area_cdf = area_cdf.data();
     d.camera = camera;
+    d.n_media = (uint32_t) media.size(); d.media = media.empty() ? nullptr : media.data();
+    d.ambient_medium = ambient_medium;
     return d;
 }
 
@@ -138,6 +155,10 @@ void FlatScene::writeNbs(const std::string &path) const {
     secs.push_back({ "emitters", sizeof(nb_emitter), emitters.data(), emitters.size() });
     secs.push_back({ "emitter_cdf", 4, emitter_cdf.data(), emitter_cdf.size() });
     secs.push_back({ "area_cdf", 4, area_cdf.data(), area_cdf.size() });
+    if (!media.empty() || ambient_medium >= 0) {
+        secs.push_back({ "media", sizeof(nb_medium), media.data(), media.size() });
+        secs.push_back({ "ambient", 4, &ambient_medium, 1 });
+    }
     secs.push_back({ "camera", sizeof(nb_camera), &camera, 1 });
     secs.push_back({ "render", sizeof(nb_render_params), &render, 1 });
     secs.push_back({ "spp", 4, &spp, 1 });

@@ -21,6 +21,21 @@ def test_flatten_matches_reference_bit_for_bit(nb, built_lib, name, xml):
         assert got[k].tobytes() == want[k].tobytes(), k
 
 
+def test_media_records(nb, built_lib):
+    """Medium / phase plugins -> nb_medium (homogmedium.cpp:48-60: mu_t = density * (sigma_a + sigma_s);
+    schlickphase.cpp:28: k = 1.55 g - 0.55 g^3), shapes without a BSDF keep bsdf = -1 (shape.cpp:33-35)."""
+    s = nb.load_xml(golden("scenes/vol/cbox_homog_ambient.xml"))
+    assert s["render"]["integrator"][0] == nb.INTEGRATORS["path_vol_mats"]
+    assert len(s["media"]) == 2 and s["ambient"][0] == 1
+    np.testing.assert_allclose(s["media"]["mu_t"], [[0.5] * 3, [0.05] * 3])
+    assert np.all(s["media"]["type"] == nb.MEDIUM_HOMOGENEOUS) and np.all(s["media"]["phase"] == nb.PHASE_ISOTROPIC)
+    sphere = s["shapes"][0]
+    assert sphere["type"] == nb.SHAPE_SPHERE and sphere["bsdf"] == -1 and sphere["medium"] == 0
+    a = nb.load_xml(golden("scenes/vol/cbox_homog_aniso.xml"))
+    assert a["media"]["phase"][0] == nb.PHASE_HENYEY_GREENSTEIN and a["media"]["phase_param"][0] == np.float32(-0.75)
+    assert a["ambient"][0] == -1
+
+
 def test_bvh_structure(nb, built_lib):
     s = nb.load_xml(golden("scenes/table/table_path_mis.xml"))
     n = s["bvh_nodes"]

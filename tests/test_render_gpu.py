@@ -52,10 +52,17 @@ def test_image_matches_reference(nb, ctx, name, integrator, spp, ref):
     ("veach/veach_mats_small.xml", "veach_mats_ref_64spp.npy", 64),    # direct_mats
     ("odyssey/odyssey_ems_small.xml", "odyssey_ref_64spp.npy", 64),
     ("odyssey/odyssey_mis_small.xml", "odyssey_mis_ref_64spp.npy", 64),
+    # participating media (scenes/project/volume): path_vol_mats / path_vol_mis, homogeneous medium
+    # in a BSDF-less sphere, isotropic and Henyey-Greenstein phase, ambient medium, mirror sphere
+    ("vol/cbox_val_mats_small.xml", "vol_val_mats_ref_128spp.npy", 128),
+    ("vol/cbox_val_mis_small.xml", "vol_val_mis_ref_128spp.npy", 128),
+    ("vol/cbox_homog_aniso_small.xml", "vol_homog_aniso_ref_128spp.npy", 128),
+    ("vol/cbox_homog_ambient_small.xml", "vol_homog_ambient_ref_128spp.npy", 128),
+    ("vol/cbox_homog_small.xml", "vol_homog_ref_128spp.npy", 128),
 ])
-def test_direct_integrators_match_reference(nb, ctx, xml, ref, spp):
-    """Depth-1 integrators on the reference's pa3 scenes, loaded from the reference's XML by the
-    C++ host loader, against reference CPU renders at equal spp."""
+def test_xml_scenes_match_reference(nb, ctx, xml, ref, spp):
+    """Depth-1 and volume integrators on the reference's own scenes, loaded from the reference's
+    XML by the C++ host loader, against reference CPU renders at equal spp."""
     s = nb.load_xml(golden("scenes/" + xml))
     want = np.load(golden(ref))
     imgs = []
