@@ -106,13 +106,25 @@ __device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, co
     const float3 r = make_float3(__fdiv_rn(1.0f, d.x), __fdiv_rn(1.0f, d.y), __fdiv_rn(1.0f, d.z));   /* Ray3f::update, ray.h */
     bool found = false;
     uint32_t idx = 0;
-    while (idx != NB_NODE_END) {
-        const float4 A = __ldg(nodes + 2 * idx), B = __ldg(nodes + 2 * idx + 1);
-        const uint32_t skip = __float_as_uint(A.x), start = __float_as_uint(A.y);
-        if (!nb_box_hit(A, B, o, d, r, mint, maxt)) { idx = skip; continue; }
-        if (start == NB_NODE_INNER) { idx = idx + 1; continue; }
-        if (start == NB_NODE_EMPTY_LEAF) { idx = skip; continue; }
-        uint32_t s = start;
+    /* "while-while": every lane first walks inner nodes until it stands on a leaf (cheap, uniform
+     * box tests), then the lanes that found one intersect their leaves together. With the leaf
+     * loop nested inside the node step instead, a warp executed the ~100-instruction primitive
+     * test for 2 of 32 lanes at a time (ncu, table scene). Per ray the sequence of visits is
+     * unchanged. */
+    while (true) {
+        uint32_t leaf = NB_NODE_INNER, after = NB_NODE_END;
+        while (idx != NB_NODE_END) {
+            const float4 A = __ldg(nodes + 2 * idx), B = __ldg(nodes + 2 * idx + 1);
+            const uint32_t skip = __float_as_uint(A.x), start = __float_as_uint(A.y);
+            if (!nb_box_hit(A, B, o, d, r, mint, maxt)) { idx = skip; continue; }
+            if (start == NB_NODE_INNER) { idx = idx + 1; continue; }
+            idx = skip;
+            if (start == NB_NODE_EMPTY_LEAF) continue;
+            leaf = start; after = skip;
+            break;
+        }
+        if (leaf == NB_NODE_INNER) break;
+        uint32_t s = leaf;
         while (true) {
             const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
             const uint32_t tag = __float_as_uint(s2.y);
@@ -128,7 +140,7 @@ __device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, co
             if (tag & NB_SLOT_LAST) break;
             ++s;
         }
-        idx = skip;
+        idx = after;
     }
     return found;
 }
