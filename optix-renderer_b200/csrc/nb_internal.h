@@ -63,6 +63,7 @@ struct nb_ctx {
     NbRenderState *render = nullptr;
     int sm_count = 148;
     int opt_profile = 0, opt_sort = 0, opt_strategy = 0;
+    int opt_walk = 1;                   /* tree scenes: K_tile_walk (per-lane state machine) instead of lock-step K_tile */
     int opt_flat = -1;                  /* -1: flat scan iff the scene has at most NB_FLAT_MAX_SLOTS primitives */
 };
 
@@ -86,4 +87,4 @@ struct NbFilm;
 struct NbPlan;
 cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const NbPlan &plan, uint32_t height, uint32_t passes,
                            uint32_t integrator, uint32_t *item_counter, unsigned long long *stats, int sm_count,
-                           cudaStream_t stream);
+                           cudaStream_t stream, bool walk);

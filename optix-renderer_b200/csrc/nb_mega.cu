@@ -330,6 +330,53 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
     return !is_black(ps.thr);
 }
 
+/* ---- work items ------------------------------------------------------------------------------
+ * A warp's position in the image: the current item (16x8-pixel tile x a chunk of sample passes)
+ * and how much of it is handed out. All members are warp-uniform. */
+struct NbItemCursor {
+    uint32_t x0 = 0, y0 = 0, tw = 1, tpx = 0, pass0 = 0, n = 0, next = 0;
+    bool exhausted = false;
+};
+
+/* Called by all 32 lanes together. Lanes with `want` get the next camera samples of the warp's
+ * item (a new item is claimed from the global counter when the current one is used up); returns
+ * false for a lane that wanted one but the image is finished. */
+__device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan &tp, uint32_t *item_counter, bool want,
+                                               uint32_t lane, uint32_t lt_mask, uint32_t &pix, uint32_t &sidx) {
+    bool got = false;
+    uint32_t need = __ballot_sync(0xffffffffu, want);
+    while (need) {
+        if (c.next == c.n) {
+            if (c.exhausted) break;
+            uint32_t item = 0;
+            if (lane == 0) item = atomicAdd(item_counter, 1u);
+            item = __shfl_sync(0xffffffffu, item, 0);
+            if (item >= tp.n_items) { c.exhausted = true; break; }
+            /* chunk-major order: concurrently running warps work on different tiles */
+            const uint32_t tile = item % tp.n_tiles, chunk = item / tp.n_tiles;
+            c.x0 = (tile % tp.tiles_x) * tp.tile_w; c.y0 = (tile / tp.tiles_x) * tp.tile_h;
+            c.tw = min(tp.tile_w, tp.plan.width - c.x0);
+            c.tpx = c.tw * min(tp.tile_h, tp.height - c.y0);
+            c.pass0 = chunk * tp.chunk;
+            c.n = c.tpx * min(tp.chunk, tp.passes - c.pass0);
+            c.next = 0;
+        }
+        const uint32_t take = min((uint32_t) __popc(need), c.n - c.next);
+        const uint32_t rank = __popc(need & lt_mask);
+        if (want && !got && rank < take) {
+            const uint32_t k = c.next + rank;
+            const uint32_t pl = k / c.tpx, q = k - pl * c.tpx;
+            const uint32_t y = q / c.tw, x = q - y * c.tw;
+            pix = (c.y0 + y) * tp.plan.width + c.x0 + x;
+            sidx = tp.plan.first + (c.pass0 + pl) * tp.plan.stride;
+            got = true;
+        }
+        c.next += take;
+        need = __ballot_sync(0xffffffffu, want && !got);
+    }
+    return got;
+}
+
 /* ---- K_tile ---------------------------------------------------------------------------------- */
 template <int INTEG, bool FLAT>
 __global__ void __launch_bounds__(NB_TILE_THREADS, NB_TILE_MIN_BLOCKS)
@@ -339,54 +386,26 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     constexpr bool MIS = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_VOL_MIS;
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t n_closest = 0, n_any = 0, n_samples = 0;
-    /* the warp's current work item (warp-uniform) */
-    uint32_t it_x0 = 0, it_y0 = 0, it_tw = 1, it_tpx = 0, it_pass0 = 0, it_n = 0, it_next = 0;
-    bool exhausted = false;
+    NbItemCursor cur;
     bool active = false;
     NbPathRegs ps;
     ps.flags = 0;
     int32_t medium = sc.ambient_medium;     /* volume integrators: the medium the path is in */
     for (;;) {
         /* --- regenerate: idle lanes take the next camera samples of the warp's item --- */
-        uint32_t need = __ballot_sync(0xffffffffu, !active);
-        while (need) {
-            if (it_next == it_n) {
-                if (exhausted) break;
-                uint32_t item = 0;
-                if (lane == 0) item = atomicAdd(item_counter, 1u);
-                item = __shfl_sync(0xffffffffu, item, 0);
-                if (item >= tp.n_items) { exhausted = true; break; }
-                /* chunk-major order: concurrently running warps work on different tiles */
-                const uint32_t tile = item % tp.n_tiles, chunk = item / tp.n_tiles;
-                it_x0 = (tile % tp.tiles_x) * tp.tile_w; it_y0 = (tile / tp.tiles_x) * tp.tile_h;
-                it_tw = min(tp.tile_w, tp.plan.width - it_x0);
-                it_tpx = it_tw * min(tp.tile_h, tp.height - it_y0);
-                it_pass0 = chunk * tp.chunk;
-                it_n = it_tpx * min(tp.chunk, tp.passes - it_pass0);
-                it_next = 0;
+        uint32_t pix, sidx;
+        if (nb_take_sample(cur, tp, item_counter, !active, lane, lt_mask, pix, sidx)) {
+            NbCameraRay r;
+            nb_camera_sample(sc.camera, tp.plan, pix, sidx, ps.rng, r);
+            ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
+            ps.Li = mk3(0.f); ps.thr = mk3(1.f); ps.w_mats = 1.f; ps.w_ems = 0.f; ps.pdfmat = 0.f;
+            ps.flags = NB_FLAG_PRIMARY;
+            if (VOL) {                       /* path_vol_mis.cpp:118-121: the camera acts like a delta bsdf */
+                ps.pdfmat = 1.f; ps.flags = NB_MEASURE_DISCRETE << NB_MEASURE_SHIFT;
+                medium = sc.ambient_medium;
             }
-            const uint32_t take = min((uint32_t) __popc(need), it_n - it_next);
-            const uint32_t rank = __popc(need & lt_mask);
-            if (!active && rank < take) {
-                const uint32_t k = it_next + rank;
-                const uint32_t pl = k / it_tpx, q = k - pl * it_tpx;
-                const uint32_t y = q / it_tw, x = q - y * it_tw;
-                const uint32_t pix = (it_y0 + y) * tp.plan.width + it_x0 + x;
-                const uint32_t sidx = tp.plan.first + (it_pass0 + pl) * tp.plan.stride;
-                NbCameraRay r;
-                nb_camera_sample(sc.camera, tp.plan, pix, sidx, ps.rng, r);
-                ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
-                ps.Li = mk3(0.f); ps.thr = mk3(1.f); ps.w_mats = 1.f; ps.w_ems = 0.f; ps.pdfmat = 0.f;
-                ps.flags = NB_FLAG_PRIMARY;
-                if (VOL) {                   /* path_vol_mis.cpp:118-121: the camera acts like a delta bsdf */
-                    ps.pdfmat = 1.f; ps.flags = NB_MEASURE_DISCRETE << NB_MEASURE_SHIFT;
-                    medium = sc.ambient_medium;
-                }
-                active = true;
-                ++n_samples;
-            }
-            it_next += take;
-            need = __ballot_sync(0xffffffffu, !active);
+            active = true;
+            ++n_samples;
         }
         if (!__any_sync(0xffffffffu, active)) break;
 
@@ -441,6 +460,186 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     }
 }
 
+/* ---- K_tile_walk: the same integrators for scenes with a real tree ----------------------------
+ * With a tree, rays of one warp need wildly different numbers of node visits (C3, 1.31 M
+ * triangles: mean 38, tail in the hundreds). K_tile's lock-step loop then runs the traversal
+ * with 5 of 32 lanes active (ncu), every bounce waiting for the warp's slowest ray. Here each
+ * lane is its own little state machine
+ *     REGEN -> NODE <-> LEAF -> TDONE -> (NODE ... shadow ray, then main ray) -> SHADE -> ...
+ * and the warp loop offers each phase's code in turn: node steps every iteration (cheap, most
+ * lanes want them), the expensive phases (leaf intersection, shading, splat + regeneration) only
+ * once enough lanes wait for them or nothing else can run. A lane with a long ray keeps walking
+ * while its neighbours shade, start new paths and walk their own rays. Per ray the visiting order
+ * and arithmetic are nb_traverse's; per path the draws are nb_path_bounce's. */
+#ifndef NB_WALK_MIN_BLOCKS
+#define NB_WALK_MIN_BLOCKS 4
+#endif
+#ifndef NB_WALK_NODE_STEPS
+#define NB_WALK_NODE_STEPS 8      /* node steps per loop iteration */
+#endif
+#ifndef NB_WALK_T_LEAF
+#define NB_WALK_T_LEAF 6          /* lanes that must wait before a phase is run (unless nothing else can) */
+#endif
+#ifndef NB_WALK_T_SHADE
+#define NB_WALK_T_SHADE 8
+#endif
+#ifndef NB_WALK_T_REGEN
+#define NB_WALK_T_REGEN 8
+#endif
+enum { NB_PH_IDLE = 0, NB_PH_REGEN = 1, NB_PH_NODE = 2, NB_PH_LEAF = 3, NB_PH_TDONE = 4, NB_PH_SHADE = 5 };
+
+template <bool MIS>
+__global__ void __launch_bounds__(NB_TILE_THREADS, NB_WALK_MIN_BLOCKS)
+nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
+    const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+    uint32_t n_closest = 0, n_any = 0, n_samples = 0;
+    NbItemCursor cur;
+    uint32_t phase = NB_PH_REGEN;
+    bool splat = false;               /* REGEN: a finished sample waits to be put on the film */
+    bool shadow = false;              /* a shadow ray is pending / being traced before the main ray */
+    bool ending = false;              /* the path ended at the last vertex; splat after its shadow ray */
+    NbPathRegs ps;
+    ps.flags = 0;
+    NbShadowRay so;
+    /* the ray being walked */
+    float3 to = make_float3(0.f, 0.f, 0.f), td = to, tr = to;
+    float tmint = 0.f, tmaxt = 0.f;
+    uint32_t idx = NB_NODE_END, leaf = 0, after = NB_NODE_END;
+    NbHit hit;
+    hit.t = INFINITY; hit.u = hit.v = 0.f; hit.slot = 0xffffffffu;
+    bool t_any = false, occluded = false;
+
+    /* prologue of nb_traverse for the lane's next ray */
+    auto begin_walk = [&](f3 o, f3 d, float mint, float maxt, bool any_hit) {
+        to = o; td = d; t_any = any_hit; occluded = false;
+        hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
+        if (mint == NB_EPSILON) {
+            float m = fabsf(o.x);
+            m = fmaxf(m, fabsf(o.y));
+            m = fmaxf(m, fabsf(o.z));
+            const float e = __fmul_rn(mint, m);
+            mint = (mint < e) ? e : mint;
+        }
+        tmint = mint; tmaxt = maxt;
+        tr = make_float3(__fdiv_rn(1.0f, d.x), __fdiv_rn(1.0f, d.y), __fdiv_rn(1.0f, d.z));
+        idx = (sc.n_nodes == 0 || maxt < mint) ? NB_NODE_END : 0u;
+        phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
+        if (any_hit) ++n_any; else ++n_closest;
+    };
+
+    for (;;) {
+        const uint32_t m_walking = __ballot_sync(0xffffffffu, phase == NB_PH_NODE || phase == NB_PH_LEAF || phase == NB_PH_TDONE);
+        /* ---- REGEN: splat the finished sample, start the next camera path ---- */
+        const uint32_t m_regen = __ballot_sync(0xffffffffu, phase == NB_PH_REGEN);
+        if (m_regen && (__popc(m_regen) >= NB_WALK_T_REGEN || !m_walking)) {
+            if (phase == NB_PH_REGEN && splat) { nb_film_put(film, ps.px, ps.py, ps.Li, stats); splat = false; }
+            uint32_t pix, sidx;
+            const bool got = nb_take_sample(cur, tp, item_counter, phase == NB_PH_REGEN, lane, lt_mask, pix, sidx);
+            if (got) {
+                NbCameraRay r;
+                nb_camera_sample(sc.camera, tp.plan, pix, sidx, ps.rng, r);
+                ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
+                ps.Li = mk3(0.f); ps.thr = mk3(1.f); ps.w_mats = 1.f; ps.w_ems = 0.f; ps.pdfmat = 0.f;
+                ps.flags = NB_FLAG_PRIMARY;
+                shadow = false; ending = false;
+                ++n_samples;
+                begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
+            } else if (phase == NB_PH_REGEN) phase = NB_PH_IDLE;      /* image finished */
+        }
+        if (!__ballot_sync(0xffffffffu, phase != NB_PH_IDLE)) break;
+
+        /* ---- NODE: inner-node steps until the lane stands on a leaf or its walk ends ---- */
+#pragma unroll 1
+        for (int step = 0; step < NB_WALK_NODE_STEPS; ++step) {
+            if (phase == NB_PH_NODE) {
+                const float4 A = __ldg(sc.nodes + 2 * idx), B = __ldg(sc.nodes + 2 * idx + 1);
+                const uint32_t skip = __float_as_uint(A.x), start = __float_as_uint(A.y);
+                if (!nb_box_hit(A, B, to, td, tr, tmint, tmaxt)) idx = skip;
+                else if (start == NB_NODE_INNER) idx = idx + 1;
+                else {
+                    idx = skip;
+                    if (start != NB_NODE_EMPTY_LEAF) { leaf = start; after = skip; phase = NB_PH_LEAF; }
+                }
+                if (phase == NB_PH_NODE && idx == NB_NODE_END) phase = NB_PH_TDONE;
+            }
+        }
+        /* ---- LEAF: lanes standing on a leaf intersect it together ---- */
+        const uint32_t m_leaf = __ballot_sync(0xffffffffu, phase == NB_PH_LEAF);
+        if (m_leaf && (__popc(m_leaf) >= NB_WALK_T_LEAF || !__ballot_sync(0xffffffffu, phase == NB_PH_NODE))) {
+            if (phase == NB_PH_LEAF) {
+                uint32_t s = leaf;
+                while (true) {
+                    const float4 s0 = __ldg(sc.slots + 3 * s), s1 = __ldg(sc.slots + 3 * s + 1), s2 = __ldg(sc.slots + 3 * s + 2);
+                    const uint32_t tag = __float_as_uint(s2.y);
+                    float u = 0.f, v = 0.f, t;
+                    const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, to, td, tmint, tmaxt, t)
+                                                           : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t);
+                    if (ok) {
+                        if (t_any) { occluded = true; break; }
+                        tmaxt = t;
+                        hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                    }
+                    if (tag & NB_SLOT_LAST) break;
+                    ++s;
+                }
+                idx = occluded ? NB_NODE_END : after;
+                phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
+            }
+        }
+        /* ---- TDONE: a walk ended. Shadow ray: add its contribution, go on to the main ray
+         * (or end the path); main ray: queue for shading ---- */
+        if (phase == NB_PH_TDONE) {
+            if (t_any) {
+                if (!occluded) {                           /* path_mis.cpp:102-105,141 */
+                    if (so.cand >= 0.f) ps.w_ems = so.cand;
+                    ps.Li += ps.w_ems * so.c;
+                }
+                shadow = false;
+                if (ending) { splat = true; phase = NB_PH_REGEN; }
+                else begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
+            } else phase = NB_PH_SHADE;
+        }
+        /* ---- SHADE: one bounce of the integrator for lanes whose closest hit arrived ---- */
+        const uint32_t m_shade = __ballot_sync(0xffffffffu, phase == NB_PH_SHADE);
+        if (m_shade && (__popc(m_shade) >= NB_WALK_T_SHADE || !__ballot_sync(0xffffffffu, phase == NB_PH_NODE || phase == NB_PH_LEAF))) {
+            if (phase == NB_PH_SHADE) {
+                bool alive = false;
+                shadow = false;
+                if (hit.slot != 0xffffffffu) alive = nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
+                ending = !alive;
+                if (MIS && shadow) begin_walk(so.o, so.d, so.mint, so.maxt, true);
+                else if (alive) begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
+                else { splat = true; phase = NB_PH_REGEN; }
+            }
+        }
+    }
+    for (int off = 16; off; off >>= 1) {
+        n_closest += __shfl_xor_sync(0xffffffffu, n_closest, off);
+        n_any += __shfl_xor_sync(0xffffffffu, n_any, off);
+        n_samples += __shfl_xor_sync(0xffffffffu, n_samples, off);
+    }
+    if (lane == 0) {
+        if (n_closest) atomicAdd(&stats[NB_STAT_RAYS_CLOSEST], (unsigned long long) n_closest);
+        if (n_any) atomicAdd(&stats[NB_STAT_RAYS_ANY], (unsigned long long) n_any);
+        if (n_samples) atomicAdd(&stats[NB_STAT_SAMPLES], (unsigned long long) n_samples);
+    }
+}
+
+template <bool MIS>
+static cudaError_t nb_tile_launch_walk(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
+                                       unsigned long long *stats, int sm_count, cudaStream_t stream) {
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile_walk<MIS>, NB_TILE_THREADS, 0);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) per_sm = 1;
+    uint64_t blocks = (uint64_t) sm_count * per_sm;
+    const uint64_t blocks_useful = ((uint64_t) tp.n_items + NB_TILE_THREADS / 32 - 1) / (NB_TILE_THREADS / 32);
+    if (blocks > blocks_useful) blocks = blocks_useful;
+    if (blocks < 1) blocks = 1;
+    nb_k_tile_walk<MIS><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
+    return cudaGetLastError();
+}
+
 template <int INTEG, bool FLAT>
 static cudaError_t nb_tile_launch_flat(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
                                     unsigned long long *stats, int sm_count, cudaStream_t stream) {
@@ -468,7 +667,7 @@ static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film,
  * sample index plan.first + k * plan.stride. Asynchronous on `stream`. */
 cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const NbPlan &plan, uint32_t height, uint32_t passes,
                            uint32_t integrator, uint32_t *item_counter, unsigned long long *stats, int sm_count,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, bool walk) {
     NbTilePlan tp;
     tp.plan = plan;
     tp.height = height; tp.passes = passes;
@@ -484,6 +683,10 @@ cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const Nb
     tp.n_items = (uint32_t) items;
     cudaError_t e = cudaMemsetAsync(item_counter, 0, sizeof(uint32_t), stream);
     if (e != cudaSuccess) return e;
+    if (!sc.flat && walk) {
+        if (integrator == NB_INTEGRATOR_PATH_MIS) return nb_tile_launch_walk<true>(sc, film, tp, item_counter, stats, sm_count, stream);
+        if (integrator == NB_INTEGRATOR_PATH_MATS) return nb_tile_launch_walk<false>(sc, film, tp, item_counter, stats, sm_count, stream);
+    }
     switch (integrator) {
         case NB_INTEGRATOR_PATH_MIS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);
         case NB_INTEGRATOR_PATH_MATS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_MATS>(sc, film, tp, item_counter, stats, sm_count, stream);

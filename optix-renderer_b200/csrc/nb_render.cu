@@ -405,7 +405,7 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     if (!is_path || nb_use_tile_strategy(ctx)) {
         /* K_tile: one persistent launch, path state in registers (nb_mega.cu) */
         cudaError_t e = nb_launch_tile(ctx->dev, r->film, plan, cam.height, passes, integ, r->tile_counter, r->stats,
-                                       ctx->sm_count, ctx->stream);
+                                       ctx->sm_count, ctx->stream, ctx->opt_walk != 0);
         if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: K_tile launch: %s", cudaGetErrorString(e));
         cudaEventRecord(r->ev_end, ctx->stream);
         cudaMemcpyAsync(r->h_stats, r->stats, NB_STAT_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream);
@@ -553,6 +553,7 @@ int nb_set_option(nb_ctx *ctx, const char *name, int64_t value) {
     if (!ctx || !name) return NB_E_INVALID;
     if (!strcmp(name, "profile")) ctx->opt_profile = (int) value;
     else if (!strcmp(name, "sort")) ctx->opt_sort = (int) value;
+    else if (!strcmp(name, "walk")) ctx->opt_walk = (int) value;
     else if (!strcmp(name, "flat_scan")) {
         ctx->opt_flat = (int) value;
         ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;

@@ -45,6 +45,7 @@ def ctx(_session_ctx):
     _session_ctx.set_option("strategy", 0)
     _session_ctx.set_option("profile", 0)
     _session_ctx.set_option("flat_scan", -1)
+    _session_ctx.set_option("walk", 1)
     return _session_ctx
 
 

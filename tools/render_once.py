@@ -17,6 +17,9 @@ if "size" in opt:
 ctx = nb.Context(0)
 ctx.set_option("strategy", {"auto": 0, "wavefront": 1, "tile": 2}[opt.get("strategy", "tile")])
 ctx.load(scene)
+for k in ("walk", "flat_scan"):
+    if k in opt:
+        ctx.set_option(k, int(opt[k]))
 ctx.render_begin(nb.make_render_params(scene, opt.get("integrator"), seed=1))
 for _ in range(int(opt.get("repeat", 1))):
     ctx.film_clear()
