@@ -265,7 +265,8 @@ def main():
                 "config": {"workload": WORKLOAD, "spp_per_gpu": args.spp, "integrator": "path_mis",
                            "strategy": "tile" if single_launch else "wavefront",
                            "parallelism": "sample slices x%d, scene replicated, 1 NCCL film reduce" % world,
-                           "l2": "256 MB flush write between timed steps; path pool (1M slots x 164 B) exceeds L2"},
+                           "l2": "256 MB flush write between timed steps" + ("; K_tile keeps path state in registers, film 7.8 MB" if single_launch
+                                                                                  else "; path pool (1M slots x 164 B) exceeds L2")},
                 "rays_per_s": rays_all / (ms * 1e-3), "rays_per_sample": rays_all / samples_all,
                 "e2e": {"value": float(se.item()) / float(te.item()), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": int(host_film.nbytes)},
