@@ -143,7 +143,8 @@ typedef struct nb_scene_desc {
 
 /* nb_build_bvh(mode = NB_BVH_IMPORT): the caller's own arrays (BVH::m_nodes / m_indices after
  * Scene::update, scene.cpp:187-194). Same tree, same visiting order => bit-identical hits. */
-enum { NB_BVH_IMPORT = 0 };
+enum { NB_BVH_IMPORT = 0,   /* the caller's tree (the reference's, or libnorib200_host's restatement of it) */
+       NB_BVH_DEVICE = 1 }; /* K_bvh_build: linear BVH built on the GPU from the uploaded scene; `imp` is ignored */
 typedef struct nb_bvh_import {
     uint32_t n_nodes;    const nb_bvh_node *nodes;
     uint32_t n_indices;  const uint32_t    *indices;    /* global primitive ids, leaf order */
@@ -196,6 +197,9 @@ const char *nb_last_error(const nb_ctx *ctx);   /* ctx may be NULL: error of the
 /* OptixState::preRender (OptixState.render.cpp:19-85): flatten + upload. */
 int  nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *scene);
 int  nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *import);
+/* node / primitive-slot counts of the current tree and the device time of the last NB_BVH_DEVICE
+ * build (0 for an imported tree); any pointer may be NULL */
+int  nb_bvh_stats(nb_ctx *ctx, uint32_t *n_nodes, uint32_t *n_slots, double *build_ms);
 
 /* Parity entry: Scene::rayIntersect (include/nori/scene.h:114-138) over n host rays.
  * any_hit = 0: closest hit per ray. any_hit = 1: also runs the shadow-ray query and fills

@@ -83,7 +83,7 @@ class Counters(C.Structure):
 EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
-           "nb_get_counters", "nb_set_option", "nb_sample_slice"]
+           "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats"]
 
 _lib = None
 
@@ -122,6 +122,7 @@ def load_library(path=None):
     lib.nb_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
     lib.nb_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     lib.nb_sample_slice.argtypes = [C.c_uint32] * 4 + [C.POINTER(C.c_uint32)] * 2
+    lib.nb_bvh_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
     if path in (LIB_PATH, os.environ.get("NORIB200_LIB")):
         _lib = lib
     return lib
@@ -229,9 +230,21 @@ class Context:
         imp = BvhImport(len(nodes), _ptr(nodes), len(indices), _ptr(indices))
         self._check(self.lib.nb_build_bvh(self.handle, 0, C.byref(imp)))
 
-    def load(self, s):
+    def build_bvh_device(self):
+        """K_bvh_build: linear BVH built on the GPU from the uploaded scene (no host tree needed)."""
+        self._check(self.lib.nb_build_bvh(self.handle, 1, None))
+
+    def bvh_stats(self):
+        n, m, ms = C.c_uint32(), C.c_uint32(), C.c_double()
+        self._check(self.lib.nb_bvh_stats(self.handle, C.byref(n), C.byref(m), C.byref(ms)))
+        return {"nodes": n.value, "slots": m.value, "build_ms": ms.value}
+
+    def load(self, s, device_bvh=False):
         self.upload_scene(s)
-        self.build_bvh(s["bvh_nodes"], s["bvh_indices"])
+        if device_bvh:
+            self.build_bvh_device()
+        else:
+            self.build_bvh(s["bvh_nodes"], s["bvh_indices"])
 
     def trace_rays(self, rays, any_hit=False):
         """rays: (n, 8) float32 [o, d, mint, maxt] or ray_dtype; returns hit_dtype array."""

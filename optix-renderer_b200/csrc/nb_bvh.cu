@@ -11,6 +11,10 @@ extern "C" {
 int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     if (!ctx) return NB_E_INVALID;
     if (!ctx->scene_ready) return nb_fail(ctx, NB_E_STATE, "nb_build_bvh: upload a scene first");
+    if (mode == NB_BVH_DEVICE) {
+        NB_CUDA(ctx, cudaSetDevice(ctx->device));
+        return nb_build_bvh_device(ctx);
+    }
     if (mode != NB_BVH_IMPORT) return nb_fail(ctx, NB_E_UNSUPPORTED, "nb_build_bvh: mode %d not available", mode);
     if (!imp || !imp->nodes || !imp->indices || imp->n_nodes == 0)
         return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: empty import");
@@ -113,6 +117,7 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
         memcpy(&ctx->h_slot_tag[k], &slots[(size_t) k * 3 + 2].y, 4);
         memcpy(&ctx->h_slot_prim[k], &slots[(size_t) k * 3 + 2].z, 4);
     }
+    ctx->bvh_build_ms = 0.0;
     ctx->bvh_ready = true;
     return NB_OK;
 }
@@ -184,6 +189,14 @@ int nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int a
     cudaFree(d_any);
     if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_trace_rays_device: %s", cudaGetErrorString(e));
     if (ms_per_launch) *ms_per_launch = ms / repeats;
+    return NB_OK;
+}
+
+int nb_bvh_stats(nb_ctx *ctx, uint32_t *n_nodes, uint32_t *n_slots, double *build_ms) {
+    if (!ctx || !ctx->bvh_ready) return nb_fail(ctx, NB_E_STATE, "nb_bvh_stats: no BVH");
+    if (n_nodes) *n_nodes = ctx->dev.n_nodes;
+    if (n_slots) *n_slots = ctx->dev.n_slots;
+    if (build_ms) *build_ms = ctx->bvh_build_ms;
     return NB_OK;
 }
 

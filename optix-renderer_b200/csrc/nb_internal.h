@@ -62,6 +62,7 @@ struct nb_ctx {
     std::vector<void *> scene_allocs, bvh_allocs;
     NbRenderState *render = nullptr;
     int sm_count = 148;
+    double bvh_build_ms = 0.0;          /* device time of the last NB_BVH_DEVICE build */
     int opt_profile = 0, opt_sort = 0, opt_strategy = 0;
     int opt_walk = 1;                   /* tree scenes: K_tile_walk (per-lane state machine) instead of lock-step K_tile */
     int opt_flat = -1;                  /* -1: flat scan iff the scene has at most NB_FLAT_MAX_SLOTS primitives */
@@ -81,6 +82,9 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
 
 /* nb_render.cu */
 int nb_render_free(nb_ctx *ctx);
+
+/* nb_bvh_build.cu */
+int nb_build_bvh_device(nb_ctx *ctx);
 
 /* nb_mega.cu */
 struct NbFilm;
