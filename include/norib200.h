@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 2
+#define NB_ABI_VERSION 3
 
 enum {
     NB_OK = 0,
@@ -108,9 +108,14 @@ typedef struct nb_bvh_node {
 
 /* One Medium with its phase function (replaces Medium::getOptixMediumData, medium.h:68).
  * Homogeneous (src/media/homogmedium.cpp:48-73): mu_t = density * (sigma_a + sigma_s) per channel.
- * Heterogeneous (src/media/heterogmedium.cpp): density on a dense grid (first_voxel/dims into the
- * scene's density array, index space mapped by world_to_grid), majorant max_density, scaled by
- * density_scale; see DESIGN.md for what is and is not pinned there. */
+ * Heterogeneous (src/media/heterogmedium.cpp:67-174): the density grid the reference samples through
+ * NanoVDB, as a dense array: grid_dims voxels (x slowest, z fastest) at first_voxel of
+ * nb_scene_desc.density, holding the box of active voxels (NanoGrid::indexBBox) plus a border of
+ * NB_GRID_BORDER background voxels on every side. world_to_grid maps a world point to array
+ * coordinates (voxel (i,j,k) of the array has its value at (i,j,k), as NanoVDB's index space), so
+ * the medium's bounding box is [NB_GRID_BORDER, grid_dims - NB_GRID_BORDER] per axis.
+ * max_density = the unscaled grid maximum (tree().root().valueMax(), heterogmedium.cpp:79). */
+#define NB_GRID_BORDER 2
 typedef struct nb_medium {
     uint32_t type;           /* NB_MEDIUM_* */
     float    mu_t[3];        /* homogeneous: extinction; heterogeneous: sigma_t = sigma_a + sigma_s */
@@ -209,6 +214,14 @@ int  nb_trace_rays(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_hit, nb_
  * n float4 {t,u,v,bits(prim slot)}; returns the kernel's CUDA-event time. */
 int  nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int any_hit,
                           void *out_device, int repeats, float *ms_per_launch);
+/* Parity entry for the medium rows: Medium::sampleFreePath (src/media/homogmedium.cpp:60-66,
+ * heterogmedium.cpp:105-130), Medium::getTransmittance (homogmedium.cpp:68-72, heterogmedium.cpp:132-174)
+ * and NvdbVolume::getDensity (src/textures/NvdbVolume.cpp:39-48) of media[medium] on n host rays.
+ * out gets 4 floats per ray: density at ray.o (0 for a medium without a grid); the fraction of
+ * `samples` free paths from ray.o along ray.d shorter than ray.maxt; their mean length; the mean
+ * transmittance (first channel) from ray.o to ray.o + ray.maxt * ray.d. */
+int  nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples,
+                     uint64_t seed, float *out);
 
 /* RenderThread::renderThreadOptix loop (render.cpp:462-574). */
 int  nb_render_begin(nb_ctx *ctx, const nb_render_params *params);  /* allocates + clears film */

@@ -83,7 +83,7 @@ class Counters(C.Structure):
 EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
-           "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats"]
+           "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe"]
 
 _lib = None
 
@@ -123,6 +123,7 @@ def load_library(path=None):
     lib.nb_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     lib.nb_sample_slice.argtypes = [C.c_uint32] * 4 + [C.POINTER(C.c_uint32)] * 2
     lib.nb_bvh_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
+    lib.nb_medium_probe.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_void_p]
     if path in (LIB_PATH, os.environ.get("NORIB200_LIB")):
         _lib = lib
     return lib
@@ -246,6 +247,13 @@ class Context:
         else:
             self.build_bvh(s["bvh_nodes"], s["bvh_indices"])
 
+    def medium_probe(self, medium, rays, samples=1024, seed=1):
+        """rays: (n, 8) float32 [o, d, mint, maxt]; returns (n, 4) [density(o), P(free path < maxt), mean path, mean Tr]."""
+        rays = np.ascontiguousarray(rays, dtype="<f4").reshape(-1, 8)
+        out = np.zeros((len(rays), 4), dtype="<f4")
+        self._check(self.lib.nb_medium_probe(self.handle, medium, _ptr(rays), len(rays), samples, seed, _ptr(out)))
+        return out
+
     def trace_rays(self, rays, any_hit=False):
         """rays: (n, 8) float32 [o, d, mint, maxt] or ray_dtype; returns hit_dtype array."""
         rays = np.ascontiguousarray(rays)
@@ -359,7 +367,37 @@ def load_host_library():
         _host.nbh_last_error.restype = C.c_char_p
         _host.nbh_flatten_xml.argtypes = [C.c_char_p, C.c_char_p]
         _host.nbh_parse_xml.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+        _host.nbh_vdb_list.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+        _host.nbh_vdb_read.restype = C.c_longlong
+        _host.nbh_vdb_read.argtypes = [C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
+        _host.nbh_vdb_to_nbv.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
+        _host.nbh_inflate.restype = C.c_longlong
+        _host.nbh_inflate.argtypes = [C.c_char_p, C.c_uint64, C.c_void_p, C.c_uint64]
     return _host
+
+
+def vdb_list(path):
+    """[(grid name, tree type)] of an OpenVDB file (host/vdb.cpp)."""
+    h = load_host_library()
+    buf = C.create_string_buffer(1 << 16)
+    if h.nbh_vdb_list(os.fsencode(path), buf, len(buf)) != 0:
+        raise NbError(-1, h.nbh_last_error().decode())
+    return [tuple(l.split(":")) for l in buf.value.decode().splitlines()]
+
+
+def vdb_read(path, grid="density"):
+    """One float grid of an OpenVDB file as a dense array over its active box (host/vdb.cpp):
+    dict(values (nx,ny,nz) f32, bbox_min, bbox_max, index_to_world (3,4), background, min, max, active_voxels)."""
+    h = load_host_library()
+    bbox = np.zeros(6, "<i4"); xf = np.zeros(12, "<f8"); st = np.zeros(3, "<f4"); act = C.c_uint64()
+    n = h.nbh_vdb_read(os.fsencode(path), grid.encode(), _ptr(bbox), _ptr(xf), _ptr(st), C.byref(act), None, 0)
+    if n < 0:
+        raise NbError(-1, h.nbh_last_error().decode())
+    v = np.zeros(n, "<f4")
+    h.nbh_vdb_read(os.fsencode(path), grid.encode(), _ptr(bbox), _ptr(xf), _ptr(st), C.byref(act), _ptr(v), n)
+    dims = bbox[3:] - bbox[:3] + 1
+    return {"values": v.reshape(dims) if n else v, "bbox_min": bbox[:3].copy(), "bbox_max": bbox[3:].copy(), "index_to_world": xf.reshape(3, 4),
+            "background": float(st[0]), "min": float(st[1]), "max": float(st[2]), "active_voxels": act.value}
 
 
 def load_xml(xml_path, nbs_path=None):

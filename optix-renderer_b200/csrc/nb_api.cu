@@ -134,12 +134,15 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
         const nb_medium &m = s->media[i];
         if (m.type > NB_MEDIUM_HETEROGENEOUS || m.phase > NB_PHASE_SCHLICK)
             return nb_fail(ctx, NB_E_UNSUPPORTED, "medium %u: medium tag %u / phase tag %u has no kernel in this backend", i, m.type, m.phase);
-        if (m.type == NB_MEDIUM_HETEROGENEOUS)
-            return nb_fail(ctx, NB_E_UNSUPPORTED, "medium %u: heterogeneous media have no kernel in this backend yet", i);
         if (m.type == NB_MEDIUM_HETEROGENEOUS) {
             const uint64_t vox = (uint64_t) m.grid_dims[0] * m.grid_dims[1] * m.grid_dims[2];
             if (vox == 0 || !s->density || (uint64_t) m.first_voxel + vox > s->n_density)
                 return nb_fail(ctx, NB_E_INVALID, "medium %u: density grid outside the density array", i);
+            for (int a = 0; a < 3; ++a)
+                if (m.grid_dims[a] < 2 * NB_GRID_BORDER + 1)
+                    return nb_fail(ctx, NB_E_INVALID, "medium %u: grid needs a border of %d voxels and at least one voxel inside", i, NB_GRID_BORDER);
+            if (!(m.max_density > 0.f) || !(fmaxf(m.mu_t[0], fmaxf(m.mu_t[1], m.mu_t[2])) > 0.f))
+                return nb_fail(ctx, NB_E_INVALID, "medium %u: heterogeneous medium needs max_density > 0 and sigma_t > 0", i);
         }
     }
 

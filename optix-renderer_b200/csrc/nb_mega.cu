@@ -247,7 +247,7 @@ __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbP
         nb_shape sh2; NbIts its2;
         nb_hit_info(sc, h, so, es.ray_d, sh2, its2);
         if (sh2.bsdf >= 0) return mk3(0.f);
-        tr = tr * nb_transmittance(sc, sm, so, its2.p);
+        tr = tr * nb_transmittance(sc, sm, so, its2.p, ps.rng);
         sm = nb_medium_behind(sc, sh2, its2.geo_n, es.ray_d);
         so = its2.p;
         smaxt -= h.t;
@@ -272,10 +272,10 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
                                               const NbHit &hit, uint32_t &n_closest) {
     nb_shape sh; NbIts its;
     nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
-    const float tm = nb_free_path(sc, medium, ps.rng);
+    const float tm = nb_free_path(sc, medium, ps.o, ps.d, ps.rng);
     const bool mi = tm < hit.t;                                          /* isMediumInteraction */
     const f3 p = mi ? ps.o + ps.d * tm : its.p;
-    ps.thr = ps.thr * nb_transmittance(sc, medium, ps.o, p);
+    ps.thr = ps.thr * nb_transmittance(sc, medium, ps.o, p, ps.rng);
     uint32_t measure = (ps.flags >> NB_MEASURE_SHIFT) & 3u;
     /* captured emission; volume emitters have no kernel (the host loader refuses them) */
     if (!mi && sh.emitter >= 0) {

@@ -1,0 +1,47 @@
+/* nb_probe.cu — parity entry for the medium row: Medium::sampleFreePath,
+ * Medium::getTransmittance and NvdbVolume::getDensity evaluated on a fixed ray set, so the device
+ * functions of nb_volume.cuh can be held against the oracle one by one (density: per point;
+ * free path and transmittance: as means over `samples` draws), not only through rendered images. */
+#include "nb_internal.h"
+#include "nb_volume.cuh"
+
+__global__ void nb_k_medium_probe(NbDeviceScene sc, int32_t medium, const float4 *rays, uint64_t n, uint32_t samples, uint64_t seed, float4 *out) {
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 a = rays[2 * i], b = rays[2 * i + 1];
+    const f3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, b.x, b.y);
+    const float maxt = b.w;
+    const nb_medium &m = sc.media[medium];
+    NbRng rng; rng.seed(seed, i);
+    float dens = 0.f;
+    if (m.type == NB_MEDIUM_HETEROGENEOUS) dens = nb_grid_density(sc, m, nb_grid_point(m, o));
+    float hit = 0.f, len = 0.f, tr = 0.f;
+    const f3 to = o + d * maxt;
+    for (uint32_t k = 0; k < samples; ++k) {
+        const float t = nb_free_path(sc, medium, o, d, rng);
+        if (t < maxt) { hit += 1.f; len += t; }
+        tr += nb_transmittance(sc, medium, o, to, rng).x;
+    }
+    out[i] = make_float4(dens, hit / (float) samples, hit > 0.f ? len / hit : 0.f, tr / (float) samples);
+}
+
+extern "C" int nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples, uint64_t seed, float *out) {
+    if (!ctx) return NB_E_INVALID;
+    if (!ctx->scene_ready) return nb_fail(ctx, NB_E_STATE, "nb_medium_probe: upload a scene first");
+    if (medium < 0 || medium >= (int32_t) ctx->dev.n_media) return nb_fail(ctx, NB_E_INVALID, "nb_medium_probe: medium %d out of range", medium);
+    if (n == 0) return NB_OK;
+    if (!rays || !out || samples == 0) return nb_fail(ctx, NB_E_INVALID, "nb_medium_probe: null argument");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    float4 *d_rays = nullptr, *d_out = nullptr;
+    NB_CUDA(ctx, cudaMalloc((void **) &d_rays, n * 32));
+    cudaError_t e = cudaMalloc((void **) &d_out, n * 16);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_rays, rays, n * 32, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) {
+        nb_k_medium_probe<<<(unsigned) ((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->dev, medium, d_rays, n, samples, seed, d_out);
+        e = cudaMemcpyAsync(out, d_out, n * 16, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_rays); cudaFree(d_out);
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_medium_probe: %s", cudaGetErrorString(e));
+    return NB_OK;
+}

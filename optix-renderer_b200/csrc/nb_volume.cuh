@@ -62,10 +62,120 @@ __device__ __forceinline__ float nb_phase_pdf(const nb_medium &m, f3 wo) {
     return NB_INV_FOURPI;
 }
 
-/* Medium::sampleFreePath. medium < 0 is the vacuum (no draws). */
-__device__ __forceinline__ float nb_free_path(const NbDeviceScene &sc, int32_t medium, NbRng &rng) {
+/* ---- heterogeneous medium (src/media/heterogmedium.cpp:105-174) ---------------------------------
+ * The reference samples a NanoVDB grid with its 27-tap triquadratic sampler (NvdbVolume.h:39-41,
+ * nanovdb/util/SampleFromVoxels.h: TriquadraticSampler) inside the grid's bounding box, delta
+ * tracking for the free path and ratio tracking for the transmittance against the majorant
+ * max(0.001, densityScale * gridMax) * max(sigma_t). Here the grid is a dense array with a
+ * border of NB_GRID_BORDER background voxels on every side (include/norib200.h), so the stencil
+ * of any point inside the box reads in bounds; world_to_grid maps a world point to array
+ * coordinates, the ray direction is mapped without renormalising, so t stays a world distance.
+ * What this restates is the reference WITH the corrections SURVEY.md 8c lists (as written the
+ * reference returns transmittance 0, mixes index- and world-space t, and holds a dangling accessor):
+ * transmittance starts at 1, a ray that misses the box has free path infinity / transmittance 1,
+ * a free path that leaves the box without a collision is infinity, t is a world distance. */
+__device__ __forceinline__ f3 nb_grid_point(const nb_medium &m, f3 p) {
+    const float *M = m.world_to_grid;
+    return mk3(M[0] * p.x + M[1] * p.y + M[2] * p.z + M[3], M[4] * p.x + M[5] * p.y + M[6] * p.z + M[7],
+               M[8] * p.x + M[9] * p.y + M[10] * p.z + M[11]);
+}
+__device__ __forceinline__ f3 nb_grid_dir(const nb_medium &m, f3 d) {
+    const float *M = m.world_to_grid;
+    return mk3(M[0] * d.x + M[1] * d.y + M[2] * d.z, M[4] * d.x + M[5] * d.y + M[6] * d.z, M[8] * d.x + M[9] * d.y + M[10] * d.z);
+}
+
+/* nanovdb::Ray::intersects(bbox, t0, t1) (nanovdb/util/Ray.h:343-363) against the box of active
+ * voxels, in grid coordinates; [t0, t1] comes back clipped to [mint, maxt] */
+__device__ __forceinline__ bool nb_grid_clip(const nb_medium &m, f3 og, f3 dg, float mint, float maxt, float &t0, float &t1) {
+    t0 = mint; t1 = maxt;
+    const float o[3] = { og.x, og.y, og.z }, d[3] = { dg.x, dg.y, dg.z };
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float lo = (float) NB_GRID_BORDER, hi = (float) (m.grid_dims[a] - NB_GRID_BORDER);
+        if (d[a] == 0.f) { if (o[a] < lo || o[a] > hi) return false; continue; }
+        const float inv = 1.f / d[a];
+        float ta = (lo - o[a]) * inv, tb = (hi - o[a]) * inv;
+        if (ta > tb) { const float x = ta; ta = tb; tb = x; }
+        t0 = fmaxf(t0, ta); t1 = fminf(t1, tb);
+    }
+    return t0 <= t1;
+}
+
+/* TriquadraticSampler::sample: one axis of the quadratic B-spline-like kernel */
+__device__ __forceinline__ float nb_quad_kernel(float v0, float v1, float v2, float w) {
+    return w * (w * (0.5f * (v0 + v2) - v1) + 0.5f * (v2 - v0)) + v1;
+}
+
+/* NvdbVolume::getDensity (src/textures/NvdbVolume.cpp:39-48): SampleFromVoxels<.., 2> at a point
+ * in grid coordinates; the stencil is ijk-1 .. ijk+1 around ijk = floor(p), z innermost */
+__device__ __forceinline__ float nb_grid_density(const NbDeviceScene &sc, const nb_medium &m, f3 p) {
+    const float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
+    const float u = p.x - fx, v = p.y - fy, w = p.z - fz;
+    const int nx = (int) m.grid_dims[0], ny = (int) m.grid_dims[1], nz = (int) m.grid_dims[2];
+    const int i = min(max((int) fx, 1), nx - 2), j = min(max((int) fy, 1), ny - 2), k = min(max((int) fz, 1), nz - 2);
+    const float *base = sc.density + m.first_voxel + ((size_t) (i - 1) * ny + (j - 1)) * nz + (k - 1);
+    float vx[3];
+#pragma unroll
+    for (int dx = 0; dx < 3; ++dx) {
+        float vy[3];
+#pragma unroll
+        for (int dy = 0; dy < 3; ++dy) {
+            const float *row = base + ((size_t) dx * ny + dy) * nz;
+            vy[dy] = nb_quad_kernel(__ldg(row), __ldg(row + 1), __ldg(row + 2), w);
+        }
+        vx[dx] = nb_quad_kernel(vy[0], vy[1], vy[2], v);
+    }
+    return nb_quad_kernel(vx[0], vx[1], vx[2], u);
+}
+
+struct NbMajorant { float inv_mu, accept; };       /* step scale 1 / (densityMax * max sigma_t); density -> collision probability */
+__device__ __forceinline__ NbMajorant nb_majorant(const nb_medium &m) {
+    const float dmax = fmaxf(0.001f, m.density_scale * m.max_density);                    /* heterogmedium.cpp:81 */
+    NbMajorant r;
+    r.inv_mu = 1.f / (dmax * fmaxf(m.mu_t[0], fmaxf(m.mu_t[1], m.mu_t[2])));
+    r.accept = m.density_scale / dmax;                                                    /* = 1 / gridMax unless clamped */
+    return r;
+}
+
+/* HeterogeneousMedium::sampleFreePath: delta tracking from ray.mint = Epsilon */
+__device__ __forceinline__ float nb_free_path_heterog(const NbDeviceScene &sc, const nb_medium &m, f3 o, f3 d, NbRng &rng) {
+    const f3 og = nb_grid_point(m, o), dg = nb_grid_dir(m, d);
+    float t, t1;
+    if (!nb_grid_clip(m, og, dg, NB_EPS, INFINITY, t, t1)) return INFINITY;
+    const NbMajorant mj = nb_majorant(m);
+    for (int guard = 0; guard < (1 << 20); ++guard) {
+        t -= __logf(rng.next_float()) * mj.inv_mu;
+        if (!(t < t1)) return INFINITY;
+        if (nb_grid_density(sc, m, og + dg * t) * mj.accept >= rng.next_float()) return t;
+    }
+    return INFINITY;
+}
+
+/* HeterogeneousMedium::getTransmittance: ratio tracking between two points */
+__device__ __forceinline__ f3 nb_transmittance_heterog(const NbDeviceScene &sc, const nb_medium &m, f3 from, f3 to, NbRng &rng) {
+    const f3 seg = to - from;
+    const float dist = length(seg);
+    if (!(dist > 0.f)) return mk3(1.f);
+    const f3 d = seg / dist;
+    const f3 og = nb_grid_point(m, from), dg = nb_grid_dir(m, d);
+    float t, t1;
+    if (!nb_grid_clip(m, og, dg, NB_EPS, dist, t, t1)) return mk3(1.f);
+    const NbMajorant mj = nb_majorant(m);
+    float tr = 1.f;
+    for (int guard = 0; guard < (1 << 20); ++guard) {
+        t -= __logf(rng.next_float()) * mj.inv_mu;
+        if (!(t < t1)) break;
+        tr *= 1.f - nb_grid_density(sc, m, og + dg * t) * mj.accept;
+        if (tr <= 0.f) { tr = 0.f; break; }
+    }
+    return mk3(tr);
+}
+
+/* Medium::sampleFreePath along the ray (o, d) from mint = Epsilon. medium < 0 is the vacuum (no draws). */
+__device__ __forceinline__ float nb_free_path(const NbDeviceScene &sc, int32_t medium, f3 o, f3 d, NbRng &rng) {
     if (medium < 0) return INFINITY;
     const nb_medium &m = sc.media[medium];
+    if (m.type == NB_MEDIUM_HETEROGENEOUS) return nb_free_path_heterog(sc, m, o, d, rng);
     if (m.type != NB_MEDIUM_HOMOGENEOUS) return INFINITY;
     const int ch = (int) (3.f * rng.next_float());                       /* homogmedium.cpp:62-66 */
     const float mu = m.mu_t[ch];
@@ -74,9 +184,10 @@ __device__ __forceinline__ float nb_free_path(const NbDeviceScene &sc, int32_t m
 }
 
 /* Medium::getTransmittance(from, to) */
-__device__ __forceinline__ f3 nb_transmittance(const NbDeviceScene &sc, int32_t medium, f3 from, f3 to) {
+__device__ __forceinline__ f3 nb_transmittance(const NbDeviceScene &sc, int32_t medium, f3 from, f3 to, NbRng &rng) {
     if (medium < 0) return mk3(1.f);
     const nb_medium &m = sc.media[medium];
+    if (m.type == NB_MEDIUM_HETEROGENEOUS) return nb_transmittance_heterog(sc, m, from, to, rng);
     if (m.type != NB_MEDIUM_HOMOGENEOUS) return mk3(1.f);
     const float dist = length(from - to);                                /* homogmedium.cpp:68-72 */
     return mk3(__expf(-m.mu_t[0] * dist), __expf(-m.mu_t[1] * dist), __expf(-m.mu_t[2] * dist));

@@ -39,3 +39,59 @@ int nbh_parse_xml(const char *xml_path, char *summary, int summary_len) {
 }
 
 }
+
+/* ---- volume files (vdb.h) ------------------------------------------------------------------------ */
+#include "vdb.h"
+extern "C" {
+
+/* "name:type\n" per grid */
+int nbh_vdb_list(const char *path, char *out, int out_len) {
+    try {
+        std::string s;
+        for (const auto &g : nori::vdbListGrids(path)) s += g.first + ":" + g.second + "\n";
+        if (out && out_len > 0) snprintf(out, out_len, "%s", s.c_str());
+        return 0;
+    } catch (const std::exception &e) { g_error = e.what(); return -1; }
+}
+
+/* One float grid as a dense array. bbox = {min xyz, max xyz} of the active voxels (inclusive),
+ * stats = {background, min, max}. With values == NULL only the header is filled. Returns the
+ * number of voxels of the dense array, or -1. */
+long long nbh_vdb_read(const char *path, const char *grid, int32_t bbox[6], double index_to_world[12], float stats[3],
+                       uint64_t *active_voxels, float *values, uint64_t capacity) {
+    try {
+        const nori::VdbGrid g = nori::vdbReadFloatGrid(path, grid);
+        for (int k = 0; k < 3; ++k) { bbox[k] = g.bbox_min[k]; bbox[3 + k] = g.bbox_max[k]; }
+        for (int k = 0; k < 12; ++k) index_to_world[k] = g.index_to_world[k];
+        stats[0] = g.background; stats[1] = g.value_min; stats[2] = g.value_max;
+        if (active_voxels) *active_voxels = g.active_voxels;
+        if (values) {
+            if (capacity < g.values.size()) { g_error = "nbh_vdb_read: buffer too small"; return -1; }
+            std::copy(g.values.begin(), g.values.end(), values);
+        }
+        return (long long) g.values.size();
+    } catch (const std::exception &e) { g_error = e.what(); return -1; }
+}
+
+}
+
+/* .vdb -> .nbv: one float grid as a dense dump ("NBV1", i32 dims[3], i32 bbox_min[3], f64
+ * index_to_world[12], f32 background, f32 values x-slowest). The oracle harness reads it in place
+ * of the OpenVDB library (oracle/ref_heterog.cpp); the `volume` plugin reads it too. */
+extern "C" int nbh_vdb_to_nbv(const char *vdb_path, const char *grid, const char *nbv_path) {
+    try {
+        nori::vdbWriteNbv(nori::vdbReadFloatGrid(vdb_path, grid), nbv_path);
+        return 0;
+    } catch (const std::exception &e) { g_error = e.what(); return -1; }
+}
+
+/* codecs.h, for the tests: zlib stream -> bytes. Returns the decoded size or -1. */
+#include "codecs.h"
+extern "C" long long nbh_inflate(const uint8_t *src, uint64_t n, uint8_t *dst, uint64_t capacity) {
+    try {
+        const std::vector<uint8_t> out = nori::zlibInflate(src, (size_t) n);
+        if (out.size() > capacity) { g_error = "nbh_inflate: buffer too small"; return -1; }
+        std::copy(out.begin(), out.end(), dst);
+        return (long long) out.size();
+    } catch (const std::exception &e) { g_error = e.what(); return -1; }
+}

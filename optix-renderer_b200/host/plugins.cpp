@@ -2,6 +2,7 @@
  * Each constructor reads the properties the reference's constructor reads, with its defaults
  * (file:line beside each class); each flatten hook fills the matching C-ABI record. */
 #include "plugins.h"
+#include "vdb.h"
 #include <cstring>
 
 namespace nori {
@@ -312,7 +313,7 @@ void Medium::activate() {
 class VacuumMedium : public Medium {
 public:
     explicit VacuumMedium(const PropertyList &p) : Medium(p) {}
-    bool getB200MediumData(nb_medium &out) const override {
+    bool getB200MediumData(nb_medium &out, FlatScene &) const override {
         memset(&out, 0, sizeof(out));
         out.type = NB_MEDIUM_VACUUM;
         return m_emitter == nullptr;
@@ -324,7 +325,7 @@ NORI_REGISTER_CLASS(VacuumMedium, "vacuum")
 class HomogeneousMedium : public Medium {           /* homogmedium.cpp:16-19, 48-60 */
 public:
     explicit HomogeneousMedium(const PropertyList &p) : Medium(p), m_density(p.getFloat("density", 1.f)) {}
-    bool getB200MediumData(nb_medium &out) const override {
+    bool getB200MediumData(nb_medium &out, FlatScene &) const override {
         memset(&out, 0, sizeof(out));
         out.type = NB_MEDIUM_HOMOGENEOUS;
         for (int i = 0; i < 3; ++i) out.mu_t[i] = m_density * m_sigma_a[i] + m_density * m_sigma_s[i];   /* mu_a + mu_s */
@@ -337,31 +338,83 @@ private:
 };
 NORI_REGISTER_CLASS(HomogeneousMedium, "homog")
 
-/* <volume type="volume"> (src/textures/NvdbVolume.cpp): an OpenVDB file converted to NanoVDB at load
- * time by OpenVDB, which this image does not have — the object parses, the medium reports no kernel */
-class NvdbVolumeStub : public NoriObject {
+/* <volume type="volume"> (src/textures/NvdbVolume.cpp, NvdbVolume.vdb.cpp): the "density" and
+ * "temperature" float grids of an OpenVDB file. The reference converts them to NanoVDB through the
+ * OpenVDB library and caches a .nvdb next to the file; here vdb.cpp reads the .vdb itself and the
+ * grid goes to the GPU as a dense array (include/norib200.h, nb_medium). */
+class NvdbVolume : public NoriObject {
 public:
-    explicit NvdbVolumeStub(const PropertyList &p) : m_filename(p.getString("filename", "")) {}
+    explicit NvdbVolume(const PropertyList &p) : m_filename(resolvePath(p.getString("filename"))) {}
     EClassType getClassType() const override { return EVolume; }
-    std::string toString() const override { return "NvdbVolume[" + m_filename + "]"; }
+    void activate() override {                          /* NvdbVolume::loadFromFile (NvdbVolume.vdb.cpp:9-40) */
+        const size_t dot = m_filename.rfind('.');
+        const std::string ext = dot == std::string::npos ? "" : m_filename.substr(dot);
+        if (ext == ".nvdb") throw NoriException("Volume: %s is a NanoVDB cache; point the scene at the .vdb it was made from", m_filename);
+        if (ext == ".nbv") { density = vdbReadNbv(m_filename); return; }     /* dense dump (vdb.h) */
+        if (ext != ".vdb") throw NoriException("Volume: file extension %s unknown.", ext);
+        density = vdbReadFloatGrid(m_filename, "density");
+    }
+    std::string toString() const override { return "Volume[\n  filename = " + m_filename + ",\n]"; }
+    VdbGrid density;
 private:
     std::string m_filename;
 };
-NORI_REGISTER_CLASS(NvdbVolumeStub, "volume")
+NORI_REGISTER_CLASS(NvdbVolume, "volume")
 
-class HeterogeneousMedium : public Medium {         /* needs a NanoVDB grid converted from .vdb by OpenVDB: not available here */
+class HeterogeneousMedium : public Medium {         /* heterogmedium.cpp:47-103 */
 public:
-    explicit HeterogeneousMedium(const PropertyList &p) : Medium(p) {}
+    explicit HeterogeneousMedium(const PropertyList &p)
+        : Medium(p), m_densityScale(p.getFloat("densityScale", 1.f)), m_temperatureScale(p.getFloat("temperatureScale", 0.f)) {}
     ~HeterogeneousMedium() override { delete m_volume; }
     void addChild(NoriObject *obj) override {
-        if (obj->getClassType() != EVolume) { Medium::addChild(obj); return; }
+        if (obj->getClassType() != EVolume) {
+            throw NoriException("HeterogeneousMedium::addChild(<%s>) is not supported!", classTypeName(obj->getClassType()));
+        }
         if (m_volume) throw NoriException("There is already an volume defined!");
-        m_volume = obj;
+        m_volume = static_cast<NvdbVolume *>(obj);
     }
-    bool getB200MediumData(nb_medium &) const override { return false; }
-    std::string toString() const override { return "HeterogeneousMedium[]"; }
+    void activate() override {
+        if (!m_volume) throw NoriException("HeterogeneousMedium requires a nvdb volume.");
+        Medium::activate();
+    }
+    bool getB200MediumData(nb_medium &out, FlatScene &flat) const override {
+        memset(&out, 0, sizeof(out));
+        const VdbGrid &g = m_volume->density;
+        if (m_emitter || m_temperatureScale > 1e-4f) return false;     /* volume emission: no kernel */
+        if (g.active_voxels == 0 || !(g.value_max > 0.f)) return false;
+        out.type = NB_MEDIUM_HETEROGENEOUS;
+        for (int i = 0; i < 3; ++i) out.mu_t[i] = m_sigma_a[i] + m_sigma_s[i];
+        m_phase->getB200PhaseData(out);
+        out.density_scale = m_densityScale;
+        out.max_density = g.value_max;
+        /* dense array = active box + border, read through getValue so stored inactive values survive */
+        const int B = NB_GRID_BORDER;
+        int org[3];
+        for (int a = 0; a < 3; ++a) { out.grid_dims[a] = (uint32_t) (g.dims[a] + 2 * B); org[a] = g.bbox_min[a] - B; }
+        out.first_voxel = (uint32_t) flat.density.size();
+        flat.density.reserve(flat.density.size() + (size_t) out.grid_dims[0] * out.grid_dims[1] * out.grid_dims[2]);
+        for (int i = 0; i < (int) out.grid_dims[0]; ++i)
+            for (int j = 0; j < (int) out.grid_dims[1]; ++j)
+                for (int k = 0; k < (int) out.grid_dims[2]; ++k) flat.density.push_back(g.at(org[0] + i, org[1] + j, org[2] + k));
+        /* world -> index (inverse of the grid's affine map, in double), then index -> array coordinates */
+        const double *M = g.index_to_world;
+        const double a = M[0], b = M[1], c = M[2], d = M[4], e = M[5], f = M[6], gg = M[8], h = M[9], k = M[10];
+        const double det = a * (e * k - f * h) - b * (d * k - f * gg) + c * (d * h - e * gg);
+        if (det == 0.0) throw NoriException("HeterogeneousMedium: the volume's transform is singular");
+        const double inv[9] = { (e * k - f * h) / det, (c * h - b * k) / det, (b * f - c * e) / det,
+                                (f * gg - d * k) / det, (a * k - c * gg) / det, (c * d - a * f) / det,
+                                (d * h - e * gg) / det, (b * gg - a * h) / det, (a * e - b * d) / det };
+        for (int r = 0; r < 3; ++r) {
+            double t = 0.0;
+            for (int cc = 0; cc < 3; ++cc) { out.world_to_grid[r * 4 + cc] = (float) inv[r * 3 + cc]; t -= inv[r * 3 + cc] * M[cc * 4 + 3]; }
+            out.world_to_grid[r * 4 + 3] = (float) (t - org[r]);
+        }
+        return true;
+    }
+    std::string toString() const override { return "HeterogeneousMedium[...]"; }
 private:
-    NoriObject *m_volume = nullptr;
+    NvdbVolume *m_volume = nullptr;
+    float m_densityScale, m_temperatureScale;
 };
 NORI_REGISTER_CLASS(HeterogeneousMedium, "heterog")
 

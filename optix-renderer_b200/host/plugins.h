@@ -11,6 +11,7 @@ std::string resolvePath(const std::string &relative);      /* filesystem::resolv
 void setResolveRoot(const std::string &dir);
 
 class Shape;
+struct FlatScene;
 
 /* include/nori/bsdf.h:82-123 */
 class BSDF : public NoriObject {
@@ -50,7 +51,7 @@ public:
     void addChild(NoriObject *obj) override;            /* medium.cpp:50-72: one phase, one emitter */
     void activate() override;                           /* isotropic phase by default (medium.cpp:22-24) */
     /* replaces getOptixMediumData (medium.h:68); false = no GPU kernel for this medium */
-    virtual bool getB200MediumData(nb_medium &out) const = 0;
+    virtual bool getB200MediumData(nb_medium &out, FlatScene &flat) const = 0;   /* heterogeneous media append their voxels to flat.density */
 protected:
     Color3f m_sigma_a, m_sigma_s;                       /* normalized colour * intensity */
     PhaseFunction *m_phase = nullptr;
@@ -147,6 +148,7 @@ struct FlatScene {
     std::vector<nb_bsdf> bsdfs;
     std::vector<nb_emitter> emitters;
     std::vector<nb_medium> media;
+    std::vector<float> density;                         /* voxel arrays of heterogeneous media */
     int32_t ambient_medium = -1;
     nb_camera camera;
     nb_render_params render;

@@ -85,7 +85,7 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
         }
         if (s->getMedium()) {
             nb_medium m;
-            if (!s->getMedium()->getB200MediumData(m)) return fail("medium '" + s->getMedium()->toString() + "' has no GPU kernel");
+            if (!s->getMedium()->getB200MediumData(m, out)) return fail("medium '" + s->getMedium()->toString() + "' has no GPU kernel");
             rec.medium = (int32_t) out.media.size();
             out.media.push_back(m);
         }
@@ -107,7 +107,7 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
     }
     if (m_ambientMedium) {
         nb_medium m;
-        if (!m_ambientMedium->getB200MediumData(m)) return fail("ambient medium '" + m_ambientMedium->toString() + "' has no GPU kernel");
+        if (!m_ambientMedium->getB200MediumData(m, out)) return fail("ambient medium '" + m_ambientMedium->toString() + "' has no GPU kernel");
         if (m.type != NB_MEDIUM_VACUUM) { out.ambient_medium = (int32_t) out.media.size(); out.media.push_back(m); }
     }
     m_camera->getB200Data(out.camera);
@@ -140,6 +140,7 @@ nb_scene_desc FlatScene::desc() const {
     d.camera = camera;
     d.n_media = (uint32_t) media.size(); d.media = media.empty() ? nullptr : media.data();
     d.ambient_medium = ambient_medium;
+    d.n_density = density.size(); d.density = density.empty() ? nullptr : density.data();
     return d;
 }
 
@@ -158,6 +159,7 @@ void FlatScene::writeNbs(const std::string &path) const {
     if (!media.empty() || ambient_medium >= 0) {
         secs.push_back({ "media", sizeof(nb_medium), media.data(), media.size() });
         secs.push_back({ "ambient", 4, &ambient_medium, 1 });
+        if (!density.empty()) secs.push_back({ "density", 4, density.data(), density.size() });
     }
     secs.push_back({ "camera", sizeof(nb_camera), &camera, 1 });
     secs.push_back({ "render", sizeof(nb_render_params), &render, 1 });

@@ -640,6 +640,51 @@ static int modeRng(int argc, char **argv) {
     return 0;
 }
 
+/* ---- medium: Medium::sampleFreePath / getTransmittance / (heterogeneous) density on fixed rays ----
+ * rays.bin: n x 8 f32 (o, d, mint, maxt). Output n x 4 f32: density at o (0 for media without a
+ * grid), fraction of `samples` free paths shorter than maxt, their mean length, mean transmittance
+ * (channel 0) from o to o + maxt*d. The medium is that of the first shape that has one, else the
+ * scene's ambient medium. */
+NORI_NAMESPACE_BEGIN
+float oracleHeterogDensity(const Medium *m, const Point3f &p, bool &isHeterog);   /* ref_heterog.cpp */
+NORI_NAMESPACE_END
+static int modeMedium(int argc, char **argv) {
+    if (argc < 5) return 2;
+    auto kv = parseKv(argc, argv, 5);
+    const int samples = kv.count("samples") ? std::stoi(kv["samples"]) : 1024;
+    LoadedScene ls = loadScene(argv[2]);
+    const Medium *medium = ls.render->getAmbientMedium();
+    for (Shape *sh : ls.render->getShapes()) if (sh->getMedium()) { medium = sh->getMedium(); break; }
+    if (!medium) throw NoriException("scene has no medium");
+    FILE *f = fopen(argv[3], "rb");
+    if (!f) throw NoriException("cannot read %s", argv[3]);
+    fseek(f, 0, SEEK_END); const size_t n = (size_t) ftell(f) / 32; fseek(f, 0, SEEK_SET);
+    std::vector<float> rays(n * 8), out(n * 4);
+    if (fread(rays.data(), 32, n, f) != n) throw NoriException("short read on %s", argv[3]);
+    fclose(f);
+    std::unique_ptr<Sampler> sampler(static_cast<Sampler *>(NoriObjectFactory::createInstance("independent")));
+    for (size_t i = 0; i < n; ++i) {
+        const float *r = &rays[i * 8];
+        Ray3f ray(Point3f(r[0], r[1], r[2]), Vector3f(r[3], r[4], r[5]), r[6], r[7]);
+        bool het = false;
+        out[i * 4] = oracleHeterogDensity(medium, ray.o, het);
+        double hit = 0, len = 0, tr = 0;
+        for (int k = 0; k < samples; ++k) {
+            MediumQueryRecord mRec(Ray3f(ray.o, ray.d, Epsilon, INFINITY));
+            const float t = medium->sampleFreePath(mRec, *sampler);
+            if (t < ray.maxt) { hit += 1; len += t; }
+            tr += medium->getTransmittance(ray.o, ray(ray.maxt), false, *sampler)(0);
+        }
+        out[i * 4 + 1] = (float) (hit / samples); out[i * 4 + 2] = hit > 0 ? (float) (len / hit) : 0.f; out[i * 4 + 3] = (float) (tr / samples);
+    }
+    f = fopen(argv[4], "wb");
+    if (!f) throw NoriException("cannot write %s", argv[4]);
+    fwrite(out.data(), 16, n, f);
+    fclose(f);
+    printf("{\"mode\": \"medium\", \"rays\": %zu, \"samples\": %d}\n", n, samples);
+    return 0;
+}
+
 static int usage() {
     fprintf(stderr,
         "nori_ref — headless harness around the reference CPU renderer (test infrastructure)\n"
@@ -650,7 +695,8 @@ static int usage() {
         "  nori_ref flat    scene.xml scene.nbs      (flattened scene container, include/nb_scene_file.h)\n"
         "  nori_ref test    test.xml\n"
         "  nori_ref ttest   test.xml [samples=N]   (scene-mode t-tests, restated: see modeTTestScenes)\n"
-        "  nori_ref rng     n\n");
+        "  nori_ref rng     n\n"
+        "  nori_ref medium  scene.xml rays.bin out.bin [samples=K]   (free path / transmittance / density probes)\n");
     return 2;
 }
 
@@ -667,6 +713,7 @@ int main(int argc, char **argv) {
         else if (mode == "test") rc = modeTest(argc, argv);
         else if (mode == "ttest") rc = modeTTestScenes(argc, argv);
         else if (mode == "rng") rc = modeRng(argc, argv);
+        else if (mode == "medium") rc = modeMedium(argc, argv);
         if (rc == 2) return usage();
         return rc;
     } catch (const std::exception &e) {
