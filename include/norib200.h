@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 3
+#define NB_ABI_VERSION 4
 
 enum {
     NB_OK = 0,
@@ -40,6 +40,8 @@ enum { NB_SHAPE_MESH = 0, NB_SHAPE_SPHERE = 1 };
 enum { NB_BSDF_DIFFUSE = 0, NB_BSDF_MIRROR = 1, NB_BSDF_DIELECTRIC = 2, NB_BSDF_MICROFACET = 3,
        NB_BSDF_NONE = 0xff };
 enum { NB_EMITTER_AREA = 0, NB_EMITTER_POINT = 1, NB_EMITTER_ENVMAP = 2 };
+enum { NB_TEXTURE_CONSTANT = 0, NB_TEXTURE_IMAGE = 1, NB_TEXTURE_CHECKERBOARD = 2 };
+enum { NB_TEXTURE_SPHERICAL = 1u };
 enum { NB_INTEGRATOR_PATH_MIS = 0, NB_INTEGRATOR_PATH_MATS = 1, NB_INTEGRATOR_DIRECT_EMS = 2,
        NB_INTEGRATOR_DIRECT_MATS = 3, NB_INTEGRATOR_DIRECT_MIS = 4, NB_INTEGRATOR_NORMALS = 5,
        NB_INTEGRATOR_DIRECT = 6, NB_INTEGRATOR_AV = 7, NB_INTEGRATOR_PATH_VOL_MATS = 8,
@@ -72,7 +74,8 @@ typedef struct nb_shape {
 /* BSDF::getOptixMaterialData replacement (bsdf/diffuse.cpp, mirror.cpp, dielectric.cpp,
  * microfacet.cpp). */
 typedef struct nb_bsdf {
-    uint32_t type;           /* NB_BSDF_* */
+    uint32_t type;           /* bits 0..7: NB_BSDF_*; bits 8..31: 1 + index of the albedo texture
+                                (Diffuse::m_albedo, diffuse.cpp:31-40,77-91), 0 = the constant below */
     float    albedo[3];      /* diffuse albedo / microfacet kd */
     float    alpha;          /* microfacet roughness */
     float    int_ior, ext_ior;
@@ -83,10 +86,28 @@ typedef struct nb_bsdf {
  * environmentmap.cpp). */
 typedef struct nb_emitter {
     uint32_t type;           /* NB_EMITTER_* */
-    int32_t  shape;          /* area light: owning shape */
-    float    radiance[3];    /* area: radiance; point: power/(4 pi) (pointlight.cpp:44) */
-    float    position[3];    /* point light */
+    int32_t  shape;          /* area light: owning shape; environment map: index of its texture (EnvMap::m_map) */
+    float    radiance[3];    /* area: radiance; point: power/(4 pi) (pointlight.cpp:44); envmap: m_radiance */
+    float    position[3];    /* point light. Environment map: the three words are
+                                { u32 cdf_offset, f32 cdf_norm, 0 } — EnvMap::dpdf (environmentmap.cpp:146-161):
+                                width*height+1 floats at cdf_offset of area_cdf, and its getNormalization() */
 } nb_emitter;                /* 32 bytes */
+
+/* Texture<Color3f> (src/textures/consttexture.cpp:37, checkerboard.cpp:34-52, PNGTexture.cpp:125-165),
+ * replaces Texture::getOptixTexture (texture.h:75). An image's texels are RGBA floats exactly as
+ * PNGTexture::data holds them after loadFromFile (inverse gamma applied), row 0 first. */
+typedef struct nb_texture {
+    uint32_t type;           /* NB_TEXTURE_* */
+    uint32_t flags;          /* NB_TEXTURE_SPHERICAL: PNGTexture::sphericalTexture */
+    uint32_t width, height;  /* Texture::getWidth/getHeight (1 x 1 for constant and checkerboard) */
+    uint32_t first_texel;    /* image: offset into nb_scene_desc.texels, in texels (4 floats each) */
+    float    value[3];       /* constant: the colour; checkerboard: value1 */
+    float    value2[3];      /* checkerboard: value2 */
+    float    scale[2];       /* image: scaleU, scaleV; checkerboard: m_scale */
+    float    offset[2];      /* image: offsetU, offsetV; checkerboard: m_delta */
+    float    rotation[9];    /* image, spherical: the row-major rotation PNGTexture::eval builds from eulerAngles */
+    uint32_t pad[2];
+} nb_texture;                /* 96 bytes */
 
 /* Camera::getOptixData replacement (cameras/perspective.cpp:48-141). Matrices are row-major
  * 4x4 as Eigen prints them (element [r*4+c]). */
@@ -144,6 +165,8 @@ typedef struct nb_scene_desc {
     uint32_t n_media;     const nb_medium  *media;       /* may be 0 / NULL */
     int32_t  ambient_medium;                             /* Scene::getAmbientMedium, -1 = vacuum */
     uint64_t n_density;   const float      *density;     /* voxel data of heterogeneous media or NULL */
+    uint32_t n_textures;  const nb_texture *textures;    /* may be 0 / NULL */
+    uint64_t n_texels;    const float      *texels;      /* 4 floats per texel, or NULL */
 } nb_scene_desc;
 
 /* nb_build_bvh(mode = NB_BVH_IMPORT): the caller's own arrays (BVH::m_nodes / m_indices after
@@ -220,6 +243,11 @@ int  nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int 
  * out gets 4 floats per ray: density at ray.o (0 for a medium without a grid); the fraction of
  * `samples` free paths from ray.o along ray.d shorter than ray.maxt; their mean length; the mean
  * transmittance (first channel) from ray.o to ray.o + ray.maxt * ray.d. */
+/* Parity entry for the emitter rows: Emitter::sample (src/emitters/arealight.cpp:75-103, pointlight.cpp:47-63,
+ * environmentmap.cpp:73-97) of emitters[emitter] on n (reference point, 2D sample) pairs — `in` holds 5
+ * floats per record (ref.xyz, sample.xy). out gets 12 floats per record: lRec.wi, the returned
+ * value (radiance / pdf), lRec.pdf, shadowRay.maxt, Emitter::eval for the sampled direction, 0. */
+int  nb_emitter_probe(nb_ctx *ctx, uint32_t emitter, const float *in, uint64_t n, float *out);
 int  nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples,
                      uint64_t seed, float *out);
 

@@ -40,6 +40,9 @@ camera_dtype = np.dtype([("sample_to_camera", "<f4", 16), ("camera_to_world", "<
 medium_dtype = np.dtype([("type", "<u4"), ("mu_t", "<f4", 3), ("phase", "<u4"), ("phase_param", "<f4"),
                          ("density_scale", "<f4"), ("max_density", "<f4"), ("grid_dims", "<u4", 3),
                          ("first_voxel", "<u4"), ("world_to_grid", "<f4", 12)])
+texture_dtype = np.dtype([("type", "<u4"), ("flags", "<u4"), ("width", "<u4"), ("height", "<u4"), ("first_texel", "<u4"),
+                          ("value", "<f4", 3), ("value2", "<f4", 3), ("scale", "<f4", 2), ("offset", "<f4", 2),
+                          ("rotation", "<f4", 9), ("pad", "<u4", 2)])
 bvh_node_dtype = np.dtype([("word0", "<u4"), ("word1", "<u4"), ("bmin", "<f4", 3), ("bmax", "<f4", 3)])
 ray_dtype = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("mint", "<f4"), ("maxt", "<f4")])
 hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("shape", "<i4"), ("prim", "<i4"), ("any_hit", "<u4")])
@@ -47,7 +50,7 @@ render_params_dtype = np.dtype([("integrator", "<u4"), ("filter_radius", "<f4"),
                                 ("filter_table", "<f4", FILTER_RESOLUTION + 1), ("pad0", "<u4"), ("seed", "<u8"),
                                 ("pool_paths", "<u4"), ("max_depth", "<u4"), ("reserved", "<u4", 4)])
 SECTION_DTYPES = {"shapes": shape_dtype, "bsdfs": bsdf_dtype, "emitters": emitter_dtype, "camera": camera_dtype,
-                  "bvh_nodes": bvh_node_dtype, "render": render_params_dtype, "media": medium_dtype}
+                  "bvh_nodes": bvh_node_dtype, "render": render_params_dtype, "media": medium_dtype, "textures": texture_dtype}
 
 
 class Camera(C.Structure):
@@ -66,7 +69,9 @@ class SceneDesc(C.Structure):
                 ("n_area_cdf", C.c_uint64), ("area_cdf", C.c_void_p),
                 ("camera", Camera),
                 ("n_media", C.c_uint32), ("media", C.c_void_p), ("ambient_medium", C.c_int32),
-                ("n_density", C.c_uint64), ("density", C.c_void_p)]
+                ("n_density", C.c_uint64), ("density", C.c_void_p),
+                ("n_textures", C.c_uint32), ("textures", C.c_void_p),
+                ("n_texels", C.c_uint64), ("texels", C.c_void_p)]
 
 
 class BvhImport(C.Structure):
@@ -83,7 +88,7 @@ class Counters(C.Structure):
 EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
-           "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe"]
+           "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe"]
 
 _lib = None
 
@@ -123,6 +128,7 @@ def load_library(path=None):
     lib.nb_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     lib.nb_sample_slice.argtypes = [C.c_uint32] * 4 + [C.POINTER(C.c_uint32)] * 2
     lib.nb_bvh_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
+    lib.nb_emitter_probe.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p]
     lib.nb_medium_probe.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_void_p]
     if path in (LIB_PATH, os.environ.get("NORIB200_LIB")):
         _lib = lib
@@ -224,6 +230,8 @@ class Context:
         md = keep.get("media"); d.n_media = 0 if md is None else len(md); d.media = _ptr(md)
         d.ambient_medium = int(keep["ambient"][0]) if "ambient" in keep else -1
         dn = keep.get("density"); d.n_density = 0 if dn is None else dn.size; d.density = _ptr(dn)
+        tx = keep.get("textures"); d.n_textures = 0 if tx is None else len(tx); d.textures = _ptr(tx)
+        tl = keep.get("texels"); d.n_texels = 0 if tl is None else tl.size // 4; d.texels = _ptr(tl)
         self._check(self.lib.nb_upload_scene(self.handle, C.byref(d)))
 
     def build_bvh(self, nodes, indices):
@@ -246,6 +254,13 @@ class Context:
             self.build_bvh_device()
         else:
             self.build_bvh(s["bvh_nodes"], s["bvh_indices"])
+
+    def emitter_probe(self, emitter, records):
+        """records: (n, 5) float32 [ref.xyz, sample.xy]; returns (n, 12) [wi, value, pdf, maxt, eval, 0]."""
+        rec = np.ascontiguousarray(records, dtype="<f4").reshape(-1, 5)
+        out = np.zeros((len(rec), 12), dtype="<f4")
+        self._check(self.lib.nb_emitter_probe(self.handle, emitter, _ptr(rec), len(rec), _ptr(out)))
+        return out
 
     def medium_probe(self, medium, rays, samples=1024, seed=1):
         """rays: (n, 8) float32 [o, d, mint, maxt]; returns (n, 4) [density(o), P(free path < maxt), mean path, mean Tr]."""

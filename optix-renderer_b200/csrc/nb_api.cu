@@ -52,6 +52,7 @@ int nb_abi_sizeof(int which) {
         case 8: return (int) sizeof(nb_render_params);
         case 9: return (int) sizeof(nb_counters);
         case 10: return (int) sizeof(nb_medium);
+        case 11: return (int) sizeof(nb_texture);
         default: return -1;
     }
 }
@@ -116,15 +117,35 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
         prims += sh.prim_count;
     }
     if (prims >= NB_SLOT_LAST) return nb_fail(ctx, NB_E_UNSUPPORTED, "too many primitives (%llu)", (unsigned long long) prims);
-    for (uint32_t i = 0; i < s->n_bsdfs; ++i)
-        if (s->bsdfs[i].type > NB_BSDF_MICROFACET)
-            return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: tag %u has no kernel in this backend", i, s->bsdfs[i].type);
+    for (uint32_t i = 0; i < s->n_bsdfs; ++i) {
+        const uint32_t tag = s->bsdfs[i].type & 0xffu, tex = s->bsdfs[i].type >> 8;
+        if (tag > NB_BSDF_MICROFACET) return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: tag %u has no kernel in this backend", i, tag);
+        if (tex && tag != NB_BSDF_DIFFUSE) return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: only the diffuse BSDF takes an albedo texture", i);
+        if (tex > s->n_textures) return nb_fail(ctx, NB_E_INVALID, "bsdf %u: texture index out of range", i);
+    }
+    if (s->n_textures && !s->textures) return nb_fail(ctx, NB_E_INVALID, "textures missing");
+    for (uint32_t i = 0; i < s->n_textures; ++i) {
+        const nb_texture &t = s->textures[i];
+        if (t.type > NB_TEXTURE_CHECKERBOARD) return nb_fail(ctx, NB_E_UNSUPPORTED, "texture %u: tag %u has no kernel in this backend", i, t.type);
+        if (t.width == 0 || t.height == 0) return nb_fail(ctx, NB_E_INVALID, "texture %u: empty", i);
+        if (t.type == NB_TEXTURE_IMAGE && (!s->texels || (uint64_t) t.first_texel + (uint64_t) t.width * t.height > s->n_texels))
+            return nb_fail(ctx, NB_E_INVALID, "texture %u: texels outside the texel array", i);
+        if (t.type == NB_TEXTURE_CHECKERBOARD && (t.scale[0] == 0.f || t.scale[1] == 0.f))
+            return nb_fail(ctx, NB_E_INVALID, "texture %u: checkerboard scale is zero", i);
+    }
     int32_t envmap = -1;
     for (uint32_t i = 0; i < s->n_emitters; ++i) {
         const nb_emitter &e = s->emitters[i];
         if (e.type == NB_EMITTER_AREA) {
             if (e.shape < 0 || e.shape >= (int32_t) s->n_shapes) return nb_fail(ctx, NB_E_INVALID, "emitter %u: area light without a shape", i);
         } else if (e.type == NB_EMITTER_POINT) {
+        } else if (e.type == NB_EMITTER_ENVMAP) {                  /* Scene::addChild keeps the last one as m_envmap (scene.cpp:218-222) */
+            if (e.shape < 0 || e.shape >= (int32_t) s->n_textures) return nb_fail(ctx, NB_E_INVALID, "emitter %u: environment map without a texture", i);
+            const nb_texture &t = s->textures[e.shape];
+            uint32_t off; memcpy(&off, &e.position[0], 4);
+            if (!(t.width == 1 && t.height == 1) && (uint64_t) off + (uint64_t) t.width * t.height + 1 > s->n_area_cdf)
+                return nb_fail(ctx, NB_E_INVALID, "emitter %u: environment map CDF outside area_cdf", i);
+            envmap = (int32_t) i;
         } else return nb_fail(ctx, NB_E_UNSUPPORTED, "emitter %u: tag %u has no kernel in this backend", i, e.type);
     }
     if (s->n_emitters && !s->emitter_cdf) return nb_fail(ctx, NB_E_INVALID, "emitter_cdf missing");
@@ -172,6 +193,8 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->area_cdf, s->n_area_cdf, &d.area_cdf))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->media, s->n_media, &d.media))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->density, s->n_density, &d.density))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->textures, s->n_textures, &d.textures))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->texels, s->n_texels * 4, &d.texels))) return rc;
     d.n_media = s->n_media; d.ambient_medium = s->ambient_medium;
     d.n_shapes = s->n_shapes; d.n_bsdfs = s->n_bsdfs; d.n_emitters = s->n_emitters;
     d.envmap_emitter = envmap;

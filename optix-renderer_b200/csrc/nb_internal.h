@@ -40,6 +40,8 @@ struct NbDeviceScene {
     const float *emitter_cdf = nullptr, *area_cdf = nullptr;
     const nb_medium *media = nullptr;
     const float *density = nullptr;     /* voxels of heterogeneous media */
+    const nb_texture *textures = nullptr;
+    const float *texels = nullptr;      /* RGBA, 16-byte aligned */
     uint32_t n_shapes = 0, n_bsdfs = 0, n_emitters = 0, n_media = 0;
     int32_t envmap_emitter = -1, ambient_medium = -1;
     nb_camera camera;

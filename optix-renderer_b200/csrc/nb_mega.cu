@@ -106,7 +106,8 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
     }
     if ((max_depth && bounce >= max_depth) || sh.bsdf < 0) return false;
 
-    const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    nb_bsdf_resolve(sc, bsdf, its.uv);
     const f3 wi = its.sh.to_local(-ps.d);
     if (MIS) {                                                       /* path_mis.cpp:75-106 */
         const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
@@ -142,14 +143,15 @@ template <int INTEG, bool FLAT>
 __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any) {
     NbHit hit;
     ++n_closest;
-    if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) return mk3(0.f);
+    if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) return nb_env_radiance(sc, ps.d);   /* direct*.cpp: getEnvMap()->eval */
     nb_shape sh; NbIts its;
     nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
     f3 result = mk3(0.f);
     if (INTEG != NB_INTEGRATOR_DIRECT && sh.emitter >= 0)
         result += nb_area_eval(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
     if (sh.bsdf < 0) return result;
-    const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    nb_bsdf_resolve(sc, bsdf, its.uv);
     const float n_lights = (float) sc.n_emitters;
 
     if (INTEG == NB_INTEGRATOR_DIRECT) {                              /* direct.cpp:37-63 */
@@ -215,7 +217,8 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
                     if (pdf_mat + pdf_ems > NB_EPS) w_mat = pdf_mat / (pdf_mat + pdf_ems);
                 }
             }
-        }
+        } else if (INTEG == NB_INTEGRATOR_DIRECT_MATS)
+            result_mats = col * nb_env_radiance(sc, d2);                 /* direct_mats.cpp:60-69; in direct_mis.cpp:122-133 the weight stays 0 */
     }
     if (INTEG == NB_INTEGRATOR_DIRECT_MATS) return result + result_mats;
     return result + w_ems * result_ems + w_mat * result_mats;
@@ -307,7 +310,8 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
         }
     } else {
         if (sh.bsdf >= 0) {
-            const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+            nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+            nb_bsdf_resolve(sc, bsdf, its.uv);
             const f3 wi = its.sh.to_local(-ps.d);
             float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
             f3 lwo; bool discrete; float pdf;
@@ -415,8 +419,10 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
             if (active) {
                 NbHit hit;
                 ++n_closest;
-                if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) ended = true;
-                else ended = !nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
+                if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) {
+                    ps.Li += ps.thr * nb_env_radiance(sc, ps.d);       /* path_mis.cpp:35-43, path_mats.cpp:26-34 */
+                    ended = true;
+                } else ended = !nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
             }
             if (MIS && shadow) {
                 ++n_any;
@@ -437,6 +443,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 ++n_closest;
                 bool alive = nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit);
                 if (alive) alive = nb_vol_bounce<MIS, FLAT>(sc, tp.plan.max_depth, ps, medium, hit, n_closest);
+                else ps.Li += ps.thr * nb_env_radiance(sc, ps.d);      /* path_vol_mats.cpp:34-39 */
                 if (!alive) {
                     nb_film_put(film, ps.px, ps.py, ps.Li, stats);
                     active = false;
@@ -606,6 +613,7 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
                 bool alive = false;
                 shadow = false;
                 if (hit.slot != 0xffffffffu) alive = nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
+                else ps.Li += ps.thr * nb_env_radiance(sc, ps.d);
                 ending = !alive;
                 if (MIS && shadow) begin_walk(so.o, so.d, so.mint, so.maxt, true);
                 else if (alive) begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);

@@ -25,6 +25,45 @@ __global__ void nb_k_medium_probe(NbDeviceScene sc, int32_t medium, const float4
     out[i] = make_float4(dens, hit / (float) samples, hit > 0.f ? len / hit : 0.f, tr / (float) samples);
 }
 
+/* Emitter::sample on fixed (reference point, sample) pairs: the row of every emitter plugin */
+__global__ void nb_k_emitter_probe(NbDeviceScene sc, uint32_t emitter, const float *in, uint64_t n, float *out) {
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const f3 ref = mk3(in[5 * i], in[5 * i + 1], in[5 * i + 2]);
+    float2 s; s.x = in[5 * i + 3]; s.y = in[5 * i + 4];
+    const nb_emitter em = sc.emitters[emitter];
+    NbEmitterSample es;
+    const f3 v = nb_emitter_sample(sc, em, ref, s, es);
+    f3 e = mk3(0.f);
+    if (em.type == NB_EMITTER_ENVMAP) e = nb_env_eval(sc, em, es.wi);
+    else if (em.type == NB_EMITTER_POINT) e = v;
+    else e = v * es.pdf;
+    float *o = out + 12 * i;
+    o[0] = es.wi.x; o[1] = es.wi.y; o[2] = es.wi.z; o[3] = v.x; o[4] = v.y; o[5] = v.z;
+    o[6] = es.pdf; o[7] = es.ray_maxt; o[8] = e.x; o[9] = e.y; o[10] = e.z; o[11] = 0.f;
+}
+
+extern "C" int nb_emitter_probe(nb_ctx *ctx, uint32_t emitter, const float *in, uint64_t n, float *out) {
+    if (!ctx) return NB_E_INVALID;
+    if (!ctx->scene_ready) return nb_fail(ctx, NB_E_STATE, "nb_emitter_probe: upload a scene first");
+    if (emitter >= ctx->dev.n_emitters) return nb_fail(ctx, NB_E_INVALID, "nb_emitter_probe: emitter %u out of range", emitter);
+    if (n == 0) return NB_OK;
+    if (!in || !out) return nb_fail(ctx, NB_E_INVALID, "nb_emitter_probe: null argument");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    float *d_in = nullptr, *d_out = nullptr;
+    NB_CUDA(ctx, cudaMalloc((void **) &d_in, n * 20));
+    cudaError_t e = cudaMalloc((void **) &d_out, n * 48);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, in, n * 20, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) {
+        nb_k_emitter_probe<<<(unsigned) ((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->dev, emitter, d_in, n, d_out);
+        e = cudaMemcpyAsync(out, d_out, n * 48, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_emitter_probe: %s", cudaGetErrorString(e));
+    return NB_OK;
+}
+
 extern "C" int nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples, uint64_t seed, float *out) {
     if (!ctx) return NB_E_INVALID;
     if (!ctx->scene_ready) return nb_fail(ctx, NB_E_STATE, "nb_medium_probe: upload a scene first");

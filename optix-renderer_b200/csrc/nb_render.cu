@@ -53,10 +53,16 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
     uint32_t flags = __float_as_uint(s2.w);
     if (flags & (NB_FLAG_EMPTY | NB_FLAG_FINALIZE)) return false;
     const uint32_t slot = __float_as_uint(hit.w);
-    if (slot == 0xffffffffu) return false;  /* miss: no environment emitter in this backend yet */
     f3 Li = mk3(s0.x, s0.y, s0.z);
     const f3 o = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
     f3 thr = mk3(s1.x, s1.y, s1.z);
+    if (slot == 0xffffffffu) {              /* miss: Scene::getEnvMap()->eval (path_mis.cpp:35-43, path_mats.cpp:26-34) */
+        if (sc.envmap_emitter >= 0) {
+            Li += thr * nb_env_radiance(sc, d);
+            w.st0[p] = make_float4(Li.x, Li.y, Li.z, s0.w);
+        }
+        return false;
+    }
     float w_mats = s0.w;
     const float4 sl = __ldg(sc.slots + 3 * slot + 2);
     const uint32_t sid = __float_as_uint(sl.y) & NB_SLOT_SHAPE_MASK, prim = __float_as_uint(sl.z);
@@ -103,7 +109,8 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
         return false;
     }
 
-    const nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+    nb_bsdf_resolve(sc, bsdf, its.uv);
     const f3 wi = its.sh.to_local(-d);
     float w_ems = s2.z;
 

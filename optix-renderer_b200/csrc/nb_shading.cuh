@@ -3,6 +3,7 @@
 #pragma once
 #include "nb_internal.h"
 #include "nb_math.cuh"
+#include "nb_texture.cuh"
 
 struct NbIts {          /* Intersection, include/nori/shape.h:44-76 */
     f3 p;
@@ -214,6 +215,23 @@ __device__ __forceinline__ f3 nb_emitter_sample(const NbDeviceScene &sc, const n
         out.wi = normalize(pos - ref);
         out.pdf = 1.f;
         return mk3(em.radiance[0], em.radiance[1], em.radiance[2]) / dot(dlt, dlt);
+    }
+    if (em.type == NB_EMITTER_ENVMAP) {                           /* environmentmap.cpp:73-97 */
+        const nb_texture &t = sc.textures[em.shape];
+        f3 v;
+        if (t.width == 1 && t.height == 1) v = square_to_uniform_sphere(s);
+        else {
+            const uint32_t elem = nb_cdf_sample(sc.area_cdf + __float_as_uint(em.position[0]), t.width * t.height, s.x);
+            const float i = (float) (int) (elem / t.width) / (float) t.height, j = (float) (int) (elem % t.width) / (float) t.width;
+            v = nb_spherical_direction(j * NB_PI, i * 2.0f * NB_PI);
+        }
+        const f3 p = v * 1.f / NB_EPS;
+        const f3 dlt = p - ref;
+        out.wi = normalize(dlt);
+        out.ray_o = p; out.ray_d = -out.wi; out.ray_mint = NB_EPS; out.ray_maxt = length(dlt) - NB_EPS;
+        out.pdf = nb_env_pdf(sc, em, out.wi);
+        if (out.pdf < NB_EPS) return mk3(0.f);
+        return nb_env_eval(sc, em, out.wi) / out.pdf;
     }
     const nb_shape sh = sc.shapes[em.shape];
     f3 p, n;

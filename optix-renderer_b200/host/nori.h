@@ -151,6 +151,8 @@ public:
     Point3f getPoint3(const std::string &n, const Point3f &d) const { return has(n) ? getPoint3(n) : d; }
     Vector3f getVector3(const std::string &n) const { return get(n, EVector3, "vector").v3; }
     Vector3f getVector3(const std::string &n, const Vector3f &d) const { return has(n) ? getVector3(n) : d; }
+    Vector2f getVector2(const std::string &n, const Vector2f &d) const { return has(n) ? get(n, EVector2, "vector2").v2 : d; }
+    Point2f getPoint2(const std::string &n, const Point2f &d) const { return has(n) ? get(n, EPoint2, "point2").v2 : d; }
     Transform getTransform(const std::string &n) const { return get(n, ETransform, "transform").t; }
     Transform getTransform(const std::string &n, const Transform &d) const { return has(n) ? getTransform(n) : d; }
 private:
@@ -182,8 +184,12 @@ public:
     }
     virtual void setParent(NoriObject *) {}
     virtual void activate() {}
+    void setIdName(const std::string &name) { m_idname = name; }        /* object.h:182-183: the XML `name` attribute */
+    const std::string &getIdName() const { return m_idname; }
     virtual std::string toString() const = 0;
     static const char *classTypeName(EClassType t);
+private:
+    std::string m_idname;
 };
 
 class NoriObjectFactory {

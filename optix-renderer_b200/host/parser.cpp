@@ -170,8 +170,11 @@ struct Parser {
         if (currentIsObject) {
             std::string type = node.attr("type");
             if (tag == EScene && type.empty()) type = "scene";
-            /* like the reference (parser.cpp:207-209) objects may also carry a `name` attribute */
+            /* like the reference (parser.cpp:207-227) an object's `name` attribute reaches its constructor as the
+             * string property "name" and its parent through getIdName() */
+            props.setString("name", node.attr("name"));
             result = NoriObjectFactory::createInstance(type, props);
+            result->setIdName(node.attr("name"));
             if ((int) result->getClassType() != tag)
                 throw NoriException("Unexpectedly constructed an object of type <%s> (expected type <%s>): %s",
                                     NoriObject::classTypeName(result->getClassType()),

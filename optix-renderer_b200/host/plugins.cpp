@@ -15,32 +15,39 @@ std::string resolvePath(const std::string &rel) {
 }
 
 /* ---- BSDFs ------------------------------------------------------------------------------------- */
-class Diffuse : public BSDF {                       /* src/bsdf/diffuse.cpp:31-60: albedo default 0.5 */
+class Diffuse : public BSDF {                       /* src/bsdf/diffuse.cpp:31-91: constant albedo (default 0.5) or an "albedo" texture */
 public:
-    explicit Diffuse(const PropertyList &p) : m_albedo(p.getColor("albedo", Color3f(0.5f))) {}
+    explicit Diffuse(const PropertyList &p) : m_albedo(p.getColor("albedo", Color3f(0.5f))), m_hasConstant(p.has("albedo")) {}
+    ~Diffuse() override { delete m_texture; }
     void addChild(NoriObject *obj) override {
-        /* textured albedo (diffuse.cpp:62-91) has no kernel yet */
-        if (obj->getClassType() == ETexture) { m_textured = true; delete obj; return; }
-        BSDF::addChild(obj);
+        if (obj->getClassType() != ETexture) throw NoriException("Diffuse::addChild(<%s>) is not supported!", classTypeName(obj->getClassType()));
+        if (obj->getIdName() != "albedo") throw NoriException("The name of this texture does not match any field!");
+        if (m_texture || m_hasConstant) throw NoriException("There is already an albedo defined!");
+        m_texture = static_cast<Texture *>(obj);
     }
-    bool getB200MaterialData(nb_bsdf &o) const override {
-        if (m_textured) return false;
+    bool getB200MaterialData(nb_bsdf &o, FlatScene &flat) const override {
         memset(&o, 0, sizeof(o));
         o.type = NB_BSDF_DIFFUSE;
         for (int i = 0; i < 3; ++i) o.albedo[i] = m_albedo[i];
+        if (m_texture) {
+            const int t = m_texture->getB200Texture(flat);
+            if (t < 0) return false;
+            o.type |= (uint32_t) (t + 1) << 8;
+        }
         return true;
     }
     std::string toString() const override { return NoriException::format("Diffuse[albedo=[%f, %f, %f]]", m_albedo[0], m_albedo[1], m_albedo[2]); }
 private:
     Color3f m_albedo;
-    bool m_textured = false;
+    bool m_hasConstant;
+    Texture *m_texture = nullptr;
 };
 NORI_REGISTER_CLASS(Diffuse, "diffuse")
 
 class Mirror : public BSDF {                        /* src/bsdf/mirror.cpp */
 public:
     explicit Mirror(const PropertyList &) {}
-    bool getB200MaterialData(nb_bsdf &o) const override { memset(&o, 0, sizeof(o)); o.type = NB_BSDF_MIRROR; return true; }
+    bool getB200MaterialData(nb_bsdf &o, FlatScene &) const override { memset(&o, 0, sizeof(o)); o.type = NB_BSDF_MIRROR; return true; }
     std::string toString() const override { return "Mirror[]"; }
 };
 NORI_REGISTER_CLASS(Mirror, "mirror")
@@ -49,7 +56,7 @@ class Dielectric : public BSDF {                    /* src/bsdf/dielectric.cpp:2
 public:
     explicit Dielectric(const PropertyList &p)
         : m_intIOR(p.getFloat("intIOR", 1.5046f)), m_extIOR(p.getFloat("extIOR", 1.000277f)) {}
-    bool getB200MaterialData(nb_bsdf &o) const override {
+    bool getB200MaterialData(nb_bsdf &o, FlatScene &) const override {
         memset(&o, 0, sizeof(o));
         o.type = NB_BSDF_DIELECTRIC; o.int_ior = m_intIOR; o.ext_ior = m_extIOR;
         return true;
@@ -67,7 +74,7 @@ public:
           m_extIOR(p.getFloat("extIOR", 1.000277f)), m_kd(p.getColor("kd", Color3f(0.5f))) {
         m_ks = 1 - m_kd.maxCoeff();
     }
-    bool getB200MaterialData(nb_bsdf &o) const override {
+    bool getB200MaterialData(nb_bsdf &o, FlatScene &) const override {
         memset(&o, 0, sizeof(o));
         o.type = NB_BSDF_MICROFACET; o.alpha = m_alpha; o.int_ior = m_intIOR; o.ext_ior = m_extIOR; o.ks = m_ks;
         for (int i = 0; i < 3; ++i) o.albedo[i] = m_kd[i];
@@ -86,7 +93,7 @@ class UnsupportedBSDF : public BSDF {
 public:
     explicit UnsupportedBSDF(const PropertyList &) {}
     void addChild(NoriObject *obj) override { delete obj; }
-    bool getB200MaterialData(nb_bsdf &) const override { return false; }
+    bool getB200MaterialData(nb_bsdf &, FlatScene &) const override { return false; }
     std::string toString() const override { return "UnsupportedBSDF[]"; }
 };
 NORI_REGISTER_CLASS(UnsupportedBSDF, "disney")
@@ -95,7 +102,7 @@ NORI_REGISTER_CLASS(UnsupportedBSDF, "disney")
 class AreaEmitter : public Emitter {                /* src/emitters/arealight.cpp:27-33 */
 public:
     explicit AreaEmitter(const PropertyList &p) { m_radiance = p.getColor("radiance"); lightProb = p.getFloat("lightWeight", 1.f); }
-    bool getB200EmitterData(nb_emitter &o) const override {
+    bool getB200EmitterData(nb_emitter &o, FlatScene &) const override {
         memset(&o, 0, sizeof(o));
         o.type = NB_EMITTER_AREA; o.shape = -1;
         for (int i = 0; i < 3; ++i) o.radiance[i] = m_radiance[i];
@@ -111,7 +118,7 @@ public:
         m_power = p.getColor("power"); m_position = p.getPoint3("position"); lightProb = p.getFloat("lightWeight", 1.f);
         m_radiance = m_power / (float) (4 * M_PI);                       /* pointlight.cpp:44 */
     }
-    bool getB200EmitterData(nb_emitter &o) const override {
+    bool getB200EmitterData(nb_emitter &o, FlatScene &) const override {
         memset(&o, 0, sizeof(o));
         o.type = NB_EMITTER_POINT; o.shape = -1;
         for (int i = 0; i < 3; ++i) { o.radiance[i] = m_radiance[i]; o.position[i] = m_position[i]; }

@@ -13,12 +13,24 @@ void setResolveRoot(const std::string &dir);
 class Shape;
 struct FlatScene;
 
+/* include/nori/texture.h:35-78, Texture<Color3f> */
+class Texture : public NoriObject {
+public:
+    EClassType getClassType() const override { return ETexture; }
+    virtual Color3f eval(const Point2f &uv) const = 0;
+    virtual unsigned getWidth() const { return 1; }
+    virtual unsigned getHeight() const { return 1; }
+    /* replaces getOptixTexture (texture.h:75): appends the record (and texels) to `flat`, returns its
+     * index or -1 when the texture has no kernel */
+    virtual int getB200Texture(FlatScene &flat) const = 0;
+};
+
 /* include/nori/bsdf.h:82-123 */
 class BSDF : public NoriObject {
 public:
     EClassType getClassType() const override { return EBSDF; }
     /* replaces getOptixMaterialData (bsdf.h:122); false = no kernel for this plugin */
-    virtual bool getB200MaterialData(nb_bsdf &out) const = 0;
+    virtual bool getB200MaterialData(nb_bsdf &out, FlatScene &flat) const = 0;
 };
 
 /* include/nori/emitter.h:72-166 */
@@ -28,7 +40,8 @@ public:
     void setShape(Shape *s) { m_shape = s; }
     bool hasShape() const { return m_shape != nullptr; }
     const Shape *getShape() const { return m_shape; }
-    virtual bool getB200EmitterData(nb_emitter &out) const = 0;     /* replaces getOptixEmitterData (emitter.h:159) */
+    virtual bool getB200EmitterData(nb_emitter &out, FlatScene &flat) const = 0;     /* replaces getOptixEmitterData (emitter.h:159) */
+    virtual bool isEnvMap() const { return false; }
     float lightProb = 1.f;                                            /* emitter.h:151 */
 protected:
     Shape *m_shape = nullptr;
@@ -149,6 +162,8 @@ struct FlatScene {
     std::vector<nb_emitter> emitters;
     std::vector<nb_medium> media;
     std::vector<float> density;                         /* voxel arrays of heterogeneous media */
+    std::vector<nb_texture> textures;
+    std::vector<float> texels;                          /* RGBA */
     int32_t ambient_medium = -1;
     nb_camera camera;
     nb_render_params render;

@@ -69,7 +69,7 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
         }
     for (Emitter *e : m_emitters) {
         nb_emitter rec;
-        if (!e->getB200EmitterData(rec)) return fail("emitter '" + e->toString() + "' has no GPU kernel");
+        if (!e->getB200EmitterData(rec, out)) return fail("emitter '" + e->toString() + "' has no GPU kernel");
         out.emitters.push_back(rec);
     }
     for (size_t i = 0; i < m_shapes.size(); ++i) {
@@ -79,7 +79,7 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
         s->getB200Shape(rec, out);
         if (s->getBSDF()) {
             nb_bsdf b;
-            if (!s->getBSDF()->getB200MaterialData(b)) return fail("bsdf '" + s->getBSDF()->toString() + "' has no GPU kernel");
+            if (!s->getBSDF()->getB200MaterialData(b, out)) return fail("bsdf '" + s->getBSDF()->toString() + "' has no GPU kernel");
             rec.bsdf = (int32_t) out.bsdfs.size();
             out.bsdfs.push_back(b);
         }
@@ -141,6 +141,8 @@ nb_scene_desc FlatScene::desc() const {
     d.n_media = (uint32_t) media.size(); d.media = media.empty() ? nullptr : media.data();
     d.ambient_medium = ambient_medium;
     d.n_density = density.size(); d.density = density.empty() ? nullptr : density.data();
+    d.n_textures = (uint32_t) textures.size(); d.textures = textures.empty() ? nullptr : textures.data();
+    d.n_texels = texels.size() / 4; d.texels = texels.empty() ? nullptr : texels.data();
     return d;
 }
 
@@ -161,6 +163,8 @@ void FlatScene::writeNbs(const std::string &path) const {
         secs.push_back({ "ambient", 4, &ambient_medium, 1 });
         if (!density.empty()) secs.push_back({ "density", 4, density.data(), density.size() });
     }
+    if (!textures.empty()) secs.push_back({ "textures", sizeof(nb_texture), textures.data(), textures.size() });
+    if (!texels.empty()) secs.push_back({ "texels", 4, texels.data(), texels.size() });
     secs.push_back({ "camera", sizeof(nb_camera), &camera, 1 });
     secs.push_back({ "render", sizeof(nb_render_params), &render, 1 });
     secs.push_back({ "spp", 4, &spp, 1 });

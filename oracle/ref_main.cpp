@@ -685,6 +685,39 @@ static int modeMedium(int argc, char **argv) {
     return 0;
 }
 
+/* ---- emitter: Emitter::sample / pdf / eval on fixed (reference point, 2D sample) pairs ----------
+ * in.bin: n x 5 f32 (ref.xyz, sample.xy). out.bin: n x 12 f32: lRec.wi, the returned value
+ * (radiance / pdf), lRec.pdf, shadowRay.maxt, emitter->eval(lRec) after sampling, 0. */
+static int modeEmitter(int argc, char **argv) {
+    if (argc < 5) return 2;
+    auto kv = parseKv(argc, argv, 5);
+    const size_t index = kv.count("index") ? (size_t) std::stoi(kv["index"]) : 0;
+    LoadedScene ls = loadScene(argv[2]);
+    const std::vector<Emitter *> &lights = ls.render->getLights();
+    if (index >= lights.size()) throw NoriException("scene has %d emitters", (int) lights.size());
+    const Emitter *em = lights[index];
+    FILE *f = fopen(argv[3], "rb");
+    if (!f) throw NoriException("cannot read %s", argv[3]);
+    fseek(f, 0, SEEK_END); const size_t n = (size_t) ftell(f) / 20; fseek(f, 0, SEEK_SET);
+    std::vector<float> in(n * 5), out(n * 12, 0.f);
+    if (fread(in.data(), 20, n, f) != n) throw NoriException("short read on %s", argv[3]);
+    fclose(f);
+    for (size_t i = 0; i < n; ++i) {
+        EmitterQueryRecord lRec(Point3f(in[i * 5], in[i * 5 + 1], in[i * 5 + 2]));
+        const Color3f v = em->sample(lRec, Point2f(in[i * 5 + 3], in[i * 5 + 4]));
+        const Color3f e = em->eval(lRec);
+        float *o = &out[i * 12];
+        o[0] = lRec.wi.x(); o[1] = lRec.wi.y(); o[2] = lRec.wi.z(); o[3] = v(0); o[4] = v(1); o[5] = v(2);
+        o[6] = lRec.pdf; o[7] = lRec.shadowRay.maxt; o[8] = e(0); o[9] = e(1); o[10] = e(2);
+    }
+    f = fopen(argv[4], "wb");
+    if (!f) throw NoriException("cannot write %s", argv[4]);
+    fwrite(out.data(), 48, n, f);
+    fclose(f);
+    printf("{\"mode\": \"emitter\", \"index\": %zu, \"emitters\": %zu, \"records\": %zu}\n", index, lights.size(), n);
+    return 0;
+}
+
 static int usage() {
     fprintf(stderr,
         "nori_ref — headless harness around the reference CPU renderer (test infrastructure)\n"
@@ -696,6 +729,7 @@ static int usage() {
         "  nori_ref test    test.xml\n"
         "  nori_ref ttest   test.xml [samples=N]   (scene-mode t-tests, restated: see modeTTestScenes)\n"
         "  nori_ref rng     n\n"
+        "  nori_ref emitter scene.xml in.bin out.bin [index=K]      (Emitter::sample/pdf/eval probes)\n"
         "  nori_ref medium  scene.xml rays.bin out.bin [samples=K]   (free path / transmittance / density probes)\n");
     return 2;
 }
@@ -714,6 +748,7 @@ int main(int argc, char **argv) {
         else if (mode == "ttest") rc = modeTTestScenes(argc, argv);
         else if (mode == "rng") rc = modeRng(argc, argv);
         else if (mode == "medium") rc = modeMedium(argc, argv);
+        else if (mode == "emitter") rc = modeEmitter(argc, argv);
         if (rc == 2) return usage();
         return rc;
     } catch (const std::exception &e) {
