@@ -198,6 +198,8 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     d.n_media = s->n_media; d.ambient_medium = s->ambient_medium;
     d.n_shapes = s->n_shapes; d.n_bsdfs = s->n_bsdfs; d.n_emitters = s->n_emitters;
     d.envmap_emitter = envmap;
+    d.ext = (envmap >= 0 || s->n_textures > 0) ? 1u : 0u;
+    for (uint32_t i = 0; i < s->n_media; ++i) if (s->media[i].type == NB_MEDIUM_HETEROGENEOUS) d.ext = 1u;
     d.camera = s->camera;
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->scene_ready = true;

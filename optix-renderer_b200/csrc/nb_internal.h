@@ -31,6 +31,7 @@ struct NbDeviceScene {
     const float4 *slots = nullptr;      /* 3 per primitive slot */
     uint32_t n_nodes = 0, n_slots = 0;
     uint32_t flat = 0;                  /* queries scan the slots instead of walking the tree (nb_trace.cuh) */
+    uint32_t ext = 0;                   /* scene uses textures, an environment map or a heterogeneous medium: the EXT kernel variants render it */
     /* shading data */
     const nb_shape *shapes = nullptr;
     const float *positions = nullptr, *normals = nullptr, *uvs = nullptr, *tangents = nullptr, *bitangents = nullptr;

@@ -74,7 +74,7 @@ __device__ __forceinline__ bool nb_closest(const NbDeviceScene &sc, f3 o, f3 d, 
 
 /* One bounce of path_mis / path_mats for a path whose closest hit just arrived. Returns false
  * when the path ended at this vertex; `shadow` is set when an NEE ray must be resolved. */
-template <bool MIS>
+template <bool MIS, bool EXT>
 __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t max_depth, NbPathRegs &ps, const NbHit &hit,
                                                bool &shadow, NbShadowRay &so) {
     nb_shape sh; NbIts its;
@@ -107,14 +107,13 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
     if ((max_depth && bounce >= max_depth) || sh.bsdf < 0) return false;
 
     nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
-    nb_bsdf_resolve(sc, bsdf, its.uv);
+    nb_bsdf_resolve<EXT>(sc, bsdf, its.uv);
     const f3 wi = its.sh.to_local(-ps.d);
     if (MIS) {                                                       /* path_mis.cpp:75-106 */
         const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
-        const nb_emitter em = sc.emitters[ei];
         float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
         NbEmitterSample es;
-        const f3 ems_col = nb_emitter_sample(sc, em, its.p, s, es);
+        const f3 ems_col = nb_emitter_sample<EXT>(sc, ei, its.p, s, es);
         if (!is_zero(ems_col, NB_EPS)) {
             const f3 we = its.sh.to_local(es.wi);
             const f3 C = ps.thr * (ems_col * we.z * nb_bsdf_eval(bsdf, wi, we) * n_lights);
@@ -139,11 +138,11 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
 }
 
 /* The depth-1 integrators, one whole sample. Returns Li. */
-template <int INTEG, bool FLAT>
+template <int INTEG, bool FLAT, bool EXT>
 __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any) {
     NbHit hit;
     ++n_closest;
-    if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) return nb_env_radiance(sc, ps.d);   /* direct*.cpp: getEnvMap()->eval */
+    if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) return nb_env_radiance<EXT>(sc, ps.d);   /* direct*.cpp: getEnvMap()->eval */
     nb_shape sh; NbIts its;
     nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
     f3 result = mk3(0.f);
@@ -151,7 +150,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
         result += nb_area_eval(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
     if (sh.bsdf < 0) return result;
     nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
-    nb_bsdf_resolve(sc, bsdf, its.uv);
+    nb_bsdf_resolve<EXT>(sc, bsdf, its.uv);
     const float n_lights = (float) sc.n_emitters;
 
     if (INTEG == NB_INTEGRATOR_DIRECT) {                              /* direct.cpp:37-63 */
@@ -159,7 +158,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
         for (uint32_t l = 0; l < sc.n_emitters; ++l) {
             float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
             NbEmitterSample es;
-            const f3 li = nb_emitter_sample(sc, sc.emitters[l], its.p, s, es);
+            const f3 li = nb_emitter_sample<EXT>(sc, l, its.p, s, es);
             const f3 wi = its.sh.to_local(es.wi);
             ++n_any;
             if (nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
@@ -173,7 +172,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
         for (uint32_t l = 0; l < sc.n_emitters; ++l) {
             float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
             NbEmitterSample es;
-            const f3 li = nb_emitter_sample(sc, sc.emitters[l], its.p, s, es);
+            const f3 li = nb_emitter_sample<EXT>(sc, l, its.p, s, es);
             if (is_zero(li, NB_EPS)) continue;
             ++n_any;
             if (nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
@@ -188,7 +187,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
         const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
         float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
         NbEmitterSample es;
-        const f3 li = nb_emitter_sample(sc, sc.emitters[ei], its.p, s, es);
+        const f3 li = nb_emitter_sample<EXT>(sc, ei, its.p, s, es);
         if (!is_zero(li, NB_EPS)) {
             ++n_any;
             if (!nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) {
@@ -218,7 +217,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
                 }
             }
         } else if (INTEG == NB_INTEGRATOR_DIRECT_MATS)
-            result_mats = col * nb_env_radiance(sc, d2);                 /* direct_mats.cpp:60-69; in direct_mis.cpp:122-133 the weight stays 0 */
+            result_mats = col * nb_env_radiance<EXT>(sc, d2);                 /* direct_mats.cpp:60-69; in direct_mis.cpp:122-133 the weight stays 0 */
     }
     if (INTEG == NB_INTEGRATOR_DIRECT_MATS) return result + result_mats;
     return result + w_ems * result_ems + w_mat * result_mats;
@@ -227,7 +226,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
 /* PathVolMISIntegrator::sampleEmitter + traceShadowray (path_vol_mis.cpp:26-104). `its`/`sh` are
  * the SURFACE hit of the current ray even when the interaction is inside the medium (the
  * reference passes `its` in both cases); exactly one of bsdf / phase is non-null. */
-template <bool FLAT>
+template <bool FLAT, bool EXT>
 __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbPathRegs &ps, int32_t medium, const NbIts &its,
                                                     const nb_shape &sh, uint32_t measure, const nb_bsdf *bsdf,
                                                     const nb_medium *phase, uint32_t &n_closest) {
@@ -236,7 +235,7 @@ __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbP
     const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
     float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
     NbEmitterSample es;
-    const f3 Le = nb_emitter_sample(sc, sc.emitters[ei], its.p, s, es) * n_lights;
+    const f3 Le = nb_emitter_sample<EXT>(sc, ei, its.p, s, es) * n_lights;
     const float pdf_em = es.pdf / n_lights;
     if (is_black(Le)) return mk3(0.f);                                   /* result would be 0; the shadow walk draws nothing */
     int32_t sm = dot(ps.d, es.ray_d) > 0.f ? nb_medium_behind(sc, sh, its.geo_n, es.ray_d) : medium;
@@ -250,7 +249,7 @@ __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbP
         nb_shape sh2; NbIts its2;
         nb_hit_info(sc, h, so, es.ray_d, sh2, its2);
         if (sh2.bsdf >= 0) return mk3(0.f);
-        tr = tr * nb_transmittance(sc, sm, so, its2.p, ps.rng);
+        tr = tr * nb_transmittance<EXT>(sc, sm, so, its2.p, ps.rng);
         sm = nb_medium_behind(sc, sh2, its2.geo_n, es.ray_d);
         so = its2.p;
         smaxt -= h.t;
@@ -270,15 +269,15 @@ __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbP
 
 /* One loop iteration of path_vol_mats.cpp:32-119 / path_vol_mis.cpp:124-229 after the closest
  * hit of the current ray arrived. Returns false when the path ended. */
-template <bool MIS, bool FLAT>
+template <bool MIS, bool FLAT, bool EXT>
 __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t max_depth, NbPathRegs &ps, int32_t &medium,
                                               const NbHit &hit, uint32_t &n_closest) {
     nb_shape sh; NbIts its;
     nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
-    const float tm = nb_free_path(sc, medium, ps.o, ps.d, ps.rng);
+    const float tm = nb_free_path<EXT>(sc, medium, ps.o, ps.d, ps.rng);
     const bool mi = tm < hit.t;                                          /* isMediumInteraction */
     const f3 p = mi ? ps.o + ps.d * tm : its.p;
-    ps.thr = ps.thr * nb_transmittance(sc, medium, ps.o, p, ps.rng);
+    ps.thr = ps.thr * nb_transmittance<EXT>(sc, medium, ps.o, p, ps.rng);
     uint32_t measure = (ps.flags >> NB_MEASURE_SHIFT) & 3u;
     /* captured emission; volume emitters have no kernel (the host loader refuses them) */
     if (!mi && sh.emitter >= 0) {
@@ -306,12 +305,12 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
         if (MIS) {
             ps.pdfmat = nb_phase_pdf(med, pwo);
             measure = NB_MEASURE_SOLID_ANGLE;
-            ps.Li += nb_vol_sample_emitter<FLAT>(sc, ps, medium, its, sh, measure, nullptr, &med, n_closest);
+            ps.Li += nb_vol_sample_emitter<FLAT, EXT>(sc, ps, medium, its, sh, measure, nullptr, &med, n_closest);
         }
     } else {
         if (sh.bsdf >= 0) {
             nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
-            nb_bsdf_resolve(sc, bsdf, its.uv);
+            nb_bsdf_resolve<EXT>(sc, bsdf, its.uv);
             const f3 wi = its.sh.to_local(-ps.d);
             float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
             f3 lwo; bool discrete; float pdf;
@@ -323,7 +322,7 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
                 measure = discrete ? NB_MEASURE_DISCRETE
                         : (bsdf.type == NB_BSDF_DIFFUSE && wi.z > 0.f) ? NB_MEASURE_SOLID_ANGLE : NB_MEASURE_UNKNOWN;
                 ps.pdfmat = pdf;
-                ps.Li += nb_vol_sample_emitter<FLAT>(sc, ps, medium, its, sh, measure, &bsdf, nullptr, n_closest);
+                ps.Li += nb_vol_sample_emitter<FLAT, EXT>(sc, ps, medium, its, sh, measure, &bsdf, nullptr, n_closest);
             }
             ps.thr = ps.thr * col;
         }
@@ -382,8 +381,15 @@ __device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan
 }
 
 /* ---- K_tile ---------------------------------------------------------------------------------- */
-template <int INTEG, bool FLAT>
-__global__ void __launch_bounds__(NB_TILE_THREADS, NB_TILE_MIN_BLOCKS)
+/* the volume integrators with heterogeneous media carry the 27-tap stencil and two tracking loops;
+ * measured on the fluid scene (B200): 6 CTAs/SM at 80 registers with spills beat 4 CTAs/SM at 128
+ * registers (699 vs 675 M samples/s path_vol_mats, 146 vs 130 path_vol_mis) */
+#ifndef NB_TILE_MIN_BLOCKS_HETEROG
+#define NB_TILE_MIN_BLOCKS_HETEROG NB_TILE_MIN_BLOCKS
+#endif
+template <int INTEG, bool FLAT, bool EXT>
+__global__ void __launch_bounds__(NB_TILE_THREADS, (EXT && (INTEG == NB_INTEGRATOR_PATH_VOL_MIS || INTEG == NB_INTEGRATOR_PATH_VOL_MATS))
+                                                       ? NB_TILE_MIN_BLOCKS_HETEROG : NB_TILE_MIN_BLOCKS)
 nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     constexpr bool PATH = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_MATS;
     constexpr bool VOL = INTEG == NB_INTEGRATOR_PATH_VOL_MIS || INTEG == NB_INTEGRATOR_PATH_VOL_MATS;
@@ -420,9 +426,9 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 NbHit hit;
                 ++n_closest;
                 if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) {
-                    ps.Li += ps.thr * nb_env_radiance(sc, ps.d);       /* path_mis.cpp:35-43, path_mats.cpp:26-34 */
+                    ps.Li += ps.thr * nb_env_radiance<EXT>(sc, ps.d);       /* path_mis.cpp:35-43, path_mats.cpp:26-34 */
                     ended = true;
-                } else ended = !nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
+                } else ended = !nb_path_bounce<MIS, EXT>(sc, tp.plan.max_depth, ps, hit, shadow, so);
             }
             if (MIS && shadow) {
                 ++n_any;
@@ -442,15 +448,15 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 NbHit hit;
                 ++n_closest;
                 bool alive = nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit);
-                if (alive) alive = nb_vol_bounce<MIS, FLAT>(sc, tp.plan.max_depth, ps, medium, hit, n_closest);
-                else ps.Li += ps.thr * nb_env_radiance(sc, ps.d);      /* path_vol_mats.cpp:34-39 */
+                if (alive) alive = nb_vol_bounce<MIS, FLAT, EXT>(sc, tp.plan.max_depth, ps, medium, hit, n_closest);
+                else ps.Li += ps.thr * nb_env_radiance<EXT>(sc, ps.d);      /* path_vol_mats.cpp:34-39 */
                 if (!alive) {
                     nb_film_put(film, ps.px, ps.py, ps.Li, stats);
                     active = false;
                 }
             }
         } else if (active) {
-            const f3 Li = nb_direct_sample<INTEG, FLAT>(sc, ps, n_closest, n_any);
+            const f3 Li = nb_direct_sample<INTEG, FLAT, EXT>(sc, ps, n_closest, n_any);
             nb_film_put(film, ps.px, ps.py, Li, stats);
             active = false;
         }
@@ -495,7 +501,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
 #endif
 enum { NB_PH_IDLE = 0, NB_PH_REGEN = 1, NB_PH_NODE = 2, NB_PH_LEAF = 3, NB_PH_TDONE = 4, NB_PH_SHADE = 5 };
 
-template <bool MIS>
+template <bool MIS, bool EXT>
 __global__ void __launch_bounds__(NB_TILE_THREADS, NB_WALK_MIN_BLOCKS)
 nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
@@ -612,8 +618,8 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
             if (phase == NB_PH_SHADE) {
                 bool alive = false;
                 shadow = false;
-                if (hit.slot != 0xffffffffu) alive = nb_path_bounce<MIS>(sc, tp.plan.max_depth, ps, hit, shadow, so);
-                else ps.Li += ps.thr * nb_env_radiance(sc, ps.d);
+                if (hit.slot != 0xffffffffu) alive = nb_path_bounce<MIS, EXT>(sc, tp.plan.max_depth, ps, hit, shadow, so);
+                else ps.Li += ps.thr * nb_env_radiance<EXT>(sc, ps.d);
                 ending = !alive;
                 if (MIS && shadow) begin_walk(so.o, so.d, so.mint, so.maxt, true);
                 else if (alive) begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
@@ -633,26 +639,26 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
     }
 }
 
-template <bool MIS>
+template <bool MIS, bool EXT>
 static cudaError_t nb_tile_launch_walk(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
                                        unsigned long long *stats, int sm_count, cudaStream_t stream) {
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile_walk<MIS>, NB_TILE_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile_walk<MIS, EXT>, NB_TILE_THREADS, 0);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
     uint64_t blocks = (uint64_t) sm_count * per_sm;
     const uint64_t blocks_useful = ((uint64_t) tp.n_items + NB_TILE_THREADS / 32 - 1) / (NB_TILE_THREADS / 32);
     if (blocks > blocks_useful) blocks = blocks_useful;
     if (blocks < 1) blocks = 1;
-    nb_k_tile_walk<MIS><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
+    nb_k_tile_walk<MIS, EXT><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
     return cudaGetLastError();
 }
 
-template <int INTEG, bool FLAT>
+template <int INTEG, bool FLAT, bool EXT>
 static cudaError_t nb_tile_launch_flat(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
                                     unsigned long long *stats, int sm_count, cudaStream_t stream) {
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile<INTEG, FLAT>, NB_TILE_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile<INTEG, FLAT, EXT>, NB_TILE_THREADS, 0);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
     const uint64_t warps_wanted = ((uint64_t) tp.n_items + 0) ;
@@ -660,15 +666,18 @@ static cudaError_t nb_tile_launch_flat(const NbDeviceScene &sc, const NbFilm &fi
     const uint64_t blocks_useful = (warps_wanted + NB_TILE_THREADS / 32 - 1) / (NB_TILE_THREADS / 32);
     if (blocks > blocks_useful) blocks = blocks_useful;
     if (blocks < 1) blocks = 1;
-    nb_k_tile<INTEG, FLAT><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
+    nb_k_tile<INTEG, FLAT, EXT><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
     return cudaGetLastError();
 }
 
 template <int INTEG>
 static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
                                     unsigned long long *stats, int sm_count, cudaStream_t stream) {
-    return sc.flat ? nb_tile_launch_flat<INTEG, true>(sc, film, tp, item_counter, stats, sm_count, stream)
-                   : nb_tile_launch_flat<INTEG, false>(sc, film, tp, item_counter, stats, sm_count, stream);
+    if (sc.ext)
+        return sc.flat ? nb_tile_launch_flat<INTEG, true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
+                       : nb_tile_launch_flat<INTEG, false, true>(sc, film, tp, item_counter, stats, sm_count, stream);
+    return sc.flat ? nb_tile_launch_flat<INTEG, true, false>(sc, film, tp, item_counter, stats, sm_count, stream)
+                   : nb_tile_launch_flat<INTEG, false, false>(sc, film, tp, item_counter, stats, sm_count, stream);
 }
 
 /* Host entry used by nb_render_subframe. `passes` sample passes over the image, pass k drawing
@@ -692,8 +701,12 @@ cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const Nb
     cudaError_t e = cudaMemsetAsync(item_counter, 0, sizeof(uint32_t), stream);
     if (e != cudaSuccess) return e;
     if (!sc.flat && walk) {
-        if (integrator == NB_INTEGRATOR_PATH_MIS) return nb_tile_launch_walk<true>(sc, film, tp, item_counter, stats, sm_count, stream);
-        if (integrator == NB_INTEGRATOR_PATH_MATS) return nb_tile_launch_walk<false>(sc, film, tp, item_counter, stats, sm_count, stream);
+        if (integrator == NB_INTEGRATOR_PATH_MIS)
+            return sc.ext ? nb_tile_launch_walk<true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
+                          : nb_tile_launch_walk<true, false>(sc, film, tp, item_counter, stats, sm_count, stream);
+        if (integrator == NB_INTEGRATOR_PATH_MATS)
+            return sc.ext ? nb_tile_launch_walk<false, true>(sc, film, tp, item_counter, stats, sm_count, stream)
+                          : nb_tile_launch_walk<false, false>(sc, film, tp, item_counter, stats, sm_count, stream);
     }
     switch (integrator) {
         case NB_INTEGRATOR_PATH_MIS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);

@@ -14,7 +14,7 @@ __global__ void nb_k_medium_probe(NbDeviceScene sc, int32_t medium, const float4
     const nb_medium &m = sc.media[medium];
     NbRng rng; rng.seed(seed, i);
     float dens = 0.f;
-    if (m.type == NB_MEDIUM_HETEROGENEOUS) dens = nb_grid_density(sc, m, nb_grid_point(m, o));
+    if (m.type == NB_MEDIUM_HETEROGENEOUS) dens = nb_grid_density(sc.density, m, nb_grid_point(m, o));
     float hit = 0.f, len = 0.f, tr = 0.f;
     const f3 to = o + d * maxt;
     for (uint32_t k = 0; k < samples; ++k) {
@@ -33,9 +33,9 @@ __global__ void nb_k_emitter_probe(NbDeviceScene sc, uint32_t emitter, const flo
     float2 s; s.x = in[5 * i + 3]; s.y = in[5 * i + 4];
     const nb_emitter em = sc.emitters[emitter];
     NbEmitterSample es;
-    const f3 v = nb_emitter_sample(sc, em, ref, s, es);
+    const f3 v = nb_emitter_sample(sc, emitter, ref, s, es);
     f3 e = mk3(0.f);
-    if (em.type == NB_EMITTER_ENVMAP) e = nb_env_eval(sc, em, es.wi);
+    if (em.type == NB_EMITTER_ENVMAP) e = nb_env_eval(sc, emitter, es.wi);
     else if (em.type == NB_EMITTER_POINT) e = v;
     else e = v * es.pdf;
     float *o = out + 12 * i;

@@ -116,10 +116,9 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
 
     if (MIS) {                                                       /* path_mis.cpp:75-106 */
         const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, rng.next_float());
-        const nb_emitter em = sc.emitters[ei];
         float2 s; s.x = rng.next_float(); s.y = rng.next_float();
         NbEmitterSample es;
-        const f3 ems_col = nb_emitter_sample(sc, em, its.p, s, es);
+        const f3 ems_col = nb_emitter_sample(sc, ei, its.p, s, es);
         if (!is_zero(ems_col, NB_EPS)) {
             const f3 we = its.sh.to_local(es.wi);
             const f3 f = nb_bsdf_eval(bsdf, wi, we);

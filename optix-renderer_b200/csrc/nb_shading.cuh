@@ -203,10 +203,32 @@ __device__ __forceinline__ uint32_t nb_cdf_sample(const float *cdf, uint32_t n_e
     return i < n_entries - 1 ? i : n_entries - 1;
 }
 
+/* EnvMap::sample (environmentmap.cpp:73-97) */
+__device__ __forceinline__ f3 nb_env_sample(const NbDeviceScene &sc, const nb_emitter *emp, f3 ref, float2 s, NbEmitterSample &out) {
+    const nb_texture &t = sc.textures[emp->shape];
+    f3 v;
+    if (t.width == 1 && t.height == 1) v = square_to_uniform_sphere(s);
+    else {
+        const uint32_t elem = nb_cdf_sample(sc.area_cdf + __float_as_uint(emp->position[0]), t.width * t.height, s.x);
+        const float i = (float) (int) (elem / t.width) / (float) t.height, j = (float) (int) (elem % t.width) / (float) t.width;
+        v = nb_spherical_direction(j * NB_PI, i * 2.0f * NB_PI);
+    }
+    const f3 p = v * 1.f / NB_EPS;
+    const f3 dlt = p - ref;
+    out.wi = normalize(dlt);
+    out.ray_o = p; out.ray_d = -out.wi; out.ray_mint = NB_EPS; out.ray_maxt = length(dlt) - NB_EPS;
+    const float4 ep = nb_env_eval_pdf(sc.textures, sc.texels, emp, out.wi.x, out.wi.y, out.wi.z);
+    out.pdf = ep.w;
+    if (out.pdf < NB_EPS) return mk3(0.f);
+    return mk3(ep.x, ep.y, ep.z) / out.pdf;
+}
+
 /* Emitter::sample for area (arealight.cpp:75-103 -> mesh.cpp:50-71 / sphere.cpp:126-132) and
  * point lights (pointlight.cpp:47-63). Returns radiance / pdf. */
-__device__ __forceinline__ f3 nb_emitter_sample(const NbDeviceScene &sc, const nb_emitter &em, f3 ref, float2 s,
+template <bool EXT = true>
+__device__ __forceinline__ f3 nb_emitter_sample(const NbDeviceScene &sc, uint32_t emitter, f3 ref, float2 s,
                                                 NbEmitterSample &out) {
+    const nb_emitter em = sc.emitters[emitter];
     if (em.type == NB_EMITTER_POINT) {
         const f3 pos = mk3(em.position[0], em.position[1], em.position[2]);
         const f3 dlt = ref - pos;
@@ -216,23 +238,7 @@ __device__ __forceinline__ f3 nb_emitter_sample(const NbDeviceScene &sc, const n
         out.pdf = 1.f;
         return mk3(em.radiance[0], em.radiance[1], em.radiance[2]) / dot(dlt, dlt);
     }
-    if (em.type == NB_EMITTER_ENVMAP) {                           /* environmentmap.cpp:73-97 */
-        const nb_texture &t = sc.textures[em.shape];
-        f3 v;
-        if (t.width == 1 && t.height == 1) v = square_to_uniform_sphere(s);
-        else {
-            const uint32_t elem = nb_cdf_sample(sc.area_cdf + __float_as_uint(em.position[0]), t.width * t.height, s.x);
-            const float i = (float) (int) (elem / t.width) / (float) t.height, j = (float) (int) (elem % t.width) / (float) t.width;
-            v = nb_spherical_direction(j * NB_PI, i * 2.0f * NB_PI);
-        }
-        const f3 p = v * 1.f / NB_EPS;
-        const f3 dlt = p - ref;
-        out.wi = normalize(dlt);
-        out.ray_o = p; out.ray_d = -out.wi; out.ray_mint = NB_EPS; out.ray_maxt = length(dlt) - NB_EPS;
-        out.pdf = nb_env_pdf(sc, em, out.wi);
-        if (out.pdf < NB_EPS) return mk3(0.f);
-        return nb_env_eval(sc, em, out.wi) / out.pdf;
-    }
+    if (EXT && em.type == NB_EMITTER_ENVMAP) return nb_env_sample(sc, sc.emitters + emitter, ref, s, out);
     const nb_shape sh = sc.shapes[em.shape];
     f3 p, n;
     if (sh.type == NB_SHAPE_SPHERE) {

@@ -108,12 +108,12 @@ __device__ __forceinline__ float nb_quad_kernel(float v0, float v1, float v2, fl
 
 /* NvdbVolume::getDensity (src/textures/NvdbVolume.cpp:39-48): SampleFromVoxels<.., 2> at a point
  * in grid coordinates; the stencil is ijk-1 .. ijk+1 around ijk = floor(p), z innermost */
-__device__ __forceinline__ float nb_grid_density(const NbDeviceScene &sc, const nb_medium &m, f3 p) {
+__device__ __forceinline__ float nb_grid_density(const float *density, const nb_medium &m, f3 p) {
     const float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
     const float u = p.x - fx, v = p.y - fy, w = p.z - fz;
     const int nx = (int) m.grid_dims[0], ny = (int) m.grid_dims[1], nz = (int) m.grid_dims[2];
     const int i = min(max((int) fx, 1), nx - 2), j = min(max((int) fy, 1), ny - 2), k = min(max((int) fz, 1), nz - 2);
-    const float *base = sc.density + m.first_voxel + ((size_t) (i - 1) * ny + (j - 1)) * nz + (k - 1);
+    const float *base = density + m.first_voxel + ((size_t) (i - 1) * ny + (j - 1)) * nz + (k - 1);
     float vx[3];
 #pragma unroll
     for (int dx = 0; dx < 3; ++dx) {
@@ -138,7 +138,8 @@ __device__ __forceinline__ NbMajorant nb_majorant(const nb_medium &m) {
 }
 
 /* HeterogeneousMedium::sampleFreePath: delta tracking from ray.mint = Epsilon */
-__device__ __forceinline__ float nb_free_path_heterog(const NbDeviceScene &sc, const nb_medium &m, f3 o, f3 d, NbRng &rng) {
+__device__ __forceinline__ float nb_free_path_heterog(const NbDeviceScene &sc, int32_t medium, f3 o, f3 d, NbRng &rng) {
+    const nb_medium &m = sc.media[medium];
     const f3 og = nb_grid_point(m, o), dg = nb_grid_dir(m, d);
     float t, t1;
     if (!nb_grid_clip(m, og, dg, NB_EPS, INFINITY, t, t1)) return INFINITY;
@@ -146,13 +147,14 @@ __device__ __forceinline__ float nb_free_path_heterog(const NbDeviceScene &sc, c
     for (int guard = 0; guard < (1 << 20); ++guard) {
         t -= __logf(rng.next_float()) * mj.inv_mu;
         if (!(t < t1)) return INFINITY;
-        if (nb_grid_density(sc, m, og + dg * t) * mj.accept >= rng.next_float()) return t;
+        if (nb_grid_density(sc.density, m, og + dg * t) * mj.accept >= rng.next_float()) return t;
     }
     return INFINITY;
 }
 
 /* HeterogeneousMedium::getTransmittance: ratio tracking between two points */
-__device__ __forceinline__ f3 nb_transmittance_heterog(const NbDeviceScene &sc, const nb_medium &m, f3 from, f3 to, NbRng &rng) {
+__device__ __forceinline__ f3 nb_transmittance_heterog(const NbDeviceScene &sc, int32_t medium, f3 from, f3 to, NbRng &rng) {
+    const nb_medium &m = sc.media[medium];
     const f3 seg = to - from;
     const float dist = length(seg);
     if (!(dist > 0.f)) return mk3(1.f);
@@ -165,17 +167,18 @@ __device__ __forceinline__ f3 nb_transmittance_heterog(const NbDeviceScene &sc, 
     for (int guard = 0; guard < (1 << 20); ++guard) {
         t -= __logf(rng.next_float()) * mj.inv_mu;
         if (!(t < t1)) break;
-        tr *= 1.f - nb_grid_density(sc, m, og + dg * t) * mj.accept;
+        tr *= 1.f - nb_grid_density(sc.density, m, og + dg * t) * mj.accept;
         if (tr <= 0.f) { tr = 0.f; break; }
     }
     return mk3(tr);
 }
 
 /* Medium::sampleFreePath along the ray (o, d) from mint = Epsilon. medium < 0 is the vacuum (no draws). */
+template <bool EXT = true>
 __device__ __forceinline__ float nb_free_path(const NbDeviceScene &sc, int32_t medium, f3 o, f3 d, NbRng &rng) {
     if (medium < 0) return INFINITY;
     const nb_medium &m = sc.media[medium];
-    if (m.type == NB_MEDIUM_HETEROGENEOUS) return nb_free_path_heterog(sc, m, o, d, rng);
+    if (EXT && m.type == NB_MEDIUM_HETEROGENEOUS) return nb_free_path_heterog(sc, medium, o, d, rng);
     if (m.type != NB_MEDIUM_HOMOGENEOUS) return INFINITY;
     const int ch = (int) (3.f * rng.next_float());                       /* homogmedium.cpp:62-66 */
     const float mu = m.mu_t[ch];
@@ -184,10 +187,11 @@ __device__ __forceinline__ float nb_free_path(const NbDeviceScene &sc, int32_t m
 }
 
 /* Medium::getTransmittance(from, to) */
+template <bool EXT = true>
 __device__ __forceinline__ f3 nb_transmittance(const NbDeviceScene &sc, int32_t medium, f3 from, f3 to, NbRng &rng) {
     if (medium < 0) return mk3(1.f);
     const nb_medium &m = sc.media[medium];
-    if (m.type == NB_MEDIUM_HETEROGENEOUS) return nb_transmittance_heterog(sc, m, from, to, rng);
+    if (EXT && m.type == NB_MEDIUM_HETEROGENEOUS) return nb_transmittance_heterog(sc, medium, from, to, rng);
     if (m.type != NB_MEDIUM_HOMOGENEOUS) return mk3(1.f);
     const float dist = length(from - to);                                /* homogmedium.cpp:68-72 */
     return mk3(__expf(-m.mu_t[0] * dist), __expf(-m.mu_t[1] * dist), __expf(-m.mu_t[2] * dist));

@@ -23,6 +23,7 @@ the cube only ever sees empty voxels. So the fixtures are our own scenes on the 
 """
 import ctypes as C
 import os
+import re
 import shutil
 import subprocess
 import sys
@@ -107,6 +108,11 @@ def main():
     assert 'type="path_vol_mis"' in fluid_mis
     open(os.path.join(VOL, "cbox_heterog_fluid_mis_small.xml"), "w").write(fluid_mis)
     open(os.path.join(VOL, "cbox_heterog_fluid_small.xml"), "w").write(fluid_mis.replace("path_vol_mis", "path_vol_mats"))
+    # full-size variants (800 x 600, as scenes/project/volume/cbox_heterog.xml) for the throughput table
+    for name in ("cbox_heterog_fluid", "cbox_heterog_fluid_mis"):
+        t = open(os.path.join(VOL, name + "_small.xml")).read()
+        t = re.sub(r'(name="width"\s+value=")\d+', r"\g<1>800", t); t = re.sub(r'(name="height"\s+value=")\d+', r"\g<1>600", t)
+        open(os.path.join(VOL, name + ".xml"), "w").write(t)
 
     def ref(*args):
         r = subprocess.run([NORI_REF] + list(args), stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)

@@ -23,7 +23,12 @@ CONFIGS = [  # name, xml, gpu spp, cpu spp
     ("C2 odyssey direct_ems 768x432", os.path.join(G, "odyssey", "odyssey_ems.xml"), 128, 32),
     ("C4 cbox_val_mis path_vol_mis 600x600", os.path.join(G, "vol", "cbox_val_mis.xml"), 128, 16),
     ("C4 cbox_homog_aniso path_vol_mats 800x600", os.path.join(G, "vol", "cbox_homog_aniso.xml"), 128, 16),
+    ("C4 heterog fluid (NanoVDB-class grid) path_vol_mats 800x600", os.path.join(G, "vol", "cbox_heterog_fluid.xml"), 128, 8),
+    ("C4 heterog fluid path_vol_mis 800x600", os.path.join(G, "vol", "cbox_heterog_fluid_mis.xml"), 128, 8),
+    ("envmap_sphere path_mis 800x800 (1500x750 PNG environment)", os.path.join(G, "envmap", "envmap_sphere.xml"), 128, 16),
 ]
+if "only" in opt:
+    CONFIGS = [c for c in CONFIGS if opt["only"] in c[0]]
 c3 = os.path.join(ROOT, "c3cache", "c3_path_mis.xml")
 if os.path.exists(c3):
     CONFIGS.append(("C3 synthetic 1310720 tris path_mis 800x600", c3, 32, 4))
