@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 4
+#define NB_ABI_VERSION 5
 
 enum {
     NB_OK = 0,
@@ -38,14 +38,16 @@ enum {
 /* ---- plugin tags (the flatten hooks emit these) -------------------------------------------- */
 enum { NB_SHAPE_MESH = 0, NB_SHAPE_SPHERE = 1 };
 enum { NB_BSDF_DIFFUSE = 0, NB_BSDF_MIRROR = 1, NB_BSDF_DIELECTRIC = 2, NB_BSDF_MICROFACET = 3,
-       NB_BSDF_NONE = 0xff };
-enum { NB_EMITTER_AREA = 0, NB_EMITTER_POINT = 1, NB_EMITTER_ENVMAP = 2 };
+       NB_BSDF_DISNEY = 4, NB_BSDF_NONE = 0xff };
+enum { NB_EMITTER_AREA = 0, NB_EMITTER_POINT = 1, NB_EMITTER_ENVMAP = 2, NB_EMITTER_SPOT = 3,
+       NB_EMITTER_DIRECTIONAL = 4 };
 enum { NB_TEXTURE_CONSTANT = 0, NB_TEXTURE_IMAGE = 1, NB_TEXTURE_CHECKERBOARD = 2 };
-enum { NB_TEXTURE_SPHERICAL = 1u };
+enum { NB_TEXTURE_SPHERICAL = 1u,   /* PNGTexture::sphericalTexture */
+       NB_TEXTURE_NORMAL_MAP = 2u }; /* PNGTexture with sRGB = false: a Texture<Normal3f> (PNGTexture.cpp:88-99, 155-162) */
 enum { NB_INTEGRATOR_PATH_MIS = 0, NB_INTEGRATOR_PATH_MATS = 1, NB_INTEGRATOR_DIRECT_EMS = 2,
        NB_INTEGRATOR_DIRECT_MATS = 3, NB_INTEGRATOR_DIRECT_MIS = 4, NB_INTEGRATOR_NORMALS = 5,
        NB_INTEGRATOR_DIRECT = 6, NB_INTEGRATOR_AV = 7, NB_INTEGRATOR_PATH_VOL_MATS = 8,
-       NB_INTEGRATOR_PATH_VOL_MIS = 9 };
+       NB_INTEGRATOR_PATH_VOL_MIS = 9, NB_INTEGRATOR_PREVIEW = 10 };
 enum { NB_MEDIUM_VACUUM = 0, NB_MEDIUM_HOMOGENEOUS = 1, NB_MEDIUM_HETEROGENEOUS = 2 };
 enum { NB_PHASE_ISOTROPIC = 0, NB_PHASE_HENYEY_GREENSTEIN = 1, NB_PHASE_SCHLICK = 2 };
 enum { NB_SHAPE_HAS_NORMALS = 1u, NB_SHAPE_HAS_UVS = 2u };
@@ -68,16 +70,21 @@ typedef struct nb_shape {
     float    pdf_norm;       /* DiscretePDF::getNormalization() = 1/total area (mesh.cpp:70) */
     float    radius;         /* sphere */
     float    center[3];      /* sphere */
-    uint32_t pad;
+    uint32_t normal_map;     /* 1 + index of the NB_TEXTURE_NORMAL_MAP texture (Shape::m_normalMap, shape.h:226;
+                                applied in mesh.cpp:168-186, sphere.cpp:115-123), 0 = none */
 } nb_shape;                  /* 64 bytes */
 
 /* BSDF::getOptixMaterialData replacement (bsdf/diffuse.cpp, mirror.cpp, dielectric.cpp,
  * microfacet.cpp). */
 typedef struct nb_bsdf {
     uint32_t type;           /* bits 0..7: NB_BSDF_*; bits 8..31: 1 + index of the albedo texture
-                                (Diffuse::m_albedo, diffuse.cpp:31-40,77-91), 0 = the constant below */
-    float    albedo[3];      /* diffuse albedo / microfacet kd */
-    float    alpha;          /* microfacet roughness */
+                                (Diffuse::m_albedo, diffuse.cpp:31-40,77-91; Disney::albedo, disney.cpp:22-29,
+                                90-104), 0 = the constant below */
+    float    albedo[3];      /* diffuse albedo / microfacet kd / disney base colour */
+    float    alpha;          /* microfacet roughness. Disney (src/bsdf/disney.cpp:31-41): the bits of a u32 —
+                                offset into nb_scene_desc.params of its 10 floats { metallic, subsurface,
+                                specular, roughness, specularTint, anisotropic, sheen, sheenTint, clearcoat,
+                                clearcoatGloss }, each already clamped to [0, 1] */
     float    int_ior, ext_ior;
     float    ks;             /* microfacet: 1 - max(kd) (microfacet.cpp:52) */
 } nb_bsdf;                   /* 32 bytes */
@@ -86,7 +93,12 @@ typedef struct nb_bsdf {
  * environmentmap.cpp). */
 typedef struct nb_emitter {
     uint32_t type;           /* NB_EMITTER_* */
-    int32_t  shape;          /* area light: owning shape; environment map: index of its texture (EnvMap::m_map) */
+    int32_t  shape;          /* area light: owning shape; environment map: index of its texture (EnvMap::m_map);
+                                spot / directional: offset into nb_scene_desc.params —
+                                spot (src/emitters/spotlight.cpp:16-24, 63-70, 167-187): { direction.xyz (normalized),
+                                  cos(falloffStart deg), cos(totalWidth / 2 deg) }, position below, radiance = power / (2 pi);
+                                directional (src/emitters/directionalLight.cpp:31-38, 90-133): { direction.xyz
+                                  (normalized), cos(angle deg) }, radiance below */
     float    radiance[3];    /* area: radiance; point: power/(4 pi) (pointlight.cpp:44); envmap: m_radiance */
     float    position[3];    /* point light. Environment map: the three words are
                                 { u32 cdf_offset, f32 cdf_norm, 0 } — EnvMap::dpdf (environmentmap.cpp:146-161):
@@ -106,7 +118,8 @@ typedef struct nb_texture {
     float    scale[2];       /* image: scaleU, scaleV; checkerboard: m_scale */
     float    offset[2];      /* image: offsetU, offsetV; checkerboard: m_delta */
     float    rotation[9];    /* image, spherical: the row-major rotation PNGTexture::eval builds from eulerAngles */
-    uint32_t pad[2];
+    float    intensity;      /* normal map: PNGTexture::intensity (PNGTexture.cpp:33, 155-162) */
+    uint32_t pad;
 } nb_texture;                /* 96 bytes */
 
 /* Camera::getOptixData replacement (cameras/perspective.cpp:48-141). Matrices are row-major
@@ -167,6 +180,8 @@ typedef struct nb_scene_desc {
     uint64_t n_density;   const float      *density;     /* voxel data of heterogeneous media or NULL */
     uint32_t n_textures;  const nb_texture *textures;    /* may be 0 / NULL */
     uint64_t n_texels;    const float      *texels;      /* 4 floats per texel, or NULL */
+    uint64_t n_params;    const float      *params;      /* parameters of plugins whose record has no room for
+                                                            them (disney, spot, directional), or NULL */
 } nb_scene_desc;
 
 /* nb_build_bvh(mode = NB_BVH_IMPORT): the caller's own arrays (BVH::m_nodes / m_indices after
@@ -197,7 +212,9 @@ typedef struct nb_render_params {
     uint64_t seed;                             /* mixed into every per-pixel pcg32 stream */
     uint32_t pool_paths;                       /* path slots in flight; 0 = library default */
     uint32_t max_depth;                        /* 0 = unbounded, as the reference */
-    uint32_t reserved[4];
+    float    integrator_params[3];             /* normals: NormalIntegrator::direction (normals.cpp:12, default 0 0 1);
+                                                  av: [0] = AverageVisibilityIntegrator::m_length (av.cpp:14) */
+    uint32_t reserved;
 } nb_render_params;
 
 typedef struct nb_counters {
@@ -248,6 +265,12 @@ int  nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int 
  * floats per record (ref.xyz, sample.xy). out gets 12 floats per record: lRec.wi, the returned
  * value (radiance / pdf), lRec.pdf, shadowRay.maxt, Emitter::eval for the sampled direction, 0. */
 int  nb_emitter_probe(nb_ctx *ctx, uint32_t emitter, const float *in, uint64_t n, float *out);
+/* Parity entry for the BSDF rows: BSDF::eval / pdf / sample (src/bsdf/{diffuse,mirror,dielectric,microfacet,
+ * disney}.cpp) of bsdfs[bsdf] on n records of 10 floats { wi.xyz, wo.xyz, sample.xy, uv.xy } (local frame).
+ * out gets 12 floats per record: eval(wi, wo) rgb for measure ESolidAngle, pdf(wi, wo), then for
+ * sample(wi, sample): the returned weight rgb, the sampled wo.xyz, 1 if the measure is EDiscrete else 0,
+ * and bsdf->pdf of the sampled direction. */
+int  nb_bsdf_probe(nb_ctx *ctx, uint32_t bsdf, const float *in, uint64_t n, float *out);
 int  nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples,
                      uint64_t seed, float *out);
 

@@ -18,10 +18,10 @@ HOST_LIB_PATH = os.path.join(HERE, "libnorib200_host.so")
 
 NB_OK, NB_E_INVALID, NB_E_CUDA, NB_E_NOMEM, NB_E_STATE, NB_E_UNSUPPORTED, NB_E_NO_DEVICE = 0, -1, -2, -3, -4, -5, -6
 SHAPE_MESH, SHAPE_SPHERE = 0, 1
-BSDF_DIFFUSE, BSDF_MIRROR, BSDF_DIELECTRIC, BSDF_MICROFACET = 0, 1, 2, 3
-EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP = 0, 1, 2
+BSDF_DIFFUSE, BSDF_MIRROR, BSDF_DIELECTRIC, BSDF_MICROFACET, BSDF_DISNEY = 0, 1, 2, 3, 4
+EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP, EMITTER_SPOT, EMITTER_DIRECTIONAL = 0, 1, 2, 3, 4
 INTEGRATORS = {"path_mis": 0, "path_mats": 1, "direct_ems": 2, "direct_mats": 3, "direct_mis": 4,
-               "normals": 5, "direct": 6, "av": 7, "path_vol_mats": 8, "path_vol_mis": 9}
+               "normals": 5, "direct": 6, "av": 7, "path_vol_mats": 8, "path_vol_mis": 9, "preview": 10}
 MEDIUM_VACUUM, MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_HENYEY_GREENSTEIN, PHASE_SCHLICK = 0, 1, 2
 FILTER_RESOLUTION = 32
@@ -30,7 +30,7 @@ FILTER_RESOLUTION = 32
 shape_dtype = np.dtype([("type", "<u4"), ("prim_count", "<u4"), ("vertex_offset", "<u4"), ("vertex_count", "<u4"),
                         ("face_offset", "<u4"), ("flags", "<u4"), ("bsdf", "<i4"), ("emitter", "<i4"),
                         ("medium", "<i4"), ("cdf_offset", "<u4"), ("pdf_norm", "<f4"), ("radius", "<f4"),
-                        ("center", "<f4", 3), ("pad", "<u4")])
+                        ("center", "<f4", 3), ("normal_map", "<u4")])
 bsdf_dtype = np.dtype([("type", "<u4"), ("albedo", "<f4", 3), ("alpha", "<f4"), ("int_ior", "<f4"),
                        ("ext_ior", "<f4"), ("ks", "<f4")])
 emitter_dtype = np.dtype([("type", "<u4"), ("shape", "<i4"), ("radiance", "<f4", 3), ("position", "<f4", 3)])
@@ -42,13 +42,14 @@ medium_dtype = np.dtype([("type", "<u4"), ("mu_t", "<f4", 3), ("phase", "<u4"), 
                          ("first_voxel", "<u4"), ("world_to_grid", "<f4", 12)])
 texture_dtype = np.dtype([("type", "<u4"), ("flags", "<u4"), ("width", "<u4"), ("height", "<u4"), ("first_texel", "<u4"),
                           ("value", "<f4", 3), ("value2", "<f4", 3), ("scale", "<f4", 2), ("offset", "<f4", 2),
-                          ("rotation", "<f4", 9), ("pad", "<u4", 2)])
+                          ("rotation", "<f4", 9), ("intensity", "<f4"), ("pad", "<u4")])
 bvh_node_dtype = np.dtype([("word0", "<u4"), ("word1", "<u4"), ("bmin", "<f4", 3), ("bmax", "<f4", 3)])
 ray_dtype = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("mint", "<f4"), ("maxt", "<f4")])
 hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("shape", "<i4"), ("prim", "<i4"), ("any_hit", "<u4")])
 render_params_dtype = np.dtype([("integrator", "<u4"), ("filter_radius", "<f4"),
                                 ("filter_table", "<f4", FILTER_RESOLUTION + 1), ("pad0", "<u4"), ("seed", "<u8"),
-                                ("pool_paths", "<u4"), ("max_depth", "<u4"), ("reserved", "<u4", 4)])
+                                ("pool_paths", "<u4"), ("max_depth", "<u4"), ("integrator_params", "<f4", 3),
+                                ("reserved", "<u4")])
 SECTION_DTYPES = {"shapes": shape_dtype, "bsdfs": bsdf_dtype, "emitters": emitter_dtype, "camera": camera_dtype,
                   "bvh_nodes": bvh_node_dtype, "render": render_params_dtype, "media": medium_dtype, "textures": texture_dtype}
 
@@ -71,7 +72,8 @@ class SceneDesc(C.Structure):
                 ("n_media", C.c_uint32), ("media", C.c_void_p), ("ambient_medium", C.c_int32),
                 ("n_density", C.c_uint64), ("density", C.c_void_p),
                 ("n_textures", C.c_uint32), ("textures", C.c_void_p),
-                ("n_texels", C.c_uint64), ("texels", C.c_void_p)]
+                ("n_texels", C.c_uint64), ("texels", C.c_void_p),
+                ("n_params", C.c_uint64), ("params", C.c_void_p)]
 
 
 class BvhImport(C.Structure):
@@ -88,7 +90,8 @@ class Counters(C.Structure):
 EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
-           "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe"]
+           "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe",
+           "nb_bsdf_probe"]
 
 _lib = None
 
@@ -129,6 +132,7 @@ def load_library(path=None):
     lib.nb_sample_slice.argtypes = [C.c_uint32] * 4 + [C.POINTER(C.c_uint32)] * 2
     lib.nb_bvh_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_double)]
     lib.nb_emitter_probe.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.nb_bsdf_probe.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64, C.c_void_p]
     lib.nb_medium_probe.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint64, C.c_void_p]
     if path in (LIB_PATH, os.environ.get("NORIB200_LIB")):
         _lib = lib
@@ -232,6 +236,7 @@ class Context:
         dn = keep.get("density"); d.n_density = 0 if dn is None else dn.size; d.density = _ptr(dn)
         tx = keep.get("textures"); d.n_textures = 0 if tx is None else len(tx); d.textures = _ptr(tx)
         tl = keep.get("texels"); d.n_texels = 0 if tl is None else tl.size // 4; d.texels = _ptr(tl)
+        pr = keep.get("params"); d.n_params = 0 if pr is None else pr.size; d.params = _ptr(pr)
         self._check(self.lib.nb_upload_scene(self.handle, C.byref(d)))
 
     def build_bvh(self, nodes, indices):
@@ -260,6 +265,14 @@ class Context:
         rec = np.ascontiguousarray(records, dtype="<f4").reshape(-1, 5)
         out = np.zeros((len(rec), 12), dtype="<f4")
         self._check(self.lib.nb_emitter_probe(self.handle, emitter, _ptr(rec), len(rec), _ptr(out)))
+        return out
+
+    def bsdf_probe(self, bsdf, records):
+        """records: (n, 10) float32 [wi.xyz, wo.xyz, sample.xy, uv.xy]; returns (n, 12)
+        [eval rgb, pdf, sample weight rgb, sampled wo xyz, discrete, pdf of the sampled direction]."""
+        rec = np.ascontiguousarray(records, dtype="<f4").reshape(-1, 10)
+        out = np.zeros((len(rec), 12), dtype="<f4")
+        self._check(self.lib.nb_bsdf_probe(self.handle, bsdf, _ptr(rec), len(rec), _ptr(out)))
         return out
 
     def medium_probe(self, medium, rays, samples=1024, seed=1):

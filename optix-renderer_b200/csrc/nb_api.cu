@@ -97,6 +97,7 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if (s->n_shapes == 0 || !s->shapes) return nb_fail(ctx, NB_E_INVALID, "nb_upload_scene: scene has no shapes");
     /* validate before touching the device */
     uint64_t prims = 0;
+    bool ext_plugins = false;      /* disney / spot / directional: rendered by the EXT kernel variants */
     for (uint32_t i = 0; i < s->n_shapes; ++i) {
         const nb_shape &sh = s->shapes[i];
         if (sh.type == NB_SHAPE_MESH) {
@@ -119,9 +120,22 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if (prims >= NB_SLOT_LAST) return nb_fail(ctx, NB_E_UNSUPPORTED, "too many primitives (%llu)", (unsigned long long) prims);
     for (uint32_t i = 0; i < s->n_bsdfs; ++i) {
         const uint32_t tag = s->bsdfs[i].type & 0xffu, tex = s->bsdfs[i].type >> 8;
-        if (tag > NB_BSDF_MICROFACET) return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: tag %u has no kernel in this backend", i, tag);
-        if (tex && tag != NB_BSDF_DIFFUSE) return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: only the diffuse BSDF takes an albedo texture", i);
+        if (tag > NB_BSDF_DISNEY) return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: tag %u has no kernel in this backend", i, tag);
+        if (tex && tag != NB_BSDF_DIFFUSE && tag != NB_BSDF_DISNEY)
+            return nb_fail(ctx, NB_E_UNSUPPORTED, "bsdf %u: only the diffuse and disney BSDFs take an albedo texture", i);
         if (tex > s->n_textures) return nb_fail(ctx, NB_E_INVALID, "bsdf %u: texture index out of range", i);
+        if (tex && s->textures && (s->textures[tex - 1].flags & NB_TEXTURE_NORMAL_MAP)) return nb_fail(ctx, NB_E_INVALID, "bsdf %u: albedo texture is a normal map", i);
+        if (tag == NB_BSDF_DISNEY) {
+            uint32_t off; memcpy(&off, &s->bsdfs[i].alpha, 4);
+            if (!s->params || (uint64_t) off + 10 > s->n_params) return nb_fail(ctx, NB_E_INVALID, "bsdf %u: disney parameters outside params", i);
+            ext_plugins = true;
+        }
+    }
+    for (uint32_t i = 0; i < s->n_shapes; ++i) {
+        const uint32_t nm = s->shapes[i].normal_map;
+        if (!nm) continue;
+        if (nm > s->n_textures || !s->textures || s->textures[nm - 1].type != NB_TEXTURE_IMAGE || !(s->textures[nm - 1].flags & NB_TEXTURE_NORMAL_MAP))
+            return nb_fail(ctx, NB_E_INVALID, "shape %u: normal_map does not name a normal-map texture", i);
     }
     if (s->n_textures && !s->textures) return nb_fail(ctx, NB_E_INVALID, "textures missing");
     for (uint32_t i = 0; i < s->n_textures; ++i) {
@@ -139,6 +153,11 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
         if (e.type == NB_EMITTER_AREA) {
             if (e.shape < 0 || e.shape >= (int32_t) s->n_shapes) return nb_fail(ctx, NB_E_INVALID, "emitter %u: area light without a shape", i);
         } else if (e.type == NB_EMITTER_POINT) {
+        } else if (e.type == NB_EMITTER_SPOT || e.type == NB_EMITTER_DIRECTIONAL) {
+            const uint64_t need = e.type == NB_EMITTER_SPOT ? 5 : 4;
+            if (e.shape < 0 || !s->params || (uint64_t) e.shape + need > s->n_params)
+                return nb_fail(ctx, NB_E_INVALID, "emitter %u: parameters outside params", i);
+            ext_plugins = true;
         } else if (e.type == NB_EMITTER_ENVMAP) {                  /* Scene::addChild keeps the last one as m_envmap (scene.cpp:218-222) */
             if (e.shape < 0 || e.shape >= (int32_t) s->n_textures) return nb_fail(ctx, NB_E_INVALID, "emitter %u: environment map without a texture", i);
             const nb_texture &t = s->textures[e.shape];
@@ -195,10 +214,11 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->density, s->n_density, &d.density))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->textures, s->n_textures, &d.textures))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->texels, s->n_texels * 4, &d.texels))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, s->params, s->n_params, &d.params))) return rc;
     d.n_media = s->n_media; d.ambient_medium = s->ambient_medium;
     d.n_shapes = s->n_shapes; d.n_bsdfs = s->n_bsdfs; d.n_emitters = s->n_emitters;
     d.envmap_emitter = envmap;
-    d.ext = (envmap >= 0 || s->n_textures > 0) ? 1u : 0u;
+    d.ext = (envmap >= 0 || s->n_textures > 0 || ext_plugins) ? 1u : 0u;
     for (uint32_t i = 0; i < s->n_media; ++i) if (s->media[i].type == NB_MEDIUM_HETEROGENEOUS) d.ext = 1u;
     d.camera = s->camera;
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -20,6 +20,7 @@ struct NbPlan {
     uint32_t npix, width;
     uint32_t first, stride;       /* sample index of pass k = first + k * stride */
     uint32_t max_depth;
+    float iparam[3];              /* nb_render_params.integrator_params */
 };
 
 /* ImageBlock::put(pos, value), block.cpp:93-123, on the full-image block (offset 0). */

@@ -31,7 +31,7 @@ struct NbDeviceScene {
     const float4 *slots = nullptr;      /* 3 per primitive slot */
     uint32_t n_nodes = 0, n_slots = 0;
     uint32_t flat = 0;                  /* queries scan the slots instead of walking the tree (nb_trace.cuh) */
-    uint32_t ext = 0;                   /* scene uses textures, an environment map or a heterogeneous medium: the EXT kernel variants render it */
+    uint32_t ext = 0;                   /* scene uses textures, normal maps, an environment map, a heterogeneous medium, the disney BSDF or a spot / directional light: the EXT kernel variants render it */
     /* shading data */
     const nb_shape *shapes = nullptr;
     const float *positions = nullptr, *normals = nullptr, *uvs = nullptr, *tangents = nullptr, *bitangents = nullptr;
@@ -43,6 +43,7 @@ struct NbDeviceScene {
     const float *density = nullptr;     /* voxels of heterogeneous media */
     const nb_texture *textures = nullptr;
     const float *texels = nullptr;      /* RGBA, 16-byte aligned */
+    const float *params = nullptr;      /* nb_scene_desc.params: disney / spot / directional parameters */
     uint32_t n_shapes = 0, n_bsdfs = 0, n_emitters = 0, n_media = 0;
     int32_t envmap_emitter = -1, ambient_medium = -1;
     nb_camera camera;

@@ -46,13 +46,14 @@ struct NbPathRegs {                   /* path_mis.cpp:18-24 locals + the ray bei
 
 struct NbShadowRay { f3 o, d, c; float mint, maxt, cand; };
 
+template <bool EXT>
 __device__ __forceinline__ void nb_hit_info(const NbDeviceScene &sc, const NbHit &hit, f3 o, f3 d, nb_shape &sh, NbIts &its) {
     const float4 sl = __ldg(sc.slots + 3 * hit.slot + 2);
     const uint32_t sid = __float_as_uint(sl.y) & NB_SLOT_SHAPE_MASK, prim = __float_as_uint(sl.z);
     sh = sc.shapes[sid];
     its.shape = sid;
-    if (sh.type == NB_SHAPE_SPHERE) nb_sphere_hit_info(sh, o, d, hit.t, its);
-    else nb_mesh_hit_info(sc, sh, prim, hit.u, hit.v, its);
+    if (sh.type == NB_SHAPE_SPHERE) nb_sphere_hit_info<EXT>(sc, sh, o, d, hit.t, its);
+    else nb_mesh_hit_info<EXT>(sc, sh, prim, hit.u, hit.v, its);
 }
 
 /* AreaEmitter::eval (arealight.cpp:58-73) for EmitterQueryRecord(ref, p, n) */
@@ -78,7 +79,7 @@ template <bool MIS, bool EXT>
 __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t max_depth, NbPathRegs &ps, const NbHit &hit,
                                                bool &shadow, NbShadowRay &so) {
     nb_shape sh; NbIts its;
-    nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
+    nb_hit_info<EXT>(sc, hit, ps.o, ps.d, sh, its);
     const float n_lights = (float) sc.n_emitters;
     /* emitter hit (path_mis.cpp:51-56); the MIS weight of the BSDF-sampled ray that led here
      * (path_mis.cpp:117-140) is evaluated now that its hit is known */
@@ -116,9 +117,9 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
         const f3 ems_col = nb_emitter_sample<EXT>(sc, ei, its.p, s, es);
         if (!is_zero(ems_col, NB_EPS)) {
             const f3 we = its.sh.to_local(es.wi);
-            const f3 C = ps.thr * (ems_col * we.z * nb_bsdf_eval(bsdf, wi, we) * n_lights);
+            const f3 C = ps.thr * (ems_col * we.z * nb_bsdf_eval<EXT>(bsdf, wi, we, sc.params) * n_lights);
             if (!is_black(C)) {
-                const float pdf_b = nb_bsdf_pdf(bsdf, wi, we), pdf_e = es.pdf / n_lights;
+                const float pdf_b = nb_bsdf_pdf<EXT>(bsdf, wi, we), pdf_e = es.pdf / n_lights;
                 shadow = true;
                 so.o = es.ray_o; so.d = es.ray_d; so.mint = es.ray_mint; so.maxt = es.ray_maxt; so.c = C;
                 so.cand = (pdf_b + pdf_e > NB_EPS) ? pdf_e / (pdf_b + pdf_e) : -1.f;
@@ -128,7 +129,7 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
     /* BSDF sampling (path_mis.cpp:108-146 / path_mats.cpp:63-74) */
     float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
     f3 wo; bool discrete;
-    const f3 col = nb_bsdf_sample(bsdf, wi, s, wo, discrete, ps.pdfmat);
+    const f3 col = nb_bsdf_sample<EXT>(bsdf, wi, s, wo, discrete, ps.pdfmat, sc.params);
     ps.flags = (bounce + 1) << NB_BOUNCE_SHIFT;
     if (discrete) { ps.flags |= NB_FLAG_DISCRETE; ps.w_ems = 0.f; }
     if (!is_zero(col, NB_EPS)) ps.flags |= NB_FLAG_BSDF_OK;
@@ -139,12 +140,46 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
 
 /* The depth-1 integrators, one whole sample. Returns Li. */
 template <int INTEG, bool FLAT, bool EXT>
-__device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any) {
+__device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, const NbPlan &plan, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any) {
     NbHit hit;
     ++n_closest;
-    if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) return nb_env_radiance<EXT>(sc, ps.d);   /* direct*.cpp: getEnvMap()->eval */
+    if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) {
+        if (INTEG == NB_INTEGRATOR_AV) return mk3(1.f);                                                     /* av.cpp:21-22 */
+        return nb_env_radiance<EXT>(sc, ps.d);                                                              /* direct*.cpp, normals.cpp, PreviewIntegrator.cpp: getEnvMap()->eval */
+    }
     nb_shape sh; NbIts its;
-    nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
+    nb_hit_info<EXT>(sc, hit, ps.o, ps.d, sh, its);
+    if (INTEG == NB_INTEGRATOR_NORMALS) {                             /* normals.cpp:31-35 */
+        const f3 n = its.sh.to_world(mk3(plan.iparam[0], plan.iparam[1], plan.iparam[2]));
+        return mk3(fabsf(n.x), fabsf(n.y), fabsf(n.z));
+    }
+    if (INTEG == NB_INTEGRATOR_AV) {                                  /* av.cpp:24-42; Warp::sampleUniformHemisphere warp.cpp:25-39 */
+        f3 v;
+        do {
+            v.x = 1.f - 2.f * ps.rng.next_float();
+            v.y = 1.f - 2.f * ps.rng.next_float();
+            v.z = 1.f - 2.f * ps.rng.next_float();
+        } while (dot(v, v) > 1.f);
+        if (dot(v, its.sh.n) < 0.f) v = -v;
+        v = v / length(v);
+        NbHit h2;
+        ++n_closest;                                                  /* the reference asks for the closest hit here, not a shadow query */
+        return nb_closest<FLAT>(sc, its.p, v, NB_EPS, plan.iparam[0], h2) ? mk3(0.f) : mk3(1.f);
+    }
+    if (INTEG == NB_INTEGRATOR_PREVIEW) {                             /* PreviewIntegrator.cpp:39-76 */
+        if (sc.n_emitters == 0) return mk3(fabsf(its.sh.n.x), fabsf(its.sh.n.y), fabsf(its.sh.n.z));
+        const f3 wo = its.sh.to_local(normalize(ps.o - its.p));
+        const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
+        float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+        NbEmitterSample es;
+        const f3 li = nb_emitter_sample<EXT>(sc, ei, its.p, s, es) * (float) sc.n_emitters;
+        ++n_any;
+        if (sh.bsdf < 0 || nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) return mk3(0.f);
+        nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
+        nb_bsdf_resolve<EXT>(sc, bsdf, its.uv);
+        const float c = fabsf(dot(es.wi, its.sh.n)) / length(es.wi);
+        return li * c * nb_bsdf_eval<EXT>(bsdf, its.sh.to_local(es.wi), wo, sc.params);
+    }
     f3 result = mk3(0.f);
     if (INTEG != NB_INTEGRATOR_DIRECT && sh.emitter >= 0)
         result += nb_area_eval(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
@@ -163,7 +198,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
             ++n_any;
             if (nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
             const float c = fabsf(dot(es.wi, its.sh.n)) / length(es.wi);
-            result += li * c * nb_bsdf_eval(bsdf, wi, wo);
+            result += li * c * nb_bsdf_eval<EXT>(bsdf, wi, wo, sc.params);
         }
         return result;
     }
@@ -177,7 +212,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
             ++n_any;
             if (nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) continue;
             const f3 we = its.sh.to_local(es.wi);
-            result += li * fabsf(we.z) * nb_bsdf_eval(bsdf, wi, we);
+            result += li * fabsf(we.z) * nb_bsdf_eval<EXT>(bsdf, wi, we, sc.params);
         }
         return result;
     }
@@ -192,8 +227,8 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
             ++n_any;
             if (!nb_occluded<FLAT>(sc, es.ray_o, es.ray_d, es.ray_mint, es.ray_maxt)) {
                 const f3 we = its.sh.to_local(es.wi);
-                const float pdf_ems = es.pdf / n_lights, pdf_mat = nb_bsdf_pdf(bsdf, wi, we);
-                result_ems = li * we.z * nb_bsdf_eval(bsdf, wi, we) * n_lights;
+                const float pdf_ems = es.pdf / n_lights, pdf_mat = nb_bsdf_pdf<EXT>(bsdf, wi, we);
+                result_ems = li * we.z * nb_bsdf_eval<EXT>(bsdf, wi, we, sc.params) * n_lights;
                 if (pdf_ems + pdf_mat > NB_EPS) w_ems = pdf_ems / (pdf_ems + pdf_mat);
             }
         }
@@ -201,14 +236,14 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, NbPathRe
     /* BSDF sampling: direct_mats.cpp:46-80 / direct_mis.cpp:92-135 */
     float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
     f3 wo; bool discrete; float pdf_mat;
-    const f3 col = nb_bsdf_sample(bsdf, wi, s, wo, discrete, pdf_mat);
+    const f3 col = nb_bsdf_sample<EXT>(bsdf, wi, s, wo, discrete, pdf_mat, sc.params);
     if (!is_zero(col, NB_EPS)) {
         const f3 d2 = its.sh.to_world(wo);
         NbHit hit2;
         ++n_closest;
         if (nb_closest<FLAT>(sc, its.p, d2, NB_EPS, INFINITY, hit2)) {
             nb_shape sh2; NbIts its2;
-            nb_hit_info(sc, hit2, its.p, d2, sh2, its2);
+            nb_hit_info<EXT>(sc, hit2, its.p, d2, sh2, its2);
             if (sh2.emitter >= 0) {
                 result_mats = col * nb_area_eval(sc.emitters[sh2.emitter], its.p, its2.p, its2.sh.n);
                 if (INTEG == NB_INTEGRATOR_DIRECT_MIS) {
@@ -247,7 +282,7 @@ __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbP
         ++n_closest;
         if (!nb_closest<FLAT>(sc, so, es.ray_d, es.ray_mint, smaxt, h)) break;
         nb_shape sh2; NbIts its2;
-        nb_hit_info(sc, h, so, es.ray_d, sh2, its2);
+        nb_hit_info<EXT>(sc, h, so, es.ray_d, sh2, its2);
         if (sh2.bsdf >= 0) return mk3(0.f);
         tr = tr * nb_transmittance<EXT>(sc, sm, so, its2.p, ps.rng);
         sm = nb_medium_behind(sc, sh2, its2.geo_n, es.ray_d);
@@ -259,8 +294,8 @@ __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbP
     if (phase) pdf_em_mat = nb_phase_pdf(*phase, its.sh.to_local(es.ray_d));
     else {
         const f3 wi = its.sh.to_local(-ps.d), we = its.sh.to_local(es.wi);
-        pdf_em_mat = nb_bsdf_pdf(*bsdf, wi, we);
-        f = nb_bsdf_eval(*bsdf, wi, we) * fabsf(dot(es.wi, its.sh.n));
+        pdf_em_mat = nb_bsdf_pdf<EXT>(*bsdf, wi, we);
+        f = nb_bsdf_eval<EXT>(*bsdf, wi, we, sc.params) * fabsf(dot(es.wi, its.sh.n));
     }
     const float w_em = pdf_em > NB_EPS ? pdf_em / (pdf_em + pdf_em_mat) : 0.f;
     if (w_em > NB_EPS) return tr * w_em * ps.thr * Le * f;
@@ -273,7 +308,7 @@ template <bool MIS, bool FLAT, bool EXT>
 __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t max_depth, NbPathRegs &ps, int32_t &medium,
                                               const NbHit &hit, uint32_t &n_closest) {
     nb_shape sh; NbIts its;
-    nb_hit_info(sc, hit, ps.o, ps.d, sh, its);
+    nb_hit_info<EXT>(sc, hit, ps.o, ps.d, sh, its);
     const float tm = nb_free_path<EXT>(sc, medium, ps.o, ps.d, ps.rng);
     const bool mi = tm < hit.t;                                          /* isMediumInteraction */
     const f3 p = mi ? ps.o + ps.d * tm : its.p;
@@ -314,13 +349,13 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
             const f3 wi = its.sh.to_local(-ps.d);
             float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
             f3 lwo; bool discrete; float pdf;
-            const f3 col = nb_bsdf_sample(bsdf, wi, s, lwo, discrete, pdf);
+            const f3 col = nb_bsdf_sample<EXT>(bsdf, wi, s, lwo, discrete, pdf, sc.params);
             wo = its.sh.to_world(lwo);
             if (MIS) {
                 /* bRec.measure after sample(): diffuse sets ESolidAngle and mirror EDiscrete only when
                  * wi is on the upper side, dielectric always EDiscrete, microfacet never sets it */
                 measure = discrete ? NB_MEASURE_DISCRETE
-                        : (bsdf.type == NB_BSDF_DIFFUSE && wi.z > 0.f) ? NB_MEASURE_SOLID_ANGLE : NB_MEASURE_UNKNOWN;
+                        : ((bsdf.type == NB_BSDF_DIFFUSE || bsdf.type == NB_BSDF_DISNEY) && wi.z > 0.f) ? NB_MEASURE_SOLID_ANGLE : NB_MEASURE_UNKNOWN;
                 ps.pdfmat = pdf;
                 ps.Li += nb_vol_sample_emitter<FLAT, EXT>(sc, ps, medium, its, sh, measure, &bsdf, nullptr, n_closest);
             }
@@ -456,7 +491,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 }
             }
         } else if (active) {
-            const f3 Li = nb_direct_sample<INTEG, FLAT, EXT>(sc, ps, n_closest, n_any);
+            const f3 Li = nb_direct_sample<INTEG, FLAT, EXT>(sc, tp.plan, ps, n_closest, n_any);
             nb_film_put(film, ps.px, ps.py, Li, stats);
             active = false;
         }
@@ -717,6 +752,9 @@ cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const Nb
         case NB_INTEGRATOR_DIRECT_MIS: return nb_tile_launch_t<NB_INTEGRATOR_DIRECT_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);
         case NB_INTEGRATOR_PATH_VOL_MATS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_VOL_MATS>(sc, film, tp, item_counter, stats, sm_count, stream);
         case NB_INTEGRATOR_PATH_VOL_MIS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_VOL_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_NORMALS: return nb_tile_launch_t<NB_INTEGRATOR_NORMALS>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_AV: return nb_tile_launch_t<NB_INTEGRATOR_AV>(sc, film, tp, item_counter, stats, sm_count, stream);
+        case NB_INTEGRATOR_PREVIEW: return nb_tile_launch_t<NB_INTEGRATOR_PREVIEW>(sc, film, tp, item_counter, stats, sm_count, stream);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -4,6 +4,7 @@
  * free path and transmittance: as means over `samples` draws), not only through rendered images. */
 #include "nb_internal.h"
 #include "nb_volume.cuh"
+#include "nb_shading.cuh"
 
 __global__ void nb_k_medium_probe(NbDeviceScene sc, int32_t medium, const float4 *rays, uint64_t n, uint32_t samples, uint64_t seed, float4 *out) {
     const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -36,7 +37,7 @@ __global__ void nb_k_emitter_probe(NbDeviceScene sc, uint32_t emitter, const flo
     const f3 v = nb_emitter_sample(sc, emitter, ref, s, es);
     f3 e = mk3(0.f);
     if (em.type == NB_EMITTER_ENVMAP) e = nb_env_eval(sc, emitter, es.wi);
-    else if (em.type == NB_EMITTER_POINT) e = v;
+    else if (em.type == NB_EMITTER_POINT || em.type == NB_EMITTER_SPOT) e = v;
     else e = v * es.pdf;
     float *o = out + 12 * i;
     o[0] = es.wi.x; o[1] = es.wi.y; o[2] = es.wi.z; o[3] = v.x; o[4] = v.y; o[5] = v.z;
@@ -82,5 +83,45 @@ extern "C" int nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, 
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(d_rays); cudaFree(d_out);
     if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_medium_probe: %s", cudaGetErrorString(e));
+    return NB_OK;
+}
+
+/* BSDF::eval / pdf / sample on fixed (wi, wo, sample, uv) records: the row of every BSDF plugin */
+__global__ void nb_k_bsdf_probe(NbDeviceScene sc, uint32_t index, const float *in, uint64_t n, float *out) {
+    const uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *r = in + 10 * i;
+    const f3 wi = mk3(r[0], r[1], r[2]), wo = mk3(r[3], r[4], r[5]);
+    float2 s; s.x = r[6]; s.y = r[7];
+    float2 uv; uv.x = r[8]; uv.y = r[9];
+    nb_bsdf b = sc.bsdfs[index];
+    nb_bsdf_resolve<true>(sc, b, uv);
+    const f3 e = nb_bsdf_eval<true>(b, wi, wo, sc.params);
+    const float pdf = nb_bsdf_pdf<true>(b, wi, wo);
+    f3 swo; bool discrete; float spdf;
+    const f3 w = nb_bsdf_sample<true>(b, wi, s, swo, discrete, spdf, sc.params);
+    float *o = out + 12 * i;
+    o[0] = e.x; o[1] = e.y; o[2] = e.z; o[3] = pdf; o[4] = w.x; o[5] = w.y; o[6] = w.z;
+    o[7] = swo.x; o[8] = swo.y; o[9] = swo.z; o[10] = discrete ? 1.f : 0.f; o[11] = spdf;
+}
+
+extern "C" int nb_bsdf_probe(nb_ctx *ctx, uint32_t bsdf, const float *in, uint64_t n, float *out) {
+    if (!ctx) return NB_E_INVALID;
+    if (!ctx->scene_ready) return nb_fail(ctx, NB_E_STATE, "nb_bsdf_probe: upload a scene first");
+    if (bsdf >= ctx->dev.n_bsdfs) return nb_fail(ctx, NB_E_INVALID, "nb_bsdf_probe: bsdf %u out of range", bsdf);
+    if (n == 0) return NB_OK;
+    if (!in || !out) return nb_fail(ctx, NB_E_INVALID, "nb_bsdf_probe: null argument");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    float *d_in = nullptr, *d_out = nullptr;
+    NB_CUDA(ctx, cudaMalloc((void **) &d_in, n * 40));
+    cudaError_t e = cudaMalloc((void **) &d_out, n * 48);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, in, n * 40, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) {
+        nb_k_bsdf_probe<<<(unsigned) ((n + 127) / 128), 128, 0, ctx->stream>>>(ctx->dev, bsdf, d_in, n, d_out);
+        e = cudaMemcpyAsync(out, d_out, n * 48, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_bsdf_probe: %s", cudaGetErrorString(e));
     return NB_OK;
 }

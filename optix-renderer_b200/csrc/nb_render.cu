@@ -69,7 +69,7 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
     const nb_shape sh = sc.shapes[sid];
     NbIts its;
     its.shape = sid;
-    if (sh.type == NB_SHAPE_SPHERE) nb_sphere_hit_info(sh, o, d, hit.x, its);
+    if (sh.type == NB_SHAPE_SPHERE) nb_sphere_hit_info(sc, sh, o, d, hit.x, its);
     else nb_mesh_hit_info(sc, sh, prim, hit.y, hit.z, its);
     const float n_lights = (float) sc.n_emitters;
 
@@ -121,10 +121,10 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
         const f3 ems_col = nb_emitter_sample(sc, ei, its.p, s, es);
         if (!is_zero(ems_col, NB_EPS)) {
             const f3 we = its.sh.to_local(es.wi);
-            const f3 f = nb_bsdf_eval(bsdf, wi, we);
+            const f3 f = nb_bsdf_eval<true>(bsdf, wi, we, sc.params);
             const f3 C = thr * (ems_col * we.z * f * n_lights);
             if (!is_black(C)) {
-                const float pdf_b = nb_bsdf_pdf(bsdf, wi, we), pdf_e = es.pdf / n_lights;
+                const float pdf_b = nb_bsdf_pdf<true>(bsdf, wi, we), pdf_e = es.pdf / n_lights;
                 emit_shadow = true;
                 so.o = es.ray_o; so.d = es.ray_d; so.mint = es.ray_mint; so.maxt = es.ray_maxt;
                 so.c = C;
@@ -136,7 +136,7 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
     /* BSDF sampling (path_mis.cpp:108-146 / path_mats.cpp:63-74) */
     float2 s; s.x = rng.next_float(); s.y = rng.next_float();
     f3 wo; bool discrete; float pdfmat;
-    const f3 col = nb_bsdf_sample(bsdf, wi, s, wo, discrete, pdfmat);
+    const f3 col = nb_bsdf_sample<true>(bsdf, wi, s, wo, discrete, pdfmat, sc.params);
     uint32_t nf = (bounce + 1) << NB_BOUNCE_SHIFT;
     if (discrete) { nf |= NB_FLAG_DISCRETE; w_ems = 0.f; }
     if (!is_zero(col, NB_EPS)) nf |= NB_FLAG_BSDF_OK;
@@ -306,7 +306,8 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     switch (params->integrator) {
         case NB_INTEGRATOR_PATH_MIS: case NB_INTEGRATOR_PATH_MATS: case NB_INTEGRATOR_DIRECT:
         case NB_INTEGRATOR_DIRECT_EMS: case NB_INTEGRATOR_DIRECT_MATS: case NB_INTEGRATOR_DIRECT_MIS:
-        case NB_INTEGRATOR_PATH_VOL_MATS: case NB_INTEGRATOR_PATH_VOL_MIS: break;
+        case NB_INTEGRATOR_PATH_VOL_MATS: case NB_INTEGRATOR_PATH_VOL_MIS:
+        case NB_INTEGRATOR_NORMALS: case NB_INTEGRATOR_AV: case NB_INTEGRATOR_PREVIEW: break;
         default: return nb_fail(ctx, NB_E_UNSUPPORTED, "integrator tag %u has no kernel in this backend", params->integrator);
     }
     if ((params->integrator == NB_INTEGRATOR_PATH_MIS || params->integrator == NB_INTEGRATOR_DIRECT_MIS ||
@@ -404,6 +405,7 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     plan.npix = cam.width * cam.height; plan.width = cam.width;
     plan.total = (unsigned long long) passes * plan.npix;
     plan.seed = r->params.seed; plan.first = s0; plan.stride = stride; plan.max_depth = r->params.max_depth;
+    for (int i = 0; i < 3; ++i) plan.iparam[i] = r->params.integrator_params[i];
     cudaEventRecord(r->ev_begin, ctx->stream);
     if (plan.total == 0) { cudaEventRecord(r->ev_end, ctx->stream); return NB_OK; }
     const uint32_t integ = r->params.integrator;

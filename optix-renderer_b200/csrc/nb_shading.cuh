@@ -15,7 +15,16 @@ struct NbIts {          /* Intersection, include/nori/shape.h:44-76 */
 
 __device__ __forceinline__ f3 ld3(const float *a, size_t i) { return mk3(__ldg(a + 3 * i), __ldg(a + 3 * i + 1), __ldg(a + 3 * i + 2)); }
 
-/* Mesh::setHitInformation (src/shapes/mesh.cpp:141-196) without normal maps */
+/* Texture<Normal3f>::eval of a normal map (PNGTexture.cpp:125-163 with sRGB = false) */
+static __device__ __noinline__ float4 nb_normal_map_eval(const nb_texture *textures, const float *texels, uint32_t index, float u, float v) {
+    const float4 c = nb_texture_eval_raw(textures, texels, index, u, v);
+    const float k = textures[index].intensity;
+    const f3 n = normalize(mk3(c.x * k, c.y * k, c.z * k + (1.f - k)));
+    return make_float4(n.x, n.y, n.z, 0.f);
+}
+
+/* Mesh::setHitInformation (src/shapes/mesh.cpp:141-196); EXT: with the normal map of :168-180 */
+template <bool EXT = true>
 __device__ __forceinline__ void nb_mesh_hit_info(const NbDeviceScene &sc, const nb_shape &sh, uint32_t prim,
                                                  float u, float v, NbIts &its) {
     const float b0 = 1.f - (u + v), b1 = u, b2 = v;
@@ -36,6 +45,10 @@ __device__ __forceinline__ void nb_mesh_hit_info(const NbDeviceScene &sc, const 
             its.sh.s = normalize(b0 * ld3(sc.tangents, i0) + b1 * ld3(sc.tangents, i1) + b2 * ld3(sc.tangents, i2));
             its.sh.t = normalize(b0 * ld3(sc.bitangents, i0) + b1 * ld3(sc.bitangents, i1) + b2 * ld3(sc.bitangents, i2));
             its.sh.n = n;
+            if (EXT && sh.normal_map) {                           /* normal = (TBN * map(uv)).normalized() */
+                const float4 m = nb_normal_map_eval(sc.textures, sc.texels, sh.normal_map - 1u, its.uv.x, its.uv.y);
+                its.sh.n = normalize(its.sh.s * m.x + its.sh.t * m.y + n * m.z);
+            }
         } else {
             its.sh = frame_from_normal(n);
         }
@@ -44,8 +57,9 @@ __device__ __forceinline__ void nb_mesh_hit_info(const NbDeviceScene &sc, const 
     }
 }
 
-/* Sphere::setHitInformation (src/shapes/sphere.cpp:96-124) without normal maps */
-__device__ __forceinline__ void nb_sphere_hit_info(const nb_shape &sh, f3 o, f3 d, float t, NbIts &its) {
+/* Sphere::setHitInformation (src/shapes/sphere.cpp:96-124); EXT: with the normal map of :115-123 */
+template <bool EXT = true>
+__device__ __forceinline__ void nb_sphere_hit_info(const NbDeviceScene &sc, const nb_shape &sh, f3 o, f3 d, float t, NbIts &its) {
     its.p = o + d * t;
     const f3 c = mk3(sh.center[0], sh.center[1], sh.center[2]);
     const f3 n = normalize(its.p - c);
@@ -56,6 +70,12 @@ __device__ __forceinline__ void nb_sphere_hit_info(const nb_shape &sh, f3 o, f3 
     its.geo_n = n;
     const f3 tt = normalize(cross(mk3(0.f, 0.f, 1.f), n));
     its.sh.s = tt; its.sh.t = cross(n, tt); its.sh.n = n;
+    if (EXT && sh.normal_map) {
+        const float4 m = nb_normal_map_eval(sc.textures, sc.texels, sh.normal_map - 1u, its.uv.x, its.uv.y);
+        const f3 n2 = normalize(its.sh.to_world(mk3(m.x, m.y, m.z)));
+        const f3 t2 = normalize(cross(mk3(0.f, 0.f, 1.f), n2));
+        its.sh.s = t2; its.sh.t = cross(n2, t2); its.sh.n = n2;
+    }
 }
 
 /* fresnel(), src/utils/common.cpp:308-337 */
@@ -107,8 +127,72 @@ __device__ __forceinline__ float nb_microfacet_pdf(const nb_bsdf &b, f3 wi, f3 w
     return part1 + part2;
 }
 
+
+/* ---- disney (src/bsdf/disney.cpp:111-205, helpers :275-318) -----------------------------------
+ * Cold code, out of line (see nb_texture.cuh). `p` = the 10 clamped parameters in nb_bsdf order. */
+__device__ __forceinline__ float nb_schlick_weight(float a) {          /* SchlickFresnel, disney.cpp:289-294 */
+    const float m = fminf(fmaxf(1.f - a, 0.f), 1.f), m2 = m * m;
+    return m2 * m2 * m;
+}
+__device__ __forceinline__ float nb_mixf(float a, float b, float t) { return a + (b - a) * t; }
+__device__ __forceinline__ float nb_smith_ggx_aniso(float ndv, float vdx, float vdy, float ax, float ay) {
+    return 1.f / (ndv + sqrtf(vdx * ax * vdx * ax + vdy * ay * vdy * ay + ndv * ndv));
+}
+__device__ __forceinline__ float nb_smith_ggx(float ndv, float alphaG) {
+    const float a = alphaG * alphaG, b = ndv * ndv;
+    return 1.f / (ndv + sqrtf(a + b - a * b));
+}
+static __device__ __noinline__ float4 nb_disney_eval_raw(const float *p, float br, float bg, float bb,
+                                                         float lx, float ly, float lz, float vx, float vy, float vz) {
+    const f3 L = mk3(lx, ly, lz), V = mk3(vx, vy, vz);                  /* L = bRec.wi, V = bRec.wo */
+    const float NdotL = L.z, NdotV = V.z;
+    if (NdotL < NB_EPS || NdotV < NB_EPS) return make_float4(0.f, 0.f, 0.f, 0.f);
+    const float metallic = __ldg(p), subsurface = __ldg(p + 1), specular = __ldg(p + 2), roughness = __ldg(p + 3),
+                specularTint = __ldg(p + 4), anisotropic = __ldg(p + 5), sheen = __ldg(p + 6), sheenTint = __ldg(p + 7),
+                clearcoat = __ldg(p + 8), clearcoatGloss = __ldg(p + 9);
+    const f3 H = normalize(L + V);
+    const float NdotH = H.z, LdotH = dot(L, H);
+    const f3 Cdlin = mk3(powf(br, 2.2f), powf(bg, 2.2f), powf(bb, 2.2f));        /* mon2lin */
+    const float Cdlum = 0.3f * Cdlin.x + 0.6f * Cdlin.y + 0.1f * Cdlin.z;
+    const f3 Ctint = Cdlum > 0.f ? Cdlin / Cdlum : mk3(1.f);
+    const f3 one = mk3(1.f);
+    const f3 tint = one + (Ctint - one) * specularTint;
+    const f3 s0 = specular * 0.08f * tint;
+    const f3 Cspec0 = s0 + (Cdlin - s0) * metallic;
+    const f3 Csheen = one + (Ctint - one) * sheenTint;
+    const float FL = nb_schlick_weight(NdotL), FV = nb_schlick_weight(NdotV);
+    const float Fd90 = 0.5f + 2.f * LdotH * LdotH * roughness;
+    const float Fd = nb_mixf(1.f, Fd90, FL) * nb_mixf(1.f, Fd90, FV);
+    const float Fss90 = LdotH * LdotH * roughness;
+    const float Fss = nb_mixf(1.f, Fss90, FL) * nb_mixf(1.f, Fss90, FV);
+    const float ss = 1.25f * (Fss * (1.f / (NdotL + NdotV) - 0.5f) + 0.5f);
+    const float aspect = sqrtf(1.f - anisotropic * 0.9f);
+    const float ax = fmaxf(0.001f, roughness * roughness / aspect), ay = fmaxf(0.001f, roughness * roughness * aspect);
+    const float hx = H.x / ax, hy = H.y / ay, q = hx * hx + hy * hy + NdotH * NdotH;
+    const float Ds = 1.f / (NB_PI * ax * ay * q * q);                    /* GTR2_aniso */
+    const float FH = nb_schlick_weight(LdotH);
+    const f3 Fs = Cspec0 + (one - Cspec0) * FH;
+    const float Gs = nb_smith_ggx_aniso(NdotL, L.x, L.y, ax, ay) * nb_smith_ggx_aniso(NdotV, V.x, V.y, ax, ay);
+    const f3 Fsheen = FH * sheen * Csheen;
+    const float a = nb_mixf(0.1f, 0.001f, clearcoatGloss);               /* GTR1(NdotH, a): a < 1 always */
+    const float a2 = a * a, t = 1.f + (a2 - 1.f) * NdotH * NdotH;
+    const float Dr = (a2 - 1.f) / (NB_PI * logf(a2) * t);
+    const float Fr = nb_mixf(0.04f, 1.f, FH);
+    const float Gr = nb_smith_ggx(NdotL, 0.25f) * nb_smith_ggx(NdotV, 0.25f);
+    f3 c = (NB_INV_PI * nb_mixf(Fd, ss, subsurface) * Cdlin + Fsheen) * (1.f - metallic) + Gs * Ds * Fs + mk3(0.25f * clearcoat * Gr * Fr * Dr);
+    const float lum = nb_luminance(c);
+    if (lum > 1.f) c = c / lum;
+    return make_float4(c.x, c.y, c.z, 0.f);
+}
+__device__ __forceinline__ f3 nb_disney_eval(const nb_bsdf &b, f3 wi, f3 wo, const float *params) {
+    const float4 r = nb_disney_eval_raw(params + __float_as_uint(b.alpha), b.albedo[0], b.albedo[1], b.albedo[2], wi.x, wi.y, wi.z, wo.x, wo.y, wo.z);
+    return mk3(r.x, r.y, r.z);
+}
+
 /* BSDF::eval for measure ESolidAngle */
-__device__ __forceinline__ f3 nb_bsdf_eval(const nb_bsdf &b, f3 wi, f3 wo) {
+template <bool EXT = true>
+__device__ __forceinline__ f3 nb_bsdf_eval(const nb_bsdf &b, f3 wi, f3 wo, const float *params) {
+    if (EXT && b.type == NB_BSDF_DISNEY) return nb_disney_eval(b, wi, wo, params);
     switch (b.type) {
         case NB_BSDF_DIFFUSE:                                  /* diffuse.cpp:94-103 */
             if (wi.z <= 0.f || wo.z <= 0.f) return mk3(0.f);
@@ -118,8 +202,11 @@ __device__ __forceinline__ f3 nb_bsdf_eval(const nb_bsdf &b, f3 wi, f3 wo) {
     }
 }
 /* BSDF::pdf for measure ESolidAngle */
+template <bool EXT = true>
 __device__ __forceinline__ float nb_bsdf_pdf(const nb_bsdf &b, f3 wi, f3 wo) {
     switch (b.type) {
+        case NB_BSDF_DISNEY:                                   /* disney.cpp:196-203: the same cosine density */
+            if (!EXT) return 0.f;
         case NB_BSDF_DIFFUSE:                                  /* diffuse.cpp:106-120 */
             if (wi.z <= 0.f || wo.z <= 0.f) return 0.f;
             return NB_INV_PI * wo.z;
@@ -130,8 +217,16 @@ __device__ __forceinline__ float nb_bsdf_pdf(const nb_bsdf &b, f3 wi, f3 wo) {
 
 /* BSDF::sample. Returns the weight; sets wo, `discrete` (measure == EDiscrete) and `pdf`
  * (= bsdf->pdf(bRec) for the sampled direction, needed by the MIS probe, path_mis.cpp:126). */
-__device__ __forceinline__ f3 nb_bsdf_sample(const nb_bsdf &b, f3 wi, float2 s, f3 &wo, bool &discrete, float &pdf) {
+template <bool EXT = true>
+__device__ __forceinline__ f3 nb_bsdf_sample(const nb_bsdf &b, f3 wi, float2 s, f3 &wo, bool &discrete, float &pdf, const float *params) {
     discrete = false; pdf = 0.f; wo = mk3(0.f, 0.f, 1.f);
+    if (EXT && b.type == NB_BSDF_DISNEY) {                      /* disney.cpp:171-194: cosine lobe, returns eval() as is */
+        if (wi.z <= 0.f) return mk3(0.f);
+        wo = square_to_cosine_hemisphere(s);
+        pdf = wo.z <= 0.f ? 0.f : NB_INV_PI * wo.z;
+        if (pdf < NB_EPS) return mk3(0.f);
+        return nb_disney_eval(b, wi, wo, params);
+    }
     switch (b.type) {
         case NB_BSDF_DIFFUSE: {                                /* diffuse.cpp:123-140 */
             if (wi.z <= 0.f) return mk3(0.f);
@@ -223,6 +318,51 @@ __device__ __forceinline__ f3 nb_env_sample(const NbDeviceScene &sc, const nb_em
     return mk3(ep.x, ep.y, ep.z) / out.pdf;
 }
 
+
+/* SpotLight::{sample,eval,falloff} (src/emitters/spotlight.cpp:53-72, 167-187) and DirectionalLight::{sample,
+ * pdf,eval} (src/emitters/directionalLight.cpp:90-133; Warp::squareToUniformSphereCap{,Pdf} warp.cpp:58-72).
+ * Cold code, out of line. p = the emitter's nb_scene_desc.params block. */
+struct NbF8 { float4 a, b; };    /* { value rgb, pdf } { wi xyz, shadow-ray maxt }: returned by value so the caller's record stays in registers */
+static __device__ __noinline__ NbF8 nb_spot_dir_sample(const float *p, const nb_emitter *emp, float rx, float ry, float rz,
+                                                       float sx, float sy) {
+    const nb_emitter em = *emp;
+    NbEmitterSample out;
+    const f3 ref = mk3(rx, ry, rz), dir = mk3(__ldg(p), __ldg(p + 1), __ldg(p + 2));
+    const NbFrame coord = frame_from_normal(dir);                         /* m_coord = Frame(m_direction) */
+    const f3 rad = mk3(em.radiance[0], em.radiance[1], em.radiance[2]);
+    f3 ret;
+    if (em.type == NB_EMITTER_SPOT) {
+        const f3 pos = mk3(em.position[0], em.position[1], em.position[2]);
+        const float cosStart = __ldg(p + 3), cosTotal = __ldg(p + 4);
+        const f3 dlt = pos - ref;
+        out.wi = normalize(dlt);
+        out.ray_o = pos; out.ray_d = -out.wi; out.ray_mint = NB_EPS; out.ray_maxt = length(dlt) - NB_EPS;
+        out.pdf = 1.f;
+        const float ct = normalize(coord.to_local(-out.wi)).z;             /* falloff(-lRec.wi) */
+        float fall;
+        if (ct < cosTotal) fall = 0.f;
+        else if (ct >= cosStart) fall = 1.f;
+        else { const float d = (ct - cosTotal) / (cosStart - cosTotal); fall = (d * d) * (d * d); }
+        const f3 i = rad / (1.f - .5f * (cosTotal + cosStart));
+        const f3 rp = ref - pos;
+        ret = i * fall / dot(rp, rp);
+    } else {
+        const float cosMax = __ldg(p + 3);
+        const float z = sx * (1.0f - cosMax) + cosMax, r = sqrtf(1.0f - z * z), th = sy * 2.0f * NB_PI;
+        float sn, cs; __sincosf(th, &sn, &cs);
+        const f3 w = normalize(coord.to_world(mk3(r * cs, r * sn, z)));
+        out.wi = -w;
+        out.ray_o = ref; out.ray_d = out.wi; out.ray_mint = NB_EPS; out.ray_maxt = INFINITY;   /* Ray3f(ref, wi) defaults */
+        const f3 lv = coord.to_local(w);
+        out.pdf = (fabsf(dot(lv, lv) - 1.0f) < NB_EPS && lv.z <= cosMax) ? 0.0f : 1.0f / (2.0f * NB_PI * (1.0f - cosMax));
+        ret = out.pdf < NB_EPS ? mk3(0.f) : rad / out.pdf;
+    }
+    NbF8 r;
+    r.a = make_float4(ret.x, ret.y, ret.z, out.pdf);
+    r.b = make_float4(out.wi.x, out.wi.y, out.wi.z, out.ray_maxt);
+    return r;
+}
+
 /* Emitter::sample for area (arealight.cpp:75-103 -> mesh.cpp:50-71 / sphere.cpp:126-132) and
  * point lights (pointlight.cpp:47-63). Returns radiance / pdf. */
 template <bool EXT = true>
@@ -239,6 +379,13 @@ __device__ __forceinline__ f3 nb_emitter_sample(const NbDeviceScene &sc, uint32_
         return mk3(em.radiance[0], em.radiance[1], em.radiance[2]) / dot(dlt, dlt);
     }
     if (EXT && em.type == NB_EMITTER_ENVMAP) return nb_env_sample(sc, sc.emitters + emitter, ref, s, out);
+    if (EXT && em.type >= NB_EMITTER_SPOT) {
+        const NbF8 r = nb_spot_dir_sample(sc.params + em.shape, sc.emitters + emitter, ref.x, ref.y, ref.z, s.x, s.y);
+        out.wi = mk3(r.b.x, r.b.y, r.b.z); out.pdf = r.a.w; out.ray_mint = NB_EPS; out.ray_maxt = r.b.w;
+        if (em.type == NB_EMITTER_SPOT) { out.ray_o = mk3(em.position[0], em.position[1], em.position[2]); out.ray_d = -out.wi; }
+        else { out.ray_o = ref; out.ray_d = out.wi; }
+        return mk3(r.a.x, r.a.y, r.a.z);
+    }
     const nb_shape sh = sc.shapes[em.shape];
     f3 p, n;
     if (sh.type == NB_SHAPE_SPHERE) {

@@ -87,16 +87,44 @@ private:
 };
 NORI_REGISTER_CLASS(Microfacet, "microfacet")
 
-/* A plugin the parser must accept so scenes load, but for which the backend has no kernel:
- * flatten() reports it and the caller keeps its CPU path. */
-class UnsupportedBSDF : public BSDF {
+/* src/bsdf/disney.cpp:19-109: ten scalars clamped to [0, 1], base colour constant (default 0.5) or an "albedo" texture */
+class Disney : public BSDF {
 public:
-    explicit UnsupportedBSDF(const PropertyList &) {}
-    void addChild(NoriObject *obj) override { delete obj; }
-    bool getB200MaterialData(nb_bsdf &, FlatScene &) const override { return false; }
-    std::string toString() const override { return "UnsupportedBSDF[]"; }
+    explicit Disney(const PropertyList &p) : m_albedo(p.getColor("albedo", Color3f(0.5f))), m_hasConstant(p.has("albedo")) {
+        auto c = [&](const char *n, float d) { return std::min(std::max(p.getFloat(n, d), 0.f), 1.f); };
+        m_p[0] = c("metallic", 0.f); m_p[1] = c("subsurface", 0.f); m_p[2] = c("specular", 0.5f); m_p[3] = c("roughness", 0.5f);
+        m_p[4] = c("specularTint", 0.f); m_p[5] = c("anisotropic", 0.f); m_p[6] = c("sheen", 0.f); m_p[7] = c("sheenTint", 0.5f);
+        m_p[8] = c("clearcoat", 0.f); m_p[9] = c("clearcoatGloss", 1.f);
+    }
+    ~Disney() override { delete m_texture; }
+    void addChild(NoriObject *obj) override {
+        if (obj->getClassType() != ETexture) throw NoriException("Disney::addChild(<%s>) is not supported!", classTypeName(obj->getClassType()));
+        if (obj->getIdName() != "albedo") throw NoriException("The name of this texture does not match any field!");
+        if (m_texture || m_hasConstant) throw NoriException("There is already an albedo defined!");
+        m_texture = static_cast<Texture *>(obj);
+    }
+    bool getB200MaterialData(nb_bsdf &o, FlatScene &flat) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_BSDF_DISNEY;
+        for (int i = 0; i < 3; ++i) o.albedo[i] = m_albedo[i];
+        if (m_texture) {
+            const int t = m_texture->getB200Texture(flat);
+            if (t < 0) return false;
+            o.type |= (uint32_t) (t + 1) << 8;
+        }
+        const uint32_t off = (uint32_t) flat.params.size();
+        memcpy(&o.alpha, &off, 4);
+        flat.params.insert(flat.params.end(), m_p, m_p + 10);
+        return true;
+    }
+    std::string toString() const override { return NoriException::format("Disney[metallic=%f, roughness=%f]", m_p[0], m_p[3]); }
+private:
+    Color3f m_albedo;
+    bool m_hasConstant;
+    Texture *m_texture = nullptr;
+    float m_p[10];
 };
-NORI_REGISTER_CLASS(UnsupportedBSDF, "disney")
+NORI_REGISTER_CLASS(Disney, "disney")
 
 /* ---- emitters ---------------------------------------------------------------------------------- */
 class AreaEmitter : public Emitter {                /* src/emitters/arealight.cpp:27-33 */
@@ -130,6 +158,56 @@ private:
     Point3f m_position;
 };
 NORI_REGISTER_CLASS(PointLight, "point")
+
+class SpotLight : public Emitter {                  /* src/emitters/spotlight.cpp:14-24, 48-49 */
+public:
+    explicit SpotLight(const PropertyList &p) {
+        m_position = p.getPoint3("position", Point3f());
+        m_direction = p.getVector3("direction", Vector3f()).normalized();
+        m_power = p.getColor("power", Color3f());
+        m_falloffStart = p.getFloat("falloffstart");
+        m_totalWidth = p.getFloat("totalwidth");
+        lightProb = p.getFloat("lightWeight", 1.f);
+        m_radiance = m_power / 2.f / (float) M_PI;                       /* spotlight.cpp:49, set by the first update() */
+    }
+    bool getB200EmitterData(nb_emitter &o, FlatScene &flat) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_EMITTER_SPOT; o.shape = (int32_t) flat.params.size();
+        for (int i = 0; i < 3; ++i) { o.radiance[i] = m_radiance[i]; o.position[i] = m_position[i]; flat.params.push_back(m_direction[i]); }
+        flat.params.push_back(std::cos(refDegToRad(m_falloffStart)));    /* spotlight.cpp:65-66, 169-170 */
+        flat.params.push_back(std::cos(refDegToRad(m_totalWidth / 2.f)));
+        return true;
+    }
+    std::string toString() const override { return "Spotlight[]"; }
+    static float refDegToRad(float v) { return (float) (v * (M_PI / 180.0f)); }   /* common.h:218: the product is formed in double */
+private:
+    Point3f m_position;
+    Vector3f m_direction;
+    Color3f m_power;
+    float m_falloffStart, m_totalWidth;
+};
+NORI_REGISTER_CLASS(SpotLight, "spot")
+
+class DirectionalLight : public Emitter {           /* src/emitters/directionalLight.cpp:31-38 */
+public:
+    explicit DirectionalLight(const PropertyList &p) {
+        m_direction = p.getVector3("direction", Vector3f(0, 0, 1)).normalized();
+        m_radiance = p.getColor("radiance", Color3f(0.f));
+        m_angle = p.getFloat("angle", 1.f);
+    }
+    bool getB200EmitterData(nb_emitter &o, FlatScene &flat) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_EMITTER_DIRECTIONAL; o.shape = (int32_t) flat.params.size();
+        for (int i = 0; i < 3; ++i) { o.radiance[i] = m_radiance[i]; flat.params.push_back(m_direction[i]); }
+        flat.params.push_back((float) std::cos((double) SpotLight::refDegToRad(m_angle)));   /* cos(degToRad(m_angle)): the unqualified cos(float) is ::cos(double) */
+        return true;
+    }
+    std::string toString() const override { return "DirectionalLight[]"; }
+private:
+    Vector3f m_direction;
+    float m_angle;
+};
+NORI_REGISTER_CLASS(DirectionalLight, "directional")
 
 /* ---- reconstruction filters (src/cameras/rfilter.cpp) -------------------------------------------- */
 class GaussianFilter : public ReconstructionFilter {                     /* rfilter.cpp:30-47 */
@@ -237,12 +315,30 @@ NB_INTEGRATOR_CLASS(DirectEMSIntegrator, "direct_ems", NB_INTEGRATOR_DIRECT_EMS)
 NB_INTEGRATOR_CLASS(DirectMATSIntegrator, "direct_mats", NB_INTEGRATOR_DIRECT_MATS)
 NB_INTEGRATOR_CLASS(DirectMISIntegrator, "direct_mis", NB_INTEGRATOR_DIRECT_MIS)
 NB_INTEGRATOR_CLASS(DirectIntegrator, "direct", NB_INTEGRATOR_DIRECT)
-NB_INTEGRATOR_CLASS(NormalIntegrator, "normals", NB_INTEGRATOR_NORMALS)
-NB_INTEGRATOR_CLASS(AverageVisibility, "av", NB_INTEGRATOR_AV)
+class NormalIntegrator : public Integrator {        /* src/integrators/normals.cpp:11-13 */
+public:
+    explicit NormalIntegrator(const PropertyList &p) : m_direction(p.getPoint3("direction", Point3f(0, 0, 1))) {}
+    int getB200IntegratorType() const override { return NB_INTEGRATOR_NORMALS; }
+    void getB200IntegratorParams(float out[3]) const override { for (int i = 0; i < 3; ++i) out[i] = m_direction[i]; }
+    std::string toString() const override { return "NormalIntegrator[]"; }
+private:
+    Vector3f m_direction;
+};
+NORI_REGISTER_CLASS(NormalIntegrator, "normals")
+class AverageVisibility : public Integrator {       /* src/integrators/av.cpp:12-15 */
+public:
+    explicit AverageVisibility(const PropertyList &p) : m_length(p.getFloat("length")) {}
+    int getB200IntegratorType() const override { return NB_INTEGRATOR_AV; }
+    void getB200IntegratorParams(float out[3]) const override { out[0] = m_length; }
+    std::string toString() const override { return NoriException::format("AverageVisibilityIntegrator[length=%f]", m_length); }
+private:
+    float m_length;
+};
+NORI_REGISTER_CLASS(AverageVisibility, "av")
 NB_INTEGRATOR_CLASS(PathVolMATSIntegrator, "path_vol_mats", NB_INTEGRATOR_PATH_VOL_MATS)
 NB_INTEGRATOR_CLASS(PathVolMISIntegrator, "path_vol_mis", NB_INTEGRATOR_PATH_VOL_MIS)
 NB_INTEGRATOR_CLASS(PhotonMapper, "photonmapper", -1)
-NB_INTEGRATOR_CLASS(PreviewIntegrator, "preview", -1)
+NB_INTEGRATOR_CLASS(PreviewIntegrator, "preview", NB_INTEGRATOR_PREVIEW)
 
 class Independent : public Sampler {                /* src/samplers/independent.cpp:35-39 */
 public:
@@ -425,7 +521,7 @@ private:
 };
 NORI_REGISTER_CLASS(HeterogeneousMedium, "heterog")
 
-Shape::~Shape() { delete m_bsdf; delete m_emitter; delete m_medium; }
+Shape::~Shape() { delete m_bsdf; delete m_emitter; delete m_medium; delete m_normalMap; }
 
 void Shape::addChild(NoriObject *obj) {
     switch (obj->getClassType()) {
@@ -441,6 +537,11 @@ void Shape::addChild(NoriObject *obj) {
         case EMedium:
             if (m_medium) throw NoriException("Shape: tried to register multiple medium instances!");
             m_medium = static_cast<Medium *>(obj);
+            break;
+        case ETexture:                                                   /* shape.cpp:139-148 */
+            if (obj->getIdName() != "normal") throw NoriException("Shape does not have a texture with name: %s", obj->getIdName());
+            if (m_normalMap) throw NoriException("There is already a normal map defined!");
+            m_normalMap = static_cast<Texture *>(obj);
             break;
         default:
             throw NoriException("Shape::addChild(<%s>) is not supported!", classTypeName(obj->getClassType()));

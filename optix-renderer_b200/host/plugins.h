@@ -85,6 +85,7 @@ public:
     const BSDF *getBSDF() const { return m_bsdf; }
     const Medium *getMedium() const { return m_medium; }
     Emitter *getEmitter() const { return m_emitter; }
+    const Texture *getNormalMap() const { return m_normalMap; }
     bool isEmitter() const { return m_emitter != nullptr; }
     /* replaces getOptixBuildInput / getOptixHitgroupRecords (shape.h:194-201): appends this
      * shape's geometry to the flat arrays and fills the geometric part of the record */
@@ -93,6 +94,7 @@ protected:
     BSDF *m_bsdf = nullptr;
     Emitter *m_emitter = nullptr;
     Medium *m_medium = nullptr;
+    Texture *m_normalMap = nullptr;                     /* shape.h:226: Texture<Normal3f>, a png_texture named "normal" */
     BoundingBox3f m_bbox;
 };
 
@@ -143,6 +145,7 @@ class Integrator : public NoriObject {
 public:
     EClassType getClassType() const override { return EIntegrator; }
     virtual int getB200IntegratorType() const = 0;                    /* replaces getOptixIntegratorType (integrator.h:91); -1 = none */
+    virtual void getB200IntegratorParams(float out[3]) const { (void) out; }   /* nb_render_params.integrator_params */
 };
 
 class Sampler : public NoriObject {
@@ -164,6 +167,7 @@ struct FlatScene {
     std::vector<float> density;                         /* voxel arrays of heterogeneous media */
     std::vector<nb_texture> textures;
     std::vector<float> texels;                          /* RGBA */
+    std::vector<float> params;                          /* nb_scene_desc.params */
     int32_t ambient_medium = -1;
     nb_camera camera;
     nb_render_params render;

@@ -83,6 +83,11 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
             rec.bsdf = (int32_t) out.bsdfs.size();
             out.bsdfs.push_back(b);
         }
+        if (s->getNormalMap()) {
+            const int t = s->getNormalMap()->getB200Texture(out);
+            if (t < 0 || !(out.textures[t].flags & NB_TEXTURE_NORMAL_MAP)) return fail("normal map '" + s->getNormalMap()->toString() + "' has no GPU kernel");
+            rec.normal_map = (uint32_t) t + 1u;
+        }
         if (s->getMedium()) {
             nb_medium m;
             if (!s->getMedium()->getB200MediumData(m, out)) return fail("medium '" + s->getMedium()->toString() + "' has no GPU kernel");
@@ -113,6 +118,7 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
     m_camera->getB200Data(out.camera);
     memset(&out.render, 0, sizeof(out.render));
     out.render.integrator = (uint32_t) m_integrator->getB200IntegratorType();
+    m_integrator->getB200IntegratorParams(out.render.integrator_params);
     const ReconstructionFilter *rf = m_camera->getReconstructionFilter();
     out.render.filter_radius = rf->getRadius();
     for (int i = 0; i < NB_FILTER_RESOLUTION; ++i)
@@ -143,6 +149,7 @@ nb_scene_desc FlatScene::desc() const {
     d.n_density = density.size(); d.density = density.empty() ? nullptr : density.data();
     d.n_textures = (uint32_t) textures.size(); d.textures = textures.empty() ? nullptr : textures.data();
     d.n_texels = texels.size() / 4; d.texels = texels.empty() ? nullptr : texels.data();
+    d.n_params = params.size(); d.params = params.empty() ? nullptr : params.data();
     return d;
 }
 
@@ -165,6 +172,7 @@ void FlatScene::writeNbs(const std::string &path) const {
     }
     if (!textures.empty()) secs.push_back({ "textures", sizeof(nb_texture), textures.data(), textures.size() });
     if (!texels.empty()) secs.push_back({ "texels", 4, texels.data(), texels.size() });
+    if (!params.empty()) secs.push_back({ "params", 4, params.data(), params.size() });
     secs.push_back({ "camera", sizeof(nb_camera), &camera, 1 });
     secs.push_back({ "render", sizeof(nb_render_params), &render, 1 });
     secs.push_back({ "spp", 4, &spp, 1 });

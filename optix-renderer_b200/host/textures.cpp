@@ -69,6 +69,7 @@ public:
         m_euler = p.getVector3("eulerAngles", Vector3f(0.f)) * (float) M_PI / 180.f;
         m_spherical = p.getBoolean("sphericalTexture", false);
         m_offsetU = p.getFloat("offsetU", 0.f); m_offsetV = p.getFloat("offsetV", 0.f);
+        m_intensity = p.getFloat("intensity", 1.f);
     }
     void activate() override {                                           /* loadFromFile, PNGTexture.cpp:68-123 */
         const size_t dot = m_filename.rfind('.');
@@ -77,8 +78,16 @@ public:
         std::vector<uint8_t> tmp;
         decodePng(m_filename, tmp, m_width, m_height);
         m_data.resize(tmp.size());
-        if (!m_sRgb) { m_supported = false; return; }                    /* normal maps: no kernel */
-        for (size_t i = 0; i < tmp.size(); ++i) m_data[i] = inverseGammaCorrect((float) tmp[i] / 255.f);
+        if (m_sRgb) for (size_t i = 0; i < tmp.size(); ++i) m_data[i] = inverseGammaCorrect((float) tmp[i] / 255.f);
+        else                                                             /* normal map, PNGTexture.cpp:88-99 as written: every third float */
+            for (size_t i = 0; i < tmp.size(); ++i) {                    /* closes a triple that is normalized in place, across the RGBA stride */
+                m_data[i] = (float) tmp[i] / 255 * 2 - 1;
+                if ((i + 1) % 3 == 0) {
+                    float *v = m_data.data() + i - 2;
+                    const float z = v[0] * v[0] + (v[1] * v[1] + v[2] * v[2]);
+                    if (z > 0.f) { const float n = std::sqrt(z); v[0] /= n; v[1] /= n; v[2] /= n; }
+                }
+            }
         /* the rotation PNGTexture::eval builds per call: Quaternion(Identity * AngleAxis(e.x, Z) * AngleAxis(e.y, X))
          * * AngleAxis(e.z, Z).toRotationMatrix() */
         float q[4] = { 1, 0, 0, 0 };                                     /* w, x, y, z */
@@ -101,14 +110,17 @@ public:
         const unsigned w = static_cast<unsigned>(u * m_scaleU * (float) m_width);
         const unsigned h = m_height - static_cast<unsigned>(v * m_scaleV * (float) m_height);
         const unsigned index = (h * m_width + w) % (m_width * m_height);
-        return Color3f(m_data[4 * index], m_data[4 * index + 1], m_data[4 * index + 2]);
+        Color3f out(m_data[4 * index], m_data[4 * index + 1], m_data[4 * index + 2]);
+        if (!m_sRgb) out = Color3f(out[0] * m_intensity, out[1] * m_intensity, out[2] * m_intensity + (1.f - m_intensity)).normalized();
+        return out;
     }
     unsigned getWidth() const override { return m_width; }
     unsigned getHeight() const override { return m_height; }
     int getB200Texture(FlatScene &flat) const override {
         if (!m_supported || m_width == 0) return -1;
         nb_texture t; memset(&t, 0, sizeof(t));
-        t.type = NB_TEXTURE_IMAGE; t.flags = m_spherical ? NB_TEXTURE_SPHERICAL : 0u;
+        t.type = NB_TEXTURE_IMAGE; t.flags = (m_spherical ? NB_TEXTURE_SPHERICAL : 0u) | (m_sRgb ? 0u : NB_TEXTURE_NORMAL_MAP);
+        t.intensity = m_intensity;
         t.width = m_width; t.height = m_height; t.first_texel = (uint32_t) (flat.texels.size() / 4);
         t.scale[0] = m_scaleU; t.scale[1] = m_scaleV; t.offset[0] = m_offsetU; t.offset[1] = m_offsetV;
         memcpy(t.rotation, m_rot, sizeof(m_rot));
@@ -141,7 +153,7 @@ private:
     }
     std::string m_filename;
     bool m_sRgb = true, m_spherical = false, m_supported = true;
-    float m_scaleU = 1, m_scaleV = 1, m_offsetU = 0, m_offsetV = 0;
+    float m_scaleU = 1, m_scaleV = 1, m_offsetU = 0, m_offsetV = 0, m_intensity = 1;
     Vector3f m_euler;
     unsigned m_width = 0, m_height = 0;
     std::vector<float> m_data;

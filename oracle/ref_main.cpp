@@ -718,6 +718,50 @@ static int modeEmitter(int argc, char **argv) {
     return 0;
 }
 
+/* BSDF::eval / pdf / sample of the BSDF of shape `index` on fixed records (include/nori/bsdf.h:33-76):
+ * in = 10 floats {wi, wo, sample, uv}; out = 12 floats {eval rgb, pdf, sample weight rgb, sampled wo,
+ * measure == EDiscrete, pdf of the sampled direction} — the layout of nb_bsdf_probe. */
+static int modeBsdf(int argc, char **argv) {
+    if (argc < 5) return 2;
+    auto kv = parseKv(argc, argv, 5);
+    const size_t index = kv.count("index") ? (size_t) std::stoi(kv["index"]) : 0;
+    LoadedScene ls = loadScene(argv[2]);
+    const auto &shapes = ls.render->getShapes();
+    if (index >= shapes.size() || !shapes[index]->getBSDF()) throw NoriException("shape %d has no bsdf", (int) index);
+    const BSDF *bsdf = shapes[index]->getBSDF();
+    FILE *f = fopen(argv[3], "rb");
+    if (!f) throw NoriException("cannot read %s", argv[3]);
+    fseek(f, 0, SEEK_END); const size_t n = (size_t) ftell(f) / 40; fseek(f, 0, SEEK_SET);
+    std::vector<float> in(n * 10), out(n * 12, 0.f);
+    if (fread(in.data(), 40, n, f) != n) throw NoriException("short read on %s", argv[3]);
+    fclose(f);
+    for (size_t i = 0; i < n; ++i) {
+        const float *r = &in[i * 10];
+        const Vector3f wi(r[0], r[1], r[2]), wo(r[3], r[4], r[5]);
+        BSDFQueryRecord bRec(wi, wo, ESolidAngle);
+        bRec.uv = Point2f(r[8], r[9]);
+        const Color3f e = bsdf->eval(bRec);
+        const float pdf = bsdf->pdf(bRec);
+        BSDFQueryRecord sRec(wi);
+        sRec.uv = Point2f(r[8], r[9]);
+        sRec.measure = EUnknownMeasure;
+        const Color3f w = bsdf->sample(sRec, Point2f(r[6], r[7]));
+        const bool discrete = sRec.measure == EDiscrete;
+        BSDFQueryRecord pRec(wi, sRec.wo, ESolidAngle);
+        pRec.uv = sRec.uv;
+        float *o = &out[i * 12];
+        o[0] = e(0); o[1] = e(1); o[2] = e(2); o[3] = pdf; o[4] = w(0); o[5] = w(1); o[6] = w(2);
+        o[7] = sRec.wo.x(); o[8] = sRec.wo.y(); o[9] = sRec.wo.z(); o[10] = discrete ? 1.f : 0.f;
+        o[11] = discrete ? 0.f : bsdf->pdf(pRec);
+    }
+    f = fopen(argv[4], "wb");
+    if (!f) throw NoriException("cannot write %s", argv[4]);
+    fwrite(out.data(), 48, n, f);
+    fclose(f);
+    printf("{\"mode\": \"bsdf\", \"shape\": %zu, \"records\": %zu}\n", index, n);
+    return 0;
+}
+
 static int usage() {
     fprintf(stderr,
         "nori_ref — headless harness around the reference CPU renderer (test infrastructure)\n"
@@ -730,6 +774,7 @@ static int usage() {
         "  nori_ref ttest   test.xml [samples=N]   (scene-mode t-tests, restated: see modeTTestScenes)\n"
         "  nori_ref rng     n\n"
         "  nori_ref emitter scene.xml in.bin out.bin [index=K]      (Emitter::sample/pdf/eval probes)\n"
+        "  nori_ref bsdf    scene.xml in.bin out.bin [index=K]      (BSDF::eval/pdf/sample probes of shape K's BSDF)\n"
         "  nori_ref medium  scene.xml rays.bin out.bin [samples=K]   (free path / transmittance / density probes)\n");
     return 2;
 }
@@ -749,6 +794,7 @@ int main(int argc, char **argv) {
         else if (mode == "rng") rc = modeRng(argc, argv);
         else if (mode == "medium") rc = modeMedium(argc, argv);
         else if (mode == "emitter") rc = modeEmitter(argc, argv);
+        else if (mode == "bsdf") rc = modeBsdf(argc, argv);
         if (rc == 2) return usage();
         return rc;
     } catch (const std::exception &e) {

@@ -80,12 +80,37 @@ def test_parser_errors_and_defaults(nb, built_lib, tmp_path):
 
 
 def test_unsupported_plugin_is_reported_not_emulated(nb, built_lib, tmp_path):
+    # disney has a kernel since ABI v5: it flattens to a tagged record + 10 clamped parameters
     xml = write(tmp_path, "<scene><integrator type='path_mis'/>" + CAM +
-                "<shape type='sphere'><bsdf type='disney'/></shape></scene>")
-    with pytest.raises(nb.NbError) as e:
-        nb.load_xml(xml)
-    assert e.value.code == nb.NB_E_UNSUPPORTED
+                "<shape type='sphere'><bsdf type='disney'><float name='metallic' value='2'/></bsdf></shape></scene>")
+    s = nb.load_xml(xml)
+    assert s["bsdfs"]["type"][0] == nb.BSDF_DISNEY and s["params"].tolist() == [1, 0, 0.5, 0.5, 0, 0, 0, 0.5, 0, 1]
     xml = write(tmp_path, "<scene><integrator type='photonmapper'/>" + CAM + "<shape type='sphere'/></scene>")
     with pytest.raises(nb.NbError) as e:
         nb.load_xml(xml)
     assert e.value.code == nb.NB_E_UNSUPPORTED
+
+
+def test_rank1_plugins_flatten(nb, built_lib):
+    """disney / spot / directional / normal maps / normals-av-preview integrators leave the
+    host loader as tagged records with their parameters in `params`."""
+    s = nb.load_xml(golden("scenes/plugins/disney_spot_dir_path_mis.xml"))
+    assert (s["bsdfs"]["type"] & 0xff).tolist() == [nb.BSDF_DISNEY, nb.BSDF_DISNEY, nb.BSDF_DISNEY, nb.BSDF_DIFFUSE]
+    assert s["bsdfs"]["type"][0] >> 8 == 2                         # checkerboard albedo: texture 1 (+1), after the envmap's constant
+    assert s["emitters"]["type"].tolist() == [nb.EMITTER_SPOT, nb.EMITTER_DIRECTIONAL, nb.EMITTER_ENVMAP]
+    p = s["params"]
+    spot = p[int(s["emitters"]["shape"][0]):][:5]
+    np.testing.assert_allclose(np.linalg.norm(spot[:3]), 1, rtol=1e-6)
+    np.testing.assert_allclose(spot[3:], np.cos(np.radians([20, 35])), rtol=1e-6)
+    np.testing.assert_allclose(s["emitters"]["radiance"][0], np.array([600, 500, 400]) / (2 * np.pi), rtol=1e-6)
+    d = p[int(s["emitters"]["shape"][1]):][:4]
+    np.testing.assert_allclose(d[3], np.cos(np.radians(3)), rtol=1e-6)
+    off = int(s["bsdfs"]["alpha"][1:2].view("<u4")[0])
+    np.testing.assert_allclose(p[off:off + 10], [0.8, 0, 0.7, 0.3, 0.4, 0.6, 0, 0.5, 0, 1], rtol=1e-6)
+    s = nb.load_xml(golden("scenes/plugins/normalmap_direct_mis.xml"))
+    assert s["shapes"]["normal_map"].tolist() == [1, 2, 3, 0]
+    t = s["textures"]
+    assert np.all(t["flags"] & 2) and t["intensity"].tolist() == [1.0, 0.6000000238418579, 1.0]
+    assert s["texels"].min() >= -1 and s["texels"].max() <= 1
+    assert int(nb.load_xml(golden("scenes/plugins/av.xml"))["render"]["integrator"][0]) == nb.INTEGRATORS["av"]
+    assert int(nb.load_xml(golden("scenes/plugins/preview.xml"))["render"]["integrator"][0]) == nb.INTEGRATORS["preview"]

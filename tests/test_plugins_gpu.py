@@ -1,0 +1,86 @@
+"""SURVEY 8(f) rank 1-2 rows on the GPU against the reference's own plugins (fixtures of
+tests/golden/make_plugins.py): the disney BSDF (eval / pdf / sample record by record, then in images),
+the spot and directional emitters (Emitter::sample record by record), normal maps on meshes and
+spheres, and the normals / av / preview integrators."""
+import numpy as np
+import pytest
+
+from conftest import golden, rel_rmse
+
+pytestmark = pytest.mark.gpu
+
+BSDF_CASES = [("disney_metal", "disney_spot_dir_path_mis", 1), ("disney_coat", "disney_spot_dir_path_mis", 2),
+              ("disney_checker", "disney_spot_dir_path_mis", 0), ("diffuse_default", "normalmap_direct_mis", 3)]
+
+
+@pytest.mark.parametrize("name,scene,shape", BSDF_CASES)
+def test_bsdf_matches_reference_plugin(nb, ctx, name, scene, shape):
+    s = nb.load_xml(golden("scenes/plugins/%s.xml" % scene))
+    rec = np.fromfile(golden("bsdf_%s_in.bin" % name), "<f4").reshape(-1, 10)
+    want = np.fromfile(golden("bsdf_%s_out.bin" % name), "<f4").reshape(-1, 12)
+    ctx.load(s)
+    got = ctx.bsdf_probe(int(s["shapes"]["bsdf"][shape]), rec)
+
+    def relerr(a, b):
+        return np.abs(a - b).max(axis=1) / np.maximum(np.abs(b).max(axis=1), 1e-3)
+    e_eval, e_pdf = relerr(got[:, 0:3], want[:, 0:3]), relerr(got[:, 3:4], want[:, 3:4])
+    up = rec[:, 2] > 0                                        # BSDF::sample leaves bRec.wo unset when it rejects wi from below
+    e_w, e_wo = relerr(got[:, 4:7], want[:, 4:7]), np.abs(got[up, 7:10] - want[up, 7:10]).max(axis=1)
+    e_spdf = relerr(got[up, 11:12], want[up, 11:12])
+    print(name, "max rel err eval %.2e pdf %.2e weight %.2e wo %.2e sampled pdf %.2e; nonzero evals %d" % (
+        e_eval.max(), e_pdf.max(), e_w.max(), e_wo.max(), e_spdf.max(), int((want[:, 0] > 0).sum())))
+    assert (want[:, 0] > 0).sum() > 1000                      # the probe exercises the lobe, not only the zero branches
+    assert np.array_equal(got[:, 10], want[:, 10])            # measure
+    # fp32 shading with fast division / powf vs glibc: a few 1e-5 relative; nothing structural may differ
+    assert e_eval.max() < 2e-3 and e_pdf.max() < 1e-4 and e_w.max() < 2e-3 and e_wo.max() < 2e-5 and e_spdf.max() < 2e-3
+
+
+@pytest.mark.parametrize("name,index", [("spot", 0), ("directional", 1)])
+def test_spot_and_directional_sample_match_reference(nb, ctx, name, index):
+    s = nb.load_xml(golden("scenes/plugins/disney_spot_dir_path_mis.xml"))
+    assert int(s["emitters"]["type"][index]) == {"spot": nb.EMITTER_SPOT, "directional": nb.EMITTER_DIRECTIONAL}[name]
+    rec = np.fromfile(golden("emit_%s_in.bin" % name), "<f4").reshape(-1, 5)
+    want = np.fromfile(golden("emit_%s_out.bin" % name), "<f4").reshape(-1, 12)
+    ctx.load(s)
+    got = ctx.emitter_probe(index, rec)
+    wi_err = np.abs(got[:, :3] - want[:, :3]).max(axis=1)
+    scale = np.maximum(np.abs(want[:, 3:7]).max(axis=1), 1e-6)
+    val_err = np.abs(got[:, 3:7] - want[:, 3:7]).max(axis=1) / scale
+    finite = np.isfinite(want[:, 7])
+    assert np.array_equal(np.isfinite(got[:, 7]), finite)     # directional: shadow ray to infinity
+    maxt_err = np.abs(got[finite, 7] - want[finite, 7]) / np.maximum(np.abs(want[finite, 7]), 1.0)
+    eval_err = np.abs(got[:, 8:11] - want[:, 8:11]).max(axis=1) / np.maximum(np.abs(want[:, 8:11]).max(axis=1), 1e-6)
+    print(name, "max wi err", wi_err.max(), "max value err", val_err.max(), "lit records", int((want[:, 3:6].max(axis=1) > 0).sum()))
+    assert (want[:, 3:6].max(axis=1) > 0).sum() > 200
+    # the spot's falloff is delta^4 of a cosine difference: the last bits of the cosine show up 4x
+    assert wi_err.max() <= 2e-5 and np.quantile(val_err, 0.99) < 5e-4 and val_err.max() < 2e-2 and eval_err.max() < 2e-2
+    assert maxt_err.size == 0 or maxt_err.max() < 1e-5
+
+
+IMAGES = [("disney_spot_dir_path_mis", 128), ("disney_spot_dir_direct_mis", 128), ("disney_path_mats_area", 128),
+          ("normalmap_direct_mis", 64), ("normalmap_normals", 32), ("normals_direction", 32), ("av", 64),
+          ("preview", 64), ("preview_nolight", 16)]
+
+
+@pytest.mark.parametrize("name,spp", IMAGES)
+@pytest.mark.parametrize("strategy", [2, 1])
+def test_plugin_scenes_match_reference_renders(nb, ctx, name, spp, strategy):
+    s = nb.load_xml(golden("scenes/plugins/%s.xml" % name))
+    want = np.load(golden("plug_%s_ref_%dspp.npy" % (name, spp)))
+    integ = int(s["render"]["integrator"][0])
+    if strategy == 1 and integ not in (nb.INTEGRATORS["path_mis"], nb.INTEGRATORS["path_mats"]):
+        pytest.skip("the wavefront pipeline renders path_mis / path_mats only")
+    imgs = []
+    for seed in (1, 2):
+        ctx.set_option("strategy", strategy)
+        ctx.load(s)
+        ctx.render_begin(nb.make_render_params(s, seed=seed))
+        ctx.render_subframe(0, spp)
+        imgs.append(ctx.film_download(normalize=True))
+    a, b = imgs
+    assert a.shape == want.shape and np.isfinite(a).all()
+    bias = (a.mean(axis=(0, 1)) - want.mean(axis=(0, 1))) / want.mean(axis=(0, 1))
+    floor, err = rel_rmse(a, b), rel_rmse(a, want)
+    print(name, "strategy", strategy, "bias", bias, "relRMSE", err, "noise floor", floor)
+    assert np.all(np.abs(bias) <= 0.02), bias
+    assert err <= 1.25 * floor + 2e-3, (err, floor)
