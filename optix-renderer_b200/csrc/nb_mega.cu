@@ -520,7 +520,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
  * while its neighbours shade, start new paths and walk their own rays. Per ray the visiting order
  * and arithmetic are nb_traverse's; per path the draws are nb_path_bounce's. */
 #ifndef NB_WALK_MIN_BLOCKS
-#define NB_WALK_MIN_BLOCKS 4
+#define NB_WALK_MIN_BLOCKS 6      /* 80 registers: the path state is parked in shared memory during the walk (B200, table: 353 vs 332 M samples/s at 4) */
 #endif
 #ifndef NB_WALK_NODE_STEPS
 #define NB_WALK_NODE_STEPS 8      /* node steps per loop iteration */
@@ -536,19 +536,24 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
 #endif
 enum { NB_PH_IDLE = 0, NB_PH_REGEN = 1, NB_PH_NODE = 2, NB_PH_LEAF = 3, NB_PH_TDONE = 4, NB_PH_SHADE = 5 };
 
+/* Path state parked in shared memory while a lane walks the tree (SoA, one word per lane per row:
+ * conflict-free). The walk itself needs ~25 registers of ray state; the path's 28 words are only
+ * touched by REGEN / TDONE / SHADE, so keeping them out of the register file during NODE / LEAF
+ * buys the occupancy the latency-bound node loop wants (124 -> NB_WALK_MIN_BLOCKS-bound registers). */
+enum { NB_W_LI = 0, NB_W_THR = 3, NB_W_O = 6, NB_W_D = 9, NB_W_MINT = 12, NB_W_MAXT = 13, NB_W_WMATS = 14, NB_W_WEMS = 15,
+       NB_W_PDFMAT = 16, NB_W_PX = 17, NB_W_PY = 18, NB_W_FLAGS = 19, NB_W_RNG = 20, NB_W_SC = 24, NB_W_CAND = 27, NB_W_WORDS = 28 };
+
 template <bool MIS, bool EXT>
 __global__ void __launch_bounds__(NB_TILE_THREADS, NB_WALK_MIN_BLOCKS)
 nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
+    __shared__ float park[NB_W_WORDS][NB_TILE_THREADS];
+    const uint32_t tid = threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t n_closest = 0, n_any = 0, n_samples = 0;
     NbItemCursor cur;
     uint32_t phase = NB_PH_REGEN;
     bool splat = false;               /* REGEN: a finished sample waits to be put on the film */
-    bool shadow = false;              /* a shadow ray is pending / being traced before the main ray */
     bool ending = false;              /* the path ended at the last vertex; splat after its shadow ray */
-    NbPathRegs ps;
-    ps.flags = 0;
-    NbShadowRay so;
     /* the ray being walked */
     float3 to = make_float3(0.f, 0.f, 0.f), td = to, tr = to;
     float tmint = 0.f, tmaxt = 0.f;
@@ -556,6 +561,25 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
     NbHit hit;
     hit.t = INFINITY; hit.u = hit.v = 0.f; hit.slot = 0xffffffffu;
     bool t_any = false, occluded = false;
+
+    auto ld3p = [&](int row) { return mk3(park[row][tid], park[row + 1][tid], park[row + 2][tid]); };
+    auto st3p = [&](int row, f3 v) { park[row][tid] = v.x; park[row + 1][tid] = v.y; park[row + 2][tid] = v.z; };
+    auto park_path = [&](const NbPathRegs &ps) {
+        st3p(NB_W_LI, ps.Li); st3p(NB_W_THR, ps.thr); st3p(NB_W_O, ps.o); st3p(NB_W_D, ps.d);
+        park[NB_W_MINT][tid] = ps.mint; park[NB_W_MAXT][tid] = ps.maxt; park[NB_W_WMATS][tid] = ps.w_mats;
+        park[NB_W_WEMS][tid] = ps.w_ems; park[NB_W_PDFMAT][tid] = ps.pdfmat; park[NB_W_PX][tid] = ps.px; park[NB_W_PY][tid] = ps.py;
+        park[NB_W_FLAGS][tid] = __uint_as_float(ps.flags);
+        park[NB_W_RNG][tid] = __uint_as_float((uint32_t) ps.rng.state); park[NB_W_RNG + 1][tid] = __uint_as_float((uint32_t) (ps.rng.state >> 32));
+        park[NB_W_RNG + 2][tid] = __uint_as_float((uint32_t) ps.rng.inc); park[NB_W_RNG + 3][tid] = __uint_as_float((uint32_t) (ps.rng.inc >> 32));
+    };
+    auto unpark_path = [&](NbPathRegs &ps) {
+        ps.Li = ld3p(NB_W_LI); ps.thr = ld3p(NB_W_THR); ps.o = ld3p(NB_W_O); ps.d = ld3p(NB_W_D);
+        ps.mint = park[NB_W_MINT][tid]; ps.maxt = park[NB_W_MAXT][tid]; ps.w_mats = park[NB_W_WMATS][tid];
+        ps.w_ems = park[NB_W_WEMS][tid]; ps.pdfmat = park[NB_W_PDFMAT][tid]; ps.px = park[NB_W_PX][tid]; ps.py = park[NB_W_PY][tid];
+        ps.flags = __float_as_uint(park[NB_W_FLAGS][tid]);
+        ps.rng.state = (uint64_t) __float_as_uint(park[NB_W_RNG][tid]) | ((uint64_t) __float_as_uint(park[NB_W_RNG + 1][tid]) << 32);
+        ps.rng.inc = (uint64_t) __float_as_uint(park[NB_W_RNG + 2][tid]) | ((uint64_t) __float_as_uint(park[NB_W_RNG + 3][tid]) << 32);
+    };
 
     /* prologue of nb_traverse for the lane's next ray */
     auto begin_walk = [&](f3 o, f3 d, float mint, float maxt, bool any_hit) {
@@ -574,22 +598,25 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
         phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
         if (any_hit) ++n_any; else ++n_closest;
     };
+    auto walk_main = [&]() { begin_walk(ld3p(NB_W_O), ld3p(NB_W_D), park[NB_W_MINT][tid], park[NB_W_MAXT][tid], false); };
 
     for (;;) {
         const uint32_t m_walking = __ballot_sync(0xffffffffu, phase == NB_PH_NODE || phase == NB_PH_LEAF || phase == NB_PH_TDONE);
         /* ---- REGEN: splat the finished sample, start the next camera path ---- */
         const uint32_t m_regen = __ballot_sync(0xffffffffu, phase == NB_PH_REGEN);
         if (m_regen && (__popc(m_regen) >= NB_WALK_T_REGEN || !m_walking)) {
-            if (phase == NB_PH_REGEN && splat) { nb_film_put(film, ps.px, ps.py, ps.Li, stats); splat = false; }
+            if (phase == NB_PH_REGEN && splat) { nb_film_put(film, park[NB_W_PX][tid], park[NB_W_PY][tid], ld3p(NB_W_LI), stats); splat = false; }
             uint32_t pix, sidx;
             const bool got = nb_take_sample(cur, tp, item_counter, phase == NB_PH_REGEN, lane, lt_mask, pix, sidx);
             if (got) {
                 NbCameraRay r;
+                NbPathRegs ps;
                 nb_camera_sample(sc.camera, tp.plan, pix, sidx, ps.rng, r);
                 ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
                 ps.Li = mk3(0.f); ps.thr = mk3(1.f); ps.w_mats = 1.f; ps.w_ems = 0.f; ps.pdfmat = 0.f;
                 ps.flags = NB_FLAG_PRIMARY;
-                shadow = false; ending = false;
+                park_path(ps);
+                ending = false;
                 ++n_samples;
                 begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
             } else if (phase == NB_PH_REGEN) phase = NB_PH_IDLE;      /* image finished */
@@ -639,25 +666,31 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
         if (phase == NB_PH_TDONE) {
             if (t_any) {
                 if (!occluded) {                           /* path_mis.cpp:102-105,141 */
-                    if (so.cand >= 0.f) ps.w_ems = so.cand;
-                    ps.Li += ps.w_ems * so.c;
+                    const float cand = park[NB_W_CAND][tid];
+                    float w_ems = park[NB_W_WEMS][tid];
+                    if (cand >= 0.f) { w_ems = cand; park[NB_W_WEMS][tid] = cand; }
+                    st3p(NB_W_LI, ld3p(NB_W_LI) + w_ems * ld3p(NB_W_SC));
                 }
-                shadow = false;
                 if (ending) { splat = true; phase = NB_PH_REGEN; }
-                else begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
+                else walk_main();
             } else phase = NB_PH_SHADE;
         }
         /* ---- SHADE: one bounce of the integrator for lanes whose closest hit arrived ---- */
         const uint32_t m_shade = __ballot_sync(0xffffffffu, phase == NB_PH_SHADE);
         if (m_shade && (__popc(m_shade) >= NB_WALK_T_SHADE || !__ballot_sync(0xffffffffu, phase == NB_PH_NODE || phase == NB_PH_LEAF))) {
             if (phase == NB_PH_SHADE) {
-                bool alive = false;
-                shadow = false;
+                bool alive = false, shadow = false;
+                NbPathRegs ps;
+                NbShadowRay so;
+                unpark_path(ps);
                 if (hit.slot != 0xffffffffu) alive = nb_path_bounce<MIS, EXT>(sc, tp.plan.max_depth, ps, hit, shadow, so);
                 else ps.Li += ps.thr * nb_env_radiance<EXT>(sc, ps.d);
+                park_path(ps);
                 ending = !alive;
-                if (MIS && shadow) begin_walk(so.o, so.d, so.mint, so.maxt, true);
-                else if (alive) begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
+                if (MIS && shadow) {
+                    st3p(NB_W_SC, so.c); park[NB_W_CAND][tid] = so.cand;
+                    begin_walk(so.o, so.d, so.mint, so.maxt, true);
+                } else if (alive) begin_walk(ps.o, ps.d, ps.mint, ps.maxt, false);
                 else { splat = true; phase = NB_PH_REGEN; }
             }
         }
@@ -723,19 +756,32 @@ cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const Nb
     NbTilePlan tp;
     tp.plan = plan;
     tp.height = height; tp.passes = passes;
-    tp.tile_w = 16; tp.tile_h = 8;
+    /* Work items are small: a warp that draws an expensive item last (glass-heavy tiles cost several
+     * times the mean) finishes alone while the rest of the GPU idles, and at a few hundred k samples/s
+     * per warp one 4096-sample item is ~10 ms of a ~100 ms render. Measured on B200 (table, 22 766
+     * triangles, 64 spp): 32 passes per item 226 M samples/s, 8: 228 M, 4: 280 M, 2: 319 M, 1: 332 M;
+     * 8x8 tiles 359 M. Lanes pick up the next item as soon as the current one is handed out
+     * (nb_take_sample), so small items cost one atomic each and nothing else. The lock-step kernel
+     * keeps 16x8 tiles x 2 passes: its camera rays run coherently (cbox 1.96 G vs 1.94 G at 1 pass). */
+    const bool walking = !sc.flat && walk && (integrator == NB_INTEGRATOR_PATH_MIS || integrator == NB_INTEGRATOR_PATH_MATS);
+#ifndef NB_TILE_CHUNK_MAX
+#define NB_TILE_CHUNK_MAX 2
+#endif
+#ifndef NB_WALK_CHUNK_MAX
+#define NB_WALK_CHUNK_MAX 1
+#endif
+    tp.tile_w = walking ? 8 : 16; tp.tile_h = 8;
     tp.tiles_x = (plan.width + tp.tile_w - 1) / tp.tile_w;
     tp.n_tiles = tp.tiles_x * ((height + tp.tile_h - 1) / tp.tile_h);
-    /* items of about 4096 samples (128 per lane), but enough of them to balance ~5000 warps */
-    uint32_t chunk = 32;
-    while (chunk > 1 && (uint64_t) tp.n_tiles * ((passes + chunk - 1) / chunk) < (uint64_t) sm_count * 16 * 8) chunk >>= 1;
+    uint32_t chunk = walking ? NB_WALK_CHUNK_MAX : NB_TILE_CHUNK_MAX;
+    while ((uint64_t) tp.n_tiles * ((passes + chunk - 1) / chunk) >= 0xffff0000ull) chunk <<= 1;   /* item ids are 32-bit */
     tp.chunk = chunk;
     const uint64_t items = (uint64_t) tp.n_tiles * ((passes + chunk - 1) / chunk);
     if (items >= 0xffff0000ull) return cudaErrorInvalidValue;
     tp.n_items = (uint32_t) items;
     cudaError_t e = cudaMemsetAsync(item_counter, 0, sizeof(uint32_t), stream);
     if (e != cudaSuccess) return e;
-    if (!sc.flat && walk) {
+    if (walking) {
         if (integrator == NB_INTEGRATOR_PATH_MIS)
             return sc.ext ? nb_tile_launch_walk<true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
                           : nb_tile_launch_walk<true, false>(sc, film, tp, item_counter, stats, sm_count, stream);
