@@ -301,7 +301,10 @@ int  nb_get_counters(nb_ctx *ctx, nb_counters *out);
 /* options: "profile" (per-kernel event timers of the wavefront pipeline), "sort" (reserved),
  * "strategy" (NB_STRATEGY_*: how path_mis / path_mats are executed; the direct_* integrators
  * always run as one K_tile launch), "flat_scan" (-1 auto, 0 always walk the tree, 1 always scan
- * the primitive list: same hits, see nb_trace.cuh) */
+ * the primitive list: same hits, see nb_trace.cuh), "walk" (1: tree scenes render path_mis / path_mats with the
+ * per-lane state machine K_tile_walk), "ordered" (1: nb_trace_rays enters the child nearer to the ray first and breaks
+ * exact-t ties by leaf-order slot, nb_traverse_ordered; 0, default: the reference's left-first order with skip links —
+ * both return the reference's bits; the render kernels walk left-first, which measured faster) */
 enum { NB_STRATEGY_AUTO = 0, NB_STRATEGY_WAVEFRONT = 1, NB_STRATEGY_TILE = 2 };
 int  nb_set_option(nb_ctx *ctx, const char *name, int64_t value);
 

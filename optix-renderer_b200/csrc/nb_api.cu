@@ -190,6 +190,7 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     nb_free_list(ctx->bvh_allocs);
     ctx->scene_ready = ctx->bvh_ready = ctx->render_begun = false;
     ctx->dev = NbDeviceScene();
+    ctx->dev.ordered = ctx->opt_ordered ? 1u : 0u;
 
     ctx->h_shapes.assign(s->shapes, s->shapes + s->n_shapes);
     ctx->h_positions.assign(s->positions, s->positions + s->n_vertices * 3);

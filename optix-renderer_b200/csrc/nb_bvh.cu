@@ -21,6 +21,7 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
     const uint32_t n = imp->n_nodes, ni = imp->n_indices;
     const uint32_t total_prims = ctx->h_shape_prim_offset.back();
+    if (n > NB_NODE_RIGHT_MASK) return nb_fail(ctx, NB_E_UNSUPPORTED, "nb_build_bvh: %u nodes exceed the node index range", n);
     if (ni != total_prims) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: %u indices for %u primitives", ni, total_prims);
 
     std::vector<uint32_t> skip(n, NB_NODE_END);
@@ -79,8 +80,11 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     std::vector<float4> nodes((size_t) n * 2);
     for (uint32_t i = 0; i < n; ++i) {
         const nb_bvh_node &nd = imp->nodes[i];
-        uint32_t w1 = NB_NODE_INNER;
-        if (nd.word0 & 1u) {
+        uint32_t w1 = 0;
+        if (!(nd.word0 & 1u)) {
+            const nb_bvh_node &l = imp->nodes[i + 1], &r = imp->nodes[nd.word1];
+            w1 = nb_inner_word(nd.word1, l.bmin, l.bmax, r.bmin, r.bmax);
+        } else {
             const uint32_t size = nd.word0 >> 1, start = nd.word1;
             if (size == 0) w1 = NB_NODE_EMPTY_LEAF;
             else {

@@ -192,7 +192,19 @@ __global__ void nb_k_build_emit_nodes(int n, uint32_t n_kept, const unsigned lon
     const float ex = 4e-7f * fmaxf(fabsf(mn.x), fabsf(mx.x)) + 1e-30f, ey = 4e-7f * fmaxf(fabsf(mn.y), fabsf(mx.y)) + 1e-30f,
                 ez = 4e-7f * fmaxf(fabsf(mn.z), fabsf(mx.z)) + 1e-30f;
     mn = make_float3(mn.x - ex, mn.y - ey, mn.z - ez); mx = make_float3(mx.x + ex, mx.y + ey, mx.z + ez);
-    nodes[2 * (size_t) p] = make_float4(__uint_as_float(skip), __uint_as_float(leaf ? a : NB_NODE_INNER), mn.x, mn.y);
+    uint32_t w1 = a;
+    if (!leaf) {
+        /* right child = first node after the left child's subtree; both children's (unpadded) boxes
+         * give the axis of the ordered traversal */
+        const unsigned long long lkey = skeys[p + 1];
+        const unsigned long long rwant = (unsigned long long) ((0xffffffffu - (uint32_t) lkey) + 1u) << 32;
+        uint32_t rl = p + 2, rh = n_kept;
+        while (rl < rh) { const uint32_t mid = (rl + rh) >> 1; if (skeys[mid] < rwant) rl = mid + 1; else rh = mid; }
+        const float3 lmn = bmin[sids[p + 1]], lmx = bmax[sids[p + 1]], rmn = bmin[sids[rl]], rmx = bmax[sids[rl]];
+        const float l0[3] = { lmn.x, lmn.y, lmn.z }, l1[3] = { lmx.x, lmx.y, lmx.z }, r0[3] = { rmn.x, rmn.y, rmn.z }, r1[3] = { rmx.x, rmx.y, rmx.z };
+        w1 = nb_inner_word(rl, l0, l1, r0, r1);
+    }
+    nodes[2 * (size_t) p] = make_float4(__uint_as_float(skip), __uint_as_float(w1), mn.x, mn.y);
     nodes[2 * (size_t) p + 1] = make_float4(mn.z, mx.x, mx.y, mx.z);
 }
 
@@ -230,7 +242,7 @@ int nb_build_bvh_device(nb_ctx *ctx) {
     int rc = NB_OK;
     const uint32_t n = ctx->h_shape_prim_offset.back();
     if (n == 0) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: scene has no primitives");
-    if (n >= (1u << 30)) return nb_fail(ctx, NB_E_UNSUPPORTED, "nb_build_bvh: too many primitives for the device builder");
+    if (n >= (1u << 27)) return nb_fail(ctx, NB_E_UNSUPPORTED, "nb_build_bvh: too many primitives for the device builder");
     const uint32_t n_all = 2 * n - 1;
     cudaStream_t st = ctx->stream;
     std::vector<void *> tmp;

@@ -22,8 +22,22 @@
 #define NB_SLOT_LAST   0x40000000u
 #define NB_SLOT_SHAPE_MASK 0x3fffffffu
 #define NB_NODE_END 0xffffffffu
-#define NB_NODE_INNER 0xffffffffu
-#define NB_NODE_EMPTY_LEAF 0xfffffffeu
+/* A.y of an inner node: bit 31 set; bits 29-30 = the axis along which its children's box centres are
+ * furthest apart; bit 28 = the LEFT child is the upper one along that axis; bits 0-27 = index of the
+ * right child (the left child is idx + 1). Only the ordered traversal reads the low bits. */
+#define NB_NODE_INNER_BIT 0x80000000u
+#define NB_NODE_RIGHT_MASK 0x0fffffffu
+#define NB_NODE_EMPTY_LEAF 0x7fffffffu
+#define NB_STACK_DEPTH 64u              /* as the reference's traversal stack (bvh.cpp:413) */
+__host__ __device__ inline uint32_t nb_inner_word(uint32_t right, const float lmin[3], const float lmax[3], const float rmin[3], const float rmax[3]) {
+    int axis = 0; float best = -1.f; bool left_upper = false;
+    for (int a = 0; a < 3; ++a) {
+        const float dl = (rmin[a] + rmax[a]) - (lmin[a] + lmax[a]);
+        const float ad = dl < 0.f ? -dl : dl;
+        if (ad > best) { best = ad; axis = a; left_upper = dl < 0.f; }
+    }
+    return NB_NODE_INNER_BIT | ((uint32_t) axis << 29) | (left_upper ? (1u << 28) : 0u) | (right & NB_NODE_RIGHT_MASK);
+}
 #define NB_FLAT_MAX_SLOTS 24u
 
 struct NbDeviceScene {
@@ -31,6 +45,7 @@ struct NbDeviceScene {
     const float4 *slots = nullptr;      /* 3 per primitive slot */
     uint32_t n_nodes = 0, n_slots = 0;
     uint32_t flat = 0;                  /* queries scan the slots instead of walking the tree (nb_trace.cuh) */
+    uint32_t ordered = 0;               /* nb_trace_rays walks near child first (nb_traverse_ordered) instead of left first */
     uint32_t ext = 0;                   /* scene uses textures, normal maps, an environment map, a heterogeneous medium, the disney BSDF or a spot / directional light: the EXT kernel variants render it */
     /* shading data */
     const nb_shape *shapes = nullptr;
@@ -69,6 +84,7 @@ struct nb_ctx {
     double bvh_build_ms = 0.0;          /* device time of the last NB_BVH_DEVICE build */
     int opt_profile = 0, opt_sort = 0, opt_strategy = 0;
     int opt_walk = 1;                   /* tree scenes: K_tile_walk (per-lane state machine) instead of lock-step K_tile */
+    int opt_ordered = 0;                /* 1: nb_trace_rays uses the near-child-first walk */
     int opt_flat = -1;                  /* -1: flat scan iff the scene has at most NB_FLAT_MAX_SLOTS primitives */
 };
 

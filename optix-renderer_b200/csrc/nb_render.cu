@@ -564,6 +564,7 @@ int nb_set_option(nb_ctx *ctx, const char *name, int64_t value) {
     if (!strcmp(name, "profile")) ctx->opt_profile = (int) value;
     else if (!strcmp(name, "sort")) ctx->opt_sort = (int) value;
     else if (!strcmp(name, "walk")) ctx->opt_walk = (int) value;
+    else if (!strcmp(name, "ordered")) { ctx->opt_ordered = value != 0; ctx->dev.ordered = value != 0 ? 1u : 0u; }
     else if (!strcmp(name, "flat_scan")) {
         ctx->opt_flat = (int) value;
         ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;

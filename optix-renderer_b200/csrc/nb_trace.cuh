@@ -112,18 +112,18 @@ __device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, co
      * test for 2 of 32 lanes at a time (ncu, table scene). Per ray the sequence of visits is
      * unchanged. */
     while (true) {
-        uint32_t leaf = NB_NODE_INNER, after = NB_NODE_END;
+        uint32_t leaf = NB_NODE_END, after = NB_NODE_END;
         while (idx != NB_NODE_END) {
             const float4 A = __ldg(nodes + 2 * idx), B = __ldg(nodes + 2 * idx + 1);
             const uint32_t skip = __float_as_uint(A.x), start = __float_as_uint(A.y);
             if (!nb_box_hit(A, B, o, d, r, mint, maxt)) { idx = skip; continue; }
-            if (start == NB_NODE_INNER) { idx = idx + 1; continue; }
+            if (start & NB_NODE_INNER_BIT) { idx = idx + 1; continue; }
             idx = skip;
             if (start == NB_NODE_EMPTY_LEAF) continue;
             leaf = start; after = skip;
             break;
         }
-        if (leaf == NB_NODE_INNER) break;
+        if (leaf == NB_NODE_END) break;
         uint32_t s = leaf;
         while (true) {
             const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
@@ -141,6 +141,80 @@ __device__ __forceinline__ bool nb_traverse(const float4 *__restrict__ nodes, co
             ++s;
         }
         idx = after;
+    }
+    return found;
+}
+
+
+/* Which child of an inner node the ordered walk enters first: the one whose box centre comes first
+ * along the ray on the node's axis (nb_inner_word). */
+__device__ __forceinline__ bool nb_right_first(uint32_t word, const float3 d) {
+    const uint32_t axis = (word >> 29) & 3u;
+    const float da = axis == 0u ? d.x : (axis == 1u ? d.y : d.z);
+    return (da < 0.f) != ((word >> 28) & 1u);
+}
+
+/* The same query with the children of every inner node visited near-to-far (an explicit stack of far
+ * children, as deep as the reference's). The set of primitives a ray can hit does not depend on the
+ * order; what the reference's fixed left-first order decides is which of two primitives hit at EXACTLY
+ * the same t is reported — it keeps the one visited later, i.e. the higher leaf-order slot, because
+ * Mesh::rayIntersect accepts t <= maxt (mesh.cpp:134) — so a tie is resolved here by slot number.
+ * Boxes are still tested against the current maxt (bbox.h:362), which only prunes primitives that
+ * could not be accepted. Held to the same oracle ray sets as nb_traverse (tests/test_trace_gpu.py). */
+template <bool ANY>
+__device__ __forceinline__ bool nb_traverse_ordered(const float4 *__restrict__ nodes, const float4 *__restrict__ slots,
+                                                    uint32_t n_nodes, float3 o, float3 d, float mint, float maxt,
+                                                    NbHit &hit) {
+    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
+    if (mint == NB_EPSILON) {
+        float m = fabsf(o.x);
+        m = fmaxf(m, fabsf(o.y));
+        m = fmaxf(m, fabsf(o.z));
+        const float s = __fmul_rn(mint, m);
+        mint = (mint < s) ? s : mint;
+    }
+    if (n_nodes == 0 || maxt < mint) return false;
+    const float3 r = make_float3(__fdiv_rn(1.0f, d.x), __fdiv_rn(1.0f, d.y), __fdiv_rn(1.0f, d.z));
+    uint32_t stk[NB_STACK_DEPTH];
+    uint32_t sp = 0, idx = 0;
+    bool found = false;
+    while (true) {
+        uint32_t leaf = NB_NODE_END;
+        while (idx != NB_NODE_END) {
+            const float4 A = __ldg(nodes + 2 * idx), B = __ldg(nodes + 2 * idx + 1);
+            const uint32_t start = __float_as_uint(A.y);
+            if (nb_box_hit(A, B, o, d, r, mint, maxt)) {
+                if (start & NB_NODE_INNER_BIT) {
+                    const uint32_t right = start & NB_NODE_RIGHT_MASK;
+                    const bool rf = nb_right_first(start, d);
+                    stk[sp++] = rf ? idx + 1 : right;
+                    idx = rf ? right : idx + 1;
+                    continue;
+                }
+                if (start != NB_NODE_EMPTY_LEAF) leaf = start;
+            }
+            idx = sp ? stk[--sp] : NB_NODE_END;
+            if (leaf != NB_NODE_END) break;
+        }
+        if (leaf == NB_NODE_END) break;
+        uint32_t s = leaf;
+        while (true) {
+            const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
+            const uint32_t tag = __float_as_uint(s2.y);
+            float u = 0.f, v = 0.f, t;
+            const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
+                                                   : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+            if (ok) {
+                if (ANY) return true;
+                if (!(found && t == hit.t && s < hit.slot)) {
+                    found = true;
+                    maxt = t;
+                    hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                }
+            }
+            if (tag & NB_SLOT_LAST) break;
+            ++s;
+        }
     }
     return found;
 }
@@ -183,7 +257,8 @@ __device__ __forceinline__ bool nb_scan(const float4 *__restrict__ slots, uint32
 /* The query the render kernels use: tree walk, or flat scan when the scene qualifies. */
 template <bool ANY, bool FLAT>
 __device__ __forceinline__ bool nb_query(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes,
-                                         uint32_t n_slots, float3 o, float3 d, float mint, float maxt, NbHit &hit) {
+                                         uint32_t n_slots, float3 o, float3 d, float mint, float maxt, NbHit &hit, bool ordered = false) {
     if (FLAT) return nb_scan<ANY>(slots, n_slots, o, d, mint, maxt, hit);
+    if (ordered) return nb_traverse_ordered<ANY>(nodes, slots, n_nodes, o, d, mint, maxt, hit);
     return nb_traverse<ANY>(nodes, slots, n_nodes, o, d, mint, maxt, hit);
 }

@@ -46,6 +46,7 @@ def ctx(_session_ctx):
     _session_ctx.set_option("profile", 0)
     _session_ctx.set_option("flat_scan", -1)
     _session_ctx.set_option("walk", 1)
+    _session_ctx.set_option("ordered", 0)
     return _session_ctx
 
 

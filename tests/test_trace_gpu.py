@@ -11,7 +11,11 @@ pytestmark = pytest.mark.gpu
 
 
 def check(nb, ctx, scene, rays, want, flat=-1):
-    ctx.set_option("flat_scan", flat)       # 0: the reference's tree walk; 1: flat scan of the primitive list
+    # 0: the reference's left-first tree walk; 1: flat scan of the primitive list; 2: the ordered (near child
+    # first) walk with its tie rule — all three must return the reference's bits
+    ctx.set_option("ordered", 1 if flat == 2 else 0)
+    flat = 0 if flat == 2 else flat
+    ctx.set_option("flat_scan", flat)
     ctx.load(scene)
     got = ctx.trace_rays(rays, any_hit=True)
     assert len(got) == len(want)
@@ -24,7 +28,7 @@ def check(nb, ctx, scene, rays, want, flat=-1):
     assert np.array_equal(got["any_hit"], want["any_hit"])
 
 
-@pytest.mark.parametrize("flat", [0, 1])
+@pytest.mark.parametrize("flat", [0, 1, 2])
 @pytest.mark.parametrize("name", ["cbox", "table"])
 def test_golden_hits_bit_exact(nb, ctx, name, flat):
     scene = nb.read_nbs(golden(name + ".nbs"))
@@ -35,7 +39,7 @@ def test_golden_hits_bit_exact(nb, ctx, name, flat):
 
 
 @pytest.mark.skipif(not have_oracle_binary(), reason="oracle/_ref/nori_ref not present")
-@pytest.mark.parametrize("flat", [0, 1])
+@pytest.mark.parametrize("flat", [0, 1, 2])
 @pytest.mark.parametrize("name,xml,n", [("cbox", "scenes/cbox/cbox_path_mis.xml", 200000), ("table", "scenes/table/table_path_mis.xml", 150000)])
 def test_live_oracle_hits_bit_exact(nb, ctx, name, xml, n, tmp_path, flat):
     """~1M rays per scene: primary, bounce (mint == Epsilon -> adaptive epsilon) and NEE shadow

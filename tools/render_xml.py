@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """One render of a scene XML through the C++ host loader, for profiling under ncu:
-   python tools/render_xml.py scene.xml [spp=16] [size=WxH] [device_bvh=1] [repeat=1] [strategy=auto|wavefront|tile] [normalize=1]"""
+   python tools/render_xml.py scene.xml [spp=16] [size=WxH] [device_bvh=1] [repeat=1] [strategy=auto|wavefront|tile] [normalize=1] [ordered=0]"""
 import os
 import sys
 
@@ -15,6 +15,7 @@ if "size" in opt:
     s["camera"] = cam
 ctx = nb.Context(0)
 ctx.set_option("strategy", {"auto": 0, "wavefront": 1, "tile": 2}[opt.get("strategy", "auto")])
+ctx.set_option("ordered", int(opt.get("ordered", 0)))
 ctx.load(s, device_bvh=opt.get("device_bvh", "0") == "1")
 ctx.render_begin(nb.make_render_params(s, seed=1))
 for _ in range(int(opt.get("repeat", 1))):
