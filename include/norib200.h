@@ -40,7 +40,7 @@ enum { NB_SHAPE_MESH = 0, NB_SHAPE_SPHERE = 1 };
 enum { NB_BSDF_DIFFUSE = 0, NB_BSDF_MIRROR = 1, NB_BSDF_DIELECTRIC = 2, NB_BSDF_MICROFACET = 3,
        NB_BSDF_DISNEY = 4, NB_BSDF_NONE = 0xff };
 enum { NB_EMITTER_AREA = 0, NB_EMITTER_POINT = 1, NB_EMITTER_ENVMAP = 2, NB_EMITTER_SPOT = 3,
-       NB_EMITTER_DIRECTIONAL = 4 };
+       NB_EMITTER_DIRECTIONAL = 4, NB_EMITTER_VOLUME = 5 };
 enum { NB_TEXTURE_CONSTANT = 0, NB_TEXTURE_IMAGE = 1, NB_TEXTURE_CHECKERBOARD = 2 };
 enum { NB_TEXTURE_SPHERICAL = 1u,   /* PNGTexture::sphericalTexture */
        NB_TEXTURE_NORMAL_MAP = 2u }; /* PNGTexture with sRGB = false: a Texture<Normal3f> (PNGTexture.cpp:88-99, 155-162) */
@@ -98,7 +98,12 @@ typedef struct nb_emitter {
                                 spot (src/emitters/spotlight.cpp:16-24, 63-70, 167-187): { direction.xyz (normalized),
                                   cos(falloffStart deg), cos(totalWidth / 2 deg) }, position below, radiance = power / (2 pi);
                                 directional (src/emitters/directionalLight.cpp:31-38, 90-133): { direction.xyz
-                                  (normalized), cos(angle deg) }, radiance below */
+                                  (normalized), cos(angle deg) }, radiance below;
+                                volume light (src/emitters/volumelight.cpp:47-77): the shape whose volume emits: the
+                                  shape's own emitter when nb_shape.emitter names this record, else the emitter of
+                                  its medium (Medium::getEmitter, medium.cpp:59-64); the three position words are
+                                  { f32 1 / volume (Shape::pdfVolume, shape.cpp:103-111; sphere.h:45), u32 offset into
+                                  params of { bbox min.xyz, bbox extents.xyz } (Shape::sampleVolume, shape.cpp:97-101), 0 } */
     float    radiance[3];    /* area: radiance; point: power/(4 pi) (pointlight.cpp:44); envmap: m_radiance */
     float    position[3];    /* point light. Environment map: the three words are
                                 { u32 cdf_offset, f32 cdf_norm, 0 } — EnvMap::dpdf (environmentmap.cpp:146-161):

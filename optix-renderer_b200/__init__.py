@@ -19,7 +19,7 @@ HOST_LIB_PATH = os.path.join(HERE, "libnorib200_host.so")
 NB_OK, NB_E_INVALID, NB_E_CUDA, NB_E_NOMEM, NB_E_STATE, NB_E_UNSUPPORTED, NB_E_NO_DEVICE = 0, -1, -2, -3, -4, -5, -6
 SHAPE_MESH, SHAPE_SPHERE = 0, 1
 BSDF_DIFFUSE, BSDF_MIRROR, BSDF_DIELECTRIC, BSDF_MICROFACET, BSDF_DISNEY = 0, 1, 2, 3, 4
-EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP, EMITTER_SPOT, EMITTER_DIRECTIONAL = 0, 1, 2, 3, 4
+EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_VOLUME = 0, 1, 2, 3, 4, 5
 INTEGRATORS = {"path_mis": 0, "path_mats": 1, "direct_ems": 2, "direct_mats": 3, "direct_mis": 4,
                "normals": 5, "direct": 6, "av": 7, "path_vol_mats": 8, "path_vol_mis": 9, "preview": 10}
 MEDIUM_VACUUM, MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1, 2

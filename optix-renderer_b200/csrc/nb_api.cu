@@ -97,6 +97,7 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if (s->n_shapes == 0 || !s->shapes) return nb_fail(ctx, NB_E_INVALID, "nb_upload_scene: scene has no shapes");
     /* validate before touching the device */
     uint64_t prims = 0;
+    std::vector<int32_t> medium_emitter;
     bool ext_plugins = false;      /* disney / spot / directional: rendered by the EXT kernel variants */
     for (uint32_t i = 0; i < s->n_shapes; ++i) {
         const nb_shape &sh = s->shapes[i];
@@ -153,6 +154,19 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
         if (e.type == NB_EMITTER_AREA) {
             if (e.shape < 0 || e.shape >= (int32_t) s->n_shapes) return nb_fail(ctx, NB_E_INVALID, "emitter %u: area light without a shape", i);
         } else if (e.type == NB_EMITTER_POINT) {
+        } else if (e.type == NB_EMITTER_VOLUME) {
+            uint32_t off; memcpy(&off, &e.position[1], 4);
+            if (e.shape < 0 || e.shape >= (int32_t) s->n_shapes) return nb_fail(ctx, NB_E_INVALID, "emitter %u: volume light without a shape", i);
+            if (s->shapes[e.shape].type == NB_SHAPE_MESH && (!s->params || (uint64_t) off + 6 > s->n_params))
+                return nb_fail(ctx, NB_E_INVALID, "emitter %u: volume light box outside params", i);
+            if (!(e.position[0] > 0.f)) return nb_fail(ctx, NB_E_INVALID, "emitter %u: volume light needs 1 / volume > 0", i);
+            if (s->shapes[e.shape].emitter != (int32_t) i) {          /* the light of the shape's medium */
+                const int32_t m = s->shapes[e.shape].medium;
+                if (m < 0) return nb_fail(ctx, NB_E_INVALID, "emitter %u: volume light on a shape without a medium", i);
+                medium_emitter.resize(s->n_media, -1);
+                medium_emitter[m] = (int32_t) i;
+            }
+            ext_plugins = true;
         } else if (e.type == NB_EMITTER_SPOT || e.type == NB_EMITTER_DIRECTIONAL) {
             const uint64_t need = e.type == NB_EMITTER_SPOT ? 5 : 4;
             if (e.shape < 0 || !s->params || (uint64_t) e.shape + need > s->n_params)
@@ -216,6 +230,7 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->textures, s->n_textures, &d.textures))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->texels, s->n_texels * 4, &d.texels))) return rc;
     if ((rc = nb_upload(ctx, ctx->scene_allocs, s->params, s->n_params, &d.params))) return rc;
+    if ((rc = nb_upload(ctx, ctx->scene_allocs, medium_emitter.data(), medium_emitter.size(), &d.medium_emitter))) return rc;
     d.n_media = s->n_media; d.ambient_medium = s->ambient_medium;
     d.n_shapes = s->n_shapes; d.n_bsdfs = s->n_bsdfs; d.n_emitters = s->n_emitters;
     d.envmap_emitter = envmap;

@@ -58,6 +58,7 @@ struct NbDeviceScene {
     const float *density = nullptr;     /* voxels of heterogeneous media */
     const nb_texture *textures = nullptr;
     const float *texels = nullptr;      /* RGBA, 16-byte aligned */
+    const int32_t *medium_emitter = nullptr;   /* per medium: index of its volume light (Medium::getEmitter), -1 = none; null when no medium has one */
     const float *params = nullptr;      /* nb_scene_desc.params: disney / spot / directional parameters */
     uint32_t n_shapes = 0, n_bsdfs = 0, n_emitters = 0, n_media = 0;
     int32_t envmap_emitter = -1, ambient_medium = -1;

@@ -57,7 +57,9 @@ __device__ __forceinline__ void nb_hit_info(const NbDeviceScene &sc, const NbHit
 }
 
 /* AreaEmitter::eval (arealight.cpp:58-73) for EmitterQueryRecord(ref, p, n) */
+template <bool EXT>
 __device__ __forceinline__ f3 nb_area_eval(const nb_emitter &em, f3 ref, f3 p, f3 n) {
+    if (EXT && em.type == NB_EMITTER_VOLUME) return mk3(em.radiance[0], em.radiance[1], em.radiance[2]);   /* VolumeEmitter::eval */
     const f3 wi = normalize(p - ref);
     if (dot(n, -wi) >= 0.f) return mk3(em.radiance[0], em.radiance[1], em.radiance[2]);
     return mk3(0.f);
@@ -87,11 +89,11 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
         const nb_emitter em = sc.emitters[sh.emitter];
         if (MIS && !(ps.flags & NB_FLAG_PRIMARY) && (ps.flags & NB_FLAG_BSDF_OK)) {
             const f3 wi_e = normalize(its.p - ps.o);
-            const float pdfmat_ems = nb_area_pdf(sh, ps.o, its.p, its.sh.n, wi_e) / n_lights;
+            const float pdfmat_ems = nb_hit_pdf<EXT>(sc, sh, ps.o, its.p, its.sh.n, wi_e) / n_lights;
             if (ps.pdfmat + pdfmat_ems > NB_EPS) ps.w_mats = ps.pdfmat / (ps.pdfmat + pdfmat_ems);
         }
         if (MIS && (ps.flags & NB_FLAG_DISCRETE)) ps.w_mats = 1.f;
-        ps.Li += (MIS ? ps.w_mats : 1.f) * ps.thr * nb_area_eval(em, ps.o, its.p, its.sh.n);
+        ps.Li += (MIS ? ps.w_mats : 1.f) * ps.thr * nb_area_eval<EXT>(em, ps.o, its.p, its.sh.n);
     } else if (MIS && (ps.flags & NB_FLAG_DISCRETE)) ps.w_mats = 1.f;
 
     const uint32_t bounce = ps.flags >> NB_BOUNCE_SHIFT;
@@ -182,7 +184,7 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, const Nb
     }
     f3 result = mk3(0.f);
     if (INTEG != NB_INTEGRATOR_DIRECT && sh.emitter >= 0)
-        result += nb_area_eval(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
+        result += nb_area_eval<EXT>(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
     if (sh.bsdf < 0) return result;
     nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
     nb_bsdf_resolve<EXT>(sc, bsdf, its.uv);
@@ -245,9 +247,9 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, const Nb
             nb_shape sh2; NbIts its2;
             nb_hit_info<EXT>(sc, hit2, its.p, d2, sh2, its2);
             if (sh2.emitter >= 0) {
-                result_mats = col * nb_area_eval(sc.emitters[sh2.emitter], its.p, its2.p, its2.sh.n);
+                result_mats = col * nb_area_eval<EXT>(sc.emitters[sh2.emitter], its.p, its2.p, its2.sh.n);
                 if (INTEG == NB_INTEGRATOR_DIRECT_MIS) {
-                    const float pdf_ems = nb_area_pdf(sh2, its.p, its2.p, its2.sh.n, normalize(its2.p - its.p)) / n_lights;
+                    const float pdf_ems = nb_hit_pdf<EXT>(sc, sh2, its.p, its2.p, its2.sh.n, normalize(its2.p - its.p)) / n_lights;
                     if (pdf_mat + pdf_ems > NB_EPS) w_mat = pdf_mat / (pdf_mat + pdf_ems);
                 }
             }
@@ -314,12 +316,26 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
     const f3 p = mi ? ps.o + ps.d * tm : its.p;
     ps.thr = ps.thr * nb_transmittance<EXT>(sc, medium, ps.o, p, ps.rng);
     uint32_t measure = (ps.flags >> NB_MEASURE_SHIFT) & 3u;
-    /* captured emission; volume emitters have no kernel (the host loader refuses them) */
+    /* captured emission (path_vol_mats.cpp:52-68, path_vol_mis.cpp:146-173): inside a medium that carries a volume
+     * light, every medium interaction collects its radiance; the MIS pdf is taken at its.p as the reference does */
+    if (EXT && mi && sc.medium_emitter) {
+        const int32_t me = sc.medium_emitter[medium];
+        if (me >= 0) {
+            const nb_emitter em = sc.emitters[me];
+            float w = 1.f;
+            if (MIS && measure != NB_MEASURE_DISCRETE) {
+                const f3 dlt = its.p - ps.o;
+                const float pdf_mat_em = em.position[0] * dot(dlt, dlt) / (float) sc.n_emitters;
+                w = ps.pdfmat > NB_EPS ? ps.pdfmat / (ps.pdfmat + pdf_mat_em) : 0.f;
+            }
+            ps.Li += w * ps.thr * mk3(em.radiance[0], em.radiance[1], em.radiance[2]);
+        }
+    }
     if (!mi && sh.emitter >= 0) {
-        const f3 Le = nb_area_eval(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
+        const f3 Le = nb_area_eval<EXT>(sc.emitters[sh.emitter], ps.o, its.p, its.sh.n);
         float w = 1.f;
         if (MIS && measure != NB_MEASURE_DISCRETE) {
-            const float pdf_mat_em = nb_area_pdf(sh, ps.o, its.p, its.sh.n, normalize(its.p - ps.o)) / (float) sc.n_emitters;
+            const float pdf_mat_em = nb_hit_pdf<EXT>(sc, sh, ps.o, its.p, its.sh.n, normalize(its.p - ps.o)) / (float) sc.n_emitters;
             w = ps.pdfmat > NB_EPS ? ps.pdfmat / (ps.pdfmat + pdf_mat_em) : 0.f;
         }
         ps.Li += w * ps.thr * Le;

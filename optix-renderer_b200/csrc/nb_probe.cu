@@ -38,6 +38,7 @@ __global__ void nb_k_emitter_probe(NbDeviceScene sc, uint32_t emitter, const flo
     f3 e = mk3(0.f);
     if (em.type == NB_EMITTER_ENVMAP) e = nb_env_eval(sc, emitter, es.wi);
     else if (em.type == NB_EMITTER_POINT || em.type == NB_EMITTER_SPOT) e = v;
+    else if (em.type == NB_EMITTER_VOLUME) e = mk3(em.radiance[0], em.radiance[1], em.radiance[2]);
     else e = v * es.pdf;
     float *o = out + 12 * i;
     o[0] = es.wi.x; o[1] = es.wi.y; o[2] = es.wi.z; o[3] = v.x; o[4] = v.y; o[5] = v.z;

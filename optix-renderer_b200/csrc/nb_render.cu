@@ -79,11 +79,11 @@ __device__ __forceinline__ bool nb_shade_path(const NbDeviceScene &sc, const NbW
         const f3 wi_e = normalize(its.p - o);                       /* EmitterQueryRecord(ref, p, n) */
         if (MIS && !(flags & NB_FLAG_PRIMARY) && (flags & NB_FLAG_BSDF_OK)) {
             const float pdfmat = s1.w;
-            const float pdfmat_ems = nb_area_pdf(sh, o, its.p, its.sh.n, wi_e) / n_lights;
+            const float pdfmat_ems = nb_hit_pdf<true>(sc, sh, o, its.p, its.sh.n, wi_e) / n_lights;
             if (pdfmat + pdfmat_ems > NB_EPS) w_mats = pdfmat / (pdfmat + pdfmat_ems);
         }
         if (MIS && (flags & NB_FLAG_DISCRETE)) w_mats = 1.f;
-        if (dot(its.sh.n, -wi_e) >= 0.f) {                           /* AreaEmitter::eval */
+        if (dot(its.sh.n, -wi_e) >= 0.f || em.type == NB_EMITTER_VOLUME) {   /* AreaEmitter::eval / VolumeEmitter::eval */
             const f3 Le = mk3(em.radiance[0], em.radiance[1], em.radiance[2]);
             Li += (MIS ? w_mats : 1.f) * thr * Le;
         }

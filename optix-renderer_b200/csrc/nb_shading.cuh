@@ -289,6 +289,17 @@ __device__ __forceinline__ float nb_area_pdf(const nb_shape &sh, f3 ref, f3 p, f
     return prob * dot(dlt, dlt) / fabsf(c);
 }
 
+/* Emitter::pdf for the emitter of a shape the path just hit: AreaEmitter::pdf, or VolumeEmitter::pdf
+ * (volumelight.cpp:79-83: pdfVolume * squared distance) when a volume light sits on the shape itself */
+template <bool EXT = true>
+__device__ __forceinline__ float nb_hit_pdf(const NbDeviceScene &sc, const nb_shape &sh, f3 ref, f3 p, f3 n, f3 wi) {
+    if (EXT) {
+        const nb_emitter *e = sc.emitters + sh.emitter;
+        if (e->type == NB_EMITTER_VOLUME) { const f3 dlt = p - ref; return e->position[0] * dot(dlt, dlt); }
+    }
+    return nb_area_pdf(sh, ref, p, n, wi);
+}
+
 /* DiscretePDF::sample (dpdf.h:124-129): lower_bound on cdf[0..n], index clamp */
 __device__ __forceinline__ uint32_t nb_cdf_sample(const float *cdf, uint32_t n_entries, float x) {
     uint32_t lo = 0, hi = n_entries + 1;         /* cdf has n_entries+1 values */
@@ -363,6 +374,34 @@ static __device__ __noinline__ NbF8 nb_spot_dir_sample(const float *p, const nb_
     return r;
 }
 
+
+/* VolumeEmitter::sample (src/emitters/volumelight.cpp:52-77) over Shape::sampleVolume (sphere.cpp:139-143 with
+ * Warp::squareToUniformSphereVolume warp.cpp:88-92; any other shape: its bounding box, shape.cpp:97-101). The
+ * reference takes the third coordinate of the volume sample from a function-local static sampler shared by all
+ * render threads; here it is a hash of the two sample coordinates the integrator hands over (documented deviation:
+ * same distribution, reproducible). */
+static __device__ __noinline__ NbF8 nb_volume_light_sample(const nb_shape *shp, const float *box, const nb_emitter *emp,
+                                                           float rx, float ry, float rz, float sx, float sy) {
+    const nb_emitter em = *emp;
+    const nb_shape sh = *shp;
+    uint32_t h = __float_as_uint(sx) * 0x9E3779B1u ^ (__float_as_uint(sy) * 0x85EBCA77u + 0x165667B1u);
+    h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 12; h *= 0x297A2D39u; h ^= h >> 15;
+    const float sz = __uint_as_float((h >> 9) | 0x3f800000u) - 1.0f;
+    f3 p;
+    if (sh.type == NB_SHAPE_SPHERE) {
+        float2 s2; s2.x = sx; s2.y = sy;
+        p = mk3(sh.center[0], sh.center[1], sh.center[2]) + sh.radius * (cbrtf(sz) * square_to_uniform_sphere(s2));
+    } else p = mk3(__ldg(box) + __ldg(box + 3) * sx, __ldg(box + 1) + __ldg(box + 4) * sy, __ldg(box + 2) + __ldg(box + 5) * sz);
+    const f3 ref = mk3(rx, ry, rz), dlt = p - ref;
+    const f3 wi = normalize(dlt);
+    const float d2 = dot(dlt, dlt), pdf = em.position[0] * d2;
+    NbF8 r;
+    const f3 v = pdf == 0.f ? mk3(0.f) : mk3(em.radiance[0], em.radiance[1], em.radiance[2]) / pdf;
+    r.a = make_float4(v.x, v.y, v.z, pdf);
+    r.b = make_float4(wi.x, wi.y, wi.z, sqrtf(d2) - NB_EPS);
+    return r;
+}
+
 /* Emitter::sample for area (arealight.cpp:75-103 -> mesh.cpp:50-71 / sphere.cpp:126-132) and
  * point lights (pointlight.cpp:47-63). Returns radiance / pdf. */
 template <bool EXT = true>
@@ -379,6 +418,13 @@ __device__ __forceinline__ f3 nb_emitter_sample(const NbDeviceScene &sc, uint32_
         return mk3(em.radiance[0], em.radiance[1], em.radiance[2]) / dot(dlt, dlt);
     }
     if (EXT && em.type == NB_EMITTER_ENVMAP) return nb_env_sample(sc, sc.emitters + emitter, ref, s, out);
+    if (EXT && em.type == NB_EMITTER_VOLUME) {
+        const NbF8 r = nb_volume_light_sample(sc.shapes + em.shape, sc.params + __float_as_uint(em.position[1]), sc.emitters + emitter,
+                                              ref.x, ref.y, ref.z, s.x, s.y);
+        out.wi = mk3(r.b.x, r.b.y, r.b.z); out.pdf = r.a.w; out.ray_mint = NB_EPS; out.ray_maxt = r.b.w;
+        out.ray_o = ref; out.ray_d = out.wi;                        /* Ray3f(ref, wi, Epsilon, dist - Epsilon), volumelight.cpp:64 */
+        return mk3(r.a.x, r.a.y, r.a.z);
+    }
     if (EXT && em.type >= NB_EMITTER_SPOT) {
         const NbF8 r = nb_spot_dir_sample(sc.params + em.shape, sc.emitters + emitter, ref.x, ref.y, ref.z, s.x, s.y);
         out.wi = mk3(r.b.x, r.b.y, r.b.z); out.pdf = r.a.w; out.ray_mint = NB_EPS; out.ray_maxt = r.b.w;

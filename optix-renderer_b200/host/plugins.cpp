@@ -159,6 +159,21 @@ private:
 };
 NORI_REGISTER_CLASS(PointLight, "point")
 
+/* src/emitters/volumelight.cpp:14-77: constant radiance inside the volume of the shape that owns it (directly, or
+ * through its medium); sampled uniformly over Shape::sampleVolume (sphere: the ball; mesh: its bounding box) */
+class VolumeEmitter : public Emitter {
+public:
+    explicit VolumeEmitter(const PropertyList &p) { m_radiance = p.getColor("radiance"); lightProb = p.getFloat("lightWeight", 1.f); }
+    bool getB200EmitterData(nb_emitter &o, FlatScene &) const override {
+        memset(&o, 0, sizeof(o));
+        o.type = NB_EMITTER_VOLUME; o.shape = -1;                        /* owner and volume are filled in by Scene::flatten */
+        for (int i = 0; i < 3; ++i) o.radiance[i] = m_radiance[i];
+        return true;
+    }
+    std::string toString() const override { return "VolumeEmitter[]"; }
+};
+NORI_REGISTER_CLASS(VolumeEmitter, "volumelight")
+
 class SpotLight : public Emitter {                  /* src/emitters/spotlight.cpp:14-24, 48-49 */
 public:
     explicit SpotLight(const PropertyList &p) {
@@ -419,7 +434,7 @@ public:
     bool getB200MediumData(nb_medium &out, FlatScene &) const override {
         memset(&out, 0, sizeof(out));
         out.type = NB_MEDIUM_VACUUM;
-        return m_emitter == nullptr;
+        return true;
     }
     std::string toString() const override { return "VacuumMedium[]"; }
 };
@@ -433,7 +448,7 @@ public:
         out.type = NB_MEDIUM_HOMOGENEOUS;
         for (int i = 0; i < 3; ++i) out.mu_t[i] = m_density * m_sigma_a[i] + m_density * m_sigma_s[i];   /* mu_a + mu_s */
         m_phase->getB200PhaseData(out);
-        return m_emitter == nullptr;                    /* volume emitters (volumelight.cpp) have no kernel */
+        return true;
     }
     std::string toString() const override { return "HomogeneousMedium[]"; }
 private:
@@ -563,6 +578,7 @@ public:
     uint32_t getPrimitiveCount() const override { return 1; }
     BoundingBox3f getBoundingBox(uint32_t) const override { return m_bbox; }
     Point3f getCentroid(uint32_t) const override { return m_position; }
+    float getVolume() const override { return (float) (4.f / 3.f * M_PI * std::pow(m_radius, 3)); }   /* sphere.h:45 */
     void getB200Shape(nb_shape &rec, FlatScene &) const override {
         rec.type = NB_SHAPE_SPHERE; rec.prim_count = 1; rec.radius = m_radius;
         for (int i = 0; i < 3; ++i) rec.center[i] = m_position[i];

@@ -64,11 +64,12 @@ public:
     void addChild(NoriObject *obj) override;            /* medium.cpp:50-72: one phase, one emitter */
     void activate() override;                           /* isotropic phase by default (medium.cpp:22-24) */
     /* replaces getOptixMediumData (medium.h:68); false = no GPU kernel for this medium */
+    Emitter *getEmitter() const { return m_emitter; }
     virtual bool getB200MediumData(nb_medium &out, FlatScene &flat) const = 0;   /* heterogeneous media append their voxels to flat.density */
 protected:
     Color3f m_sigma_a, m_sigma_s;                       /* normalized colour * intensity */
     PhaseFunction *m_phase = nullptr;
-    Emitter *m_emitter = nullptr;                       /* volume emitter: no kernel */
+    Emitter *m_emitter = nullptr;                       /* volume emitter (volumelight.cpp) */
 };
 
 /* include/nori/shape.h:104-237 */
@@ -86,6 +87,10 @@ public:
     const Medium *getMedium() const { return m_medium; }
     Emitter *getEmitter() const { return m_emitter; }
     const Texture *getNormalMap() const { return m_normalMap; }
+    Emitter *getMediumEmitter() const { return m_medium ? m_medium->getEmitter() : nullptr; }       /* shape.h */
+    virtual float getVolume() const {                   /* Shape::updateVolume, shape.cpp:108-111: the bounding box's */
+        return (m_bbox.max[0] - m_bbox.min[0]) * (m_bbox.max[1] - m_bbox.min[1]) * (m_bbox.max[2] - m_bbox.min[2]);
+    }
     bool isEmitter() const { return m_emitter != nullptr; }
     /* replaces getOptixBuildInput / getOptixHitgroupRecords (shape.h:194-201): appends this
      * shape's geometry to the flat arrays and fills the geometric part of the record */

@@ -11,7 +11,11 @@ namespace nori {
 Scene::Scene(const PropertyList &) {}
 
 Scene::~Scene() {
-    for (Emitter *e : m_emitters) if (!e->hasShape()) delete e;   /* shape-owned emitters die with their shape */
+    for (Emitter *e : m_emitters) {                               /* shape- and medium-owned emitters die with their owner */
+        bool owned = e->hasShape();
+        for (Shape *s : m_shapes) owned |= s->getMediumEmitter() == e;
+        if (!owned) delete e;
+    }
     for (Shape *s : m_shapes) delete s;
     delete m_camera; delete m_integrator; delete m_sampler; delete m_ambientMedium;
     for (NoriObject *o : m_other) delete o;
@@ -22,7 +26,8 @@ void Scene::addChild(NoriObject *obj) {
         case EShape: {
             Shape *shape = static_cast<Shape *>(obj);
             m_shapes.push_back(shape);
-            if (shape->isEmitter()) m_emitters.push_back(shape->getEmitter());   /* scene.cpp:211-213 */
+            if (shape->isEmitter()) m_emitters.push_back(shape->getEmitter());   /* scene.cpp:211-215 */
+            if (shape->getMediumEmitter()) m_emitters.push_back(shape->getMediumEmitter());
         } break;
         case EEmitter: m_emitters.push_back(static_cast<Emitter *>(obj)); break;
         case ESampler:
@@ -94,8 +99,21 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
             rec.medium = (int32_t) out.media.size();
             out.media.push_back(m);
         }
-        for (size_t e = 0; e < m_emitters.size(); ++e)
-            if (m_emitters[e] == s->getEmitter()) { rec.emitter = (int32_t) e; out.emitters[e].shape = (int32_t) i; }
+        for (size_t e = 0; e < m_emitters.size(); ++e) {
+            const bool surface = m_emitters[e] == s->getEmitter(), inside = m_emitters[e] == s->getMediumEmitter();
+            if (!surface && !inside) continue;
+            if (surface) rec.emitter = (int32_t) e;
+            out.emitters[e].shape = (int32_t) i;
+            if (out.emitters[e].type == NB_EMITTER_VOLUME) {             /* VolumeEmitter::cloneAndInit, volumelight.cpp:20-22 */
+                if (!s->getMedium()) return fail("There is no shape or medium attached to this volume light.");
+                out.emitters[e].position[0] = 1 / s->getVolume();        /* Shape::pdfVolume, shape.cpp:103-106 */
+                const uint32_t off = (uint32_t) out.params.size();       /* Shape::sampleVolume's box, shape.cpp:97-101 */
+                memcpy(&out.emitters[e].position[1], &off, 4);
+                const BoundingBox3f &b = s->getBoundingBox();
+                for (int k = 0; k < 3; ++k) out.params.push_back(b.min[k]);
+                for (int k = 0; k < 3; ++k) out.params.push_back(b.max[k] - b.min[k]);
+            }
+        }
         out.shapes.push_back(rec);
     }
     /* pad optional vertex attributes to the full vertex count */

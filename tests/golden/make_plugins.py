@@ -116,6 +116,13 @@ def scene(integrator, size, spp, lights, **extra):
             + CAMERA % size + GEOMETRY % e + lights + "</scene>\n")
 
 
+VOL_LIGHT = """<medium type="homog">
+			<color name="sigma_a" value="0.4 0.4 0.4"/>
+			<color name="sigma_s" value="1.5 1.5 1.5"/>%s
+			<emitter type="volumelight"><color name="radiance" value="%s"/></emitter>
+		</medium>"""
+SURFACE_VOL_LIGHT = '<emitter type="volumelight"><color name="radiance" value="0.5 1 0.5"/></emitter>\n\t\t'
+
 W = (160, 120)
 SCENES = {
     # name: (xml text, golden spp)
@@ -134,6 +141,14 @@ SCENES = {
     "normals_direction": (scene('<integrator type="normals"><point name="direction" value="0.6,0,0.8"/></integrator>', W, 32, ""), 32),
     "av": (scene('<integrator type="av"><float name="length" value="1.5"/></integrator>', W, 64, ""), 64),
     "preview": (scene('<integrator type="preview"/>', W, 64, LIGHTS_SPOT_DIR, sphere_extra=DISNEY_A), 64),
+    # volume lights (volumelight.cpp): inside the ball of a sphere and inside the bounding box of a mesh, seen by both
+    # volume integrators; one of them also attached to the shape itself ("with-surface" case of the reference's scenes)
+    "volumelight_mats": (scene('<integrator type="path_vol_mats"/>', W, 128, "", sphere_extra=VOL_LIGHT % ("", "3 2 1"),
+                               cube_extra=VOL_LIGHT % ('\n\t\t\t<phase type="anisophase"/>', "1 2 4")), 128),
+    "volumelight_mis": (scene('<integrator type="path_vol_mis"/>', W, 128, "", sphere_extra=VOL_LIGHT % ("", "3 2 1"),
+                              cube_extra=VOL_LIGHT % ('\n\t\t\t<phase type="anisophase"/>', "1 2 4")), 128),
+    "volumelight_surface_mis": (scene('<integrator type="path_vol_mis"/>', W, 128, POINT.replace("1000,1000,1000", "60,60,60"),
+                                      sphere_extra=SURFACE_VOL_LIGHT + VOL_LIGHT % ("", "3 2 1")), 128),
     "preview_nolight": (scene('<integrator type="preview"/>', W, 16, ""), 16),
 }
 BSDF_PROBES = {  # name: (scene, shape index)

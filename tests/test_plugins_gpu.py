@@ -1,7 +1,7 @@
 """SURVEY 8(f) rank 1-2 rows on the GPU against the reference's own plugins (fixtures of
 tests/golden/make_plugins.py): the disney BSDF (eval / pdf / sample record by record, then in images),
 the spot and directional emitters (Emitter::sample record by record), normal maps on meshes and
-spheres, and the normals / av / preview integrators."""
+spheres, the normals / av / preview integrators, and volume lights inside media (sphere ball, mesh box)."""
 import numpy as np
 import pytest
 
@@ -59,7 +59,8 @@ def test_spot_and_directional_sample_match_reference(nb, ctx, name, index):
 
 IMAGES = [("disney_spot_dir_path_mis", 128), ("disney_spot_dir_direct_mis", 128), ("disney_path_mats_area", 128),
           ("normalmap_direct_mis", 64), ("normalmap_normals", 32), ("normals_direction", 32), ("av", 64),
-          ("preview", 64), ("preview_nolight", 16)]
+          ("preview", 64), ("preview_nolight", 16),
+          ("volumelight_mats", 128), ("volumelight_mis", 128), ("volumelight_surface_mis", 128)]
 
 
 @pytest.mark.parametrize("name,spp", IMAGES)
