@@ -210,6 +210,12 @@ typedef struct nb_hit {
 /* ---- rendering ----------------------------------------------------------------------------- */
 #define NB_FILTER_RESOLUTION 32   /* NORI_FILTER_RESOLUTION, include/nori/rfilter.h:25 */
 
+/* Render layers of the reference (integrator.h:29-39). Composite is the film itself. Normal: the shading normal of
+ * the first hit as PreviewIntegrator reports it (PreviewIntegrator.cpp:37), 0 from every other integrator and on a
+ * miss; like every ImageBlock it drops samples with a negative component (block.cpp:94). Albedo: 0 in every
+ * integrator of the reference, so it has no buffer here. */
+enum { NB_LAYER_COMPOSITE = 0, NB_LAYER_NORMAL = 1 };
+
 typedef struct nb_render_params {
     uint32_t integrator;                       /* NB_INTEGRATOR_* */
     float    filter_radius;                    /* ReconstructionFilter::getRadius() */
@@ -219,7 +225,8 @@ typedef struct nb_render_params {
     uint32_t max_depth;                        /* 0 = unbounded, as the reference */
     float    integrator_params[3];             /* normals: NormalIntegrator::direction (normals.cpp:12, default 0 0 1);
                                                   av: [0] = AverageVisibilityIntegrator::m_length (av.cpp:14) */
-    uint32_t reserved;
+    uint32_t layers;                           /* NB_LAYER_* bits: extra render layers to accumulate beside the composite
+                                                  (ERenderLayer, integrator.h:29-39; renderBlock puts them at render.cpp:455-457) */
 } nb_render_params;
 
 typedef struct nb_counters {
@@ -300,6 +307,8 @@ int  nb_film_shape(nb_ctx *ctx, uint32_t *rows, uint32_t *cols, uint32_t *border
  * Color4f = {sum w*r, sum w*g, sum w*b, sum w}, block.h:49). normalize != 0: instead writes
  * H x W x 3 floats = ImageBlock::toBitmap() (block.cpp:76-82). */
 int  nb_film_download(nb_ctx *ctx, float *out, int normalize);
+/* The same for one layer (NB_LAYER_*); a layer that was not requested in nb_render_params.layers fails with NB_E_STATE. */
+int  nb_film_download_layer(nb_ctx *ctx, int layer, float *out, int normalize);
 /* Device address of the accumulators (rows*cols*4 floats) for the NCCL film reduce. */
 int  nb_film_device_ptr(nb_ctx *ctx, void **ptr, uint64_t *n_floats);
 int  nb_get_counters(nb_ctx *ctx, nb_counters *out);

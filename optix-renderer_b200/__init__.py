@@ -49,7 +49,7 @@ hit_dtype = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("shape", "<i4")
 render_params_dtype = np.dtype([("integrator", "<u4"), ("filter_radius", "<f4"),
                                 ("filter_table", "<f4", FILTER_RESOLUTION + 1), ("pad0", "<u4"), ("seed", "<u8"),
                                 ("pool_paths", "<u4"), ("max_depth", "<u4"), ("integrator_params", "<f4", 3),
-                                ("reserved", "<u4")])
+                                ("layers", "<u4")])
 SECTION_DTYPES = {"shapes": shape_dtype, "bsdfs": bsdf_dtype, "emitters": emitter_dtype, "camera": camera_dtype,
                   "bvh_nodes": bvh_node_dtype, "render": render_params_dtype, "media": medium_dtype, "textures": texture_dtype}
 
@@ -91,7 +91,7 @@ EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_las
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
            "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe",
-           "nb_bsdf_probe"]
+           "nb_bsdf_probe", "nb_film_download_layer"]
 
 _lib = None
 
@@ -126,6 +126,7 @@ def load_library(path=None):
     lib.nb_film_clear.argtypes = [C.c_void_p]
     lib.nb_film_shape.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     lib.nb_film_download.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    lib.nb_film_download_layer.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
     lib.nb_film_device_ptr.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.nb_get_counters.argtypes = [C.c_void_p, C.POINTER(Counters)]
     lib.nb_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
@@ -315,12 +316,13 @@ class Context:
         self._check(self.lib.nb_film_shape(self.handle, C.byref(r), C.byref(c), C.byref(b)))
         return r.value, c.value, b.value
 
-    def film_download(self, normalize=True, out=None):
+    def film_download(self, normalize=True, out=None, layer=0):
+        """layer 0: the composite; 1: the normal layer (needs render params with layers=1)."""
         rows, cols, b = self.film_shape()
         shape = (rows - 2 * b, cols - 2 * b, 3) if normalize else (rows, cols, 4)
         if out is None:
             out = np.empty(shape, dtype=np.float32)
-        self._check(self.lib.nb_film_download(self.handle, _ptr(out), int(normalize)))
+        self._check(self.lib.nb_film_download_layer(self.handle, int(layer), _ptr(out), int(normalize)))
         return out
 
     def film_device_ptr(self):
@@ -337,7 +339,7 @@ class Context:
         self._check(self.lib.nb_set_option(self.handle, name.encode(), int(value)))
 
 
-def make_render_params(scene, integrator=None, seed=0, pool_paths=0, max_depth=0):
+def make_render_params(scene, integrator=None, seed=0, pool_paths=0, max_depth=0, layers=0):
     """nb_render_params from a scene dict's "render" section (filter table, integrator) + overrides."""
     p = np.zeros(1, dtype=render_params_dtype)
     if "render" in scene:
@@ -349,6 +351,7 @@ def make_render_params(scene, integrator=None, seed=0, pool_paths=0, max_depth=0
     p["seed"] = seed
     p["pool_paths"] = pool_paths
     p["max_depth"] = max_depth
+    p["layers"] = layers
     return p
 
 

@@ -9,6 +9,7 @@
 
 struct NbFilm {
     float4 *data;
+    float4 *normal;               /* NB_LAYER_NORMAL accumulators, same geometry; null unless requested */
     uint32_t rows, cols, border;
     float radius, lookup;
     float table[NB_FILTER_RESOLUTION + 1];
@@ -24,9 +25,10 @@ struct NbPlan {
 };
 
 /* ImageBlock::put(pos, value), block.cpp:93-123, on the full-image block (offset 0). */
-__device__ __forceinline__ void nb_film_put(const NbFilm &film, float px, float py, f3 v, unsigned long long *stats) {
+__device__ __forceinline__ void nb_film_put(const NbFilm &film, float px, float py, f3 v, unsigned long long *stats, float4 *layer = nullptr) {
     const bool valid = v.x >= 0.f && v.y >= 0.f && v.z >= 0.f && isfinite(v.x) && isfinite(v.y) && isfinite(v.z);
-    if (!valid) { atomicAdd(&stats[NB_STAT_INVALID], 1ULL); return; }      /* Color3f::isValid, common.cpp:254 */
+    if (!valid) { if (!layer) atomicAdd(&stats[NB_STAT_INVALID], 1ULL); return; }      /* Color3f::isValid, common.cpp:254 */
+    float4 *const data = layer ? layer : film.data;
     const float posx = px - 0.5f + (float) film.border, posy = py - 0.5f + (float) film.border;
     int x0 = (int) ceilf(posx - film.radius), x1 = (int) floorf(posx + film.radius);
     int y0 = (int) ceilf(posy - film.radius), y1 = (int) floorf(posy + film.radius);
@@ -34,7 +36,7 @@ __device__ __forceinline__ void nb_film_put(const NbFilm &film, float px, float 
     x1 = min(x1, (int) film.cols - 1); y1 = min(y1, (int) film.rows - 1);
     for (int y = y0; y <= y1; ++y) {
         const float wy = film.table[(int) (fabsf((float) y - posy) * film.lookup)];
-        float4 *row = film.data + (size_t) y * film.cols;
+        float4 *row = data + (size_t) y * film.cols;
         for (int x = x0; x <= x1; ++x) {
             const float wgt = film.table[(int) (fabsf((float) x - posx) * film.lookup)] * wy;
             atomicAdd(row + x, make_float4(v.x * wgt, v.y * wgt, v.z * wgt, wgt));   /* RED.128 on sm_90+ */

@@ -142,8 +142,10 @@ __device__ __forceinline__ bool nb_path_bounce(const NbDeviceScene &sc, uint32_t
 
 /* The depth-1 integrators, one whole sample. Returns Li. */
 template <int INTEG, bool FLAT, bool EXT>
-__device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, const NbPlan &plan, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any) {
+__device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, const NbPlan &plan, NbPathRegs &ps, uint32_t &n_closest, uint32_t &n_any,
+                                                f3 &layer_normal) {
     NbHit hit;
+    layer_normal = mk3(0.f);
     ++n_closest;
     if (!nb_closest<FLAT>(sc, ps.o, ps.d, ps.mint, ps.maxt, hit)) {
         if (INTEG == NB_INTEGRATOR_AV) return mk3(1.f);                                                     /* av.cpp:21-22 */
@@ -168,7 +170,8 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, const Nb
         ++n_closest;                                                  /* the reference asks for the closest hit here, not a shadow query */
         return nb_closest<FLAT>(sc, its.p, v, NB_EPS, plan.iparam[0], h2) ? mk3(0.f) : mk3(1.f);
     }
-    if (INTEG == NB_INTEGRATOR_PREVIEW) {                             /* PreviewIntegrator.cpp:39-76 */
+    if (INTEG == NB_INTEGRATOR_PREVIEW) {                             /* PreviewIntegrator.cpp:37-76 */
+        layer_normal = its.sh.n;
         if (sc.n_emitters == 0) return mk3(fabsf(its.sh.n.x), fabsf(its.sh.n.y), fabsf(its.sh.n.z));
         const f3 wo = its.sh.to_local(normalize(ps.o - its.p));
         const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
@@ -507,8 +510,10 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 }
             }
         } else if (active) {
-            const f3 Li = nb_direct_sample<INTEG, FLAT, EXT>(sc, tp.plan, ps, n_closest, n_any);
+            f3 layer_normal;
+            const f3 Li = nb_direct_sample<INTEG, FLAT, EXT>(sc, tp.plan, ps, n_closest, n_any, layer_normal);
             nb_film_put(film, ps.px, ps.py, Li, stats);
+            if (INTEG == NB_INTEGRATOR_PREVIEW && film.normal) nb_film_put(film, ps.px, ps.py, layer_normal, stats, film.normal);
             active = false;
         }
     }

@@ -322,8 +322,9 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     uint32_t pool = params->pool_paths ? params->pool_paths : (1u << 20);
     pool = (pool + 255u) & ~255u;
     const uint32_t border = (uint32_t) ceilf(params->filter_radius - 0.5f);      /* block.cpp:57 */
+    const bool want_normal = (params->layers & NB_LAYER_NORMAL) != 0;
     if (ctx->render && ctx->render->wave.pool == pool && ctx->render->film.rows == cam.height + 2 * border &&
-        ctx->render->film.cols == cam.width + 2 * border) {
+        ctx->render->film.cols == cam.width + 2 * border && (ctx->render->film.normal != nullptr) == want_normal) {
         /* same geometry as the previous render: keep the device buffers, start a fresh film */
         NbRenderState *r = ctx->render;
         r->params = *params;
@@ -346,6 +347,11 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     memcpy(r->film.table, params->filter_table, sizeof(r->film.table));
     int rc;
     if ((rc = nb_dev_alloc(ctx, r, &r->film.data, (size_t) r->film.rows * r->film.cols))) return rc;
+    r->film.normal = nullptr;
+    if (want_normal) {
+        if ((rc = nb_dev_alloc(ctx, r, &r->film.normal, (size_t) r->film.rows * r->film.cols))) return rc;
+        NB_CUDA(ctx, cudaMemsetAsync(r->film.normal, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
+    }
     NbWave &w = r->wave;
     w.pool = pool;
     if ((rc = nb_dev_alloc(ctx, r, &w.ray_o, pool)) || (rc = nb_dev_alloc(ctx, r, &w.ray_d, pool)) ||
@@ -387,6 +393,7 @@ int nb_film_clear(nb_ctx *ctx) {
     NbRenderState *r = ctx->render;
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
     NB_CUDA(ctx, cudaMemsetAsync(r->film.data, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
+    if (r->film.normal) NB_CUDA(ctx, cudaMemsetAsync(r->film.normal, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
     NB_CUDA(ctx, cudaMemsetAsync(r->stats, 0, NB_STAT_WORDS * sizeof(unsigned long long), ctx->stream));
     memset(&r->totals, 0, sizeof(r->totals));
     return NB_OK;
@@ -525,12 +532,17 @@ int nb_film_shape(nb_ctx *ctx, uint32_t *rows, uint32_t *cols, uint32_t *border)
     return NB_OK;
 }
 
-int nb_film_download(nb_ctx *ctx, float *out, int normalize) {
+int nb_film_download(nb_ctx *ctx, float *out, int normalize) { return nb_film_download_layer(ctx, NB_LAYER_COMPOSITE, out, normalize); }
+
+int nb_film_download_layer(nb_ctx *ctx, int layer, float *out, int normalize) {
     if (!ctx || !ctx->render || !out) return nb_fail(ctx, NB_E_STATE, "nb_film_download: no render in progress or NULL buffer");
     NbRenderState *r = ctx->render;
+    if (layer != NB_LAYER_COMPOSITE && layer != NB_LAYER_NORMAL) return nb_fail(ctx, NB_E_INVALID, "nb_film_download_layer: layer %d unknown", layer);
+    float4 *const film_data = layer == NB_LAYER_NORMAL ? r->film.normal : r->film.data;
+    if (!film_data) return nb_fail(ctx, NB_E_STATE, "nb_film_download_layer: layer %d was not requested in nb_render_params.layers", layer);
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
     if (!normalize) {
-        NB_CUDA(ctx, cudaMemcpyAsync(out, r->film.data, (size_t) r->film.rows * r->film.cols * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+        NB_CUDA(ctx, cudaMemcpyAsync(out, film_data, (size_t) r->film.rows * r->film.cols * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
         NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         return NB_OK;
     }
@@ -538,7 +550,7 @@ int nb_film_download(nb_ctx *ctx, float *out, int normalize) {
     const size_t n = (size_t) cam.width * cam.height;
     float *d_rgb = nullptr;
     NB_CUDA(ctx, cudaMalloc((void **) &d_rgb, n * 3 * sizeof(float)));
-    nb_k_film_finalize<<<(unsigned) ((n + 255) / 256), 256, 0, ctx->stream>>>(r->film.data, r->film.cols, r->film.border, cam.width, cam.height, d_rgb);
+    nb_k_film_finalize<<<(unsigned) ((n + 255) / 256), 256, 0, ctx->stream>>>(film_data, r->film.cols, r->film.border, cam.width, cam.height, d_rgb);
     cudaMemcpyAsync(out, d_rgb, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     cudaFree(d_rgb);

@@ -12,11 +12,11 @@ public:
     B200State(const B200State &) = delete;
     /* OptixState::preRender (OptixState.render.cpp:19-85): flatten + upload + BVH + film setup.
      * false = the scene uses a plugin without a GPU kernel (the caller renders on its CPU path). */
-    bool preRender(const Scene &scene, uint64_t seed = 0, uint32_t poolPaths = 0);
+    bool preRender(const Scene &scene, uint64_t seed = 0, uint32_t poolPaths = 0, uint32_t layers = 0);   /* layers: NB_LAYER_* bits */
     /* OptixState::renderSubframe (OptixState.cpp:485-510) */
     void renderSubframe(uint32_t currentSample, uint32_t samplesPerLaunch, uint32_t stride = 1, uint32_t offset = 0);
     /* accumulators in ImageBlock layout (rows x cols x {sum w*rgb, sum w}) or the normalised bitmap */
-    void download(std::vector<float> &out, bool normalize, uint32_t *rows = nullptr, uint32_t *cols = nullptr);
+    void download(std::vector<float> &out, bool normalize, uint32_t *rows = nullptr, uint32_t *cols = nullptr, int layer = NB_LAYER_COMPOSITE);
     void clear();                                   /* OptixState::clear */
     nb_counters counters() const;
     const FlatScene &flat() const { return m_flat; }

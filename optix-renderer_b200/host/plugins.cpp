@@ -362,6 +362,24 @@ public:
 };
 NORI_REGISTER_CLASS(Independent, "independent")
 
+/* src/samplers/adaptive.cpp:36-39: the variance feedback loop lives in the host render loop (render.cpp:323-336),
+ * which is not on the GPU path; the backend renders the scene's sampleCount uniformly */
+class AdaptiveSampler : public Sampler {
+public:
+    explicit AdaptiveSampler(const PropertyList &p) { m_sampleCount = (size_t) p.getInteger("sampleCount", 1); (void) p.getInteger("initialUniform", 2); }
+    std::string toString() const override { return NoriException::format("Adaptive[sampleCount=%d]", (int) m_sampleCount); }
+};
+NORI_REGISTER_CLASS(AdaptiveSampler, "adaptive")
+
+/* src/denoiser/simple.cpp: a CPU post-process of the finished image, outside the GPU path; accepted so its scenes load */
+class SimpleDenoiser : public NoriObject {
+public:
+    explicit SimpleDenoiser(const PropertyList &p) { (void) p.getFloat("sigma_d", 0.f); (void) p.getFloat("sigma_vr", 0.6f); (void) p.getInteger("range", 1); (void) p.getInteger("amount", 1); }
+    EClassType getClassType() const override { return EDenoiser; }
+    std::string toString() const override { return "SimpleDenoiser[]"; }
+};
+NORI_REGISTER_CLASS(SimpleDenoiser, "simple")
+
 /* the GPU side-car's own settings object (OptixRenderer, include/nori/optix/OptixRenderer.cpp:9-14) */
 class B200Renderer : public NoriObject {
 public:

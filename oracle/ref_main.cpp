@@ -154,11 +154,13 @@ static std::map<std::string, std::string> parseKv(int argc, char **argv, int fir
 }
 
 /* ---- render: renderThreadMain (render.cpp:232-360) + renderBlock (:421-459) ------------ */
-static void renderBlockRef(const Scene *scene, Integrator *integrator, Sampler *sampler, ImageBlock &block) {
+static void renderBlockRef(const Scene *scene, Integrator *integrator, Sampler *sampler, ImageBlock &block,
+                           ImageBlock *blockNormal = nullptr) {
     const Camera *camera = scene->getCamera();
     Point2i offset = block.getOffset();
     std::vector<std::pair<int, int>> sampleIndices = sampler->getSampleIndices(block);
     block.clear();
+    if (blockNormal) blockNormal->clear();
     for (size_t i = 0; i < sampleIndices.size(); i++) {
         int x = sampleIndices[i].first, y = sampleIndices[i].second;
         Point2f pixelSample = Point2f((float) (x + offset.x()), (float) (y + offset.y())) + sampler->next2D();
@@ -168,6 +170,9 @@ static void renderBlockRef(const Scene *scene, Integrator *integrator, Sampler *
         Color3f albedo = 0.f, normal = 0.f;
         value *= integrator->Li(scene, sampler, ray, albedo, normal);
         block.put(pixelSample, value);
+        if (blockNormal) {                      /* render.cpp:456-457; the albedo layer is 0 in every integrator */
+            blockNormal->put(pixelSample, normal);   /* put() rejects (and reports) every normal with a negative component */
+        }
     }
 }
 
@@ -184,6 +189,9 @@ static int modeRender(int argc, char **argv) {
 
     ImageBlock result(outputSize, camera->getReconstructionFilter());
     result.clear();
+    const bool wantNormal = kv.count("normal") != 0;
+    ImageBlock resultNormal(outputSize, camera->getReconstructionFilter());
+    resultNormal.clear();
     const int blockSize = NORI_BLOCK_SIZE;
     BlockGenerator blockGenerator(outputSize, blockSize);
     Integrator *integrator = scene->getIntegrator(false);
@@ -196,23 +204,27 @@ static int modeRender(int argc, char **argv) {
     std::vector<std::unique_ptr<Sampler>> samplers(numBlocks);
 
     std::vector<RayCounters> counters(nThreads);
+    std::streambuf *cerrBuf = wantNormal ? std::cerr.rdbuf(nullptr) : nullptr;   /* one warning per rejected normal otherwise */
     auto t0 = std::chrono::steady_clock::now();
     for (int currentSample = 0; currentSample < spp; ++currentSample) {
         scene->getSampler()->setSampleRound(currentSample);
         std::atomic<int> nextBlock(0);
         auto worker = [&](int tid) {
             ImageBlock block(Vector2i(blockSize), camera->getReconstructionFilter());
+            ImageBlock blockN(Vector2i(blockSize), camera->getReconstructionFilter());
             while (true) {
                 if (nextBlock.fetch_add(1) >= numBlocks) break;
                 blockGenerator.next(block);
+                blockN.setOffset(block.getOffset()); blockN.setSize(block.getSize());
                 uint32_t blockId = block.getBlockId();
                 if (currentSample == 0) {
                     std::unique_ptr<Sampler> sampler(scene->getSampler()->clone());
                     sampler->prepare(block);
                     samplers.at(blockId) = std::move(sampler);
                 }
-                renderBlockRef(scene, integrator, samplers.at(blockId).get(), block);
+                renderBlockRef(scene, integrator, samplers.at(blockId).get(), block, wantNormal ? &blockN : nullptr);
                 result.put(block);
+                if (wantNormal) resultNormal.put(blockN);
             }
             RayCounters &c = tlsCounters;
             counters[tid].closest += c.closest; counters[tid].any += c.any; counters[tid].dup += c.dup;
@@ -225,9 +237,14 @@ static int modeRender(int argc, char **argv) {
         blockGenerator.reset();
     }
     double seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (cerrBuf) std::cerr.rdbuf(cerrBuf);
 
     std::unique_ptr<Bitmap> bitmap(result.toBitmap());
     writeNpy(argv[3], (const float *) bitmap->data(), { (size_t) outputSize.y(), (size_t) outputSize.x(), 3 });
+    if (wantNormal) {                           /* the Normal render layer (integrator.h:29-39), as toBitmap() gives it */
+        std::unique_ptr<Bitmap> nb(resultNormal.toBitmap());
+        writeNpy(kv["normal"], (const float *) nb->data(), { (size_t) outputSize.y(), (size_t) outputSize.x(), 3 });
+    }
     if (kv.count("film"))
         writeNpy(kv["film"], (const float *) result.data(), { (size_t) result.rows(), (size_t) result.cols(), 4 });
 
@@ -765,7 +782,7 @@ static int modeBsdf(int argc, char **argv) {
 static int usage() {
     fprintf(stderr,
         "nori_ref — headless harness around the reference CPU renderer (test infrastructure)\n"
-        "  nori_ref render  scene.xml out.npy [spp=N] [threads=T] [film=raw.npy]\n"
+        "  nori_ref render  scene.xml out.npy [spp=N] [threads=T] [film=raw.npy] [normal=layer.npy]\n"
         "  nori_ref genrays scene.xml rays.bin n_primary seed\n"
         "  nori_ref hits    scene.xml rays.bin hits.bin\n"
         "  nori_ref bvh     scene.xml bvh.bin\n"

@@ -6,6 +6,7 @@ oracle/_ref/nori_ref); the GPU box only reads what this writes.
   scenes/plugins/*.xml        small scenes written here (data) over the reference's own plane / cube /
                               cone meshes and normal-map PNG, copied verbatim from scenes/project
   plug_<name>_ref_<spp>.npy   reference CPU render of each scene (`nori_ref render`)
+  plug_preview_normal_*.npy   the Normal render layer of the preview scene (`nori_ref render ... normal=`)
   bsdf_<name>_{in,out}.bin    BSDF::eval / pdf / sample records from the reference's plugins (`nori_ref bsdf`)
   emit_<name>_{in,out}.bin    Emitter::sample records for the spot and directional lights (`nori_ref emitter`)
 """
@@ -175,7 +176,8 @@ def main():
     for name, (text, spp) in SCENES.items():
         xml = os.path.join(DST, name + ".xml")
         open(xml, "w").write(text)
-        print(name, run("render", xml, os.path.join(HERE, "plug_%s_ref_%dspp.npy" % (name, spp)), "spp=%d" % spp))
+        extra = ["normal=" + os.path.join(HERE, "plug_%s_normal_%dspp.npy" % (name, spp))] if name == "preview" else []
+        print(name, run("render", xml, os.path.join(HERE, "plug_%s_ref_%dspp.npy" % (name, spp)), "spp=%d" % spp, *extra))
     rng = np.random.default_rng(77)
     n = 4096
 
