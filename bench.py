@@ -120,7 +120,32 @@ def impl_reference(args):
             "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "reference",
                              "sample": "same scene and 800x600 image, %d spp per step, sample loop only (render.cpp:281-360)" % spp},
             "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(obj), flush=True)
+
+
+def ncu_capture(path):
+    """metric -> value (bytes for the dram counters) of a tools/ncu_summary.py file, or None."""
+    if not os.path.exists(path):
+        return None
+    import csv
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    out = {}
+    for row in csv.DictReader(open(path)):
+        try:
+            out[row["metric"]] = float(row["value"]) * scale.get(row["unit"], 1.0)
+        except ValueError:
+            pass
+    return out
 
 
 def main():
@@ -135,6 +160,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--strategy", default="auto", choices=["auto", "wavefront", "tile"])
     args = ap.parse_args()
+    # rank 0 prints ONE JSON line on stdout: anything a library writes there meanwhile (NCCL prints its version on
+    # the first collective when NCCL_DEBUG is set on the box) goes to stderr instead
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return impl_reference(args)
 
@@ -231,10 +262,25 @@ def main():
             # K_tile: the step IS one launch of the dominant kernel, timed by the library's own
             # CUDA events on its launch stream during the timed steps above
             achieved = bytes_per_ray * rays / (kernel_ms * 1e-3) / 1e9
+            # the committed `ncu --set full` capture of this very launch (cbox, 512 spp, one GPU): DRAM traffic per
+            # launch, and the warp-instruction count that gives the kernel's real (instruction-issue) roofline
+            traffic, issue = None, None
+            cap = ncu_capture(os.path.join(ROOT, "profiles", "r01_ncu_tile_cbox.csv"))
+            if cap and args.spp == 512 and world == 1:
+                traffic = cap.get("dram__bytes_read.sum", 0.0) + cap.get("dram__bytes_write.sum", 0.0)
+                warp_inst = cap.get("smsp__inst_executed.sum")
+                clk_hz = (clk.summary().get("sm_mhz") or 1965.0) * 1e6
+                if warp_inst:
+                    sms = torch.cuda.get_device_properties(local).multi_processor_count
+                    floor_ms = warp_inst / (sms * 4 * clk_hz) * 1e3          # one warp instruction per scheduler per cycle
+                    issue = {"bound": "sm_issue", "warp_inst_per_launch": warp_inst, "schedulers": sms * 4, "sm_mhz": clk_hz / 1e6,
+                             "floor_ms": floor_ms, "frac": floor_ms / (kernel_ms / args.steps),
+                             "lanes_per_warp_inst": cap.get("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                             "source": "profiles/r01_ncu_tile_cbox.csv (instruction count) / live launch time"}
             roofline = {"bound": "hbm", "kernel": "nb_k_tile<path_mis>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": None, "peak_source": how, "bytes_per_ray": bytes_per_ray,
+                        "frac": achieved / peak, "traffic": traffic, "peak_source": how, "bytes_per_ray": bytes_per_ray,
                         "launches_timed": args.steps, "avg_launch_ms": kernel_ms / args.steps,
-                        "kernel_share": {"tile": kernel_ms / ms}, "note": note}
+                        "kernel_share": {"tile": kernel_ms / ms}, "issue": issue, "note": note}
         else:
             # wavefront: dominant kernel K_trace, one extra step with per-kernel event timers
             ctx.render_begin(params)
@@ -271,7 +317,7 @@ def main():
                 "e2e": {"value": float(se.item()) / float(te.item()), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": int(host_film.nbytes)},
                 "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roofline, "cpu_baseline": cpu}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

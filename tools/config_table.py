@@ -27,13 +27,30 @@ CONFIGS = [  # name, xml, gpu spp, cpu spp
     ("C4 heterog fluid path_vol_mis 800x600", os.path.join(G, "vol", "cbox_heterog_fluid_mis.xml"), 128, 8),
     ("envmap_sphere path_mis 800x800 (1500x750 PNG environment)", os.path.join(G, "envmap", "envmap_sphere.xml"), 128, 16),
 ]
+P = os.path.join(G, "plugins")
+CONFIGS += [  # the 8(f) rows at a measurable size (their fixtures are 160x120): same XML with the camera enlarged
+    ("disney + spot + directional path_mis 800x600", os.path.join(P, "disney_spot_dir_path_mis.xml"), 128, 16, (800, 600)),
+    ("normal maps direct_mis 800x600", os.path.join(P, "normalmap_direct_mis.xml"), 128, 32, (800, 600)),
+    ("volume lights path_vol_mis 800x600", os.path.join(P, "volumelight_mis.xml"), 64, 8, (800, 600)),
+]
 if "only" in opt:
     CONFIGS = [c for c in CONFIGS if opt["only"] in c[0]]
 c3 = os.path.join(ROOT, "c3cache", "c3_path_mis.xml")
 if os.path.exists(c3):
     CONFIGS.append(("C3 synthetic 1310720 tris path_mis 800x600", c3, 32, 4))
+c5 = os.path.join(ROOT, "c5cache", "c5_path_mis.xml")
+if os.path.exists(c5):
+    CONFIGS.append(("C5-class 64 x camelhead 1453066 tris path_mis 1920x1080 (one GPU)", c5, 16, 2))
 ctx = nb.Context(0)
-for name, xml, gspp, cspp in CONFIGS:
+for cfg in CONFIGS:
+    name, xml, gspp, cspp = cfg[:4]
+    if len(cfg) > 4:                     # enlarged copy next to the original (relative mesh paths keep working)
+        import re
+        text = open(xml).read()
+        text = re.sub(r'(name="width"\s+value=")\d+', r"\g<1>%d" % cfg[4][0], text)
+        text = re.sub(r'(name="height"\s+value=")\d+', r"\g<1>%d" % cfg[4][1], text)
+        xml = xml[:-4] + "_cfgtable.xml"
+        open(xml, "w").write(text)
     t0 = time.perf_counter()
     s = nb.load_xml(xml)
     host_s = time.perf_counter() - t0
@@ -56,3 +73,5 @@ for name, xml, gspp, cspp in CONFIGS:
                         "cpu_rays_raw_per_s": j["rays_raw_per_s"], "cpu_rays_dedup_per_s": j["rays_dedup_per_s"],
                         "cpu_load_bvh_s": j["load_seconds"], "speedup_samples": row["gpu_samples_per_s"] / j["samples_per_s"]})
     print(json.dumps(row), flush=True)
+    if len(cfg) > 4:
+        os.remove(xml)
