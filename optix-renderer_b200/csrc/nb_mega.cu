@@ -268,9 +268,8 @@ __device__ __forceinline__ f3 nb_direct_sample(const NbDeviceScene &sc, const Nb
  * reference passes `its` in both cases); exactly one of bsdf / phase is non-null. */
 template <bool FLAT, bool EXT>
 __device__ __forceinline__ f3 nb_vol_sample_emitter(const NbDeviceScene &sc, NbPathRegs &ps, int32_t medium, const NbIts &its,
-                                                    const nb_shape &sh, uint32_t measure, const nb_bsdf *bsdf,
+                                                    const nb_shape &sh, const nb_bsdf *bsdf,
                                                     const nb_medium *phase, uint32_t &n_closest) {
-    if (measure != NB_MEASURE_SOLID_ANGLE) return mk3(0.f);              /* skip delta bsdfs */
     const float n_lights = (float) sc.n_emitters;
     const uint32_t ei = nb_cdf_sample(sc.emitter_cdf, sc.n_emitters, ps.rng.next_float());
     float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
@@ -351,37 +350,41 @@ __device__ __forceinline__ bool nb_vol_bounce(const NbDeviceScene &sc, uint32_t 
     }
     if (max_depth && bounce >= max_depth) return false;
     f3 wo = ps.d;                                                        /* default: unperturbed */
+    /* the two kinds of interaction meet again at ONE emitter-sampling site: lanes at a medium interaction and lanes
+     * at a surface walk their shadow rays together, and the kernel holds one copy of that code instead of two */
+    nb_medium med; nb_bsdf bsdf;
+    f3 col = mk3(1.f);
+    bool nee = false;
     if (mi) {
-        const nb_medium med = sc.media[medium];
+        med = sc.media[medium];
         float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
         const f3 pwo = nb_phase_sample(med, s);
         wo = frame_from_normal(ps.d).to_world(pwo);
         if (MIS) {
             ps.pdfmat = nb_phase_pdf(med, pwo);
             measure = NB_MEASURE_SOLID_ANGLE;
-            ps.Li += nb_vol_sample_emitter<FLAT, EXT>(sc, ps, medium, its, sh, measure, nullptr, &med, n_closest);
+            nee = true;
         }
-    } else {
-        if (sh.bsdf >= 0) {
-            nb_bsdf bsdf = sc.bsdfs[sh.bsdf];
-            nb_bsdf_resolve<EXT>(sc, bsdf, its.uv);
-            const f3 wi = its.sh.to_local(-ps.d);
-            float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
-            f3 lwo; bool discrete; float pdf;
-            const f3 col = nb_bsdf_sample<EXT>(bsdf, wi, s, lwo, discrete, pdf, sc.params);
-            wo = its.sh.to_world(lwo);
-            if (MIS) {
-                /* bRec.measure after sample(): diffuse sets ESolidAngle and mirror EDiscrete only when
-                 * wi is on the upper side, dielectric always EDiscrete, microfacet never sets it */
-                measure = discrete ? NB_MEASURE_DISCRETE
-                        : ((bsdf.type == NB_BSDF_DIFFUSE || bsdf.type == NB_BSDF_DISNEY) && wi.z > 0.f) ? NB_MEASURE_SOLID_ANGLE : NB_MEASURE_UNKNOWN;
-                ps.pdfmat = pdf;
-                ps.Li += nb_vol_sample_emitter<FLAT, EXT>(sc, ps, medium, its, sh, measure, &bsdf, nullptr, n_closest);
-            }
-            ps.thr = ps.thr * col;
+    } else if (sh.bsdf >= 0) {
+        bsdf = sc.bsdfs[sh.bsdf];
+        nb_bsdf_resolve<EXT>(sc, bsdf, its.uv);
+        const f3 wi = its.sh.to_local(-ps.d);
+        float2 s; s.x = ps.rng.next_float(); s.y = ps.rng.next_float();
+        f3 lwo; bool discrete; float pdf;
+        col = nb_bsdf_sample<EXT>(bsdf, wi, s, lwo, discrete, pdf, sc.params);
+        wo = its.sh.to_world(lwo);
+        if (MIS) {
+            /* bRec.measure after sample(): diffuse sets ESolidAngle and mirror EDiscrete only when
+             * wi is on the upper side, dielectric always EDiscrete, microfacet never sets it */
+            measure = discrete ? NB_MEASURE_DISCRETE
+                    : ((bsdf.type == NB_BSDF_DIFFUSE || bsdf.type == NB_BSDF_DISNEY) && wi.z > 0.f) ? NB_MEASURE_SOLID_ANGLE : NB_MEASURE_UNKNOWN;
+            ps.pdfmat = pdf;
+            nee = measure == NB_MEASURE_SOLID_ANGLE;                     /* skip delta bsdfs */
         }
-        if (dot(ps.d, wo) > 0.f) medium = nb_medium_behind(sc, sh, its.geo_n, wo);   /* transmitted: entering or leaving */
     }
+    if (MIS && nee) ps.Li += nb_vol_sample_emitter<FLAT, EXT>(sc, ps, medium, its, sh, mi ? nullptr : &bsdf, mi ? &med : nullptr, n_closest);
+    ps.thr = ps.thr * col;
+    if (!mi && dot(ps.d, wo) > 0.f) medium = nb_medium_behind(sc, sh, its.geo_n, wo);   /* transmitted: entering or leaving */
     ps.o = p; ps.d = wo; ps.mint = NB_EPS; ps.maxt = INFINITY;
     ps.flags = ((bounce + 1) << NB_BOUNCE_SHIFT) | (measure << NB_MEASURE_SHIFT);
     return !is_black(ps.thr);
