@@ -27,6 +27,15 @@
 #ifndef NB_TILE_MIN_BLOCKS
 #define NB_TILE_MIN_BLOCKS 6
 #endif
+/* CTAs per SM asked of the EXT variants (launch bounds): the kernels that carry the texture / disney / spot /
+ * environment / heterogeneous code are 1.5-2x larger and wait on instruction fetch (see nb_k_tile), so they trade
+ * registers for resident warps; the kernels without that code are best at 6 (80 registers) */
+#ifndef NB_TILE_MIN_BLOCKS_EXT
+#define NB_TILE_MIN_BLOCKS_EXT 8
+#endif
+#ifndef NB_WALK_MIN_BLOCKS_EXT
+#define NB_WALK_MIN_BLOCKS_EXT 8
+#endif
 
 struct NbTilePlan {
     NbPlan plan;
@@ -438,15 +447,22 @@ __device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan
 }
 
 /* ---- K_tile ---------------------------------------------------------------------------------- */
-/* the volume integrators with heterogeneous media carry the 27-tap stencil and two tracking loops;
- * measured on the fluid scene (B200): 6 CTAs/SM at 80 registers with spills beat 4 CTAs/SM at 128
- * registers (699 vs 675 M samples/s path_vol_mats, 146 vs 130 path_vol_mis) */
-#ifndef NB_TILE_MIN_BLOCKS_HETEROG
-#define NB_TILE_MIN_BLOCKS_HETEROG NB_TILE_MIN_BLOCKS
+/* Occupancy of the EXT variants, measured (B200, M samples/s at 6 / 8 CTAs per SM): normal-map direct_mis 3146 / 3444,
+ * disney direct_mis 1728 / 1977, environment-map path_mis 11.42 / 11.36 G. path_vol_mis with the EXT code
+ * (heterogeneous media, volume lights, textures) is the largest kernel (119 KB) and waits on instruction fetch more
+ * than on anything else (ncu: 11 `stall_no_instruction` per issue at 6 CTAs/SM), so resident warps pay even at
+ * the price of spills: fluid scene / volume-light scene at 6 CTAs/SM (80 regs) 203 / 810, 8 (64) 220 / 875,
+ * 10 (48) 236 / 936, 12 (40) 249 / 975, 16 (32) 257 / 1007. path_vol_mats with EXT loses 3-5 % beyond 6 on the
+ * fluid scene, and the kernels without EXT lose 2-4 % at 8. At 10 CTAs/SM direct_mis gains another 11-12 % (normal maps
+ * 3880, disney 2198) while path_mis / path_mats / preview lose 2-15 % (flat and walk kernels alike), at 12 all lose. */
+#ifndef NB_TILE_MIN_BLOCKS_VOL_MIS_EXT
+#define NB_TILE_MIN_BLOCKS_VOL_MIS_EXT 16
 #endif
 template <int INTEG, bool FLAT, bool EXT>
-__global__ void __launch_bounds__(NB_TILE_THREADS, (EXT && (INTEG == NB_INTEGRATOR_PATH_VOL_MIS || INTEG == NB_INTEGRATOR_PATH_VOL_MATS))
-                                                       ? NB_TILE_MIN_BLOCKS_HETEROG : NB_TILE_MIN_BLOCKS)
+__global__ void __launch_bounds__(NB_TILE_THREADS, !EXT ? NB_TILE_MIN_BLOCKS
+                                                   : INTEG == NB_INTEGRATOR_PATH_VOL_MIS ? NB_TILE_MIN_BLOCKS_VOL_MIS_EXT
+                                                   : INTEG == NB_INTEGRATOR_PATH_VOL_MATS ? NB_TILE_MIN_BLOCKS
+                                                   : INTEG == NB_INTEGRATOR_DIRECT_MIS ? NB_TILE_MIN_BLOCKS_EXT + 2 : NB_TILE_MIN_BLOCKS_EXT)
 nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     constexpr bool PATH = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_MATS;
     constexpr bool VOL = INTEG == NB_INTEGRATOR_PATH_VOL_MIS || INTEG == NB_INTEGRATOR_PATH_VOL_MATS;
@@ -568,7 +584,7 @@ enum { NB_W_LI = 0, NB_W_THR = 3, NB_W_O = 6, NB_W_D = 9, NB_W_MINT = 12, NB_W_M
        NB_W_PDFMAT = 16, NB_W_PX = 17, NB_W_PY = 18, NB_W_FLAGS = 19, NB_W_RNG = 20, NB_W_SC = 24, NB_W_CAND = 27, NB_W_WORDS = 28 };
 
 template <bool MIS, bool EXT>
-__global__ void __launch_bounds__(NB_TILE_THREADS, NB_WALK_MIN_BLOCKS)
+__global__ void __launch_bounds__(NB_TILE_THREADS, EXT ? NB_WALK_MIN_BLOCKS_EXT : NB_WALK_MIN_BLOCKS)
 nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     __shared__ float park[NB_W_WORDS][NB_TILE_THREADS];
     const uint32_t tid = threadIdx.x;
