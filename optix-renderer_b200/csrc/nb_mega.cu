@@ -25,7 +25,8 @@
 #define NB_TILE_THREADS 128
 #endif
 #ifndef NB_TILE_MIN_BLOCKS
-#define NB_TILE_MIN_BLOCKS 6
+#define NB_TILE_MIN_BLOCKS 7      /* 72 registers. B200, 6 / 7 / 8 CTAs per SM, M samples/s: cbox path_mis 1961 / 1988 / 2032, path_mats 3058 / 3199 / 3137,
+                                   * cbox_val_mis 1018 / 1004 / 978, cbox_homog_aniso 2920 / 3052 / 2915, veach direct_mis 1449 / 1489 / 1445 */
 #endif
 /* CTAs per SM asked of the EXT variants (launch bounds): the kernels that carry the texture / disney / spot /
  * environment / heterogeneous code are 1.5-2x larger and wait on instruction fetch (see nb_k_tile), so they trade
@@ -461,7 +462,7 @@ __device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan
 template <int INTEG, bool FLAT, bool EXT>
 __global__ void __launch_bounds__(NB_TILE_THREADS, !EXT ? NB_TILE_MIN_BLOCKS
                                                    : INTEG == NB_INTEGRATOR_PATH_VOL_MIS ? NB_TILE_MIN_BLOCKS_VOL_MIS_EXT
-                                                   : INTEG == NB_INTEGRATOR_PATH_VOL_MATS ? NB_TILE_MIN_BLOCKS
+                                                   : INTEG == NB_INTEGRATOR_PATH_VOL_MATS ? 6
                                                    : INTEG == NB_INTEGRATOR_DIRECT_MIS ? NB_TILE_MIN_BLOCKS_EXT + 2 : NB_TILE_MIN_BLOCKS_EXT)
 nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     constexpr bool PATH = INTEG == NB_INTEGRATOR_PATH_MIS || INTEG == NB_INTEGRATOR_PATH_MATS;
@@ -560,7 +561,8 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
  * while its neighbours shade, start new paths and walk their own rays. Per ray the visiting order
  * and arithmetic are nb_traverse's; per path the draws are nb_path_bounce's. */
 #ifndef NB_WALK_MIN_BLOCKS
-#define NB_WALK_MIN_BLOCKS 6      /* 80 registers: the path state is parked in shared memory during the walk (B200, table: 353 vs 332 M samples/s at 4) */
+#define NB_WALK_MIN_BLOCKS 7      /* 72 registers: the path state is parked in shared memory during the walk. B200, M samples/s at 4 / 6 / 7 / 8 CTAs per SM:
+                                   * table 332 / 355 / 369 / 356, C3 (1.31 M triangles) - / 444 / 479 / 477 (three interleaved runs each) */
 #endif
 #ifndef NB_WALK_NODE_STEPS
 #define NB_WALK_NODE_STEPS 8      /* node steps per loop iteration */
