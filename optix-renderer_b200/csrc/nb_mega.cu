@@ -571,7 +571,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
 #define NB_WALK_T_LEAF 6          /* lanes that must wait before a phase is run (unless nothing else can) */
 #endif
 #ifndef NB_WALK_T_SHADE
-#define NB_WALK_T_SHADE 8
+#define NB_WALK_T_SHADE 16        /* B200 at 7 CTAs/SM, M samples/s at 8 / 12 / 16 / 20: table 365 / 386 / 402 / 404, C3 479 / 492 / 493 / 466 */
 #endif
 #ifndef NB_WALK_T_REGEN
 #define NB_WALK_T_REGEN 8

@@ -6,5 +6,5 @@ echo "C3 $(timeout 200 python tools/render_xml.py /tmp/c3p/c3_path_mis.xml spp=3
 echo "C5 $(timeout 300 python tools/render_xml.py /tmp/c5p/c5_path_mis.xml spp=8 repeat=3 normalize=0 | tail -1 | cut -c1-170)"
 echo "table $(timeout 200 python tools/render_xml.py tests/golden/scenes/table/table_path_mis.xml spp=64 repeat=3 normalize=0 | tail -1 | cut -c1-170)"
 timeout 200 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -1
-timeout 300 python bench.py 2> gpurun_out/bench_final.err | tail -1 > gpurun_out/bench_final.json
-cut -c1-300 gpurun_out/bench_final.json
+
+
