@@ -30,7 +30,7 @@
 #endif
 /* CTAs per SM asked of the EXT variants (launch bounds): the kernels that carry the texture / disney / spot /
  * environment / heterogeneous code are 1.5-2x larger and wait on instruction fetch (see nb_k_tile), so they trade
- * registers for resident warps; the kernels without that code are best at 6 (80 registers) */
+ * registers for resident warps; the kernels without that code are best at 7 (72 registers) */
 #ifndef NB_TILE_MIN_BLOCKS_EXT
 #define NB_TILE_MIN_BLOCKS_EXT 8
 #endif
