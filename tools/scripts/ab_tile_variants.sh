@@ -1,4 +1,4 @@
-# tuning builds (tools_build_variants.sh) against the default library: walk-kernel phase thresholds at 7 CTAs per SM
+# tuning builds (tools/scripts/build_variants.sh) against the default library: walk-kernel phase thresholds at 7 CTAs per SM
 python tools/make_c3_scene.py /tmp/c3p > /dev/null 2>&1
 run() { echo "== $1 $2 $(timeout 120 python tools/render_xml.py $2 spp=$3 repeat=4 normalize=0 2>&1 | tail -1 | grep -o "'samples_per_s': [0-9.]*")"; }
 for rep in 1 2; do

@@ -1,6 +1,6 @@
 #!/bin/bash
 # tuning builds of libnorib200.so with different K_tile_walk parameters -> optix-renderer_b200/variants/
-# usage: tools_build_variants.sh [file with "name flags" lines]  (default: the min-blocks sweep)
+# usage: bash tools/scripts/build_variants.sh [file with "name flags" lines]  (default: the min-blocks sweep)
 set -e
 cd /root/repo/optix-renderer_b200/csrc
 mkdir -p ../variants
