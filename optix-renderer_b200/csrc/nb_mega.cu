@@ -460,7 +460,8 @@ __device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan
 #define NB_TILE_MIN_BLOCKS_VOL_MIS_EXT 16
 #endif
 template <int INTEG, bool FLAT, bool EXT>
-__global__ void __launch_bounds__(NB_TILE_THREADS, !EXT ? NB_TILE_MIN_BLOCKS
+__global__ void __launch_bounds__(NB_TILE_THREADS, !EXT ? (INTEG == NB_INTEGRATOR_PATH_MIS ? NB_TILE_MIN_BLOCKS + 1           /* see NB_TILE_MIN_BLOCKS: 8 for path_mis, */
+                                                          : INTEG == NB_INTEGRATOR_PATH_VOL_MIS ? NB_TILE_MIN_BLOCKS - 1 : NB_TILE_MIN_BLOCKS)   /* 6 for path_vol_mis */
                                                    : INTEG == NB_INTEGRATOR_PATH_VOL_MIS ? NB_TILE_MIN_BLOCKS_VOL_MIS_EXT
                                                    : INTEG == NB_INTEGRATOR_PATH_VOL_MATS ? 6
                                                    : INTEG == NB_INTEGRATOR_DIRECT_MIS ? NB_TILE_MIN_BLOCKS_EXT + 2 : NB_TILE_MIN_BLOCKS_EXT)
