@@ -26,7 +26,8 @@
 #endif
 #ifndef NB_TILE_MIN_BLOCKS
 #define NB_TILE_MIN_BLOCKS 7      /* 72 registers. B200, 6 / 7 / 8 CTAs per SM, M samples/s: cbox path_mis 1961 / 1988 / 2032, path_mats 3058 / 3199 / 3137,
-                                   * cbox_val_mis 1018 / 1004 / 978, cbox_homog_aniso 2920 / 3052 / 2915, veach direct_mis 1449 / 1489 / 1445 */
+                                   * cbox_val_mis 1018 / 1004 / 978, cbox_homog_aniso 2920 / 3052 / 2915, veach direct_mis 1449 / 1489 / 1445;
+                                   * cbox path_mis at 8 / 9 / 10 / 12: 2027 / 2026 / 1904 / 1875 */
 #endif
 /* CTAs per SM asked of the EXT variants (launch bounds): the kernels that carry the texture / disney / spot /
  * environment / heterogeneous code are 1.5-2x larger and wait on instruction fetch (see nb_k_tile), so they trade
