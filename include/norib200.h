@@ -266,6 +266,16 @@ int  nb_trace_rays(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_hit, nb_
  * n float4 {t,u,v,bits(prim slot)}; returns the kernel's CUDA-event time. */
 int  nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int any_hit,
                           void *out_device, int repeats, float *ms_per_launch);
+/* nb_trace_rays for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). It has no counterpart in the reference.
+ * Same arguments, same results bit for bit as nb_trace_rays, but it calls no cudaMalloc / cudaFree / allocating
+ * library routine and no host heap: the device staging is a fixed file-scope __device__ array inside the library
+ * (3.5 MiB, held by every GPU that loads the library until exit), so n is limited to NB_TRACE_STATIC_MAX_RAYS —
+ * a larger n fails with NB_E_INVALID and a message saying so. All calls on one GPU share that array (it keeps the
+ * last call's contents; nothing in it needs clearing): calls that overlap on the same GPU race and must be
+ * serialised by the caller. Synchronous: `out` is complete on return. */
+#define NB_TRACE_STATIC_MAX_RAYS 65536u
+int  nb_trace_rays_static(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_hit, nb_hit *out);
 /* Parity entry for the medium rows: Medium::sampleFreePath (src/media/homogmedium.cpp:60-66,
  * heterogmedium.cpp:105-130), Medium::getTransmittance (homogmedium.cpp:68-72, heterogmedium.cpp:132-174)
  * and NvdbVolume::getDensity (src/textures/NvdbVolume.cpp:39-48) of media[medium] on n host rays.

@@ -25,6 +25,7 @@ INTEGRATORS = {"path_mis": 0, "path_mats": 1, "direct_ems": 2, "direct_mats": 3,
 MEDIUM_VACUUM, MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_HENYEY_GREENSTEIN, PHASE_SCHLICK = 0, 1, 2
 FILTER_RESOLUTION = 32
+TRACE_STATIC_MAX_RAYS = 65536
 
 # numpy mirrors of the records (field order and padding as in the header)
 shape_dtype = np.dtype([("type", "<u4"), ("prim_count", "<u4"), ("vertex_offset", "<u4"), ("vertex_count", "<u4"),
@@ -91,7 +92,7 @@ EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_las
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
            "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe",
-           "nb_bsdf_probe", "nb_film_download_layer"]
+           "nb_bsdf_probe", "nb_film_download_layer", "nb_trace_rays_static"]
 
 _lib = None
 
@@ -119,6 +120,7 @@ def load_library(path=None):
     lib.nb_upload_scene.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
     lib.nb_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(BvhImport)]
     lib.nb_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
+    lib.nb_trace_rays_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
     lib.nb_trace_rays_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_float)]
     lib.nb_render_begin.argtypes = [C.c_void_p, C.c_void_p]
     lib.nb_render_subframe.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
@@ -289,6 +291,15 @@ class Context:
         n = rays.size * rays.dtype.itemsize // 32
         out = np.zeros(n, dtype=hit_dtype)
         self._check(self.lib.nb_trace_rays(self.handle, _ptr(rays), n, int(any_hit), _ptr(out)))
+        return out
+
+    def trace_rays_static(self, rays, any_hit=False):
+        """nb_trace_rays_static: the same query through the library's fixed device scratch (no allocation,
+        at most TRACE_STATIC_MAX_RAYS rays per call)."""
+        rays = np.ascontiguousarray(rays)
+        n = rays.size * rays.dtype.itemsize // 32
+        out = np.zeros(n, dtype=hit_dtype)
+        self._check(self.lib.nb_trace_rays_static(self.handle, _ptr(rays), n, int(any_hit), _ptr(out)))
         return out
 
     def trace_rays_device(self, rays_ptr, n, out_ptr, any_hit=False, repeats=1):

@@ -29,7 +29,7 @@ NVCC_FLAGS = (["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-
 # the render kernels' shading math is judged statistically (t-tests, image RMSE): approximate
 # division / square root there; nb_trace.cuh asks for IEEE operations explicitly where hits depend on them
 FAST = ["-prec-div=false", "-prec-sqrt=false"]
-PER_FILE = {"nb_trace.cu": ["-fmad=false"], "nb_mega.cu": FAST, "nb_render.cu": FAST}
+PER_FILE = {"nb_trace.cu": ["-fmad=false"], "nb_static.cu": ["-fmad=false"], "nb_mega.cu": FAST, "nb_render.cu": FAST}
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-ffp-contract=off", "-pthread"]
 
 
