@@ -1,21 +1,27 @@
 #!/usr/bin/env python
 """bench.py — headline benchmark: samples/s and rays/s on the Cornell box, path_mis.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--spp S]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--spp S] [--scaling strong|weak]
 
 Workload (BASELINE.json configs[0], the scene the north-star target is quoted on):
 tests/golden/scenes/cbox/cbox_path_mis.xml, 800x600, 512 spp, gaussian r=2 — one "step" is one
-full render of it. N>1 (torchrun, one rank per GPU): every rank renders its own sample slice
-(sample s = rank + N*k, 512 spp each: weak scaling), scene replicated, film accumulators summed
-on rank 0 with one NCCL reduce inside the timed region.
+full render of it. N>1 (torchrun, one rank per GPU): STRONG scaling by default — the one 512-spp render is split
+into sample slices (rank g renders the samples s with s % N == g of every pixel, 512/N spp each), scene replicated,
+the per-rank film accumulators summed onto rank 0 by ONE NCCL reduce issued by the library itself (nb_film_reduce)
+inside the timed region. `--scaling weak` gives every rank its own 512 spp instead (round 1's curve).
 
-`value`   camera samples/s, scene already resident in HBM, device-timed (CUDA events), max over ranks.
-`e2e`     the same through the C ABI with HOST buffers: scene upload + BVH import (H2D), render,
-          film download (D2H) every step, wall-clocked around the calls.
+`value`   camera samples/s with the scene already resident in HBM: film clear + render + film reduce, timed with CUDA
+          events recorded on the library's own stream (nb_timer_mark), max over ranks.
+`e2e`     the same through the C ABI with HOST buffers every step: scene + BVH upload from pinned host memory (H2D),
+          render, reduce, ImageBlock::toBitmap on the device (nb_k_film_finalize) and the download of the finished
+          image into pinned host memory (D2H) on rank 0, wall-clocked around the calls, max over ranks.
+`roofline` the dominant kernel against the roofline that binds it: SM instruction issue (the 14-primitive scene is
+          L1-resident; SURVEY 8d names issue as C1's roof). `configs` (N=1 only): the BVH kernels on C2 table and C3.
 `--impl reference` times the reference's own CPU renderer (oracle/_ref/nori_ref, all host
 threads) on a bounded sample of the same workload (same scene and image size, fewer spp).
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -32,13 +38,14 @@ SCENE_XML = os.path.join(GOLDEN, "scenes", "cbox", "cbox_path_mis.xml")
 SCENE_NBS = os.path.join(GOLDEN, "cbox.nbs")
 NORI_REF = os.path.join(ROOT, "oracle", "_ref", "nori_ref")
 WORKLOAD = "cbox_path_mis 800x600 512spp (scenes/pa4/cbox/cbox_path_mis.xml)"
+NCU_CAPTURE = os.path.join(ROOT, "profiles", "r02_ncu_tile_cbox.csv")       # ncu --set full of this very launch + .meta.json
 
 
-def run_reference(spp, threads=None):
+def run_reference(spp, threads=None, xml=SCENE_XML):
     """One bounded run of the reference CPU renderer; returns its JSON line."""
     if not os.path.exists(NORI_REF):
         raise FileNotFoundError("oracle/_ref/nori_ref is missing: run `make -C oracle ref` where /root/reference is mounted")
-    args = [NORI_REF, "render", SCENE_XML, "/tmp/nb_bench_ref.npy", "spp=%d" % spp]
+    args = [NORI_REF, "render", xml, "/tmp/nb_bench_ref.npy", "spp=%d" % spp]
     if threads:
         args.append("threads=%d" % threads)
     r = subprocess.run(args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
@@ -95,6 +102,17 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def kernel_source_sha():
+    """Fingerprint of what the kernels are built from: an ncu capture only describes the binary it was taken on."""
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "optix-renderer_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".h")):
+            h.update(f.encode()); h.update(open(os.path.join(d, f), "rb").read())
+    h.update(open(os.path.join(ROOT, "optix-renderer_b200", "build.py"), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def impl_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -114,8 +132,9 @@ def impl_reference(args):
     v = samples / secs
     line = {"impl": "reference", "metric": "samples_per_s", "value": v, "unit": "samples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": "%d spp per step instead of 512 (throughput is spp-independent)" % spp},
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": "%d spp per step instead of 512 (throughput is spp-independent: "
+                                                       "BASELINE.md has the full 512-spp run next to the 16-spp one)" % spp},
             "rays_per_s": rays / secs, "wall_s": wall,
             "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cores, "kind": "reference",
                              "sample": "same scene and 800x600 image, %d spp per step, sample loop only (render.cpp:281-360)" % spp},
@@ -148,6 +167,60 @@ def ncu_capture(path):
     return out
 
 
+def pinned(shape, dtype=np.float32):
+    """numpy view of page-locked host memory (the e2e legs copy from / to pinned buffers)."""
+    import torch
+    t = torch.empty(int(np.prod(shape)) * np.dtype(dtype).itemsize, dtype=torch.uint8, pin_memory=True)
+    a = t.numpy().view(dtype).reshape(shape)
+    a.flags.writeable = True
+    return a, t
+
+
+def pin_scene(scene):
+    keep, out = [], {}
+    for k, v in scene.items():
+        v = np.ascontiguousarray(v)
+        if v.size == 0:
+            out[k] = v
+            continue
+        a, t = pinned(v.shape, v.dtype)
+        a[...] = v
+        out[k] = a; keep.append(t)
+    return out, keep
+
+
+def tree_config(nb, ctx, name, xml, spp, sms, clk_mhz, cap_csv):
+    """One BVH-walking configuration, driver-timed: samples/s, rays/s and (from the committed ncu capture of the same
+    kernel, when its source fingerprint matches) the lane-issue fraction."""
+    t0 = time.perf_counter()
+    s = nb.load_xml(xml)
+    host_s = time.perf_counter() - t0
+    ctx.load(s)
+    ctx.render_begin(nb.make_render_params(s, seed=1))
+    best = None
+    for _ in range(3):
+        ctx.film_clear()
+        ctx.render_subframe(0, spp)
+        c = ctx.counters()
+        if best is None or c["device_ms"] < best["device_ms"]:
+            best = c
+    rays = best["rays_closest"] + best["rays_any"]
+    row = {"config": name, "triangles": int(s["faces"].size // 3), "spp": spp, "ms": best["device_ms"],
+           "samples_per_s": best["samples"] / best["device_ms"] * 1e3, "rays_per_s": rays / best["device_ms"] * 1e3,
+           "host_load_flatten_bvh_s": round(host_s, 2)}
+    cap = ncu_capture(cap_csv)
+    meta = cap_csv[:-4] + ".meta.json"
+    if cap and os.path.exists(meta):
+        m = json.load(open(meta))
+        per_sample = cap.get("smsp__thread_inst_executed.sum", 0.0) / max(1.0, m.get("samples", 0.0))
+        lanes = sms * 128 * clk_mhz * 1e6
+        row["lane_issue_frac"] = per_sample * row["samples_per_s"] / lanes if per_sample else None
+        row["lanes_per_warp_inst"] = cap.get("smsp__thread_inst_executed_per_inst_executed.ratio")
+        row["capture"] = os.path.relpath(cap_csv, ROOT)
+        row["capture_matches_build"] = m.get("src_sha") == kernel_source_sha()
+    return row
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -157,7 +230,9 @@ def main():
     ap.add_argument("--spp", type=int, default=512)
     ap.add_argument("--ref-spp", type=int, default=16)
     ap.add_argument("--pool", type=int, default=0)
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true")
     ap.add_argument("--strategy", default="auto", choices=["auto", "wavefront", "tile"])
     args = ap.parse_args()
     # rank 0 prints ONE JSON line on stdout: anything a library writes there meanwhile (NCCL prints its version on
@@ -180,42 +255,46 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if args.scaling == "strong" and args.spp % world:
+        raise SystemExit("bench.py: --spp %d does not split over %d ranks" % (args.spp, world))
+    spp_total = args.spp if args.scaling == "strong" else args.spp * world      # samples of one step, all ranks together
     scene = nb.read_nbs(SCENE_NBS)
     params = nb.make_render_params(scene, "path_mis", seed=1, pool_paths=args.pool)
     ctx = nb.Context(local)
     ctx.set_option("strategy", {"auto": 0, "wavefront": 1, "tile": 2}[args.strategy])
+    if world > 1:
+        nb.comm_init_torch(ctx)             # the library's own NCCL communicator; torch only carries the 128-byte id
     ctx.load(scene)
     ctx.render_begin(params)
-    film = nb.film_tensor(ctx, local)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+        ctx.sync()
 
     def step():
+        """film clear -> this rank's sample slice -> one NCCL sum onto rank 0; all queued on the library's stream"""
         ctx.film_clear()
-        ctx.render_subframe(0, args.spp * world, world, rank)
-        nb.reduce_film(film, dst=0)
+        ctx.render_subframe(0, spp_total, world, rank)
+        ctx.film_reduce()
 
     for _ in range(args.warmup):
         step()
-    torch.cuda.synchronize()
-    dev_ms, c0 = 0.0, None
+    ctx.sync()
+    dev_ms = 0.0
     launches = samples = rays = 0
     kernel_ms = 0.0
     barrier()
     with ClockSampler(local) as clk:
         for _ in range(args.steps):
             flush.zero_()
-            torch.cuda.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
+            barrier()                       # every rank starts the step together: the reduce then waits for the slowest
+            ctx.timer_mark(0)
             step()
-            e1.record()
-            e1.synchronize()
-            dev_ms += e0.elapsed_time(e1)
+            ctx.timer_mark(1)
+            dev_ms += ctx.timer_elapsed()
             c = ctx.counters()
             launches += c["kernel_launches"] + (1 if world > 1 else 0)
             kernel_ms += c["device_ms"]
@@ -229,73 +308,76 @@ def main():
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     ms = float(t.item()); samples_all, rays_all = float(tot[0]), float(tot[1])
 
-    # ---- e2e: host buffers in, host film out, every step
-    h2d = sum(int(scene[k].nbytes) for k in scene if k not in ("render", "spp"))
-    rows, cols, _ = ctx.film_shape()
-    host_film = np.empty((rows, cols, 4), dtype=np.float32)
+    # ---- e2e: pinned host buffers in, finished image in pinned host memory out, every step
+    host_scene, _keep = pin_scene(scene)
+    h2d = sum(int(host_scene[k].nbytes) for k in host_scene if k not in ("render", "spp"))
+    cam = scene["camera"][0] if scene["camera"].shape else scene["camera"]
+    host_img, _keep2 = pinned((int(cam["height"]), int(cam["width"]), 3))
+    d2h = int(host_img.nbytes)
+
+    def e2e_step():
+        ctx.load(host_scene)                         # H2D: scene arrays + BVH, through the C ABI
+        ctx.render_begin(params)
+        ctx.render_subframe(0, spp_total, world, rank)
+        ctx.film_reduce()
+        if rank == 0:
+            ctx.film_download(normalize=True, out=host_img)   # ImageBlock::toBitmap on the device + D2H
+        else:
+            ctx.sync()
+        return ctx.counters()["samples"]
+
+    e2e_step()
     barrier()
     t0 = time.perf_counter()
     e2e_samples = 0
     for _ in range(args.steps):
-        ctx.load(scene)                              # H2D: scene arrays + BVH, through the C ABI
-        ctx.render_begin(params)
-        ctx.render_subframe(0, args.spp * world, world, rank)
-        nb.reduce_film(nb.film_tensor(ctx, local), dst=0)
-        ctx.film_download(normalize=False, out=host_film)   # D2H
-        e2e_samples += ctx.counters()["samples"]
+        e2e_samples += e2e_step()
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     se = torch.tensor([float(e2e_samples)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX); dist.all_reduce(se, op=dist.ReduceOp.SUM)
+    assert np.isfinite(host_img).all() or rank != 0
 
     if rank == 0:
         stats = json.load(open(os.path.join(GOLDEN, "cbox_raystats.json")))
-        # algorithmic bytes per ray: 32 B per node visited + 48 B per primitive tested
+        clocks = clk.summary()
+        clk_mhz = clocks.get("sm_mhz") or 1965.0
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        # algorithmic bytes per ray (SURVEY 8d's convention): 32 B per node visited + 48 B per primitive tested
         # + 32 B ray in + 16 B hit out, with the oracle's mean counters for this ray population
         bytes_per_ray = 32.0 * stats["mean_nodes_visited"] + 48.0 * stats["mean_prims_tested"] + 48.0
         peak, how = measured_peak()
-        note = ("cbox is 14 primitives (L1-resident): the kernel is SM-issue-bound, the HBM figure is the "
-                "algorithmic-bytes convention of SURVEY 8(d); see DESIGN.md for the issue roofline")
-        if single_launch:
-            # K_tile: the step IS one launch of the dominant kernel, timed by the library's own
-            # CUDA events on its launch stream during the timed steps above
-            achieved = bytes_per_ray * rays / (kernel_ms * 1e-3) / 1e9
-            # the committed `ncu --set full` capture of this very launch (cbox, 512 spp, one GPU): DRAM traffic per
-            # launch, and the warp-instruction count that gives the kernel's real (instruction-issue) roofline
-            traffic, issue = None, None
-            cap = ncu_capture(os.path.join(ROOT, "profiles", "r01_ncu_tile_cbox.csv"))
-            if cap and args.spp == 512 and world == 1:
-                traffic = cap.get("dram__bytes_read.sum", 0.0) + cap.get("dram__bytes_write.sum", 0.0)
-                warp_inst = cap.get("smsp__inst_executed.sum")
-                clk_hz = (clk.summary().get("sm_mhz") or 1965.0) * 1e6
-                if warp_inst:
-                    sms = torch.cuda.get_device_properties(local).multi_processor_count
-                    floor_ms = warp_inst / (sms * 4 * clk_hz) * 1e3          # one warp instruction per scheduler per cycle
-                    issue = {"bound": "sm_issue", "warp_inst_per_launch": warp_inst, "schedulers": sms * 4, "sm_mhz": clk_hz / 1e6,
-                             "floor_ms": floor_ms, "frac": floor_ms / (kernel_ms / args.steps),
-                             "lanes_per_warp_inst": cap.get("smsp__thread_inst_executed_per_inst_executed.ratio"),
-                             "source": "profiles/r01_ncu_tile_cbox.csv (instruction count) / live launch time"}
-            roofline = {"bound": "hbm", "kernel": "nb_k_tile<path_mis>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": traffic, "peak_source": how, "bytes_per_ray": bytes_per_ray,
-                        "launches_timed": args.steps, "avg_launch_ms": kernel_ms / args.steps,
-                        "kernel_share": {"tile": kernel_ms / ms}, "issue": issue, "note": note}
-        else:
-            # wavefront: dominant kernel K_trace, one extra step with per-kernel event timers
-            ctx.render_begin(params)
-            ctx.set_option("profile", 1)
-            ctx.render_subframe(0, max(16, args.spp // 8))
-            ctx.set_option("profile", 0)
-            pc = ctx.counters()
-            prof_rays = pc["rays_closest"] + pc["rays_any"]
-            achieved = bytes_per_ray * prof_rays / (pc["trace_ms"] * 1e-3) / 1e9 if pc["trace_ms"] > 0 else None
-            roofline = {"bound": "hbm", "kernel": "nb_k_trace_wave", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak if achieved else None, "traffic": None, "peak_source": how,
-                        "bytes_per_ray": bytes_per_ray, "launches_timed": int(pc["iterations"]),
-                        "avg_launch_ms": pc["trace_ms"] / max(1, pc["iterations"]),
-                        "kernel_share": {"trace": pc["trace_ms"] / pc["device_ms"], "shade": pc["shade_ms"] / pc["device_ms"], "regen": pc["regen_ms"] / pc["device_ms"]},
-                        "note": note}
+        avg_launch_ms = kernel_ms / args.steps
+        lanes_peak = sms * 128 * clk_mhz * 1e6       # thread-instructions/s: SMs x 4 schedulers x 32 lanes x clock (8d, C1)
+        roofline = {"bound": "sm_issue", "kernel": "nb_k_tile<path_mis, FLAT>" if single_launch else "wavefront (K_shade + K_trace)",
+                    "achieved": None, "peak": lanes_peak / 1e12, "unit": "T lane-inst/s", "frac": None, "traffic": None,
+                    "peak_source": "%d SMs x 128 lanes x %.0f MHz (median SM clock sampled during the timed steps)" % (sms, clk_mhz),
+                    "launches_timed": args.steps, "avg_launch_ms": avg_launch_ms, "kernel_share": {"tile": kernel_ms / ms},
+                    "note": "cbox is 14 primitives (L1-resident): the kernel is bound by SM instruction issue, not by HBM; "
+                            "frac = thread-instructions/s / (SMs x 128 lanes x clock), instruction counts per sample from the "
+                            "committed ncu --set full capture of this launch, launch time measured live"}
+        cap = ncu_capture(NCU_CAPTURE)
+        meta_p = NCU_CAPTURE[:-4] + ".meta.json"
+        if cap and os.path.exists(meta_p) and single_launch:
+            meta = json.load(open(meta_p))
+            n_cap = float(meta["samples"])
+            thread_inst = cap.get("smsp__thread_inst_executed.sum", 0.0) / n_cap * (samples_all / args.steps / world)
+            warp_inst = cap.get("smsp__inst_executed.sum", 0.0) / n_cap * (samples_all / args.steps / world)
+            roofline.update({
+                "achieved": thread_inst / (avg_launch_ms * 1e-3) / 1e12,
+                "frac": thread_inst / (avg_launch_ms * 1e-3) / lanes_peak,
+                "warp_issue_frac": warp_inst / (avg_launch_ms * 1e-3) / (sms * 4 * clk_mhz * 1e6),
+                "lanes_per_warp_inst": cap.get("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                "traffic": (cap.get("dram__bytes_read.sum", 0.0) + cap.get("dram__bytes_write.sum", 0.0)) / n_cap * (samples_all / args.steps / world),
+                "capture": os.path.relpath(NCU_CAPTURE, ROOT), "capture_src_sha": meta.get("src_sha"),
+                "capture_matches_build": meta.get("src_sha") == kernel_source_sha()})
+        algorithmic = {"convention": "SURVEY 8(d) algorithmic bytes: (32 B x nodes + 48 B x primitives + 48 B) per ray; on cbox these "
+                                     "bytes never leave L1, so this is NOT an HBM roofline — kept as the contract's per-ray figure",
+                       "bytes_per_ray": bytes_per_ray, "gb_per_s": bytes_per_ray * rays / (kernel_ms * 1e-3) / 1e9 / 1.0,
+                       "hbm_peak_gb_per_s": peak, "peak_source": how}
+        roofline["algorithmic_bytes"] = algorithmic
         cpu = None
         if not args.no_cpu_baseline:
             try:
@@ -305,21 +387,43 @@ def main():
                        "rays_per_s": j["rays_dedup_per_s"]}
             except Exception as ex:   # the checker is missing: say so, never substitute
                 cpu = {"value": None, "unit": "samples/s", "cores": 0, "kind": "reference", "sample": "unavailable: %s" % ex}
+        configs = None
+        if world == 1 and not args.no_configs:
+            configs = []
+            try:
+                configs.append(tree_config(nb, ctx, "C2 table path_mis 800x600 (22 766 triangles)",
+                                           os.path.join(GOLDEN, "scenes", "table", "table_path_mis.xml"), 64, sms, clk_mhz,
+                                           os.path.join(ROOT, "profiles", "r02_ncu_walk_table.csv")))
+                import tempfile
+                d = tempfile.mkdtemp(prefix="c3_")
+                subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_c3_scene.py"), d, "spp=16"], check=True,
+                               stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                configs.append(tree_config(nb, ctx, "C3 synthetic 1 310 720 triangles path_mis 800x600",
+                                           os.path.join(d, "c3_path_mis.xml"), 16, sms, clk_mhz,
+                                           os.path.join(ROOT, "profiles", "r02_ncu_walk_c3.csv")))
+            except Exception as ex:
+                configs.append({"error": str(ex)[:300]})
         line = {"metric": "samples_per_s", "value": samples_all / (ms * 1e-3), "unit": "samples/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "spp_per_gpu": args.spp, "integrator": "path_mis",
+                "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "spp_total": spp_total, "spp_per_gpu": spp_total // world, "integrator": "path_mis",
                            "strategy": "tile" if single_launch else "wavefront",
-                           "parallelism": "sample slices x%d, scene replicated, 1 NCCL film reduce" % world,
+                           "parallelism": "sample slices x%d of ONE render, scene replicated, 1 NCCL film reduce issued by the library "
+                                          "(nb_film_reduce) inside the timed region" % world,
+                           "timed": "film clear + render + reduce, CUDA events on the library's stream; every rank starts each step at a barrier",
                            "l2": "256 MB flush write between timed steps" + ("; K_tile keeps path state in registers, film 7.8 MB" if single_launch
                                                                                   else "; path pool (1M slots x 164 B) exceeds L2")},
                 "rays_per_s": rays_all / (ms * 1e-3), "rays_per_sample": rays_all / samples_all,
                 "e2e": {"value": float(se.item()) / float(te.item()), "unit": "samples/s", "h2d_bytes_per_step": h2d,
-                        "d2h_bytes_per_step": int(host_film.nbytes)},
-                "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roofline, "cpu_baseline": cpu}
+                        "d2h_bytes_per_step": d2h,
+                        "what": "pinned scene + BVH upload, render, reduce, toBitmap on device, finished image to pinned host memory (rank 0)"},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+        if configs is not None:
+            line["configs"] = configs
         emit(line)
     ctx.close()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

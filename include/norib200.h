@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 5
+#define NB_ABI_VERSION 6
 
 enum {
     NB_OK = 0,
@@ -248,6 +248,12 @@ int  nb_abi_version(void);
 int  nb_abi_sizeof(int which);
 
 int  nb_create(int device, nb_ctx **out);       /* fails with NB_E_NO_DEVICE when there is none */
+/* One context per listed device, in ONE process, joined by one NCCL communicator clique (ncclCommInitAll): the shape
+ * the reference's single render thread needs (src/utils/render.cpp:462-574 drives one OptixState). out gets n
+ * contexts; out[0] is the root of nb_film_reduce. Upload the scene / build the BVH / nb_render_begin on each, give
+ * context g the sample slice (stride n, offset g) in nb_render_subframe (asynchronous, so the loop over contexts keeps
+ * all devices busy), then nb_film_reduce(out[0]) and nb_film_download(out[0]). Destroy each with nb_destroy. */
+int  nb_create_multi(const int *devices, int n, nb_ctx **out);
 int  nb_destroy(nb_ctx *ctx);
 const char *nb_last_error(const nb_ctx *ctx);   /* ctx may be NULL: error of the last nb_create */
 
@@ -301,7 +307,11 @@ int  nb_render_begin(nb_ctx *ctx, const nb_render_params *params);  /* allocates
 /* OptixState::renderSubframe (OptixState.cpp:485-510): samples [first, first+count) of every
  * pixel; sample s of pixel p always uses the same random stream, whatever the launch split.
  * Only samples with (s % sample_stride) == sample_offset are rendered (multi-GPU sample slices;
- * 1,0 = all). Asynchronous: returns once the work is queued. */
+ * 1,0 = all). Asynchronous (the default, persistent-kernel strategy): returns once the launch is queued on the
+ * context's stream, so one host thread can keep several devices busy; nb_sync, nb_get_counters, nb_film_download*,
+ * nb_film_clear and nb_render_begin wait for it, and a kernel failure is reported by whichever of them runs first.
+ * (The optional wavefront strategy polls its queues and returns when the subframe is done. OptixState::renderSubframe
+ * itself ends with cudaStreamSynchronize, OptixState.cpp:507 — call nb_sync for that behaviour.) */
 int  nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count,
                         uint32_t sample_stride, uint32_t sample_offset);
 /* Host-only helper (no device needed): which samples a (first, count, stride, offset) slice holds:
@@ -319,9 +329,29 @@ int  nb_film_shape(nb_ctx *ctx, uint32_t *rows, uint32_t *cols, uint32_t *border
 int  nb_film_download(nb_ctx *ctx, float *out, int normalize);
 /* The same for one layer (NB_LAYER_*); a layer that was not requested in nb_render_params.layers fails with NB_E_STATE. */
 int  nb_film_download_layer(nb_ctx *ctx, int layer, float *out, int normalize);
-/* Device address of the accumulators (rows*cols*4 floats) for the NCCL film reduce. */
+/* Device address of the accumulators (rows*cols*4 floats), for callers that run their own collective. */
 int  nb_film_device_ptr(nb_ctx *ctx, void **ptr, uint64_t *n_floats);
+/* ---- multi-GPU: the film reduce (the film is linear, block.cpp:120-122) --------------
+ * One process per GPU: rank 0 fills NB_COMM_ID_BYTES with nb_comm_unique_id, the launcher's own channel (MPI,
+ * torch.distributed, a file) carries them to every rank, each rank calls nb_comm_init_rank on its context (collective:
+ * returns when all n_ranks have joined). One process, n GPUs: nb_create_multi above.
+ * nb_film_reduce: ncclReduce(sum, float, root = rank 0) of the film accumulators (and of the normal layer when the
+ * render has one), in place, queued on the context's stream after the subframes already queued there — no host
+ * synchronisation; a following nb_film_download on rank 0 returns the sum, and the other ranks' films are cleared (their
+ * samples moved to the root, so render-more-then-reduce-again never counts a sample twice). With one rank it does nothing. In an
+ * nb_create_multi group ONE call (on any member) reduces the whole group. NCCL is loaded at run time (libnccl.so.2);
+ * without it these entries fail with NB_E_UNSUPPORTED and everything else still works. */
+#define NB_COMM_ID_BYTES 128
+int  nb_comm_unique_id(void *id);
+int  nb_comm_init_rank(nb_ctx *ctx, int n_ranks, int rank, const void *id);
+int  nb_comm_info(nb_ctx *ctx, int *rank, int *n_ranks, int *nccl_version);
+int  nb_film_reduce(nb_ctx *ctx);
 int  nb_get_counters(nb_ctx *ctx, nb_counters *out);
+/* Device-side stopwatch on the context's own stream (the stream every kernel, copy and reduce of this library is
+ * queued on — a caller's events on another stream do not see that work): nb_timer_mark(ctx, 0) ... queued work ...
+ * nb_timer_mark(ctx, 1); nb_timer_elapsed waits for mark 1 and returns the CUDA-event time between the two. */
+int  nb_timer_mark(nb_ctx *ctx, int which);
+int  nb_timer_elapsed(nb_ctx *ctx, float *ms);
 /* options: "profile" (per-kernel event timers of the wavefront pipeline), "sort" (reserved),
  * "strategy" (NB_STRATEGY_*: how path_mis / path_mats are executed; the direct_* integrators
  * always run as one K_tile launch), "flat_scan" (-1 auto, 0 always walk the tree, 1 always scan

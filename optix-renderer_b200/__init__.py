@@ -26,6 +26,7 @@ MEDIUM_VACUUM, MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1, 2
 PHASE_ISOTROPIC, PHASE_HENYEY_GREENSTEIN, PHASE_SCHLICK = 0, 1, 2
 FILTER_RESOLUTION = 32
 TRACE_STATIC_MAX_RAYS = 65536
+COMM_ID_BYTES = 128
 
 # numpy mirrors of the records (field order and padding as in the header)
 shape_dtype = np.dtype([("type", "<u4"), ("prim_count", "<u4"), ("vertex_offset", "<u4"), ("vertex_count", "<u4"),
@@ -92,7 +93,8 @@ EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_las
            "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
            "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe",
-           "nb_bsdf_probe", "nb_film_download_layer", "nb_trace_rays_static"]
+           "nb_bsdf_probe", "nb_film_download_layer", "nb_trace_rays_static", "nb_create_multi", "nb_comm_unique_id",
+           "nb_comm_init_rank", "nb_comm_info", "nb_film_reduce", "nb_timer_mark", "nb_timer_elapsed"]
 
 _lib = None
 
@@ -117,6 +119,13 @@ def load_library(path=None):
     lib.nb_last_error.argtypes = [C.c_void_p]
     lib.nb_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     lib.nb_destroy.argtypes = [C.c_void_p]
+    lib.nb_create_multi.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+    lib.nb_comm_unique_id.argtypes = [C.c_void_p]
+    lib.nb_comm_init_rank.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.nb_comm_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    lib.nb_film_reduce.argtypes = [C.c_void_p]
+    lib.nb_timer_mark.argtypes = [C.c_void_p, C.c_int]
+    lib.nb_timer_elapsed.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     lib.nb_upload_scene.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
     lib.nb_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(BvhImport)]
     lib.nb_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p]
@@ -196,13 +205,40 @@ def _ptr(a):
 class Context:
     """One nb_ctx: a device, its uploaded scene and (optionally) a render in progress."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, _handle=None):
         self.lib = load_library()
         self.handle = C.c_void_p()
-        rc = self.lib.nb_create(device, C.byref(self.handle))
-        if rc != NB_OK:
-            raise NbError(rc, self.lib.nb_last_error(None).decode())
+        if _handle is not None:                 # one member of a create_multi() group
+            self.handle = C.c_void_p(_handle)
+        else:
+            rc = self.lib.nb_create(device, C.byref(self.handle))
+            if rc != NB_OK:
+                raise NbError(rc, self.lib.nb_last_error(None).decode())
+        self.device = device
         self._keep = []
+
+    def comm_init(self, n_ranks, rank, unique_id):
+        """nb_comm_init_rank: join the NCCL communicator of a one-process-per-GPU job (collective)."""
+        buf = C.create_string_buffer(bytes(unique_id), COMM_ID_BYTES)
+        self._check(self.lib.nb_comm_init_rank(self.handle, n_ranks, rank, buf))
+
+    def comm_info(self):
+        r, n, v = C.c_int(), C.c_int(), C.c_int()
+        self._check(self.lib.nb_comm_info(self.handle, C.byref(r), C.byref(n), C.byref(v)))
+        return {"rank": r.value, "n_ranks": n.value, "nccl_version": v.value}
+
+    def timer_mark(self, which):
+        self._check(self.lib.nb_timer_mark(self.handle, which))
+
+    def timer_elapsed(self):
+        """CUDA-event milliseconds between timer_mark(0) and timer_mark(1) on the library's stream (waits for mark 1)."""
+        ms = C.c_float()
+        self._check(self.lib.nb_timer_elapsed(self.handle, C.byref(ms)))
+        return ms.value
+
+    def film_reduce(self):
+        """nb_film_reduce: ncclReduce(sum) of the film accumulators to rank 0, queued on the context's stream."""
+        self._check(self.lib.nb_film_reduce(self.handle))
 
     def _check(self, rc):
         if rc != NB_OK:
@@ -375,7 +411,37 @@ def sample_slice(first, count, stride, offset):
     return a.value, b.value
 
 
-# ---- multi-GPU plumbing (torch.distributed; NCCL on GPUs, gloo in the CPU tests) ----------------
+# ---- multi-GPU: the library's own NCCL film reduce (include/norib200.h) ---------------------------
+def comm_unique_id():
+    """nb_comm_unique_id: the 128 bytes rank 0 hands to the other ranks (over the launcher's channel)."""
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    rc = load_library().nb_comm_unique_id(buf)
+    if rc != NB_OK:
+        raise NbError(rc, load_library().nb_last_error(None).decode())
+    return buf.raw
+
+
+def create_multi(devices):
+    """nb_create_multi: one Context per device in THIS process, joined by one NCCL clique; [0] is the reduce root."""
+    lib = load_library()
+    devs = (C.c_int * len(devices))(*devices)
+    out = (C.c_void_p * len(devices))()
+    rc = lib.nb_create_multi(devs, len(devices), out)
+    if rc != NB_OK:
+        raise NbError(rc, lib.nb_last_error(None).decode())
+    return [Context(d, _handle=h) for d, h in zip(devices, out)]
+
+
+def comm_init_torch(ctx):
+    """Join the library's communicator in a torchrun job: rank 0 makes the id, torch.distributed carries it."""
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(), dist.get_rank()
+    box = [comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    ctx.comm_init(world, rank, box[0])
+
+
+# ---- the same sum through torch.distributed (gloo in the CPU tests of the slice arithmetic) -------
 def film_tensor(ctx, device_index):
     """torch tensor aliasing the context's film accumulators (no copy)."""
     import torch
@@ -392,6 +458,11 @@ def reduce_film(film, dst=0):
     import torch.distributed as dist
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.reduce(film, dst=dst, op=dist.ReduceOp.SUM)
+        if film.is_cuda:
+            # the nb_* entries run on the library's own non-blocking stream, which never orders against torch's:
+            # the host must see the collective finished before it touches the film through the library again
+            import torch
+            torch.cuda.current_stream(film.device).synchronize()
     return film
 
 

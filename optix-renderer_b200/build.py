@@ -76,7 +76,7 @@ def build_cuda(verbose=False, extra=()):
         with ThreadPoolExecutor(max_workers=min(len(jobs), os.cpu_count() or 1)) as ex:
             list(ex.map(lambda cmd: _run(cmd, verbose), jobs))
     if _newer(LIB_CUDA, objs):
-        _run([NVCC] + ARCH + ["-shared", "-o", LIB_CUDA] + objs + ["-cudart", "static"], verbose)
+        _run([NVCC] + ARCH + ["-shared", "-o", LIB_CUDA] + objs + ["-cudart", "static", "-ldl"], verbose)
     return LIB_CUDA
 
 

@@ -83,11 +83,30 @@ int nb_destroy(nb_ctx *ctx) {
     if (!ctx) return NB_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    nb_comm_free(ctx);
+    for (int i = 0; i < 2; ++i) if (ctx->timer[i]) cudaEventDestroy(ctx->timer[i]);
     nb_render_free(ctx);
     nb_free_list(ctx->scene_allocs);
     nb_free_list(ctx->bvh_allocs);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
+    return NB_OK;
+}
+
+int nb_timer_mark(nb_ctx *ctx, int which) {
+    if (!ctx || which < 0 || which > 1) return nb_fail(ctx, NB_E_INVALID, "nb_timer_mark: which must be 0 or 1");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!ctx->timer[which]) NB_CUDA(ctx, cudaEventCreate(&ctx->timer[which]));
+    NB_CUDA(ctx, cudaEventRecord(ctx->timer[which], ctx->stream));
+    return NB_OK;
+}
+
+int nb_timer_elapsed(nb_ctx *ctx, float *ms) {
+    if (!ctx || !ms) return nb_fail(ctx, NB_E_INVALID, "nb_timer_elapsed: NULL argument");
+    if (!ctx->timer[0] || !ctx->timer[1]) return nb_fail(ctx, NB_E_STATE, "nb_timer_elapsed: mark 0 and 1 first");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaEventSynchronize(ctx->timer[1]));
+    NB_CUDA(ctx, cudaEventElapsedTime(ms, ctx->timer[0], ctx->timer[1]));
     return NB_OK;
 }
 
@@ -200,6 +219,7 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
         }
     }
 
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }     /* queued subframes still read the old scene */
     nb_free_list(ctx->scene_allocs);
     nb_free_list(ctx->bvh_allocs);
     ctx->scene_ready = ctx->bvh_ready = ctx->render_begun = false;

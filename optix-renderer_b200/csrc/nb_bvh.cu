@@ -28,6 +28,8 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     std::vector<uint8_t> seen(n, 0);
     std::vector<uint32_t> stack;
     stack.push_back(0);
+    uint32_t leaf_end = 0;          /* end of the last leaf range met in pre-order */
+    bool leaves_in_order = true;
     while (!stack.empty()) {
         const uint32_t i = stack.back();
         stack.pop_back();
@@ -37,6 +39,7 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
         if (nd.word0 & 1u) {
             const uint32_t size = nd.word0 >> 1, start = nd.word1;
             if ((uint64_t) start + size > ni) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: leaf %u range outside indices", i);
+            if (size) { if (start < leaf_end) leaves_in_order = false; leaf_end = start + size; }
         } else {
             const uint32_t left = i + 1, right = nd.word1;
             if (left >= n || right >= n) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: inner node %u has a child out of range", i);
@@ -103,6 +106,9 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
         nodes[(size_t) i * 2] = A; nodes[(size_t) i * 2 + 1] = B;
     }
 
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }     /* queued subframes still walk the old tree */
+    ctx->bvh_ready = false;                      /* a failure below must not leave a context pointing at freed memory */
+    ctx->dev.nodes = nullptr; ctx->dev.slots = nullptr; ctx->dev.n_nodes = 0; ctx->dev.n_slots = 0;
     for (void *p : ctx->bvh_allocs) cudaFree(p);
     ctx->bvh_allocs.clear();
     void *dn = nullptr, *ds = nullptr;
@@ -115,6 +121,9 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->dev.nodes = (const float4 *) dn; ctx->dev.slots = (const float4 *) ds;
     ctx->dev.n_nodes = n; ctx->dev.n_slots = ni;
+    /* the flat scan tests slots 0..n-1 in order; that is the walk's order only when the caller's leaves come in
+     * increasing index order (true of BVH::build's output; a foreign tree that breaks it is walked instead) */
+    ctx->flat_ok = leaves_in_order;
     ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;
     ctx->h_slot_tag.resize(ni); ctx->h_slot_prim.resize(ni);
     for (uint32_t k = 0; k < ni; ++k) {

@@ -239,7 +239,8 @@ __global__ void nb_k_build_emit_slots(NbDeviceScene sc, const uint32_t *prim_off
 #define NB_TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { rc = nb_fail(ctx, NB_E_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); goto done; } } while (0)
 
 int nb_build_bvh_device(nb_ctx *ctx) {
-    int rc = NB_OK;
+    int rc = nb_render_finish(ctx);              /* queued subframes still walk the old tree */
+    if (rc != NB_OK) return rc;
     const uint32_t n = ctx->h_shape_prim_offset.back();
     if (n == 0) return nb_fail(ctx, NB_E_INVALID, "nb_build_bvh: scene has no primitives");
     if (n >= (1u << 27)) return nb_fail(ctx, NB_E_UNSUPPORTED, "nb_build_bvh: too many primitives for the device builder");
@@ -318,6 +319,7 @@ int nb_build_bvh_device(nb_ctx *ctx) {
     ctx->bvh_allocs.push_back(d_nodes); ctx->bvh_allocs.push_back(d_slots);
     ctx->dev.nodes = d_nodes; ctx->dev.slots = d_slots;
     ctx->dev.n_nodes = n_kept; ctx->dev.n_slots = n;
+    ctx->flat_ok = true;                         /* slots are emitted in the pre-order of the leaves */
     ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;
     d_nodes = nullptr; d_slots = nullptr;
     ctx->bvh_ready = true;

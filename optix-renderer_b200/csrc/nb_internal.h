@@ -87,10 +87,17 @@ struct nb_ctx {
     int opt_walk = 1;                   /* tree scenes: K_tile_walk (per-lane state machine) instead of lock-step K_tile */
     int opt_ordered = 0;                /* 1: nb_trace_rays uses the near-child-first walk */
     int opt_flat = -1;                  /* -1: flat scan iff the scene has at most NB_FLAT_MAX_SLOTS primitives */
+    bool flat_ok = true;                /* leaves of the imported tree cover the slot list in pre-order: the flat scan visits what the walk visits */
+    /* multi-GPU film reduce (nb_comm.cu): one NCCL communicator per context */
+    void *comm = nullptr;               /* ncclComm_t */
+    int comm_rank = 0, comm_size = 1;
+    struct NbGroup *group = nullptr;    /* contexts created together by nb_create_multi (one process, n devices) */
+    cudaEvent_t timer[2] = { nullptr, nullptr };   /* nb_timer_mark / nb_timer_elapsed */
 };
 
 int nb_fail(nb_ctx *ctx, int code, const char *fmt, ...);
 inline bool nb_scene_flat(const nb_ctx *ctx) {
+    if (!ctx->flat_ok) return false;
     if (ctx->opt_flat >= 0) return ctx->opt_flat != 0;
     return ctx->dev.n_slots <= NB_FLAT_MAX_SLOTS;
 }
@@ -103,6 +110,13 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
 
 /* nb_render.cu */
 int nb_render_free(nb_ctx *ctx);
+/* waits for the subframes queued by nb_render_subframe and folds their timers / counters into the totals */
+int nb_render_finish(nb_ctx *ctx);
+/* film accumulators of the current render: data (+ normal layer or null), float count of one layer */
+int nb_render_film(nb_ctx *ctx, float **data, float **normal, uint64_t *n_floats);
+
+/* nb_comm.cu */
+void nb_comm_free(nb_ctx *ctx);
 
 /* nb_bvh_build.cu */
 int nb_build_bvh_device(nb_ctx *ctx);

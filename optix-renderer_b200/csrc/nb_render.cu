@@ -258,12 +258,41 @@ struct NbRenderState {
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_batch[2] = { nullptr, nullptr };
     nb_counters totals;
     int grid = 0;
+    int pending = 0;              /* K_tile subframes queued since the last nb_render_finish */
     std::vector<cudaEvent_t> prof_events;   /* "profile" option: 4 per iteration (shade | regen | trace) */
 };
+
+int nb_render_finish(nb_ctx *ctx) {
+    NbRenderState *r = ctx->render;
+    if (!r || !r->pending) return NB_OK;
+    const int n = r->pending;
+    r->pending = 0;
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: %s", cudaGetErrorString(e));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end);
+    r->totals.device_ms += ms;
+    r->totals.iterations += n;
+    r->totals.kernel_launches += n;
+    r->totals.samples = r->h_stats[NB_STAT_SAMPLES];
+    r->totals.rays_closest = r->h_stats[NB_STAT_RAYS_CLOSEST];
+    r->totals.rays_any = r->h_stats[NB_STAT_RAYS_ANY];
+    r->totals.invalid_samples = r->h_stats[NB_STAT_INVALID];
+    return NB_OK;
+}
+
+int nb_render_film(nb_ctx *ctx, float **data, float **normal, uint64_t *n_floats) {
+    if (!ctx->render || !ctx->render_begun) return nb_fail(ctx, NB_E_STATE, "no render in progress");
+    *data = (float *) ctx->render->film.data; *normal = (float *) ctx->render->film.normal;
+    *n_floats = (uint64_t) ctx->render->film.rows * ctx->render->film.cols * 4;
+    return NB_OK;
+}
 
 int nb_render_free(nb_ctx *ctx) {
     NbRenderState *r = ctx->render;
     if (!r) return NB_OK;
+    if (r->pending) { cudaStreamSynchronize(ctx->stream); r->pending = 0; }
     for (void *p : r->allocs) cudaFree(p);
     if (r->h_counts) cudaFreeHost(r->h_counts);
     if (r->h_stats) cudaFreeHost(r->h_stats);
@@ -319,6 +348,7 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     const nb_camera &cam = ctx->dev.camera;
     if (cam.width == 0 || cam.height == 0) return nb_fail(ctx, NB_E_INVALID, "camera has no output size");
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }
     uint32_t pool = params->pool_paths ? params->pool_paths : (1u << 20);
     pool = (pool + 255u) & ~255u;
     const uint32_t border = (uint32_t) ceilf(params->filter_radius - 0.5f);      /* block.cpp:57 */
@@ -392,6 +422,7 @@ int nb_film_clear(nb_ctx *ctx) {
     if (!ctx || !ctx->render || !ctx->render_begun) return nb_fail(ctx, NB_E_STATE, "nb_film_clear: no render in progress");
     NbRenderState *r = ctx->render;
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }
     NB_CUDA(ctx, cudaMemsetAsync(r->film.data, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
     if (r->film.normal) NB_CUDA(ctx, cudaMemsetAsync(r->film.normal, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
     NB_CUDA(ctx, cudaMemsetAsync(r->stats, 0, NB_STAT_WORDS * sizeof(unsigned long long), ctx->stream));
@@ -415,31 +446,24 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
     plan.total = (unsigned long long) passes * plan.npix;
     plan.seed = r->params.seed; plan.first = s0; plan.stride = stride; plan.max_depth = r->params.max_depth;
     for (int i = 0; i < 3; ++i) plan.iparam[i] = r->params.integrator_params[i];
-    cudaEventRecord(r->ev_begin, ctx->stream);
-    if (plan.total == 0) { cudaEventRecord(r->ev_end, ctx->stream); return NB_OK; }
+    if (plan.total == 0) return NB_OK;
     const uint32_t integ = r->params.integrator;
     const bool is_path = integ == NB_INTEGRATOR_PATH_MIS || integ == NB_INTEGRATOR_PATH_MATS;
     if (!is_path || nb_use_tile_strategy(ctx)) {
-        /* K_tile: one persistent launch, path state in registers (nb_mega.cu) */
+        /* K_tile: one persistent launch, path state in registers (nb_mega.cu). Asynchronous: the launch, its end
+         * event and the copy of the device counters are queued on the context's stream; nb_render_finish (called by
+         * nb_sync, nb_get_counters, nb_film_download*, nb_film_clear, nb_render_begin) waits and reads them */
+        if (!r->pending) cudaEventRecord(r->ev_begin, ctx->stream);
         cudaError_t e = nb_launch_tile(ctx->dev, r->film, plan, cam.height, passes, integ, r->tile_counter, r->stats,
                                        ctx->sm_count, ctx->stream, ctx->opt_walk != 0);
         if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: K_tile launch: %s", cudaGetErrorString(e));
         cudaEventRecord(r->ev_end, ctx->stream);
         cudaMemcpyAsync(r->h_stats, r->stats, NB_STAT_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream);
-        e = cudaStreamSynchronize(ctx->stream);
-        if (e == cudaSuccess) e = cudaGetLastError();
-        if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_subframe: %s", cudaGetErrorString(e));
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end);
-        r->totals.device_ms += ms;
-        r->totals.iterations += 1;
-        r->totals.kernel_launches += 1;
-        r->totals.samples = r->h_stats[NB_STAT_SAMPLES];
-        r->totals.rays_closest = r->h_stats[NB_STAT_RAYS_CLOSEST];
-        r->totals.rays_any = r->h_stats[NB_STAT_RAYS_ANY];
-        r->totals.invalid_samples = r->h_stats[NB_STAT_INVALID];
+        r->pending += 1;
         return NB_OK;
     }
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }
+    cudaEventRecord(r->ev_begin, ctx->stream);
     NbWave w = r->wave;
     const uint32_t n_live = (uint32_t) std::min<unsigned long long>(w.pool, plan.total);
     w.total_samples = plan.total;
@@ -520,6 +544,7 @@ int nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count, uint32_t str
 int nb_sync(nb_ctx *ctx) {
     if (!ctx) return NB_E_INVALID;
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return NB_OK;
 }
@@ -541,6 +566,7 @@ int nb_film_download_layer(nb_ctx *ctx, int layer, float *out, int normalize) {
     float4 *const film_data = layer == NB_LAYER_NORMAL ? r->film.normal : r->film.data;
     if (!film_data) return nb_fail(ctx, NB_E_STATE, "nb_film_download_layer: layer %d was not requested in nb_render_params.layers", layer);
     NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }
     if (!normalize) {
         NB_CUDA(ctx, cudaMemcpyAsync(out, film_data, (size_t) r->film.rows * r->film.cols * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
         NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -567,6 +593,11 @@ int nb_film_device_ptr(nb_ctx *ctx, void **ptr, uint64_t *n_floats) {
 
 int nb_get_counters(nb_ctx *ctx, nb_counters *out) {
     if (!ctx || !ctx->render || !out) return nb_fail(ctx, NB_E_STATE, "nb_get_counters: no render in progress");
+    if (ctx->render->pending) {
+        NB_CUDA(ctx, cudaSetDevice(ctx->device));
+        const int rc0 = nb_render_finish(ctx);
+        if (rc0 != NB_OK) return rc0;
+    }
     *out = ctx->render->totals;
     return NB_OK;
 }

@@ -8,6 +8,10 @@ namespace nori {
 class B200State {
 public:
     explicit B200State(int device = 0);
+    /* several GPUs of one box behind the same object (nb_create_multi): every device holds the scene, renders the
+     * sample slice (stride n, offset g) of each subframe, and download() sums the films on the first device with one
+     * NCCL reduce (nb_film_reduce) */
+    explicit B200State(const std::vector<int> &devices);
     ~B200State();
     B200State(const B200State &) = delete;
     /* OptixState::preRender (OptixState.render.cpp:19-85): flatten + upload + BVH + film setup.
@@ -22,9 +26,11 @@ public:
     const FlatScene &flat() const { return m_flat; }
     const std::string &whyUnsupported() const { return m_why; }
     nb_ctx *handle() const { return m_ctx; }
+    size_t deviceCount() const { return m_all.size(); }
 private:
     void check(int rc) const;
-    nb_ctx *m_ctx = nullptr;
+    nb_ctx *m_ctx = nullptr;                        /* the root: m_all[0] */
+    std::vector<nb_ctx *> m_all;
     FlatScene m_flat;
     std::string m_why;
 };

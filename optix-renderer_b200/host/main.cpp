@@ -34,16 +34,26 @@ static void writePfm(const std::string &path, const float *data, size_t h, size_
 
 int main(int argc, char **argv) {
     if (argc < 3) {
-        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D] [seed=S] [launch=N] [flat=scene.nbs]\n");
+        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [flat=scene.nbs]\n");
         return 2;
     }
     try {
         int spp = -1, device = 0, launch = 0;
         uint64_t seed = 0;
         std::string flatOut;
+        std::vector<int> devices;
         for (int i = 3; i < argc; ++i) {
             if (!strncmp(argv[i], "spp=", 4)) spp = atoi(argv[i] + 4);
             else if (!strncmp(argv[i], "device=", 7)) device = atoi(argv[i] + 7);
+            else if (!strncmp(argv[i], "devices=", 8)) {
+                for (const char *p = argv[i] + 8; *p;) {
+                    char *end = nullptr;
+                    const long d = strtol(p, &end, 10);
+                    if (end == p) throw NoriException("devices=: expected a comma-separated list of device numbers");
+                    devices.push_back((int) d);
+                    p = *end == ',' ? end + 1 : end;
+                }
+            }
             else if (!strncmp(argv[i], "seed=", 5)) seed = strtoull(argv[i] + 5, nullptr, 10);
             else if (!strncmp(argv[i], "launch=", 7)) launch = atoi(argv[i] + 7);
             else if (!strncmp(argv[i], "flat=", 5)) flatOut = argv[i] + 5;
@@ -52,7 +62,8 @@ int main(int argc, char **argv) {
         std::unique_ptr<NoriObject> root(loadFromXML(argv[1]));
         if (root->getClassType() != NoriObject::EScene) throw NoriException("root of %s is not a scene", argv[1]);
         Scene *scene = static_cast<Scene *>(root.get());
-        B200State state(device);
+        if (devices.empty()) devices.push_back(device);
+        B200State state(devices);
         if (!state.preRender(*scene, seed)) {
             fprintf(stderr, "nori_b200: this scene cannot run on the GPU backend: %s\n", state.whyUnsupported().c_str());
             return 3;
@@ -72,10 +83,10 @@ int main(int argc, char **argv) {
         nb_counters c = state.counters();
         printf("{\"scene\": \"%s\", \"width\": %u, \"height\": %u, \"spp\": %d, \"load_seconds\": %.3f, \"seconds\": %.6f, "
                "\"samples\": %llu, \"samples_per_s\": %.1f, \"rays_closest\": %llu, \"rays_any\": %llu, \"rays_per_s\": %.1f, "
-               "\"device_ms\": %.3f, \"invalid_samples\": %llu}\n",
+               "\"device_ms\": %.3f, \"invalid_samples\": %llu, \"devices\": %zu}\n",
                argv[1], w, h, spp, load_s, render_s, (unsigned long long) c.samples, c.samples / render_s,
                (unsigned long long) c.rays_closest, (unsigned long long) c.rays_any, (c.rays_closest + c.rays_any) / render_s,
-               c.device_ms, (unsigned long long) c.invalid_samples);
+               c.device_ms, (unsigned long long) c.invalid_samples, state.deviceCount());
         return 0;
     } catch (const std::exception &e) {
         fprintf(stderr, "nori_b200: %s\n", e.what());
