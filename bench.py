@@ -326,12 +326,16 @@ def main():
             ctx.sync()
         return ctx.counters()["samples"]
 
-    e2e_step()
+    for _ in range(min(2, args.warmup)):
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
     e2e_samples = 0
+    e2e_step_ms = []
     for _ in range(args.steps):
+        t1 = time.perf_counter()
         e2e_samples += e2e_step()
+        e2e_step_ms.append(round(1e3 * (time.perf_counter() - t1), 3))
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
@@ -415,7 +419,7 @@ def main():
                                                                                   else "; path pool (1M slots x 164 B) exceeds L2")},
                 "rays_per_s": rays_all / (ms * 1e-3), "rays_per_sample": rays_all / samples_all,
                 "e2e": {"value": float(se.item()) / float(te.item()), "unit": "samples/s", "h2d_bytes_per_step": h2d,
-                        "d2h_bytes_per_step": d2h,
+                        "d2h_bytes_per_step": d2h, "step_ms_rank0": e2e_step_ms,
                         "what": "pinned scene + BVH upload, render, reduce, toBitmap on device, finished image to pinned host memory (rank 0)"},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
         if configs is not None:

@@ -91,6 +91,20 @@ void nb_comm_free(nb_ctx *ctx) {
     }
 }
 
+/* After the reduce the samples live in the root's film: the other ranks start again from zero, so that rendering more
+ * subframes and reducing again (progressive display, render.cpp:725-747) counts nothing twice. Must be queued AFTER
+ * ncclGroupEnd: calls inside an NCCL group reach the stream only when the group closes. */
+static int nb_reduce_clear(nb_ctx *ctx) {
+    if (ctx->comm_rank == 0) return NB_OK;
+    float *data = nullptr, *normal = nullptr;
+    uint64_t count = 0;
+    const int rc = nb_render_film(ctx, &data, &normal, &count);
+    if (rc != NB_OK) return rc;
+    NB_CUDA(ctx, cudaMemsetAsync(data, 0, (size_t) count * sizeof(float), ctx->stream));
+    if (normal) NB_CUDA(ctx, cudaMemsetAsync(normal, 0, (size_t) count * sizeof(float), ctx->stream));
+    return NB_OK;
+}
+
 /* ncclReduce calls of one context: composite film, then the normal layer when the render has one */
 static int nb_reduce_enqueue(nb_ctx *ctx, NbNccl *n) {
     float *data = nullptr, *normal = nullptr;
@@ -99,12 +113,6 @@ static int nb_reduce_enqueue(nb_ctx *ctx, NbNccl *n) {
     if (rc != NB_OK) return rc;
     NB_NCCL(ctx, n, n->Reduce(data, data, (size_t) count, NB_NCCL_FLOAT, NB_NCCL_SUM, 0, (NbNcclComm) ctx->comm, ctx->stream));
     if (normal) NB_NCCL(ctx, n, n->Reduce(normal, normal, (size_t) count, NB_NCCL_FLOAT, NB_NCCL_SUM, 0, (NbNcclComm) ctx->comm, ctx->stream));
-    if (ctx->comm_rank != 0) {
-        /* the samples now live in the root's film: start again from zero, so that rendering more subframes and
-         * reducing again (progressive display, render.cpp:725-747) counts nothing twice */
-        NB_CUDA(ctx, cudaMemsetAsync(data, 0, (size_t) count * sizeof(float), ctx->stream));
-        if (normal) NB_CUDA(ctx, cudaMemsetAsync(normal, 0, (size_t) count * sizeof(float), ctx->stream));
-    }
     return NB_OK;
 }
 
@@ -182,7 +190,8 @@ int nb_film_reduce(nb_ctx *ctx) {
     if (!n || !ctx->comm) return nb_fail(ctx, NB_E_STATE, "nb_film_reduce: no communicator (nb_comm_init_rank / nb_create_multi)");
     if (!ctx->group) {
         NB_CUDA(ctx, cudaSetDevice(ctx->device));
-        return nb_reduce_enqueue(ctx, n);
+        const int rc = nb_reduce_enqueue(ctx, n);
+        return rc != NB_OK ? rc : nb_reduce_clear(ctx);
     }
     /* one process, n devices: every member's reduce is issued here, inside one NCCL group */
     for (nb_ctx *m : ctx->group->members)
@@ -195,6 +204,11 @@ int nb_film_reduce(nb_ctx *ctx) {
         if (rc != NB_OK) { if (m != ctx) nb_fail(ctx, rc, "nb_film_reduce: device %d: %s", m->device, m->error.c_str()); break; }
     }
     const int r = n->GroupEnd();
+    if (rc == NB_OK && r == NB_NCCL_SUCCESS)
+        for (nb_ctx *m : ctx->group->members) {
+            cudaSetDevice(m->device);
+            if ((rc = nb_reduce_clear(m)) != NB_OK) { if (m != ctx) nb_fail(ctx, rc, "nb_film_reduce: device %d: %s", m->device, m->error.c_str()); break; }
+        }
     cudaSetDevice(ctx->device);
     if (rc != NB_OK) return rc;
     if (r != NB_NCCL_SUCCESS) return nb_fail(ctx, NB_E_CUDA, "ncclGroupEnd failed: %s", n->GetErrorString(r));
