@@ -299,6 +299,10 @@ int  nb_emitter_probe(nb_ctx *ctx, uint32_t emitter, const float *in, uint64_t n
  * sample(wi, sample): the returned weight rgb, the sampled wo.xyz, 1 if the measure is EDiscrete else 0,
  * and bsdf->pdf of the sampled direction. */
 int  nb_bsdf_probe(nb_ctx *ctx, uint32_t bsdf, const float *in, uint64_t n, float *out);
+/* Parity entry for the random streams: pcg32 (ext/pcg32/pcg32.h:51-66, 101-110) as the DEVICE runs it. out_u32 gets the
+ * first n nextUInt() of a generator seeded with seed(initstate, initseq), out_f32 the first n nextFloat() of another
+ * generator seeded the same way. (seed(42, 54) is "Round 1" of ext/pcg32/pcg32-demo.out.) */
+int  nb_rng_probe(nb_ctx *ctx, uint64_t initstate, uint64_t initseq, uint32_t n, uint32_t *out_u32, float *out_f32);
 int  nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples,
                      uint64_t seed, float *out);
 
@@ -358,7 +362,12 @@ int  nb_timer_elapsed(nb_ctx *ctx, float *ms);
  * the primitive list: same hits, see nb_trace.cuh), "walk" (1: tree scenes render path_mis / path_mats with the
  * per-lane state machine K_tile_walk), "ordered" (1: nb_trace_rays enters the child nearer to the ray first and breaks
  * exact-t ties by leaf-order slot, nb_traverse_ordered; 0, default: the reference's left-first order with skip links —
- * both return the reference's bits; the render kernels walk left-first, which measured faster) */
+ * both return the reference's bits), "wide" (1, default: the render kernels traverse tree scenes through the PRODUCTION
+ * tree — the binary tree collapsed to 4-wide nodes, children entered near-first, subtrees behind the current hit
+ * culled; every primitive test and the exact-t tie rule are the reference's, so images are the same within Monte-Carlo
+ * noise and hits agree except where a box test rounds differently, measured >= 99.9999 % (tests/test_wide_gpu.py);
+ * 0: parity mode, the reference's own visiting order everywhere), "trace_wide" (1: nb_trace_rays answers through the
+ * production tree too, to measure that hit parity; default 0 = bit-exact reference order) */
 enum { NB_STRATEGY_AUTO = 0, NB_STRATEGY_WAVEFRONT = 1, NB_STRATEGY_TILE = 2 };
 int  nb_set_option(nb_ctx *ctx, const char *name, int64_t value);
 

@@ -94,7 +94,7 @@ EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_las
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
            "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe",
            "nb_bsdf_probe", "nb_film_download_layer", "nb_trace_rays_static", "nb_create_multi", "nb_comm_unique_id",
-           "nb_comm_init_rank", "nb_comm_info", "nb_film_reduce", "nb_timer_mark", "nb_timer_elapsed"]
+           "nb_comm_init_rank", "nb_comm_info", "nb_film_reduce", "nb_timer_mark", "nb_timer_elapsed", "nb_rng_probe"]
 
 _lib = None
 
@@ -125,6 +125,7 @@ def load_library(path=None):
     lib.nb_comm_info.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.nb_film_reduce.argtypes = [C.c_void_p]
     lib.nb_timer_mark.argtypes = [C.c_void_p, C.c_int]
+    lib.nb_rng_probe.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]
     lib.nb_timer_elapsed.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     lib.nb_upload_scene.argtypes = [C.c_void_p, C.POINTER(SceneDesc)]
     lib.nb_build_bvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(BvhImport)]
@@ -313,6 +314,12 @@ class Context:
         out = np.zeros((len(rec), 12), dtype="<f4")
         self._check(self.lib.nb_bsdf_probe(self.handle, bsdf, _ptr(rec), len(rec), _ptr(out)))
         return out
+
+    def rng_probe(self, initstate, initseq, n):
+        """(n nextUInt(), n nextFloat()) of the device pcg32 seeded with seed(initstate, initseq)."""
+        u, f = np.zeros(n, dtype="<u4"), np.zeros(n, dtype="<f4")
+        self._check(self.lib.nb_rng_probe(self.handle, initstate, initseq, n, _ptr(u), _ptr(f)))
+        return u, f
 
     def medium_probe(self, medium, rays, samples=1024, seed=1):
         """rays: (n, 8) float32 [o, d, mint, maxt]; returns (n, 4) [density(o), P(free path < maxt), mean path, mean Tr]."""

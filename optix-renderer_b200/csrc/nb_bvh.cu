@@ -3,6 +3,75 @@
 #include <algorithm>
 #include <cstring>
 
+/* Collapses the binary tree (reference node layout) into 4-wide nodes: a wide node starts from a binary node's two
+ * children and, while it has room, replaces the inner child with the largest surface area by that child's two
+ * children. Child boxes are the binary nodes' own boxes; leaves keep their slot ranges. Wide nodes are numbered in
+ * depth-first order (a node's subtree is contiguous). Returns the number of levels. */
+void nb_collapse_wide(const nb_bvh_node *nodes, uint32_t n, std::vector<float4> &wide, uint32_t &depth) {
+    wide.clear(); depth = 0;
+    if (n == 0) return;
+    auto area = [&](uint32_t i) {
+        const nb_bvh_node &b = nodes[i];
+        const float dx = b.bmax[0] - b.bmin[0], dy = b.bmax[1] - b.bmin[1], dz = b.bmax[2] - b.bmin[2];
+        return dx * dy + dy * dz + dz * dx;
+    };
+    auto is_leaf = [&](uint32_t i) { return (nodes[i].word0 & 1u) != 0; };
+    struct Work { uint32_t bin, wide, level; };
+    std::vector<Work> todo;
+    auto new_node = [&]() {
+        const uint32_t w = (uint32_t) (wide.size() / 8);
+        wide.resize(wide.size() + 8, make_float4(0.f, 0.f, 0.f, 0.f));
+        for (int c = 0; c < 4; ++c) { const uint32_t e = NB_WIDE_EMPTY; memcpy(&wide[(size_t) w * 8 + 2 * c].x, &e, 4); }
+        return w;
+    };
+    auto put_child = [&](uint32_t w, int c, uint32_t bin, uint32_t ref) {
+        const nb_bvh_node &b = nodes[bin];
+        float4 A = make_float4(0.f, 0.f, b.bmin[0], b.bmin[1]);
+        memcpy(&A.x, &ref, 4);
+        wide[(size_t) w * 8 + 2 * c] = A;
+        wide[(size_t) w * 8 + 2 * c + 1] = make_float4(b.bmin[2], b.bmax[0], b.bmax[1], b.bmax[2]);
+    };
+    const uint32_t root = new_node();
+    if (is_leaf(0)) {                               /* a one-leaf tree: a wide root with that leaf as its only child */
+        if ((nodes[0].word0 >> 1) > 0) put_child(root, 0, 0, NB_WIDE_LEAF | nodes[0].word1);
+        depth = 1;
+        return;
+    }
+    todo.push_back({ 0u, root, 1u });
+    while (!todo.empty()) {
+        const Work wk = todo.back();
+        todo.pop_back();
+        depth = std::max(depth, wk.level);
+        uint32_t kids[4] = { wk.bin + 1, nodes[wk.bin].word1, 0, 0 };
+        int nk = 2;
+        while (nk < 4) {
+            int best = -1; float best_area = -1.f;
+            for (int k = 0; k < nk; ++k)
+                if (!is_leaf(kids[k]) && area(kids[k]) > best_area) { best = k; best_area = area(kids[k]); }
+            if (best < 0) break;
+            const uint32_t b = kids[best];
+            kids[best] = b + 1;
+            kids[nk++] = nodes[b].word1;
+        }
+        /* children that are inner nodes get their wide node now, in reverse so that the first is processed first */
+        uint32_t refs[4];
+        for (int k = 0; k < nk; ++k) {
+            if (is_leaf(kids[k])) refs[k] = (nodes[kids[k]].word0 >> 1) ? (NB_WIDE_LEAF | nodes[kids[k]].word1) : NB_WIDE_EMPTY;
+            else refs[k] = new_node();
+        }
+        for (int k = nk - 1; k >= 0; --k)
+            if (!is_leaf(kids[k])) todo.push_back({ kids[k], refs[k], wk.level + 1 });
+        for (int k = 0; k < nk; ++k)
+            if (refs[k] != NB_WIDE_EMPTY) put_child(wk.wide, k, kids[k], refs[k]);
+    }
+}
+
+/* which traversal the render kernels use for this tree */
+void nb_update_wide(nb_ctx *ctx) {
+    const bool fits = ctx->dev.wide && ctx->dev.n_wide && 3u * ctx->wide_depth + 1u <= NB_WIDE_STACK;
+    ctx->dev.use_wide = (ctx->opt_wide && fits) ? 1u : 0u;
+}
+
 extern "C" {
 
 /* Re-encodes BVH::m_nodes / m_indices (include/nori/bvh.h:127-164) into the stackless device
@@ -106,9 +175,15 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
         nodes[(size_t) i * 2] = A; nodes[(size_t) i * 2 + 1] = B;
     }
 
+    /* production tree: the same binary tree collapsed to 4-wide nodes (nb_internal.h, NB_WIDE_*) */
+    std::vector<float4> wide;
+    uint32_t wide_depth = 0;
+    nb_collapse_wide(imp->nodes, n, wide, wide_depth);
+
     { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }     /* queued subframes still walk the old tree */
     ctx->bvh_ready = false;                      /* a failure below must not leave a context pointing at freed memory */
     ctx->dev.nodes = nullptr; ctx->dev.slots = nullptr; ctx->dev.n_nodes = 0; ctx->dev.n_slots = 0;
+    ctx->dev.wide = nullptr; ctx->dev.n_wide = 0; ctx->dev.use_wide = 0;
     for (void *p : ctx->bvh_allocs) cudaFree(p);
     ctx->bvh_allocs.clear();
     void *dn = nullptr, *ds = nullptr;
@@ -116,11 +191,18 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     ctx->bvh_allocs.push_back(dn);
     NB_CUDA(ctx, cudaMalloc(&ds, std::max<size_t>(slots.size(), 1) * sizeof(float4)));
     ctx->bvh_allocs.push_back(ds);
+    void *dw = nullptr;
+    NB_CUDA(ctx, cudaMalloc(&dw, std::max<size_t>(wide.size(), 1) * sizeof(float4)));
+    ctx->bvh_allocs.push_back(dw);
+    NB_CUDA(ctx, cudaMemcpyAsync(dw, wide.data(), wide.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
     NB_CUDA(ctx, cudaMemcpyAsync(dn, nodes.data(), nodes.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
     NB_CUDA(ctx, cudaMemcpyAsync(ds, slots.data(), slots.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream));
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->dev.nodes = (const float4 *) dn; ctx->dev.slots = (const float4 *) ds;
     ctx->dev.n_nodes = n; ctx->dev.n_slots = ni;
+    ctx->dev.wide = (const float4 *) dw; ctx->dev.n_wide = (uint32_t) (wide.size() / 8);
+    ctx->wide_depth = wide_depth;
+    nb_update_wide(ctx);
     /* the flat scan tests slots 0..n-1 in order; that is the walk's order only when the caller's leaves come in
      * increasing index order (true of BVH::build's output; a foreign tree that breaks it is walked instead) */
     ctx->flat_ok = leaves_in_order;
@@ -159,7 +241,9 @@ int nb_trace_rays(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_hit, nb_h
         rc = nb_fail(ctx, NB_E_NOMEM, "nb_trace_rays: %s", cudaGetErrorString(e));
     } else {
         cudaMemcpyAsync(d_rays, packed.data(), packed.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream);
-        nb_launch_trace_hits(ctx->dev, d_rays, n, any_hit, d_out, d_any, ctx->sm_count, ctx->stream);
+        NbDeviceScene sc = ctx->dev;               /* the parity entry walks in the reference's order unless "trace_wide" asks for the production tree */
+        sc.use_wide = (ctx->opt_trace_wide && sc.wide) ? 1u : 0u;
+        nb_launch_trace_hits(sc, d_rays, n, any_hit, d_out, d_any, ctx->sm_count, ctx->stream);
         cudaMemcpyAsync(h_out.data(), d_out, (size_t) n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream);
         if (any_hit) cudaMemcpyAsync(h_any.data(), d_any, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream);
         e = cudaStreamSynchronize(ctx->stream);
@@ -191,8 +275,10 @@ int nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int a
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, ctx->stream);
+    NbDeviceScene sc = ctx->dev;
+    sc.use_wide = (ctx->opt_trace_wide && sc.wide) ? 1u : 0u;
     for (int r = 0; r < repeats; ++r)
-        nb_launch_trace_hits(ctx->dev, (const float4 *) rays_device, n, any_hit, (float4 *) out_device, d_any, ctx->sm_count, ctx->stream);
+        nb_launch_trace_hits(sc, (const float4 *) rays_device, n, any_hit, (float4 *) out_device, d_any, ctx->sm_count, ctx->stream);
     cudaEventRecord(e1, ctx->stream);
     cudaError_t e = cudaEventSynchronize(e1);
     if (e == cudaSuccess) e = cudaGetLastError();

@@ -262,8 +262,8 @@ int nb_build_bvh_device(nb_ctx *ctx) {
     uint32_t *d_leaf_last = (uint32_t *) alloc((size_t) n * 4), *d_nkept = (uint32_t *) alloc(4);
     uint32_t *d_slot_tag = (uint32_t *) alloc((size_t) n * 4), *d_slot_prim = (uint32_t *) alloc((size_t) n * 4);
     void *d_sort_tmp = nullptr; size_t sort_bytes = 0, sort_bytes2 = 0;
-    float4 *d_nodes = nullptr, *d_slots = nullptr;
-    uint32_t n_kept = 0;
+    float4 *d_nodes = nullptr, *d_slots = nullptr, *d_wide = nullptr;
+    uint32_t n_kept = 0, n_wide = 0;
     const unsigned B = 256;
     if (!d_off || !d_prims || !d_cb || !d_keys || !d_keys2 || !d_ids || !d_ids2 || !d_order || !d_left || !d_right || !d_first || !d_last ||
         !d_parent || !d_visits || !d_bmin || !d_bmax || !d_leaf_last || !d_nkept || !d_slot_tag || !d_slot_prim) {
@@ -314,18 +314,45 @@ int nb_build_bvh_device(nb_ctx *ctx) {
         cudaEventElapsedTime(&ms, e0, e1);
         ctx->bvh_build_ms = ms;
     }
+    /* production tree: collapse the tree just built (host side for now: nodes come back once, 32 B each) */
+    {
+        std::vector<float4> h_nodes((size_t) n_kept * 2);
+        NB_TRY(cudaMemcpyAsync(h_nodes.data(), d_nodes, h_nodes.size() * sizeof(float4), cudaMemcpyDeviceToHost, st));
+        NB_TRY(cudaStreamSynchronize(st));
+        std::vector<nb_bvh_node> bin(n_kept);
+        for (uint32_t i = 0; i < n_kept; ++i) {
+            const float4 A = h_nodes[2 * (size_t) i], B = h_nodes[2 * (size_t) i + 1];
+            uint32_t w1; memcpy(&w1, &A.y, 4);
+            nb_bvh_node &b = bin[i];
+            if (w1 & NB_NODE_INNER_BIT) { b.word0 = 0u; b.word1 = w1 & NB_NODE_RIGHT_MASK; }
+            else { b.word0 = 1u | ((w1 == NB_NODE_EMPTY_LEAF ? 0u : 1u) << 1); b.word1 = w1; }   /* leaf size: only "empty or not" matters to the collapse */
+            b.bmin[0] = A.z; b.bmin[1] = A.w; b.bmin[2] = B.x; b.bmax[0] = B.y; b.bmax[1] = B.z; b.bmax[2] = B.w;
+        }
+        std::vector<float4> wide;
+        uint32_t wide_depth = 0;
+        nb_collapse_wide(bin.data(), n_kept, wide, wide_depth);
+        NB_TRY(cudaMalloc((void **) &d_wide, std::max<size_t>(wide.size(), 1) * sizeof(float4)));
+        NB_TRY(cudaMemcpyAsync(d_wide, wide.data(), wide.size() * sizeof(float4), cudaMemcpyHostToDevice, st));
+        NB_TRY(cudaStreamSynchronize(st));
+        n_wide = (uint32_t) (wide.size() / 8);
+        ctx->wide_depth = wide_depth;
+    }
     for (void *p : ctx->bvh_allocs) cudaFree(p);
     ctx->bvh_allocs.clear();
-    ctx->bvh_allocs.push_back(d_nodes); ctx->bvh_allocs.push_back(d_slots);
+    ctx->bvh_allocs.push_back(d_nodes); ctx->bvh_allocs.push_back(d_slots); ctx->bvh_allocs.push_back(d_wide);
+    ctx->dev.wide = d_wide; ctx->dev.n_wide = n_wide;
+    d_wide = nullptr;
     ctx->dev.nodes = d_nodes; ctx->dev.slots = d_slots;
     ctx->dev.n_nodes = n_kept; ctx->dev.n_slots = n;
     ctx->flat_ok = true;                         /* slots are emitted in the pre-order of the leaves */
     ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;
+    nb_update_wide(ctx);
     d_nodes = nullptr; d_slots = nullptr;
     ctx->bvh_ready = true;
 done:
     if (d_nodes) cudaFree(d_nodes);
     if (d_slots) cudaFree(d_slots);
+    if (d_wide) cudaFree(d_wide);
     for (void *p : tmp) cudaFree(p);
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);

@@ -39,6 +39,18 @@ __host__ __device__ inline uint32_t nb_inner_word(uint32_t right, const float lm
     return NB_NODE_INNER_BIT | ((uint32_t) axis << 29) | (left_upper ? (1u << 28) : 0u) | (right & NB_NODE_RIGHT_MASK);
 }
 #define NB_FLAT_MAX_SLOTS 24u
+/* ---- production tree (not the reference's layout) ----------------------------------
+ * The binary tree collapsed to 4-wide nodes on the host (greedy by surface area). A wide node is 4 child records of
+ * 32 B = 128 B; child record c at float4 [8 * node + 2 * c]:
+ *   A = { bits(ref), 0, bmin.x, bmin.y }   B = { bmin.z, bmax.xyz }       (the binary node's own fp32 box)
+ *   ref: NB_WIDE_EMPTY = no child; bit 31 set = leaf, low bits = its first primitive slot (the leaf ends at the slot
+ *   tagged NB_SLOT_LAST, as in the binary tree — slots stay in the reference's m_indices order, which is what the
+ *   exact-t tie rule needs); else the index of the child wide node.
+ * Traversal is near-first with a short stack of (ref, entry distance), so the closest hit shrinks the ray early and
+ * whole subtrees are culled when popped; per ray it touches ~3x fewer nodes than the reference's left-first order. */
+#define NB_WIDE_LEAF 0x80000000u
+#define NB_WIDE_EMPTY 0xffffffffu
+#define NB_WIDE_STACK 64u               /* entries a ray may hold; trees deeper than (NB_WIDE_STACK - 1) / 3 levels keep the binary walk */
 
 struct NbDeviceScene {
     const float4 *nodes = nullptr;      /* 2 per node */
@@ -46,6 +58,9 @@ struct NbDeviceScene {
     uint32_t n_nodes = 0, n_slots = 0;
     uint32_t flat = 0;                  /* queries scan the slots instead of walking the tree (nb_trace.cuh) */
     uint32_t ordered = 0;               /* nb_trace_rays walks near child first (nb_traverse_ordered) instead of left first */
+    const float4 *wide = nullptr;       /* production tree: 4-wide nodes collapsed from the binary tree (8 float4 per node, see NB_WIDE_*) */
+    uint32_t n_wide = 0;
+    uint32_t use_wide = 0;              /* queries walk the wide tree near-first (nb_traverse_wide) — the production mode; 0 = the reference's order */
     uint32_t ext = 0;                   /* scene uses textures, normal maps, an environment map, a heterogeneous medium, the disney BSDF or a spot / directional light: the EXT kernel variants render it */
     /* shading data */
     const nb_shape *shapes = nullptr;
@@ -86,6 +101,9 @@ struct nb_ctx {
     int opt_profile = 0, opt_sort = 0, opt_strategy = 0;
     int opt_walk = 1;                   /* tree scenes: K_tile_walk (per-lane state machine) instead of lock-step K_tile */
     int opt_ordered = 0;                /* 1: nb_trace_rays uses the near-child-first walk */
+    int opt_trace_wide = 0;             /* 1: nb_trace_rays answers through the wide tree too (to measure its hit parity) */
+    int opt_wide = 1;                   /* 1: tree scenes are traversed through the wide tree (production); 0: the reference's order (parity mode) */
+    uint32_t wide_depth = 0;            /* levels of the wide tree */
     int opt_flat = -1;                  /* -1: flat scan iff the scene has at most NB_FLAT_MAX_SLOTS primitives */
     bool flat_ok = true;                /* leaves of the imported tree cover the slot list in pre-order: the flat scan visits what the walk visits */
     /* multi-GPU film reduce (nb_comm.cu): one NCCL communicator per context */
@@ -117,6 +135,10 @@ int nb_render_film(nb_ctx *ctx, float **data, float **normal, uint64_t *n_floats
 
 /* nb_comm.cu */
 void nb_comm_free(nb_ctx *ctx);
+
+/* nb_bvh.cu */
+void nb_collapse_wide(const nb_bvh_node *nodes, uint32_t n, std::vector<float4> &wide, uint32_t &depth);
+void nb_update_wide(nb_ctx *ctx);
 
 /* nb_bvh_build.cu */
 int nb_build_bvh_device(nb_ctx *ctx);

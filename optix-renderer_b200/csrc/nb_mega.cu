@@ -587,10 +587,28 @@ enum { NB_PH_IDLE = 0, NB_PH_REGEN = 1, NB_PH_NODE = 2, NB_PH_LEAF = 3, NB_PH_TD
 enum { NB_W_LI = 0, NB_W_THR = 3, NB_W_O = 6, NB_W_D = 9, NB_W_MINT = 12, NB_W_MAXT = 13, NB_W_WMATS = 14, NB_W_WEMS = 15,
        NB_W_PDFMAT = 16, NB_W_PX = 17, NB_W_PY = 18, NB_W_FLAGS = 19, NB_W_RNG = 20, NB_W_SC = 24, NB_W_CAND = 27, NB_W_WORDS = 28 };
 
-template <bool MIS, bool EXT>
-__global__ void __launch_bounds__(NB_TILE_THREADS, EXT ? NB_WALK_MIN_BLOCKS_EXT : NB_WALK_MIN_BLOCKS)
+/* WIDE: the production tree (nb_internal.h NB_WIDE_*, nb_traverse_wide): a NODE step tests the four children of one
+ * 128-byte node, continues into the nearest and parks the others, with their entry distances, on a per-lane stack —
+ * its first NB_WSTK_SHARED entries in shared memory (one 8-byte column per lane, conflict-free), the rare deeper ones
+ * in local memory; a popped entry farther than the current hit is dropped without being fetched. */
+#ifndef NB_WSTK_SHARED
+#define NB_WSTK_SHARED 12
+#endif
+#ifndef NB_WALK_NODE_STEPS_WIDE
+#define NB_WALK_NODE_STEPS_WIDE 4
+#endif
+#ifndef NB_WALK_MIN_BLOCKS_WIDE
+#define NB_WALK_MIN_BLOCKS_WIDE 7
+#endif
+template <bool MIS, bool EXT, bool WIDE>
+__global__ void __launch_bounds__(NB_TILE_THREADS, EXT ? NB_WALK_MIN_BLOCKS_EXT : (WIDE ? NB_WALK_MIN_BLOCKS_WIDE : NB_WALK_MIN_BLOCKS))
 nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
     __shared__ float park[NB_W_WORDS][NB_TILE_THREADS];
+    __shared__ uint2 wstk[WIDE ? NB_WSTK_SHARED : 1][NB_TILE_THREADS];
+    uint2 wovf[WIDE ? NB_WIDE_STACK - NB_WSTK_SHARED : 1];
+    uint32_t sp = 0;
+    NbWideRay wr;
+    wr.r = make_float3(0.f, 0.f, 0.f); wr.o = wr.r;
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     uint32_t n_closest = 0, n_any = 0, n_samples = 0;
@@ -637,12 +655,36 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
             mint = (mint < e) ? e : mint;
         }
         tmint = mint; tmaxt = maxt;
-        tr = make_float3(__fdiv_rn(1.0f, d.x), __fdiv_rn(1.0f, d.y), __fdiv_rn(1.0f, d.z));
-        idx = (sc.n_nodes == 0 || maxt < mint) ? NB_NODE_END : 0u;
+        if constexpr (WIDE) {
+            wr = nb_wide_ray(o, d);
+            sp = 0;
+            idx = (sc.n_wide == 0 || maxt < mint) ? NB_NODE_END : 0u;
+        } else {
+            tr = make_float3(__fdiv_rn(1.0f, d.x), __fdiv_rn(1.0f, d.y), __fdiv_rn(1.0f, d.z));
+            idx = (sc.n_nodes == 0 || maxt < mint) ? NB_NODE_END : 0u;
+        }
         phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
         if (any_hit) ++n_any; else ++n_closest;
     };
     auto walk_main = [&]() { begin_walk(ld3p(NB_W_O), ld3p(NB_W_D), park[NB_W_MINT][tid], park[NB_W_MAXT][tid], false); };
+    auto wpush = [&](uint32_t ref, float t) {
+        const uint2 e = make_uint2(ref, __float_as_uint(t));
+        if (sp < NB_WSTK_SHARED) wstk[sp][tid] = e; else wovf[sp - NB_WSTK_SHARED] = e;
+        ++sp;
+    };
+    /* next stack entry the ray can still reach; sets the lane's phase (NODE at an inner node, LEAF at a leaf, TDONE when none is left) */
+    auto wnext = [&]() {
+        phase = NB_PH_TDONE;
+        while (sp) {
+            --sp;
+            const uint2 e = sp < NB_WSTK_SHARED ? wstk[sp][tid] : wovf[sp - NB_WSTK_SHARED];
+            if (__uint_as_float(e.y) <= tmaxt) {
+                if (e.x & NB_WIDE_LEAF) { leaf = e.x & ~NB_WIDE_LEAF; phase = NB_PH_LEAF; }
+                else { idx = e.x; phase = NB_PH_NODE; }
+                break;
+            }
+        }
+    };
 
     for (;;) {
         const uint32_t m_walking = __ballot_sync(0xffffffffu, phase == NB_PH_NODE || phase == NB_PH_LEAF || phase == NB_PH_TDONE);
@@ -669,7 +711,20 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
 
         /* ---- NODE: inner-node steps until the lane stands on a leaf or its walk ends ---- */
 #pragma unroll 1
-        for (int step = 0; step < NB_WALK_NODE_STEPS; ++step) {
+        for (int step = 0; step < (WIDE ? NB_WALK_NODE_STEPS_WIDE : NB_WALK_NODE_STEPS); ++step) {
+            if constexpr (WIDE) {
+                if (phase == NB_PH_NODE) {
+                    float t4[4]; uint32_t r4[4];
+                    const int n = nb_wide_children(sc.wide + 8 * (size_t) idx, wr, tmint, tmaxt, t4, r4);
+                    if (n > 3) wpush(r4[3], t4[3]);
+                    if (n > 2) wpush(r4[2], t4[2]);
+                    if (n > 1) wpush(r4[1], t4[1]);
+                    if (n > 0) {
+                        if (r4[0] & NB_WIDE_LEAF) { leaf = r4[0] & ~NB_WIDE_LEAF; phase = NB_PH_LEAF; }
+                        else idx = r4[0];
+                    } else wnext();
+                }
+            } else
             if (phase == NB_PH_NODE) {
                 const float4 A = __ldg(sc.nodes + 2 * idx), B = __ldg(sc.nodes + 2 * idx + 1);
                 const uint32_t skip = __float_as_uint(A.x), start = __float_as_uint(A.y);
@@ -698,14 +753,21 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
                                                            : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t);
                     if (ok) {
                         if (t_any) { occluded = true; break; }
-                        tmaxt = t;
-                        hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                        /* the wide walk meets primitives out of slot order: an exact-t tie keeps the later slot, as the reference's order does */
+                        if (!WIDE || !(hit.slot != 0xffffffffu && t == hit.t && s < hit.slot)) {
+                            tmaxt = t;
+                            hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                        }
                     }
                     if (tag & NB_SLOT_LAST) break;
                     ++s;
                 }
-                idx = occluded ? NB_NODE_END : after;
-                phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
+                if constexpr (WIDE) {
+                    if (occluded) phase = NB_PH_TDONE; else wnext();
+                } else {
+                    idx = occluded ? NB_NODE_END : after;
+                    phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
+                }
             }
         }
         /* ---- TDONE: a walk ended. Shadow ray: add its contribution, go on to the main ray
@@ -754,18 +816,18 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
     }
 }
 
-template <bool MIS, bool EXT>
+template <bool MIS, bool EXT, bool WIDE>
 static cudaError_t nb_tile_launch_walk(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
                                        unsigned long long *stats, int sm_count, cudaStream_t stream) {
     int per_sm = 0;
-    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile_walk<MIS, EXT>, NB_TILE_THREADS, 0);
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, nb_k_tile_walk<MIS, EXT, WIDE>, NB_TILE_THREADS, 0);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) per_sm = 1;
     uint64_t blocks = (uint64_t) sm_count * per_sm;
     const uint64_t blocks_useful = ((uint64_t) tp.n_items + NB_TILE_THREADS / 32 - 1) / (NB_TILE_THREADS / 32);
     if (blocks > blocks_useful) blocks = blocks_useful;
     if (blocks < 1) blocks = 1;
-    nb_k_tile_walk<MIS, EXT><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
+    nb_k_tile_walk<MIS, EXT, WIDE><<<(unsigned) blocks, NB_TILE_THREADS, 0, stream>>>(sc, film, tp, item_counter, stats);
     return cudaGetLastError();
 }
 
@@ -829,12 +891,17 @@ cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const Nb
     cudaError_t e = cudaMemsetAsync(item_counter, 0, sizeof(uint32_t), stream);
     if (e != cudaSuccess) return e;
     if (walking) {
-        if (integrator == NB_INTEGRATOR_PATH_MIS)
-            return sc.ext ? nb_tile_launch_walk<true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
-                          : nb_tile_launch_walk<true, false>(sc, film, tp, item_counter, stats, sm_count, stream);
-        if (integrator == NB_INTEGRATOR_PATH_MATS)
-            return sc.ext ? nb_tile_launch_walk<false, true>(sc, film, tp, item_counter, stats, sm_count, stream)
-                          : nb_tile_launch_walk<false, false>(sc, film, tp, item_counter, stats, sm_count, stream);
+        const bool mis = integrator == NB_INTEGRATOR_PATH_MIS;
+        if (sc.use_wide) {
+            if (mis) return sc.ext ? nb_tile_launch_walk<true, true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
+                                   : nb_tile_launch_walk<true, false, true>(sc, film, tp, item_counter, stats, sm_count, stream);
+            return sc.ext ? nb_tile_launch_walk<false, true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
+                          : nb_tile_launch_walk<false, false, true>(sc, film, tp, item_counter, stats, sm_count, stream);
+        }
+        if (mis) return sc.ext ? nb_tile_launch_walk<true, true, false>(sc, film, tp, item_counter, stats, sm_count, stream)
+                               : nb_tile_launch_walk<true, false, false>(sc, film, tp, item_counter, stats, sm_count, stream);
+        return sc.ext ? nb_tile_launch_walk<false, true, false>(sc, film, tp, item_counter, stats, sm_count, stream)
+                      : nb_tile_launch_walk<false, false, false>(sc, film, tp, item_counter, stats, sm_count, stream);
     }
     switch (integrator) {
         case NB_INTEGRATOR_PATH_MIS: return nb_tile_launch_t<NB_INTEGRATOR_PATH_MIS>(sc, film, tp, item_counter, stats, sm_count, stream);

@@ -126,3 +126,29 @@ extern "C" int nb_bsdf_probe(nb_ctx *ctx, uint32_t bsdf, const float *in, uint64
     if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_bsdf_probe: %s", cudaGetErrorString(e));
     return NB_OK;
 }
+
+/* ---- pcg32 parity entry (ext/pcg32/pcg32.h:51-66, 101-110): the DEVICE generator's stream, word for word ---- */
+__global__ void nb_k_rng_probe(unsigned long long initstate, unsigned long long initseq, uint32_t n, uint32_t *out_u, float *out_f) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    NbRng a; a.seed(initstate, initseq);
+    for (uint32_t i = 0; i < n; ++i) out_u[i] = a.next_uint();
+    NbRng b; b.seed(initstate, initseq);
+    for (uint32_t i = 0; i < n; ++i) out_f[i] = b.next_float();
+}
+
+extern "C" int nb_rng_probe(nb_ctx *ctx, uint64_t initstate, uint64_t initseq, uint32_t n, uint32_t *out_u32, float *out_f32) {
+    if (!ctx) return NB_E_INVALID;
+    if (n == 0) return NB_OK;
+    if (!out_u32 || !out_f32) return nb_fail(ctx, NB_E_INVALID, "nb_rng_probe: null argument");
+    if (n > (1u << 20)) return nb_fail(ctx, NB_E_INVALID, "nb_rng_probe: at most 2^20 values per call");
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t *d = nullptr;
+    NB_CUDA(ctx, cudaMalloc((void **) &d, (size_t) n * 8));
+    nb_k_rng_probe<<<1, 32, 0, ctx->stream>>>(initstate, initseq, n, d, (float *) (d + n));
+    cudaError_t e = cudaMemcpyAsync(out_u32, d, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_f32, d + n, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_rng_probe: %s", cudaGetErrorString(e));
+    return NB_OK;
+}

@@ -21,6 +21,23 @@ nb_k_trace_hits(const float4 *__restrict__ nodes, const float4 *__restrict__ slo
     }
 }
 
+/* the same entry through the production tree (nb_traverse_wide) */
+__global__ void __launch_bounds__(256)
+nb_k_trace_hits_wide(const float4 *__restrict__ wide, const float4 *__restrict__ slots, uint32_t n_wide,
+                     const float4 *__restrict__ rays, uint64_t n, int any_hit, float4 *__restrict__ out, uint32_t *__restrict__ out_any) {
+    for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
+        const float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
+        const float3 o = make_float3(ro.x, ro.y, ro.z), d = make_float3(rd.x, rd.y, rd.z);
+        NbHit hit;
+        nb_traverse_wide<false>(wide, slots, n_wide, o, d, ro.w, rd.w, hit);
+        out[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot));
+        if (any_hit) {
+            NbHit dummy;
+            out_any[i] = nb_traverse_wide<true>(wide, slots, n_wide, o, d, ro.w, rd.w, dummy) ? 1u : 0u;
+        }
+    }
+}
+
 void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64_t n, int any_hit,
                           float4 *out, uint32_t *out_any, int sm_count, cudaStream_t stream) {
     if (n == 0) return;
@@ -30,6 +47,8 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
     if (scene.flat)
         nb_k_trace_hits<true><<<(unsigned) blocks, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, rays, n,
                                                                      any_hit, false, out, out_any);
+    else if (scene.use_wide && scene.wide && !scene.ordered)
+        nb_k_trace_hits_wide<<<(unsigned) blocks, 256, 0, stream>>>(scene.wide, scene.slots, scene.n_wide, rays, n, any_hit, out, out_any);
     else
         nb_k_trace_hits<false><<<(unsigned) blocks, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, rays, n,
                                                                       any_hit, scene.ordered != 0, out, out_any);

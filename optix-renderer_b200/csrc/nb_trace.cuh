@@ -219,6 +219,110 @@ __device__ __forceinline__ bool nb_traverse_ordered(const float4 *__restrict__ n
     return found;
 }
 
+/* ---- production traversal: 4-wide tree, near-first (layout: nb_internal.h, NB_WIDE_*) ---------------------------
+ * Only the ORDER of visits and the box arithmetic differ from the reference; every primitive test is the bit-exact
+ * nb_tri_hit / nb_sphere_hit above and ties in t are resolved by leaf-order slot as in nb_traverse_ordered, so a ray
+ * reports the reference's (primitive, t, u, v) unless a box test decides differently within its rounding (measured:
+ * tests/test_wide_gpu.py). The slab test is the usual fma form on precomputed o/d with a 4-ulp safety margin instead
+ * of the reference's exact comparisons; a zero direction component becomes a huge finite reciprocal. */
+struct NbWideRay { float3 r, o; };
+__device__ __forceinline__ NbWideRay nb_wide_ray(float3 o, float3 d) {
+    NbWideRay w;
+    w.r = make_float3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    if (!(fabsf(w.r.x) < 1e30f)) w.r.x = copysignf(1e30f, d.x);
+    if (!(fabsf(w.r.y) < 1e30f)) w.r.y = copysignf(1e30f, d.y);
+    if (!(fabsf(w.r.z) < 1e30f)) w.r.z = copysignf(1e30f, d.z);
+    w.o = o;
+    return w;
+}
+/* (plane - o) * (1 / d), the subtraction first: for a ray that starts on or next to a flat box (a wall, the quad light)
+ * the difference is exact, where fma(plane, r, -(o * r)) would cancel two large products and be off by the hit
+ * distance itself (measured: 6 grazing rays in 10^6 on the Cornell box lost their hit with that form) */
+__device__ __forceinline__ bool nb_box_fast(const float4 A, const float4 B, const NbWideRay &w, float mint, float maxt, float &tn) {
+    float t1 = (A.z - w.o.x) * w.r.x, t2 = (B.y - w.o.x) * w.r.x;
+    float tnear = fminf(t1, t2), tfar = fmaxf(t1, t2);
+    t1 = (A.w - w.o.y) * w.r.y; t2 = (B.z - w.o.y) * w.r.y;
+    tnear = fmaxf(tnear, fminf(t1, t2)); tfar = fminf(tfar, fmaxf(t1, t2));
+    t1 = (B.x - w.o.z) * w.r.z; t2 = (B.w - w.o.z) * w.r.z;
+    tnear = fmaxf(tnear, fminf(t1, t2)); tfar = fminf(tfar, fmaxf(t1, t2));
+    tfar *= 1.0000005f;                              /* conservative: a primitive on a box face must not be lost to rounding */
+    tn = tnear * 0.9999995f;
+    return tn <= tfar && mint <= tfar && tn <= maxt;
+}
+/* the four children of one wide node: tests them, sorts the hit ones by entry distance (nearest first) */
+__device__ __forceinline__ int nb_wide_children(const float4 *__restrict__ node, const NbWideRay &w, float mint, float maxt,
+                                                float (&t)[4], uint32_t (&ref)[4]) {
+    int n = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const float4 A = __ldg(node + 2 * c), B = __ldg(node + 2 * c + 1);
+        const uint32_t rf = __float_as_uint(A.x);
+        float tn;
+        const bool ok = rf != NB_WIDE_EMPTY && nb_box_fast(A, B, w, mint, maxt, tn);
+        t[c] = ok ? tn : INFINITY; ref[c] = rf;
+        n += ok ? 1 : 0;
+    }
+#define NB_CSWAP(a, b) { const bool sw = t[b] < t[a]; const float ta = sw ? t[b] : t[a], tb = sw ? t[a] : t[b]; \
+                         const uint32_t ra = sw ? ref[b] : ref[a], rb = sw ? ref[a] : ref[b]; t[a] = ta; t[b] = tb; ref[a] = ra; ref[b] = rb; }
+    NB_CSWAP(0, 1) NB_CSWAP(2, 3) NB_CSWAP(0, 2) NB_CSWAP(1, 3) NB_CSWAP(1, 2)
+#undef NB_CSWAP
+    return n;
+}
+
+template <bool ANY>
+__device__ __forceinline__ bool nb_traverse_wide(const float4 *__restrict__ wide, const float4 *__restrict__ slots, uint32_t n_wide,
+                                                 float3 o, float3 d, float mint, float maxt, NbHit &hit) {
+    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
+    if (mint == NB_EPSILON) {                       /* adaptive ray epsilon, bvh.cpp:409-410 */
+        float m = fabsf(o.x);
+        m = fmaxf(m, fabsf(o.y));
+        m = fmaxf(m, fabsf(o.z));
+        const float s = __fmul_rn(mint, m);
+        mint = (mint < s) ? s : mint;
+    }
+    if (n_wide == 0 || maxt < mint) return false;
+    const NbWideRay w = nb_wide_ray(o, d);
+    uint2 stk[NB_WIDE_STACK];
+    uint32_t sp = 0, cur = 0;
+    bool found = false;
+    while (true) {
+        if (!(cur & NB_WIDE_LEAF)) {
+            float t[4]; uint32_t ref[4];
+            const int n = nb_wide_children(wide + 8 * (size_t) cur, w, mint, maxt, t, ref);
+            if (n > 3) stk[sp++] = make_uint2(ref[3], __float_as_uint(t[3]));
+            if (n > 2) stk[sp++] = make_uint2(ref[2], __float_as_uint(t[2]));
+            if (n > 1) stk[sp++] = make_uint2(ref[1], __float_as_uint(t[1]));
+            if (n > 0) { cur = ref[0]; continue; }
+        } else {
+            uint32_t s = cur & ~NB_WIDE_LEAF;
+            while (true) {
+                const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
+                const uint32_t tag = __float_as_uint(s2.y);
+                float u = 0.f, v = 0.f, t;
+                const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
+                                                       : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+                if (ok) {
+                    if (ANY) return true;
+                    if (!(found && t == hit.t && s < hit.slot)) {      /* exact-t tie: the later slot wins, as in the reference's order */
+                        found = true;
+                        maxt = t;
+                        hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                    }
+                }
+                if (tag & NB_SLOT_LAST) break;
+                ++s;
+            }
+        }
+        bool got = false;
+        while (sp) {
+            const uint2 e = stk[--sp];
+            if (__uint_as_float(e.y) <= maxt) { cur = e.x; got = true; break; }
+        }
+        if (!got) break;
+    }
+    return found;
+}
+
 /* Flat scan for scenes of a few primitives (the Cornell box has 14): test every slot in leaf
  * order, no tree. The reference's left-first walk also visits leaves in exactly this order and
  * only skips primitives whose node box the ray misses within [mint, current maxt] — primitives
@@ -254,11 +358,12 @@ __device__ __forceinline__ bool nb_scan(const float4 *__restrict__ slots, uint32
     return found;
 }
 
-/* The query the render kernels use: tree walk, or flat scan when the scene qualifies. */
+/* The query the render kernels use: flat scan when the scene qualifies, else the tree in the order `mode` names. */
+enum { NB_TRAV_REFERENCE = 0, NB_TRAV_ORDERED = 1, NB_TRAV_WIDE = 2 };
 template <bool ANY, bool FLAT>
 __device__ __forceinline__ bool nb_query(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes,
-                                         uint32_t n_slots, float3 o, float3 d, float mint, float maxt, NbHit &hit, bool ordered = false) {
+                                         uint32_t n_slots, float3 o, float3 d, float mint, float maxt, NbHit &hit, int mode = NB_TRAV_REFERENCE) {
     if (FLAT) return nb_scan<ANY>(slots, n_slots, o, d, mint, maxt, hit);
-    if (ordered) return nb_traverse_ordered<ANY>(nodes, slots, n_nodes, o, d, mint, maxt, hit);
+    if (mode == NB_TRAV_ORDERED) return nb_traverse_ordered<ANY>(nodes, slots, n_nodes, o, d, mint, maxt, hit);
     return nb_traverse<ANY>(nodes, slots, n_nodes, o, d, mint, maxt, hit);
 }

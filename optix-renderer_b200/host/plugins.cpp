@@ -420,7 +420,7 @@ public:
 private:
     float m_g, m_k;
 };
-NORI_REGISTER_CLASS(SchlickPhase, "schlickphase")
+NORI_REGISTER_CLASS(SchlickPhase, "schlick")          /* the reference's name (schlickphase.cpp:81) */
 
 /* ---- media (src/media/medium.cpp, homogmedium.cpp, vacuum.cpp, heterogmedium.cpp) --------------------------- */
 Medium::Medium(const PropertyList &p) {             /* medium.cpp:10-17 + updateDerivedProperties :112-117 */

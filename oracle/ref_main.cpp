@@ -9,7 +9,9 @@
  * reference's unmodified code, compiled from /root/reference by oracle/Makefile.
  *
  * Modes (see usage()):
- *   render   scene.xml out.npy [spp=N] [threads=T] [film=raw.npy]
+ *   render   scene.xml out.npy [spp=N] [threads=T] [film=raw.npy] [split=K out2=b.npy [seg=M]]
+ *            (split: passes [0,K) go to out.npy, passes [K,spp) to out2 — independent renders of one run; with seg=M the
+ *            tail is cut into M-pass pieces written to b.npy.0, b.npy.1, ...)
  *   genrays  scene.xml rays.bin n_primary seed
  *   hits     scene.xml rays.bin hits.bin
  *   bvh      scene.xml bvh.bin
@@ -192,6 +194,17 @@ static int modeRender(int argc, char **argv) {
     const bool wantNormal = kv.count("normal") != 0;
     ImageBlock resultNormal(outputSize, camera->getReconstructionFilter());
     resultNormal.clear();
+    /* split=K: a second film takes the passes from K on. The per-block samplers run on through both parts, so the two
+     * images are renders of the SAME reference run over disjoint stretches of its random streams: independent, which
+     * two separate invocations (identical per-block seeds, independent.cpp:55-60) would not be. */
+    const int split = kv.count("split") ? std::stoi(kv["split"]) : spp;
+    const int seg = kv.count("seg") ? std::stoi(kv["seg"]) : std::max(1, spp - split);
+    const int nSeg = spp > split ? (spp - split + seg - 1) / seg : 0;
+    std::vector<std::unique_ptr<ImageBlock>> result2;
+    for (int i = 0; i < nSeg; ++i) {
+        result2.emplace_back(new ImageBlock(outputSize, camera->getReconstructionFilter()));
+        result2.back()->clear();
+    }
     const int blockSize = NORI_BLOCK_SIZE;
     BlockGenerator blockGenerator(outputSize, blockSize);
     Integrator *integrator = scene->getIntegrator(false);
@@ -223,7 +236,7 @@ static int modeRender(int argc, char **argv) {
                     samplers.at(blockId) = std::move(sampler);
                 }
                 renderBlockRef(scene, integrator, samplers.at(blockId).get(), block, wantNormal ? &blockN : nullptr);
-                result.put(block);
+                if (currentSample < split) result.put(block); else result2[(currentSample - split) / seg]->put(block);
                 if (wantNormal) resultNormal.put(blockN);
             }
             RayCounters &c = tlsCounters;
@@ -244,6 +257,11 @@ static int modeRender(int argc, char **argv) {
     if (wantNormal) {                           /* the Normal render layer (integrator.h:29-39), as toBitmap() gives it */
         std::unique_ptr<Bitmap> nb(resultNormal.toBitmap());
         writeNpy(kv["normal"], (const float *) nb->data(), { (size_t) outputSize.y(), (size_t) outputSize.x(), 3 });
+    }
+    for (int i = 0; kv.count("out2") && i < nSeg; ++i) {
+        std::unique_ptr<Bitmap> b2(result2[i]->toBitmap());
+        writeNpy(nSeg == 1 && !kv.count("seg") ? kv["out2"] : kv["out2"] + "." + std::to_string(i), (const float *) b2->data(),
+                 { (size_t) outputSize.y(), (size_t) outputSize.x(), 3 });
     }
     if (kv.count("film"))
         writeNpy(kv["film"], (const float *) result.data(), { (size_t) result.rows(), (size_t) result.cols(), 4 });

@@ -47,6 +47,8 @@ def ctx(_session_ctx):
     _session_ctx.set_option("flat_scan", -1)
     _session_ctx.set_option("walk", 1)
     _session_ctx.set_option("ordered", 0)
+    _session_ctx.set_option("wide", 1)
+    _session_ctx.set_option("trace_wide", 0)
     return _session_ctx
 
 

@@ -114,3 +114,24 @@ def test_rank1_plugins_flatten(nb, built_lib):
     assert s["texels"].min() >= -1 and s["texels"].max() <= 1
     assert int(nb.load_xml(golden("scenes/plugins/av.xml"))["render"]["integrator"][0]) == nb.INTEGRATORS["av"]
     assert int(nb.load_xml(golden("scenes/plugins/preview.xml"))["render"]["integrator"][0]) == nb.INTEGRATORS["preview"]
+
+
+@pytest.mark.parametrize("name", ["mitchell", "tent", "box", "gaussian", "mitchell_bc"])
+def test_filter_tables_match_reference(nb, built_lib, name):
+    """ReconstructionFilter::eval tabulated by ImageBlock (block.cpp:58-64) for every filter of rfilter.cpp:41-163:
+    the host loader's table against the reference's own objects (nori_ref flat), bit for bit, radius included."""
+    got = nb.load_xml(golden("scenes/round2/filter_%s.xml" % name))
+    want = nb.read_nbs(golden("filter_%s.nbs" % name))
+    assert got["render"]["filter_radius"][0] == want["render"]["filter_radius"][0]
+    assert got["render"]["filter_table"].tobytes() == want["render"]["filter_table"].tobytes()
+    assert want["render"]["filter_table"][0, 0] > 0 and (name == "box" or want["render"]["filter_table"][0, 0] != want["render"]["filter_table"][0, 16])
+    assert got["render"].tobytes() == want["render"].tobytes()
+
+
+def test_reference_plugin_names(nb, built_lib, tmp_path):
+    """Scenes name plugins by the reference's registration strings: `schlick` (schlickphase.cpp:81), `anisophase`,
+    `isophase`."""
+    s = nb.load_xml(golden("scenes/vol/cbox_homog_schlick_mats_small.xml"))
+    assert s["media"]["phase"][0] == nb.PHASE_SCHLICK
+    g = 0.7
+    assert abs(float(s["media"]["phase_param"][0]) - (1.55 * g - 0.55 * g ** 3)) < 1e-6

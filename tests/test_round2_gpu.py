@@ -1,0 +1,241 @@
+"""Parity pins added in round 2 (fixtures: tests/golden/make_round2.py): the branches of the product path that had no
+test — device pcg32 stream, mirror / dielectric / microfacet records, the reference's microfacet t-test answers, thin-lens
+camera, `direct` integrator, Schlick phase — plus the high-spp image gates of SURVEY 8(d) and the reference's own EXR
+goldens at their own size and spp."""
+import json
+import os
+
+import numpy as np
+import pytest
+from scipy import stats
+
+from conftest import golden, rel_rmse
+
+pytestmark = pytest.mark.gpu
+
+
+# ---- a34: the DEVICE pcg32 stream ------------------------------------------------------------------------------
+def test_device_pcg32_stream_is_the_reference_stream(nb, ctx):
+    demo = [int(x, 16) for x in open(golden("pcg32_demo_round1.txt")).read().split()]      # ext/pcg32/pcg32-demo.out, Round 1
+    assert demo[:2] == [0xa15c02b7, 0x7b47f409] and len(demo) == 6
+    kat = open(golden("rng_kat.txt")).read().split("\n")                                      # the oracle's 16-value streams
+    u, _ = ctx.rng_probe(42, 54, 16)
+    assert u[:6].tolist() == demo
+    assert u.tolist() == [int(x, 16) for x in kat[2].split()]
+    _, f = ctx.rng_probe(32, 64, 16)             # Independent::prepare(block at (32, 64)), nextFloat
+    assert f.tobytes() == np.array([float(x) for x in kat[1].split()], dtype="<f4").tobytes()
+    u2, f2 = ctx.rng_probe(42, 54, 4096)         # a long stream stays in [0, 1) and equals its own prefix
+    assert np.array_equal(u2[:16], u) and f2.min() >= 0.0 and f2.max() < 1.0
+
+
+# ---- a18 / a19 / a20: BSDF records against the reference's plugins -------------------------------------------
+BSDFS = [("mirror", "scenes/cbox/cbox_path_mis.xml", 3), ("dielectric", "scenes/cbox/cbox_path_mis.xml", 4),
+         ("microfacet_veach", "scenes/veach/veach_mis.xml", 4), ("microfacet_table", "scenes/table/table_path_mis.xml", 2)]
+
+
+@pytest.mark.parametrize("name,xml,shape", BSDFS)
+def test_bsdf_records_match_reference_plugin(nb, ctx, name, xml, shape):
+    s = nb.load_xml(golden(xml))
+    rec = np.fromfile(golden("bsdf_%s_in.bin" % name), "<f4").reshape(-1, 10)
+    want = np.fromfile(golden("bsdf_%s_out.bin" % name), "<f4").reshape(-1, 12)
+    ctx.load(s)
+    b = int(s["shapes"]["bsdf"][shape])
+    assert (int(s["bsdfs"]["type"][b]) & 0xff) == {"mirror": 1, "dielectric": 2}.get(name, 3)
+    got = ctx.bsdf_probe(b, rec)
+
+    def relerr(a, c):
+        return np.abs(a - c).max(axis=1) / np.maximum(np.abs(c).max(axis=1), 1e-3)
+    # a Fresnel coin (dielectric: sample.x < F) or lobe coin that lands within an ulp of its threshold may fall the
+    # other way under fast-math division: such a record differs wholesale; none or a handful in 6000 are allowed
+    sampled = (np.abs(want[:, 4:7]).max(axis=1) > 0) | (np.abs(got[:, 4:7]).max(axis=1) > 0)      # a rejected sample leaves bRec.wo unset
+    flipped = sampled & (np.abs(got[:, 7:10] - want[:, 7:10]).max(axis=1) > 1e-2)
+    assert flipped.sum() <= 3, flipped.sum()
+    ok = ~flipped
+    assert np.array_equal(got[ok, 10], want[ok, 10])                                  # measure
+    e_eval, e_pdf = relerr(got[:, 0:3], want[:, 0:3]), relerr(got[:, 3:4], want[:, 3:4])
+    e_w = relerr(got[ok, 4:7], want[ok, 4:7])
+    valid = ok & (np.abs(want[:, 4:7]).max(axis=1) > 0)                               # a rejected sample leaves bRec.wo unset
+    e_wo = np.abs(got[valid, 7:10] - want[valid, 7:10]).max(axis=1)
+    e_spdf = relerr(got[valid, 11:12], want[valid, 11:12])
+    print(name, "max rel err eval %.2e pdf %.2e weight %.2e wo %.2e sampled pdf %.2e; nonzero evals %d, discrete %d" % (
+        e_eval.max(), e_pdf.max(), e_w.max(), e_wo.max() if e_wo.size else 0, e_spdf.max() if e_spdf.size else 0,
+        int((want[:, 0] > 0).sum()), int(want[:, 10].sum())))
+    if name.startswith("microfacet"):
+        assert (want[:, 0] > 0).sum() > 2000 and want[:, 0].max() > 5.0               # the specular lobe is exercised, peak included
+        # Conditioning, not implementation: the Beckmann exponent is tan^2(theta_h) / alpha^2 with tan^2 = (1 - c^2) / c^2
+        # and c = cos(theta_h) ~ 1, so ONE ulp of c (6e-8) moves the exponent by 1.2e-7 / alpha^2 — 5e-3 relative on
+        # veach's sharpest plate (alpha = 0.005), 1e-5 on the table's (alpha = 0.1). Both sides are fp32 and round c
+        # differently (fast division / rsqrt here, glibc there): allow 4 such ulps on top of 3e-3.
+        alpha = float(s["bsdfs"]["alpha"][b])
+        tol = 3e-3 + 5e-7 / alpha ** 2
+        # a sampled direction near the horizon comes out of z = sqrt(1 - x^2 - y^2): absolute error ~ 1e-7 / z
+        wz = np.maximum(np.abs(want[valid, 9]), 1e-4)
+        print("  alpha", alpha, "tolerance", tol, "worst wo record", rec[valid][np.argmax(e_wo * wz)], "wo", want[valid][np.argmax(e_wo * wz), 7:10])
+        assert e_eval.max() < tol and e_pdf.max() < tol and e_w.max() < 2 * tol and e_spdf.max() < tol
+        assert np.all(e_wo <= 5e-5 + 3e-7 / wz + (2e-7 / alpha if alpha < 0.05 else 0.0))
+    else:
+        assert not want[:, 0:4].any() and not got[:, 0:4].any()                       # eval / pdf of a discrete BSDF are 0
+        assert want[:, 10].sum() > 2000
+        assert e_w.max() < 1e-4 and e_wo.max() < 2e-5
+
+
+def test_microfacet_ttest_known_answers(nb, ctx):
+    """scenes/pa3/tests/ttest-microfacet.xml through the DEVICE BSDF: StudentsTTest::execute (ttest.cpp:150-189) draws
+    sampleCount samples per incident angle, takes the luminance of BSDF::sample's return value and t-tests its mean
+    against the stored reference (significance 0.01, Sidak-corrected over the 5 angles)."""
+    ka = json.load(open(golden("microfacet_ttest.json")))
+    s = nb.load_xml(golden("scenes/round2/microfacet_ttest.xml"))
+    ctx.load(s)
+    b = int(s["shapes"]["bsdf"][0])
+    assert (int(s["bsdfs"]["type"][b]) & 0xff) == 3
+    n = 100000                                                                        # ttest.cpp default sampleCount
+    rng = np.random.default_rng(7)
+    alpha = 1.0 - (1.0 - 0.01) ** (1.0 / len(ka["angles"]))
+    for angle, ref in zip(ka["angles"], ka["references"]):
+        th = np.deg2rad(angle)
+        rec = np.zeros((n, 10), dtype="<f4")
+        rec[:, 0], rec[:, 2] = np.sin(th), np.cos(th)                                 # sphericalDirection(theta, 0)
+        rec[:, 3:6] = [0, 0, 1]
+        rec[:, 6:8] = rng.random((n, 2), dtype=np.float32)
+        w = ctx.bsdf_probe(b, rec)[:, 4:7].astype(np.float64)
+        lum = w[:, 0] * 0.212671 + w[:, 1] * 0.715160 + w[:, 2] * 0.072169
+        mean, var = lum.mean(), lum.var(ddof=1)
+        t = abs(mean - ref) * np.sqrt(n / max(var, 1e-30))
+        p = 2.0 * stats.t.sf(t, n - 1)
+        print("angle %5.1f ref %.6f mean %.6f t %.2f p %.3f" % (angle, ref, mean, t, p))
+        assert p >= alpha, (angle, ref, mean, p)
+
+
+# ---- images of the branches that had none ----------------------------------------------------------------------
+def render_pair(nb, ctx, xml, spp, seeds=(1, 2)):
+    s = nb.load_xml(golden(xml))
+    imgs = []
+    for seed in seeds:
+        ctx.load(s)
+        ctx.render_begin(nb.make_render_params(s, seed=seed))
+        ctx.render_subframe(0, spp)
+        imgs.append(ctx.film_download(normalize=True))
+    return s, imgs
+
+
+@pytest.mark.parametrize("name,xml,spp,check", [
+    ("dof", "scenes/round2/cbox_dof.xml", 256, "lens"),                              # a35: thin lens (perspective.cpp:112-127)
+    ("direct", "scenes/round2/cbox_direct.xml", 64, "direct"),                       # a15: DirectIntegrator (direct.cpp:16-67)
+    ("schlick_mats", "scenes/vol/cbox_homog_schlick_mats_small.xml", 256, "schlick"),   # a32: SchlickPhase
+    ("schlick_mis", "scenes/vol/cbox_homog_schlick_mis_small.xml", 256, "schlick")])
+def test_untested_branches_match_reference_renders(nb, ctx, name, xml, spp, check):
+    s, (a, b) = render_pair(nb, ctx, xml, spp)
+    want = np.load(golden("r2_%s_ref_%dspp.npy" % (name, spp)))
+    if check == "lens":
+        assert s["camera"]["lens_radius"][0] == np.float32(0.06) and s["camera"]["focal_distance"][0] == np.float32(4.9)
+    if check == "direct":
+        assert s["render"]["integrator"][0] == nb.INTEGRATORS["direct"] and len(s["emitters"]) == 3
+    if check == "schlick":
+        g = 0.7
+        assert s["media"]["phase"][0] == nb.PHASE_SCHLICK and abs(s["media"]["phase_param"][0] - (1.55 * g - 0.55 * g ** 3)) < 1e-6
+    assert a.shape == want.shape and np.isfinite(a).all()
+    bias = (a.mean(axis=(0, 1)) - want.mean(axis=(0, 1))) / want.mean(axis=(0, 1))
+    floor, err = rel_rmse(a, b), rel_rmse(a, want)
+    print(name, "bias", bias, "relRMSE", err, "noise floor", floor)
+    assert np.all(np.abs(bias) <= 0.01), bias
+    assert err <= 1.25 * floor + 2e-3, (err, floor)
+    if check == "lens":
+        # and the blur is really the reference's: at 2048 spp the thin-lens render matches the reference's 2048-spp render
+        # within the noise, while the same scene through a pinhole (lens radius zeroed) is visibly further away
+        want_hi = np.load(golden("r2_dof_ref_2048spp.npy"))
+        imgs = []
+        for lens, seed in ((0.06, 5), (0.06, 6), (0.0, 5)):
+            t = dict(s); cam = s["camera"].copy(); cam["lens_radius"] = lens; t["camera"] = cam
+            ctx.load(t); ctx.render_begin(nb.make_render_params(t, seed=seed)); ctx.render_subframe(0, 2048)
+            imgs.append(ctx.film_download(normalize=True))
+        floor_hi, err_hi, err_pin = rel_rmse(imgs[0], imgs[1]), rel_rmse(imgs[0], want_hi), rel_rmse(imgs[2], want_hi)
+        print("dof at 2048 spp: relRMSE", err_hi, "noise floor", floor_hi, "pinhole vs thin-lens golden", err_pin)
+        assert err_hi <= 1.25 * floor_hi + 2e-3 and err_pin > 1.5 * err_hi
+
+
+# ---- SURVEY 8(d) image gate: relRMSE(GPU_N, R) <= 1.10 x relRMSE(CPU_N, R), |bias| <= 0.5 % (1 % for volumes) ------------------
+PINS = [("cbox_path_mis", "scenes/cbox/cbox_path_mis_small.xml", 512, 0.005), ("cbox_path_mats", "scenes/cbox/cbox_path_mats_small.xml", 512, 0.005),
+        ("veach_direct_mis", "scenes/veach/veach_mis_small.xml", 256, 0.005), ("table_path_mis", "scenes/table/table_path_mis_small.xml", 128, 0.005),
+        ("val_path_vol_mis", "scenes/vol/cbox_val_mis_small.xml", 256, 0.01),
+        ("homog_aniso_path_vol_mats", "scenes/vol/cbox_homog_aniso_small.xml", 256, 0.01)]
+
+
+@pytest.mark.parametrize("name,xml,n,bias_tol", PINS)
+def test_high_spp_gate(nb, ctx, name, xml, n, bias_tol):
+    """R = the reference CPU renderer at 8N spp (committed), CPU_N = an independent reference render at N spp (its
+    relRMSE against R is committed), GPU_N = this backend at N spp. And the bias at high spp: GPU at 32N spp against R."""
+    R = np.load(golden("hi_%s_R%d.npy" % (name, 8 * n)))
+    cpu = json.load(open(golden("hi_%s_cpu%d.json" % (name, n))))
+    s = nb.load_xml(golden(xml))
+    ctx.load(s)
+    errs = []
+    for seed in (11, 12, 13):
+        ctx.render_begin(nb.make_render_params(s, seed=seed))
+        ctx.render_subframe(0, n)
+        errs.append(rel_rmse(ctx.film_download(normalize=True), R))
+    ctx.render_begin(nb.make_render_params(s, seed=99))
+    for first in range(0, 32 * n, 4 * n):
+        ctx.render_subframe(first, 4 * n)
+    hi = ctx.film_download(normalize=True)
+    assert ctx.counters()["samples"] == R.shape[0] * R.shape[1] * 32 * n
+    bias = (hi.mean(axis=(0, 1)) - R.mean(axis=(0, 1))) / R.mean(axis=(0, 1))
+    # R itself carries noise: the standard error of its mean, from the per-pixel spread of the CPU_N-vs-R figure
+    print(name, "relRMSE(GPU_N, R) %s vs relRMSE(CPU_N, R) %.5f; bias of GPU at %d spp vs R at %d spp: %s (CPU_N bias %s)" % (
+        ["%.5f" % e for e in errs], cpu["cpu_relrmse_vs_R"], 32 * n, 8 * n, bias, cpu["cpu_bias_vs_R"]))
+    assert np.median(errs) <= 1.10 * cpu["cpu_relrmse_vs_R"], (errs, cpu["cpu_relrmse_vs_R"])
+    # R is itself a finite render: its channel means carry a standard error (committed with the fixture, estimated from
+    # the per-pixel spread of CPU_N around R; heavy-tailed on the specular veach plates, where even the reference's own
+    # CPU_N mean sits 1.2 % off R). The 0.5 % / 1 % gate of SURVEY 8(d) applies on top of that.
+    # (The committed figure treats pixels as independent; the gaussian filter (r = 2, sigma = 0.5) spreads every sample
+    # over an effective 4 pi sigma^2 = 3.1 pixels, so the true standard error is 1.77x larger: 6 x figure = 3.4 sigma.)
+    se = np.array(cpu["rel_se_of_R_mean"])
+    assert np.all(np.abs(bias) <= bias_tol + 6.0 * se), (bias, se)
+    assert rel_rmse(hi, R) < 0.6 * np.median(errs)                                    # and it converges towards R
+
+
+# ---- the reference's own EXR goldens, at their own size and spp -----------------------------------------------------------
+EXR = ["table_path_mis", "table_path_mats", "veach_mis", "veach_ems", "veach_mats", "odyssey_mis", "odyssey_ems", "odyssey_mats",
+       "sphere_point_ems", "sphere_sphere_ems", "sphere_sphere_mats", "sphere_sphere2_ems", "sphere_sphere2_mats",
+       "sphere_sphere_mesh_ems", "sphere_sphere2_mesh_ems"]
+EXR_SCENES = {"table_path_mis": "scenes/table/table_path_mis.xml", "table_path_mats": "scenes/table/table_path_mats.xml"}
+
+
+def pool4(img):
+    h, w = img.shape[0] // 4 * 4, img.shape[1] // 4 * 4
+    return img[:h, :w].reshape(h // 4, 4, w // 4, 4, 3).mean(axis=(1, 3))
+
+
+@pytest.mark.parametrize("name", EXR)
+def test_reference_exr_goldens(nb, ctx, name):
+    """The images the reference ships (scenes/pa3/**/ref/*.exr, scenes/pa4/table/ref/*.exr; fixture = 4x4 box means in
+    fp16 + full-resolution channel means, tests/golden/make_round2.py) against this backend rendering the same XML at the
+    golden's size and spp. Two noisy renders are compared, so the gate is the noise between two GPU seeds."""
+    fx = np.load(golden("exr_%s.npz" % name))
+    ref_xml = str(fx["scene"])                                     # path in the reference tree; the same file lives under tests/golden/scenes
+    local = EXR_SCENES.get(name) or {"scenes/pa3/veach_mi": "scenes/veach", "scenes/pa3/odyssey": "scenes/odyssey",
+                                     "scenes/pa3/sphere": "scenes/sphere"}[os.path.dirname(ref_xml)] + "/" + os.path.basename(ref_xml)
+    spp = int(fx["spp"])
+    s, (a, b) = render_pair(nb, ctx, local, spp)
+    assert list(a.shape[:2]) == fx["shape"].tolist()
+    want = fx["pooled"].astype(np.float32)
+    pa, pb = pool4(a), pool4(b)
+    lit = fx["mean"] > 1e-6                                           # the sphere scenes are green only
+    gm, om = fx["mean"][lit], fx["oracle_mean"][lit]
+    am, bm = a.reshape(-1, 3).mean(axis=0), b.reshape(-1, 3).mean(axis=0)
+    assert np.all(am[~lit] == 0)
+    bias, seed_bias, oracle_bias = (am[lit] - gm) / gm, np.abs(am[lit] - bm[lit]) / gm, np.abs(om - gm) / gm
+    floor, err = rel_rmse(pa, pb), rel_rmse(pa, want)
+    print(name, "spp", spp, "bias vs golden", bias, "(two GPU seeds differ by", seed_bias, ", the oracle sits", oracle_bias,
+          "off) pooled relRMSE", err, "noise floor", floor, "oracle vs golden", float(fx["oracle_relrmse_pooled4"]))
+    # Two finite renders are compared. 1 % on the mean, unless the estimator itself is heavy-tailed at this spp (BSDF
+    # sampling of a small light: sphere_mats at 256 spp, where the reference's own code lands 7 % below its golden): then
+    # the spread between two GPU seeds and the oracle's own distance from the golden set the scale.
+    assert np.all(np.abs(bias) <= np.maximum(0.01, np.maximum(4 * seed_bias, 1.5 * oracle_bias))), bias
+    # Several goldens were NOT rendered by this reference's code as it stands (the reference's own CPU code lands 7 % below
+    # sphere_mats.exr and a systematic 3 % relRMSE off table_path_mis_512spp.exr, far outside its noise — and this backend
+    # lands on the same figures to 3-4 digits): the gate is therefore "no further from the golden than the noise or the
+    # reference code itself is", and, where the oracle is outside the noise, "as far from it as the oracle is".
+    oracle_err = float(fx["oracle_relrmse_pooled4"])
+    assert err <= 1.25 * max(floor, oracle_err) + 3e-3, (err, floor, oracle_err)
+    if oracle_err > 2.0 * floor:
+        assert abs(err - oracle_err) <= 0.1 * oracle_err + floor, (err, oracle_err)

@@ -20,7 +20,8 @@ from conftest import golden
 pytestmark = pytest.mark.gpu
 
 RENDERS, SPP = 24, 8192
-FILES = ["pa3/test-mesh.xml", "pa3/test-mesh-furnace.xml", "pa4/test-direct.xml", "pa4/test-furnace.xml"]
+FILES = ["pa3/test-mesh.xml", "pa3/test-mesh-furnace.xml", "pa4/test-direct.xml", "pa4/test-furnace.xml",
+         "pa1/test-direct.xml"]          # pa1: the `direct` integrator with point lights (1, 0.06317, 0, 1.06317)
 
 
 def scenes_of(path, tmp_path):
@@ -71,7 +72,9 @@ def test_reference_known_answers(nb, ctx, tmp_path, rel, strategy):
         assert ctx.counters()["samples"] == SPP
         means = np.array(means)
         mean, var = means.mean(), means.var(ddof=1)
-        t = abs(mean - ref) * np.sqrt(RENDERS / max(var, 1e-12))
+        # hypothesis.h:320 floors the sample variance at 1e-5 over its 100 000 samples, i.e. the standard error of the
+        # mean at 1e-5 (the stored references are rounded to about that); the same floor here on the RENDERS means
+        t = abs(mean - ref) * np.sqrt(RENDERS / max(var, RENDERS * 1e-10))
         p = 2.0 * stats.t.sf(t, RENDERS - 1)
         print("%-12s ref %.6f mean %.6f sd(mean) %.2e t %.2f p %.3f" % (integ, ref, mean, np.sqrt(var / RENDERS), t, p))
         # The film sums SPP fp32 splats per pixel: with a (nearly) constant integrand — the furnace
