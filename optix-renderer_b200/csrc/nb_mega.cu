@@ -600,6 +600,9 @@ enum { NB_W_LI = 0, NB_W_THR = 3, NB_W_O = 6, NB_W_D = 9, NB_W_MINT = 12, NB_W_M
 #ifndef NB_WALK_MIN_BLOCKS_WIDE
 #define NB_WALK_MIN_BLOCKS_WIDE 7
 #endif
+#ifndef NB_WALK_LEAF_STEPS
+#define NB_WALK_LEAF_STEPS 3      /* primitive tests per loop iteration (wide kernel) */
+#endif
 template <bool MIS, bool EXT, bool WIDE>
 __global__ void __launch_bounds__(NB_TILE_THREADS, EXT ? NB_WALK_MIN_BLOCKS_EXT : (WIDE ? NB_WALK_MIN_BLOCKS_WIDE : NB_WALK_MIN_BLOCKS))
 nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
@@ -741,6 +744,35 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
             }
         }
         /* ---- LEAF: lanes standing on a leaf intersect it together ---- */
+        if constexpr (WIDE) {
+            /* one primitive per lane per step: leaves hold 1..n primitives, and a loop over the whole leaf left the
+             * 100-instruction triangle test running for the lanes with the longest leaves only (ncu: 7 of 32 lanes);
+             * a lane whose leaf is finished pops its stack at once and, if that is another leaf, stays in step */
+#pragma unroll 1
+            for (int ls = 0; ls < NB_WALK_LEAF_STEPS; ++ls) {
+                const uint32_t m_leaf = __ballot_sync(0xffffffffu, phase == NB_PH_LEAF);
+                if (!m_leaf || (__popc(m_leaf) < NB_WALK_T_LEAF && __ballot_sync(0xffffffffu, phase == NB_PH_NODE))) break;
+                if (phase == NB_PH_LEAF) {
+                    const uint32_t s = leaf;
+                    const float4 s0 = __ldg(sc.slots + 3 * s), s1 = __ldg(sc.slots + 3 * s + 1), s2 = __ldg(sc.slots + 3 * s + 2);
+                    const uint32_t tag = __float_as_uint(s2.y);
+                    float u = 0.f, v = 0.f, t;
+                    const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, to, td, tmint, tmaxt, t)
+                                                           : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t);
+                    if (ok) {
+                        if (t_any) occluded = true;
+                        /* the wide walk meets primitives out of slot order: an exact-t tie keeps the later slot, as the reference's order does */
+                        else if (!(hit.slot != 0xffffffffu && t == hit.t && s < hit.slot)) {
+                            tmaxt = t;
+                            hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                        }
+                    }
+                    if (occluded) phase = NB_PH_TDONE;
+                    else if (tag & NB_SLOT_LAST) wnext();
+                    else leaf = s + 1;
+                }
+            }
+        } else {
         const uint32_t m_leaf = __ballot_sync(0xffffffffu, phase == NB_PH_LEAF);
         if (m_leaf && (__popc(m_leaf) >= NB_WALK_T_LEAF || !__ballot_sync(0xffffffffu, phase == NB_PH_NODE))) {
             if (phase == NB_PH_LEAF) {
@@ -753,22 +785,16 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
                                                            : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t);
                     if (ok) {
                         if (t_any) { occluded = true; break; }
-                        /* the wide walk meets primitives out of slot order: an exact-t tie keeps the later slot, as the reference's order does */
-                        if (!WIDE || !(hit.slot != 0xffffffffu && t == hit.t && s < hit.slot)) {
-                            tmaxt = t;
-                            hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
-                        }
+                        tmaxt = t;
+                        hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
                     }
                     if (tag & NB_SLOT_LAST) break;
                     ++s;
                 }
-                if constexpr (WIDE) {
-                    if (occluded) phase = NB_PH_TDONE; else wnext();
-                } else {
-                    idx = occluded ? NB_NODE_END : after;
-                    phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
-                }
+                idx = occluded ? NB_NODE_END : after;
+                phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
             }
+        }
         }
         /* ---- TDONE: a walk ended. Shadow ray: add its contribution, go on to the main ray
          * (or end the path); main ray: queue for shading ---- */

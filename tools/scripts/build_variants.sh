@@ -6,11 +6,11 @@ cd /root/repo/optix-renderer_b200/csrc
 mkdir -p ../variants
 build_one() {
   name=$1; shift
-  nvcc -O3 -std=c++17 -lineinfo -Xcompiler -fPIC --expt-relaxed-constexpr -gencode arch=compute_100a,code=sm_100a -prec-div=false -prec-sqrt=false "$@" -Xptxas -v -c nb_mega.cu -o /tmp/nb_mega_$name.o 2>&1 | grep -A2 "tile_walkILb1ELb0" | grep -E "registers|spill" | tr '\n' ' '
+  nvcc -O3 -std=c++17 -lineinfo -Xcompiler -fPIC --expt-relaxed-constexpr -gencode arch=compute_100a,code=sm_100a -prec-div=false -prec-sqrt=false "$@" -Xptxas -v -c nb_mega.cu -o /tmp/nb_mega_$name.o 2>&1 | grep -A2 "tile_walkILb1ELb0ELb1" | grep -E "registers|spill" | tr '\n' ' '
   echo " <- $name $*"
   objs=""
-  for f in nb_api nb_bvh nb_bvh_build nb_probe nb_render nb_trace; do objs="$objs ../build/$f.o"; done
-  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libnorib200_$name.so $objs /tmp/nb_mega_$name.o -cudart static
+  for f in ../build/nb_*.o; do [ "$f" != "../build/nb_mega.o" ] && objs="$objs $f"; done
+  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/libnorib200_$name.so $objs /tmp/nb_mega_$name.o -cudart static -ldl
 }
 if [ -n "$1" ]; then LIST=$(cat "$1"); else LIST=$'b4 -DNB_WALK_MIN_BLOCKS=4\nb5 -DNB_WALK_MIN_BLOCKS=5\nb6 -DNB_WALK_MIN_BLOCKS=6\nb8 -DNB_WALK_MIN_BLOCKS=8'; fi
 while read -r name flags; do
