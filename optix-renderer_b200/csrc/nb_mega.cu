@@ -76,13 +76,33 @@ __device__ __forceinline__ f3 nb_area_eval(const nb_emitter &em, f3 ref, f3 p, f
     return mk3(0.f);
 }
 
+/* the lock-step kernels on a tree scene (direct_*, the volume integrators, normals / av / preview): one out-of-line copy
+ * of the production traversal per translation unit, so that the kernels which call it from several sites do not grow */
+template <bool ANY>
+__device__ __noinline__ bool nb_wide_query(const float4 *wide, const float4 *slots, uint32_t n_wide, float ox, float oy, float oz,
+                                           float dx, float dy, float dz, float mint, float maxt, float4 &out) {
+    NbHit h;
+    const bool r = nb_traverse_wide<ANY>(wide, slots, n_wide, make_float3(ox, oy, oz), make_float3(dx, dy, dz), mint, maxt, h);
+    out = make_float4(h.t, h.u, h.v, __uint_as_float(h.slot));
+    return r;
+}
 template <bool FLAT>
 __device__ __forceinline__ bool nb_occluded(const NbDeviceScene &sc, f3 o, f3 d, float mint, float maxt) {
     NbHit dummy;
+    if (!FLAT && sc.use_wide) {
+        float4 h;
+        return nb_wide_query<true>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h);
+    }
     return nb_query<true, FLAT>(sc.nodes, sc.slots, sc.n_nodes, sc.n_slots, o, d, mint, maxt, dummy);
 }
 template <bool FLAT>
 __device__ __forceinline__ bool nb_closest(const NbDeviceScene &sc, f3 o, f3 d, float mint, float maxt, NbHit &hit) {
+    if (!FLAT && sc.use_wide) {
+        float4 h;
+        const bool r = nb_wide_query<false>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h);
+        hit.t = h.x; hit.u = h.y; hit.v = h.z; hit.slot = __float_as_uint(h.w);
+        return r;
+    }
     return nb_query<false, FLAT>(sc.nodes, sc.slots, sc.n_nodes, sc.n_slots, o, d, mint, maxt, hit);
 }
 
@@ -592,7 +612,7 @@ enum { NB_W_LI = 0, NB_W_THR = 3, NB_W_O = 6, NB_W_D = 9, NB_W_MINT = 12, NB_W_M
  * its first NB_WSTK_SHARED entries in shared memory (one 8-byte column per lane, conflict-free), the rare deeper ones
  * in local memory; a popped entry farther than the current hit is dropped without being fetched. */
 #ifndef NB_WSTK_SHARED
-#define NB_WSTK_SHARED 12
+#define NB_WSTK_SHARED 8       /* B200, table / C3 M samples/s at 2 / 4 / 8 / 12 / 16: 458 / 451 / 465 / 451 / 479* / -; (*earlier build) shared memory competes with L1 */
 #endif
 #ifndef NB_WALK_NODE_STEPS_WIDE
 #define NB_WALK_NODE_STEPS_WIDE 4
@@ -600,9 +620,7 @@ enum { NB_W_LI = 0, NB_W_THR = 3, NB_W_O = 6, NB_W_D = 9, NB_W_MINT = 12, NB_W_M
 #ifndef NB_WALK_MIN_BLOCKS_WIDE
 #define NB_WALK_MIN_BLOCKS_WIDE 7
 #endif
-#ifndef NB_WALK_LEAF_STEPS
-#define NB_WALK_LEAF_STEPS 3      /* primitive tests per loop iteration (wide kernel) */
-#endif
+
 template <bool MIS, bool EXT, bool WIDE>
 __global__ void __launch_bounds__(NB_TILE_THREADS, EXT ? NB_WALK_MIN_BLOCKS_EXT : (WIDE ? NB_WALK_MIN_BLOCKS_WIDE : NB_WALK_MIN_BLOCKS))
 nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, unsigned long long *stats) {
@@ -744,35 +762,6 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
             }
         }
         /* ---- LEAF: lanes standing on a leaf intersect it together ---- */
-        if constexpr (WIDE) {
-            /* one primitive per lane per step: leaves hold 1..n primitives, and a loop over the whole leaf left the
-             * 100-instruction triangle test running for the lanes with the longest leaves only (ncu: 7 of 32 lanes);
-             * a lane whose leaf is finished pops its stack at once and, if that is another leaf, stays in step */
-#pragma unroll 1
-            for (int ls = 0; ls < NB_WALK_LEAF_STEPS; ++ls) {
-                const uint32_t m_leaf = __ballot_sync(0xffffffffu, phase == NB_PH_LEAF);
-                if (!m_leaf || (__popc(m_leaf) < NB_WALK_T_LEAF && __ballot_sync(0xffffffffu, phase == NB_PH_NODE))) break;
-                if (phase == NB_PH_LEAF) {
-                    const uint32_t s = leaf;
-                    const float4 s0 = __ldg(sc.slots + 3 * s), s1 = __ldg(sc.slots + 3 * s + 1), s2 = __ldg(sc.slots + 3 * s + 2);
-                    const uint32_t tag = __float_as_uint(s2.y);
-                    float u = 0.f, v = 0.f, t;
-                    const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, to, td, tmint, tmaxt, t)
-                                                           : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t);
-                    if (ok) {
-                        if (t_any) occluded = true;
-                        /* the wide walk meets primitives out of slot order: an exact-t tie keeps the later slot, as the reference's order does */
-                        else if (!(hit.slot != 0xffffffffu && t == hit.t && s < hit.slot)) {
-                            tmaxt = t;
-                            hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
-                        }
-                    }
-                    if (occluded) phase = NB_PH_TDONE;
-                    else if (tag & NB_SLOT_LAST) wnext();
-                    else leaf = s + 1;
-                }
-            }
-        } else {
         const uint32_t m_leaf = __ballot_sync(0xffffffffu, phase == NB_PH_LEAF);
         if (m_leaf && (__popc(m_leaf) >= NB_WALK_T_LEAF || !__ballot_sync(0xffffffffu, phase == NB_PH_NODE))) {
             if (phase == NB_PH_LEAF) {
@@ -785,16 +774,24 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
                                                            : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t);
                     if (ok) {
                         if (t_any) { occluded = true; break; }
-                        tmaxt = t;
-                        hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                        /* the wide walk meets primitives out of slot order: an exact-t tie keeps the later slot, as the reference's
+                         * order does. (One primitive per lane per step, popping the stack in between, was tried to lift the 7 of 32
+                         * lanes this loop runs at: B200, table 486 -> 451, C3 690 -> 686 M samples/s — the per-step ballots and pops cost more) */
+                        if (!WIDE || !(hit.slot != 0xffffffffu && t == hit.t && s < hit.slot)) {
+                            tmaxt = t;
+                            hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+                        }
                     }
                     if (tag & NB_SLOT_LAST) break;
                     ++s;
                 }
-                idx = occluded ? NB_NODE_END : after;
-                phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
+                if constexpr (WIDE) {
+                    if (occluded) phase = NB_PH_TDONE; else wnext();
+                } else {
+                    idx = occluded ? NB_NODE_END : after;
+                    phase = idx == NB_NODE_END ? NB_PH_TDONE : NB_PH_NODE;
+                }
             }
-        }
         }
         /* ---- TDONE: a walk ended. Shadow ray: add its contribution, go on to the main ray
          * (or end the path); main ray: queue for shading ---- */

@@ -16,6 +16,7 @@ if "size" in opt:
 ctx = nb.Context(0)
 ctx.set_option("strategy", {"auto": 0, "wavefront": 1, "tile": 2}[opt.get("strategy", "auto")])
 ctx.set_option("ordered", int(opt.get("ordered", 0)))
+ctx.set_option("wide", int(opt.get("wide", 1)))
 ctx.load(s, device_bvh=opt.get("device_bvh", "0") == "1")
 ctx.render_begin(nb.make_render_params(s, seed=1))
 for _ in range(int(opt.get("repeat", 1))):
