@@ -233,6 +233,7 @@ def main():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true")
+    ap.add_argument("--no-flush", action="store_true", help="skip the 256 MB L2-flush write between steps (for the ncu capture that attributes DRAM writes)")
     ap.add_argument("--strategy", default="auto", choices=["auto", "wavefront", "tile"])
     args = ap.parse_args()
     # rank 0 prints ONE JSON line on stdout: anything a library writes there meanwhile (NCCL prints its version on
@@ -266,7 +267,7 @@ def main():
         nb.comm_init_torch(ctx)             # the library's own NCCL communicator; torch only carries the 128-byte id
     ctx.load(scene)
     ctx.render_begin(params)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
+    flush = None if args.no_flush else torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
 
     def barrier():
         if world > 1:
@@ -289,7 +290,8 @@ def main():
     barrier()
     with ClockSampler(local) as clk:
         for _ in range(args.steps):
-            flush.zero_()
+            if flush is not None:
+                flush.zero_()
             barrier()                       # every rank starts the step together: the reduce then waits for the slowest
             ctx.timer_mark(0)
             step()
@@ -415,7 +417,7 @@ def main():
                            "parallelism": "sample slices x%d of ONE render, scene replicated, 1 NCCL film reduce issued by the library "
                                           "(nb_film_reduce) inside the timed region" % world,
                            "timed": "film clear + render + reduce, CUDA events on the library's stream; every rank starts each step at a barrier",
-                           "l2": "256 MB flush write between timed steps" + ("; K_tile keeps path state in registers, film 7.8 MB" if single_launch
+                           "l2": ("no flush (--no-flush)" if args.no_flush else "256 MB flush write between timed steps") + ("; K_tile keeps path state in registers, film 7.8 MB" if single_launch
                                                                                   else "; path pool (1M slots x 164 B) exceeds L2")},
                 "rays_per_s": rays_all / (ms * 1e-3), "rays_per_sample": rays_all / samples_all,
                 "e2e": {"value": float(se.item()) / float(te.item()), "unit": "samples/s", "h2d_bytes_per_step": h2d,

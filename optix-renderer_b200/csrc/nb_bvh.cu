@@ -207,6 +207,13 @@ int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
      * increasing index order (true of BVH::build's output; a foreign tree that breaks it is walked instead) */
     ctx->flat_ok = leaves_in_order;
     ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;
+    ctx->dev.flat_in_params = 0;
+#ifdef NB_PARAM_SLOTS
+    if (ni <= NB_FLAT_MAX_SLOTS) {
+        memcpy(ctx->dev.flat_slots, slots.data(), slots.size() * sizeof(float4));
+        ctx->dev.flat_in_params = 1;
+    }
+#endif
     ctx->h_slot_tag.resize(ni); ctx->h_slot_prim.resize(ni);
     for (uint32_t k = 0; k < ni; ++k) {
         memcpy(&ctx->h_slot_tag[k], &slots[(size_t) k * 3 + 2].y, 4);

@@ -344,6 +344,13 @@ int nb_build_bvh_device(nb_ctx *ctx) {
     d_wide = nullptr;
     ctx->dev.nodes = d_nodes; ctx->dev.slots = d_slots;
     ctx->dev.n_nodes = n_kept; ctx->dev.n_slots = n;
+    ctx->dev.flat_in_params = 0;
+#ifdef NB_PARAM_SLOTS
+    if (n <= NB_FLAT_MAX_SLOTS) {
+        NB_TRY(cudaMemcpy(ctx->dev.flat_slots, d_slots, (size_t) n * 3 * sizeof(float4), cudaMemcpyDeviceToHost));
+        ctx->dev.flat_in_params = 1;
+    }
+#endif
     ctx->flat_ok = true;                         /* slots are emitted in the pre-order of the leaves */
     ctx->dev.flat = nb_scene_flat(ctx) ? 1u : 0u;
     nb_update_wide(ctx);

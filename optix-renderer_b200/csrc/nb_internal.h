@@ -78,6 +78,14 @@ struct NbDeviceScene {
     uint32_t n_shapes = 0, n_bsdfs = 0, n_emitters = 0, n_media = 0;
     int32_t envmap_emitter = -1, ambient_medium = -1;
     nb_camera camera;
+#ifdef NB_PARAM_SLOTS
+    /* Experiment kept behind a macro, not adopted: the primitive slots of a flat scene (<= NB_FLAT_MAX_SLOTS) once more
+     * inside the kernel parameters, so that the flat scan's warp-uniform slot reads become constant-bank broadcasts (LDCU
+     * into uniform registers) instead of three per-lane LDG.128. B200, M samples/s, global loads -> parameter space:
+     * cbox path_mis 2019 -> 1817, cbox_val_mis 988 -> 847, path_mats 2756 -> 2691, homog_aniso 3005 -> 2926. */
+    float4 flat_slots[3 * NB_FLAT_MAX_SLOTS];
+#endif
+    uint32_t flat_in_params = 0;
 };
 
 struct NbRenderState;   /* nb_render.cu */

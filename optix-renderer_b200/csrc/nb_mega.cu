@@ -59,7 +59,11 @@ struct NbShadowRay { f3 o, d, c; float mint, maxt, cand; };
 
 template <bool EXT>
 __device__ __forceinline__ void nb_hit_info(const NbDeviceScene &sc, const NbHit &hit, f3 o, f3 d, nb_shape &sh, NbIts &its) {
+#ifdef NB_SMEM_SLOTS
+    const float4 sl = sc.slots[3 * hit.slot + 2];
+#else
     const float4 sl = __ldg(sc.slots + 3 * hit.slot + 2);
+#endif
     const uint32_t sid = __float_as_uint(sl.y) & NB_SLOT_SHAPE_MASK, prim = __float_as_uint(sl.z);
     sh = sc.shapes[sid];
     its.shape = sid;
@@ -89,6 +93,9 @@ __device__ __noinline__ bool nb_wide_query(const float4 *wide, const float4 *slo
 template <bool FLAT>
 __device__ __forceinline__ bool nb_occluded(const NbDeviceScene &sc, f3 o, f3 d, float mint, float maxt) {
     NbHit dummy;
+#ifdef NB_PARAM_SLOTS
+    if (FLAT) return nb_scan_params<true>(sc.flat_slots, sc.n_slots, o, d, mint, maxt, dummy);
+#endif
     if (!FLAT && sc.use_wide) {
         float4 h;
         return nb_wide_query<true>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h);
@@ -97,6 +104,9 @@ __device__ __forceinline__ bool nb_occluded(const NbDeviceScene &sc, f3 o, f3 d,
 }
 template <bool FLAT>
 __device__ __forceinline__ bool nb_closest(const NbDeviceScene &sc, f3 o, f3 d, float mint, float maxt, NbHit &hit) {
+#ifdef NB_PARAM_SLOTS
+    if (FLAT) return nb_scan_params<false>(sc.flat_slots, sc.n_slots, o, d, mint, maxt, hit);
+#endif
     if (!FLAT && sc.use_wide) {
         float4 h;
         const bool r = nb_wide_query<false>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h);
@@ -497,6 +507,15 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     NbPathRegs ps;
     ps.flags = 0;
     int32_t medium = sc.ambient_medium;     /* volume integrators: the medium the path is in */
+#ifdef NB_SMEM_SLOTS
+    /* experiment: the flat scene's slots staged in shared memory once per CTA (broadcast LDS instead of per-lane LDG) */
+    __shared__ float4 sm_slots[3 * NB_FLAT_MAX_SLOTS];
+    if (FLAT) {
+        for (uint32_t i = threadIdx.x; i < 3 * sc.n_slots && i < 3 * NB_FLAT_MAX_SLOTS; i += blockDim.x) sm_slots[i] = sc.slots[i];
+        __syncthreads();
+        if (sc.n_slots <= NB_FLAT_MAX_SLOTS) sc.slots = sm_slots;
+    }
+#endif
     for (;;) {
         /* --- regenerate: idle lanes take the next camera samples of the warp's item --- */
         uint32_t pix, sidx;
@@ -873,10 +892,15 @@ static cudaError_t nb_tile_launch_flat(const NbDeviceScene &sc, const NbFilm &fi
 template <int INTEG>
 static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film, const NbTilePlan &tp, uint32_t *item_counter,
                                     unsigned long long *stats, int sm_count, cudaStream_t stream) {
+#ifdef NB_PARAM_SLOTS
+    const bool flat = sc.flat && sc.flat_in_params;      /* the flat kernels read the slots from their parameters */
+#else
+    const bool flat = sc.flat != 0;
+#endif
     if (sc.ext)
-        return sc.flat ? nb_tile_launch_flat<INTEG, true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
+        return flat ? nb_tile_launch_flat<INTEG, true, true>(sc, film, tp, item_counter, stats, sm_count, stream)
                        : nb_tile_launch_flat<INTEG, false, true>(sc, film, tp, item_counter, stats, sm_count, stream);
-    return sc.flat ? nb_tile_launch_flat<INTEG, true, false>(sc, film, tp, item_counter, stats, sm_count, stream)
+    return flat ? nb_tile_launch_flat<INTEG, true, false>(sc, film, tp, item_counter, stats, sm_count, stream)
                    : nb_tile_launch_flat<INTEG, false, false>(sc, film, tp, item_counter, stats, sm_count, stream);
 }
 
@@ -895,7 +919,12 @@ cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const Nb
      * 8x8 tiles 359 M. Lanes pick up the next item as soon as the current one is handed out
      * (nb_take_sample), so small items cost one atomic each and nothing else. The lock-step kernel
      * keeps 16x8 tiles x 2 passes: its camera rays run coherently (cbox 1.96 G vs 1.94 G at 1 pass). */
-    const bool walking = !sc.flat && walk && (integrator == NB_INTEGRATOR_PATH_MIS || integrator == NB_INTEGRATOR_PATH_MATS);
+#ifdef NB_PARAM_SLOTS
+    const bool is_flat = sc.flat && sc.flat_in_params;
+#else
+    const bool is_flat = sc.flat != 0;
+#endif
+    const bool walking = !is_flat && walk && (integrator == NB_INTEGRATOR_PATH_MIS || integrator == NB_INTEGRATOR_PATH_MATS);
 #ifndef NB_TILE_CHUNK_MAX
 #define NB_TILE_CHUNK_MAX 2
 #endif

@@ -52,6 +52,27 @@ __device__ __forceinline__ bool nb_box_hit(const float4 A, const float4 B, const
     return mint <= farT && nearT <= maxt;
 }
 
+#ifdef NB_FAST_HITS
+/* experiment: the same test with contraction allowed (fma) and a fast reciprocal — NOT bit-exact */
+__device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, const float4 s2, const float3 o,
+                                           const float3 d, float mint, float maxt, float &u, float &v, float &t) {
+    const float p0x = s0.x, p0y = s0.y, p0z = s0.z;
+    const float e1x = s0.w, e1y = s1.x, e1z = s1.y;
+    const float e2x = s1.z, e2y = s1.w, e2z = s2.x;
+    const float pvx = d.y * e2z - d.z * e2y, pvy = d.z * e2x - d.x * e2z, pvz = d.x * e2y - d.y * e2x;
+    const float det = e1x * pvx + e1y * pvy + e1z * pvz;
+    if (det > -1e-8f && det < 1e-8f) return false;
+    const float inv = __fdividef(1.0f, det);
+    const float tvx = o.x - p0x, tvy = o.y - p0y, tvz = o.z - p0z;
+    u = (tvx * pvx + tvy * pvy + tvz * pvz) * inv;
+    if (u < 0.0f || u > 1.0f) return false;
+    const float qvx = tvy * e1z - tvz * e1y, qvy = tvz * e1x - tvx * e1z, qvz = tvx * e1y - tvy * e1x;
+    v = (d.x * qvx + d.y * qvy + d.z * qvz) * inv;
+    if (v < 0.0f || u + v > 1.0f) return false;
+    t = (e2x * qvx + e2y * qvy + e2z * qvz) * inv;
+    return t >= mint && t <= maxt;
+}
+#else
 /* mesh.cpp:101-139 with e1/e2 precomputed */
 __device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, const float4 s2, const float3 o,
                                            const float3 d, float mint, float maxt, float &u, float &v, float &t) {
@@ -72,6 +93,7 @@ __device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, con
     return t >= mint && t <= maxt;
 }
 
+#endif
 /* sphere.cpp:67-94 */
 __device__ __forceinline__ bool nb_sphere_hit(const float4 s0, const float3 o, const float3 d, float mint,
                                               float maxt, float &t) {
@@ -347,7 +369,41 @@ __device__ __forceinline__ bool nb_scan(const float4 *__restrict__ slots, uint32
     if (maxt < mint) return false;
     bool found = false;
     for (uint32_t s = 0; s < n_slots; ++s) {
+        #ifdef NB_SMEM_SLOTS
+        const float4 s0 = slots[3 * s], s1 = slots[3 * s + 1], s2 = slots[3 * s + 2];       /* may point into shared memory */
+#else
         const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
+#endif
+        float u = 0.f, v = 0.f, t;
+        const bool ok = (__float_as_uint(s2.y) & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
+                                                                : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+        if (ok) {
+            if (ANY) return true;
+            found = true;
+            maxt = t;
+            hit.t = t; hit.u = u; hit.v = v; hit.slot = s;
+        }
+    }
+    return found;
+}
+
+/* nb_scan over slots held in kernel-parameter space (NbDeviceScene::flat_slots): same tests, same order, same bits;
+ * the warp-uniform slot index makes every fetch a constant-bank broadcast. */
+template <bool ANY>
+__device__ __forceinline__ bool nb_scan_params(const float4 *slots, uint32_t n_slots, float3 o, float3 d,
+                                               float mint, float maxt, NbHit &hit) {
+    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
+    if (mint == NB_EPSILON) {
+        float m = fabsf(o.x);
+        m = fmaxf(m, fabsf(o.y));
+        m = fmaxf(m, fabsf(o.z));
+        const float s = __fmul_rn(mint, m);
+        mint = (mint < s) ? s : mint;
+    }
+    if (maxt < mint) return false;
+    bool found = false;
+    for (uint32_t s = 0; s < n_slots; ++s) {
+        const float4 s0 = slots[3 * s], s1 = slots[3 * s + 1], s2 = slots[3 * s + 2];
         float u = 0.f, v = 0.f, t;
         const bool ok = (__float_as_uint(s2.y) & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
                                                                 : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
