@@ -34,11 +34,11 @@ static void writePfm(const std::string &path, const float *data, size_t h, size_
 
 int main(int argc, char **argv) {
     if (argc < 3) {
-        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [flat=scene.nbs]\n");
+        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs]\n");
         return 2;
     }
     try {
-        int spp = -1, device = 0, launch = 0;
+        int spp = -1, device = 0, launch = 0, snapshot = 0;
         uint64_t seed = 0;
         std::string flatOut;
         std::vector<int> devices;
@@ -56,6 +56,7 @@ int main(int argc, char **argv) {
             }
             else if (!strncmp(argv[i], "seed=", 5)) seed = strtoull(argv[i] + 5, nullptr, 10);
             else if (!strncmp(argv[i], "launch=", 7)) launch = atoi(argv[i] + 7);
+            else if (!strncmp(argv[i], "snapshot=", 9)) snapshot = atoi(argv[i] + 9);
             else if (!strncmp(argv[i], "flat=", 5)) flatOut = argv[i] + 5;
         }
         auto t0 = std::chrono::steady_clock::now();
@@ -73,20 +74,37 @@ int main(int argc, char **argv) {
         if (launch <= 0) launch = spp;
         double load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         auto t1 = std::chrono::steady_clock::now();
-        for (int s = 0; s < spp; s += launch) state.renderSubframe((uint32_t) s, (uint32_t) std::min(launch, spp - s));
+        /* progressive output without a window (the reference shows the running image through GL and saves on demand,
+         * render.cpp:725-747): every `snapshot` launches the accumulators so far are normalised and written next to
+         * the final image as <out>.<samples>spp.<ext>. With several devices each snapshot reduces the films onto the
+         * first one, which is safe to repeat: the reduce moves the samples (nb_film_reduce). */
+        const std::string outPath(argv[2]);
+        const bool pfm = outPath.size() > 4 && outPath.substr(outPath.size() - 4) == ".pfm";
+        int launches = 0, snapshots = 0;
+        for (int s = 0; s < spp; s += launch) {
+            const int n = std::min(launch, spp - s);
+            state.renderSubframe((uint32_t) s, (uint32_t) n);
+            if (snapshot > 0 && ++launches % snapshot == 0 && s + n < spp) {
+                std::vector<float> snap;
+                uint32_t sh = 0, sw = 0;
+                state.download(snap, true, &sh, &sw);
+                const std::string name = outPath.substr(0, outPath.size() - 4) + "." + std::to_string(s + n) + "spp" + outPath.substr(outPath.size() - 4);
+                if (pfm) writePfm(name, snap.data(), sh, sw); else writeNpy(name, snap.data(), sh, sw, 3);
+                ++snapshots;
+            }
+        }
         double render_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
         std::vector<float> img;
         uint32_t h = 0, w = 0;
         state.download(img, true, &h, &w);
-        std::string out(argv[2]);
-        if (out.size() > 4 && out.substr(out.size() - 4) == ".pfm") writePfm(out, img.data(), h, w); else writeNpy(out, img.data(), h, w, 3);
+        if (pfm) writePfm(outPath, img.data(), h, w); else writeNpy(outPath, img.data(), h, w, 3);
         nb_counters c = state.counters();
         printf("{\"scene\": \"%s\", \"width\": %u, \"height\": %u, \"spp\": %d, \"load_seconds\": %.3f, \"seconds\": %.6f, "
                "\"samples\": %llu, \"samples_per_s\": %.1f, \"rays_closest\": %llu, \"rays_any\": %llu, \"rays_per_s\": %.1f, "
-               "\"device_ms\": %.3f, \"invalid_samples\": %llu, \"devices\": %zu}\n",
+               "\"device_ms\": %.3f, \"invalid_samples\": %llu, \"devices\": %zu, \"snapshots\": %d}\n",
                argv[1], w, h, spp, load_s, render_s, (unsigned long long) c.samples, c.samples / render_s,
                (unsigned long long) c.rays_closest, (unsigned long long) c.rays_any, (c.rays_closest + c.rays_any) / render_s,
-               c.device_ms, (unsigned long long) c.invalid_samples, state.deviceCount());
+               c.device_ms, (unsigned long long) c.invalid_samples, state.deviceCount(), snapshots);
         return 0;
     } catch (const std::exception &e) {
         fprintf(stderr, "nori_b200: %s\n", e.what());

@@ -143,3 +143,29 @@ def test_cli_renders_reference_xml(nb, tmp_path):
     bias = (img.mean(axis=(0, 1)) - want.mean(axis=(0, 1))) / want.mean(axis=(0, 1))
     assert np.all(np.abs(bias) <= 0.01), bias
     assert rel_rmse(img, want) < 0.2
+
+
+def test_cli_progressive_snapshots(nb, tmp_path):
+    """Progressive output without a window (the reference shows the running image through GL, render.cpp:725-747): with
+    snapshot=K nori_b200 writes the normalised image so far every K launches; each is the render of its sample prefix
+    (per-(pixel, sample) streams), so a snapshot equals a fresh render of that many samples and the noise falls."""
+    import json
+    import os
+    import subprocess
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nori_b200")
+    xml = golden("scenes/cbox/cbox_path_mis_small.xml")
+    out = tmp_path / "prog.npy"
+    r = subprocess.run([cli, xml, str(out), "spp=64", "launch=16", "snapshot=1", "seed=9"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert r.returncode == 0, r.stderr
+    stats = json.loads(r.stdout.strip().splitlines()[-1])
+    assert stats["snapshots"] == 3 and stats["samples"] == 200 * 150 * 64
+    snaps = [np.load(str(tmp_path / ("prog.%dspp.npy" % k))) for k in (16, 32, 48)]
+    final = np.load(out)
+    want = np.load(golden("cbox_ref_256spp.npy"))
+    errs = [rel_rmse(s, want) for s in snaps] + [rel_rmse(final, want)]
+    assert errs[0] > errs[1] > errs[3]
+    fresh = tmp_path / "fresh.npy"
+    r = subprocess.run([cli, xml, str(fresh), "spp=32", "seed=9"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert r.returncode == 0, r.stderr
+    a, b = np.load(fresh), snaps[1]
+    assert np.abs(a - b).max() <= 1e-4 * max(1.0, np.abs(a).max())      # same samples, different order of fp32 additions

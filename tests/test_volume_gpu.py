@@ -102,3 +102,57 @@ def test_reference_heterog_scene_loads_and_renders(nb, ctx):
     ctx.load(e); ctx.render_begin(nb.make_render_params(e, seed=1)); ctx.render_subframe(0, 64)
     b = ctx.film_download(normalize=True)
     assert np.isfinite(a).all() and abs(a.mean() / b.mean() - 1) < 0.02
+
+
+def test_linear_density_ramp_closed_form(nb, ctx):
+    """The one closed-form pin beyond the constant grid (the reference holds no golden for its heterogeneous medium): a
+    density that is linear in x. The 27-tap triquadratic sampler reproduces a linear field exactly, the optical depth of
+    a ray segment is then (density at its midpoint) x length, so transmittance = exp(-sigma_t * scale * depth) and
+    P(free path < maxt) = 1 - transmittance — checked against the device's ratio- and delta-tracking means."""
+    s = nb.load_xml(golden("scenes/vol/cbox_heterog_const_small.xml"))
+    m = s["media"][0]
+    assert m["type"] == nb.MEDIUM_HETEROGENEOUS
+    nx, ny, nz = (int(v) for v in m["grid_dims"])
+    first = int(m["first_voxel"])
+    a, b = 0.2, 0.06                                     # density = a + b * (array x coordinate): 0.32 .. 1.28 inside the box
+    ramp = (a + b * np.arange(nx, dtype=np.float32))[:, None, None] * np.ones((1, ny, nz), np.float32)
+    t = dict(s)
+    dens = s["density"].copy()
+    dens[first:first + nx * ny * nz] = ramp.ravel()
+    t["density"] = dens
+    med = s["media"].copy()
+    B = 2                                                # NB_GRID_BORDER
+    med["max_density"][0] = a + b * (nx - B)             # the largest value the box can show
+    t["media"] = med
+    ctx.load(t)
+    W = m["world_to_grid"].reshape(3, 4).astype(np.float64)
+    rng = np.random.default_rng(5)
+    n = 192
+    Winv = np.linalg.inv(W[:, :3])
+    og = rng.uniform([B + 0.5] * 3, [nx - B - 0.5, ny - B - 0.5, nz - B - 0.5], (n, 3))      # start inside the box
+    o = (og - W[:, 3]) @ Winv.T
+    d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    maxt = rng.uniform(0.05, 0.6, n)
+    rays = np.concatenate([o, d, np.full((n, 1), 1e-4), maxt[:, None]], axis=1).astype("<f4")
+    draws = 1 << 16
+    got = ctx.medium_probe(0, rays, samples=draws, seed=3)
+    # closed form in float64
+    o64, d64 = rays[:, :3].astype(np.float64), rays[:, 3:6].astype(np.float64)
+    g0, gd = o64 @ W[:, :3].T + W[:, 3], d64 @ W[:, :3].T
+    lo, hi = np.array([B, B, B], float), np.array([nx - B, ny - B, nz - B], float)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ta, tb = (lo - g0) / gd, (hi - g0) / gd
+    t0 = np.maximum(np.minimum(ta, tb).max(axis=1), 1e-4)
+    t1 = np.minimum(np.maximum(ta, tb).min(axis=1), rays[:, 7].astype(np.float64))
+    assert np.all(t1 > t0)
+    xm = g0[:, 0] + gd[:, 0] * 0.5 * (t0 + t1)
+    depth = (a + b * xm) * (t1 - t0)
+    sigma = float(max(m["mu_t"])) * float(m["density_scale"])
+    T = np.exp(-sigma * depth)
+    np.testing.assert_allclose(got[:, 0], a + b * g0[:, 0], rtol=2e-5, atol=2e-6)          # the sampler is exact on a linear field
+    se = 5.0 * np.sqrt(np.maximum(T * (1 - T), 1e-4) / draws) + 2e-4
+    print("ramp: transmittance range %.3f..%.3f, max |ratio-tracking mean - exp(-tau)| %.2e, max |P(collision) - (1 - exp(-tau))| %.2e" % (
+        T.min(), T.max(), np.abs(got[:, 3] - T).max(), np.abs(got[:, 1] - (1 - T)).max()))
+    assert T.min() < 0.9 and T.max() > 0.95
+    assert np.all(np.abs(got[:, 3] - T) <= se)           # ratio tracking: unbiased estimate of exp(-tau), variance below Bernoulli's
+    assert np.all(np.abs(got[:, 1] - (1 - T)) <= se)     # delta tracking: collision before maxt with probability 1 - exp(-tau)
