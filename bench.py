@@ -167,6 +167,14 @@ def ncu_capture(path):
     return out
 
 
+def thread_inst(cap):
+    """thread-instructions of a captured launch: the counter itself when the report has it, else warp instructions x lanes"""
+    v = cap.get("smsp__thread_inst_executed.sum", 0.0)
+    if not v:
+        v = cap.get("smsp__inst_executed.sum", 0.0) * cap.get("smsp__thread_inst_executed_per_inst_executed.ratio", 0.0)
+    return v
+
+
 def pinned(shape, dtype=np.float32):
     """numpy view of page-locked host memory (the e2e legs copy from / to pinned buffers)."""
     import torch
@@ -212,7 +220,7 @@ def tree_config(nb, ctx, name, xml, spp, sms, clk_mhz, cap_csv):
     meta = cap_csv[:-4] + ".meta.json"
     if cap and os.path.exists(meta):
         m = json.load(open(meta))
-        per_sample = cap.get("smsp__thread_inst_executed.sum", 0.0) / max(1.0, m.get("samples", 0.0))
+        per_sample = thread_inst(cap) / max(1.0, m.get("samples", 0.0))
         lanes = sms * 128 * clk_mhz * 1e6
         row["lane_issue_frac"] = per_sample * row["samples_per_s"] / lanes if per_sample else None
         row["lanes_per_warp_inst"] = cap.get("smsp__thread_inst_executed_per_inst_executed.ratio")
@@ -369,11 +377,11 @@ def main():
         if cap and os.path.exists(meta_p) and single_launch:
             meta = json.load(open(meta_p))
             n_cap = float(meta["samples"])
-            thread_inst = cap.get("smsp__thread_inst_executed.sum", 0.0) / n_cap * (samples_all / args.steps / world)
+            t_inst = thread_inst(cap) / n_cap * (samples_all / args.steps / world)
             warp_inst = cap.get("smsp__inst_executed.sum", 0.0) / n_cap * (samples_all / args.steps / world)
             roofline.update({
-                "achieved": thread_inst / (avg_launch_ms * 1e-3) / 1e12,
-                "frac": thread_inst / (avg_launch_ms * 1e-3) / lanes_peak,
+                "achieved": t_inst / (avg_launch_ms * 1e-3) / 1e12,
+                "frac": t_inst / (avg_launch_ms * 1e-3) / lanes_peak,
                 "warp_issue_frac": warp_inst / (avg_launch_ms * 1e-3) / (sms * 4 * clk_mhz * 1e6),
                 "lanes_per_warp_inst": cap.get("smsp__thread_inst_executed_per_inst_executed.ratio"),
                 "traffic": (cap.get("dram__bytes_read.sum", 0.0) + cap.get("dram__bytes_write.sum", 0.0)) / n_cap * (samples_all / args.steps / world),

@@ -250,6 +250,7 @@ int nb_trace_rays(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_hit, nb_h
         cudaMemcpyAsync(d_rays, packed.data(), packed.size() * sizeof(float4), cudaMemcpyHostToDevice, ctx->stream);
         NbDeviceScene sc = ctx->dev;               /* the parity entry walks in the reference's order unless "trace_wide" asks for the production tree */
         sc.use_wide = (ctx->opt_trace_wide && sc.wide) ? 1u : 0u;
+        sc.fast_hits = ctx->opt_trace_fast ? 1u : 0u;
         nb_launch_trace_hits(sc, d_rays, n, any_hit, d_out, d_any, ctx->sm_count, ctx->stream);
         cudaMemcpyAsync(h_out.data(), d_out, (size_t) n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream);
         if (any_hit) cudaMemcpyAsync(h_any.data(), d_any, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream);
@@ -284,6 +285,7 @@ int nb_trace_rays_device(nb_ctx *ctx, const void *rays_device, uint64_t n, int a
     cudaEventRecord(e0, ctx->stream);
     NbDeviceScene sc = ctx->dev;
     sc.use_wide = (ctx->opt_trace_wide && sc.wide) ? 1u : 0u;
+    sc.fast_hits = ctx->opt_trace_fast ? 1u : 0u;
     for (int r = 0; r < repeats; ++r)
         nb_launch_trace_hits(sc, (const float4 *) rays_device, n, any_hit, (float4 *) out_device, d_any, ctx->sm_count, ctx->stream);
     cudaEventRecord(e1, ctx->stream);

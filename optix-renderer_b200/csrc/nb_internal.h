@@ -86,6 +86,7 @@ struct NbDeviceScene {
     float4 flat_slots[3 * NB_FLAT_MAX_SLOTS];
 #endif
     uint32_t flat_in_params = 0;
+    uint32_t fast_hits = 0;             /* nb_trace_rays only ("trace_fast"): the production triangle test instead of the reference's */
 };
 
 struct NbRenderState;   /* nb_render.cu */
@@ -109,6 +110,7 @@ struct nb_ctx {
     int opt_profile = 0, opt_sort = 0, opt_strategy = 0;
     int opt_walk = 1;                   /* tree scenes: K_tile_walk (per-lane state machine) instead of lock-step K_tile */
     int opt_ordered = 0;                /* 1: nb_trace_rays uses the near-child-first walk */
+    int opt_trace_fast = 0;             /* 1: nb_trace_rays uses the production triangle test too (to measure its parity) */
     int opt_trace_wide = 0;             /* 1: nb_trace_rays answers through the wide tree too (to measure its hit parity) */
     int opt_wide = 1;                   /* 1: tree scenes are traversed through the wide tree (production); 0: the reference's order (parity mode) */
     uint32_t wide_depth = 0;            /* levels of the wide tree */

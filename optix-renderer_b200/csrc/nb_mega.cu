@@ -80,13 +80,22 @@ __device__ __forceinline__ f3 nb_area_eval(const nb_emitter &em, f3 ref, f3 p, f
     return mk3(0.f);
 }
 
+/* Experiment kept behind a macro, NOT adopted: nb_tri_hit_fast (fma-contracted Moeller-Trumbore, fast reciprocal;
+ * nb_trace.cuh) as the render kernels' triangle test. B200: cbox path_mis +11-14 %, val_mis +10 %, table +3-16 %, C3 +4 %.
+ * But through the trace entry ("trace_fast") it reports another primitive on 3 of 24 656 table rays (1.2e-4, the bar is
+ * 1e-6), and the reference's own known-answer scenes scenes/pa3/tests/test-mesh.xml — a camera ray aimed exactly at the
+ * edge two triangles share — lose HALF their energy (0.0451 against 0.0898): with the reference's arithmetic u + v == 1
+ * exactly on that edge and one triangle takes the ray, contracted it is > 1 in both and the ray falls through the crack. */
+#ifndef NB_RENDER_FAST_HITS
+#define NB_RENDER_FAST_HITS false
+#endif
 /* the lock-step kernels on a tree scene (direct_*, the volume integrators, normals / av / preview): one out-of-line copy
  * of the production traversal per translation unit, so that the kernels which call it from several sites do not grow */
 template <bool ANY>
 __device__ __noinline__ bool nb_wide_query(const float4 *wide, const float4 *slots, uint32_t n_wide, float ox, float oy, float oz,
-                                           float dx, float dy, float dz, float mint, float maxt, float4 &out) {
+                                           float dx, float dy, float dz, float mint, float maxt, float4 &out, bool fast) {
     NbHit h;
-    const bool r = nb_traverse_wide<ANY>(wide, slots, n_wide, make_float3(ox, oy, oz), make_float3(dx, dy, dz), mint, maxt, h);
+    const bool r = nb_traverse_wide<ANY>(wide, slots, n_wide, make_float3(ox, oy, oz), make_float3(dx, dy, dz), mint, maxt, h, fast);
     out = make_float4(h.t, h.u, h.v, __uint_as_float(h.slot));
     return r;
 }
@@ -98,8 +107,9 @@ __device__ __forceinline__ bool nb_occluded(const NbDeviceScene &sc, f3 o, f3 d,
 #endif
     if (!FLAT && sc.use_wide) {
         float4 h;
-        return nb_wide_query<true>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h);
+        return nb_wide_query<true>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h, NB_RENDER_FAST_HITS);
     }
+    if (FLAT) return nb_scan<true>(sc.slots, sc.n_slots, o, d, mint, maxt, dummy, NB_RENDER_FAST_HITS);
     return nb_query<true, FLAT>(sc.nodes, sc.slots, sc.n_nodes, sc.n_slots, o, d, mint, maxt, dummy);
 }
 template <bool FLAT>
@@ -109,10 +119,11 @@ __device__ __forceinline__ bool nb_closest(const NbDeviceScene &sc, f3 o, f3 d, 
 #endif
     if (!FLAT && sc.use_wide) {
         float4 h;
-        const bool r = nb_wide_query<false>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h);
+        const bool r = nb_wide_query<false>(sc.wide, sc.slots, sc.n_wide, o.x, o.y, o.z, d.x, d.y, d.z, mint, maxt, h, NB_RENDER_FAST_HITS);
         hit.t = h.x; hit.u = h.y; hit.v = h.z; hit.slot = __float_as_uint(h.w);
         return r;
     }
+    if (FLAT) return nb_scan<false>(sc.slots, sc.n_slots, o, d, mint, maxt, hit, NB_RENDER_FAST_HITS);
     return nb_query<false, FLAT>(sc.nodes, sc.slots, sc.n_nodes, sc.n_slots, o, d, mint, maxt, hit);
 }
 
@@ -790,7 +801,7 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
                     const uint32_t tag = __float_as_uint(s2.y);
                     float u = 0.f, v = 0.f, t;
                     const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, to, td, tmint, tmaxt, t)
-                                                           : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t);
+                                                           : nb_tri_hit(s0, s1, s2, to, td, tmint, tmaxt, u, v, t, WIDE && NB_RENDER_FAST_HITS);
                     if (ok) {
                         if (t_any) { occluded = true; break; }
                         /* the wide walk meets primitives out of slot order: an exact-t tie keeps the later slot, as the reference's

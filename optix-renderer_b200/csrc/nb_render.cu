@@ -609,6 +609,7 @@ int nb_set_option(nb_ctx *ctx, const char *name, int64_t value) {
     else if (!strcmp(name, "walk")) ctx->opt_walk = (int) value;
     else if (!strcmp(name, "wide")) { ctx->opt_wide = value != 0; nb_update_wide(ctx); }
     else if (!strcmp(name, "trace_wide")) ctx->opt_trace_wide = value != 0;
+    else if (!strcmp(name, "trace_fast")) ctx->opt_trace_fast = value != 0;
     else if (!strcmp(name, "ordered")) { ctx->opt_ordered = value != 0; ctx->dev.ordered = value != 0 ? 1u : 0u; }
     else if (!strcmp(name, "flat_scan")) {
         ctx->opt_flat = (int) value;

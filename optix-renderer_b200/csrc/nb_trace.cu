@@ -6,17 +6,19 @@
 template <bool FLAT>
 __global__ void __launch_bounds__(256)
 nb_k_trace_hits(const float4 *__restrict__ nodes, const float4 *__restrict__ slots, uint32_t n_nodes, uint32_t n_slots,
-                const float4 *__restrict__ rays, uint64_t n, int any_hit, bool ordered,
+                const float4 *__restrict__ rays, uint64_t n, int any_hit, bool ordered, bool fast,
                 float4 *__restrict__ out, uint32_t *__restrict__ out_any) {
     for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
         const float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
         const float3 o = make_float3(ro.x, ro.y, ro.z), d = make_float3(rd.x, rd.y, rd.z);
         NbHit hit;
-        nb_query<false, FLAT>(nodes, slots, n_nodes, n_slots, o, d, ro.w, rd.w, hit, ordered);
+        if (FLAT) nb_scan<false>(slots, n_slots, o, d, ro.w, rd.w, hit, fast);
+        else nb_query<false, FLAT>(nodes, slots, n_nodes, n_slots, o, d, ro.w, rd.w, hit, ordered);
         out[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot));
         if (any_hit) {
             NbHit dummy;
-            out_any[i] = nb_query<true, FLAT>(nodes, slots, n_nodes, n_slots, o, d, ro.w, rd.w, dummy, ordered) ? 1u : 0u;
+            out_any[i] = (FLAT ? nb_scan<true>(slots, n_slots, o, d, ro.w, rd.w, dummy, fast)
+                               : nb_query<true, FLAT>(nodes, slots, n_nodes, n_slots, o, d, ro.w, rd.w, dummy, ordered)) ? 1u : 0u;
         }
     }
 }
@@ -24,16 +26,16 @@ nb_k_trace_hits(const float4 *__restrict__ nodes, const float4 *__restrict__ slo
 /* the same entry through the production tree (nb_traverse_wide) */
 __global__ void __launch_bounds__(256)
 nb_k_trace_hits_wide(const float4 *__restrict__ wide, const float4 *__restrict__ slots, uint32_t n_wide,
-                     const float4 *__restrict__ rays, uint64_t n, int any_hit, float4 *__restrict__ out, uint32_t *__restrict__ out_any) {
+                     const float4 *__restrict__ rays, uint64_t n, int any_hit, bool fast, float4 *__restrict__ out, uint32_t *__restrict__ out_any) {
     for (uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t) gridDim.x * blockDim.x) {
         const float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
         const float3 o = make_float3(ro.x, ro.y, ro.z), d = make_float3(rd.x, rd.y, rd.z);
         NbHit hit;
-        nb_traverse_wide<false>(wide, slots, n_wide, o, d, ro.w, rd.w, hit);
+        nb_traverse_wide<false>(wide, slots, n_wide, o, d, ro.w, rd.w, hit, fast);
         out[i] = make_float4(hit.t, hit.u, hit.v, __uint_as_float(hit.slot));
         if (any_hit) {
             NbHit dummy;
-            out_any[i] = nb_traverse_wide<true>(wide, slots, n_wide, o, d, ro.w, rd.w, dummy) ? 1u : 0u;
+            out_any[i] = nb_traverse_wide<true>(wide, slots, n_wide, o, d, ro.w, rd.w, dummy, fast) ? 1u : 0u;
         }
     }
 }
@@ -46,12 +48,12 @@ void nb_launch_trace_hits(const NbDeviceScene &scene, const float4 *rays, uint64
     if (blocks > cap) blocks = cap;
     if (scene.flat)
         nb_k_trace_hits<true><<<(unsigned) blocks, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, rays, n,
-                                                                     any_hit, false, out, out_any);
+                                                                     any_hit, false, scene.fast_hits != 0, out, out_any);
     else if (scene.use_wide && scene.wide && !scene.ordered)
-        nb_k_trace_hits_wide<<<(unsigned) blocks, 256, 0, stream>>>(scene.wide, scene.slots, scene.n_wide, rays, n, any_hit, out, out_any);
+        nb_k_trace_hits_wide<<<(unsigned) blocks, 256, 0, stream>>>(scene.wide, scene.slots, scene.n_wide, rays, n, any_hit, scene.fast_hits != 0, out, out_any);
     else
         nb_k_trace_hits<false><<<(unsigned) blocks, 256, 0, stream>>>(scene.nodes, scene.slots, scene.n_nodes, scene.n_slots, rays, n,
-                                                                      any_hit, scene.ordered != 0, out, out_any);
+                                                                      any_hit, scene.ordered != 0, false, out, out_any);
 }
 
 /* ---- wavefront stage: K_trace -------------------------------------------------------------

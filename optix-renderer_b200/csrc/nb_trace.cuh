@@ -52,9 +52,10 @@ __device__ __forceinline__ bool nb_box_hit(const float4 A, const float4 B, const
     return mint <= farT && nearT <= maxt;
 }
 
-#ifdef NB_FAST_HITS
-/* experiment: the same test with contraction allowed (fma) and a fast reciprocal — NOT bit-exact */
-__device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, const float4 s2, const float3 o,
+/* Experiment (nb_mega.cu NB_RENDER_FAST_HITS, trace option "trace_fast"), not used by the shipped kernels: the same
+ * Moeller-Trumbore test with contraction allowed (fma) and a fast reciprocal — 45 instead of ~105 instructions, but it
+ * opens cracks along shared edges that the reference's arithmetic does not have. */
+__device__ __forceinline__ bool nb_tri_hit_fast(const float4 s0, const float4 s1, const float4 s2, const float3 o,
                                            const float3 d, float mint, float maxt, float &u, float &v, float &t) {
     const float p0x = s0.x, p0y = s0.y, p0z = s0.z;
     const float e1x = s0.w, e1y = s1.x, e1z = s1.y;
@@ -72,9 +73,8 @@ __device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, con
     t = (e2x * qvx + e2y * qvy + e2z * qvz) * inv;
     return t >= mint && t <= maxt;
 }
-#else
-/* mesh.cpp:101-139 with e1/e2 precomputed */
-__device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, const float4 s2, const float3 o,
+/* mesh.cpp:101-139 with e1/e2 precomputed: the reference's arithmetic, bit for bit */
+__device__ __forceinline__ bool nb_tri_hit_exact(const float4 s0, const float4 s1, const float4 s2, const float3 o,
                                            const float3 d, float mint, float maxt, float &u, float &v, float &t) {
     const float p0x = s0.x, p0y = s0.y, p0z = s0.z;
     const float e1x = s0.w, e1y = s1.x, e1z = s1.y;
@@ -93,7 +93,10 @@ __device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, con
     return t >= mint && t <= maxt;
 }
 
-#endif
+__device__ __forceinline__ bool nb_tri_hit(const float4 s0, const float4 s1, const float4 s2, const float3 o,
+                                           const float3 d, float mint, float maxt, float &u, float &v, float &t, bool fast = false) {
+    return fast ? nb_tri_hit_fast(s0, s1, s2, o, d, mint, maxt, u, v, t) : nb_tri_hit_exact(s0, s1, s2, o, d, mint, maxt, u, v, t);
+}
 /* sphere.cpp:67-94 */
 __device__ __forceinline__ bool nb_sphere_hit(const float4 s0, const float3 o, const float3 d, float mint,
                                               float maxt, float &t) {
@@ -296,7 +299,7 @@ __device__ __forceinline__ int nb_wide_children(const float4 *__restrict__ node,
 
 template <bool ANY>
 __device__ __forceinline__ bool nb_traverse_wide(const float4 *__restrict__ wide, const float4 *__restrict__ slots, uint32_t n_wide,
-                                                 float3 o, float3 d, float mint, float maxt, NbHit &hit) {
+                                                 float3 o, float3 d, float mint, float maxt, NbHit &hit, bool fast = false) {
     hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
     if (mint == NB_EPSILON) {                       /* adaptive ray epsilon, bvh.cpp:409-410 */
         float m = fabsf(o.x);
@@ -325,7 +328,7 @@ __device__ __forceinline__ bool nb_traverse_wide(const float4 *__restrict__ wide
                 const uint32_t tag = __float_as_uint(s2.y);
                 float u = 0.f, v = 0.f, t;
                 const bool ok = (tag & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
-                                                       : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+                                                       : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t, fast);
                 if (ok) {
                     if (ANY) return true;
                     if (!(found && t == hit.t && s < hit.slot)) {      /* exact-t tie: the later slot wins, as in the reference's order */
@@ -357,7 +360,7 @@ __device__ __forceinline__ bool nb_traverse_wide(const float4 *__restrict__ wide
  * 1M-ray oracle set as the tree walk (tests/test_trace_gpu.py). */
 template <bool ANY>
 __device__ __forceinline__ bool nb_scan(const float4 *__restrict__ slots, uint32_t n_slots, float3 o, float3 d,
-                                        float mint, float maxt, NbHit &hit) {
+                                        float mint, float maxt, NbHit &hit, bool fast = false) {
     hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
     if (mint == NB_EPSILON) {
         float m = fabsf(o.x);
@@ -376,7 +379,7 @@ __device__ __forceinline__ bool nb_scan(const float4 *__restrict__ slots, uint32
 #endif
         float u = 0.f, v = 0.f, t;
         const bool ok = (__float_as_uint(s2.y) & NB_SLOT_SPHERE) ? nb_sphere_hit(s0, o, d, mint, maxt, t)
-                                                                : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+                                                                : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t, fast);
         if (ok) {
             if (ANY) return true;
             found = true;

@@ -49,6 +49,7 @@ def ctx(_session_ctx):
     _session_ctx.set_option("ordered", 0)
     _session_ctx.set_option("wide", 1)
     _session_ctx.set_option("trace_wide", 0)
+    _session_ctx.set_option("trace_fast", 0)
     return _session_ctx
 
 

@@ -79,3 +79,4 @@ def test_wide_and_reference_order_render_the_same_image(nb, ctx):
         a = imgs[key]
         bias = (a.mean(axis=(0, 1)) - want.mean(axis=(0, 1))) / want.mean(axis=(0, 1))
         assert np.all(np.abs(bias) <= 0.01) and rel_rmse(a, want) <= 1.25 * floor + 1e-3
+
