@@ -491,6 +491,7 @@ def load_host_library():
         _host.nbh_vdb_read.restype = C.c_longlong
         _host.nbh_vdb_read.argtypes = [C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         _host.nbh_vdb_to_nbv.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
+        _host.nbh_to_nvdb.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
         _host.nbh_inflate.restype = C.c_longlong
         _host.nbh_inflate.argtypes = [C.c_char_p, C.c_uint64, C.c_void_p, C.c_uint64]
     return _host
@@ -518,6 +519,13 @@ def vdb_read(path, grid="density"):
     dims = bbox[3:] - bbox[:3] + 1
     return {"values": v.reshape(dims) if n else v, "bbox_min": bbox[:3].copy(), "bbox_max": bbox[3:].copy(), "index_to_world": xf.reshape(3, 4),
             "background": float(st[0]), "min": float(st[1]), "max": float(st[2]), "active_voxels": act.value}
+
+
+def to_nvdb(src_path, nvdb_path, grid="density"):
+    """.vdb / .nbv / .nvdb -> the NanoVDB cache file the reference would write next to a .vdb (host/nvdb.cpp)."""
+    h = load_host_library()
+    if h.nbh_to_nvdb(os.fsencode(src_path), grid.encode(), os.fsencode(nvdb_path)) != 0:
+        raise NbError(-1, h.nbh_last_error().decode())
 
 
 def load_xml(xml_path, nbs_path=None):

@@ -60,7 +60,9 @@ int nbh_vdb_list(const char *path, char *out, int out_len) {
 long long nbh_vdb_read(const char *path, const char *grid, int32_t bbox[6], double index_to_world[12], float stats[3],
                        uint64_t *active_voxels, float *values, uint64_t capacity) {
     try {
-        const nori::VdbGrid g = nori::vdbReadFloatGrid(path, grid);
+        const std::string p(path);
+        const bool nano = p.size() > 5 && p.substr(p.size() - 5) == ".nvdb";
+        const nori::VdbGrid g = nano ? nori::nvdbReadFloatGrid(p, grid) : nori::vdbReadFloatGrid(p, grid);
         for (int k = 0; k < 3; ++k) { bbox[k] = g.bbox_min[k]; bbox[3 + k] = g.bbox_max[k]; }
         for (int k = 0; k < 12; ++k) index_to_world[k] = g.index_to_world[k];
         stats[0] = g.background; stats[1] = g.value_min; stats[2] = g.value_max;
@@ -81,6 +83,18 @@ long long nbh_vdb_read(const char *path, const char *grid, int32_t bbox[6], doub
 extern "C" int nbh_vdb_to_nbv(const char *vdb_path, const char *grid, const char *nbv_path) {
     try {
         nori::vdbWriteNbv(nori::vdbReadFloatGrid(vdb_path, grid), nbv_path);
+        return 0;
+    } catch (const std::exception &e) { g_error = e.what(); return -1; }
+}
+
+/* .vdb / .nbv / .nvdb -> .nvdb: the NanoVDB cache the reference would write (NvdbVolume.vdb.cpp:83-134) */
+extern "C" int nbh_to_nvdb(const char *src_path, const char *grid, const char *nvdb_path) {
+    try {
+        const std::string p(src_path);
+        const std::string ext = p.rfind('.') == std::string::npos ? "" : p.substr(p.rfind('.'));
+        nori::VdbGrid g = ext == ".nbv" ? nori::vdbReadNbv(p) : ext == ".nvdb" ? nori::nvdbReadFloatGrid(p, grid) : nori::vdbReadFloatGrid(p, grid);
+        if (g.name.empty() || ext == ".nbv") g.name = grid;          /* a .nbv dump carries no grid name */
+        nori::nvdbWriteFloatGrid(g, nvdb_path);
         return 0;
     } catch (const std::exception &e) { g_error = e.what(); return -1; }
 }

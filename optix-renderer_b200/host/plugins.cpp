@@ -485,7 +485,7 @@ public:
     void activate() override {                          /* NvdbVolume::loadFromFile (NvdbVolume.vdb.cpp:9-40) */
         const size_t dot = m_filename.rfind('.');
         const std::string ext = dot == std::string::npos ? "" : m_filename.substr(dot);
-        if (ext == ".nvdb") throw NoriException("Volume: %s is a NanoVDB cache; point the scene at the .vdb it was made from", m_filename);
+        if (ext == ".nvdb") { density = nvdbReadFloatGrid(m_filename, "density"); return; }     /* the reference's cache format (nvdb.cpp) */
         if (ext == ".nbv") { density = vdbReadNbv(m_filename); return; }     /* dense dump (vdb.h) */
         if (ext != ".vdb") throw NoriException("Volume: file extension %s unknown.", ext);
         density = vdbReadFloatGrid(m_filename, "density");

@@ -33,5 +33,10 @@ VdbGrid vdbReadFloatGrid(const std::string &path, const std::string &gridName);
  * (row-major 3x4), f32 background, f32 values (x slowest). Every voxel of the box counts as active. */
 void vdbWriteNbv(const VdbGrid &g, const std::string &path);
 VdbGrid vdbReadNbv(const std::string &path);
+/* ".nvdb": NanoVDB 28 files as the reference reads and caches them (nvdb.cpp). Reading takes the named float grid (the
+ * first one when the name is empty); writing stores one float grid, every voxel of the box active, uncompressed —
+ * the cache NvdbVolume::loadOpenVdbAndCacheNanoVdb leaves next to a .vdb (NvdbVolume.vdb.cpp:83-134). */
+VdbGrid nvdbReadFloatGrid(const std::string &path, const std::string &gridName);
+void nvdbWriteFloatGrid(const VdbGrid &g, const std::string &path);
 
 }

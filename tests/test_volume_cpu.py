@@ -1,8 +1,11 @@
 """On-disk formats in front of the heterogeneous-medium path, no GPU: the OpenVDB reader
 (host/vdb.cpp: Blosc + LZ4, active-mask compression, half floats), inflate, the `volume` /
 `heterog` plugins' flatten hook."""
+import json
+import os
 import re
 import struct
+import subprocess
 import zlib
 
 import ctypes as C
@@ -11,6 +14,7 @@ import pytest
 
 from conftest import golden
 
+HERE = os.path.dirname(os.path.abspath(__file__))
 VDB = "scenes/vol/fluid_data_0050.vdb"      # the reference's scenes/project/volume/fluid_data_0050.vdb, verbatim
 
 
@@ -97,3 +101,94 @@ def test_heterogeneous_medium_record(nb, built_lib):
     p = w2g @ np.array([0.102 + 21 / 32, 0.03 + 32 / 32, -0.028 + 21 / 32, 1.0])
     np.testing.assert_allclose(p, [23, 23, 34], atol=1e-4)
     assert np.allclose(f["media"][0]["mu_t"], 5.0) and f["media"][0]["density_scale"] == 2.0
+
+
+# ---- .nvdb: the NanoVDB cache file the reference reads and writes (NvdbVolume.vdb.cpp:9-61, :120-133) ----------------------
+NVDB = "scenes/vol/fluid_data_0050.nvdb"    # written by the reference's own NanoVDB 28.1.2 (tests/golden/make_nvdb.py)
+NVDB_TOOL = os.path.join(os.path.dirname(HERE), "oracle", "_ref", "nvdb_tool")
+
+
+def test_nvdb_reader_on_a_file_written_by_nanovdb(nb, built_lib):
+    g, v = nb.vdb_read(golden(NVDB), "density"), nb.vdb_read(golden(VDB), "density")
+    assert np.array_equal(g["values"], np.load(golden("vdb_density_21x21x32.npy")))
+    assert np.array_equal(g["bbox_min"], v["bbox_min"]) and np.array_equal(g["bbox_max"], v["bbox_max"])
+    assert np.array_equal(g["index_to_world"], v["index_to_world"])
+    assert g["active_voxels"] == 21 * 21 * 32 and g["background"] == 0.0 and g["max"] == v["max"] and g["min"] == v["min"]
+    assert np.array_equal(nb.vdb_read(golden(NVDB), "")["values"], g["values"])     # readGrid(file, 0): the first grid
+    with pytest.raises(nb.NbError, match="nope"):
+        nb.vdb_read(golden(NVDB), "nope")
+
+
+def test_nvdb_reader_rejects_damaged_files(nb, built_lib, tmp_path):
+    data = open(golden(NVDB), "rb").read()
+    for name, bad, what in (("short.nvdb", data[:100000], "truncated"), ("magic.nvdb", b"NanoVDB1" + data[8:], "magic"),
+                            ("version.nvdb", data[:8] + b"\x1d\x00" + data[10:], "version"), ("empty.nvdb", b"", "no float grid")):
+        p = tmp_path / name
+        p.write_bytes(bad)
+        with pytest.raises(nb.NbError, match=what):
+            nb.vdb_read(str(p), "density")
+
+
+def test_nvdb_writer_makes_the_file_nanovdb_makes(nb, built_lib, tmp_path):
+    """host/nvdb.cpp's writer against nanovdb::io::writeGrid on the same grid: the same bytes except the checksum (not
+    computed: ~0, which NanoVDB reads as "no checksum") and the average / standard deviation of the upper node and the
+    root, where this writer stores the exact moments of the active voxels (NanoVDB 28.1.2's own differ in the 2nd digit
+    from the mean of the values it stores; nothing on the path reads them)."""
+    out = str(tmp_path / "mine.nvdb")
+    nb.to_nvdb(golden(VDB), out, "density")
+    mine, ref = open(out, "rb").read(), open(golden(NVDB), "rb").read()
+    assert len(mine) == len(ref) == 235000
+    grid = 16 + 160 + len("density") + 1
+    root, upper = grid + 672 + 64, grid + 672 + 160
+    free = set(range(grid + 8, grid + 16)) | set(range(root + 48, root + 56)) | set(range(upper + 8224 + 8, upper + 8224 + 16))
+    diff = [i for i in np.nonzero(np.frombuffer(mine, np.uint8) != np.frombuffer(ref, np.uint8))[0] if i not in free]
+    assert diff == []
+    v = np.load(golden("vdb_density_21x21x32.npy")).astype(np.float64)
+    avg, dev = np.frombuffer(mine[root + 48:root + 56], "<f4")
+    assert abs(avg - v.mean()) < 1e-6 and abs(dev - v.std()) < 1e-6
+    back = nb.vdb_read(out, "density")                                               # and through this side's reader
+    assert np.array_equal(back["values"], v.astype(np.float32)) and back["active_voxels"] == v.size
+
+
+@pytest.mark.parametrize("case", ["offset", "negative", "two_uppers", "single"])
+def test_nvdb_writer_round_trips(nb, built_lib, tmp_path, case):
+    """Boxes that start off a leaf boundary, below zero, across two 4096^3 root tiles, one voxel: written, read back
+    here, and — where oracle/_ref/nvdb_tool exists (the build container) — read back by the reference's NanoVDB."""
+    rng = np.random.default_rng(7)
+    org, dims = {"offset": ((3, 9, 130), (13, 5, 20)), "negative": ((-11, -3, -140), (17, 9, 21)), "two_uppers": ((4090, 0, -5), (12, 3, 9)),
+                 "single": ((5, 6, 7), (1, 1, 1))}[case]
+    vals = (rng.random(dims, dtype=np.float32) + 0.25).astype("<f4")
+    M = np.array([[0.5, 0, 0, 1.0], [0, 0, 0.25, -2.0], [0, -0.125, 0, 3.0]])
+    nbv = tmp_path / "g.nbv"
+    nbv.write_bytes(b"NBV1" + np.array(dims, "<i4").tobytes() + np.array(org, "<i4").tobytes() + M.astype("<f8").tobytes() +
+                    np.float32(0.125).tobytes() + vals.tobytes())
+    out = str(tmp_path / "g.nvdb")
+    nb.to_nvdb(str(nbv), out, "smoke")
+    g = nb.vdb_read(out, "smoke")
+    assert g["active_voxels"] == vals.size and g["background"] == np.float32(0.125)
+    assert np.array_equal(g["values"], vals) and list(g["bbox_min"]) == list(org)
+    assert np.array_equal(g["index_to_world"], M) and g["min"] == vals.min() and g["max"] == vals.max()
+    if not os.path.exists(NVDB_TOOL):
+        return
+    dump = tmp_path / "dump.bin"
+    r = subprocess.run([NVDB_TOOL, "dump", out, str(dump), "smoke"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    info = json.loads(r.stdout)
+    assert info["name"] == "smoke" and info["active"] == vals.size
+    raw = dump.read_bytes()
+    mn, dd = np.frombuffer(raw, "<i4", 3, 0), np.frombuffer(raw, "<i4", 3, 12)
+    assert list(mn) == [o - 2 for o in org] and list(dd) == [d + 4 for d in dims]
+    np.testing.assert_allclose(np.frombuffer(raw, "<f8", 12, 24).reshape(3, 4), M, atol=1e-12)
+    bg, lo, hi = np.frombuffer(raw, "<f4", 3, 120)
+    assert bg == np.float32(0.125) and lo == vals.min() and hi == vals.max()
+    seen = np.frombuffer(raw, "<f4", int(np.prod(dd)), 140).reshape(dd)
+    want = np.full(dd, np.float32(0.125)); want[2:-2, 2:-2, 2:-2] = vals
+    assert np.array_equal(seen, want)
+
+
+def test_scene_naming_a_nvdb_file(nb, built_lib):
+    """<string name="filename" value="….nvdb"/> (NvdbVolume.vdb.cpp:36-37) gives the medium the .vdb gives."""
+    a, b = nb.load_xml(golden("scenes/vol/cbox_heterog_nvdb.xml")), nb.load_xml(golden("scenes/vol/cbox_heterog.xml"))
+    assert np.array_equal(a["density"], b["density"])
+    for key in ("grid_dims", "world_to_grid", "mu_t", "max_density", "density_scale", "first_voxel"):
+        assert np.array_equal(np.asarray(a["media"][0][key]), np.asarray(b["media"][0][key])), key
