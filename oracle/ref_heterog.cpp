@@ -24,13 +24,15 @@
  * Grid input: a ".nbv" dense dump (magic "NBV1", i32 dims[3], i32 bbox_min[3], f64
  * index_to_world[12] row-major 3x4, f32 background, f32 values x-slowest) written by
  * libnorib200_host's own .vdb reader (nbh_vdb_to_nbv); a scene that names a .vdb is served from
- * $NORI_ORACLE_NBV_DIR/<stem>.nbv. */
+ * $NORI_ORACLE_NBV_DIR/<stem>.nbv; a scene that names a .nvdb goes through the reference's own
+ * nanovdb::io::readGrid, as NvdbVolume::loadNanoVdb does. */
 #include <nori/medium.h>
 #include <nori/sampler.h>
 #include <nori/NvdbVolume.h>
 #include <nanovdb/NanoVDB.h>
 #include <nanovdb/util/Ray.h>
 #include <nanovdb/util/GridBuilder.h>
+#include <nanovdb/util/IO.h>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -44,6 +46,13 @@ void NvdbVolume::loadFromFile() {
         if (!dir) throw NoriException("oracle harness: %s needs OpenVDB; set NORI_ORACLE_NBV_DIR to a directory holding its .nbv dump", filename.string());
         file = std::filesystem::path(dir) / file.stem();
         file += ".nbv";
+    }
+    if (file.extension() == ".nvdb") {                       /* NvdbVolume::readGrid (NvdbVolume.vdb.cpp:42-61): grid 0 of the file */
+        densityHandle = nanovdb::io::readGrid(file.string(), 0);
+        densityGrid = densityHandle.grid<float>();
+        if (!densityGrid) throw NoriException("GridHandle 0 does not contain a grid with value type float. (%s)", file.string());
+        temperatureGrid = densityGrid;
+        return;
     }
     FILE *f = fopen(file.string().c_str(), "rb");
     if (!f) throw NoriException("oracle harness: cannot open %s", file.string());

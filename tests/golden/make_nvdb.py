@@ -18,3 +18,24 @@ with tempfile.TemporaryDirectory() as tmp:
     out = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "nvdb_tool"), "write", nbv, os.path.join(vol, "fluid_data_0050.nvdb"), "density"],
                          check=True, capture_output=True, text=True).stdout
 print(json.loads(out))
+
+# nvdb_probe_rays.bin / nvdb_probe_out.bin: `nori_ref medium` on cbox_heterog_nvdb.xml — the .nvdb through the reference's own
+# nanovdb::io::readGrid and SampleFromVoxels<.., 2> (oracle/ref_heterog.cpp): density at points, collision probability, mean
+# free path, mean transmittance on rays through the grid's world box (index box x voxel size 0.1875, sigma_t = 2)
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+rng = np.random.default_rng(23)
+n = 192
+lo, hi = np.zeros(3), np.array([21, 21, 32]) * 0.1875
+o = rng.uniform(lo - 0.3, hi + 0.3, (n, 3))
+d = rng.normal(size=(n, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+rays = np.concatenate([o, d, np.full((n, 1), 1e-4), rng.uniform(0.3, 4.0, (n, 1))], axis=1).astype("<f4")
+rays.tofile(os.path.join(HERE, "nvdb_probe_rays.bin"))
+r = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "nori_ref"), "medium", os.path.join(vol, "cbox_heterog_nvdb.xml"),
+                    os.path.join(HERE, "nvdb_probe_rays.bin"), os.path.join(HERE, "nvdb_probe_out.bin"), "samples=16384"],
+                   capture_output=True, text=True)
+assert r.returncode == 0, r.stderr[-2000:]
+print(r.stdout.strip().splitlines()[-1])
+out = np.fromfile(os.path.join(HERE, "nvdb_probe_out.bin"), "<f4").reshape(-1, 4)
+print("nonzero densities", int((out[:, 0] != 0).sum()), "collision probability range", out[:, 1].min(), out[:, 1].max())

@@ -44,6 +44,26 @@ def test_density_free_path_transmittance_vs_nanovdb_oracle(nb, ctx):
     np.testing.assert_allclose(1.0 - got[:, 1], np.clip(got[:, 3], 0, 1), atol=0.03)
 
 
+def test_nvdb_scene_vs_nanovdb_reading_the_same_file(nb, ctx):
+    """cbox_heterog_nvdb.xml names a .nvdb written by the reference's NanoVDB: host/nvdb.cpp + the kernels here against
+    nanovdb::io::readGrid + SampleFromVoxels<.., 2> + the restated tracking there (tests/golden/make_nvdb.py)."""
+    s = nb.load_xml(golden("scenes/vol/cbox_heterog_nvdb.xml"))
+    rays = np.fromfile(golden("nvdb_probe_rays.bin"), "<f4").reshape(-1, 8)
+    want = np.fromfile(golden("nvdb_probe_out.bin"), "<f4").reshape(-1, 4)
+    ctx.load(s)
+    n = 16384
+    got = ctx.medium_probe(0, rays, samples=n, seed=5)
+    print("density max abs diff", np.abs(got[:, 0] - want[:, 0]).max(), "nonzero points", int((want[:, 0] != 0).sum()))
+    np.testing.assert_allclose(got[:, 0], want[:, 0], atol=2e-6, rtol=1e-5)
+    assert (want[:, 0] != 0).sum() > 100
+    p = want[:, 1]
+    tol = 5.0 * np.sqrt(2.0 * np.maximum(p * (1 - p), 1e-4) / n) + 1e-4
+    assert p.max() > 0.9 and np.all(np.abs(got[:, 1] - p) <= tol), np.abs(got[:, 1] - p).max()
+    assert np.all(np.abs(got[:, 3] - want[:, 3]) <= 5.0 * np.sqrt(2.0 * 0.3 / n) + 1e-4), np.abs(got[:, 3] - want[:, 3]).max()
+    both = (p > 0.05)
+    assert np.all(np.abs(got[both, 2] - want[both, 2]) <= 0.05 * want[both, 2] + 2e-3)
+
+
 def render_pair(nb, ctx, xml, spp):
     s = nb.load_xml(golden("scenes/" + xml))
     imgs = []
