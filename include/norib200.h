@@ -288,6 +288,8 @@ int  nb_trace_rays_static(nb_ctx *ctx, const nb_ray *rays, uint64_t n, int any_h
  * out gets 4 floats per ray: density at ray.o (0 for a medium without a grid); the fraction of
  * `samples` free paths from ray.o along ray.d shorter than ray.maxt; their mean length; the mean
  * transmittance (first channel) from ray.o to ray.o + ray.maxt * ray.d. */
+int  nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples,
+                     uint64_t seed, float *out);
 /* Parity entry for the emitter rows: Emitter::sample (src/emitters/arealight.cpp:75-103, pointlight.cpp:47-63,
  * environmentmap.cpp:73-97) of emitters[emitter] on n (reference point, 2D sample) pairs — `in` holds 5
  * floats per record (ref.xyz, sample.xy). out gets 12 floats per record: lRec.wi, the returned
@@ -303,8 +305,6 @@ int  nb_bsdf_probe(nb_ctx *ctx, uint32_t bsdf, const float *in, uint64_t n, floa
  * first n nextUInt() of a generator seeded with seed(initstate, initseq), out_f32 the first n nextFloat() of another
  * generator seeded the same way. (seed(42, 54) is "Round 1" of ext/pcg32/pcg32-demo.out.) */
 int  nb_rng_probe(nb_ctx *ctx, uint64_t initstate, uint64_t initseq, uint32_t n, uint32_t *out_u32, float *out_f32);
-int  nb_medium_probe(nb_ctx *ctx, int32_t medium, const nb_ray *rays, uint64_t n, uint32_t samples,
-                     uint64_t seed, float *out);
 
 /* RenderThread::renderThreadOptix loop (render.cpp:462-574). */
 int  nb_render_begin(nb_ctx *ctx, const nb_render_params *params);  /* allocates + clears film */
@@ -367,7 +367,10 @@ int  nb_timer_elapsed(nb_ctx *ctx, float *ms);
  * culled; every primitive test and the exact-t tie rule are the reference's, so images are the same within Monte-Carlo
  * noise and hits agree except where a box test rounds differently, measured >= 99.9999 % (tests/test_wide_gpu.py);
  * 0: parity mode, the reference's own visiting order everywhere), "trace_wide" (1: nb_trace_rays answers through the
- * production tree too, to measure that hit parity; default 0 = bit-exact reference order) */
+ * production tree too, to measure that hit parity; default 0 = bit-exact reference order), "trace_fast" (1: nb_trace_rays
+ * tests triangles with fused multiply-adds — an experiment kept to MEASURE what contraction costs in parity: 3 of 24 656
+ * primitive ids differ on the table scene and rays through shared edges can slip between triangles, which fails the
+ * reference's own t-tests, so the render kernels never use it; default 0) */
 enum { NB_STRATEGY_AUTO = 0, NB_STRATEGY_WAVEFRONT = 1, NB_STRATEGY_TILE = 2 };
 int  nb_set_option(nb_ctx *ctx, const char *name, int64_t value);
 
