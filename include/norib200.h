@@ -48,7 +48,7 @@ enum { NB_INTEGRATOR_PATH_MIS = 0, NB_INTEGRATOR_PATH_MATS = 1, NB_INTEGRATOR_DI
        NB_INTEGRATOR_DIRECT_MATS = 3, NB_INTEGRATOR_DIRECT_MIS = 4, NB_INTEGRATOR_NORMALS = 5,
        NB_INTEGRATOR_DIRECT = 6, NB_INTEGRATOR_AV = 7, NB_INTEGRATOR_PATH_VOL_MATS = 8,
        NB_INTEGRATOR_PATH_VOL_MIS = 9, NB_INTEGRATOR_PREVIEW = 10 };
-enum { NB_MEDIUM_VACUUM = 0, NB_MEDIUM_HOMOGENEOUS = 1, NB_MEDIUM_HETEROGENEOUS = 2 };
+enum { NB_MEDIUM_VACUUM = 0, NB_MEDIUM_HOMOGENEOUS = 1, NB_MEDIUM_HETEROGENEOUS = 2, NB_MEDIUM_HETEROGENEOUS_BRICKS = 3 };
 enum { NB_PHASE_ISOTROPIC = 0, NB_PHASE_HENYEY_GREENSTEIN = 1, NB_PHASE_SCHLICK = 2 };
 enum { NB_SHAPE_HAS_NORMALS = 1u, NB_SHAPE_HAS_UVS = 2u };
 
@@ -153,8 +153,16 @@ typedef struct nb_bvh_node {
  * NB_GRID_BORDER background voxels on every side. world_to_grid maps a world point to array
  * coordinates (voxel (i,j,k) of the array has its value at (i,j,k), as NanoVDB's index space), so
  * the medium's bounding box is [NB_GRID_BORDER, grid_dims - NB_GRID_BORDER] per axis.
- * max_density = the unscaled grid maximum (tree().root().valueMax(), heterogmedium.cpp:79). */
+ * max_density = the unscaled grid maximum (tree().root().valueMax(), heterogmedium.cpp:79).
+ * NB_MEDIUM_HETEROGENEOUS_BRICKS: the same medium over a SPARSE grid (what NanoVDB's tree is for; a 1024^3 box of smoke
+ * would be 4 GB dense). grid_dims, world_to_grid and the border mean what they mean above — the array is virtual. At
+ * first_voxel the density array holds a table of ceil(grid_dims / 8) entries per axis (x slowest), each the bit pattern of
+ * a uint32 brick number, followed by the bricks: NB_BRICK_VOXELS floats each, the 8^3 voxels of the block plus one voxel
+ * of its neighbours on every side (10^3, x slowest), so the 27-tap stencil of any point in a block reads ONE brick.
+ * Brick 0 is all background; table entries of blocks that hold nothing else point to it. */
 #define NB_GRID_BORDER 2
+#define NB_BRICK_EDGE 10
+#define NB_BRICK_VOXELS 1000
 typedef struct nb_medium {
     uint32_t type;           /* NB_MEDIUM_* */
     float    mu_t[3];        /* homogeneous: extinction; heterogeneous: sigma_t = sigma_a + sigma_s */

@@ -22,7 +22,7 @@ BSDF_DIFFUSE, BSDF_MIRROR, BSDF_DIELECTRIC, BSDF_MICROFACET, BSDF_DISNEY = 0, 1,
 EMITTER_AREA, EMITTER_POINT, EMITTER_ENVMAP, EMITTER_SPOT, EMITTER_DIRECTIONAL, EMITTER_VOLUME = 0, 1, 2, 3, 4, 5
 INTEGRATORS = {"path_mis": 0, "path_mats": 1, "direct_ems": 2, "direct_mats": 3, "direct_mis": 4,
                "normals": 5, "direct": 6, "av": 7, "path_vol_mats": 8, "path_vol_mis": 9, "preview": 10}
-MEDIUM_VACUUM, MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1, 2
+MEDIUM_VACUUM, MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS, MEDIUM_HETEROGENEOUS_BRICKS = 0, 1, 2, 3
 PHASE_ISOTROPIC, PHASE_HENYEY_GREENSTEIN, PHASE_SCHLICK = 0, 1, 2
 FILTER_RESOLUTION = 32
 TRACE_STATIC_MAX_RAYS = 65536
@@ -491,7 +491,8 @@ def load_host_library():
         _host.nbh_vdb_read.restype = C.c_longlong
         _host.nbh_vdb_read.argtypes = [C.c_char_p, C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64]
         _host.nbh_vdb_to_nbv.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
-        _host.nbh_to_nvdb.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
+        _host.nbh_to_nvdb.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
+        _host.nbh_nvdb_write_leaves.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float]
         _host.nbh_inflate.restype = C.c_longlong
         _host.nbh_inflate.argtypes = [C.c_char_p, C.c_uint64, C.c_void_p, C.c_uint64]
     return _host
@@ -521,10 +522,21 @@ def vdb_read(path, grid="density"):
             "background": float(st[0]), "min": float(st[1]), "max": float(st[2]), "active_voxels": act.value}
 
 
-def to_nvdb(src_path, nvdb_path, grid="density"):
-    """.vdb / .nbv / .nvdb -> the NanoVDB cache file the reference would write next to a .vdb (host/nvdb.cpp)."""
+def to_nvdb(src_path, nvdb_path, grid="density", sparse=False):
+    """.vdb / .nbv / .nvdb -> the NanoVDB cache file the reference would write next to a .vdb (host/nvdb.cpp).
+    sparse: only the voxels that differ from the background are active and only the 8^3 leaves that hold some are stored."""
     h = load_host_library()
-    if h.nbh_to_nvdb(os.fsencode(src_path), grid.encode(), os.fsencode(nvdb_path)) != 0:
+    if h.nbh_to_nvdb(os.fsencode(src_path), grid.encode(), os.fsencode(nvdb_path), int(bool(sparse))) != 0:
+        raise NbError(-1, h.nbh_last_error().decode())
+
+
+def nvdb_write_leaves(nvdb_path, origins, values, index_to_world, grid="density", background=0.0):
+    """A sparse float grid from 8^3 blocks — origins (n, 3) int32 multiples of 8, values (n, 8, 8, 8) f32, x slowest — as a
+    .nvdb file (host/nvdb.cpp): voxels that differ from the background are active."""
+    h = load_host_library()
+    o = np.ascontiguousarray(origins, "<i4").reshape(-1, 3); v = np.ascontiguousarray(values, "<f4").reshape(len(o), 512)
+    M = np.ascontiguousarray(index_to_world, "<f8").reshape(12)
+    if h.nbh_nvdb_write_leaves(os.fsencode(nvdb_path), grid.encode(), len(o), _ptr(o), _ptr(v), _ptr(M), float(background)) != 0:
         raise NbError(-1, h.nbh_last_error().decode())
 
 

@@ -205,11 +205,21 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     if (s->ambient_medium >= (int32_t) s->n_media) return nb_fail(ctx, NB_E_INVALID, "ambient medium index out of range");
     for (uint32_t i = 0; i < s->n_media; ++i) {
         const nb_medium &m = s->media[i];
-        if (m.type > NB_MEDIUM_HETEROGENEOUS || m.phase > NB_PHASE_SCHLICK)
+        if (m.type > NB_MEDIUM_HETEROGENEOUS_BRICKS || m.phase > NB_PHASE_SCHLICK)
             return nb_fail(ctx, NB_E_UNSUPPORTED, "medium %u: medium tag %u / phase tag %u has no kernel in this backend", i, m.type, m.phase);
-        if (m.type == NB_MEDIUM_HETEROGENEOUS) {
+        if (m.type >= NB_MEDIUM_HETEROGENEOUS) {
             const uint64_t vox = (uint64_t) m.grid_dims[0] * m.grid_dims[1] * m.grid_dims[2];
-            if (vox == 0 || !s->density || (uint64_t) m.first_voxel + vox > s->n_density)
+            if (m.type == NB_MEDIUM_HETEROGENEOUS_BRICKS) {
+                /* sparse layout: the table, then every brick a table entry names, inside the density array */
+                const uint64_t entries = (uint64_t) ((m.grid_dims[0] + 7) / 8) * ((m.grid_dims[1] + 7) / 8) * ((m.grid_dims[2] + 7) / 8);
+                if (vox == 0 || !s->density || (uint64_t) m.first_voxel + entries + NB_BRICK_VOXELS > s->n_density)
+                    return nb_fail(ctx, NB_E_INVALID, "medium %u: brick table outside the density array", i);
+                const uint64_t room = (s->n_density - m.first_voxel - entries) / NB_BRICK_VOXELS;
+                for (uint64_t e = 0; e < entries; ++e) {
+                    uint32_t brick; memcpy(&brick, s->density + m.first_voxel + e, 4);
+                    if (brick >= room) return nb_fail(ctx, NB_E_INVALID, "medium %u: brick table entry %llu names brick %u of %llu", i, (unsigned long long) e, brick, (unsigned long long) room);
+                }
+            } else if (vox == 0 || !s->density || (uint64_t) m.first_voxel + vox > s->n_density)
                 return nb_fail(ctx, NB_E_INVALID, "medium %u: density grid outside the density array", i);
             for (int a = 0; a < 3; ++a)
                 if (m.grid_dims[a] < 2 * NB_GRID_BORDER + 1)
@@ -255,7 +265,7 @@ int nb_upload_scene(nb_ctx *ctx, const nb_scene_desc *s) {
     d.n_shapes = s->n_shapes; d.n_bsdfs = s->n_bsdfs; d.n_emitters = s->n_emitters;
     d.envmap_emitter = envmap;
     d.ext = (envmap >= 0 || s->n_textures > 0 || ext_plugins) ? 1u : 0u;
-    for (uint32_t i = 0; i < s->n_media; ++i) if (s->media[i].type == NB_MEDIUM_HETEROGENEOUS) d.ext = 1u;
+    for (uint32_t i = 0; i < s->n_media; ++i) if (s->media[i].type >= NB_MEDIUM_HETEROGENEOUS) d.ext = 1u;
     d.camera = s->camera;
     NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->scene_ready = true;

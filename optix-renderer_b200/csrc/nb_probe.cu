@@ -15,7 +15,7 @@ __global__ void nb_k_medium_probe(NbDeviceScene sc, int32_t medium, const float4
     const nb_medium &m = sc.media[medium];
     NbRng rng; rng.seed(seed, i);
     float dens = 0.f;
-    if (m.type == NB_MEDIUM_HETEROGENEOUS) dens = nb_grid_density(sc.density, m, nb_grid_point(m, o));
+    if (m.type >= NB_MEDIUM_HETEROGENEOUS) dens = nb_grid_density(sc.density, m, nb_grid_point(m, o));
     float hit = 0.f, len = 0.f, tr = 0.f;
     const f3 to = o + d * maxt;
     for (uint32_t k = 0; k < samples; ++k) {

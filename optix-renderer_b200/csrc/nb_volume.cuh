@@ -113,14 +113,26 @@ __device__ __forceinline__ float nb_grid_density(const float *density, const nb_
     const float u = p.x - fx, v = p.y - fy, w = p.z - fz;
     const int nx = (int) m.grid_dims[0], ny = (int) m.grid_dims[1], nz = (int) m.grid_dims[2];
     const int i = min(max((int) fx, 1), nx - 2), j = min(max((int) fy, 1), ny - 2), k = min(max((int) fz, 1), nz - 2);
-    const float *base = density + m.first_voxel + ((size_t) (i - 1) * ny + (j - 1)) * nz + (k - 1);
+    const float *base = density + m.first_voxel;
+    size_t sx, sy;                                     /* strides of one step in x / y; z is contiguous in both layouts */
+    if (m.type == NB_MEDIUM_HETEROGENEOUS_BRICKS) {
+        /* sparse grid (include/norib200.h): table entry of the 8^3 block -> its 10^3 brick, whose apron holds the stencil */
+        const int by = (ny + 7) >> 3, bz = (nz + 7) >> 3;
+        const size_t entries = (size_t) ((nx + 7) >> 3) * by * bz;
+        const uint32_t brick = __float_as_uint(__ldg(base + ((size_t) (i >> 3) * by + (j >> 3)) * bz + (k >> 3)));
+        base += entries + (size_t) brick * NB_BRICK_VOXELS + ((i & 7) * NB_BRICK_EDGE + (j & 7)) * NB_BRICK_EDGE + (k & 7);
+        sx = NB_BRICK_EDGE * NB_BRICK_EDGE; sy = NB_BRICK_EDGE;
+    } else {
+        base += ((size_t) (i - 1) * ny + (j - 1)) * nz + (k - 1);
+        sx = (size_t) ny * nz; sy = (size_t) nz;
+    }
     float vx[3];
 #pragma unroll
     for (int dx = 0; dx < 3; ++dx) {
         float vy[3];
 #pragma unroll
         for (int dy = 0; dy < 3; ++dy) {
-            const float *row = base + ((size_t) dx * ny + dy) * nz;
+            const float *row = base + dx * sx + dy * sy;
             vy[dy] = nb_quad_kernel(__ldg(row), __ldg(row + 1), __ldg(row + 2), w);
         }
         vx[dx] = nb_quad_kernel(vy[0], vy[1], vy[2], v);
@@ -192,7 +204,7 @@ template <bool EXT = true>
 __device__ __forceinline__ float nb_free_path(const NbDeviceScene &sc, int32_t medium, f3 o, f3 d, NbRng &rng) {
     if (medium < 0) return INFINITY;
     const nb_medium &m = sc.media[medium];
-    if (EXT && m.type == NB_MEDIUM_HETEROGENEOUS) return nb_free_path_heterog(sc, medium, o, d, rng);
+    if (EXT && m.type >= NB_MEDIUM_HETEROGENEOUS) return nb_free_path_heterog(sc, medium, o, d, rng);
     if (m.type != NB_MEDIUM_HOMOGENEOUS) return INFINITY;
     const int ch = (int) (3.f * rng.next_float());                       /* homogmedium.cpp:62-66 */
     const float mu = m.mu_t[ch];
@@ -205,7 +217,7 @@ template <bool EXT = true>
 __device__ __forceinline__ f3 nb_transmittance(const NbDeviceScene &sc, int32_t medium, f3 from, f3 to, NbRng &rng) {
     if (medium < 0) return mk3(1.f);
     const nb_medium &m = sc.media[medium];
-    if (EXT && m.type == NB_MEDIUM_HETEROGENEOUS) return nb_transmittance_heterog(sc, medium, from, to, rng);
+    if (EXT && m.type >= NB_MEDIUM_HETEROGENEOUS) return nb_transmittance_heterog(sc, medium, from, to, rng);
     if (m.type != NB_MEDIUM_HOMOGENEOUS) return mk3(1.f);
     const float dist = length(from - to);                                /* homogmedium.cpp:68-72 */
     return mk3(__expf(-m.mu_t[0] * dist), __expf(-m.mu_t[1] * dist), __expf(-m.mu_t[2] * dist));

@@ -1,5 +1,8 @@
 /* capi.cpp — a small C surface over the host library so the Python tests can drive it:
  * load a scene XML, flatten it (plugins' hooks + BVH build), write the result as .nbs. No GPU. */
+#include <climits>
+#include <cmath>
+#include <cstring>
 #include "plugins.h"
 #include <memory>
 
@@ -88,12 +91,49 @@ extern "C" int nbh_vdb_to_nbv(const char *vdb_path, const char *grid, const char
 }
 
 /* .vdb / .nbv / .nvdb -> .nvdb: the NanoVDB cache the reference would write (NvdbVolume.vdb.cpp:83-134) */
-extern "C" int nbh_to_nvdb(const char *src_path, const char *grid, const char *nvdb_path) {
+extern "C" int nbh_to_nvdb(const char *src_path, const char *grid, const char *nvdb_path, int sparse) {
     try {
         const std::string p(src_path);
         const std::string ext = p.rfind('.') == std::string::npos ? "" : p.substr(p.rfind('.'));
         nori::VdbGrid g = ext == ".nbv" ? nori::vdbReadNbv(p) : ext == ".nvdb" ? nori::nvdbReadFloatGrid(p, grid) : nori::vdbReadFloatGrid(p, grid);
         if (g.name.empty() || ext == ".nbv") g.name = grid;          /* a .nbv dump carries no grid name */
+        nori::nvdbWriteFloatGrid(sparse ? nori::vdbSparsify(g) : g, nvdb_path);    /* sparse: only blocks that hold something other than background */
+        return 0;
+    } catch (const std::exception &e) { g_error = e.what(); return -1; }
+}
+
+/* A sparse float grid from a list of 8^3 blocks (origins multiples of 8, 512 values each, x slowest), written as .nvdb:
+ * voxels that differ from the background are the active ones. index_to_world: row-major 3x4. */
+extern "C" int nbh_nvdb_write_leaves(const char *nvdb_path, const char *grid, uint64_t n_leaves, const int32_t *origins, const float *values,
+                                     const double *index_to_world, float background) {
+    try {
+        nori::VdbGrid g;
+        g.name = grid; g.type = "NanoVDB float"; g.background = background;
+        for (int i = 0; i < 12; ++i) g.index_to_world[i] = index_to_world[i];
+        g.value_min = INFINITY; g.value_max = -INFINITY;
+        int lo[3] = { INT32_MAX, INT32_MAX, INT32_MAX }, hi[3] = { INT32_MIN, INT32_MIN, INT32_MIN };
+        for (uint64_t n = 0; n < n_leaves; ++n) {
+            nori::VdbLeaf l;
+            for (int a = 0; a < 3; ++a) {
+                l.org[a] = origins[3 * n + a];
+                if (l.org[a] & 7) throw nori::NoriException("nbh_nvdb_write_leaves: block %llu does not start at a multiple of 8", (unsigned long long) n);
+            }
+            memcpy(l.v, values + 512 * n, sizeof(l.v));
+            memset(l.mask, 0, sizeof(l.mask));
+            for (int v = 0; v < 512; ++v) {
+                if (l.v[v] == background) continue;
+                l.mask[v >> 6] |= 1ull << (v & 63);
+                ++g.active_voxels;
+                g.value_min = std::min(g.value_min, l.v[v]); g.value_max = std::max(g.value_max, l.v[v]);
+                const int c[3] = { l.org[0] + (v >> 6), l.org[1] + ((v >> 3) & 7), l.org[2] + (v & 7) };
+                for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], c[a]); hi[a] = std::max(hi[a], c[a]); }
+            }
+            g.leaves.push_back(l);
+        }
+        if (!g.active_voxels) throw nori::NoriException("nbh_nvdb_write_leaves: no voxel differs from the background");
+        for (int a = 0; a < 3; ++a) { g.bbox_min[a] = lo[a]; g.bbox_max[a] = hi[a]; g.dims[a] = hi[a] - lo[a] + 1; }
+        g.indexLeaves();
+        if (g.leafIndex.size() != g.leaves.size()) throw nori::NoriException("nbh_nvdb_write_leaves: two blocks share an origin");
         nori::nvdbWriteFloatGrid(g, nvdb_path);
         return 0;
     } catch (const std::exception &e) { g_error = e.what(); return -1; }

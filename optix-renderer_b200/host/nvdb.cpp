@@ -22,6 +22,7 @@
 #include <climits>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 
@@ -78,11 +79,85 @@ std::vector<uint8_t> readFile(const std::string &path) {
     return data;
 }
 
+/* the grid's leaves as they are, plus lower-level value tiles (8^3 constant) that differ from the background as leaves of
+ * their own; a 128^3 value tile that differs from the background has no place in a leaf list */
+void readSparse(const Blob &b, uint32_t nUpper, uint32_t nLower, uint32_t nLeaf, VdbGrid &g, const std::string &path) {
+    g.leaves.reserve(nLeaf);
+    for (uint32_t n = 0; n < nLeaf; ++n) {
+        const uint8_t *f = b.leaf + (size_t) n * LEAF_BYTES;
+        VdbLeaf l;
+        for (int a = 0; a < 3; ++a) l.org[a] = rd<int32_t>(f + 4 * a) & ~7;
+        memcpy(l.v, f + LEAF_VALUES, sizeof(l.v));
+        memcpy(l.mask, f + LEAF_MASK, sizeof(l.mask));
+        g.leaves.push_back(l);
+    }
+    for (uint32_t n = 0; n < nLower; ++n) {
+        const uint8_t *l = b.lower + (size_t) n * LOWER_BYTES;
+        int org[3];
+        for (int a = 0; a < 3; ++a) org[a] = rd<int32_t>(l + 4 * a) & ~127;
+        for (uint32_t t = 0; t < 4096; ++t) {
+            if (bit(l + LOWER_CHILD_MASK, t)) continue;
+            const float v = rd<float>(l + LOWER_TABLE + 4 * (size_t) t);
+            const bool active = bit(l + 32, t);
+            if (v == b.background && !active) continue;
+            VdbLeaf c;
+            c.org[0] = org[0] + (int) (t >> 8) * 8; c.org[1] = org[1] + (int) ((t >> 4) & 15) * 8; c.org[2] = org[2] + (int) (t & 15) * 8;
+            std::fill(c.v, c.v + 512, v);
+            std::fill(c.mask, c.mask + 8, active ? ~0ull : 0ull);
+            g.leaves.push_back(c);
+        }
+    }
+    for (uint32_t n = 0; n < nUpper; ++n) {
+        const uint8_t *u = b.upper + (size_t) n * UPPER_BYTES;
+        for (uint32_t t = 0; t < 32768; ++t)
+            if (!bit(u + UPPER_CHILD_MASK, t) && (rd<float>(u + UPPER_TABLE + 4 * (size_t) t) != b.background || bit(u + 32, t)))
+                throw NoriException("%s: the grid holds a 128^3 value tile that differs from the background; not supported in the sparse form", path);
+    }
+    for (auto &t : b.tiles)
+        if (rd<int32_t>(t.second + 8) < 0 && (rd<float>(t.second + 16) != b.background || rd<uint32_t>(t.second + 12)))
+            throw NoriException("%s: the grid holds a 4096^3 value tile that differs from the background; not supported in the sparse form", path);
+    g.indexLeaves();
+}
+
 } // namespace
+
+VdbGrid vdbSparsify(const VdbGrid &src) {
+    if (src.sparse()) return src;
+    VdbGrid g = src;
+    g.values.clear(); g.leaves.clear();
+    g.active_voxels = 0; g.value_min = INFINITY; g.value_max = -INFINITY;
+    int lo[3] = { INT32_MAX, INT32_MAX, INT32_MAX }, hi[3] = { INT32_MIN, INT32_MIN, INT32_MIN };
+    if (!src.values.empty())
+        for (int x = src.bbox_min[0] & ~7; x <= src.bbox_max[0]; x += 8)
+            for (int y = src.bbox_min[1] & ~7; y <= src.bbox_max[1]; y += 8)
+                for (int z = src.bbox_min[2] & ~7; z <= src.bbox_max[2]; z += 8) {
+                    VdbLeaf l;
+                    l.org[0] = x; l.org[1] = y; l.org[2] = z;
+                    memset(l.mask, 0, sizeof(l.mask));
+                    uint32_t active = 0;
+                    for (int n = 0; n < 512; ++n) {
+                        const int i = x + (n >> 6), j = y + ((n >> 3) & 7), k = z + (n & 7);
+                        const float v = src.at(i, j, k);
+                        l.v[n] = v;
+                        if (v == src.background) continue;
+                        l.mask[n >> 6] |= 1ull << (n & 63);
+                        ++active;
+                        g.value_min = std::min(g.value_min, v); g.value_max = std::max(g.value_max, v);
+                        const int c[3] = { i, j, k };
+                        for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], c[a]); hi[a] = std::max(hi[a], c[a]); }
+                    }
+                    if (active) { g.leaves.push_back(l); g.active_voxels += active; }
+                }
+    if (!g.active_voxels) { g.value_min = g.value_max = src.background; g.bbox_min[0] = g.bbox_min[1] = g.bbox_min[2] = 0; g.bbox_max[0] = g.bbox_max[1] = g.bbox_max[2] = -1; }
+    else for (int a = 0; a < 3; ++a) { g.bbox_min[a] = lo[a]; g.bbox_max[a] = hi[a]; }
+    for (int a = 0; a < 3; ++a) g.dims[a] = g.bbox_max[a] - g.bbox_min[a] + 1;
+    g.indexLeaves();
+    return g;
+}
 
 /* nanovdb::io::readGrid(file, gridName) (NvdbVolume.vdb.cpp:42-61): the named float grid — or the first one when the name is
  * empty — as the dense box the volume kernels sample: getValue over the index bounding box, background elsewhere. */
-VdbGrid nvdbReadFloatGrid(const std::string &path, const std::string &gridName) {
+VdbGrid nvdbReadFloatGrid(const std::string &path, const std::string &gridName, bool keepSparse) {
     const std::vector<uint8_t> data = readFile(path);
     size_t pos = 0;
     while (pos + HEADER_BYTES <= data.size()) {
@@ -147,8 +222,13 @@ VdbGrid nvdbReadFloatGrid(const std::string &path, const std::string &gridName) 
                 for (int a = 0; a < 3; ++a) empty = empty || g.bbox_max[a] < g.bbox_min[a];
                 if (empty) { g.bbox_max[0] = g.bbox_max[1] = g.bbox_max[2] = -1; g.bbox_min[0] = g.bbox_min[1] = g.bbox_min[2] = 0; return g; }
                 const uint64_t vox = (uint64_t) (g.bbox_max[0] - g.bbox_min[0] + 1) * (uint64_t) (g.bbox_max[1] - g.bbox_min[1] + 1) * (uint64_t) (g.bbox_max[2] - g.bbox_min[2] + 1);
-                if (vox > (1ull << 31)) throw NoriException("%s: grid '%s': a dense copy of its %llu-voxel box does not fit the volume kernels' layout", path, meta.name, (unsigned long long) vox);
                 for (int a = 0; a < 3; ++a) g.dims[a] = g.bbox_max[a] - g.bbox_min[a] + 1;
+                /* sparse form: the file's leaves as they are, when the caller can take them and the box is mostly background
+                 * or too large to fill (NB_VOLUME_SPARSE=1 / 0 forces the choice, for tests) */
+                const char *force = getenv("NB_VOLUME_SPARSE");
+                const bool wantSparse = force ? atoi(force) != 0 : (vox > (1ull << 27) || (uint64_t) nLeaf * 512 * 4 < vox);
+                if (keepSparse && nLeaf > 0 && wantSparse) { readSparse(b, nUpper, nLower, nLeaf, g, path); return g; }
+                if (vox > (1ull << 31)) throw NoriException("%s: grid '%s': a dense copy of its %llu-voxel box does not fit the volume kernels' layout", path, meta.name, (unsigned long long) vox);
                 g.values.resize((size_t) vox);
                 size_t n = 0;
                 for (int i = 0; i < g.dims[0]; ++i)
@@ -202,24 +282,25 @@ int floorTo(int v, int step) { return v & ~(step - 1); }     /* two's complement
  * origin), uncompressed, no checksum. The reference's own reader (nanovdb::io::readGrid) reads it back voxel for voxel, with
  * the same bounding boxes, active count, min / max (tests/test_volume_cpu.py through oracle/_ref/nvdb_tool). */
 void nvdbWriteFloatGrid(const VdbGrid &g, const std::string &path) {
-    if (g.values.size() != (size_t) g.dims[0] * g.dims[1] * g.dims[2]) throw NoriException("nvdbWriteFloatGrid: grid '%s' is inconsistent", g.name);
+    if (!g.sparse() && g.values.size() != (size_t) g.dims[0] * g.dims[1] * g.dims[2]) throw NoriException("nvdbWriteFloatGrid: grid '%s' is inconsistent", g.name);
     /* upper node (root tile key; tiles are kept sorted by key) -> lower node (its index in the upper) -> leaf (its index in the
      * lower): map order is array order at every level */
-    struct Org { int v[3]; };
+    struct Org { int v[3]; int32_t src; };                 /* src: index into g.leaves (sparse form) or -1 (fill from the dense box) */
     std::map<uint64_t, std::map<uint32_t, std::map<uint32_t, Org>>> tree;
-    std::map<uint64_t, Org> upperOrg;
     size_t nLeaves = 0;
-    if (!g.values.empty())
+    auto place = [&](int x, int y, int z, int32_t src) {
+        const uint64_t key = (uint64_t) ((uint32_t) z >> 12) | ((uint64_t) ((uint32_t) y >> 12) << 21) | ((uint64_t) ((uint32_t) x >> 12) << 42);
+        const uint32_t nu = (((uint32_t) x & 4095u) >> 7) << 10 | (((uint32_t) y & 4095u) >> 7) << 5 | (((uint32_t) z & 4095u) >> 7);
+        const uint32_t nl = (((uint32_t) x & 127u) >> 3) << 8 | (((uint32_t) y & 127u) >> 3) << 4 | (((uint32_t) z & 127u) >> 3);
+        tree[key][nu][nl] = { { x, y, z }, src };
+        ++nLeaves;
+    };
+    if (g.sparse())
+        for (size_t n = 0; n < g.leaves.size(); ++n) place(g.leaves[n].org[0], g.leaves[n].org[1], g.leaves[n].org[2], (int32_t) n);
+    else if (!g.values.empty())
         for (int x = floorTo(g.bbox_min[0], 8); x <= g.bbox_max[0]; x += 8)
             for (int y = floorTo(g.bbox_min[1], 8); y <= g.bbox_max[1]; y += 8)
-                for (int z = floorTo(g.bbox_min[2], 8); z <= g.bbox_max[2]; z += 8) {
-                    const uint64_t key = (uint64_t) ((uint32_t) z >> 12) | ((uint64_t) ((uint32_t) y >> 12) << 21) | ((uint64_t) ((uint32_t) x >> 12) << 42);
-                    const uint32_t nu = (((uint32_t) x & 4095u) >> 7) << 10 | (((uint32_t) y & 4095u) >> 7) << 5 | (((uint32_t) z & 4095u) >> 7);
-                    const uint32_t nl = (((uint32_t) x & 127u) >> 3) << 8 | (((uint32_t) y & 127u) >> 3) << 4 | (((uint32_t) z & 127u) >> 3);
-                    tree[key][nu][nl] = { { x, y, z } };
-                    upperOrg[key] = { { floorTo(x, 4096), floorTo(y, 4096), floorTo(z, 4096) } };
-                    ++nLeaves;
-                }
+                for (int z = floorTo(g.bbox_min[2], 8); z <= g.bbox_max[2]; z += 8) place(x, y, z, -1);
     uint32_t nUpper = (uint32_t) tree.size(), nLower = 0, nLeaf = (uint32_t) nLeaves;
     for (auto &u : tree) nLower += (uint32_t) u.second.size();
     const uint32_t nTiles = nUpper;
@@ -246,19 +327,23 @@ void nvdbWriteFloatGrid(const VdbGrid &g, const std::string &path) {
                 uint8_t *fn = leaf + (size_t) iLeaf * LEAF_BYTES;
                 const int *o = f.second.v;
                 Stats fs;
+                const VdbLeaf *src = f.second.src >= 0 ? &g.leaves[(size_t) f.second.src] : nullptr;
                 for (int n = 0; n < 512; ++n) {
                     const int x = o[0] + (n >> 6), y = o[1] + ((n >> 3) & 7), z = o[2] + (n & 7);
                     float v = g.background;
-                    if (inside(x, y, z)) {
+                    bool active = false;
+                    if (src) { v = src->v[n]; active = (src->mask[n >> 6] >> (n & 63)) & 1u; }
+                    else if (inside(x, y, z)) {
                         v = g.values[((size_t) (x - g.bbox_min[0]) * dy + (size_t) (y - g.bbox_min[1])) * dz + (size_t) (z - g.bbox_min[2])];
-                        setBit(fn + LEAF_MASK, (uint32_t) n);
-                        fs.add(v, x, y, z);
+                        active = true;
                     }
+                    if (active) { setBit(fn + LEAF_MASK, (uint32_t) n); fs.add(v, x, y, z); }
                     wr<float>(fn + LEAF_VALUES + 4 * (size_t) n, v);
                 }
+                if (!fs.n) for (int a = 0; a < 3; ++a) fs.lo[a] = fs.hi[a] = o[a];          /* a leaf without active voxels keeps its origin */
                 for (int a = 0; a < 3; ++a) { wr<int32_t>(fn + 4 * a, fs.lo[a]); fn[12 + a] = (uint8_t) (fs.hi[a] - fs.lo[a]); }
                 fn[15] = 2;                                                             /* LeafData::mFlags: the bounding box is set */
-                wr<float>(fn + 80, fs.mn); wr<float>(fn + 84, fs.mx); wr<float>(fn + 88, fs.avg()); wr<float>(fn + 92, fs.dev());
+                wr<float>(fn + 80, fs.n ? fs.mn : g.background); wr<float>(fn + 84, fs.n ? fs.mx : g.background); wr<float>(fn + 88, fs.avg()); wr<float>(fn + 92, fs.dev());
                 setBit(ln + LOWER_CHILD_MASK, f.first);
                 wr<int32_t>(ln + LOWER_TABLE + 4 * (size_t) f.first, (int32_t) iLeaf);
                 ls.merge(fs);

@@ -480,22 +480,74 @@ NORI_REGISTER_CLASS(HomogeneousMedium, "homog")
  * grid goes to the GPU as a dense array (include/norib200.h, nb_medium). */
 class NvdbVolume : public NoriObject {
 public:
-    explicit NvdbVolume(const PropertyList &p) : m_filename(resolvePath(p.getString("filename"))) {}
+    explicit NvdbVolume(const PropertyList &p) : layout(p.getString("layout", "auto")), m_filename(resolvePath(p.getString("filename"))) {
+        if (const char *env = getenv("NB_VOLUME_LAYOUT")) layout = env;
+        if (layout != "auto" && layout != "dense" && layout != "bricks") throw NoriException("Volume: layout '%s' unknown (auto, dense, bricks)", layout);
+    }
     EClassType getClassType() const override { return EVolume; }
     void activate() override {                          /* NvdbVolume::loadFromFile (NvdbVolume.vdb.cpp:9-40) */
         const size_t dot = m_filename.rfind('.');
         const std::string ext = dot == std::string::npos ? "" : m_filename.substr(dot);
-        if (ext == ".nvdb") { density = nvdbReadFloatGrid(m_filename, "density"); return; }     /* the reference's cache format (nvdb.cpp) */
+        if (ext == ".nvdb") { density = nvdbReadFloatGrid(m_filename, "density", layout != "dense"); return; }     /* the reference's cache format (nvdb.cpp); leaves kept as they are when the box is mostly empty */
         if (ext == ".nbv") { density = vdbReadNbv(m_filename); return; }     /* dense dump (vdb.h) */
         if (ext != ".vdb") throw NoriException("Volume: file extension %s unknown.", ext);
         density = vdbReadFloatGrid(m_filename, "density");
     }
     std::string toString() const override { return "Volume[\n  filename = " + m_filename + ",\n]"; }
     VdbGrid density;
+    /* how the grid goes to the GPU (include/norib200.h, nb_medium) — a property of this backend, not of the reference:
+     * "dense", "bricks" (sparse), or "auto": bricks when they take less than half of what the dense box takes */
+    std::string layout;
 private:
     std::string m_filename;
 };
 NORI_REGISTER_CLASS(NvdbVolume, "volume")
+
+/* The sparse device layout (include/norib200.h, NB_MEDIUM_HETEROGENEOUS_BRICKS): blocks of 8^3 voxels of the virtual array
+ * (origin `org` in index space, `dims` voxels), each stored with a one-voxel apron — 10^3 floats — when anything in those 10^3
+ * differs from the background; brick 0 is the background. A sparse source only visits the blocks its leaves can touch. */
+static void buildBricks(const VdbGrid &g, const uint32_t dims[3], const int org[3], std::vector<uint32_t> &table, std::vector<float> &payload) {
+    const int nb[3] = { (int) (dims[0] + 7) / 8, (int) (dims[1] + 7) / 8, (int) (dims[2] + 7) / 8 };
+    const uint64_t entries = (uint64_t) nb[0] * nb[1] * nb[2];
+    if (entries > (1ull << 30)) throw NoriException("HeterogeneousMedium: a brick table of %llu entries is too large", (unsigned long long) entries);
+    table.assign((size_t) entries, 0u);
+    payload.assign(NB_BRICK_VOXELS, g.background);
+    std::vector<uint8_t> candidate;
+    if (g.sparse()) {
+        candidate.assign((size_t) entries, 0);
+        for (const VdbLeaf &l : g.leaves) {
+            int lo[3], hi[3];
+            for (int a = 0; a < 3; ++a) {
+                const int a0 = l.org[a] - org[a];                                   /* array coordinates of the leaf: a0 .. a0 + 7 */
+                lo[a] = std::max(0, (a0 - 1) >> 3); hi[a] = std::min(nb[a] - 1, (a0 + 8) >> 3);
+            }
+            for (int i = lo[0]; i <= hi[0]; ++i)
+                for (int j = lo[1]; j <= hi[1]; ++j)
+                    for (int k = lo[2]; k <= hi[2]; ++k) candidate[((size_t) i * nb[1] + j) * nb[2] + k] = 1;
+        }
+    }
+    float brick[NB_BRICK_VOXELS];
+    for (int i = 0; i < nb[0]; ++i)
+        for (int j = 0; j < nb[1]; ++j)
+            for (int k = 0; k < nb[2]; ++k) {
+                const size_t e = ((size_t) i * nb[1] + j) * nb[2] + k;
+                if (!candidate.empty() && !candidate[e]) continue;
+                bool any = false;
+                int n = 0;
+                for (int x = 0; x < NB_BRICK_EDGE; ++x)
+                    for (int y = 0; y < NB_BRICK_EDGE; ++y)
+                        for (int z = 0; z < NB_BRICK_EDGE; ++z) {
+                            const float v = g.at(org[0] + i * 8 - 1 + x, org[1] + j * 8 - 1 + y, org[2] + k * 8 - 1 + z);
+                            brick[n++] = v;
+                            any = any || v != g.background;
+                        }
+                if (!any) continue;
+                const uint64_t id = payload.size() / NB_BRICK_VOXELS;
+                if (id >= 0x7f800000ull) throw NoriException("HeterogeneousMedium: too many bricks");
+                table[e] = (uint32_t) id;
+                payload.insert(payload.end(), brick, brick + NB_BRICK_VOXELS);
+            }
+}
 
 class HeterogeneousMedium : public Medium {         /* heterogmedium.cpp:47-103 */
 public:
@@ -518,20 +570,38 @@ public:
         const VdbGrid &g = m_volume->density;
         if (m_emitter || m_temperatureScale > 1e-4f) return false;     /* volume emission: no kernel */
         if (g.active_voxels == 0 || !(g.value_max > 0.f)) return false;
-        out.type = NB_MEDIUM_HETEROGENEOUS;
+        out.type = NB_MEDIUM_HETEROGENEOUS;                              /* or _BRICKS, below */
         for (int i = 0; i < 3; ++i) out.mu_t[i] = m_sigma_a[i] + m_sigma_s[i];
         m_phase->getB200PhaseData(out);
         out.density_scale = m_densityScale;
         out.max_density = g.value_max;
-        /* dense array = active box + border, read through getValue so stored inactive values survive */
+        /* virtual array = active box + border, read through getValue so stored inactive values survive */
         const int B = NB_GRID_BORDER;
         int org[3];
         for (int a = 0; a < 3; ++a) { out.grid_dims[a] = (uint32_t) (g.dims[a] + 2 * B); org[a] = g.bbox_min[a] - B; }
+        const uint64_t vox = (uint64_t) out.grid_dims[0] * out.grid_dims[1] * out.grid_dims[2];
+        if (flat.density.size() > 0xffffffffull) throw NoriException("HeterogeneousMedium: the density array is full");
         out.first_voxel = (uint32_t) flat.density.size();
-        flat.density.reserve(flat.density.size() + (size_t) out.grid_dims[0] * out.grid_dims[1] * out.grid_dims[2]);
-        for (int i = 0; i < (int) out.grid_dims[0]; ++i)
-            for (int j = 0; j < (int) out.grid_dims[1]; ++j)
-                for (int k = 0; k < (int) out.grid_dims[2]; ++k) flat.density.push_back(g.at(org[0] + i, org[1] + j, org[2] + k));
+        bool bricks = g.sparse() || m_volume->layout == "bricks";
+        std::vector<uint32_t> table;
+        std::vector<float> payload;
+        if (bricks || (m_volume->layout == "auto" && vox >= (1ull << 24))) {
+            buildBricks(g, out.grid_dims, org, table, payload);
+            if (!bricks) bricks = (table.size() + payload.size()) * 2 < vox;
+        }
+        if (bricks) {
+            out.type = NB_MEDIUM_HETEROGENEOUS_BRICKS;
+            const size_t at = flat.density.size();
+            flat.density.resize(at + table.size() + payload.size());
+            memcpy(flat.density.data() + at, table.data(), table.size() * 4);
+            memcpy(flat.density.data() + at + table.size(), payload.data(), payload.size() * 4);
+        } else {
+            if (vox > (1ull << 31)) throw NoriException("HeterogeneousMedium: a dense copy of the grid's %llu-voxel box does not fit; use layout=bricks", (unsigned long long) vox);
+            flat.density.reserve(flat.density.size() + (size_t) vox);
+            for (int i = 0; i < (int) out.grid_dims[0]; ++i)
+                for (int j = 0; j < (int) out.grid_dims[1]; ++j)
+                    for (int k = 0; k < (int) out.grid_dims[2]; ++k) flat.density.push_back(g.at(org[0] + i, org[1] + j, org[2] + k));
+        }
         /* world -> index (inverse of the grid's affine map, in double), then index -> array coordinates */
         const double *M = g.index_to_world;
         const double a = M[0], b = M[1], c = M[2], d = M[4], e = M[5], f = M[6], gg = M[8], h = M[9], k = M[10];

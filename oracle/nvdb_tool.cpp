@@ -8,6 +8,7 @@
  *                                            widened by 2 voxels: i32 min[3], i32 dims[3], f64 index_to_world[12],
  *                                            f32 background, min, max, u64 active voxels, then the values (x slowest)
  *                                            — what the reference would see in a file written by host/nvdb.cpp
+ *   nvdb_tool info in.nvdb                   the same reader on a grid too large to dump: box, active count, getValue probes
  */
 #include <cstdio>
 #include <cstring>
@@ -96,12 +97,37 @@ static int modeDump(int argc, char **argv) {
     return 0;
 }
 
+/* info in.nvdb: what nanovdb::io::readGrid sees of a grid too large to dump — bounding box, active count, and getValue at
+ * voxel (1, 2, 3) of the leaves that hold the box's minimum corner, its middle and its maximum corner, and at one empty place */
+static int modeInfo(int argc, char **argv) {
+    if (argc < 3) return 2;
+    auto handle = nanovdb::io::readGrid(argv[2], 0);
+    const auto *grid = handle.grid<float>();
+    if (!grid) return fail("no float grid in the file");
+    const nanovdb::CoordBBox box = grid->indexBBox();
+    auto acc = grid->getAccessor();
+    float probe[4];
+    int n = 0;
+    for (int leaf = 0; leaf < (int) grid->tree().nodeCount(0) && n < 3; ++leaf) {
+        const auto *l = grid->tree().getNode<0>(leaf);
+        const nanovdb::Coord o = l->origin();
+        probe[n++] = acc.getValue(nanovdb::Coord(o[0] + 1, o[1] + 2, o[2] + 3));
+    }
+    for (; n < 3; ++n) probe[n] = 0.f;
+    probe[3] = acc.getValue(nanovdb::Coord(box.min()[0] + 100, box.min()[1] + 100, box.min()[2] + 100));
+    printf("{\"mode\": \"info\", \"active\": %llu, \"min\": [%d, %d, %d], \"max\": [%d, %d, %d], \"leaves\": %u, \"probe\": [%.9g, %.9g, %.9g, %.9g]}\n",
+           (unsigned long long) grid->activeVoxelCount(), box.min()[0], box.min()[1], box.min()[2], box.max()[0], box.max()[1], box.max()[2],
+           (unsigned) grid->tree().nodeCount(0), probe[0], probe[1], probe[2], probe[3]);
+    return 0;
+}
+
 int main(int argc, char **argv) {
     if (argc < 2) return fail("usage: nvdb_tool write in.nbv out.nvdb [name] | dump in.nvdb out.bin [grid name]");
     try {
         int rc = 2;
         if (!strcmp(argv[1], "write")) rc = modeWrite(argc, argv);
         else if (!strcmp(argv[1], "dump")) rc = modeDump(argc, argv);
+        else if (!strcmp(argv[1], "info")) rc = modeInfo(argc, argv);
         if (rc == 2) return fail("usage: nvdb_tool write in.nbv out.nvdb [name] | dump in.nvdb out.bin [grid name]");
         return rc;
     } catch (const std::exception &e) {

@@ -192,3 +192,104 @@ def test_scene_naming_a_nvdb_file(nb, built_lib):
     assert np.array_equal(a["density"], b["density"])
     for key in ("grid_dims", "world_to_grid", "mu_t", "max_density", "density_scale", "first_voxel"):
         assert np.array_equal(np.asarray(a["media"][0][key]), np.asarray(b["media"][0][key])), key
+
+
+# ---- sparse grids: leaves kept as they are on the host, 10^3 bricks behind a table on the device (include/norib200.h) --------
+def expand_bricks(density, m):
+    """The virtual dense array a NB_MEDIUM_HETEROGENEOUS_BRICKS record describes, and the stencil property of every brick."""
+    nx, ny, nz = (int(v) for v in m["grid_dims"])
+    nb = [(v + 7) // 8 for v in (nx, ny, nz)]
+    first = int(m["first_voxel"])
+    entries = nb[0] * nb[1] * nb[2]
+    table = density[first:first + entries].view("<u4").reshape(nb)
+    bricks = density[first + entries:].reshape(-1, 10, 10, 10)[: int(table.max()) + 1]
+    full = np.zeros([8 * b + 2 for b in nb], np.float32)              # array coordinates -1 .. 8 nb
+    for (i, j, k), b in np.ndenumerate(table):
+        full[8 * i + 1:8 * i + 9, 8 * j + 1:8 * j + 9, 8 * k + 1:8 * k + 9] = bricks[b][1:9, 1:9, 1:9]
+    for (i, j, k), b in np.ndenumerate(table):                        # aprons repeat the neighbours' voxels
+        assert np.array_equal(full[8 * i:8 * i + 10, 8 * j:8 * j + 10, 8 * k:8 * k + 10], bricks[b]), (i, j, k)
+    return full[1:nx + 1, 1:ny + 1, 1:nz + 1], table, bricks
+
+
+def test_brick_layout_of_the_fluid_equals_its_dense_array(nb, built_lib, monkeypatch):
+    dense = nb.load_xml(golden("scenes/vol/cbox_heterog.xml"))
+    monkeypatch.setenv("NB_VOLUME_LAYOUT", "bricks")
+    s = nb.load_xml(golden("scenes/vol/cbox_heterog.xml"))
+    m, d = s["media"][0], dense["media"][0]
+    assert m["type"] == nb.MEDIUM_HETEROGENEOUS_BRICKS and d["type"] == nb.MEDIUM_HETEROGENEOUS
+    for key in ("grid_dims", "world_to_grid", "mu_t", "max_density", "density_scale"):
+        assert np.array_equal(np.asarray(m[key]), np.asarray(d[key])), key
+    full, table, bricks = expand_bricks(s["density"], m)
+    assert np.array_equal(full, dense["density"].reshape(25, 25, 36))
+    assert not bricks[0].any() and table.shape == (4, 4, 5)
+
+
+def test_sparse_nvdb_stays_sparse_on_the_way_to_the_device(nb, built_lib, monkeypatch):
+    """sparse_smoke.nvdb (tests/golden/make_nvdb.py): 2 puffs in a 96 x 48 x 120 box. The host keeps the file's leaves, the
+    device record is the brick layout, and both describe the voxels a dense read of the same file gives."""
+    g = nb.vdb_read(golden("scenes/vol/sparse_smoke.nvdb"), "density")            # dense read: box of ACTIVE voxels
+    assert g["active_voxels"] == np.count_nonzero(g["values"]) and 0 < g["active_voxels"] < g["values"].size // 8
+    s = nb.load_xml(golden("scenes/vol/cbox_sparse_small.xml"))
+    m = s["media"][0]
+    assert m["type"] == nb.MEDIUM_HETEROGENEOUS_BRICKS and m["max_density"] == g["max"]
+    assert list(m["grid_dims"]) == [d + 4 for d in g["values"].shape]
+    full, table, bricks = expand_bricks(s["density"], m)
+    assert np.array_equal(full[2:-2, 2:-2, 2:-2], g["values"]) and not (full[:2].any() or full[-2:].any() or full[:, :2].any() or full[:, :, -2:].any())
+    used = len(bricks) - 1
+    assert used == len(np.unique(table)) - 1 and used * 1000 + table.size < full.size // 2     # the point of the layout
+    monkeypatch.setenv("NB_VOLUME_LAYOUT", "dense")                                # the same file, forced dense: same voxels
+    d = nb.load_xml(golden("scenes/vol/cbox_sparse_small.xml"))
+    assert d["media"][0]["type"] == nb.MEDIUM_HETEROGENEOUS
+    assert np.array_equal(d["density"].reshape(full.shape), full)
+    assert np.array_equal(d["media"][0]["world_to_grid"], m["world_to_grid"])
+
+
+def test_sparse_nvdb_round_trip_keeps_leaves_and_masks(nb, built_lib, tmp_path, monkeypatch):
+    """read sparse -> write -> the same bytes (leaf order, masks, statistics), whatever form the reader chose"""
+    src = golden("scenes/vol/sparse_smoke.nvdb")
+    want = open(src, "rb").read()
+    nb.to_nvdb(src, str(tmp_path / "dense_form.nvdb"), "density", sparse=True)    # via the dense box, re-sparsified
+    assert open(tmp_path / "dense_form.nvdb", "rb").read() == want
+    if os.path.exists(NVDB_TOOL):
+        r = subprocess.run([NVDB_TOOL, "dump", src, str(tmp_path / "dump.bin")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        g = nb.vdb_read(src, "density")
+        assert json.loads(r.stdout)["active"] == g["active_voxels"]
+        raw = (tmp_path / "dump.bin").read_bytes()
+        dd = np.frombuffer(raw, "<i4", 3, 12)
+        seen = np.frombuffer(raw, "<f4", int(np.prod(dd)), 140).reshape(dd)
+        assert np.array_equal(seen[2:-2, 2:-2, 2:-2], g["values"])
+
+
+def test_a_1024_cubed_box_of_sparse_smoke_is_never_filled(nb, built_lib, tmp_path):
+    """Three 8^3 blocks at the corners and the middle of a 1024^3 box: 4.3 GB dense; here the leaves stay leaves on the host,
+    the device record is a 2 M-entry table plus the few bricks those blocks touch, and NanoVDB reads the file."""
+    import shutil
+    rng = np.random.default_rng(3)
+    org = np.array([[0, 0, 0], [504, 512, 520], [1016, 1016, 1016]], "<i4")
+    vals = (rng.random((3, 8, 8, 8), dtype=np.float32) + 0.5).astype("<f4")
+    M = np.array([[0.7 / 1024, 0, 0, 0.08], [0, 1.04 / 1024, 0, 0.02], [0, 0, 0.7 / 1024, -0.05]])
+    for name in ("meshes",):
+        shutil.copytree(golden("scenes/vol/meshes"), tmp_path / name)
+    nb.nvdb_write_leaves(str(tmp_path / "big.nvdb"), org, vals, M)
+    (tmp_path / "scene.xml").write_text(open(golden("scenes/vol/cbox_sparse_small.xml")).read().replace("sparse_smoke.nvdb", "big.nvdb"))
+    s = nb.load_xml(str(tmp_path / "scene.xml"))
+    m = s["media"][0]
+    assert m["type"] == nb.MEDIUM_HETEROGENEOUS_BRICKS and list(m["grid_dims"]) == [1028] * 3
+    entries = 129 ** 3
+    first = int(m["first_voxel"])
+    table = s["density"][first:first + entries].view("<u4").reshape(129, 129, 129)
+    bricks = s["density"][first + entries:].reshape(-1, 10, 10, 10)
+    # a block at array offset 2 (the border) straddles 8 bricks when its apron counts; the three are far apart
+    assert 3 * 8 <= len(bricks) - 1 <= 3 * 27 and s["density"].size < 3 * 10 ** 6
+    for o, v in zip(org, vals):                                                    # voxel (1, 2, 3) of each block, through the table
+        a = o + 2 + np.array([1, 2, 3])
+        b = table[tuple(a >> 3)]
+        assert b != 0 and bricks[b][tuple((a & 7) + 1)] == v[1, 2, 3]
+    assert m["max_density"] == vals.max()
+    if os.path.exists(NVDB_TOOL):
+        r = subprocess.run([NVDB_TOOL, "info", str(tmp_path / "big.nvdb")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        info = json.loads(r.stdout)
+        assert info["active"] == 3 * 512 and info["min"] == [0, 0, 0] and info["max"] == [1023, 1023, 1023]
+        assert info["probe"] == pytest.approx([float(vals[0][1, 2, 3]), float(vals[1][1, 2, 3]), float(vals[2][1, 2, 3]), 0.0])

@@ -64,6 +64,51 @@ def test_nvdb_scene_vs_nanovdb_reading_the_same_file(nb, ctx):
     assert np.all(np.abs(got[both, 2] - want[both, 2]) <= 0.05 * want[both, 2] + 2e-3)
 
 
+def test_brick_layout_is_the_dense_layout_bit_for_bit(nb, ctx, monkeypatch):
+    """NB_MEDIUM_HETEROGENEOUS_BRICKS holds the same voxels behind a table: the same 27 taps in the same order, so densities,
+    tracking results and a render are the dense layout's bits."""
+    xml = golden("scenes/vol/cbox_heterog_fluid_small.xml")
+    rays = np.fromfile(golden("vol_fluid_probe_rays.bin"), "<f4").reshape(-1, 8)
+    out = {}
+    for layout in ("dense", "bricks"):
+        monkeypatch.setenv("NB_VOLUME_LAYOUT", layout)
+        s = nb.load_xml(xml)
+        assert s["media"][0]["type"] == (nb.MEDIUM_HETEROGENEOUS if layout == "dense" else nb.MEDIUM_HETEROGENEOUS_BRICKS)
+        ctx.load(s)
+        probe = ctx.medium_probe(0, rays, samples=512, seed=3)
+        ctx.render_begin(nb.make_render_params(s, seed=4))
+        ctx.render_subframe(0, 8)
+        out[layout] = (probe, ctx.film_download(normalize=True))
+    assert (out["dense"][0][:, 0] != 0).sum() > 100
+    assert np.array_equal(out["dense"][0], out["bricks"][0])
+    assert np.array_equal(out["dense"][1], out["bricks"][1])
+
+
+def test_sparse_scene_vs_nanovdb_reading_the_same_file(nb, ctx):
+    """cbox_sparse_small.xml: a sparse .nvdb (written here, leaves only where there is smoke) -> leaves on the host -> bricks
+    on the device, against nanovdb::io::readGrid + SampleFromVoxels<.., 2> on the same file (tests/golden/make_nvdb.py)."""
+    s = nb.load_xml(golden("scenes/vol/cbox_sparse_small.xml"))
+    assert s["media"][0]["type"] == nb.MEDIUM_HETEROGENEOUS_BRICKS
+    rays = np.fromfile(golden("sparse_probe_rays.bin"), "<f4").reshape(-1, 8)
+    want = np.fromfile(golden("sparse_probe_out.bin"), "<f4").reshape(-1, 4)
+    ctx.load(s)
+    n = 16384
+    got = ctx.medium_probe(0, rays, samples=n, seed=9)
+    print("density max abs diff", np.abs(got[:, 0] - want[:, 0]).max(), "nonzero points", int((want[:, 0] != 0).sum()))
+    np.testing.assert_allclose(got[:, 0], want[:, 0], atol=2e-6, rtol=1e-5)
+    assert (want[:, 0] != 0).sum() > 100
+    p = want[:, 1]
+    tol = 5.0 * np.sqrt(2.0 * np.maximum(p * (1 - p), 1e-4) / n) + 1e-4
+    assert p.max() > 0.5 and np.all(np.abs(got[:, 1] - p) <= tol), np.abs(got[:, 1] - p).max()
+    assert np.all(np.abs(got[:, 3] - want[:, 3]) <= 5.0 * np.sqrt(2.0 * 0.3 / n) + 1e-4), np.abs(got[:, 3] - want[:, 3]).max()
+    both = (p > 0.05)
+    assert np.all(np.abs(got[both, 2] - want[both, 2]) <= 0.05 * want[both, 2] + 2e-3)
+    ctx.render_begin(nb.make_render_params(s, seed=1))                              # and it renders: finite, smoke visible
+    ctx.render_subframe(0, 16)
+    img = ctx.film_download(normalize=True)
+    assert np.isfinite(img).all() and img.mean() > 0.01
+
+
 def render_pair(nb, ctx, xml, spp):
     s = nb.load_xml(golden("scenes/" + xml))
     imgs = []
