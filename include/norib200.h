@@ -326,6 +326,29 @@ int  nb_render_begin(nb_ctx *ctx, const nb_render_params *params);  /* allocates
  * itself ends with cudaStreamSynchronize, OptixState.cpp:507 — call nb_sync for that behaviour.) */
 int  nb_render_subframe(nb_ctx *ctx, uint32_t first, uint32_t count,
                         uint32_t sample_stride, uint32_t sample_offset);
+/* One round of the outer sample loop (render.cpp:283-360) for a scene whose sampler is `adaptive`
+ * (src/samplers/adaptive.cpp): for every block_size^2 block (NORI_BLOCK_SIZE_ADAPTIVE = 4, block.h:31) the loop
+ * `while (sampler->computeVariance(block)) renderBlock(..)` of render.cpp:323-335 — initial_uniform (+1, the reference's
+ * post-increment) passes of one sample per pixel, then passes whose samples are placed by the 3x3 luminance variance of the
+ * block's previous pass (common.cpp:339-399) until the variance map stops settling — run as a feedback loop ON the device:
+ * a decision kernel per pass (one warp per block) writes the list of samples, the render kernel consumes it and feeds the
+ * blocks' own images back; the host reads one word per pass. All blocks advance together; a round ends when no block
+ * goes on. Synchronous. The film accumulates like nb_render_subframe's (the two can be mixed); how many samples a round
+ * draws depends on the image and comes back in `out`. block_size 2..8. round_cap: the sampler's limit of 1000 decisions per
+ * block and round (adaptive.cpp:79), which only black blocks reach — they cost the reference 1000 passes per round, and
+ * cost them here too unless the caller lowers the cap (0 = the reference's 1000). What is kept of the reference's quirks and
+ * why is listed at the decision kernel in csrc/nb_render.cu. */
+typedef struct nb_adaptive_info {
+    uint64_t samples;         /* camera samples drawn in this round */
+    uint64_t block_passes;    /* sum over blocks of the passes each one rendered */
+    uint32_t passes;          /* device passes = the longest block loop */
+    uint32_t blocks;          /* blocks in the image */
+} nb_adaptive_info;
+int  nb_render_adaptive_round(nb_ctx *ctx, uint32_t block_size, uint32_t initial_uniform, uint32_t round_cap, nb_adaptive_info *out);
+/* Passes each block has rendered in adaptive rounds since they began (blocks row-major, ceil(width / block_size) per row) —
+ * what AdaptiveSampler::writeVarianceMatrix's option (a) would show (adaptive.cpp:176-181); the tests compare its
+ * distribution with the reference's. The counts restart when a round uses another block size. */
+int  nb_adaptive_block_passes(nb_ctx *ctx, uint32_t *out, uint32_t n_blocks);
 /* Host-only helper (no device needed): which samples a (first, count, stride, offset) slice holds:
  * *first_sample = smallest s >= first with s % stride == offset, *n_samples = how many such s lie
  * below first+count. The slices of offsets 0..stride-1 partition [first, first+count). */

@@ -90,7 +90,7 @@ class Counters(C.Structure):
 
 
 EXPORTS = ["nb_abi_version", "nb_abi_sizeof", "nb_create", "nb_destroy", "nb_last_error", "nb_upload_scene",
-           "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe",
+           "nb_build_bvh", "nb_trace_rays", "nb_trace_rays_device", "nb_render_begin", "nb_render_subframe", "nb_render_adaptive_round", "nb_adaptive_block_passes",
            "nb_sync", "nb_film_clear", "nb_film_shape", "nb_film_download", "nb_film_device_ptr",
            "nb_get_counters", "nb_set_option", "nb_sample_slice", "nb_bvh_stats", "nb_medium_probe", "nb_emitter_probe",
            "nb_bsdf_probe", "nb_film_download_layer", "nb_trace_rays_static", "nb_create_multi", "nb_comm_unique_id",
@@ -134,6 +134,8 @@ def load_library(path=None):
     lib.nb_trace_rays_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_float)]
     lib.nb_render_begin.argtypes = [C.c_void_p, C.c_void_p]
     lib.nb_render_subframe.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+    lib.nb_render_adaptive_round.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
+    lib.nb_adaptive_block_passes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
     lib.nb_sync.argtypes = [C.c_void_p]
     lib.nb_film_clear.argtypes = [C.c_void_p]
     lib.nb_film_shape.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
@@ -173,7 +175,7 @@ def read_nbs(path):
             dt = SECTION_DTYPES[name]
             assert dt.itemsize == int(sec["elem_size"]), (name, dt.itemsize, int(sec["elem_size"]))
             out[name] = np.frombuffer(buf, dtype=dt).copy()
-        elif name in ("faces", "bvh_indices", "spp"):
+        elif name in ("faces", "bvh_indices", "spp", "adaptive"):
             out[name] = np.frombuffer(buf, dtype="<u4").copy()
         elif name == "ambient":
             out[name] = np.frombuffer(buf, dtype="<i4").copy()
@@ -358,6 +360,18 @@ class Context:
 
     def render_subframe(self, first, count, stride=1, offset=0):
         self._check(self.lib.nb_render_subframe(self.handle, first, count, stride, offset))
+
+    def adaptive_block_passes(self, n_blocks):
+        out = np.zeros(n_blocks, "<u4")
+        self._check(self.lib.nb_adaptive_block_passes(self.handle, _ptr(out), n_blocks))
+        return out
+
+    def render_adaptive_round(self, block_size=4, initial_uniform=2, round_cap=0):
+        """One round of the adaptive sampler's feedback loop on the device (nb_render_adaptive_round):
+        dict(samples, block_passes, passes, blocks)."""
+        info = (C.c_uint64 * 3)()
+        self._check(self.lib.nb_render_adaptive_round(self.handle, block_size, initial_uniform, round_cap, info))
+        return {"samples": int(info[0]), "block_passes": int(info[1]), "passes": int(info[2] & 0xffffffff), "blocks": int(info[2] >> 32)}
 
     def sync(self):
         self._check(self.lib.nb_sync(self.handle))

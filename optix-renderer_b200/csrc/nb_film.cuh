@@ -10,6 +10,10 @@
 struct NbFilm {
     float4 *data;
     float4 *normal;               /* NB_LAYER_NORMAL accumulators, same geometry; null unless requested */
+    float4 *pass;                 /* adaptive rounds only (nb_render_adaptive_round; pass_block != 0): the block-local images of the
+                                   * current pass — renderBlock's `block` (render.cpp:421-459) for every block at once, same
+                                   * geometry as data; a sample only reaches the pixels of the block_size^2 block it was drawn in */
+    uint32_t pass_block;
     uint32_t rows, cols, border;
     float radius, lookup;
     float table[NB_FILTER_RESOLUTION + 1];
@@ -25,6 +29,10 @@ struct NbPlan {
 };
 
 /* ImageBlock::put(pos, value), block.cpp:93-123, on the full-image block (offset 0). */
+/* PASS: also fill the sample's own block image (adaptive rounds). Only the EXT kernel variants are built with it — adaptive
+ * rounds run those — because the headline kernels are issue-bound: the untaken branch and its live registers cost the cbox
+ * path_mis kernel 3 % (121.7 -> 125.7 ms, measured). */
+template <bool PASS = false>
 __device__ __forceinline__ void nb_film_put(const NbFilm &film, float px, float py, f3 v, unsigned long long *stats, float4 *layer = nullptr) {
     const bool valid = v.x >= 0.f && v.y >= 0.f && v.z >= 0.f && isfinite(v.x) && isfinite(v.y) && isfinite(v.z);
     if (!valid) { if (!layer) atomicAdd(&stats[NB_STAT_INVALID], 1ULL); return; }      /* Color3f::isValid, common.cpp:254 */
@@ -40,6 +48,21 @@ __device__ __forceinline__ void nb_film_put(const NbFilm &film, float px, float 
         for (int x = x0; x <= x1; ++x) {
             const float wgt = film.table[(int) (fabsf((float) x - posx) * film.lookup)] * wy;
             atomicAdd(row + x, make_float4(v.x * wgt, v.y * wgt, v.z * wgt, wgt));   /* RED.128 on sm_90+ */
+        }
+    }
+    if (PASS && film.pass_block && !layer) {
+        /* the same put into the sample's own block image: what AdaptiveSampler::computeVariance reads (adaptive.cpp:70-133) */
+        const int bs = (int) film.pass_block, b = (int) film.border;
+        const int bx = ((int) px / bs) * bs + b, by = ((int) py / bs) * bs + b;
+        x0 = max(x0, bx); y0 = max(y0, by);
+        x1 = min(x1, bx + bs - 1); y1 = min(y1, by + bs - 1);
+        for (int y = y0; y <= y1; ++y) {
+            const float wy = film.table[(int) (fabsf((float) y - posy) * film.lookup)];
+            float4 *row = film.pass + (size_t) y * film.cols;
+            for (int x = x0; x <= x1; ++x) {
+                const float wgt = film.table[(int) (fabsf((float) x - posx) * film.lookup)] * wy;
+                atomicAdd(row + x, make_float4(v.x * wgt, v.y * wgt, v.z * wgt, wgt));
+            }
         }
     }
 }

@@ -158,4 +158,4 @@ struct NbFilm;
 struct NbPlan;
 cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const NbPlan &plan, uint32_t height, uint32_t passes,
                            uint32_t integrator, uint32_t *item_counter, unsigned long long *stats, int sm_count,
-                           cudaStream_t stream, bool walk);
+                           cudaStream_t stream, bool walk, const uint32_t *list = nullptr, const uint32_t *list_ctl = nullptr);

@@ -46,7 +46,13 @@ struct NbTilePlan {
     uint32_t tiles_x, n_tiles;
     uint32_t chunk;                   /* passes per work item */
     uint32_t n_items;                 /* n_tiles * ceil(passes / chunk) */
+    /* adaptive rounds (nb_render_adaptive_round): the camera samples of this launch are an explicit LIST of pixel indices
+     * written by the device (nb_k_adaptive_decide), its length and first sample index in list_ctl[0], [1] — the host sizes
+     * nothing. Items are NB_LIST_ITEM consecutive entries. Null for every other launch; read by the EXT kernel variants only
+     * (nb_launch_tile runs those for a list). */
+    const uint32_t *list, *list_ctl;
 };
+#define NB_LIST_ITEM 128u
 
 struct NbPathRegs {                   /* path_mis.cpp:18-24 locals + the ray being traced */
     f3 Li, thr, o, d;
@@ -453,6 +459,7 @@ struct NbItemCursor {
 /* Called by all 32 lanes together. Lanes with `want` get the next camera samples of the warp's
  * item (a new item is claimed from the global counter when the current one is used up); returns
  * false for a lane that wanted one but the image is finished. */
+template <bool LIST>
 __device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan &tp, uint32_t *item_counter, bool want,
                                                uint32_t lane, uint32_t lt_mask, uint32_t &pix, uint32_t &sidx) {
     bool got = false;
@@ -463,6 +470,12 @@ __device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan
             uint32_t item = 0;
             if (lane == 0) item = atomicAdd(item_counter, 1u);
             item = __shfl_sync(0xffffffffu, item, 0);
+            if (LIST && tp.list) {
+                const uint32_t n = __ldg(tp.list_ctl), start = item * NB_LIST_ITEM;
+                if (item >= (n + NB_LIST_ITEM - 1) / NB_LIST_ITEM) { c.exhausted = true; break; }
+                c.x0 = start; c.n = min(NB_LIST_ITEM, n - start); c.next = 0;
+                continue;
+            }
             if (item >= tp.n_items) { c.exhausted = true; break; }
             /* chunk-major order: concurrently running warps work on different tiles */
             const uint32_t tile = item % tp.n_tiles, chunk = item / tp.n_tiles;
@@ -477,10 +490,15 @@ __device__ __forceinline__ bool nb_take_sample(NbItemCursor &c, const NbTilePlan
         const uint32_t rank = __popc(need & lt_mask);
         if (want && !got && rank < take) {
             const uint32_t k = c.next + rank;
-            const uint32_t pl = k / c.tpx, q = k - pl * c.tpx;
-            const uint32_t y = q / c.tw, x = q - y * c.tw;
-            pix = (c.y0 + y) * tp.plan.width + c.x0 + x;
-            sidx = tp.plan.first + (c.pass0 + pl) * tp.plan.stride;
+            if (LIST && tp.list) {
+                pix = __ldg(tp.list + c.x0 + k);
+                sidx = __ldg(tp.list_ctl + 1) + c.x0 + k;      /* every entry of every pass has its own random stream */
+            } else {
+                const uint32_t pl = k / c.tpx, q = k - pl * c.tpx;
+                const uint32_t y = q / c.tw, x = q - y * c.tw;
+                pix = (c.y0 + y) * tp.plan.width + c.x0 + x;
+                sidx = tp.plan.first + (c.pass0 + pl) * tp.plan.stride;
+            }
             got = true;
         }
         c.next += take;
@@ -530,7 +548,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     for (;;) {
         /* --- regenerate: idle lanes take the next camera samples of the warp's item --- */
         uint32_t pix, sidx;
-        if (nb_take_sample(cur, tp, item_counter, !active, lane, lt_mask, pix, sidx)) {
+        if (nb_take_sample<EXT>(cur, tp, item_counter, !active, lane, lt_mask, pix, sidx)) {
             NbCameraRay r;
             nb_camera_sample(sc.camera, tp.plan, pix, sidx, ps.rng, r);
             ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
@@ -566,7 +584,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 }
             }
             if (active && ended) {
-                nb_film_put(film, ps.px, ps.py, ps.Li, stats);
+                nb_film_put<EXT>(film, ps.px, ps.py, ps.Li, stats);
                 active = false;
             }
         } else if (VOL) {
@@ -577,14 +595,14 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
                 if (alive) alive = nb_vol_bounce<MIS, FLAT, EXT>(sc, tp.plan.max_depth, ps, medium, hit, n_closest);
                 else ps.Li += ps.thr * nb_env_radiance<EXT>(sc, ps.d);      /* path_vol_mats.cpp:34-39 */
                 if (!alive) {
-                    nb_film_put(film, ps.px, ps.py, ps.Li, stats);
+                    nb_film_put<EXT>(film, ps.px, ps.py, ps.Li, stats);
                     active = false;
                 }
             }
         } else if (active) {
             f3 layer_normal;
             const f3 Li = nb_direct_sample<INTEG, FLAT, EXT>(sc, tp.plan, ps, n_closest, n_any, layer_normal);
-            nb_film_put(film, ps.px, ps.py, Li, stats);
+            nb_film_put<EXT>(film, ps.px, ps.py, Li, stats);
             if (INTEG == NB_INTEGRATOR_PREVIEW && film.normal) nb_film_put(film, ps.px, ps.py, layer_normal, stats, film.normal);
             active = false;
         }
@@ -742,9 +760,9 @@ nb_k_tile_walk(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_coun
         /* ---- REGEN: splat the finished sample, start the next camera path ---- */
         const uint32_t m_regen = __ballot_sync(0xffffffffu, phase == NB_PH_REGEN);
         if (m_regen && (__popc(m_regen) >= NB_WALK_T_REGEN || !m_walking)) {
-            if (phase == NB_PH_REGEN && splat) { nb_film_put(film, park[NB_W_PX][tid], park[NB_W_PY][tid], ld3p(NB_W_LI), stats); splat = false; }
+            if (phase == NB_PH_REGEN && splat) { nb_film_put<EXT>(film, park[NB_W_PX][tid], park[NB_W_PY][tid], ld3p(NB_W_LI), stats); splat = false; }
             uint32_t pix, sidx;
-            const bool got = nb_take_sample(cur, tp, item_counter, phase == NB_PH_REGEN, lane, lt_mask, pix, sidx);
+            const bool got = nb_take_sample<EXT>(cur, tp, item_counter, phase == NB_PH_REGEN, lane, lt_mask, pix, sidx);
             if (got) {
                 NbCameraRay r;
                 NbPathRegs ps;
@@ -917,11 +935,14 @@ static cudaError_t nb_tile_launch_t(const NbDeviceScene &sc, const NbFilm &film,
 
 /* Host entry used by nb_render_subframe. `passes` sample passes over the image, pass k drawing
  * sample index plan.first + k * plan.stride. Asynchronous on `stream`. */
-cudaError_t nb_launch_tile(const NbDeviceScene &sc, const NbFilm &film, const NbPlan &plan, uint32_t height, uint32_t passes,
+cudaError_t nb_launch_tile(const NbDeviceScene &sc_in, const NbFilm &film, const NbPlan &plan, uint32_t height, uint32_t passes,
                            uint32_t integrator, uint32_t *item_counter, unsigned long long *stats, int sm_count,
-                           cudaStream_t stream, bool walk) {
+                           cudaStream_t stream, bool walk, const uint32_t *list, const uint32_t *list_ctl) {
+    NbDeviceScene sc = sc_in;
+    if (list) sc.ext = 1u;             /* the list and the block images are read by the EXT variants only (nb_film.cuh) */
     NbTilePlan tp;
     tp.plan = plan;
+    tp.list = list; tp.list_ctl = list_ctl;
     tp.height = height; tp.passes = passes;
     /* Work items are small: a warp that draws an expensive item last (glass-heavy tiles cost several
      * times the mean) finishes alone while the rest of the GPU idles, and at a few hundred k samples/s

@@ -260,6 +260,13 @@ struct NbRenderState {
     int grid = 0;
     int pending = 0;              /* K_tile subframes queued since the last nb_render_finish */
     std::vector<cudaEvent_t> prof_events;   /* "profile" option: 4 per iteration (shade | regen | trace) */
+    /* adaptive rounds (nb_render_adaptive_round), allocated on first use */
+    float *adp_old_var = nullptr, *adp_old_norm = nullptr;     /* m_oldVariance (per pixel), m_oldNorm (per block) of every block's sampler */
+    uint32_t *adp_total = nullptr;                             /* per block: passes rendered since nb_render_begin */
+    uint32_t *adp_count = nullptr;                             /* per block: `count` of render.cpp:326, NB_ADP_DONE once its loop ended */
+    uint32_t *adp_list = nullptr, *adp_ctl = nullptr;          /* sample list; [0] length [1] first sample index [2] blocks in this pass */
+    unsigned long long *adp_acc = nullptr, *adp_h_acc = nullptr;   /* round totals: samples, block passes, passes, length of the last pass */
+    uint32_t adp_block = 0, adp_blocks = 0, adp_serial = 0;
 };
 
 int nb_render_finish(nb_ctx *ctx) {
@@ -296,6 +303,7 @@ int nb_render_free(nb_ctx *ctx) {
     for (void *p : r->allocs) cudaFree(p);
     if (r->h_counts) cudaFreeHost(r->h_counts);
     if (r->h_stats) cudaFreeHost(r->h_stats);
+    if (r->adp_h_acc) cudaFreeHost(r->adp_h_acc);
     if (r->ev_begin) cudaEventDestroy(r->ev_begin);
     if (r->ev_end) cudaEventDestroy(r->ev_end);
     for (int i = 0; i < 2; ++i) if (r->ev_batch[i]) cudaEventDestroy(r->ev_batch[i]);
@@ -362,6 +370,7 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
         r->film.lookup = NB_FILTER_RESOLUTION / params->filter_radius;
         memcpy(r->film.table, params->filter_table, sizeof(r->film.table));
         ctx->render_begun = true;
+        if (r->adp_total) NB_CUDA(ctx, cudaMemsetAsync(r->adp_total, 0, r->adp_blocks * sizeof(uint32_t), ctx->stream));   /* nb_adaptive_block_passes counts per render */
         return nb_film_clear(ctx);
     }
     nb_render_free(ctx);
@@ -378,6 +387,7 @@ int nb_render_begin(nb_ctx *ctx, const nb_render_params *params) {
     int rc;
     if ((rc = nb_dev_alloc(ctx, r, &r->film.data, (size_t) r->film.rows * r->film.cols))) return rc;
     r->film.normal = nullptr;
+    r->film.pass = nullptr; r->film.pass_block = 0;
     if (want_normal) {
         if ((rc = nb_dev_alloc(ctx, r, &r->film.normal, (size_t) r->film.rows * r->film.cols))) return rc;
         NB_CUDA(ctx, cudaMemsetAsync(r->film.normal, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
@@ -427,6 +437,210 @@ int nb_film_clear(nb_ctx *ctx) {
     if (r->film.normal) NB_CUDA(ctx, cudaMemsetAsync(r->film.normal, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
     NB_CUDA(ctx, cudaMemsetAsync(r->stats, 0, NB_STAT_WORDS * sizeof(unsigned long long), ctx->stream));
     memset(&r->totals, 0, sizeof(r->totals));
+    return NB_OK;
+}
+
+/* ---- adaptive rounds: AdaptiveSampler (src/samplers/adaptive.cpp) as a device feedback loop --------------------------------
+ * The reference renders an adaptive image block by block (NORI_BLOCK_SIZE_ADAPTIVE = 4, block.h:31): for every block, in
+ * every round of the outer sample loop, `while (sampler->computeVariance(block)) { renderBlock(..); m_block.put(block); }`
+ * (render.cpp:323-333) — each pass draws width x height camera samples, the first ones one per pixel, the later ones placed by
+ * a discrete pdf made from the 3x3 luminance variance of the block's PREVIOUS pass (common.cpp:339-399), until the change of
+ * that variance map stops shrinking. Here all blocks advance together: one warp per block takes the decision the block's
+ * sampler would take and appends the block's samples to a list, the persistent render kernel consumes the list
+ * (NbTilePlan::list), its puts also fill the blocks' own images (NbFilm::pass) for the next decision. The host only reads back
+ * "how many blocks went on". Kept from the reference, because they shape what it computes: the rounds computeVariance sees
+ * (0, 0, 1, 2, .. — render.cpp:327, :334 post-increment), the reset at round 0, the cap at round 1000, the [1, 1.254] rescale,
+ * the Frobenius normalisation of the stored map, the stop rule |sum(old - new)| > previous, and the transposed placement
+ * (getSampleIndices returns {row, col}, renderBlock reads it as {x, y}: adaptive.cpp:166-168, render.cpp:438-440).
+ * A block whose variance map is constant (black, a flat emitter, a dim corner with no lucky sample) is not special either:
+ * common.cpp:381-386 makes the map zero, Eigen's normalize() leaves a zero matrix alone, DiscretePDF::normalize() leaves a zero
+ * cdf alone, and DiscretePDF::sample() then answers "the last entry" for every draw — so the reference renders one pass with
+ * all of the block's samples on its last pixel, and the NEXT decision stops the block (the sum of any non-zero map exceeds the
+ * stored 0) unless that pass was black too, in which case it goes round again, up to the cap: a black block costs the
+ * reference 1000 passes per round. All of that is reproduced (tests/test_adaptive_gpu.py compares the law of the passes per
+ * block with the reference's, black blocks included); `round_cap` lets a caller who does not want to pay for it lower the cap.
+ * Partial blocks at the image edge place samples inside the block (the reference's transposed indices leave it). */
+#define NB_ADP_DONE 0xffffffffu
+#define NB_ADP_MAX_BLOCK 8u
+__global__ void __launch_bounds__(256) nb_k_adaptive_decide(NbFilm film, uint32_t W, uint32_t H, uint32_t bs, uint32_t nbx, uint32_t n_blocks,
+                                                            uint32_t initial_uniform, uint32_t round_cap, float *old_var, float *old_norm, uint32_t *count, uint32_t *total,
+                                                            uint32_t *list, uint32_t *ctl, unsigned long long seed, uint32_t serial) {
+    __shared__ float sm[8][2][NB_ADP_MAX_BLOCK * NB_ADP_MAX_BLOCK];
+    const uint32_t block = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (block >= n_blocks) return;
+    const uint32_t cnt = count[block];
+    if (cnt == NB_ADP_DONE) return;
+    const uint32_t round = cnt == 0 ? 0u : cnt - 1u;           /* m_sampleRound at this call of computeVariance */
+    const uint32_t x0 = (block % nbx) * bs, y0 = (block / nbx) * bs, w = min(bs, W - x0), h = min(bs, H - y0), n = w * h;
+    float *lum = sm[threadIdx.x >> 5][0], *cdf = sm[threadIdx.x >> 5][1];
+    auto pixel = [&](uint32_t p) { return (size_t) (y0 + p / w + film.border) * film.cols + (x0 + p % w + film.border); };
+    auto own = [&](uint32_t p) { return (size_t) (y0 + p / w) * W + (x0 + p % w); };          /* old_var is W x H */
+    auto sum = [&](float v) { for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o); return v; };
+    bool go = true, uniform = true, zero_pdf = false;
+    float onorm = old_norm[block];
+    if (round == 0) {                                          /* adaptive.cpp:72-78 */
+        for (uint32_t p = lane; p < n; p += 32) old_var[own(p)] = 0.f;
+        onorm = 10000.f;
+    } else if (round >= round_cap) go = false;                 /* adaptive.cpp:79-82: 1000 */
+    if (go && round >= initial_uniform) {
+        uniform = false;
+        for (uint32_t p = lane; p < n; p += 32) {              /* |luminance| of the block's own image, Color4f::divideByFilterWeight */
+            const float4 c = film.pass[pixel(p)];
+            lum[p] = c.w != 0.f ? fabsf((c.x / c.w) * 0.212671f + (c.y / c.w) * 0.715160f + (c.z / c.w) * 0.072169f) : 0.f;
+        }
+        __syncwarp();
+        float v[2] = { 0.f, 0.f }, lo = INFINITY, hi = -INFINITY;
+        for (uint32_t p = lane, q = 0; p < n; p += 32, ++q) {  /* computeVarianceFromImage, common.cpp:339-378: neighbours inside the block */
+            const int i = (int) (p / w), j = (int) (p % w);
+            float mean = 0.f, cntf = 0.f;
+            for (int k = -1; k <= 1; ++k)
+                for (int l = -1; l <= 1; ++l)
+                    if (i + k >= 0 && i + k < (int) h && j + l >= 0 && j + l < (int) w) { mean += lum[(i + k) * w + j + l]; cntf += 1.f; }
+            mean /= cntf;
+            float col = 0.f;
+            for (int k = -1; k <= 1; ++k)
+                for (int l = -1; l <= 1; ++l)
+                    if (i + k >= 0 && i + k < (int) h && j + l >= 0 && j + l < (int) w) {
+                        const float d = lum[(i + k) * w + j + l] - mean;
+                        col += 1.f / cntf * (d * d);
+                    }
+            v[q] = col; lo = fminf(lo, col); hi = fmaxf(hi, col);
+        }
+        for (int o = 16; o; o >>= 1) { lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+        const bool flat = hi - lo < NB_EPS;                    /* common.cpp:381-386: the map becomes zero */
+        float diff = 0.f, sq = 0.f, tot = 0.f;
+        for (uint32_t p = lane, q = 0; p < n; p += 32, ++q) {
+            v[q] = flat ? 0.f : 1.f + (v[q] - lo) / (hi - lo) * 0.254f;
+            diff += old_var[own(p)] - v[q]; sq += v[q] * v[q]; tot += v[q];
+        }
+        const float var_diff = fabsf(sum(diff));               /* adaptive.cpp:98 */
+        sq = sum(sq); tot = sum(tot);
+        if (var_diff > onorm) go = false;                      /* adaptive.cpp:127-128 */
+        else {
+            onorm = var_diff;
+            const float inv = sq > 0.f ? 1.f / sqrtf(sq) : 1.f; /* variance.normalize(): the unit-norm map is what is kept; a zero map stays */
+            zero_pdf = !(tot > 0.f);                           /* DiscretePDF::normalize() leaves a zero cdf alone */
+            for (uint32_t p = lane, q = 0; p < n; p += 32, ++q) { old_var[own(p)] = v[q] * inv; lum[p] = zero_pdf ? 0.f : v[q] / tot; }
+            __syncwarp();
+            if (lane == 0) { float c = 0.f; for (uint32_t p = 0; p + 1 < n; ++p) { c += lum[p]; cdf[p + 1] = c; } }
+            __syncwarp();                                      /* cdf[p] = sum of the first p probabilities, 0 < p < n (the bounds 0 and 1 are implied) */
+        }
+    }
+    if (!go) { if (lane == 0) count[block] = NB_ADP_DONE; return; }
+    uint32_t at = 0;
+    if (lane == 0) {
+        old_norm[block] = onorm;
+        count[block] = cnt + 1u;                               /* render.cpp:334 */
+        total[block] += 1u;
+        at = atomicAdd(ctl, n);
+        atomicAdd(ctl + 2, 1u);
+    }
+    at = __shfl_sync(0xffffffffu, at, 0);
+    for (uint32_t p = lane; p < n; p += 32) {
+        uint32_t x = p % w, y = p / w;                         /* uniform pass: every pixel once (adaptive.cpp:150-160) */
+        if (!uniform) {
+            NbRng rng; rng.seed(seed ^ 0xada9715eULL, ((uint64_t) block << 32) | ((uint64_t) serial << 6) | p);
+            const float u = rng.next_float();                  /* DiscretePDF::sample (dpdf.h): last bound not above u */
+            uint32_t e = 0;
+            for (uint32_t k = 1; k < n; ++k) e += cdf[k] < u ? 1u : 0u;
+            if (zero_pdf) e = u > 0.f ? n - 1u : 0u;           /* every bound of an unnormalised zero cdf lies below u */
+            const uint32_t row = e / w, col = e % w;           /* {row, col} read as {x, y} */
+            x = min(row, w - 1u); y = min(col, h - 1u);
+        }
+        list[at + p] = (y0 + y) * W + x0 + x;
+    }
+    for (uint32_t p = lane; p < n; p += 32) film.pass[pixel(p)] = make_float4(0.f, 0.f, 0.f, 0.f);   /* renderBlock: block.clear() */
+}
+
+/* after a pass: its length joins the running totals and the first sample index of the next pass; the list starts empty again */
+__global__ void nb_k_adaptive_next(uint32_t *ctl, unsigned long long *acc) {
+    const uint32_t n = ctl[0];
+    acc[0] += n; acc[1] += ctl[2]; acc[2] += n ? 1u : 0u; acc[3] = n;
+    ctl[1] += n; ctl[0] = 0u; ctl[2] = 0u;
+}
+
+/* One round of the outer sample loop of render.cpp:283-360 for a scene whose sampler is `adaptive`: every block's
+ * while-loop, all blocks in step. Synchronous. */
+int nb_render_adaptive_round(nb_ctx *ctx, uint32_t block_size, uint32_t initial_uniform, uint32_t round_cap, nb_adaptive_info *out) {
+    if (!ctx || !ctx->render || !ctx->render_begun) return nb_fail(ctx, NB_E_STATE, "nb_render_adaptive_round: call nb_render_begin first");
+    if (block_size < 2 || block_size > NB_ADP_MAX_BLOCK) return nb_fail(ctx, NB_E_INVALID, "nb_render_adaptive_round: block size %u outside 2..%u", block_size, NB_ADP_MAX_BLOCK);
+    if (initial_uniform < 1) initial_uniform = 1;              /* adaptive.cpp:21: clamp(initialUniform, 1, sampleCount) */
+    if (round_cap == 0 || round_cap > 1000) round_cap = 1000;  /* adaptive.cpp:79 */
+    NbRenderState *r = ctx->render;
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    { const int rc0 = nb_render_finish(ctx); if (rc0 != NB_OK) return rc0; }
+    const nb_camera &cam = ctx->dev.camera;
+    const uint32_t W = cam.width, H = cam.height, npix = W * H;
+    const uint32_t nbx = (W + block_size - 1) / block_size, nby = (H + block_size - 1) / block_size, n_blocks = nbx * nby;
+    int rc;
+    if (!r->adp_list) {
+        if ((rc = nb_dev_alloc(ctx, r, &r->film.pass, (size_t) r->film.rows * r->film.cols)) || (rc = nb_dev_alloc(ctx, r, &r->adp_old_var, npix)) ||
+            (rc = nb_dev_alloc(ctx, r, &r->adp_list, npix)) || (rc = nb_dev_alloc(ctx, r, &r->adp_ctl, 4)) || (rc = nb_dev_alloc(ctx, r, &r->adp_acc, 4)))
+            return rc;
+        NB_CUDA(ctx, cudaMallocHost((void **) &r->adp_h_acc, 4 * sizeof(unsigned long long)));
+        NB_CUDA(ctx, cudaMemsetAsync(r->film.pass, 0, (size_t) r->film.rows * r->film.cols * sizeof(float4), ctx->stream));
+        NB_CUDA(ctx, cudaMemsetAsync(r->adp_ctl, 0, 4 * sizeof(uint32_t), ctx->stream));      /* the sample index runs on from round to round */
+    }
+    if (r->adp_block != block_size) {                          /* per-block state for this block size */
+        if ((rc = nb_dev_alloc(ctx, r, &r->adp_old_norm, n_blocks)) || (rc = nb_dev_alloc(ctx, r, &r->adp_count, n_blocks)) ||
+            (rc = nb_dev_alloc(ctx, r, &r->adp_total, n_blocks))) return rc;
+        NB_CUDA(ctx, cudaMemsetAsync(r->adp_total, 0, n_blocks * sizeof(uint32_t), ctx->stream));
+        r->adp_block = block_size; r->adp_blocks = n_blocks;
+    }
+    r->film.pass_block = block_size;
+    NB_CUDA(ctx, cudaMemsetAsync(r->adp_count, 0, n_blocks * sizeof(uint32_t), ctx->stream));      /* render.cpp:326: count = 0 */
+    NB_CUDA(ctx, cudaMemsetAsync(r->adp_acc, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    NbPlan plan;
+    plan.npix = npix; plan.width = W; plan.total = 0;
+    plan.seed = r->params.seed; plan.first = 0; plan.stride = 1; plan.max_depth = r->params.max_depth;
+    for (int i = 0; i < 3; ++i) plan.iparam[i] = r->params.integrator_params[i];
+    cudaEventRecord(r->ev_begin, ctx->stream);
+    /* passes are queued in batches and the host looks at the totals once per batch: a pass past the end of the round finds
+     * every block done and costs two empty launches */
+    const uint32_t BATCH = 8;
+    uint32_t queued = 0;
+    for (;;) {
+        for (uint32_t k = 0; k < BATCH; ++k, ++queued) {
+            nb_k_adaptive_decide<<<(n_blocks + 7) / 8, 256, 0, ctx->stream>>>(r->film, W, H, block_size, nbx, n_blocks, initial_uniform, round_cap, r->adp_old_var,
+                                                                            r->adp_old_norm, r->adp_count, r->adp_total, r->adp_list, r->adp_ctl, r->params.seed, r->adp_serial++);
+            const cudaError_t e = nb_launch_tile(ctx->dev, r->film, plan, H, 1, r->params.integrator, r->tile_counter, r->stats, ctx->sm_count, ctx->stream,
+                                                 ctx->opt_walk != 0, r->adp_list, r->adp_ctl);
+            if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_adaptive_round: K_tile launch: %s", cudaGetErrorString(e));
+            nb_k_adaptive_next<<<1, 1, 0, ctx->stream>>>(r->adp_ctl, r->adp_acc);
+        }
+        NB_CUDA(ctx, cudaMemcpyAsync(r->adp_h_acc, r->adp_acc, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) return nb_fail(ctx, NB_E_CUDA, "nb_render_adaptive_round: %s", cudaGetErrorString(e));
+        if (r->adp_h_acc[3] == 0) break;                       /* the last pass of the batch drew nothing: every block's loop has ended */
+        if (queued > round_cap + 2 + BATCH) return nb_fail(ctx, NB_E_CUDA, "nb_render_adaptive_round: internal: blocks still running after the round cap");
+    }
+    cudaEventRecord(r->ev_end, ctx->stream);
+    NB_CUDA(ctx, cudaMemcpyAsync(r->h_stats, r->stats, NB_STAT_WORDS * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    NB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    nb_adaptive_info info; memset(&info, 0, sizeof(info));
+    info.samples = r->adp_h_acc[0]; info.block_passes = r->adp_h_acc[1]; info.passes = (uint32_t) r->adp_h_acc[2]; info.blocks = n_blocks;
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end);
+    r->totals.device_ms += ms;
+    r->totals.iterations += info.passes;
+    r->totals.kernel_launches += 3ull * queued;
+    r->totals.samples = r->h_stats[NB_STAT_SAMPLES];
+    r->totals.rays_closest = r->h_stats[NB_STAT_RAYS_CLOSEST];
+    r->totals.rays_any = r->h_stats[NB_STAT_RAYS_ANY];
+    r->totals.invalid_samples = r->h_stats[NB_STAT_INVALID];
+    r->film.pass_block = 0;                                    /* plain subframes after this round do not touch the block images */
+    if (out) *out = info;
+    return NB_OK;
+}
+
+int nb_adaptive_block_passes(nb_ctx *ctx, uint32_t *out, uint32_t n) {
+    if (!ctx || !ctx->render || !ctx->render->adp_total) return nb_fail(ctx, NB_E_STATE, "nb_adaptive_block_passes: no adaptive round has run");
+    const nb_camera &cam = ctx->dev.camera;
+    const uint32_t bs = ctx->render->adp_block, n_blocks = ((cam.width + bs - 1) / bs) * ((cam.height + bs - 1) / bs);
+    if (n != n_blocks) return nb_fail(ctx, NB_E_INVALID, "nb_adaptive_block_passes: the image has %u blocks of %u x %u, not %u", n_blocks, bs, bs, n);
+    NB_CUDA(ctx, cudaSetDevice(ctx->device));
+    NB_CUDA(ctx, cudaMemcpy(out, ctx->render->adp_total, n * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     return NB_OK;
 }
 

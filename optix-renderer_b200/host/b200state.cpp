@@ -55,6 +55,13 @@ void B200State::renderSubframe(uint32_t currentSample, uint32_t samplesPerLaunch
     for (nb_ctx *c : m_all) checkOn(c, nb_sync(c));
 }
 
+nb_adaptive_info B200State::renderAdaptiveRound(uint32_t blockSize, uint32_t initialUniform, uint32_t roundCap) {
+    if (m_all.size() > 1) throw NoriException("B200State: the adaptive sampler runs on one device (its feedback reads a block's own samples)");
+    nb_adaptive_info info;
+    check(nb_render_adaptive_round(m_ctx, blockSize, initialUniform, roundCap, &info));
+    return info;
+}
+
 void B200State::download(std::vector<float> &out, bool normalize, uint32_t *rows, uint32_t *cols, int layer) {
     uint32_t r = 0, c = 0, b = 0;
     check(nb_film_shape(m_ctx, &r, &c, &b));

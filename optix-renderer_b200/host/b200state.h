@@ -19,6 +19,9 @@ public:
     bool preRender(const Scene &scene, uint64_t seed = 0, uint32_t poolPaths = 0, uint32_t layers = 0);   /* layers: NB_LAYER_* bits */
     /* OptixState::renderSubframe (OptixState.cpp:485-510) */
     void renderSubframe(uint32_t currentSample, uint32_t samplesPerLaunch, uint32_t stride = 1, uint32_t offset = 0);
+    /* one round of the sample loop for an `adaptive` sampler (render.cpp:283-360 with :323-335 inside): the blocks' variance
+     * loops on the device. One device: the feedback needs a block's own samples in one place. */
+    nb_adaptive_info renderAdaptiveRound(uint32_t blockSize, uint32_t initialUniform, uint32_t roundCap = 0);
     /* accumulators in ImageBlock layout (rows x cols x {sum w*rgb, sum w}) or the normalised bitmap */
     void download(std::vector<float> &out, bool normalize, uint32_t *rows = nullptr, uint32_t *cols = nullptr, int layer = NB_LAYER_COMPOSITE);
     void clear();                                   /* OptixState::clear */

@@ -34,11 +34,11 @@ static void writePfm(const std::string &path, const float *data, size_t h, size_
 
 int main(int argc, char **argv) {
     if (argc < 3) {
-        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs]\n");
+        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs] [adaptive_cap=N]\n");
         return 2;
     }
     try {
-        int spp = -1, device = 0, launch = 0, snapshot = 0;
+        int spp = -1, device = 0, launch = 0, snapshot = 0, adaptiveCap = 0;   /* adaptive_cap: AdaptiveSampler's 1000-decision limit (black blocks reach it) */
         uint64_t seed = 0;
         std::string flatOut;
         std::vector<int> devices;
@@ -58,6 +58,7 @@ int main(int argc, char **argv) {
             else if (!strncmp(argv[i], "launch=", 7)) launch = atoi(argv[i] + 7);
             else if (!strncmp(argv[i], "snapshot=", 9)) snapshot = atoi(argv[i] + 9);
             else if (!strncmp(argv[i], "flat=", 5)) flatOut = argv[i] + 5;
+            else if (!strncmp(argv[i], "adaptive_cap=", 13)) adaptiveCap = atoi(argv[i] + 13);
         }
         auto t0 = std::chrono::steady_clock::now();
         std::unique_ptr<NoriObject> root(loadFromXML(argv[1]));
@@ -81,9 +82,13 @@ int main(int argc, char **argv) {
         const std::string outPath(argv[2]);
         const bool pfm = outPath.size() > 4 && outPath.substr(outPath.size() - 4) == ".pfm";
         int launches = 0, snapshots = 0;
+        const bool adaptive = scene->getSampler()->isAdaptive();
+        if (adaptive) launch = 1;                                   /* one round of the sample loop per call */
+        uint64_t adaptivePasses = 0;
         for (int s = 0; s < spp; s += launch) {
             const int n = std::min(launch, spp - s);
-            state.renderSubframe((uint32_t) s, (uint32_t) n);
+            if (adaptive) adaptivePasses += state.renderAdaptiveRound(4, (uint32_t) scene->getSampler()->getInitialUniform(), (uint32_t) std::max(0, adaptiveCap)).block_passes;   /* block.h:31 */
+            else state.renderSubframe((uint32_t) s, (uint32_t) n);
             if (snapshot > 0 && ++launches % snapshot == 0 && s + n < spp) {
                 std::vector<float> snap;
                 uint32_t sh = 0, sw = 0;
@@ -101,10 +106,10 @@ int main(int argc, char **argv) {
         nb_counters c = state.counters();
         printf("{\"scene\": \"%s\", \"width\": %u, \"height\": %u, \"spp\": %d, \"load_seconds\": %.3f, \"seconds\": %.6f, "
                "\"samples\": %llu, \"samples_per_s\": %.1f, \"rays_closest\": %llu, \"rays_any\": %llu, \"rays_per_s\": %.1f, "
-               "\"device_ms\": %.3f, \"invalid_samples\": %llu, \"devices\": %zu, \"snapshots\": %d}\n",
+               "\"device_ms\": %.3f, \"invalid_samples\": %llu, \"devices\": %zu, \"snapshots\": %d, \"adaptive_block_passes\": %llu}\n",
                argv[1], w, h, spp, load_s, render_s, (unsigned long long) c.samples, c.samples / render_s,
                (unsigned long long) c.rays_closest, (unsigned long long) c.rays_any, (c.rays_closest + c.rays_any) / render_s,
-               c.device_ms, (unsigned long long) c.invalid_samples, state.deviceCount(), snapshots);
+               c.device_ms, (unsigned long long) c.invalid_samples, state.deviceCount(), snapshots, (unsigned long long) adaptivePasses);
         return 0;
     } catch (const std::exception &e) {
         fprintf(stderr, "nori_b200: %s\n", e.what());

@@ -362,12 +362,19 @@ public:
 };
 NORI_REGISTER_CLASS(Independent, "independent")
 
-/* src/samplers/adaptive.cpp:36-39: the variance feedback loop lives in the host render loop (render.cpp:323-336),
- * which is not on the GPU path; the backend renders the scene's sampleCount uniformly */
+/* src/samplers/adaptive.cpp:18-23: the variance feedback loop of render.cpp:323-336 runs on the device
+ * (nb_render_adaptive_round, one call per round of the sample loop: B200State::renderAdaptiveRound) */
 class AdaptiveSampler : public Sampler {
 public:
-    explicit AdaptiveSampler(const PropertyList &p) { m_sampleCount = (size_t) p.getInteger("sampleCount", 1); (void) p.getInteger("initialUniform", 2); }
-    std::string toString() const override { return NoriException::format("Adaptive[sampleCount=%d]", (int) m_sampleCount); }
+    explicit AdaptiveSampler(const PropertyList &p) {
+        m_sampleCount = (size_t) p.getInteger("sampleCount", 1);
+        m_initialUniform = std::min(std::max(p.getInteger("initialUniform", 2), 1), (int) m_sampleCount);
+    }
+    bool isAdaptive() const override { return true; }
+    int getInitialUniform() const override { return m_initialUniform; }
+    std::string toString() const override { return NoriException::format("AdaptiveSampler[\n  sampleCount = %d,\n  initialUniform = %d\n  ]", (int) m_sampleCount, m_initialUniform); }
+private:
+    int m_initialUniform;
 };
 NORI_REGISTER_CLASS(AdaptiveSampler, "adaptive")
 

@@ -157,6 +157,8 @@ class Sampler : public NoriObject {
 public:
     EClassType getClassType() const override { return ESampler; }
     size_t getSampleCount() const { return m_sampleCount; }
+    virtual bool isAdaptive() const { return false; }           /* sampler.h:117 */
+    virtual int getInitialUniform() const { return 0; }
 protected:
     size_t m_sampleCount = 1;
 };
@@ -177,6 +179,7 @@ struct FlatScene {
     nb_camera camera;
     nb_render_params render;
     uint32_t spp = 1;
+    uint32_t adaptive[2] = { 0, 0 };          /* `adaptive` sampler: { block size (NORI_BLOCK_SIZE_ADAPTIVE), initialUniform }; { 0, 0 } otherwise */
     std::vector<nb_bvh_node> bvh_nodes;
     std::vector<uint32_t> bvh_indices;
     bool any_normals = false, any_uvs = false, any_tangents = false;

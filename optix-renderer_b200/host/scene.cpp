@@ -143,6 +143,7 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
         out.render.filter_table[i] = rf->eval((out.render.filter_radius * i) / NB_FILTER_RESOLUTION);
     out.render.filter_table[NB_FILTER_RESOLUTION] = 0.0f;
     out.spp = (uint32_t) m_sampler->getSampleCount();
+    if (m_sampler->isAdaptive()) { out.adaptive[0] = 4; out.adaptive[1] = (uint32_t) m_sampler->getInitialUniform(); }   /* block.h:31 */
     buildBVH(m_shapes, out.bvh_nodes, out.bvh_indices);
     return true;
 }
@@ -194,6 +195,7 @@ void FlatScene::writeNbs(const std::string &path) const {
     secs.push_back({ "camera", sizeof(nb_camera), &camera, 1 });
     secs.push_back({ "render", sizeof(nb_render_params), &render, 1 });
     secs.push_back({ "spp", 4, &spp, 1 });
+    if (adaptive[0]) secs.push_back({ "adaptive", 4, adaptive, 2 });
     secs.push_back({ "bvh_nodes", sizeof(nb_bvh_node), bvh_nodes.data(), bvh_nodes.size() });
     secs.push_back({ "bvh_indices", 4, bvh_indices.data(), bvh_indices.size() });
     FILE *f = fopen(path.c_str(), "wb");

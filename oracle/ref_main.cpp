@@ -205,7 +205,9 @@ static int modeRender(int argc, char **argv) {
         result2.emplace_back(new ImageBlock(outputSize, camera->getReconstructionFilter()));
         result2.back()->clear();
     }
-    const int blockSize = NORI_BLOCK_SIZE;
+    /* render.cpp:266: the adaptive sampler works on 4 x 4 blocks, and each block runs the loop of render.cpp:323-335 */
+    const bool adaptive = scene->getSampler()->isAdaptive();
+    const int blockSize = adaptive ? NORI_BLOCK_SIZE_ADAPTIVE : NORI_BLOCK_SIZE;
     BlockGenerator blockGenerator(outputSize, blockSize);
     Integrator *integrator = scene->getIntegrator(false);
     {
@@ -215,6 +217,8 @@ static int modeRender(int argc, char **argv) {
     }
     const int numBlocks = blockGenerator.getBlockCount();
     std::vector<std::unique_ptr<Sampler>> samplers(numBlocks);
+    std::vector<float> blockFlat(numBlocks, 0.f);        /* adaptive: rounds whose first placed decision saw a constant variance map */
+    std::vector<float> blockPasses(numBlocks, 0.f);      /* adaptive: passes each block rendered, summed over the rounds */
 
     std::vector<RayCounters> counters(nThreads);
     std::streambuf *cerrBuf = wantNormal ? std::cerr.rdbuf(nullptr) : nullptr;   /* one warning per rejected normal otherwise */
@@ -234,6 +238,21 @@ static int modeRender(int argc, char **argv) {
                     std::unique_ptr<Sampler> sampler(scene->getSampler()->clone());
                     sampler->prepare(block);
                     samplers.at(blockId) = std::move(sampler);
+                }
+                if (adaptive) {
+                    int count = 0;
+                    samplers.at(blockId)->setSampleRound(count);
+                    for (;;) {
+                        /* what the sampler is about to see at its first placed decision of this round (count == 3 with the
+                         * default initialUniform = 2): is the variance map constant? */
+                        if (count == 3 && computeVarianceFromImage(block).maxCoeff() == 0.f) ++blockFlat[blockId];
+                        if (!samplers.at(blockId)->computeVariance(block)) break;
+                        renderBlockRef(scene, integrator, samplers.at(blockId).get(), block, nullptr);
+                        result.put(block);
+                        samplers.at(blockId)->setSampleRound(count++);
+                        ++blockPasses[blockId];
+                    }
+                    continue;
                 }
                 renderBlockRef(scene, integrator, samplers.at(blockId).get(), block, wantNormal ? &blockN : nullptr);
                 if (currentSample < split) result.put(block); else result2[(currentSample - split) / seg]->put(block);
@@ -265,6 +284,8 @@ static int modeRender(int argc, char **argv) {
     }
     if (kv.count("film"))
         writeNpy(kv["film"], (const float *) result.data(), { (size_t) result.rows(), (size_t) result.cols(), 4 });
+    if (adaptive && kv.count("passes")) writeNpy(kv["passes"], blockPasses.data(), { (size_t) numBlocks });
+    if (adaptive && kv.count("flat")) writeNpy(kv["flat"], blockFlat.data(), { (size_t) numBlocks });
 
     uint64_t closest = 0, any = 0, dup = 0;
     for (auto &c : counters) { closest += c.closest; any += c.any; dup += c.dup; }

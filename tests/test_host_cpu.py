@@ -135,3 +135,11 @@ def test_reference_plugin_names(nb, built_lib, tmp_path):
     assert s["media"]["phase"][0] == nb.PHASE_SCHLICK
     g = 0.7
     assert abs(float(s["media"]["phase_param"][0]) - (1.55 * g - 0.55 * g ** 3)) < 1e-6
+
+
+def test_adaptive_sampler_reaches_the_flat_scene(nb, built_lib):
+    """<sampler type="adaptive"> (src/samplers/adaptive.cpp:18-23): block size NORI_BLOCK_SIZE_ADAPTIVE and initialUniform
+    travel with the flattened scene; other samplers leave no such section."""
+    s = nb.load_xml(golden("scenes/cbox/cbox_adaptive_small.xml"))
+    assert list(s["adaptive"]) == [4, 2] and int(s["spp"][0]) == 8
+    assert "adaptive" not in nb.load_xml(golden("scenes/cbox/cbox_path_mis_small.xml"))

@@ -65,8 +65,8 @@ def test_nvdb_scene_vs_nanovdb_reading_the_same_file(nb, ctx):
 
 
 def test_brick_layout_is_the_dense_layout_bit_for_bit(nb, ctx, monkeypatch):
-    """NB_MEDIUM_HETEROGENEOUS_BRICKS holds the same voxels behind a table: the same 27 taps in the same order, so densities,
-    tracking results and a render are the dense layout's bits."""
+    """NB_MEDIUM_HETEROGENEOUS_BRICKS holds the same voxels behind a table: the same 27 taps in the same order, so densities and
+    tracking results are the dense layout's bits, and a render is the dense layout's render."""
     xml = golden("scenes/vol/cbox_heterog_fluid_small.xml")
     rays = np.fromfile(golden("vol_fluid_probe_rays.bin"), "<f4").reshape(-1, 8)
     out = {}
@@ -81,7 +81,8 @@ def test_brick_layout_is_the_dense_layout_bit_for_bit(nb, ctx, monkeypatch):
         out[layout] = (probe, ctx.film_download(normalize=True))
     assert (out["dense"][0][:, 0] != 0).sum() > 100
     assert np.array_equal(out["dense"][0], out["bricks"][0])
-    assert np.array_equal(out["dense"][1], out["bricks"][1])
+    # the film sums splats with atomics in whatever order the tiles finish: equal up to that reassociation
+    np.testing.assert_allclose(out["dense"][1], out["bricks"][1], rtol=2e-5, atol=1e-6)
 
 
 def test_sparse_scene_vs_nanovdb_reading_the_same_file(nb, ctx):
