@@ -216,6 +216,21 @@ def tree_config(nb, ctx, name, xml, spp, sms, clk_mhz, cap_csv):
     row = {"config": name, "triangles": int(s["faces"].size // 3), "spp": spp, "ms": best["device_ms"],
            "samples_per_s": best["samples"] / best["device_ms"] * 1e3, "rays_per_s": rays / best["device_ms"] * 1e3,
            "host_load_flatten_bvh_s": round(host_s, 2)}
+    # the same scene on the tree the device builds itself (NB_BVH_DEVICE_SAH: no host build at all)
+    t0 = time.perf_counter()
+    ctx.load(s, device_bvh="sah")
+    dev_load_s = time.perf_counter() - t0
+    ctx.render_begin(nb.make_render_params(s, seed=1))
+    dbest = None
+    for _ in range(3):
+        ctx.film_clear()
+        ctx.render_subframe(0, spp)
+        c = ctx.counters()
+        if dbest is None or c["device_ms"] < dbest["device_ms"]:
+            dbest = c
+    row["device_sah"] = {"build_ms": round(ctx.bvh_stats()["build_ms"], 3), "upload_build_collapse_s": round(dev_load_s, 3), "ms": dbest["device_ms"],
+                         "samples_per_s": dbest["samples"] / dbest["device_ms"] * 1e3,
+                         "rays_per_s": (dbest["rays_closest"] + dbest["rays_any"]) / dbest["device_ms"] * 1e3}
     cap = ncu_capture(cap_csv)
     meta = cap_csv[:-4] + ".meta.json"
     if cap and os.path.exists(meta):

@@ -200,7 +200,9 @@ typedef struct nb_scene_desc {
 /* nb_build_bvh(mode = NB_BVH_IMPORT): the caller's own arrays (BVH::m_nodes / m_indices after
  * Scene::update, scene.cpp:187-194). Same tree, same visiting order => bit-identical hits. */
 enum { NB_BVH_IMPORT = 0,   /* the caller's tree (the reference's, or libnorib200_host's restatement of it) */
-       NB_BVH_DEVICE = 1 }; /* K_bvh_build: linear BVH built on the GPU from the uploaded scene; `imp` is ignored */
+       NB_BVH_DEVICE = 1,   /* K_bvh_build: linear BVH built on the GPU from the uploaded scene; `imp` is ignored */
+       NB_BVH_DEVICE_SAH = 2 }; /* the reference's SAH criterion (bvh.cpp:100-233) built top-down on the GPU, one tree level per pass:
+                             * the quality of the host build in milliseconds instead of seconds; `imp` is ignored */
 typedef struct nb_bvh_import {
     uint32_t n_nodes;    const nb_bvh_node *nodes;
     uint32_t n_indices;  const uint32_t    *indices;    /* global primitive ids, leaf order */

@@ -286,9 +286,10 @@ class Context:
         imp = BvhImport(len(nodes), _ptr(nodes), len(indices), _ptr(indices))
         self._check(self.lib.nb_build_bvh(self.handle, 0, C.byref(imp)))
 
-    def build_bvh_device(self):
-        """K_bvh_build: linear BVH built on the GPU from the uploaded scene (no host tree needed)."""
-        self._check(self.lib.nb_build_bvh(self.handle, 1, None))
+    def build_bvh_device(self, sah=False):
+        """K_bvh_build: the tree built on the GPU from the uploaded scene (no host tree needed) — a linear BVH (2 ms per
+        million triangles) or, sah=True, the reference's SAH criterion top-down (NB_BVH_DEVICE_SAH)."""
+        self._check(self.lib.nb_build_bvh(self.handle, 2 if sah else 1, None))
 
     def bvh_stats(self):
         n, m, ms = C.c_uint32(), C.c_uint32(), C.c_double()
@@ -298,7 +299,7 @@ class Context:
     def load(self, s, device_bvh=False):
         self.upload_scene(s)
         if device_bvh:
-            self.build_bvh_device()
+            self.build_bvh_device(sah=(device_bvh == "sah"))
         else:
             self.build_bvh(s["bvh_nodes"], s["bvh_indices"])
 
@@ -500,6 +501,7 @@ def load_host_library():
         _host = C.CDLL(HOST_LIB_PATH)
         _host.nbh_last_error.restype = C.c_char_p
         _host.nbh_flatten_xml.argtypes = [C.c_char_p, C.c_char_p]
+        _host.nbh_flatten_xml_opts.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         _host.nbh_parse_xml.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         _host.nbh_vdb_list.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         _host.nbh_vdb_read.restype = C.c_longlong
@@ -554,13 +556,15 @@ def nvdb_write_leaves(nvdb_path, origins, values, index_to_world, grid="density"
         raise NbError(-1, h.nbh_last_error().decode())
 
 
-def load_xml(xml_path, nbs_path=None):
+def load_xml(xml_path, nbs_path=None, host_bvh=True):
     """Scene XML -> flattened scene dict, through the C++ host loader (parser, OBJ loader, plugin
-    flatten hooks, SAH BVH build). Raises NbError(NB_E_UNSUPPORTED) for plugins without a kernel."""
+    flatten hooks, SAH BVH build). Raises NbError(NB_E_UNSUPPORTED) for plugins without a kernel.
+    host_bvh=False skips the host SAH build (bvh_nodes / bvh_indices come back empty): load with
+    Context.load(s, device_bvh="sah")."""
     import tempfile
     h = load_host_library()
     tmp = nbs_path or os.path.join(tempfile.mkdtemp(prefix="nbs_"), "scene.nbs")
-    rc = h.nbh_flatten_xml(os.fsencode(xml_path), os.fsencode(tmp))
+    rc = h.nbh_flatten_xml_opts(os.fsencode(xml_path), os.fsencode(tmp), 1 if host_bvh else 0)
     if rc != 0:
         raise NbError(rc, h.nbh_last_error().decode())
     s = read_nbs(tmp)

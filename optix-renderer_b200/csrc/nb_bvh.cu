@@ -80,9 +80,9 @@ extern "C" {
 int nb_build_bvh(nb_ctx *ctx, int mode, const nb_bvh_import *imp) {
     if (!ctx) return NB_E_INVALID;
     if (!ctx->scene_ready) return nb_fail(ctx, NB_E_STATE, "nb_build_bvh: upload a scene first");
-    if (mode == NB_BVH_DEVICE) {
+    if (mode == NB_BVH_DEVICE || mode == NB_BVH_DEVICE_SAH) {
         NB_CUDA(ctx, cudaSetDevice(ctx->device));
-        return nb_build_bvh_device(ctx);
+        return nb_build_bvh_device(ctx, mode == NB_BVH_DEVICE_SAH ? 1 : 0);
     }
     if (mode != NB_BVH_IMPORT) return nb_fail(ctx, NB_E_UNSUPPORTED, "nb_build_bvh: mode %d not available", mode);
     if (!imp || !imp->nodes || !imp->indices || imp->n_nodes == 0)

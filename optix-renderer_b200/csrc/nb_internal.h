@@ -151,7 +151,7 @@ void nb_collapse_wide(const nb_bvh_node *nodes, uint32_t n, std::vector<float4> 
 void nb_update_wide(nb_ctx *ctx);
 
 /* nb_bvh_build.cu */
-int nb_build_bvh_device(nb_ctx *ctx);
+int nb_build_bvh_device(nb_ctx *ctx, int sah);
 
 /* nb_mega.cu */
 struct NbFilm;

@@ -1,4 +1,5 @@
 #include "b200state.h"
+#include <cstdlib>
 
 namespace nori {
 
@@ -27,7 +28,13 @@ static void checkOn(nb_ctx *c, int rc) {
 }
 
 bool B200State::preRender(const Scene &scene, uint64_t seed, uint32_t poolPaths, uint32_t layers) {
-    if (!scene.flatten(m_flat, &m_why)) return false;
+    int mode = m_treeMode;
+    if (const char *env = getenv("NB_BVH_BUILDER")) {
+        const std::string b(env);
+        if (b == "host") mode = NB_BVH_IMPORT; else if (b == "lbvh") mode = NB_BVH_DEVICE; else if (b == "sah") mode = NB_BVH_DEVICE_SAH;
+        else throw NoriException("NB_BVH_BUILDER=%s: host, lbvh or sah", b);
+    }
+    if (!scene.flatten(m_flat, &m_why, mode == NB_BVH_IMPORT)) return false;
     nb_scene_desc d = m_flat.desc();
     nb_bvh_import imp = { (uint32_t) m_flat.bvh_nodes.size(), m_flat.bvh_nodes.data(),
                           (uint32_t) m_flat.bvh_indices.size(), m_flat.bvh_indices.data() };
@@ -37,7 +44,7 @@ bool B200State::preRender(const Scene &scene, uint64_t seed, uint32_t poolPaths,
         int rc = nb_upload_scene(c, &d);
         if (rc == NB_E_UNSUPPORTED) { m_why = nb_last_error(c); return false; }
         checkOn(c, rc);
-        checkOn(c, nb_build_bvh(c, NB_BVH_IMPORT, &imp));
+        checkOn(c, nb_build_bvh(c, mode, mode == NB_BVH_IMPORT ? &imp : nullptr));
         rc = nb_render_begin(c, &p);
         if (rc == NB_E_UNSUPPORTED) { m_why = nb_last_error(c); return false; }
         checkOn(c, rc);

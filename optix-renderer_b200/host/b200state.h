@@ -17,6 +17,10 @@ public:
     /* OptixState::preRender (OptixState.render.cpp:19-85): flatten + upload + BVH + film setup.
      * false = the scene uses a plugin without a GPU kernel (the caller renders on its CPU path). */
     bool preRender(const Scene &scene, uint64_t seed = 0, uint32_t poolPaths = 0, uint32_t layers = 0);   /* layers: NB_LAYER_* bits */
+    /* which tree the GPUs traverse: NB_BVH_DEVICE_SAH (default: the reference's SAH criterion built on the device in
+     * milliseconds, no host build at all), NB_BVH_DEVICE (linear BVH), or NB_BVH_IMPORT (the reference's own tree from the
+     * host builder — what the bit-parity mode of the traversal needs). NB_BVH_BUILDER=host|lbvh|sah overrides. */
+    void setTreeBuilder(int mode) { m_treeMode = mode; }
     /* OptixState::renderSubframe (OptixState.cpp:485-510) */
     void renderSubframe(uint32_t currentSample, uint32_t samplesPerLaunch, uint32_t stride = 1, uint32_t offset = 0);
     /* one round of the sample loop for an `adaptive` sampler (render.cpp:283-360 with :323-335 inside): the blocks' variance
@@ -36,6 +40,7 @@ private:
     std::vector<nb_ctx *> m_all;
     FlatScene m_flat;
     std::string m_why;
+    int m_treeMode = NB_BVH_DEVICE_SAH;
 };
 
 } // namespace nori

@@ -14,13 +14,17 @@ const char *nbh_last_error(void) { return g_error.c_str(); }
 
 /* XML -> flattened scene file. Returns 0, or -1 (error text in nbh_last_error), or -5 when a
  * plugin of the scene has no GPU kernel (NB_E_UNSUPPORTED). */
-int nbh_flatten_xml(const char *xml_path, const char *nbs_path) {
+int nbh_flatten_xml_opts(const char *xml_path, const char *nbs_path, int host_tree);
+int nbh_flatten_xml(const char *xml_path, const char *nbs_path) { return nbh_flatten_xml_opts(xml_path, nbs_path, 1); }
+/* host_tree = 0: skip the host SAH build (seconds for a million triangles); the caller builds the tree on the device
+ * (nb_build_bvh NB_BVH_DEVICE_SAH) and the file's bvh sections are empty */
+int nbh_flatten_xml_opts(const char *xml_path, const char *nbs_path, int host_tree) {
     try {
         std::unique_ptr<nori::NoriObject> root(nori::loadFromXML(xml_path));
         if (root->getClassType() != nori::NoriObject::EScene) { g_error = "root element is not a <scene>"; return -1; }
         nori::FlatScene flat;
         std::string why;
-        if (!static_cast<nori::Scene *>(root.get())->flatten(flat, &why)) { g_error = why; return NB_E_UNSUPPORTED; }
+        if (!static_cast<nori::Scene *>(root.get())->flatten(flat, &why, host_tree != 0)) { g_error = why; return NB_E_UNSUPPORTED; }
         flat.writeNbs(nbs_path);
         return 0;
     } catch (const std::exception &e) {

@@ -34,11 +34,11 @@ static void writePfm(const std::string &path, const float *data, size_t h, size_
 
 int main(int argc, char **argv) {
     if (argc < 3) {
-        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs] [adaptive_cap=N]\n");
+        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs] [adaptive_cap=N] [bvh=sah|lbvh|host]\n");
         return 2;
     }
     try {
-        int spp = -1, device = 0, launch = 0, snapshot = 0, adaptiveCap = 0;   /* adaptive_cap: AdaptiveSampler's 1000-decision limit (black blocks reach it) */
+        int spp = -1, device = 0, launch = 0, snapshot = 0, adaptiveCap = 0, treeMode = NB_BVH_DEVICE_SAH;   /* adaptive_cap: AdaptiveSampler's 1000-decision limit (black blocks reach it) */
         uint64_t seed = 0;
         std::string flatOut;
         std::vector<int> devices;
@@ -59,6 +59,11 @@ int main(int argc, char **argv) {
             else if (!strncmp(argv[i], "snapshot=", 9)) snapshot = atoi(argv[i] + 9);
             else if (!strncmp(argv[i], "flat=", 5)) flatOut = argv[i] + 5;
             else if (!strncmp(argv[i], "adaptive_cap=", 13)) adaptiveCap = atoi(argv[i] + 13);
+            else if (!strncmp(argv[i], "bvh=", 4)) {
+                const std::string b(argv[i] + 4);
+                if (b == "host") treeMode = NB_BVH_IMPORT; else if (b == "lbvh") treeMode = NB_BVH_DEVICE; else if (b == "sah") treeMode = NB_BVH_DEVICE_SAH;
+                else throw NoriException("bvh=%s: host (the reference's tree, built on the host), lbvh or sah (built on the device; sah is the default)", b);
+            }
         }
         auto t0 = std::chrono::steady_clock::now();
         std::unique_ptr<NoriObject> root(loadFromXML(argv[1]));
@@ -66,6 +71,7 @@ int main(int argc, char **argv) {
         Scene *scene = static_cast<Scene *>(root.get());
         if (devices.empty()) devices.push_back(device);
         B200State state(devices);
+        state.setTreeBuilder(treeMode);
         if (!state.preRender(*scene, seed)) {
             fprintf(stderr, "nori_b200: this scene cannot run on the GPU backend: %s\n", state.whyUnsupported().c_str());
             return 3;

@@ -204,7 +204,8 @@ public:
     /* OptixState::preRender's gathering loop (OptixState.render.cpp:19-72): every plugin's hook,
      * then the BVH (built here with the reference's SAH algorithm, src/utils/bvh.cpp:100-380).
      * Returns false when some plugin has no GPU kernel (caller keeps its CPU renderer). */
-    bool flatten(FlatScene &out, std::string *why = nullptr) const;
+    /* buildTree = false: no host SAH build (bvh_nodes / bvh_indices stay empty); the caller builds the tree on the device */
+    bool flatten(FlatScene &out, std::string *why = nullptr, bool buildTree = true) const;
 private:
     std::vector<Shape *> m_shapes;
     std::vector<Emitter *> m_emitters;

@@ -61,7 +61,7 @@ std::string Scene::toString() const {
     return NoriException::format("Scene[shapes=%d, emitters=%d]", (int) m_shapes.size(), (int) m_emitters.size());
 }
 
-bool Scene::flatten(FlatScene &out, std::string *why) const {
+bool Scene::flatten(FlatScene &out, std::string *why, bool buildTree) const {
     auto fail = [&](const std::string &msg) { if (why) *why = msg; return false; };
     out = FlatScene();
     if (!m_integrator || m_integrator->getB200IntegratorType() < 0)
@@ -144,7 +144,8 @@ bool Scene::flatten(FlatScene &out, std::string *why) const {
     out.render.filter_table[NB_FILTER_RESOLUTION] = 0.0f;
     out.spp = (uint32_t) m_sampler->getSampleCount();
     if (m_sampler->isAdaptive()) { out.adaptive[0] = 4; out.adaptive[1] = (uint32_t) m_sampler->getInitialUniform(); }   /* block.h:31 */
-    buildBVH(m_shapes, out.bvh_nodes, out.bvh_indices);
+    out.bvh_nodes.clear(); out.bvh_indices.clear();
+    if (buildTree) buildBVH(m_shapes, out.bvh_nodes, out.bvh_indices);
     return true;
 }
 

@@ -1,4 +1,4 @@
-"""K_bvh_build (nb_build_bvh mode NB_BVH_DEVICE): a linear BVH built on the GPU. The tree differs
+"""K_bvh_build (nb_build_bvh modes NB_BVH_DEVICE, NB_BVH_DEVICE_SAH): a linear BVH, or a top-down binned SAH tree, built on the GPU. The tree differs
 from the reference's SAH tree, the intersection arithmetic does not, so on the oracle's ray sets
 the hits must agree except where the reference's own visiting order decides: exact-t ties and hits
 exactly on a box face. Counted here; images must match the reference renders like any other."""
@@ -10,13 +10,14 @@ from conftest import golden, rel_rmse
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("builder", [True, "sah"])
 @pytest.mark.parametrize("name", ["cbox", "table"])
-def test_device_tree_finds_the_same_hits(nb, ctx, name):
+def test_device_tree_finds_the_same_hits(nb, ctx, name, builder):
     scene = nb.read_nbs(golden(name + ".nbs"))
     rays = np.fromfile(golden(name + "_rays.bin"), dtype="<f4").reshape(-1, 8)
     want = np.fromfile(golden(name + "_hits.bin"), dtype=nb.hit_dtype)
     ctx.set_option("flat_scan", 0)               # walk the device-built tree even for the 14-primitive box
-    ctx.load(scene, device_bvh=True)
+    ctx.load(scene, device_bvh=builder)
     st = ctx.bvh_stats()
     n_prims = int(scene["shapes"]["prim_count"].sum())
     assert st["slots"] == n_prims and 1 <= st["nodes"] <= 2 * n_prims - 1 and st["build_ms"] > 0
@@ -26,7 +27,7 @@ def test_device_tree_finds_the_same_hits(nb, ctx, name):
     exact = same & np.where(hit, (got["t"].view("<u4") == want["t"].view("<u4")) & (got["u"].view("<u4") == want["u"].view("<u4"))
                             & (got["v"].view("<u4") == want["v"].view("<u4")), True)
     bad = ~exact
-    print(name, st, "rays", len(rays), "different", int(bad.sum()), "any-hit different", int((got["any_hit"] != want["any_hit"]).sum()))
+    print(name, builder, st, "rays", len(rays), "different", int(bad.sum()), "any-hit different", int((got["any_hit"] != want["any_hit"]).sum()))
     assert bad.mean() <= 1e-4
     # where the primitive differs, both found a hit at the same distance (a tie) or on a box face
     both = bad & hit & (got["shape"] >= 0)
@@ -34,7 +35,8 @@ def test_device_tree_finds_the_same_hits(nb, ctx, name):
     assert (got["any_hit"] != want["any_hit"]).mean() <= 1e-4
 
 
-def test_render_on_device_tree(nb, ctx):
+@pytest.mark.parametrize("builder", [True, "sah"])
+def test_render_on_device_tree(nb, ctx, builder):
     scene = nb.read_nbs(golden("table.nbs"))
     want = np.load(golden("table_ref_64spp.npy"))
     h, w, _ = want.shape
@@ -44,7 +46,7 @@ def test_render_on_device_tree(nb, ctx):
     cam["inv_output_size"] = [1.0 / w, 1.0 / h]
     s["camera"] = cam
     imgs = []
-    for device_bvh in (True, False):
+    for device_bvh in (builder, False):
         ctx.load(s, device_bvh=device_bvh)
         ctx.render_begin(nb.make_render_params(s, "path_mis", seed=7))
         ctx.render_subframe(0, 64)
@@ -53,3 +55,34 @@ def test_render_on_device_tree(nb, ctx):
     print("device tree vs imported tree relRMSE", rel_rmse(imgs[0], imgs[1]), "bias vs reference", bias)
     assert np.all(np.abs(bias) <= 0.01)
     assert rel_rmse(imgs[0], imgs[1]) <= 0.02      # same seed, same paths up to ties
+
+
+def test_cli_builds_its_tree_on_the_device(nb, tmp_path):
+    """nori_b200's default: no host SAH build, NB_BVH_DEVICE_SAH on the GPU. Same seed, same paths up to ties: the image of
+    bvh=host (the reference's tree, imported) within fp32 reassociation and a handful of tie pixels."""
+    import json, os, subprocess
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nori_b200")
+    xml = golden("scenes/table/table_path_mis.xml")
+    imgs = {}
+    for mode in ("sah", "host", "lbvh"):
+        out = tmp_path / (mode + ".npy")
+        r = subprocess.run([cli, xml, str(out), "spp=4", "seed=2", "bvh=" + mode], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+        imgs[mode] = np.load(out)
+        assert json.loads(r.stdout.strip().splitlines()[-1])["invalid_samples"] == 0
+    default = tmp_path / "default.npy"
+    r = subprocess.run([cli, xml, str(default), "spp=4", "seed=2"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert r.returncode == 0 and np.array_equal(np.load(default), imgs["sah"]) or rel_rmse(np.load(default), imgs["sah"]) < 1e-5
+    print("sah vs host", rel_rmse(imgs["sah"], imgs["host"]), "lbvh vs host", rel_rmse(imgs["lbvh"], imgs["host"]))
+    assert rel_rmse(imgs["sah"], imgs["host"]) <= 0.02 and rel_rmse(imgs["lbvh"], imgs["host"]) <= 0.02
+
+
+def test_python_loader_without_host_tree(nb, ctx):
+    s = nb.load_xml(golden("scenes/table/table_path_mis.xml"), host_bvh=False)
+    assert s["bvh_nodes"].size == 0 and s["bvh_indices"].size == 0
+    ctx.load(s, device_bvh="sah")
+    st = ctx.bvh_stats()
+    assert st["slots"] == int(s["shapes"]["prim_count"].sum()) and st["nodes"] > st["slots"] // 4
+    ctx.render_begin(nb.make_render_params(s, seed=1))
+    ctx.render_subframe(0, 2)
+    assert np.isfinite(ctx.film_download(normalize=True)).all()
