@@ -112,10 +112,15 @@ __device__ __forceinline__ float nb_grid_density(const float *density, const nb_
     const float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
     const float u = p.x - fx, v = p.y - fy, w = p.z - fz;
     const int nx = (int) m.grid_dims[0], ny = (int) m.grid_dims[1], nz = (int) m.grid_dims[2];
-    const int i = min(max((int) fx, 1), nx - 2), j = min(max((int) fy, 1), ny - 2), k = min(max((int) fz, 1), nz - 2);
+    const int i = (int) fx, j = (int) fy, k = (int) fz;
     const float *base = density + m.first_voxel;
+    const bool bricks = m.type == NB_MEDIUM_HETEROGENEOUS_BRICKS;
+    /* a stencil that would leave the array lies wholly in the border or beyond it: the sampler reads background there (the
+     * tracking loops never ask — they stay inside the box — but nb_medium_probe may) */
+    if (i < 1 || i > nx - 2 || j < 1 || j > ny - 2 || k < 1 || k > nz - 2)
+        return __ldg(bricks ? base + (size_t) ((nx + 7) >> 3) * ((ny + 7) >> 3) * ((nz + 7) >> 3) : base);   /* brick 0 / the array's corner voxel */
     size_t sx, sy;                                     /* strides of one step in x / y; z is contiguous in both layouts */
-    if (m.type == NB_MEDIUM_HETEROGENEOUS_BRICKS) {
+    if (bricks) {
         /* sparse grid (include/norib200.h): table entry of the 8^3 block -> its 10^3 brick, whose apron holds the stencil */
         const int by = (ny + 7) >> 3, bz = (nz + 7) >> 3;
         const size_t entries = (size_t) ((nx + 7) >> 3) * by * bz;
