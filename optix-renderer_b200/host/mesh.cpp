@@ -2,6 +2,9 @@
  * toWorld baked into positions/normals while reading, (v, vt, vn) triples deduplicated in order
  * of first use, quads split 0-1-2 / 3-0-2, per-vertex tangents/bitangents accumulated per
  * triangle; area CDF as DiscretePDF builds it (include/nori/dpdf.h:40-113). */
+#include <cstdlib>
+#include <cstring>
+#include <cstdio>
 #include "plugins.h"
 #include <fstream>
 #include <map>
@@ -96,51 +99,122 @@ private:
         if (t.size() >= 3 && !t[2].empty()) v.n = toUInt(t[2]);
         return v;
     }
+    /* The reference reads the file line by line through std::istringstream (obj.cpp:60-140): 4.6 s for the 49 MB, 1.3 M-triangle
+     * mesh of C3 — more than a hundred times the render it feeds once the tree is built on the device. Same grammar, same
+     * values (strtof rounds like operator>>(float)), same vertex numbering (first appearance of a p/uv/n triple), read from
+     * one buffer with a hash table in place of the ordered map. A number that does not parse reads as 0 and ends the line's
+     * numbers, as a failed stream extraction does. */
+    static const char *skipSpace(const char *p, const char *end) { while (p < end && (*p == ' ' || *p == '\t' || *p == '\r' || *p == '\v' || *p == '\f')) ++p; return p; }
+    static const char *tokenEnd(const char *p, const char *end) { while (p < end && !(*p == ' ' || *p == '\t' || *p == '\r' || *p == '\v' || *p == '\f')) ++p; return p; }
+    static int readFloats(const char *p, const char *end, float *out, int n) {
+        int got = 0;
+        for (; got < n; ++got) {
+            p = skipSpace(p, end);
+            if (p >= end) break;
+            char *stop = nullptr;
+            const float v = strtof(p, &stop);             /* the buffer ends with a NUL; a line ends with one too (see load) */
+            if (stop == p) break;
+            out[got] = v;
+            p = stop;
+        }
+        return got;
+    }
+    static OBJVertex parseVertexFast(const char *p, const char *end) {       /* obj.cpp:312-326: p[/uv[/n]] */
+        OBJVertex v;
+        uint32_t *field[3] = { &v.p, &v.uv, &v.n };
+        int f = 0;
+        const char *tok = p;
+        for (;; ++f) {
+            if (f > 2) throw NoriException("Invalid vertex data: \"%s\"", std::string(tok, end));
+            const char *q = p;
+            uint64_t r = 0;
+            while (q < end && *q >= '0' && *q <= '9') { r = r * 10 + (uint64_t) (*q - '0'); ++q; }
+            if (q < end && *q != '/') throw NoriException("Could not parse integer value \"%s\"", std::string(p, tokenEndSlash(p, end)));
+            if (q > p) *field[f] = (uint32_t) r;
+            else if (f == 0) throw NoriException("Could not parse integer value \"\"");
+            if (q >= end) break;
+            p = q + 1;
+        }
+        return v;
+    }
+    static const char *tokenEndSlash(const char *p, const char *end) { while (p < end && *p != '/') ++p; return p; }
     void load() {
-        std::ifstream is(m_filename);
-        if (is.fail()) throw NoriException("Unable to open OBJ file \"%s\"!", m_filename);
+        FILE *file = fopen(m_filename.c_str(), "rb");
+        if (!file) throw NoriException("Unable to open OBJ file \"%s\"!", m_filename);
+        std::vector<char> buf;
+        {
+            fseek(file, 0, SEEK_END);
+            const long size = ftell(file);
+            fseek(file, 0, SEEK_SET);
+            buf.resize((size_t) std::max(0L, size) + 1);
+            const size_t got = fread(buf.data(), 1, buf.size() - 1, file);
+            fclose(file);
+            buf.resize(got + 1);
+            buf[got] = '\0';
+        }
         std::vector<Vector3f> positions, normals;
         std::vector<Vector2f> texcoords;
         std::vector<uint32_t> indices;
         std::vector<OBJVertex> vertices;
-        std::map<std::tuple<uint32_t, uint32_t, uint32_t>, uint32_t> vertexMap;
-        std::string line_str;
-        while (std::getline(is, line_str)) {
-            std::istringstream line(line_str);
-            std::string prefix;
-            line >> prefix;
-            if (prefix == "v") {
-                float x = 0, y = 0, z = 0;
-                line >> x >> y >> z;
-                Point3f p = m_trafo.point(Point3f(x, y, z));
-                m_bbox.expandBy(p);
-                positions.push_back(p);
-            } else if (prefix == "vt") {
-                float x = 0, y = 0;
-                line >> x >> y;
-                texcoords.push_back(Vector2f(x, y));
-            } else if (prefix == "vn") {
-                float x = 0, y = 0, z = 0;
-                line >> x >> y >> z;
-                normals.push_back(m_trafo.normal(Normal3f(x, y, z)).normalized());
-            } else if (prefix == "f") {
-                std::string v1, v2, v3, v4;
-                line >> v1 >> v2 >> v3 >> v4;
-                OBJVertex verts[6];
-                int nVertices = 3;
-                verts[0] = parseVertex(v1); verts[1] = parseVertex(v2); verts[2] = parseVertex(v3);
-                if (!v4.empty()) { verts[3] = parseVertex(v4); verts[4] = verts[0]; verts[5] = verts[2]; nVertices = 6; }
-                for (int i = 0; i < nVertices; ++i) {
-                    const OBJVertex &v = verts[i];
-                    auto key = std::make_tuple(v.p, v.uv, v.n);
-                    auto it = vertexMap.find(key);
-                    if (it == vertexMap.end()) {
-                        vertexMap[key] = (uint32_t) vertices.size();
-                        indices.push_back((uint32_t) vertices.size());
-                        vertices.push_back(v);
-                    } else indices.push_back(it->second);
+        /* open addressing over (p, uv, n): the slot holds the vertex number + 1 */
+        std::vector<uint32_t> table(1u << 16, 0u);
+        auto hashOf = [](const OBJVertex &v) { uint64_t h = v.p * 0x9E3779B97F4A7C15ull; h ^= (h >> 29) + v.uv * 0xBF58476D1CE4E5B9ull; h ^= (h >> 31) + v.n * 0x94D049BB133111EBull; return h ^ (h >> 32); };
+        auto lookup = [&](const OBJVertex &v) -> uint32_t {
+            if ((vertices.size() + 1) * 2 > table.size()) {           /* grow and re-insert */
+                std::vector<uint32_t> bigger(table.size() * 4, 0u);
+                for (uint32_t id = 0; id < vertices.size(); ++id) {
+                    size_t at = hashOf(vertices[id]) & (bigger.size() - 1);
+                    while (bigger[at]) at = (at + 1) & (bigger.size() - 1);
+                    bigger[at] = id + 1;
                 }
+                table.swap(bigger);
             }
+            size_t at = hashOf(v) & (table.size() - 1);
+            for (;; at = (at + 1) & (table.size() - 1)) {
+                const uint32_t id = table[at];
+                if (!id) { table[at] = (uint32_t) vertices.size() + 1; vertices.push_back(v); return (uint32_t) vertices.size() - 1; }
+                const OBJVertex &o = vertices[id - 1];
+                if (o.p == v.p && o.uv == v.uv && o.n == v.n) return id - 1;
+            }
+        };
+        char *cur = buf.data(), *const fileEnd = buf.data() + buf.size() - 1;
+        while (cur < fileEnd) {
+            char *eol = (char *) memchr(cur, '\n', (size_t) (fileEnd - cur));
+            if (!eol) eol = fileEnd;
+            *eol = '\0';                                              /* strtof stops at the end of the line */
+            const char *p = skipSpace(cur, eol), *pe = tokenEnd(p, eol);
+            const size_t plen = (size_t) (pe - p);
+            if (plen == 1 && p[0] == 'v') {
+                float v[3] = { 0.f, 0.f, 0.f };
+                readFloats(pe, eol, v, 3);
+                const Point3f pt = m_trafo.point(Point3f(v[0], v[1], v[2]));
+                m_bbox.expandBy(pt);
+                positions.push_back(pt);
+            } else if (plen == 2 && p[0] == 'v' && p[1] == 't') {
+                float v[2] = { 0.f, 0.f };
+                readFloats(pe, eol, v, 2);
+                texcoords.push_back(Vector2f(v[0], v[1]));
+            } else if (plen == 2 && p[0] == 'v' && p[1] == 'n') {
+                float v[3] = { 0.f, 0.f, 0.f };
+                readFloats(pe, eol, v, 3);
+                normals.push_back(m_trafo.normal(Normal3f(v[0], v[1], v[2])).normalized());
+            } else if (plen == 1 && p[0] == 'f') {
+                OBJVertex verts[6];
+                int nTokens = 0;
+                const char *q = pe;
+                for (; nTokens < 4; ++nTokens) {
+                    q = skipSpace(q, eol);
+                    if (q >= eol) break;
+                    const char *qe = tokenEnd(q, eol);
+                    verts[nTokens] = parseVertexFast(q, qe);
+                    q = qe;
+                }
+                if (nTokens < 3) throw NoriException("Could not parse integer value \"\"");      /* parseVertex of an empty token */
+                int nVertices = 3;
+                if (nTokens == 4) { verts[4] = verts[0]; verts[5] = verts[2]; nVertices = 6; }
+                for (int i = 0; i < nVertices; ++i) indices.push_back(lookup(verts[i]));
+            }
+            cur = eol + 1;
         }
         m_F = indices;
         const size_t nv = vertices.size();

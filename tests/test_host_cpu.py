@@ -143,3 +143,35 @@ def test_adaptive_sampler_reaches_the_flat_scene(nb, built_lib):
     s = nb.load_xml(golden("scenes/cbox/cbox_adaptive_small.xml"))
     assert list(s["adaptive"]) == [4, 2] and int(s["spp"][0]) == 8
     assert "adaptive" not in nb.load_xml(golden("scenes/cbox/cbox_path_mis_small.xml"))
+
+
+def test_obj_reader_grammar(nb, built_lib, tmp_path):
+    """host/mesh.cpp reads OBJ files from one buffer (the reference: line by line through istringstream, obj.cpp:60-140) —
+    same grammar: v / vt / vn / f, p, p/uv, p//n and p/uv/n corners, quads cut into (0 1 2) (3 0 2), vertices numbered by
+    the first appearance of a corner triple, CRLF and trailing blanks, exponents, comments and unknown lines skipped."""
+    obj = ("# a comment\r\n"
+           "v 0 0 0\r\nv 1 0 0 \r\nv 1 1 0\nv 0 1 0\n  v 2.5e-1 -1.25E+0 +3.\n"
+           "vt 0 0\nvt 1 0\nvt 1 1\nvt 0 1\n"
+           "vn 0 0 2\n"
+           "o ignored\ns off\nusemtl none\n"
+           "f 1/1/1 2/2/1 3/3/1 4/4/1\n"          # quad
+           "f 1/1/1 3/3/1 5/1/1   \n"             # reuses corners 1/1/1 and 3/3/1, adds 5/1/1
+           "\n")
+    (tmp_path / "m.obj").write_text(obj, newline="")
+    xml = """<scene><integrator type="normals"/><camera type="perspective"><integer name="width" value="8"/><integer name="height" value="8"/></camera>
+<mesh type="obj"><string name="filename" value="m.obj"/><bsdf type="diffuse"/></mesh></scene>"""
+    (tmp_path / "s.xml").write_text(xml)
+    s = nb.load_xml(str(tmp_path / "s.xml"))
+    assert s["faces"].tolist() == [0, 1, 2, 3, 0, 2, 0, 2, 4]
+    want = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0], [0.25, -1.25, 3.0]], np.float32)
+    assert np.array_equal(s["positions"].reshape(-1, 3), want)
+    assert np.array_equal(s["uvs"].reshape(-1, 2), np.array([[0, 0], [1, 0], [1, 1], [0, 1], [0, 0]], np.float32))
+    assert np.array_equal(s["normals"].reshape(-1, 3), np.tile(np.float32([0, 0, 1]), (5, 1)))
+    for bad, what in (("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 x\n", "integer"), ("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1/1/1/1 2 3\n", "Invalid vertex"),
+                      ("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2\n", "integer")):
+        (tmp_path / "m.obj").write_text(bad)
+        with pytest.raises(nb.NbError, match=what):
+            nb.load_xml(str(tmp_path / "s.xml"))
+    (tmp_path / "m.obj").write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 7\n")      # a corner that names no vertex
+    with pytest.raises(nb.NbError):
+        nb.load_xml(str(tmp_path / "s.xml"))
