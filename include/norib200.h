@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 6
+#define NB_ABI_VERSION 7
 
 enum {
     NB_OK = 0,

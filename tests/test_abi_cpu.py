@@ -19,7 +19,7 @@ def test_exports_every_declared_symbol(nb, built_lib):
 
 
 def test_record_sizes_match(nb, built_lib):
-    assert built_lib.nb_abi_version() == 6
+    assert built_lib.nb_abi_version() == 7
     expect = [nb.shape_dtype.itemsize, nb.bsdf_dtype.itemsize, nb.emitter_dtype.itemsize, nb.camera_dtype.itemsize,
               nb.bvh_node_dtype.itemsize, C.sizeof(nb.SceneDesc), nb.ray_dtype.itemsize, nb.hit_dtype.itemsize,
               nb.render_params_dtype.itemsize, C.sizeof(nb.Counters), nb.medium_dtype.itemsize, nb.texture_dtype.itemsize]
