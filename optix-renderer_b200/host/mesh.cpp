@@ -4,7 +4,10 @@
  * triangle; area CDF as DiscretePDF builds it (include/nori/dpdf.h:40-113). */
 #include <cstdlib>
 #include <cstring>
+#include <chrono>
 #include <cstdio>
+#include <thread>
+#include <functional>
 #include "plugins.h"
 #include <fstream>
 #include <map>
@@ -139,6 +142,8 @@ private:
     }
     static const char *tokenEndSlash(const char *p, const char *end) { while (p < end && *p != '/') ++p; return p; }
     void load() {
+        const auto tStart = std::chrono::steady_clock::now();
+        auto lap = [&](const char *what) { if (getenv("NB_HOST_TIMING")) fprintf(stderr, "obj %s: %.3f s\n", what, std::chrono::duration<double>(std::chrono::steady_clock::now() - tStart).count()); };
         FILE *file = fopen(m_filename.c_str(), "rb");
         if (!file) throw NoriException("Unable to open OBJ file \"%s\"!", m_filename);
         std::vector<char> buf;
@@ -155,14 +160,15 @@ private:
         std::vector<Vector3f> positions, normals;
         std::vector<Vector2f> texcoords;
         std::vector<uint32_t> indices;
-        std::vector<OBJVertex> vertices;
+        std::vector<OBJVertex> vertices, corners;
         /* open addressing over (p, uv, n): the slot holds the vertex number + 1 */
         std::vector<uint32_t> table(1u << 16, 0u);
         auto hashOf = [](const OBJVertex &v) { uint64_t h = v.p * 0x9E3779B97F4A7C15ull; h ^= (h >> 29) + v.uv * 0xBF58476D1CE4E5B9ull; h ^= (h >> 31) + v.n * 0x94D049BB133111EBull; return h ^ (h >> 32); };
+        std::vector<uint32_t> hashed;                                  /* the vertices the table holds (the others are found by position) */
         auto lookup = [&](const OBJVertex &v) -> uint32_t {
-            if ((vertices.size() + 1) * 2 > table.size()) {           /* grow and re-insert */
+            if ((hashed.size() + 1) * 2 > table.size()) {             /* grow and re-insert */
                 std::vector<uint32_t> bigger(table.size() * 4, 0u);
-                for (uint32_t id = 0; id < vertices.size(); ++id) {
+                for (uint32_t id : hashed) {
                     size_t at = hashOf(vertices[id]) & (bigger.size() - 1);
                     while (bigger[at]) at = (at + 1) & (bigger.size() - 1);
                     bigger[at] = id + 1;
@@ -172,50 +178,125 @@ private:
             size_t at = hashOf(v) & (table.size() - 1);
             for (;; at = (at + 1) & (table.size() - 1)) {
                 const uint32_t id = table[at];
-                if (!id) { table[at] = (uint32_t) vertices.size() + 1; vertices.push_back(v); return (uint32_t) vertices.size() - 1; }
+                if (!id) {
+                    table[at] = (uint32_t) vertices.size() + 1;
+                    hashed.push_back((uint32_t) vertices.size());
+                    vertices.push_back(v);
+                    return (uint32_t) vertices.size() - 1;
+                }
                 const OBJVertex &o = vertices[id - 1];
                 if (o.p == v.p && o.uv == v.uv && o.n == v.n) return id - 1;
             }
         };
-        char *cur = buf.data(), *const fileEnd = buf.data() + buf.size() - 1;
-        while (cur < fileEnd) {
-            char *eol = (char *) memchr(cur, '\n', (size_t) (fileEnd - cur));
-            if (!eol) eol = fileEnd;
-            *eol = '\0';                                              /* strtof stops at the end of the line */
-            const char *p = skipSpace(cur, eol), *pe = tokenEnd(p, eol);
-            const size_t plen = (size_t) (pe - p);
-            if (plen == 1 && p[0] == 'v') {
-                float v[3] = { 0.f, 0.f, 0.f };
-                readFloats(pe, eol, v, 3);
-                const Point3f pt = m_trafo.point(Point3f(v[0], v[1], v[2]));
-                m_bbox.expandBy(pt);
-                positions.push_back(pt);
-            } else if (plen == 2 && p[0] == 'v' && p[1] == 't') {
-                float v[2] = { 0.f, 0.f };
-                readFloats(pe, eol, v, 2);
-                texcoords.push_back(Vector2f(v[0], v[1]));
-            } else if (plen == 2 && p[0] == 'v' && p[1] == 'n') {
-                float v[3] = { 0.f, 0.f, 0.f };
-                readFloats(pe, eol, v, 3);
-                normals.push_back(m_trafo.normal(Normal3f(v[0], v[1], v[2])).normalized());
-            } else if (plen == 1 && p[0] == 'f') {
-                OBJVertex verts[6];
-                int nTokens = 0;
-                const char *q = pe;
-                for (; nTokens < 4; ++nTokens) {
-                    q = skipSpace(q, eol);
-                    if (q >= eol) break;
-                    const char *qe = tokenEnd(q, eol);
-                    verts[nTokens] = parseVertexFast(q, qe);
-                    q = qe;
-                }
-                if (nTokens < 3) throw NoriException("Could not parse integer value \"\"");      /* parseVertex of an empty token */
-                int nVertices = 3;
-                if (nTokens == 4) { verts[4] = verts[0]; verts[5] = verts[2]; nVertices = 6; }
-                for (int i = 0; i < nVertices; ++i) indices.push_back(lookup(verts[i]));
+        /* the text is cut at line ends into one piece per host thread; the pieces are read side by side and joined in file
+         * order, so the arrays are the ones a single pass gives. Corners are numbered afterwards, in file order. */
+        struct Piece {
+            char *begin = nullptr, *end = nullptr;
+            std::vector<Vector3f> positions, normals;
+            std::vector<Vector2f> texcoords;
+            std::vector<OBJVertex> corners;
+            BoundingBox3f bbox;
+            std::string error;
+        };
+        char *const fileBegin = buf.data(), *const fileEnd = buf.data() + buf.size() - 1;
+        const size_t bytes = (size_t) (fileEnd - fileBegin);
+        size_t nPieces = std::max<size_t>(1, std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), bytes >> 21));
+        if (const char *env = getenv("NB_OBJ_THREADS")) nPieces = (size_t) std::max(1, atoi(env));
+        std::vector<Piece> pieces(nPieces);
+        {
+            char *at = fileBegin;
+            for (size_t k = 0; k < nPieces; ++k) {
+                pieces[k].begin = at;
+                char *stop = k + 1 == nPieces ? fileEnd : fileBegin + bytes * (k + 1) / nPieces;
+                if (stop < at) stop = at;
+                if (stop < fileEnd) { char *nl = (char *) memchr(stop, '\n', (size_t) (fileEnd - stop)); stop = nl ? nl + 1 : fileEnd; }
+                pieces[k].end = stop;
+                at = stop;
             }
-            cur = eol + 1;
         }
+        auto readPiece = [this](Piece &pc) {
+            try {
+                char *cur = pc.begin;
+                while (cur < pc.end) {
+                    char *eol = (char *) memchr(cur, '\n', (size_t) (pc.end - cur));
+                    if (!eol) eol = pc.end;
+                    *eol = '\0';                                      /* strtof stops at the end of the line (the buffer has one byte to spare) */
+                    const char *p = skipSpace(cur, eol), *pe = tokenEnd(p, eol);
+                    const size_t plen = (size_t) (pe - p);
+                    if (plen == 1 && p[0] == 'v') {
+                        float v[3] = { 0.f, 0.f, 0.f };
+                        readFloats(pe, eol, v, 3);
+                        const Point3f pt = m_trafo.point(Point3f(v[0], v[1], v[2]));
+                        pc.bbox.expandBy(pt);
+                        pc.positions.push_back(pt);
+                    } else if (plen == 2 && p[0] == 'v' && p[1] == 't') {
+                        float v[2] = { 0.f, 0.f };
+                        readFloats(pe, eol, v, 2);
+                        pc.texcoords.push_back(Vector2f(v[0], v[1]));
+                    } else if (plen == 2 && p[0] == 'v' && p[1] == 'n') {
+                        float v[3] = { 0.f, 0.f, 0.f };
+                        readFloats(pe, eol, v, 3);
+                        pc.normals.push_back(m_trafo.normal(Normal3f(v[0], v[1], v[2])).normalized());
+                    } else if (plen == 1 && p[0] == 'f') {
+                        OBJVertex verts[6];
+                        int nTokens = 0;
+                        const char *q = pe;
+                        for (; nTokens < 4; ++nTokens) {
+                            q = skipSpace(q, eol);
+                            if (q >= eol) break;
+                            const char *qe = tokenEnd(q, eol);
+                            verts[nTokens] = parseVertexFast(q, qe);
+                            q = qe;
+                        }
+                        if (nTokens < 3) throw NoriException("Could not parse integer value \"\"");      /* parseVertex of an empty token */
+                        int nVertices = 3;
+                        if (nTokens == 4) { verts[4] = verts[0]; verts[5] = verts[2]; nVertices = 6; }
+                        pc.corners.insert(pc.corners.end(), verts, verts + nVertices);
+                    }
+                    cur = eol + 1;
+                }
+            } catch (const std::exception &e) { pc.error = e.what(); }
+        };
+        {
+            std::vector<std::thread> workers;
+            for (size_t k = 1; k < nPieces; ++k) workers.emplace_back(readPiece, std::ref(pieces[k]));
+            readPiece(pieces[0]);
+            for (std::thread &w : workers) w.join();
+        }
+        lap("read + parse");
+        for (Piece &pc : pieces) {                                      /* the first error in file order is the one a single pass reports */
+            if (!pc.error.empty()) throw NoriException("%s", pc.error);
+            positions.insert(positions.end(), pc.positions.begin(), pc.positions.end());
+            normals.insert(normals.end(), pc.normals.begin(), pc.normals.end());
+            texcoords.insert(texcoords.end(), pc.texcoords.begin(), pc.texcoords.end());
+            m_bbox.expandBy(pc.bbox);
+            corners.insert(corners.end(), pc.corners.begin(), pc.corners.end());
+            pc = Piece();
+        }
+        /* corner numbering: nearly every corner of a mesh repeats the (uv, n) its position was first seen with — one array
+         * indexed by position answers those; the rest go through the hash table */
+        {
+            std::vector<uint32_t> firstOf(positions.size() + 2, 0u);      /* vertex number + 1 of the first corner seen at a position */
+            indices.reserve(corners.size());
+            for (const OBJVertex &v : corners) {
+                if ((size_t) v.p < firstOf.size()) {
+                    uint32_t &f = firstOf[v.p];
+                    if (f) {
+                        const OBJVertex &o = vertices[f - 1];
+                        if (o.uv == v.uv && o.n == v.n) { indices.push_back(f - 1); continue; }
+                    } else {
+                        /* first corner at this position: it is new unless the table already knows it — it cannot, a known corner
+                         * would have set firstOf */
+                        vertices.push_back(v);
+                        f = (uint32_t) vertices.size();
+                        indices.push_back(f - 1);
+                        continue;
+                    }
+                }
+                indices.push_back(lookup(v));
+            }
+        }
+        lap("join + corner numbering");
         m_F = indices;
         const size_t nv = vertices.size();
         m_V.resize(nv * 3);
@@ -251,6 +332,7 @@ private:
             }
         }
         m_name = m_filename;
+        lap("arrays");
     }
     std::string m_filename;
     Transform m_trafo;
