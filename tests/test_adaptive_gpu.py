@@ -34,8 +34,6 @@ def test_adaptive_rounds_follow_the_reference_sampler(nb, ctx):
     # a round: initialUniform + 1 uniform passes for every block (the reference's post-increment), then the first placed
     # pass always goes on (its change is measured against 10000): no block stops before 4
     assert passes.min() >= 4 * ROUNDS
-    import os
-    if os.path.isdir("gpurun_out"): np.save("gpurun_out/adaptive_dev_passes.npy", passes)
     print([(i["passes"], i["block_passes"], i["samples"]) for i in infos])
     # black blocks: their variance map is zero at every decision and they go round to the cap of 1000 decisions, 1001 passes
     # per round, in the reference and here (the same blocks: the image's black margin)
