@@ -535,6 +535,12 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     bool active = false;
     NbPathRegs ps;
     ps.flags = 0;
+#ifdef NB_FUSED_SCAN
+    bool pend = false, fin = false;         /* an NEE ray waits for the next pass over the slots; its path has ended and waits for it */
+    NbShadowRay pso;
+#else
+    const bool pend = false, fin = false;
+#endif
     int32_t medium = sc.ambient_medium;     /* volume integrators: the medium the path is in */
 #ifdef NB_SMEM_SLOTS
     /* experiment: the flat scene's slots staged in shared memory once per CTA (broadcast LDS instead of per-lane LDG) */
@@ -548,7 +554,7 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
     for (;;) {
         /* --- regenerate: idle lanes take the next camera samples of the warp's item --- */
         uint32_t pix, sidx;
-        if (nb_take_sample<EXT>(cur, tp, item_counter, !active, lane, lt_mask, pix, sidx)) {
+        if (nb_take_sample<EXT>(cur, tp, item_counter, !active && !fin, lane, lt_mask, pix, sidx)) {
             NbCameraRay r;
             nb_camera_sample(sc.camera, tp.plan, pix, sidx, ps.rng, r);
             ps.o = r.o; ps.d = r.d; ps.mint = r.mint; ps.maxt = r.maxt; ps.px = r.px; ps.py = r.py;
@@ -561,8 +567,33 @@ nb_k_tile(NbDeviceScene sc, NbFilm film, NbTilePlan tp, uint32_t *item_counter, 
             active = true;
             ++n_samples;
         }
-        if (!__any_sync(0xffffffffu, active)) break;
+        if (!__any_sync(0xffffffffu, active || pend)) break;
 
+#ifdef NB_FUSED_SCAN
+        if (PATH && FLAT && MIS) {
+            /* experiment: the NEE ray of the last bounce and the path's next ray share one pass over the slots (nb_scan2) */
+            NbHit hit;
+            bool occluded = false;
+            if (active) ++n_closest;
+            if (pend) ++n_any;
+            const bool found = nb_scan2(sc.slots, sc.n_slots, active, ps.o, ps.d, ps.mint, ps.maxt, hit, pend, pso.o, pso.d, pso.mint, pso.maxt, occluded);
+            if (pend) {
+                if (!occluded) { if (pso.cand >= 0.f) ps.w_ems = pso.cand; ps.Li += ps.w_ems * pso.c; }
+                pend = false;
+            }
+            if (fin) { nb_film_put<EXT>(film, ps.px, ps.py, ps.Li, stats); fin = false; }
+            if (active) {
+                bool ended = false, shadow = false;
+                if (!found) { ps.Li += ps.thr * nb_env_radiance<EXT>(sc, ps.d); ended = true; }
+                else ended = !nb_path_bounce<MIS, EXT>(sc, tp.plan.max_depth, ps, hit, shadow, pso);
+                pend = shadow;
+                if (ended) {
+                    active = false;
+                    if (pend) fin = true; else nb_film_put<EXT>(film, ps.px, ps.py, ps.Li, stats);
+                }
+            }
+        } else
+#endif
         if (PATH) {
             bool ended = false, shadow = false;
             NbShadowRay so;

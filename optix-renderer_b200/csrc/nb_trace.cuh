@@ -390,6 +390,45 @@ __device__ __forceinline__ bool nb_scan(const float4 *__restrict__ slots, uint32
     return found;
 }
 
+/* Experiment (NB_FUSED_SCAN, off: measured slower): two rays per lane in ONE pass over the slots — the closest hit of
+ * a main ray (if `main_on`) and the any-hit answer of a shadow ray (if `shadow_on`), i.e. the flat render kernels' NEE ray of
+ * bounce k and the path's ray of bounce k + 1. Each ray sees the tests of nb_scan<false> / nb_scan<true> in the same order with
+ * the same arithmetic; what is shared is the slot fetch and the loop. Returns the main ray's "found"; `occluded` answers the
+ * shadow ray. */
+__device__ __forceinline__ bool nb_scan2(const float4 *__restrict__ slots, uint32_t n_slots, bool main_on, float3 o, float3 d, float mint, float maxt,
+                                         NbHit &hit, bool shadow_on, float3 so, float3 sd, float smint, float smaxt, bool &occluded) {
+    hit.t = INFINITY; hit.u = 0.f; hit.v = 0.f; hit.slot = 0xffffffffu;
+    occluded = false;
+    if (mint == NB_EPSILON) {
+        const float m = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z));
+        const float s = __fmul_rn(mint, m);
+        mint = (mint < s) ? s : mint;
+    }
+    if (smint == NB_EPSILON) {
+        const float m = fmaxf(fmaxf(fabsf(so.x), fabsf(so.y)), fabsf(so.z));
+        const float s = __fmul_rn(smint, m);
+        smint = (smint < s) ? s : smint;
+    }
+    main_on = main_on && !(maxt < mint);
+    shadow_on = shadow_on && !(smaxt < smint);
+    bool found = false;
+    for (uint32_t s = 0; s < n_slots; ++s) {
+        const float4 s0 = __ldg(slots + 3 * s), s1 = __ldg(slots + 3 * s + 1), s2 = __ldg(slots + 3 * s + 2);
+        const bool sphere = (__float_as_uint(s2.y) & NB_SLOT_SPHERE) != 0u;
+        if (main_on) {
+            float u = 0.f, v = 0.f, t;
+            const bool ok = sphere ? nb_sphere_hit(s0, o, d, mint, maxt, t) : nb_tri_hit(s0, s1, s2, o, d, mint, maxt, u, v, t);
+            if (ok) { found = true; maxt = t; hit.t = t; hit.u = u; hit.v = v; hit.slot = s; }
+        }
+        if (shadow_on) {
+            float u = 0.f, v = 0.f, t;
+            const bool ok = sphere ? nb_sphere_hit(s0, so, sd, smint, smaxt, t) : nb_tri_hit(s0, s1, s2, so, sd, smint, smaxt, u, v, t);
+            if (ok) { occluded = true; shadow_on = false; }
+        }
+    }
+    return found;
+}
+
 /* nb_scan over slots held in kernel-parameter space (NbDeviceScene::flat_slots): same tests, same order, same bits;
  * the warp-uniform slot index makes every fetch a constant-bank broadcast. */
 template <bool ANY>

@@ -1,4 +1,5 @@
 # fused closest + shadow scan (NB_FUSED_SCAN) against the shipped kernel: throughput and per-seed image identity, cbox path_mis
+# variants first: printf 'fused -DNB_FUSED_SCAN\nfused7 -DNB_FUSED_SCAN -DNB_TILE_MIN_BLOCKS=6\n' > /tmp/v.txt && bash tools/scripts/build_variants.sh /tmp/v.txt
 mkdir -p gpurun_out
 for lib in optix-renderer_b200/libnorib200.so optix-renderer_b200/variants/libnorib200_fused.so optix-renderer_b200/variants/libnorib200_fused7.so; do
   echo "== $lib"
