@@ -495,7 +495,9 @@ public:
     void activate() override {                          /* NvdbVolume::loadFromFile (NvdbVolume.vdb.cpp:9-40) */
         const size_t dot = m_filename.rfind('.');
         const std::string ext = dot == std::string::npos ? "" : m_filename.substr(dot);
-        if (ext == ".nvdb") { density = nvdbReadFloatGrid(m_filename, "density", layout != "dense"); return; }     /* the reference's cache format (nvdb.cpp); leaves kept as they are when the box is mostly empty */
+        /* the reference's cache format (nvdb.cpp). Grid 0 of the file, whatever its name (NvdbVolume::loadNanoVdb, NvdbVolume.vdb.cpp:65:
+         * readGrid(filename, 0, ..)); leaves kept as they are when the box is mostly empty */
+        if (ext == ".nvdb") { density = nvdbReadFloatGrid(m_filename, "", layout != "dense"); return; }
         if (ext == ".nbv") { density = vdbReadNbv(m_filename); return; }     /* dense dump (vdb.h) */
         if (ext != ".vdb") throw NoriException("Volume: file extension %s unknown.", ext);
         density = vdbReadFloatGrid(m_filename, "density");

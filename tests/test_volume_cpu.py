@@ -293,3 +293,28 @@ def test_a_1024_cubed_box_of_sparse_smoke_is_never_filled(nb, built_lib, tmp_pat
         info = json.loads(r.stdout)
         assert info["active"] == 3 * 512 and info["min"] == [0, 0, 0] and info["max"] == [1023, 1023, 1023]
         assert info["probe"] == pytest.approx([float(vals[0][1, 2, 3]), float(vals[1][1, 2, 3]), float(vals[2][1, 2, 3]), 0.0])
+
+
+def test_nvdb_scene_takes_grid_zero_whatever_its_name(nb, built_lib, tmp_path):
+    """NvdbVolume::loadNanoVdb reads grid 0 of the file by INDEX (NvdbVolume.vdb.cpp:65): a cache whose first grid is not
+    called "density" still loads."""
+    import shutil
+    shutil.copytree(golden("scenes/vol/meshes"), tmp_path / "meshes")
+    nb.to_nvdb(golden(VDB), str(tmp_path / "other.nvdb"), "density")
+    g = nb.vdb_read(str(tmp_path / "other.nvdb"), "density")
+    org = (np.array(g["bbox_min"]) & ~7)
+    # the same voxels under another grid name, through the leaf writer
+    v = g["values"]; pad = [(int(b - o), int((-(b - o + s)) % 8)) for b, o, s in zip(g["bbox_min"], org, v.shape)]
+    vp = np.pad(v, pad)
+    leaves, origins = [], []
+    for i in range(0, vp.shape[0], 8):
+        for j in range(0, vp.shape[1], 8):
+            for k in range(0, vp.shape[2], 8):
+                leaves.append(vp[i:i + 8, j:j + 8, k:k + 8]); origins.append(org + [i, j, k])
+    nb.nvdb_write_leaves(str(tmp_path / "smoke.nvdb"), np.array(origins), np.array(leaves), g["index_to_world"], grid="smoke")
+    xml = open(golden("scenes/vol/cbox_heterog_nvdb.xml")).read().replace("fluid_data_0050.nvdb", "smoke.nvdb")
+    (tmp_path / "s.xml").write_text(xml)
+    a, b = nb.load_xml(str(tmp_path / "s.xml")), nb.load_xml(golden("scenes/vol/cbox_heterog_nvdb.xml"))
+    assert a["media"][0]["max_density"] == b["media"][0]["max_density"]
+    # the leaf writer marks zero voxels inactive, so the box is the box of the non-zero voxels: compare where both have voxels
+    assert np.count_nonzero(a["density"]) == np.count_nonzero(b["density"])
