@@ -169,3 +169,23 @@ def test_cli_progressive_snapshots(nb, tmp_path):
     assert r.returncode == 0, r.stderr
     a, b = np.load(fresh), snaps[1]
     assert np.abs(a - b).max() <= 1e-4 * max(1.0, np.abs(a).max())      # same samples, different order of fp32 additions
+
+
+def test_cli_writes_png_like_save_to_ldr(nb, tmp_path):
+    """out.png: Bitmap::saveToLDR (src/utils/bitmap.cpp:109-140) — sRGB transfer, x 255 + 0.5, clamp — decoded here by PIL and
+    compared with the same render written as .npy."""
+    import os
+    import subprocess
+    from PIL import Image
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nori_b200")
+    xml = golden("scenes/cbox/cbox_path_mis_small.xml")
+    for name in ("a.png", "a.npy"):
+        r = subprocess.run([cli, xml, str(tmp_path / name), "spp=16", "seed=5"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        assert r.returncode == 0, r.stderr
+    png = np.asarray(Image.open(tmp_path / "a.png").convert("RGB")).astype(np.int32)
+    lin = np.load(tmp_path / "a.npy").astype(np.float32)
+    g = np.where(lin <= 0.0031308, 12.92 * lin, 1.055 * np.power(np.maximum(lin, 0), 1 / 2.4) - 0.055)
+    want = np.clip(255.0 * g + 0.5, 0, 255).astype(np.uint8).astype(np.int32)
+    assert png.shape == want.shape
+    assert np.abs(png - want).max() <= 1              # the two runs sum their film in different orders: a byte may round the other way
+    assert (png != want).mean() < 0.01
