@@ -540,9 +540,10 @@ def vdb_read(path, grid="density"):
 
 def to_nvdb(src_path, nvdb_path, grid="density", sparse=False):
     """.vdb / .nbv / .nvdb -> the NanoVDB cache file the reference would write next to a .vdb (host/nvdb.cpp).
-    sparse: only the voxels that differ from the background are active and only the 8^3 leaves that hold some are stored."""
+    sparse=True: only the voxels that differ from the background are active and only the 8^3 leaves that hold some are stored;
+    sparse="file": the source file's own leaves and active masks, as openToNanoVDB keeps them (NvdbVolume.vdb.cpp:118-119)."""
     h = load_host_library()
-    if h.nbh_to_nvdb(os.fsencode(src_path), grid.encode(), os.fsencode(nvdb_path), int(bool(sparse))) != 0:
+    if h.nbh_to_nvdb(os.fsencode(src_path), grid.encode(), os.fsencode(nvdb_path), 2 if sparse == "file" else int(bool(sparse))) != 0:
         raise NbError(-1, h.nbh_last_error().decode())
 
 

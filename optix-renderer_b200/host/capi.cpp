@@ -99,9 +99,10 @@ extern "C" int nbh_to_nvdb(const char *src_path, const char *grid, const char *n
     try {
         const std::string p(src_path);
         const std::string ext = p.rfind('.') == std::string::npos ? "" : p.substr(p.rfind('.'));
-        nori::VdbGrid g = ext == ".nbv" ? nori::vdbReadNbv(p) : ext == ".nvdb" ? nori::nvdbReadFloatGrid(p, grid) : nori::vdbReadFloatGrid(p, grid);
+        /* sparse = 2: keep the source file's own leaves and masks (what openToNanoVDB keeps of a .vdb, NvdbVolume.vdb.cpp:118-119) */
+        nori::VdbGrid g = ext == ".nbv" ? nori::vdbReadNbv(p) : ext == ".nvdb" ? nori::nvdbReadFloatGrid(p, grid, sparse == 2) : nori::vdbReadFloatGrid(p, grid, sparse == 2);
         if (g.name.empty() || ext == ".nbv") g.name = grid;          /* a .nbv dump carries no grid name */
-        nori::nvdbWriteFloatGrid(sparse ? nori::vdbSparsify(g) : g, nvdb_path);    /* sparse: only blocks that hold something other than background */
+        nori::nvdbWriteFloatGrid(sparse == 1 ? nori::vdbSparsify(g) : g, nvdb_path);    /* sparse: only blocks that hold something other than background */
         return 0;
     } catch (const std::exception &e) { g_error = e.what(); return -1; }
 }

@@ -500,7 +500,7 @@ public:
         if (ext == ".nvdb") { density = nvdbReadFloatGrid(m_filename, "", layout != "dense"); return; }
         if (ext == ".nbv") { density = vdbReadNbv(m_filename); return; }     /* dense dump (vdb.h) */
         if (ext != ".vdb") throw NoriException("Volume: file extension %s unknown.", ext);
-        density = vdbReadFloatGrid(m_filename, "density");
+        density = vdbReadFloatGrid(m_filename, "density", layout != "dense");
     }
     std::string toString() const override { return "Volume[\n  filename = " + m_filename + ",\n]"; }
     VdbGrid density;

@@ -2,6 +2,7 @@
  * compression flags, node-mask compression, optional half-float storage, Blosc / zip / raw
  * buffers). Written from the published file layout; replaces the openvdb::io::File use of
  * src/textures/NvdbVolume.vdb.cpp:83-134. See vdb.h. */
+#include <cstdlib>
 #include "vdb.h"
 #include "codecs.h"
 #include <cstring>
@@ -200,7 +201,7 @@ std::vector<std::pair<std::string, std::string>> vdbListGrids(const std::string 
     return out;
 }
 
-VdbGrid vdbReadFloatGrid(const std::string &path, const std::string &gridName) {
+VdbGrid vdbReadFloatGrid(const std::string &path, const std::string &gridName, bool keepSparse) {
     Reader r = openFile(path);
     const FileHeader h = readHeader(r);
     const Descriptor *d = nullptr;
@@ -265,6 +266,34 @@ VdbGrid vdbReadFloatGrid(const std::string &path, const std::string &gridName) {
      * boundary leaves) equal the background in fog volumes and are dropped */
     double total = 1.0;
     for (int k = 0; k < 3; ++k) { out.bbox_min[k] = amin[k]; out.bbox_max[k] = amax[k]; out.dims[k] = amax[k] - amin[k] + 1; total *= out.dims[k]; }
+    /* sparse form (vdb.h): the file's leaves with their masks — what openToNanoVDB keeps (NvdbVolume.vdb.cpp:118-119) — when the
+     * caller can take them and the box is mostly background or too large to fill; 8^3 tiles become constant leaves */
+    {
+        const char *force = getenv("NB_VOLUME_SPARSE");
+        const bool wantSparse = force ? atoi(force) != 0 : (total > 134217728.0 || (double) tree.leaves.size() * 512.0 * 4.0 < total);
+        if (keepSparse && wantSparse && !tree.leaves.empty()) {
+            for (const Tile &t : tree.tiles)
+                if (t.dim > 8) throw NoriException("%s: grid \"%s\" holds a %d^3 value tile; not supported in the sparse form", path, gridName, t.dim);
+            out.leaves.reserve(tree.leaves.size() + tree.tiles.size());
+            for (const Leaf &leaf : tree.leaves) {
+                VdbLeaf l;
+                memcpy(l.org, leaf.origin, sizeof(l.org));
+                memcpy(l.v, leaf.values.data(), sizeof(l.v));
+                for (int w = 0; w < 8; ++w) l.mask[w] = 0;
+                for (uint32_t n = 0; n < 512; ++n) if (leaf.valueMask.on(n)) l.mask[n >> 6] |= 1ull << (n & 63);
+                out.leaves.push_back(l);
+            }
+            for (const Tile &t : tree.tiles) {
+                VdbLeaf l;
+                memcpy(l.org, t.origin, sizeof(l.org));
+                std::fill(l.v, l.v + 512, t.value);
+                std::fill(l.mask, l.mask + 8, t.active ? ~0ull : 0ull);
+                out.leaves.push_back(l);
+            }
+            out.indexLeaves();
+            return out;
+        }
+    }
     if (total > 2147483648.0) throw NoriException("%s: grid \"%s\" spans %dx%dx%d voxels, too large for a dense array", path, gridName, out.dims[0], out.dims[1], out.dims[2]);
     out.values.assign((size_t) total, out.background);
     auto put = [&](int i, int j, int k, float v) {

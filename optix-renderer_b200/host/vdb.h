@@ -66,7 +66,7 @@ VdbGrid vdbSparsify(const VdbGrid &g);
 /* All grids' names and types, in file order (openvdb::io::File::beginName) */
 std::vector<std::pair<std::string, std::string>> vdbListGrids(const std::string &path);
 /* One float grid by name; throws NoriException if absent or not a float 5-4-3 tree */
-VdbGrid vdbReadFloatGrid(const std::string &path, const std::string &gridName);
+VdbGrid vdbReadFloatGrid(const std::string &path, const std::string &gridName, bool keepSparse = false);   /* keepSparse: as nvdbReadFloatGrid */
 /* ".nbv": a grid as a plain dense dump — "NBV1", i32 dims[3], i32 bbox_min[3], f64 index_to_world[12]
  * (row-major 3x4), f32 background, f32 values (x slowest). Every voxel of the box counts as active. */
 void vdbWriteNbv(const VdbGrid &g, const std::string &path);

@@ -318,3 +318,28 @@ def test_nvdb_scene_takes_grid_zero_whatever_its_name(nb, built_lib, tmp_path):
     assert a["media"][0]["max_density"] == b["media"][0]["max_density"]
     # the leaf writer marks zero voxels inactive, so the box is the box of the non-zero voxels: compare where both have voxels
     assert np.count_nonzero(a["density"]) == np.count_nonzero(b["density"])
+
+
+def test_vdb_leaves_kept_as_they_are(nb, built_lib, tmp_path, monkeypatch):
+    """The .vdb reader's sparse form: the file's own leaf nodes and active masks (what the reference's openToNanoVDB keeps,
+    NvdbVolume.vdb.cpp:118-119) go to the .nvdb cache and to the device's bricks without a dense box in between; the voxels
+    are the dense reader's."""
+    dense = nb.vdb_read(golden(VDB), "density")
+    nb.to_nvdb(golden(VDB), str(tmp_path / "leaves.nvdb"), "density", sparse="file")
+    back = nb.vdb_read(str(tmp_path / "leaves.nvdb"), "density")
+    for key in ("bbox_min", "bbox_max", "index_to_world"):
+        assert np.array_equal(back[key], dense[key]), key
+    assert np.array_equal(back["values"], dense["values"]) and back["active_voxels"] == dense["active_voxels"] == 14112
+    assert back["max"] == dense["max"] and back["min"] == dense["min"]
+    if os.path.exists(NVDB_TOOL):                                          # and NanoVDB agrees about the file
+        r = subprocess.run([NVDB_TOOL, "info", str(tmp_path / "leaves.nvdb")], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        info = json.loads(r.stdout)
+        assert info["active"] == 14112 and info["min"] == [0, 0, 0] and info["max"] == [20, 20, 31] and info["leaves"] == 36
+    monkeypatch.setenv("NB_VOLUME_SPARSE", "1")                            # the scene, through leaves -> bricks
+    s = nb.load_xml(golden("scenes/vol/cbox_heterog.xml"))
+    monkeypatch.delenv("NB_VOLUME_SPARSE")
+    d = nb.load_xml(golden("scenes/vol/cbox_heterog.xml"))
+    assert s["media"][0]["type"] == nb.MEDIUM_HETEROGENEOUS_BRICKS and d["media"][0]["type"] == nb.MEDIUM_HETEROGENEOUS
+    full, _, _ = expand_bricks(s["density"], s["media"][0])
+    assert np.array_equal(full, d["density"].reshape(25, 25, 36))
