@@ -77,3 +77,42 @@ def test_adaptive_rounds_mix_with_plain_subframes(nb, ctx):
     assert np.isfinite(img).all() and img.mean() > 0.1
     with pytest.raises(nb.NbError):
         ctx.render_adaptive_round(16, 2)          # block sizes 2..8
+
+
+@pytest.mark.parametrize("bs", [2, 8])
+def test_adaptive_rounds_other_block_sizes(nb, ctx, bs):
+    """block_size is a parameter of the entry (the reference compiles 4 in): 2 and 8 keep the books and the image."""
+    s = nb.load_xml(golden("scenes/cbox/cbox_adaptive_small.xml"))
+    ctx.load(s)
+    ctx.render_begin(nb.make_render_params(s, seed=6))
+    infos = [ctx.render_adaptive_round(bs, 2, round_cap=12) for _ in range(3)]
+    n_blocks = ((200 + bs - 1) // bs) * ((150 + bs - 1) // bs)
+    passes = ctx.adaptive_block_passes(n_blocks)
+    by, bx = np.divmod(np.arange(n_blocks), (200 + bs - 1) // bs)
+    area = np.minimum(bs, 200 - bs * bx) * np.minimum(bs, 150 - bs * by)
+    assert all(i["blocks"] == n_blocks for i in infos)
+    assert sum(i["samples"] for i in infos) == ctx.counters()["samples"] == int((passes * area).sum())
+    assert passes.min() >= 4 * 3
+    img = ctx.film_download(normalize=True)
+    want = np.load(golden("cbox_ref_256spp.npy"))
+    bias = (img.mean(axis=(0, 1)) - want.mean(axis=(0, 1))) / want.mean(axis=(0, 1))
+    assert np.isfinite(img).all() and np.all(np.abs(bias) <= 0.03), bias
+
+
+def test_adaptive_rounds_on_a_tree_scene(nb, ctx):
+    """The sample list is consumed by the per-lane walk kernels too (table: 22 766 triangles, production tree)."""
+    s = dict(nb.load_xml(golden("scenes/table/table_path_mis.xml")))
+    cam = s["camera"].copy(); cam["width"], cam["height"] = 200, 150; cam["inv_output_size"] = [1 / 200, 1 / 150]
+    s["camera"] = cam
+    ctx.load(s)
+    ctx.render_begin(nb.make_render_params(s, seed=2))
+    infos = [ctx.render_adaptive_round(4, 2, round_cap=10) for _ in range(4)]
+    c = ctx.counters()
+    assert sum(i["samples"] for i in infos) == c["samples"] and c["invalid_samples"] == 0
+    a = ctx.film_download(normalize=True)
+    ctx.render_begin(nb.make_render_params(s, seed=3))
+    ctx.render_subframe(0, max(1, int(round(c["samples"] / (200 * 150)))))
+    b = ctx.film_download(normalize=True)
+    bias = (a.mean(axis=(0, 1)) - b.mean(axis=(0, 1))) / b.mean(axis=(0, 1))
+    print("table adaptive vs uniform at the same sample count: bias", bias, "relRMSE", rel_rmse(a, b))
+    assert np.isfinite(a).all() and np.all(np.abs(bias) <= 0.03)
