@@ -180,10 +180,10 @@ def test_device_sah_degenerate_inputs(nb, ctx, case):
 
 @pytest.mark.parametrize("n,seed,clustered", [(1000, 0, False), (100000, 1, False), (100000, 2, True), (400000, 3, True)])
 def test_device_builders_agree_on_random_soups(nb, ctx, n, seed, clustered):
-    """Two independent builders (Morton radix tree, top-down SAH) over the same random triangles: the same nearest hit for
-    every ray, bit for bit in t — any valid tree finds the nearest primitive, and ties between distinct triangles have measure
-    zero in a random soup. What remains is the slab test's rounding: a ray that grazes a node's (ulp-padded) box can lose that
-    node in one tree and not in the other; seen once in 200 000 rays on the densest soup, allowed at that rate."""
+    """Two independent builders (Morton radix tree, top-down SAH) over the same random triangles: the same nearest distance for
+    every ray, bit for bit — any valid tree finds the nearest primitive. The primitive may differ only where two triangles are
+    hit at the same fp32 distance (seen once in 200 000 rays on the densest soup: t = 8.546967 for both, 8.5469658 and
+    8.5469684 in double; the trees order their leaves differently and each keeps the later one, tools/debug/soup_dbg.py)."""
     rng = np.random.default_rng(seed)
     c = rng.normal(size=(n, 1, 3)) * (0.05 if clustered else 1.0) + (rng.integers(0, 5, (n, 1, 1)) * 3.0 if clustered else 0.0)
     tris = (c + rng.normal(size=(n, 3, 3)) * (0.01 if clustered else 0.05)).astype(np.float32)
@@ -201,6 +201,8 @@ def test_device_builders_agree_on_random_soups(nb, ctx, n, seed, clustered):
         out[sah] = (ctx.trace_rays(rays, any_hit=True), ctx.bvh_stats())
     x, y = out[False][0], out[True][0]
     hits = int((x["shape"] >= 0).sum())
-    differ = int((x["t"].view("<u4") != y["t"].view("<u4")).sum()) + int((x["prim"] != y["prim"]).sum()) + int((x["any_hit"] != y["any_hit"]).sum())
-    print(n, "triangles, rays that hit", hits, "differences", differ, out[False][1], out[True][1])
-    assert hits > m // 4 and differ <= 3 * 3              # a lost node changes t, primitive and any-hit of its ray
+    other_prim = int((x["prim"] != y["prim"]).sum())
+    print(n, "triangles, rays that hit", hits, "same distance but another primitive", other_prim, out[False][1], out[True][1])
+    assert hits > m // 4
+    assert np.array_equal(x["t"].view("<u4"), y["t"].view("<u4")) and np.array_equal(x["any_hit"], y["any_hit"]) and np.array_equal(x["shape"], y["shape"])
+    assert other_prim <= 3
