@@ -577,7 +577,9 @@ public:
     bool getB200MediumData(nb_medium &out, FlatScene &flat) const override {
         memset(&out, 0, sizeof(out));
         const VdbGrid &g = m_volume->density;
-        if (m_emitter || m_temperatureScale > 1e-4f) return false;     /* volume emission: no kernel */
+        /* temperatureScale: the reference sums colorFromTemperature into a local it never returns (heterogmedium.cpp:152, :165-167) —
+         * the property has no effect there, so it has none here. A volume light inside a heterogeneous medium: no kernel. */
+        if (m_emitter) return false;
         if (g.active_voxels == 0 || !(g.value_max > 0.f)) return false;
         out.type = NB_MEDIUM_HETEROGENEOUS;                              /* or _BRICKS, below */
         for (int i = 0; i < 3; ++i) out.mu_t[i] = m_sigma_a[i] + m_sigma_s[i];

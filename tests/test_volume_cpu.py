@@ -343,3 +343,16 @@ def test_vdb_leaves_kept_as_they_are(nb, built_lib, tmp_path, monkeypatch):
     assert s["media"][0]["type"] == nb.MEDIUM_HETEROGENEOUS_BRICKS and d["media"][0]["type"] == nb.MEDIUM_HETEROGENEOUS
     full, _, _ = expand_bricks(s["density"], s["media"][0])
     assert np.array_equal(full, d["density"].reshape(25, 25, 36))
+
+
+def test_temperature_scale_is_accepted_and_has_no_effect(nb, built_lib, tmp_path):
+    """heterog's temperatureScale feeds a local the reference never returns (heterogmedium.cpp:152, :165-167): a scene that sets
+    it loads, and flattens to the scene without it."""
+    import shutil
+    shutil.copytree(golden("scenes/vol/meshes"), tmp_path / "meshes")
+    shutil.copy(golden("scenes/vol/fluid.nbv"), tmp_path / "fluid.nbv")
+    xml = open(golden("scenes/vol/cbox_heterog_fluid_small.xml")).read()
+    assert '<float name="densityScale"' in xml
+    (tmp_path / "s.xml").write_text(xml.replace('<float name="densityScale"', '<float name="temperatureScale" value="3.5"/>\n\t\t\t<float name="densityScale"', 1))
+    a, b = nb.load_xml(str(tmp_path / "s.xml")), nb.load_xml(golden("scenes/vol/cbox_heterog_fluid_small.xml"))
+    assert a["media"].tobytes() == b["media"].tobytes() and np.array_equal(a["density"], b["density"])
