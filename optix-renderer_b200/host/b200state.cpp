@@ -40,6 +40,11 @@ bool B200State::preRender(const Scene &scene, uint64_t seed, uint32_t poolPaths,
                           (uint32_t) m_flat.bvh_indices.size(), m_flat.bvh_indices.data() };
     nb_render_params p = m_flat.render;
     p.seed = seed; p.pool_paths = poolPaths; p.layers = layers;
+    if (m_boxFilter) {
+        p.filter_radius = 0.5f;
+        for (int i = 0; i < NB_FILTER_RESOLUTION; ++i) p.filter_table[i] = 1.f;
+        p.filter_table[NB_FILTER_RESOLUTION] = 0.f;
+    }
     for (nb_ctx *c : m_all) {                        /* the scene is replicated per GPU */
         int rc = nb_upload_scene(c, &d);
         if (rc == NB_E_UNSUPPORTED) { m_why = nb_last_error(c); return false; }

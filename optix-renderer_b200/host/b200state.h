@@ -21,6 +21,9 @@ public:
      * milliseconds, no host build at all), NB_BVH_DEVICE (linear BVH), or NB_BVH_IMPORT (the reference's own tree from the
      * host builder — what the bit-parity mode of the traversal needs). NB_BVH_BUILDER=host|lbvh|sah overrides. */
     void setTreeBuilder(int mode) { m_treeMode = mode; }
+    /* every filter weight 1 over the pixel's own square: a pixel of the film is then the plain mean of its samples
+     * (what the t-test harness averages, src/utils/ttest.cpp:205-222) */
+    void setBoxFilter(bool on) { m_boxFilter = on; }
     /* OptixState::renderSubframe (OptixState.cpp:485-510) */
     void renderSubframe(uint32_t currentSample, uint32_t samplesPerLaunch, uint32_t stride = 1, uint32_t offset = 0);
     /* one round of the sample loop for an `adaptive` sampler (render.cpp:283-360 with :323-335 inside): the blocks' variance
@@ -41,6 +44,7 @@ private:
     FlatScene m_flat;
     std::string m_why;
     int m_treeMode = NB_BVH_DEVICE_SAH;
+    bool m_boxFilter = false;
 };
 
 } // namespace nori

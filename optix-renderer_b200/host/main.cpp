@@ -91,9 +91,11 @@ static void writeImage(const std::string &path, const float *data, size_t h, siz
     else writeNpy(path, data, h, w, 3);
 }
 
+namespace nori { bool runTTest(NoriObject *root, int device); }
+
 int main(int argc, char **argv) {
-    if (argc < 3) {
-        fprintf(stderr, "usage: nori_b200 scene.xml out.{npy,pfm,png} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs] [adaptive_cap=N] [bvh=sah|lbvh|host]\n");
+    if (argc < 2 || (argc < 3 && !(argc == 2 && strstr(argv[1], ".xml")))) {
+        fprintf(stderr, "usage: nori_b200 test.xml | nori_b200 scene.xml out.{npy,pfm,png} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs] [adaptive_cap=N] [bvh=sah|lbvh|host]\n");
         return 2;
     }
     try {
@@ -101,7 +103,7 @@ int main(int argc, char **argv) {
         uint64_t seed = 0;
         std::string flatOut;
         std::vector<int> devices;
-        for (int i = 3; i < argc; ++i) {
+        for (int i = (argc > 2 && strchr(argv[2], '=')) ? 2 : 3; i < argc; ++i) {      /* a test file takes no output path */
             if (!strncmp(argv[i], "spp=", 4)) spp = atoi(argv[i] + 4);
             else if (!strncmp(argv[i], "device=", 7)) device = atoi(argv[i] + 7);
             else if (!strncmp(argv[i], "devices=", 8)) {
@@ -126,7 +128,11 @@ int main(int argc, char **argv) {
         }
         auto t0 = std::chrono::steady_clock::now();
         std::unique_ptr<NoriObject> root(loadFromXML(argv[1]));
+        if (root->getClassType() == NoriObject::ETest) {              /* <test type="ttest">: the reference's known-answer harness, on the GPU */
+            return runTTest(root.get(), devices.empty() ? device : devices[0]) ? 0 : 1;
+        }
         if (root->getClassType() != NoriObject::EScene) throw NoriException("root of %s is not a scene", argv[1]);
+        if (argc < 3) throw NoriException("no output file given for the scene %s", argv[1]);
         Scene *scene = static_cast<Scene *>(root.get());
         if (devices.empty()) devices.push_back(device);
         B200State state(devices);

@@ -90,7 +90,9 @@ private:
             const char q = s[p++];
             size_t e = s.find(q, p);
             if (e == std::string::npos) fail("unterminated attribute value");
-            n.attrs.emplace_back(an, unescape(s.substr(p, e - p)));
+            std::string value = unescape(s.substr(p, e - p));
+            for (char &c : value) if (c == '\t' || c == '\n' || c == '\r') c = ' ';      /* attribute-value normalisation (XML 1.0, 3.3.3; pugixml's parse_wconv_attribute) */
+            n.attrs.emplace_back(an, value);
             p = e + 1;
         }
         for (;;) {                        /* content: child elements; text is ignored as pugixml's node iteration does */

@@ -181,11 +181,12 @@ def test_obj_reader_grammar(nb, built_lib, tmp_path):
 def test_every_scene_of_the_reference_is_accounted_for(nb, built_lib):
     """All 79 scene files under the reference's scenes/: they flatten for the GPU, or they cannot run in the reference either
     (assets it does not ship, classes it does not have, a tag its parser rejects), or they are what SURVEY 8 leaves on the CPU
-    (the photon mapper, the ttest / chi2test harness objects — run here by tests/test_ttest_gpu.py instead)."""
+    (the photon mapper) — or they are <test type="ttest" / "chi2test"> files, which parse here and run through
+    `nori_b200 test.xml` (host/ttest.cpp; tests/test_ttest_gpu.py)."""
     import glob
     files = sorted(glob.glob("/root/reference/scenes/**/*.xml", recursive=True))
     assert len(files) >= 79
-    expected = {"Unable to open OBJ file": "mesh not shipped", "image file not found": "texture not shipped", 'class "ttest"': "harness",
+    expected = {"Unable to open OBJ file": "mesh not shipped", "image file not found": "texture not shipped", "root element is not a <scene>": "harness",
                 'class "chi2test"': "harness", "PhotonMapper": "photon mapper", ".hdr": "no .hdr loader in the reference build, file not shipped",
                 'class "envmaptester"': "no such class in the reference", 'unexpected tag "envmap"': "the reference's parser rejects it too"}
     loaded, why = 0, {}

@@ -84,3 +84,20 @@ def test_reference_known_answers(nb, ctx, tmp_path, rel, strategy):
         if not ok:
             failures.append((integ, ref, mean, p))
     assert not failures, failures
+
+
+@pytest.mark.parametrize("rel", ["pa3/test-mesh.xml", "pa3/test-mesh-furnace.xml", "pa4/test-direct.xml", "pa4/test-furnace.xml", "pa1/test-direct.xml",
+                                 "pa3/ttest-microfacet.xml", "pa3/chi2test-microfacet.xml"])
+def test_reference_test_files_run_through_the_cli(nb, rel):
+    """`nori_b200 test.xml`: the reference's own <test type="ttest"> and <test type="chi2test"> files, unchanged, through the
+    native harness (host/ttest.cpp = src/utils/ttest.cpp:60-268 and chi2test.cpp:44-250 driven by the GPU backend): every case
+    accepted, exit code 0."""
+    import re
+    import subprocess
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nori_b200")
+    r = subprocess.run([cli, golden("scenes/ttests/" + rel)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=900)
+    tail = r.stdout.strip().splitlines()[-1] if r.stdout.strip() else r.stderr[-500:]
+    m = re.match(r"Passed (\d+)/(\d+) tests\.", tail)
+    print(rel, tail, "| rejected:", r.stdout.count("***** Rejected"))
+    assert m, (tail, r.stderr[-800:])
+    assert m.group(1) == m.group(2) and int(m.group(2)) >= 1 and r.returncode == 0, r.stdout[-3000:]
