@@ -509,6 +509,7 @@ def load_host_library():
         _host.nbh_vdb_to_nbv.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p]
         _host.nbh_to_nvdb.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
         _host.nbh_nvdb_write_leaves.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float]
+        _host.nbh_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
         _host.nbh_inflate.restype = C.c_longlong
         _host.nbh_inflate.argtypes = [C.c_char_p, C.c_uint64, C.c_void_p, C.c_uint64]
     return _host

@@ -144,6 +144,12 @@ extern "C" int nbh_nvdb_write_leaves(const char *nvdb_path, const char *grid, ui
     } catch (const std::exception &e) { g_error = e.what(); return -1; }
 }
 
+/* png.h, for the tests: the image writer of nori_b200 out.png */
+#include "png.h"
+extern "C" int nbh_write_png(const char *path, const float *rgb, uint32_t h, uint32_t w) {
+    try { nori::writePng(path, rgb, h, w); return 0; } catch (const std::exception &e) { g_error = e.what(); return -1; }
+}
+
 /* codecs.h, for the tests: zlib stream -> bytes. Returns the decoded size or -1. */
 #include "codecs.h"
 extern "C" long long nbh_inflate(const uint8_t *src, uint64_t n, uint8_t *dst, uint64_t capacity) {

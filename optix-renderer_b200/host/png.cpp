@@ -4,6 +4,9 @@
  * high byte, grey samples below 8 bits are scaled to 0..255). CRCs are not verified. */
 #include "png.h"
 #include "codecs.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <fstream>
 
@@ -135,4 +138,58 @@ void decodePng(const std::string &path, std::vector<uint8_t> &rgba, unsigned &wi
     }
 }
 
+
+/* Bitmap::saveToLDR (src/utils/bitmap.cpp:109-140): sRGB transfer, x 255 + 0.5, clamped, 8-bit RGB — written as a PNG whose
+ * zlib stream uses stored blocks (no compressor on this side; every PNG reader takes them) */
+static uint32_t crc32Of(const uint8_t *p, size_t n, uint32_t crc = 0) {
+    static uint32_t table[256];
+    static bool ready = false;
+    if (!ready) { for (uint32_t i = 0; i < 256; ++i) { uint32_t c = i; for (int k = 0; k < 8; ++k) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1; table[i] = c; } ready = true; }
+    crc = ~crc;
+    for (size_t i = 0; i < n; ++i) crc = table[(crc ^ p[i]) & 0xffu] ^ (crc >> 8);
+    return ~crc;
 }
+void writePng(const std::string &path, const float *data, size_t h, size_t w) {
+    std::vector<uint8_t> raw;
+    raw.reserve(h * (1 + 3 * w));
+    for (size_t y = 0; y < h; ++y) {
+        raw.push_back(0);                                                   /* filter type: none */
+        for (size_t i = 0; i < 3 * w; ++i) {
+            const float v = data[y * 3 * w + i];
+            const float g = v <= 0.0031308f ? 12.92f * v : 1.055f * std::pow(v, 1.f / 2.4f) - 0.055f;
+            const float b = 255.f * g + 0.5f;
+            raw.push_back((uint8_t) (b < 0.f ? 0.f : b > 255.f ? 255.f : b));
+        }
+    }
+    std::vector<uint8_t> z = { 0x78, 0x01 };                                /* zlib header, then stored deflate blocks of <= 65535 bytes */
+    uint32_t a = 1, b = 0;
+    for (size_t at = 0; at < raw.size() || at == 0; at += 65535) {
+        const size_t n = std::min<size_t>(65535, raw.size() - at);
+        z.push_back(at + n >= raw.size() ? 1 : 0);
+        z.push_back((uint8_t) (n & 0xff)); z.push_back((uint8_t) (n >> 8)); z.push_back((uint8_t) (~n & 0xff)); z.push_back((uint8_t) ((~n >> 8) & 0xff));
+        z.insert(z.end(), raw.begin() + at, raw.begin() + at + n);
+        if (at + n >= raw.size()) break;
+    }
+    for (uint8_t c : raw) { a = (a + c) % 65521u; b = (b + a) % 65521u; }    /* Adler-32 */
+    const uint32_t adler = (b << 16) | a;
+    for (int k = 3; k >= 0; --k) z.push_back((uint8_t) (adler >> (8 * k)));
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) throw NoriException("cannot write %s", path);
+    auto chunk = [&](const char *type, const std::vector<uint8_t> &body) {
+        std::vector<uint8_t> c(type, type + 4);
+        c.insert(c.end(), body.begin(), body.end());
+        const uint32_t n = (uint32_t) body.size(), crc = crc32Of(c.data(), c.size());
+        const uint8_t len[4] = { (uint8_t) (n >> 24), (uint8_t) (n >> 16), (uint8_t) (n >> 8), (uint8_t) n };
+        const uint8_t tail[4] = { (uint8_t) (crc >> 24), (uint8_t) (crc >> 16), (uint8_t) (crc >> 8), (uint8_t) crc };
+        fwrite(len, 1, 4, f); fwrite(c.data(), 1, c.size(), f); fwrite(tail, 1, 4, f);
+    };
+    const uint8_t sig[8] = { 0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a };
+    fwrite(sig, 1, 8, f);
+    std::vector<uint8_t> ihdr = { (uint8_t) (w >> 24), (uint8_t) (w >> 16), (uint8_t) (w >> 8), (uint8_t) w,
+                                  (uint8_t) (h >> 24), (uint8_t) (h >> 16), (uint8_t) (h >> 8), (uint8_t) h, 8, 2, 0, 0, 0 };
+    chunk("IHDR", ihdr); chunk("IDAT", z); chunk("IEND", {});
+    if (fclose(f) != 0) throw NoriException("cannot write %s", path);
+}
+
+
+} // namespace nori

@@ -200,3 +200,20 @@ def test_every_scene_of_the_reference_is_accounted_for(nb, built_lib):
             why[reason[0]] = why.get(reason[0], 0) + 1
     print(loaded, "of", len(files), "flatten;", why)
     assert loaded >= 59
+
+
+def test_png_writer_is_save_to_ldr(nb, built_lib, tmp_path):
+    """host/png.cpp::writePng = Bitmap::saveToLDR (src/utils/bitmap.cpp:109-140): sRGB transfer, x 255 + 0.5, clamp, 8-bit RGB;
+    decoded by PIL (the zlib stream is stored deflate blocks, several of them)."""
+    from PIL import Image
+    rng = np.random.default_rng(4)
+    img = np.concatenate([rng.random((150, 200, 3), dtype=np.float32) * 1.5 - 0.1, np.zeros((3, 200, 3), np.float32)])
+    img[0, 0] = [0.0031308, 0.0031309, 1.0]
+    h = nb.load_host_library()
+    assert h.nbh_write_png(os.fsencode(str(tmp_path / "a.png")), img.ctypes.data_as(__import__("ctypes").c_void_p), img.shape[0], img.shape[1]) == 0
+    got = np.asarray(Image.open(tmp_path / "a.png"))
+    g = np.where(img <= np.float32(0.0031308), np.float32(12.92) * img, np.float32(1.055) * np.power(np.maximum(img, 0), np.float32(1 / 2.4), dtype=np.float32) - np.float32(0.055))
+    want = np.clip(np.float32(255.0) * g + np.float32(0.5), 0, 255).astype(np.uint8)
+    assert got.shape == want.shape and got.dtype == np.uint8
+    assert np.abs(got.astype(int) - want.astype(int)).max() <= 1 and (got != want).mean() < 1e-3      # powf rounding at a byte boundary
+    assert os.path.getsize(tmp_path / "a.png") > 65535                                              # more than one stored block
