@@ -510,6 +510,8 @@ def load_host_library():
         _host.nbh_to_nvdb.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
         _host.nbh_nvdb_write_leaves.argtypes = [C.c_char_p, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float]
         _host.nbh_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        _host.nbh_student_t_two_sided_p.restype = C.c_double; _host.nbh_student_t_two_sided_p.argtypes = [C.c_double, C.c_double]
+        _host.nbh_chi2_upper_p.restype = C.c_double; _host.nbh_chi2_upper_p.argtypes = [C.c_double, C.c_double]
         _host.nbh_inflate.restype = C.c_longlong
         _host.nbh_inflate.argtypes = [C.c_char_p, C.c_uint64, C.c_void_p, C.c_uint64]
     return _host

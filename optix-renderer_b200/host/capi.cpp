@@ -144,6 +144,11 @@ extern "C" int nbh_nvdb_write_leaves(const char *nvdb_path, const char *grid, ui
     } catch (const std::exception &e) { g_error = e.what(); return -1; }
 }
 
+/* ttest.cpp, for the tests: the tail probabilities the t-test / chi^2 harness decides with */
+namespace nori { double studentTwoSidedP(double t, double dof); double chi2UpperP(double chsq, double dof); }
+extern "C" double nbh_student_t_two_sided_p(double t, double dof) { return nori::studentTwoSidedP(t, dof); }
+extern "C" double nbh_chi2_upper_p(double chsq, double dof) { return nori::chi2UpperP(chsq, dof); }
+
 /* png.h, for the tests: the image writer of nori_b200 out.png */
 #include "png.h"
 extern "C" int nbh_write_png(const char *path, const float *rgb, uint32_t h, uint32_t w) {

@@ -217,3 +217,18 @@ def test_png_writer_is_save_to_ldr(nb, built_lib, tmp_path):
     assert got.shape == want.shape and got.dtype == np.uint8
     assert np.abs(got.astype(int) - want.astype(int)).max() <= 1 and (got != want).mean() < 1e-3      # powf rounding at a byte boundary
     assert os.path.getsize(tmp_path / "a.png") > 65535                                              # more than one stored block
+
+
+def test_harness_tail_probabilities_against_scipy(nb, built_lib):
+    """host/ttest.cpp decides with its own incomplete beta / gamma functions (the reference: ext/hypothesis): checked against
+    scipy over the ranges the harness meets — 23 and 99 999 degrees of freedom for t, 6 .. 199 for chi^2."""
+    from scipy import stats
+    h = nb.load_host_library()
+    for dof in (1, 5, 23, 100, 99999):
+        for t in (0.0, 0.3, 1.0, 2.5, 4.0, 8.0, 30.0):
+            got, want = h.nbh_student_t_two_sided_p(t, dof), 2.0 * stats.t.sf(t, dof)
+            assert abs(got - want) <= 1e-10 + 1e-8 * want, (dof, t, got, want)
+    for dof in (1, 6, 27, 99, 199):
+        for x in (0.5, 5.0, 20.0, 90.0, 130.0, 400.0):
+            got, want = h.nbh_chi2_upper_p(x, dof), stats.chi2.sf(x, dof)
+            assert abs(got - want) <= 1e-12 + 1e-8 * want, (dof, x, got, want)
