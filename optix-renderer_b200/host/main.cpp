@@ -4,6 +4,8 @@
  * float32) or .pfm — the reference's EXR writer needs OpenEXR, which this build does not carry. */
 #include "b200state.h"
 #include <chrono>
+#include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <memory>
 
@@ -22,6 +24,27 @@ static void writeNpy(const std::string &path, const float *data, size_t h, size_
     fwrite(hdr.data(), 1, hdr.size(), f);
     fwrite(data, 4, h * w * c, f);
     fclose(f);
+}
+
+/* the accumulator file of checkpoint= / resume=: a 3-d '<f4' array in C order, as writeNpy makes it */
+static std::vector<float> readNpy(const std::string &path, size_t shape[3]) {
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) throw NoriException("cannot open %s", path);
+    unsigned char head[10];
+    if (fread(head, 1, 10, f) != 10 || memcmp(head, "\x93NUMPY", 6) != 0 || head[6] != 1) { fclose(f); throw NoriException("%s: not a version-1 .npy file", path); }
+    const size_t hl = head[8] | ((size_t) head[9] << 8);
+    std::string hdr(hl, ' ');
+    if (fread(&hdr[0], 1, hl, f) != hl) { fclose(f); throw NoriException("%s: truncated", path); }
+    if (hdr.find("'<f4'") == std::string::npos || hdr.find("False") == std::string::npos) { fclose(f); throw NoriException("%s: expected a C-ordered float32 array", path); }
+    const size_t a = hdr.find("'shape': ("), b = hdr.find(')', a);
+    unsigned long long d[3] = { 0, 0, 0 };
+    if (a == std::string::npos || b == std::string::npos || sscanf(hdr.c_str() + a + 10, "%llu, %llu, %llu", &d[0], &d[1], &d[2]) != 3) { fclose(f); throw NoriException("%s: expected a 3-d array", path); }
+    for (int k = 0; k < 3; ++k) shape[k] = (size_t) d[k];
+    std::vector<float> data(shape[0] * shape[1] * shape[2]);
+    const bool ok = fread(data.data(), 4, data.size(), f) == data.size();
+    fclose(f);
+    if (!ok) throw NoriException("%s: truncated", path);
+    return data;
 }
 
 static void writePfm(const std::string &path, const float *data, size_t h, size_t w) {
@@ -46,13 +69,14 @@ namespace nori { bool runTTest(NoriObject *root, int device); }
 
 int main(int argc, char **argv) {
     if (argc < 2 || (argc < 3 && !(argc == 2 && strstr(argv[1], ".xml")))) {
-        fprintf(stderr, "usage: nori_b200 test.xml | nori_b200 scene.xml out.{npy,pfm,png} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs] [adaptive_cap=N] [bvh=sah|lbvh|host]\n");
+        fprintf(stderr, "usage: nori_b200 test.xml | nori_b200 scene.xml out.{npy,pfm,png} [spp=N] [device=D | devices=0,1,...] [seed=S] [launch=N] [snapshot=K] [flat=scene.nbs] [adaptive_cap=N] [bvh=sah|lbvh|host] [checkpoint=film.npy] [resume=film.npy first=K]\n");
         return 2;
     }
     try {
         int spp = -1, device = 0, launch = 0, snapshot = 0, adaptiveCap = 0, treeMode = NB_BVH_DEVICE_SAH;   /* adaptive_cap: AdaptiveSampler's 1000-decision limit (black blocks reach it) */
         uint64_t seed = 0;
-        std::string flatOut;
+        std::string flatOut, checkpointPath, resumePath;     /* checkpoint=: also write the film's accumulators; resume=: add a film written that way */
+        int firstSample = 0;                                  /* first=K: the samples [K, spp) — what a resumed render still has to draw */
         std::vector<int> devices;
         for (int i = (argc > 2 && strchr(argv[2], '=')) ? 2 : 3; i < argc; ++i) {      /* a test file takes no output path */
             if (!strncmp(argv[i], "spp=", 4)) spp = atoi(argv[i] + 4);
@@ -71,6 +95,9 @@ int main(int argc, char **argv) {
             else if (!strncmp(argv[i], "snapshot=", 9)) snapshot = atoi(argv[i] + 9);
             else if (!strncmp(argv[i], "flat=", 5)) flatOut = argv[i] + 5;
             else if (!strncmp(argv[i], "adaptive_cap=", 13)) adaptiveCap = atoi(argv[i] + 13);
+            else if (!strncmp(argv[i], "checkpoint=", 11)) checkpointPath = argv[i] + 11;
+            else if (!strncmp(argv[i], "resume=", 7)) resumePath = argv[i] + 7;
+            else if (!strncmp(argv[i], "first=", 6)) firstSample = atoi(argv[i] + 6);
             else if (!strncmp(argv[i], "bvh=", 4)) {
                 const std::string b(argv[i] + 4);
                 if (b == "host") treeMode = NB_BVH_IMPORT; else if (b == "lbvh") treeMode = NB_BVH_DEVICE; else if (b == "sah") treeMode = NB_BVH_DEVICE_SAH;
@@ -106,7 +133,8 @@ int main(int argc, char **argv) {
         const bool adaptive = scene->getSampler()->isAdaptive();
         if (adaptive) launch = 1;                                   /* one round of the sample loop per call */
         uint64_t adaptivePasses = 0;
-        for (int s = 0; s < spp; s += launch) {
+        if (firstSample < 0 || firstSample > spp) throw NoriException("first=%d outside 0..%d", firstSample, spp);
+        for (int s = firstSample; s < spp; s += launch) {
             const int n = std::min(launch, spp - s);
             if (adaptive) adaptivePasses += state.renderAdaptiveRound(4, (uint32_t) scene->getSampler()->getInitialUniform(), (uint32_t) std::max(0, adaptiveCap)).block_passes;   /* block.h:31 */
             else state.renderSubframe((uint32_t) s, (uint32_t) n);
@@ -122,7 +150,31 @@ int main(int argc, char **argv) {
         double render_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
         std::vector<float> img;
         uint32_t h = 0, w = 0;
-        state.download(img, true, &h, &w);
+        if (checkpointPath.empty() && resumePath.empty()) state.download(img, true, &h, &w);
+        else {
+            /* checkpoint / resume (the reference can only interrupt a render, render.cpp:285; SURVEY 5 notes that the film is
+             * linear): the accumulators (sum w rgb, sum w) in ImageBlock layout ARE the state of a render, and sample s of
+             * pixel p has its own random stream, so samples [0, K) saved + samples [K, n) drawn later = one render of n */
+            std::vector<float> film;
+            uint32_t rows = 0, cols = 0;
+            state.download(film, false, &rows, &cols);
+            if (!resumePath.empty()) {
+                size_t shape[3];
+                const std::vector<float> saved = readNpy(resumePath, shape);
+                if (shape[0] != rows || shape[1] != cols || shape[2] != 4) throw NoriException("%s: a %zux%zux%zu film, this render's is %ux%ux4", resumePath, shape[0], shape[1], shape[2], rows, cols);
+                for (size_t k = 0; k < film.size(); ++k) film[k] += saved[k];
+            }
+            if (!checkpointPath.empty()) writeNpy(checkpointPath, film.data(), rows, cols, 4);
+            std::vector<float> plain;                                /* ImageBlock::toBitmap: crop the border, divide by the weight */
+            state.download(plain, true, &h, &w);
+            const uint32_t border = (rows - h) / 2;
+            img.assign((size_t) h * w * 3, 0.f);
+            for (uint32_t y = 0; y < h; ++y)
+                for (uint32_t x = 0; x < w; ++x) {
+                    const float *a = film.data() + ((size_t) (y + border) * cols + x + border) * 4;
+                    if (std::fabs(a[3]) > 1e-4f) for (int k = 0; k < 3; ++k) img[((size_t) y * w + x) * 3 + k] = a[k] / a[3];
+                }
+        }
         writeImage(outPath, img.data(), h, w);
         nb_counters c = state.counters();
         printf("{\"scene\": \"%s\", \"width\": %u, \"height\": %u, \"spp\": %d, \"load_seconds\": %.3f, \"seconds\": %.6f, "

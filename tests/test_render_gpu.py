@@ -189,3 +189,30 @@ def test_cli_writes_png_like_save_to_ldr(nb, tmp_path):
     assert png.shape == want.shape
     assert np.abs(png - want).max() <= 1              # the two runs sum their film in different orders: a byte may round the other way
     assert (png != want).mean() < 0.01
+
+
+def test_cli_checkpoint_and_resume(nb, tmp_path):
+    """The film's accumulators are the whole state of a render (they are linear, and sample s of pixel p has its own random
+    stream): 24 samples saved with checkpoint=, the other 40 drawn later with resume= first=24, give the image of one
+    64-sample render."""
+    import json
+    import os
+    import subprocess
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nori_b200")
+    xml = golden("scenes/cbox/cbox_path_mis_small.xml")
+
+    def run(out, *opts):
+        r = subprocess.run([cli, xml, str(tmp_path / out), "seed=21"] + list(opts), stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        assert r.returncode == 0, r.stderr
+        return json.loads(r.stdout.strip().splitlines()[-1])
+
+    whole = run("whole.npy", "spp=64")
+    part = run("part.npy", "spp=24", "checkpoint=" + str(tmp_path / "film.npy"))
+    rest = run("resumed.npy", "spp=64", "first=24", "resume=" + str(tmp_path / "film.npy"), "checkpoint=" + str(tmp_path / "film2.npy"))
+    assert whole["samples"] == 200 * 150 * 64 and part["samples"] == 200 * 150 * 24 and rest["samples"] == 200 * 150 * 40
+    a, b = np.load(tmp_path / "whole.npy"), np.load(tmp_path / "resumed.npy")
+    assert np.abs(a - b).max() <= 1e-4 * max(1.0, np.abs(a).max())          # same samples, summed in two parts
+    film, film2 = np.load(tmp_path / "film.npy"), np.load(tmp_path / "film2.npy")
+    assert film.shape == film2.shape == (150 + 4, 200 + 4, 4)                # ImageBlock layout: gaussian filter, border 2
+    np.testing.assert_allclose(film2[2:-2, 2:-2, 3].sum() / film[2:-2, 2:-2, 3].sum(), 64 / 24, rtol=2e-3)
+    assert rel_rmse(np.load(tmp_path / "part.npy"), np.load(golden("cbox_ref_256spp.npy"))) > rel_rmse(b, np.load(golden("cbox_ref_256spp.npy")))
