@@ -222,3 +222,32 @@ def test_linear_density_ramp_closed_form(nb, ctx):
     assert T.min() < 0.9 and T.max() > 0.95
     assert np.all(np.abs(got[:, 3] - T) <= se)           # ratio tracking: unbiased estimate of exp(-tau), variance below Bernoulli's
     assert np.all(np.abs(got[:, 1] - (1 - T)) <= se)     # delta tracking: collision before maxt with probability 1 - exp(-tau)
+
+
+def test_a_1024_cubed_sparse_grid_on_the_device(nb, ctx, tmp_path):
+    """Three 8^3 blocks in a 1024^3 box (4.3 GB dense): 8.6 MB of table + a few bricks on the device. At a voxel's own position
+    the triquadratic stencil returns the voxel (weights 0, 1, 0 per axis), far from the blocks it returns the background."""
+    import shutil
+    rng = np.random.default_rng(3)
+    org = np.array([[0, 0, 0], [504, 512, 520], [1016, 1016, 1016]], "<i4")
+    vals = (rng.random((3, 8, 8, 8), dtype=np.float32) + 0.5).astype("<f4")
+    M = np.array([[0.7 / 1024, 0, 0, 0.08], [0, 1.04 / 1024, 0, 0.02], [0, 0, 0.7 / 1024, -0.05]])
+    shutil.copytree(golden("scenes/vol/meshes"), tmp_path / "meshes")
+    nb.nvdb_write_leaves(str(tmp_path / "big.nvdb"), org, vals, M)
+    (tmp_path / "scene.xml").write_text(open(golden("scenes/vol/cbox_sparse_small.xml")).read().replace("sparse_smoke.nvdb", "big.nvdb"))
+    s = nb.load_xml(str(tmp_path / "scene.xml"))
+    assert s["media"][0]["type"] == nb.MEDIUM_HETEROGENEOUS_BRICKS and list(s["media"][0]["grid_dims"]) == [1028] * 3 and s["density"].size < 3 * 10 ** 6
+    ctx.load(s)
+    pts, want = [], []
+    for o, v in zip(org, vals):
+        for ijk in ((1, 2, 3), (4, 4, 4), (6, 1, 5)):
+            pts.append(M[:, :3] @ (o + np.array(ijk, np.float64)) + M[:, 3]); want.append(v[ijk])
+    pts.append(M[:, :3] @ np.array([300.0, 300.0, 300.0]) + M[:, 3]); want.append(0.0)
+    rays = np.concatenate([np.array(pts), np.tile([0.0, 0.0, 1.0], (len(pts), 1)), np.full((len(pts), 1), 1e-4), np.full((len(pts), 1), 0.01)], axis=1).astype("<f4")
+    got = ctx.medium_probe(0, rays, samples=16, seed=1)
+    # the voxel positions go through fp32 world coordinates and the fp32 world -> grid map: at 1024 voxels across 0.7 units a
+    # position is good to ~1e-4 voxels, the stencil's neighbours (values 0.5 .. 1.5) weigh in with that much
+    np.testing.assert_allclose(got[:, 0], np.array(want, np.float32), atol=2e-3)
+    ctx.render_begin(nb.make_render_params(s, seed=1))
+    ctx.render_subframe(0, 8)
+    assert np.isfinite(ctx.film_download(normalize=True)).all()
