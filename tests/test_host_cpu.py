@@ -232,3 +232,20 @@ def test_harness_tail_probabilities_against_scipy(nb, built_lib):
         for x in (0.5, 5.0, 20.0, 90.0, 130.0, 400.0):
             got, want = h.nbh_chi2_upper_p(x, dof), stats.chi2.sf(x, dof)
             assert abs(got - want) <= 1e-12 + 1e-8 * want, (dof, x, got, want)
+
+
+def test_xml_attribute_whitespace_is_normalised(nb, built_lib, tmp_path):
+    """Tabs and line breaks inside an attribute value read as blanks (XML 1.0, 3.3.3; pugixml's default in the reference): the
+    reference's own test files wrap their `references` lists over several lines."""
+    import ctypes as C
+    h = nb.load_host_library()
+    xml = """<scene><integrator type="normals"/>
+<camera type="perspective"><integer name="width" value="4"/><integer name="height"
+   value="4"/><transform name="toWorld"><lookat target="0,\n\t0, 1" origin="0,0,\r\n0" up="0,\t1,0"/></transform></camera>
+<shape type="sphere"><point name="center" value="0,\n 0,\t5"/><float name="radius" value="1"/><bsdf type="diffuse"/></shape></scene>"""
+    (tmp_path / "s.xml").write_text(xml, newline="")
+    s = nb.load_xml(str(tmp_path / "s.xml"))
+    assert np.allclose(s["shapes"]["center"][0], [0, 0, 5])
+    buf = C.create_string_buffer(1 << 16)
+    assert h.nbh_parse_xml(os.fsencode(golden("scenes/ttests/pa3/test-mesh-furnace.xml")), buf, len(buf)) == 0, h.nbh_last_error()
+    assert b"StudentsTTest" in buf.value
