@@ -55,3 +55,22 @@ def test_nbs_roundtrip(nb, tmp_path):
     assert set(s) == set(t)
     for k in s:
         assert s[k].tobytes() == t[k].tobytes(), k
+
+
+def test_cli_fails_loudly_without_a_gpu(nb, built_lib):
+    """nori_b200 on a machine without a GPU: an error that says so and a non-zero exit code, for scenes and for the
+    reference's <test> files alike — no CPU path is taken."""
+    import subprocess
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present")
+    except ImportError:
+        pass
+    cli = os.path.join(os.path.dirname(nb.LIB_PATH), "nori_b200")
+    golden = os.path.join(ROOT, "tests", "golden", "scenes")
+    for args in ([os.path.join(golden, "cbox", "cbox_path_mis_small.xml"), "/tmp/never_written.npy", "spp=1"],
+                 [os.path.join(golden, "ttests", "pa3", "ttest-microfacet.xml")]):
+        r = subprocess.run([cli] + args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        assert r.returncode == 1 and "no CPU fallback" in r.stderr, (r.returncode, r.stderr[-300:])
+    assert subprocess.run([cli], stdout=subprocess.PIPE, stderr=subprocess.PIPE).returncode == 2
